@@ -1,0 +1,150 @@
+// Index handle: reads the files `bwa index` writes and keeps the FM-index image, sampled SA and packed reference
+// resident in HBM.  Replaces bwa_idx_load / bwt_restore_bwt / bwt_restore_sa / bns_restore
+// (bwa/bwa.c:262-294, bwa/bwt.c:421-462, bwa/bntseq.c:98-196).
+#pragma once
+#include <cuda_runtime.h>
+#include <string>
+#include <vector>
+#include <cstdio>
+#include <cstring>
+#include "fmindex.cuh"
+#include "../../include/arachne_cuda.h"
+
+namespace arachne {
+void set_error(const char* fmt, ...);
+}
+
+struct arachne_index {
+    int device = 0;
+    arachne::FMIndex fm{};   // device pointers
+    arachne::RefView ref{};  // device pointers
+    void *d_bwt = nullptr, *d_sa = nullptr, *d_pac = nullptr, *d_contigs = nullptr;
+    size_t device_bytes = 0;
+    std::vector<arachne::Contig> contigs;
+    std::vector<std::string> names;
+    int64_t l_pac = 0;
+    // host copy of the packed reference (GetSeq-style host queries, compat shims)
+    std::vector<uint8_t> h_pac;
+};
+
+namespace arachne {
+
+#define AR_CUDA(x)                                                                         \
+    do {                                                                                   \
+        cudaError_t e_ = (x);                                                              \
+        if (e_ != cudaSuccess) {                                                           \
+            set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #x, cudaGetErrorString(e_)); \
+            return ARACHNE_ERR_CUDA;                                                       \
+        }                                                                                  \
+    } while (0)
+
+inline bool read_file(const std::string& path, std::vector<uint8_t>& out) {
+    FILE* fp = fopen(path.c_str(), "rb");
+    if (!fp) return false;
+    fseek(fp, 0, SEEK_END);
+    long n = ftell(fp);
+    fseek(fp, 0, SEEK_SET);
+    out.resize(n);
+    size_t got = n ? fread(out.data(), 1, n, fp) : 0;
+    fclose(fp);
+    return got == (size_t)n;
+}
+
+inline int index_load(const char* prefix_, int device, arachne_index** out) {
+    if (!prefix_ || !out) { set_error("arachne_index_load: null argument"); return ARACHNE_ERR_ARG; }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        set_error("arachne_index_load: no CUDA device (this library has no CPU path)");
+        return ARACHNE_ERR_CUDA;
+    }
+    if (device < 0 || device >= ndev) { set_error("arachne_index_load: device %d out of range (%d present)", device, ndev); return ARACHNE_ERR_ARG; }
+    std::string prefix(prefix_);
+    {   // bwa_idx_infer_prefix, bwa/bwa.c:218-243
+        FILE* fp = fopen((prefix + ".64.bwt").c_str(), "rb");
+        if (fp) { fclose(fp); prefix += ".64"; }
+    }
+    std::vector<uint8_t> bwt, sa, pac;
+    if (!read_file(prefix + ".bwt", bwt) || bwt.size() < 40 + 64) { set_error("cannot read %s.bwt", prefix.c_str()); return ARACHNE_ERR_IO; }
+    if (!read_file(prefix + ".sa", sa) || sa.size() < 56) { set_error("cannot read %s.sa", prefix.c_str()); return ARACHNE_ERR_IO; }
+    if (!read_file(prefix + ".pac", pac) || pac.empty()) { set_error("cannot read %s.pac", prefix.c_str()); return ARACHNE_ERR_IO; }
+    auto* idx = new arachne_index();
+    idx->device = device;
+    const uint64_t* bh = reinterpret_cast<const uint64_t*>(bwt.data());
+    FMIndex& fm = idx->fm;
+    fm.primary = bh[0];
+    fm.L2[0] = 0;
+    for (int i = 1; i <= 4; ++i) fm.L2[i] = bh[i];
+    fm.seq_len = fm.L2[4];
+    size_t bwt_bytes = bwt.size() - 40;
+    size_t n_blocks = (fm.seq_len + 127) / 128 + 1;  // bwt_bwtupdate_core writes one trailing count block
+    if (bwt_bytes < (n_blocks - 1) * 64 + 32) { delete idx; set_error("%s.bwt is not an occ-interleaved BWT (run `bwa index`)", prefix.c_str()); return ARACHNE_ERR_IO; }
+    const uint64_t* sh = reinterpret_cast<const uint64_t*>(sa.data());
+    if (sh[0] != fm.primary || sh[6] != fm.seq_len) { delete idx; set_error("SA-BWT inconsistency in %s", prefix.c_str()); return ARACHNE_ERR_IO; }
+    fm.sa_intv = (int)sh[5];
+    fm.n_sa = (fm.seq_len + fm.sa_intv) / fm.sa_intv;
+    if (sa.size() < 56 + (fm.n_sa - 1) * 8 || (fm.sa_intv & (fm.sa_intv - 1))) { delete idx; set_error("truncated %s.sa", prefix.c_str()); return ARACHNE_ERR_IO; }
+    // .ann / .amb (text)
+    {
+        FILE* fp = fopen((prefix + ".ann").c_str(), "r");
+        if (!fp) { delete idx; set_error("cannot read %s.ann", prefix.c_str()); return ARACHNE_ERR_IO; }
+        long long lp; int ns; unsigned seed;
+        if (fscanf(fp, "%lld%d%u", &lp, &ns, &seed) != 3) { fclose(fp); delete idx; set_error("parse error in %s.ann", prefix.c_str()); return ARACHNE_ERR_IO; }
+        idx->l_pac = lp;
+        idx->contigs.resize(ns); idx->names.resize(ns);
+        char str[8192];
+        for (int i = 0; i < ns; ++i) {
+            unsigned gi; long long off; int len, nambs, c;
+            if (fscanf(fp, "%u%8191s", &gi, str) != 2) { fclose(fp); delete idx; set_error("parse error in %s.ann", prefix.c_str()); return ARACHNE_ERR_IO; }
+            idx->names[i] = str;
+            while ((c = fgetc(fp)) != '\n' && c != EOF) {}
+            if (fscanf(fp, "%lld%d%d", &off, &len, &nambs) != 3) { fclose(fp); delete idx; set_error("parse error in %s.ann", prefix.c_str()); return ARACHNE_ERR_IO; }
+            idx->contigs[i].offset = off; idx->contigs[i].len = len; idx->contigs[i].is_alt = 0;
+        }
+        fclose(fp);
+        fp = fopen((prefix + ".alt").c_str(), "r");  // bns_restore, bntseq.c:176-196: names listed in .alt are ALT contigs
+        if (fp) {
+            while (fscanf(fp, "%8191s", str) == 1) {
+                if (str[0] != '@')
+                    for (int i = 0; i < ns; ++i) if (idx->names[i] == str) idx->contigs[i].is_alt = 1;
+                int c; while ((c = fgetc(fp)) != '\n' && c != EOF) {}
+            }
+            fclose(fp);
+        }
+    }
+    if ((uint64_t)idx->l_pac * 2 != fm.seq_len || pac.size() < (size_t)(idx->l_pac / 4 + 1)) { delete idx; set_error("inconsistent .pac/.ann/.bwt for %s", prefix.c_str()); return ARACHNE_ERR_IO; }
+    // upload
+    cudaError_t e = cudaSetDevice(device);
+    size_t img = n_blocks * 64, sab = fm.n_sa * 8, pacb = (size_t)(idx->l_pac / 4 + 1);
+    std::vector<uint8_t> image(img, 0);
+    memcpy(image.data(), bwt.data() + 40, bwt_bytes < img ? bwt_bytes : img);
+    std::vector<uint64_t> sav(fm.n_sa);
+    sav[0] = (uint64_t)-1;
+    memcpy(sav.data() + 1, sa.data() + 56, (fm.n_sa - 1) * 8);
+    if (e == cudaSuccess) e = cudaMalloc(&idx->d_bwt, img);
+    if (e == cudaSuccess) e = cudaMalloc(&idx->d_sa, sab);
+    if (e == cudaSuccess) e = cudaMalloc(&idx->d_pac, pacb + 16);
+    if (e == cudaSuccess) e = cudaMalloc(&idx->d_contigs, sizeof(Contig) * idx->contigs.size());
+    if (e == cudaSuccess) e = cudaMemcpy(idx->d_bwt, image.data(), img, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(idx->d_sa, sav.data(), sab, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemset(idx->d_pac, 0, pacb + 16);
+    if (e == cudaSuccess) e = cudaMemcpy(idx->d_pac, pac.data(), pacb, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(idx->d_contigs, idx->contigs.data(), sizeof(Contig) * idx->contigs.size(), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+        set_error("index upload failed: %s", cudaGetErrorString(e));
+        cudaFree(idx->d_bwt); cudaFree(idx->d_sa); cudaFree(idx->d_pac); cudaFree(idx->d_contigs);
+        delete idx;
+        return ARACHNE_ERR_CUDA;
+    }
+    fm.blocks = reinterpret_cast<const OccBlock*>(idx->d_bwt);
+    fm.sa = reinterpret_cast<const uint64_t*>(idx->d_sa);
+    idx->ref.pac = reinterpret_cast<const uint8_t*>(idx->d_pac);
+    idx->ref.contigs = reinterpret_cast<const Contig*>(idx->d_contigs);
+    idx->ref.l_pac = idx->l_pac;
+    idx->ref.n_seqs = (int)idx->contigs.size();
+    idx->device_bytes = img + sab + pacb + sizeof(Contig) * idx->contigs.size();
+    idx->h_pac.assign(pac.begin(), pac.begin() + pacb);
+    *out = idx;
+    return ARACHNE_OK;
+}
+
+}  // namespace arachne

@@ -1,0 +1,681 @@
+// libarachne_cuda: kernels and batch orchestration of the candidate-alignment hot path (sm_100a).
+//
+// Stages of one batch (reads = 2 x pairs), every stage a kernel over the whole batch:
+//   k_seed    thread / read   mem_collect_intv: SMEMs + re-seeding + LAST-like seeds -> SA intervals
+//   (scan)                    seeds per read -> offsets
+//   k_expand  thread / read   one SA row per seed occurrence (bwamem.c:278-283)
+//   k_sa      thread / row    bwt_sa LF walks (geometric length), each touching one 64-byte occ line per step
+//   k_chain   thread / read   B-tree chaining, chain weights, chain filter
+//   k_extend  warp   / read   mem_chain2aln (ksw_extend2 left/right, band retry) + mem_sort_dedup_patch
+//   ...       rescue, CIGAR, placement: see rescue.cuh / cigar.cuh / place.cuh
+// The index is read-only and shared; all per-batch state lives in one device workspace that is reused.
+#include <cuda_runtime.h>
+#include <cub/device/device_scan.cuh>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+#include <algorithm>
+#include "index.cuh"
+#include "smem.cuh"
+#include "warp_ctx.cuh"
+
+namespace arachne {
+
+static thread_local char g_err[1024] = "";
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+static_assert(sizeof(MemOpt) == sizeof(arachne_mem_opt_t), "MemOpt layout");
+static_assert(sizeof(AlnReg) == sizeof(arachne_alnreg_t), "AlnReg layout");
+
+struct Counters {
+    unsigned long long occ, sa_lookups, lf_steps, ext_calls, ext_cells, glb_cells;
+    int err;       // first internal error code (negative) raised by a kernel
+    int err_read;
+};
+
+__device__ __forceinline__ void raise(Counters* c, int code, int read) {
+    if (atomicCAS(&c->err, 0, code) == 0) c->err_read = read;
+}
+
+// ------------------------------------------------------------------------------------------------ k_seed
+__global__ void __launch_bounds__(128) k_seed(FMIndex fm, MemOpt opt, const uint8_t* __restrict__ seq, const int64_t* __restrict__ off,
+                                              int n_reads, Intv* scratch, int L1, Intv* arena, unsigned long long arena_cap,
+                                              unsigned long long* arena_used, unsigned long long* intv_off, int* intv_n,
+                                              unsigned int* n_sa, Counters* cnt) {
+    const int tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
+    Intv* sc = scratch + (size_t)tid * 7 * L1;
+    Intv* out = sc + 3 * L1;
+    const int cap = 4 * L1;
+    for (int r = tid; r < n_reads; r += nth) {
+        const int len = (int)(off[r + 1] - off[r]);
+        const uint8_t* s = seq + off[r];
+        int n = 0;
+        if (len >= opt.min_seed_len) n = collect_intv(opt, fm, len, s, out, cap, sc);
+        if (n < 0) { raise(cnt, ARACHNE_ERR_OVERFLOW, r); n = 0; }
+        unsigned long long pos = 0;
+        unsigned int nsa = 0;
+        if (n > 0) {
+            pos = atomicAdd(arena_used, (unsigned long long)n);
+            if (pos + n > arena_cap) { raise(cnt, ARACHNE_ERR_OVERFLOW, r); n = 0; }
+        }
+        for (int i = 0; i < n; ++i) {
+            arena[pos + i] = out[i];
+            nsa += out[i].x2 > (uint64_t)opt.max_occ ? (unsigned)opt.max_occ : (unsigned)out[i].x2;
+        }
+        intv_off[r] = pos; intv_n[r] = n; n_sa[r] = nsa;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ k_expand / k_sa
+__global__ void k_expand(MemOpt opt, int n_reads, const Intv* __restrict__ arena, const unsigned long long* __restrict__ intv_off,
+                         const int* __restrict__ intv_n, const unsigned long long* __restrict__ sa_off, uint64_t* rows) {
+    for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < n_reads; r += gridDim.x * blockDim.x) {
+        const Intv* iv = arena + intv_off[r];
+        unsigned long long o = sa_off[r];
+        for (int i = 0; i < intv_n[r]; ++i) {
+            const Intv p = iv[i];
+            int64_t step = p.x2 > (uint64_t)opt.max_occ ? (int64_t)(p.x2 / opt.max_occ) : 1;
+            int count = 0;
+            for (int64_t k = 0; k < (int64_t)p.x2 && count < opt.max_occ; k += step, ++count) rows[o++] = p.x0 + k;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) k_sa(FMIndex fm, unsigned long long n, uint64_t* rows, Counters* cnt) {
+    unsigned long long steps = 0;
+    for (unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; i < n; i += (unsigned long long)gridDim.x * blockDim.x) {
+        uint64_t k = rows[i], sa = 0, mask = (uint64_t)fm.sa_intv - 1;
+        while (k & mask) { ++sa; k = fm_inv_psi(fm, k); }
+        rows[i] = sa + fm.sa[k / fm.sa_intv];
+        steps += sa;
+    }
+    steps = __reduce_add_sync(FULL, (unsigned)steps);  // per-thread totals stay far below 2^32 / 32
+    if ((threadIdx.x & 31) == 0 && steps) atomicAdd(&cnt->lf_steps, steps);
+}
+
+// ------------------------------------------------------------------------------------------------ k_chain
+struct ChainBufs {
+    Seed* seeds;     // [total_sa]   chaining order, linked
+    Seed* kseeds;    // [total_sa]   seeds of kept chains, contiguous per chain
+    Chain* chains;   // [total_sa]
+    BNode* nodes;    // [total_sa/4 + 4*n_reads]
+    int32_t* order;  // [total_sa]   chain ids: in-order, then sorted/filtered (kept chains first n_kept)
+    int32_t* kept;   // [total_sa]   scratch
+    int* n_chain;    // [n_reads] kept chains
+    int* n_kseed;    // [n_reads] seeds in kept chains (region capacity)
+};
+
+__global__ void __launch_bounds__(128) k_chain(MemOpt opt, RefView ref, const int64_t* __restrict__ off, int n_reads, const Intv* __restrict__ arena,
+                                               const unsigned long long* __restrict__ intv_off, const int* __restrict__ intv_n,
+                                               const unsigned long long* __restrict__ sa_off, const uint64_t* __restrict__ sa_vals,
+                                               ChainBufs b, Counters* cnt) {
+    for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < n_reads; r += gridDim.x * blockDim.x) {
+        const int len = (int)(off[r + 1] - off[r]);
+        const unsigned long long o = sa_off[r];
+        const int nsa = (int)(sa_off[r + 1] - o);
+        int nk = 0, nks = 0;
+        if (nsa > 0) {
+            Seed* seeds = b.seeds + o;
+            Chain* chains = b.chains + o;
+            int32_t* order = b.order + o;
+            BNode* nodes = b.nodes + (o / 4 + 4ull * r);
+            float fr;
+            int n = chain_seeds(opt, ref, len, arena + intv_off[r], intv_n[r], sa_vals + o, seeds, chains, nodes, nsa / 4 + 4, order, &fr);
+            if (n < 0) { raise(cnt, ARACHNE_ERR_OVERFLOW, r); n = 0; }
+            nk = chain_filter(opt, n, order, chains, seeds, b.kept + o);
+            Seed* ks = b.kseeds + o;
+            for (int i = 0; i < nk; ++i) {  // materialise the kept chains' seeds contiguously
+                Chain& c = chains[order[i]];
+                int s = c.first_seed;
+                c.first_seed = nks;
+                for (int j = 0; j < c.n; ++j, s = seeds[s].next) ks[nks++] = seeds[s];
+            }
+        }
+        b.n_chain[r] = nk; b.n_kseed[r] = nks;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ k_extend
+constexpr int EXT_WARPS = 4;
+
+__global__ void __launch_bounds__(EXT_WARPS * 32) k_extend(MemOpt opt, RefView ref, const uint8_t* __restrict__ seq, const int64_t* __restrict__ off,
+                                                           int n_reads, const unsigned long long* __restrict__ sa_off, ChainBufs b, uint64_t* srt,
+                                                           AlnReg* regs, int* n_regs, uint8_t* win, int win_cap, unsigned int* next, Counters* cnt) {
+    const int lane = threadIdx.x & 31;
+    const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    WarpCtx ctx;
+    unsigned long long cells = 0, calls = 0;
+    ctx.lane = lane; ctx.cells = &cells; ctx.z = nullptr; ctx.z_cap = 0;
+    ExtScratch sc;
+    sc.rseq = win + (size_t)gw * win_cap; sc.win_cap = win_cap;
+    for (;;) {
+        int r = 0;
+        if (lane == 0) r = (int)atomicAdd(next, 1u);
+        r = __shfl_sync(FULL, r, 0);
+        if (r >= n_reads) break;
+        const int nk = b.n_chain[r];
+        int n_av = 0;
+        if (nk > 0) {
+            const unsigned long long o = sa_off[r];
+            const int len = (int)(off[r + 1] - off[r]);
+            const uint8_t* q = seq + off[r];
+            AlnReg* av = regs + o;
+            const int cap = b.n_kseed[r];
+            sc.srt = srt + o;
+            int rc = 0;
+            for (int i = 0; i < nk && rc == 0; ++i) {
+                const Chain c = b.chains[o + b.order[o + i]];
+                rc = chain2aln(ctx, opt, ref, len, q, c, b.kseeds + o + c.first_seed, av, &n_av, cap, sc);
+            }
+            if (rc == 0) {
+                calls += n_av;
+                int m = sort_dedup_patch(ctx, opt, ref, q, n_av, av, sc.rseq, win_cap);
+                if (m < 0) rc = m; else n_av = m;
+            }
+            if (rc != 0) { if (lane == 0) raise(cnt, ARACHNE_ERR_OVERFLOW, r); n_av = 0; }
+            if (lane == 0)
+                for (int i = 0; i < n_av; ++i)  // mem_align1_core tail, bwamem.c:1078-1082
+                    if (av[i].rid >= 0 && ref.contigs[av[i].rid].is_alt) av[i].n_comp_is_alt |= 1 << 30;
+            __syncwarp();
+        }
+        if (lane == 0) n_regs[r] = n_av;
+    }
+    if (lane == 0 && (cells || calls)) { atomicAdd(&cnt->ext_cells, cells); atomicAdd(&cnt->ext_calls, calls); }
+}
+
+__global__ void k_gather_regs(int n_reads, const unsigned long long* __restrict__ sa_off, const unsigned long long* __restrict__ reg_off,
+                              const AlnReg* __restrict__ regs, AlnReg* out) {
+    const int lane = threadIdx.x & 31;
+    for (int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; r < n_reads; r += (gridDim.x * blockDim.x) >> 5) {
+        const uint32_t* src = reinterpret_cast<const uint32_t*>(regs + sa_off[r]);
+        uint32_t* dst = reinterpret_cast<uint32_t*>(out + reg_off[r]);
+        int nw = (int)(reg_off[r + 1] - reg_off[r]) * (int)(sizeof(AlnReg) / 4);
+        for (int k = lane; k < nw; k += 32) dst[k] = src[k];
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ stage kernels
+__global__ void k_occ(FMIndex fm, long n, const uint64_t* k, const uint64_t* l, uint64_t* cnt) {
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x)
+        fm_2occ4(fm, k[i], l[i], cnt + 8 * i, cnt + 8 * i + 4);
+}
+
+__global__ void __launch_bounds__(EXT_WARPS * 32) k_ksw_extend(MemOpt opt, long n, const uint8_t* __restrict__ q, const int64_t* __restrict__ q_off,
+                                                               const uint8_t* __restrict__ t, const int64_t* __restrict__ t_off,
+                                                               const int* __restrict__ h0, const int* __restrict__ w, int end_bonus, int zdrop,
+                                                               int* out, unsigned long long* cells_out) {
+    const int lane = threadIdx.x & 31;
+    unsigned long long cells = 0;
+    WarpCtx ctx; ctx.lane = lane; ctx.cells = &cells; ctx.z = nullptr; ctx.z_cap = 0;
+    for (long i = (blockIdx.x * (long)blockDim.x + threadIdx.x) >> 5; i < n; i += ((long)gridDim.x * blockDim.x) >> 5) {
+        int qle, tle, gtle, gscore, max_off;
+        int qlen = (int)(q_off[i + 1] - q_off[i]), tlen = (int)(t_off[i + 1] - t_off[i]);
+        int sc = ctx.ksw_extend(opt, qlen, q + q_off[i], 1, tlen, t + t_off[i], 1, w[i], end_bonus, zdrop, h0[i], &qle, &tle, &gtle, &gscore, &max_off);
+        if (lane == 0) {
+            int* o = out + 6 * i;
+            o[0] = sc; o[1] = qle; o[2] = tle; o[3] = gtle; o[4] = gscore; o[5] = max_off;
+        }
+    }
+    if (lane == 0 && cells) atomicAdd(cells_out, cells);
+}
+
+__global__ void __launch_bounds__(EXT_WARPS * 32) k_ksw_global(MemOpt opt, long n, const uint8_t* __restrict__ q, const int64_t* __restrict__ q_off,
+                                                               const uint8_t* __restrict__ t, const int64_t* __restrict__ t_off,
+                                                               const int* __restrict__ w, int* scores, uint8_t* zbuf, long z_cap,
+                                                               uint32_t* cig, int cig_cap, int* n_cig) {
+    const int lane = threadIdx.x & 31;
+    const long gw = (blockIdx.x * (long)blockDim.x + threadIdx.x) >> 5;
+    WarpCtx ctx; ctx.lane = lane; ctx.cells = nullptr; ctx.z = zbuf ? zbuf + gw * z_cap : nullptr; ctx.z_cap = z_cap;
+    for (long i = gw; i < n; i += ((long)gridDim.x * blockDim.x) >> 5) {
+        int qlen = (int)(q_off[i + 1] - q_off[i]), tlen = (int)(t_off[i + 1] - t_off[i]);
+        int nc = 0;
+        int sc = ctx.ksw_global(opt, qlen, q + q_off[i], 1, tlen, t + t_off[i], 1, w[i], cig ? cig + i * (long)cig_cap : nullptr, cig_cap, &nc);
+        if (lane == 0) { scores[i] = sc; if (n_cig) n_cig[i] = nc; }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ host side
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    int ensure(size_t bytes) {
+        if (bytes <= cap) return 0;
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        size_t want = bytes + bytes / 4 + 256;
+        if (cudaMalloc(&p, want) != cudaSuccess) { p = nullptr; return -1; }
+        cap = want;
+        return 0;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+static int validate_opts(const arachne_mem_opt_t* o) {
+    if (!o) { set_error("null options"); return ARACHNE_ERR_ARG; }
+    if (o->e_del <= 0 || o->e_ins <= 0 || o->a <= 0 || o->w <= 0 || o->max_occ <= 0 || o->min_seed_len <= 0) {
+        set_error("options out of range"); return ARACHNE_ERR_OPTS;
+    }
+    for (int i = 0, k = 0; i < 5; ++i)
+        for (int j = 0; j < 5; ++j, ++k) {
+            int want = (i < 4 && j < 4) ? (i == j ? o->a : -o->b) : -1;
+            if (o->mat[k] != want) { set_error("scoring matrix is not bwa_fill_scmat(a,b): not implemented by the kernels"); return ARACHNE_ERR_OPTS; }
+        }
+    return ARACHNE_OK;
+}
+
+static int sm_count(int device) {
+    int n = 148;
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device);
+    return n;
+}
+
+}  // namespace arachne
+
+using namespace arachne;
+
+struct BatchPriv {
+    std::vector<int64_t> reg_off;
+    std::vector<arachne_alnreg_t> regs;
+    std::vector<arachne_aln_t> alns;
+    std::vector<uint32_t> cigar;
+    std::vector<int32_t> mm;
+};
+
+extern "C" {
+
+const char* arachne_last_error(void) { return g_err; }
+
+int arachne_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+    return n;
+}
+
+int arachne_index_load(const char* prefix, int device, arachne_index_t** out) { return index_load(prefix, device, out); }
+
+void arachne_index_free(arachne_index_t* idx) {
+    if (!idx) return;
+    cudaSetDevice(idx->device);
+    cudaFree(idx->d_bwt); cudaFree(idx->d_sa); cudaFree(idx->d_pac); cudaFree(idx->d_contigs);
+    delete idx;
+}
+int64_t arachne_index_l_pac(const arachne_index_t* idx) { return idx ? idx->l_pac : -1; }
+int32_t arachne_index_n_seqs(const arachne_index_t* idx) { return idx ? (int32_t)idx->contigs.size() : -1; }
+size_t arachne_index_device_bytes(const arachne_index_t* idx) { return idx ? idx->device_bytes : 0; }
+int arachne_index_contig(const arachne_index_t* idx, int32_t rid, const char** name, int64_t* offset, int32_t* len) {
+    if (!idx || rid < 0 || rid >= (int32_t)idx->contigs.size()) { set_error("contig id out of range"); return ARACHNE_ERR_ARG; }
+    if (name) *name = idx->names[rid].c_str();
+    if (offset) *offset = idx->contigs[rid].offset;
+    if (len) *len = idx->contigs[rid].len;
+    return ARACHNE_OK;
+}
+
+int arachne_opts_default(arachne_mem_opt_t* o) {  // mem_opt_init, bwa/bwamem.c:48-84
+    if (!o) { set_error("null options"); return ARACHNE_ERR_ARG; }
+    memset(o, 0, sizeof(*o));
+    o->a = 1; o->b = 4;
+    o->o_del = o->o_ins = 6;
+    o->e_del = o->e_ins = 1;
+    o->w = 100; o->T = 30; o->zdrop = 100;
+    o->pen_unpaired = 17;
+    o->pen_clip5 = o->pen_clip3 = 5;
+    o->max_mem_intv = 20;
+    o->min_seed_len = 19; o->split_width = 10; o->max_occ = 500; o->max_chain_gap = 10000; o->max_ins = 10000;
+    o->mask_level = 0.50f; o->drop_ratio = 0.50f; o->XA_drop_ratio = 0.80f; o->split_factor = 1.5f;
+    o->chunk_size = 10000000; o->n_threads = 1;
+    o->max_XA_hits = 5; o->max_XA_hits_alt = 200; o->max_matesw = 50;
+    o->mask_level_redun = 0.95f; o->min_chain_weight = 0; o->max_chain_extend = 1 << 30;
+    o->mapQ_coef_len = 50; o->mapQ_coef_fac = 3;  // (int)log(50)
+    for (int i = 0, k = 0; i < 4; ++i) {
+        for (int j = 0; j < 4; ++j) o->mat[k++] = i == j ? o->a : -o->b;
+        o->mat[k++] = -1;
+    }
+    for (int j = 0; j < 5; ++j) o->mat[20 + j] = -1;
+    return ARACHNE_OK;
+}
+
+// ---------------------------------------------------------------------------------------------- batch
+int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, const arachne_batch_in_t* in, arachne_batch_out_t** out_) {
+    if (!idx || !in || !out_ || !in->seq_off || (!in->seq && in->n_pairs > 0)) { set_error("arachne_align_batch: null argument"); return ARACHNE_ERR_ARG; }
+    int rc = validate_opts(opt_);
+    if (rc) return rc;
+    MemOpt opt;
+    memcpy(&opt, opt_, sizeof(opt));
+    const int64_t n_reads = in->n_pairs * 2;
+    const int64_t n_bases = n_reads ? in->seq_off[n_reads] : 0;
+    int maxlen = 0;
+    for (int64_t i = 0; i < n_reads; ++i) {
+        int64_t l = in->seq_off[i + 1] - in->seq_off[i];
+        if (l < 0 || l > ARACHNE_MAX_READ_LEN) { set_error("read %lld has length %lld; supported 0..%d", (long long)i, (long long)l, ARACHNE_MAX_READ_LEN); return ARACHNE_ERR_ARG; }
+        if (l > maxlen) maxlen = (int)l;
+    }
+    if (n_reads > 0x7fffffff / 2) { set_error("batch too large"); return ARACHNE_ERR_ARG; }
+    AR_CUDA(cudaSetDevice(idx->device));
+    const int sms = sm_count(idx->device);
+    cudaStream_t st;
+    AR_CUDA(cudaStreamCreate(&st));
+    cudaEvent_t ev[8];
+    for (auto& e : ev) cudaEventCreate(&e);
+
+    auto* out = new arachne_batch_out_t();
+    memset(out, 0, sizeof(*out));
+    auto* priv = new BatchPriv();
+    out->priv = priv;
+    out->n_reads = n_reads;
+    priv->reg_off.assign(n_reads + 1, 0);
+
+    DevBuf d_seq, d_off, d_scratch, d_arena, d_misc, d_intv_off, d_intv_n, d_nsa, d_sa_off, d_rows, d_cnt, d_tmp;
+    DevBuf d_seeds, d_kseeds, d_chains, d_nodes, d_order, d_kept, d_nchain, d_nkseed, d_srt, d_regs, d_nregs, d_win, d_reg_off, d_out;
+    std::vector<DevBuf*> all = {&d_seq, &d_off, &d_scratch, &d_arena, &d_misc, &d_intv_off, &d_intv_n, &d_nsa, &d_sa_off, &d_rows, &d_cnt, &d_tmp,
+                                &d_seeds, &d_kseeds, &d_chains, &d_nodes, &d_order, &d_kept, &d_nchain, &d_nkseed, &d_srt, &d_regs, &d_nregs,
+                                &d_win, &d_reg_off, &d_out};
+    auto cleanup = [&]() {
+        for (auto* b : all) b->release();
+        for (auto& e : ev) cudaEventDestroy(e);
+        cudaStreamDestroy(st);
+    };
+    auto fail = [&](int code) { cleanup(); arachne_batch_free(out); return code; };
+#define AR_TRY(x) do { if ((x) != cudaSuccess) { set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #x, cudaGetErrorString(cudaGetLastError())); return fail(ARACHNE_ERR_CUDA); } } while (0)
+#define AR_ALLOC(buf, bytes) do { if ((buf).ensure(bytes)) { set_error("out of device memory allocating %zu bytes (%s)", (size_t)(bytes), #buf); return fail(ARACHNE_ERR_CUDA); } } while (0)
+
+    if (n_reads == 0) { cleanup(); out->reg_off = priv->reg_off.data(); *out_ = out; return ARACHNE_OK; }
+
+    const int L1 = maxlen + 1;
+    const int seed_threads = sms * 512;
+    AR_ALLOC(d_seq, n_bases + 16);
+    AR_ALLOC(d_off, (n_reads + 1) * 8);
+    AR_ALLOC(d_scratch, (size_t)seed_threads * 7 * L1 * sizeof(Intv));
+    AR_ALLOC(d_misc, 64);
+    AR_ALLOC(d_intv_off, n_reads * 8);
+    AR_ALLOC(d_intv_n, n_reads * 4);
+    AR_ALLOC(d_nsa, (n_reads + 1) * 4);
+    AR_ALLOC(d_sa_off, (n_reads + 1) * 8);
+    AR_ALLOC(d_cnt, sizeof(Counters));
+    AR_ALLOC(d_nchain, n_reads * 4);
+    AR_ALLOC(d_nkseed, n_reads * 4);
+    AR_ALLOC(d_nregs, (n_reads + 1) * 4);
+    AR_ALLOC(d_reg_off, (n_reads + 1) * 8);
+    AR_TRY(cudaMemcpyAsync(d_seq.p, in->seq, n_bases, cudaMemcpyHostToDevice, st));
+    AR_TRY(cudaMemcpyAsync(d_off.p, in->seq_off, (n_reads + 1) * 8, cudaMemcpyHostToDevice, st));
+    AR_TRY(cudaMemsetAsync(d_cnt.p, 0, sizeof(Counters), st));
+    AR_TRY(cudaMemsetAsync(d_nsa.p, 0, (n_reads + 1) * 4, st));
+    AR_TRY(cudaMemsetAsync(d_nregs.p, 0, (n_reads + 1) * 4, st));
+
+    Counters hc;
+    unsigned long long arena_cap = (unsigned long long)n_reads * 24 + 1024;
+    // ---- seeding (retry with a larger interval arena if it overflows) ----
+    cudaEventRecord(ev[0], st);
+    for (int attempt = 0;; ++attempt) {
+        AR_ALLOC(d_arena, arena_cap * sizeof(Intv));
+        AR_TRY(cudaMemsetAsync(d_misc.p, 0, 64, st));
+        k_seed<<<seed_threads / 128, 128, 0, st>>>(idx->fm, opt, d_seq.as<uint8_t>(), d_off.as<int64_t>(), (int)n_reads, d_scratch.as<Intv>(), L1,
+                                                    d_arena.as<Intv>(), arena_cap, d_misc.as<unsigned long long>(), d_intv_off.as<unsigned long long>(),
+                                                    d_intv_n.as<int>(), d_nsa.as<unsigned int>(), d_cnt.as<Counters>());
+        AR_TRY(cudaGetLastError());
+        AR_TRY(cudaMemcpyAsync(&hc, d_cnt.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
+        AR_TRY(cudaStreamSynchronize(st));
+        if (hc.err == 0) break;
+        if (attempt >= 3) { set_error("seeding: interval arena/scratch overflow at read %d", hc.err_read); return fail(ARACHNE_ERR_OVERFLOW); }
+        arena_cap *= 4;
+        AR_TRY(cudaMemsetAsync(d_cnt.p, 0, sizeof(Counters), st));
+    }
+    cudaEventRecord(ev[1], st);
+    // ---- seeds per read -> offsets ----
+    size_t tmp_bytes = 0;
+    cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, d_nsa.as<unsigned int>(), d_sa_off.as<unsigned long long>(), (int)n_reads + 1, st);
+    AR_ALLOC(d_tmp, tmp_bytes + 16);
+    AR_TRY(cub::DeviceScan::ExclusiveSum(d_tmp.p, tmp_bytes, d_nsa.as<unsigned int>(), d_sa_off.as<unsigned long long>(), (int)n_reads + 1, st));
+    unsigned long long total_sa = 0;
+    AR_TRY(cudaMemcpyAsync(&total_sa, d_sa_off.as<unsigned long long>() + n_reads, 8, cudaMemcpyDeviceToHost, st));
+    AR_TRY(cudaStreamSynchronize(st));
+    const size_t tsa = (size_t)total_sa + 8;
+    AR_ALLOC(d_rows, tsa * 8);
+    AR_ALLOC(d_seeds, tsa * sizeof(Seed));
+    AR_ALLOC(d_kseeds, tsa * sizeof(Seed));
+    AR_ALLOC(d_chains, tsa * sizeof(Chain));
+    AR_ALLOC(d_nodes, (tsa / 4 + 4 * (size_t)n_reads + 8) * sizeof(BNode));
+    AR_ALLOC(d_order, tsa * 4);
+    AR_ALLOC(d_kept, tsa * 4);
+    AR_ALLOC(d_srt, tsa * 8);
+    AR_ALLOC(d_regs, tsa * sizeof(AlnReg));
+    k_expand<<<sms * 4, 256, 0, st>>>(opt, (int)n_reads, d_arena.as<Intv>(), d_intv_off.as<unsigned long long>(), d_intv_n.as<int>(),
+                                       d_sa_off.as<unsigned long long>(), d_rows.as<uint64_t>());
+    AR_TRY(cudaGetLastError());
+    k_sa<<<sms * 8, 256, 0, st>>>(idx->fm, total_sa, d_rows.as<uint64_t>(), d_cnt.as<Counters>());
+    AR_TRY(cudaGetLastError());
+    cudaEventRecord(ev[2], st);
+    // ---- chaining ----
+    ChainBufs cb;
+    cb.seeds = d_seeds.as<Seed>(); cb.kseeds = d_kseeds.as<Seed>(); cb.chains = d_chains.as<Chain>(); cb.nodes = d_nodes.as<BNode>();
+    cb.order = d_order.as<int32_t>(); cb.kept = d_kept.as<int32_t>(); cb.n_chain = d_nchain.as<int>(); cb.n_kseed = d_nkseed.as<int>();
+    k_chain<<<sms * 8, 128, 0, st>>>(opt, idx->ref, d_off.as<int64_t>(), (int)n_reads, d_arena.as<Intv>(), d_intv_off.as<unsigned long long>(),
+                                      d_intv_n.as<int>(), d_sa_off.as<unsigned long long>(), d_rows.as<uint64_t>(), cb, d_cnt.as<Counters>());
+    AR_TRY(cudaGetLastError());
+    cudaEventRecord(ev[3], st);
+    // ---- extension + dedup ----
+    const int ext_blocks = sms * 8;
+    const int win_cap = 2 * maxlen + 1024 + 4 * opt.w;
+    AR_ALLOC(d_win, (size_t)ext_blocks * EXT_WARPS * win_cap);
+    AR_TRY(cudaMemsetAsync(d_misc.p, 0, 64, st));
+    k_extend<<<ext_blocks, EXT_WARPS * 32, 0, st>>>(opt, idx->ref, d_seq.as<uint8_t>(), d_off.as<int64_t>(), (int)n_reads, d_sa_off.as<unsigned long long>(),
+                                                    cb, d_srt.as<uint64_t>(), d_regs.as<AlnReg>(), d_nregs.as<int>(), d_win.as<uint8_t>(), win_cap,
+                                                    d_misc.as<unsigned int>(), d_cnt.as<Counters>());
+    AR_TRY(cudaGetLastError());
+    cudaEventRecord(ev[4], st);
+    // ---- compact regions ----
+    cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, d_nregs.as<int>(), d_reg_off.as<unsigned long long>(), (int)n_reads + 1, st);
+    AR_ALLOC(d_tmp, tmp_bytes + 16);
+    AR_TRY(cub::DeviceScan::ExclusiveSum(d_tmp.p, tmp_bytes, d_nregs.as<int>(), d_reg_off.as<unsigned long long>(), (int)n_reads + 1, st));
+    unsigned long long total_regs = 0;
+    AR_TRY(cudaMemcpyAsync(&total_regs, d_reg_off.as<unsigned long long>() + n_reads, 8, cudaMemcpyDeviceToHost, st));
+    AR_TRY(cudaMemcpyAsync(&hc, d_cnt.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
+    AR_TRY(cudaStreamSynchronize(st));
+    if (hc.err != 0) { set_error("internal scratch overflow (code %d) at read %d", hc.err, hc.err_read); return fail(ARACHNE_ERR_OVERFLOW); }
+    AR_ALLOC(d_out, (total_regs + 1) * sizeof(AlnReg));
+    k_gather_regs<<<sms * 4, 256, 0, st>>>((int)n_reads, d_sa_off.as<unsigned long long>(), d_reg_off.as<unsigned long long>(), d_regs.as<AlnReg>(),
+                                            d_out.as<AlnReg>());
+    AR_TRY(cudaGetLastError());
+    priv->regs.resize(total_regs);
+    static_assert(sizeof(unsigned long long) == sizeof(int64_t), "");
+    AR_TRY(cudaMemcpyAsync(priv->reg_off.data(), d_reg_off.p, (n_reads + 1) * 8, cudaMemcpyDeviceToHost, st));
+    if (total_regs) AR_TRY(cudaMemcpyAsync(priv->regs.data(), d_out.p, total_regs * sizeof(AlnReg), cudaMemcpyDeviceToHost, st));
+    cudaEventRecord(ev[5], st);
+    AR_TRY(cudaStreamSynchronize(st));
+
+    out->n_regs = (int64_t)total_regs;
+    out->reg_off = priv->reg_off.data();
+    out->regs = priv->regs.data();
+    out->n_sa_lookups = total_sa;
+    out->n_lf_steps = hc.lf_steps;
+    out->n_ext_calls = hc.ext_calls;
+    out->n_ext_cells = hc.ext_cells;
+    cudaEventElapsedTime(&out->ms_seed, ev[0], ev[1]);
+    cudaEventElapsedTime(&out->ms_sa, ev[1], ev[2]);
+    cudaEventElapsedTime(&out->ms_chain, ev[2], ev[3]);
+    cudaEventElapsedTime(&out->ms_extend, ev[3], ev[4]);
+    cudaEventElapsedTime(&out->ms_total, ev[0], ev[5]);
+    cleanup();
+    *out_ = out;
+    return ARACHNE_OK;
+}
+
+void arachne_batch_free(arachne_batch_out_t* out) {
+    if (!out) return;
+    delete reinterpret_cast<BatchPriv*>(out->priv);
+    delete out;
+}
+
+// ---------------------------------------------------------------------------------------------- stage entry points
+int arachne_occ_batch(arachne_index_t* idx, int64_t n, const uint64_t* k, const uint64_t* l, uint64_t* cnt) {
+    if (!idx || !k || !l || !cnt || n < 0) { set_error("arachne_occ_batch: bad argument"); return ARACHNE_ERR_ARG; }
+    AR_CUDA(cudaSetDevice(idx->device));
+    uint64_t *dk = nullptr, *dl = nullptr, *dc = nullptr;
+    AR_CUDA(cudaMalloc(&dk, n * 8 + 8)); AR_CUDA(cudaMalloc(&dl, n * 8 + 8)); AR_CUDA(cudaMalloc(&dc, n * 64 + 8));
+    AR_CUDA(cudaMemcpy(dk, k, n * 8, cudaMemcpyHostToDevice));
+    AR_CUDA(cudaMemcpy(dl, l, n * 8, cudaMemcpyHostToDevice));
+    k_occ<<<256, 256>>>(idx->fm, (long)n, dk, dl, dc);
+    AR_CUDA(cudaGetLastError());
+    AR_CUDA(cudaMemcpy(cnt, dc, n * 64, cudaMemcpyDeviceToHost));
+    cudaFree(dk); cudaFree(dl); cudaFree(dc);
+    return ARACHNE_OK;
+}
+
+int arachne_sa_batch(arachne_index_t* idx, int64_t n, const uint64_t* k, uint64_t* sa) {
+    if (!idx || !k || !sa || n < 0) { set_error("arachne_sa_batch: bad argument"); return ARACHNE_ERR_ARG; }
+    AR_CUDA(cudaSetDevice(idx->device));
+    uint64_t* dk = nullptr; Counters* dc = nullptr;
+    AR_CUDA(cudaMalloc(&dk, n * 8 + 8)); AR_CUDA(cudaMalloc(&dc, sizeof(Counters)));
+    AR_CUDA(cudaMemset(dc, 0, sizeof(Counters)));
+    AR_CUDA(cudaMemcpy(dk, k, n * 8, cudaMemcpyHostToDevice));
+    k_sa<<<256, 256>>>(idx->fm, (unsigned long long)n, dk, dc);
+    AR_CUDA(cudaGetLastError());
+    AR_CUDA(cudaMemcpy(sa, dk, n * 8, cudaMemcpyDeviceToHost));
+    cudaFree(dk); cudaFree(dc);
+    return ARACHNE_OK;
+}
+
+int arachne_seed_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, int64_t n_reads, const uint8_t* seq, const int64_t* seq_off,
+                       int64_t* intv_off, uint64_t* intv, int64_t intv_cap) {
+    if (!idx || !seq || !seq_off || !intv_off || !intv) { set_error("arachne_seed_batch: null argument"); return ARACHNE_ERR_ARG; }
+    int rc = validate_opts(opt_);
+    if (rc) return rc;
+    MemOpt opt; memcpy(&opt, opt_, sizeof(opt));
+    AR_CUDA(cudaSetDevice(idx->device));
+    int maxlen = 0;
+    for (int64_t i = 0; i < n_reads; ++i) maxlen = std::max<int>(maxlen, (int)(seq_off[i + 1] - seq_off[i]));
+    if (maxlen > ARACHNE_MAX_READ_LEN) { set_error("read longer than %d", ARACHNE_MAX_READ_LEN); return ARACHNE_ERR_ARG; }
+    const int L1 = maxlen + 1, threads = 148 * 128;
+    DevBuf d_seq, d_off, d_scr, d_arena, d_used, d_ioff, d_in, d_nsa, d_cnt;
+    int64_t nb = seq_off[n_reads];
+    if (d_seq.ensure(nb + 16) || d_off.ensure((n_reads + 1) * 8) || d_scr.ensure((size_t)threads * 7 * L1 * sizeof(Intv)) ||
+        d_arena.ensure((size_t)intv_cap * sizeof(Intv) + 32) || d_used.ensure(64) || d_ioff.ensure(n_reads * 8 + 8) || d_in.ensure(n_reads * 4 + 4) ||
+        d_nsa.ensure(n_reads * 4 + 4) || d_cnt.ensure(sizeof(Counters))) { set_error("out of device memory"); return ARACHNE_ERR_CUDA; }
+    AR_CUDA(cudaMemcpy(d_seq.p, seq, nb, cudaMemcpyHostToDevice));
+    AR_CUDA(cudaMemcpy(d_off.p, seq_off, (n_reads + 1) * 8, cudaMemcpyHostToDevice));
+    AR_CUDA(cudaMemset(d_used.p, 0, 64)); AR_CUDA(cudaMemset(d_cnt.p, 0, sizeof(Counters)));
+    k_seed<<<threads / 128, 128>>>(idx->fm, opt, d_seq.as<uint8_t>(), d_off.as<int64_t>(), (int)n_reads, d_scr.as<Intv>(), L1, d_arena.as<Intv>(),
+                                    (unsigned long long)intv_cap, d_used.as<unsigned long long>(), d_ioff.as<unsigned long long>(), d_in.as<int>(),
+                                    d_nsa.as<unsigned int>(), d_cnt.as<Counters>());
+    AR_CUDA(cudaGetLastError());
+    Counters hc;
+    AR_CUDA(cudaMemcpy(&hc, d_cnt.p, sizeof(hc), cudaMemcpyDeviceToHost));
+    if (hc.err) { set_error("interval capacity too small"); return ARACHNE_ERR_OVERFLOW; }
+    std::vector<unsigned long long> ioff(n_reads); std::vector<int> in_(n_reads);
+    unsigned long long used = 0;
+    AR_CUDA(cudaMemcpy(ioff.data(), d_ioff.p, n_reads * 8, cudaMemcpyDeviceToHost));
+    AR_CUDA(cudaMemcpy(in_.data(), d_in.p, n_reads * 4, cudaMemcpyDeviceToHost));
+    AR_CUDA(cudaMemcpy(&used, d_used.p, 8, cudaMemcpyDeviceToHost));
+    std::vector<Intv> a(used + 1);
+    AR_CUDA(cudaMemcpy(a.data(), d_arena.p, used * sizeof(Intv), cudaMemcpyDeviceToHost));
+    int64_t o = 0;
+    for (int64_t r = 0; r < n_reads; ++r) {  // arena slots are handed out in completion order; re-pack in read order
+        intv_off[r] = o;
+        memcpy(intv + 4 * o, a.data() + ioff[r], (size_t)in_[r] * sizeof(Intv));
+        o += in_[r];
+    }
+    intv_off[n_reads] = o;
+    for (DevBuf* b : {&d_seq, &d_off, &d_scr, &d_arena, &d_used, &d_ioff, &d_in, &d_nsa, &d_cnt}) b->release();
+    return ARACHNE_OK;
+}
+
+int arachne_ksw_extend_batch(int device, const arachne_mem_opt_t* opt_, int64_t n, const uint8_t* q, const int64_t* q_off, const uint8_t* t,
+                             const int64_t* t_off, const int32_t* h0, const int32_t* w, int end_bonus, int zdrop, int32_t* out, uint64_t* cells,
+                             float* kernel_ms, int repeat) {
+    if (!q || !q_off || !t || !t_off || !h0 || !w || !out || n < 0) { set_error("arachne_ksw_extend_batch: null argument"); return ARACHNE_ERR_ARG; }
+    int rc = validate_opts(opt_);
+    if (rc) return rc;
+    for (int64_t i = 0; i < n; ++i) {
+        if (q_off[i + 1] - q_off[i] > ARACHNE_MAX_READ_LEN || q_off[i + 1] - q_off[i] < 1 || h0[i] <= 0) {
+            set_error("problem %lld: qlen must be 1..%d and h0 > 0 (ksw.c:385)", (long long)i, ARACHNE_MAX_READ_LEN); return ARACHNE_ERR_ARG;
+        }
+    }
+    MemOpt opt; memcpy(&opt, opt_, sizeof(opt));
+    if (arachne_device_count() <= device) { set_error("no CUDA device %d (no CPU path)", device); return ARACHNE_ERR_CUDA; }
+    AR_CUDA(cudaSetDevice(device));
+    DevBuf dq, dqo, dt, dto, dh, dw, dout, dc;
+    if (dq.ensure(q_off[n] + 16) || dqo.ensure((n + 1) * 8) || dt.ensure(t_off[n] + 16) || dto.ensure((n + 1) * 8) || dh.ensure(n * 4 + 4) ||
+        dw.ensure(n * 4 + 4) || dout.ensure(n * 24 + 8) || dc.ensure(8)) { set_error("out of device memory"); return ARACHNE_ERR_CUDA; }
+    AR_CUDA(cudaMemcpy(dq.p, q, q_off[n], cudaMemcpyHostToDevice)); AR_CUDA(cudaMemcpy(dqo.p, q_off, (n + 1) * 8, cudaMemcpyHostToDevice));
+    AR_CUDA(cudaMemcpy(dt.p, t, t_off[n], cudaMemcpyHostToDevice)); AR_CUDA(cudaMemcpy(dto.p, t_off, (n + 1) * 8, cudaMemcpyHostToDevice));
+    AR_CUDA(cudaMemcpy(dh.p, h0, n * 4, cudaMemcpyHostToDevice)); AR_CUDA(cudaMemcpy(dw.p, w, n * 4, cudaMemcpyHostToDevice));
+    cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    if (repeat < 1) repeat = 1;
+    const int blocks = sm_count(device) * 8;
+    // one untimed launch, then `repeat` timed ones
+    for (int it = 0; it <= repeat; ++it) {
+        if (it == 1) cudaEventRecord(e0);
+        AR_CUDA(cudaMemsetAsync(dc.p, 0, 8));
+        k_ksw_extend<<<blocks, EXT_WARPS * 32>>>(opt, (long)n, dq.as<uint8_t>(), dqo.as<int64_t>(), dt.as<uint8_t>(), dto.as<int64_t>(), dh.as<int>(),
+                                                 dw.as<int>(), end_bonus, zdrop, dout.as<int>(), dc.as<unsigned long long>());
+        AR_CUDA(cudaGetLastError());
+    }
+    cudaEventRecord(e1);
+    AR_CUDA(cudaDeviceSynchronize());
+    float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
+    if (kernel_ms) *kernel_ms = ms / repeat;
+    AR_CUDA(cudaMemcpy(out, dout.p, n * 24, cudaMemcpyDeviceToHost));
+    if (cells) AR_CUDA(cudaMemcpy(cells, dc.p, 8, cudaMemcpyDeviceToHost));
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    for (DevBuf* b : {&dq, &dqo, &dt, &dto, &dh, &dw, &dout, &dc}) b->release();
+    return ARACHNE_OK;
+}
+
+int arachne_ksw_global_batch(int device, const arachne_mem_opt_t* opt_, int64_t n, const uint8_t* q, const int64_t* q_off, const uint8_t* t,
+                             const int64_t* t_off, const int32_t* w, int32_t* scores, int64_t* cigar_off, uint32_t* cigar, int64_t cigar_cap) {
+    if (!q || !q_off || !t || !t_off || !w || !scores || n < 0) { set_error("arachne_ksw_global_batch: null argument"); return ARACHNE_ERR_ARG; }
+    int rc = validate_opts(opt_);
+    if (rc) return rc;
+    MemOpt opt; memcpy(&opt, opt_, sizeof(opt));
+    if (arachne_device_count() <= device) { set_error("no CUDA device %d (no CPU path)", device); return ARACHNE_ERR_CUDA; }
+    AR_CUDA(cudaSetDevice(device));
+    long zmax = 1; int cmax = 8;
+    for (int64_t i = 0; i < n; ++i) {
+        long ql = q_off[i + 1] - q_off[i], tl = t_off[i + 1] - t_off[i];
+        if (ql > ARACHNE_MAX_READ_LEN || ql < 1) { set_error("problem %lld: qlen must be 1..%d", (long long)i, ARACHNE_MAX_READ_LEN); return ARACHNE_ERR_ARG; }
+        long ncol = std::min<long>(ql, 2L * w[i] + 1);
+        zmax = std::max(zmax, ncol * tl);
+        cmax = std::max<int>(cmax, (int)(ql + tl + 2));
+    }
+    const int blocks = sm_count(device) * 2;
+    const long nwarps = (long)blocks * EXT_WARPS;
+    DevBuf dq, dqo, dt, dto, dw, ds, dz, dcg, dn;
+    bool want = cigar_off != nullptr;
+    if (dq.ensure(q_off[n] + 16) || dqo.ensure((n + 1) * 8) || dt.ensure(t_off[n] + 16) || dto.ensure((n + 1) * 8) || dw.ensure(n * 4 + 4) ||
+        ds.ensure(n * 4 + 4) || (want && (dz.ensure((size_t)nwarps * zmax) || dcg.ensure((size_t)n * cmax * 4 + 4) || dn.ensure(n * 4 + 4)))) {
+        set_error("out of device memory"); return ARACHNE_ERR_CUDA;
+    }
+    AR_CUDA(cudaMemcpy(dq.p, q, q_off[n], cudaMemcpyHostToDevice)); AR_CUDA(cudaMemcpy(dqo.p, q_off, (n + 1) * 8, cudaMemcpyHostToDevice));
+    AR_CUDA(cudaMemcpy(dt.p, t, t_off[n], cudaMemcpyHostToDevice)); AR_CUDA(cudaMemcpy(dto.p, t_off, (n + 1) * 8, cudaMemcpyHostToDevice));
+    AR_CUDA(cudaMemcpy(dw.p, w, n * 4, cudaMemcpyHostToDevice));
+    k_ksw_global<<<blocks, EXT_WARPS * 32>>>(opt, (long)n, dq.as<uint8_t>(), dqo.as<int64_t>(), dt.as<uint8_t>(), dto.as<int64_t>(), dw.as<int>(),
+                                             ds.as<int>(), want ? dz.as<uint8_t>() : nullptr, zmax, want ? dcg.as<uint32_t>() : nullptr, cmax,
+                                             want ? dn.as<int>() : nullptr);
+    AR_CUDA(cudaGetLastError());
+    AR_CUDA(cudaMemcpy(scores, ds.p, n * 4, cudaMemcpyDeviceToHost));
+    if (want) {
+        std::vector<int> nc(n); std::vector<uint32_t> cg((size_t)n * cmax);
+        AR_CUDA(cudaMemcpy(nc.data(), dn.p, n * 4, cudaMemcpyDeviceToHost));
+        AR_CUDA(cudaMemcpy(cg.data(), dcg.p, (size_t)n * cmax * 4, cudaMemcpyDeviceToHost));
+        int64_t o = 0;
+        for (int64_t i = 0; i < n; ++i) {
+            cigar_off[i] = o;
+            if (o + nc[i] > cigar_cap) { set_error("cigar pool too small"); return ARACHNE_ERR_OVERFLOW; }
+            memcpy(cigar + o, cg.data() + (size_t)i * cmax, (size_t)nc[i] * 4);
+            o += nc[i];
+        }
+        cigar_off[n] = o;
+    }
+    for (DevBuf* b : {&dq, &dqo, &dt, &dto, &dw, &ds, &dz, &dcg, &dn}) b->release();
+    return ARACHNE_OK;
+}
+
+}  // extern "C"

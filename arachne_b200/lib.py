@@ -1,0 +1,190 @@
+"""ctypes view of libarachne_cuda.so (include/arachne_cuda.h).  No fallback: a missing library or device raises."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+ALNREG = np.dtype([("rb", "<i8"), ("re", "<i8"), ("qb", "<i4"), ("qe", "<i4"), ("rid", "<i4"), ("score", "<i4"),
+                   ("truesc", "<i4"), ("sub", "<i4"), ("alt_sc", "<i4"), ("csub", "<i4"), ("sub_n", "<i4"),
+                   ("w", "<i4"), ("seedcov", "<i4"), ("secondary", "<i4"), ("secondary_all", "<i4"),
+                   ("seedlen0", "<i4"), ("n_comp_is_alt", "<i4"), ("frac_rep", "<f4"), ("hash", "<u8")])
+ALN = np.dtype([("pos", "<i8"), ("rid", "<i4"), ("is_rev", "<i4"), ("nm", "<i4"), ("n_cigar", "<i4"), ("cigar_off", "<i8"),
+                ("score", "<i4"), ("sub", "<i4"), ("matches", "<i4"), ("mismatches", "<i4"), ("indels", "<i4"),
+                ("soft_clipped", "<i4"), ("soft_clipped_length", "<i4"), ("n_mm", "<i4"), ("mm_off", "<i8")])
+assert ALNREG.itemsize == 88 and ALN.itemsize == 72
+
+STAGE_REGIONS, STAGE_RESCUE, STAGE_CIGAR, STAGE_PLACE = 1, 2, 4, 8
+
+
+class ArachneError(RuntimeError):
+    pass
+
+
+def lib_path() -> str:
+    return os.path.join(HERE, "libarachne_cuda.so")
+
+
+class MemOpt(C.Structure):  # arachne_mem_opt_t == mem_opt_t (bwa/bwamem.h:27-66)
+    _fields_ = [("a", C.c_int), ("b", C.c_int), ("o_del", C.c_int), ("e_del", C.c_int), ("o_ins", C.c_int), ("e_ins", C.c_int),
+                ("pen_unpaired", C.c_int), ("pen_clip5", C.c_int), ("pen_clip3", C.c_int), ("w", C.c_int), ("zdrop", C.c_int),
+                ("max_mem_intv", C.c_uint64), ("T", C.c_int), ("flag", C.c_int), ("min_seed_len", C.c_int),
+                ("min_chain_weight", C.c_int), ("max_chain_extend", C.c_int), ("split_factor", C.c_float), ("split_width", C.c_int),
+                ("max_occ", C.c_int), ("max_chain_gap", C.c_int), ("n_threads", C.c_int), ("chunk_size", C.c_int),
+                ("mask_level", C.c_float), ("drop_ratio", C.c_float), ("XA_drop_ratio", C.c_float), ("mask_level_redun", C.c_float),
+                ("mapQ_coef_len", C.c_float), ("mapQ_coef_fac", C.c_int), ("max_ins", C.c_int), ("max_matesw", C.c_int),
+                ("max_XA_hits", C.c_int), ("max_XA_hits_alt", C.c_int), ("mat", C.c_int8 * 25)]
+
+
+class BatchIn(C.Structure):
+    _fields_ = [("n_pairs", C.c_int64), ("seq", C.POINTER(C.c_uint8)), ("seq_off", C.POINTER(C.c_int64)), ("n_barcodes", C.c_int64),
+                ("barcode_off", C.POINTER(C.c_int64)), ("score_delta", C.c_int32), ("stages", C.c_int32)]
+
+
+class BatchOut(C.Structure):
+    _fields_ = [("n_reads", C.c_int64), ("n_regs", C.c_int64), ("n_cigar", C.c_int64), ("n_mm", C.c_int64),
+                ("reg_off", C.POINTER(C.c_int64)), ("regs", C.c_void_p), ("alns", C.c_void_p), ("cigar", C.POINTER(C.c_uint32)),
+                ("mm", C.POINTER(C.c_int32)),
+                ("n_occ_lookups", C.c_uint64), ("n_sa_lookups", C.c_uint64), ("n_lf_steps", C.c_uint64), ("n_ext_calls", C.c_uint64),
+                ("n_ext_cells", C.c_uint64), ("n_glb_cells", C.c_uint64),
+                ("ms_seed", C.c_float), ("ms_sa", C.c_float), ("ms_chain", C.c_float), ("ms_extend", C.c_float), ("ms_rescue", C.c_float),
+                ("ms_cigar", C.c_float), ("ms_place", C.c_float), ("ms_total", C.c_float), ("priv", C.c_void_p)]
+
+
+def _p(a, t):
+    return a.ctypes.data_as(C.POINTER(t))
+
+
+class ArachneCuda:
+    """One loaded index on one device + the kernel entry points."""
+
+    def __init__(self, path: str | None = None):
+        path = path or lib_path()
+        if not os.path.exists(path):
+            raise ArachneError(f"{path} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                               "(there is no CPU fallback)")
+        L = self.lib = C.CDLL(path)
+        L.arachne_last_error.restype = C.c_char_p
+        L.arachne_index_load.argtypes = [C.c_char_p, C.c_int, C.POINTER(C.c_void_p)]
+        L.arachne_index_free.argtypes = [C.c_void_p]
+        L.arachne_index_l_pac.restype = C.c_int64; L.arachne_index_l_pac.argtypes = [C.c_void_p]
+        L.arachne_index_n_seqs.argtypes = [C.c_void_p]
+        L.arachne_index_device_bytes.restype = C.c_size_t; L.arachne_index_device_bytes.argtypes = [C.c_void_p]
+        L.arachne_index_contig.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_char_p), C.POINTER(C.c_int64), C.POINTER(C.c_int32)]
+        L.arachne_opts_default.argtypes = [C.POINTER(MemOpt)]
+        L.arachne_align_batch.argtypes = [C.c_void_p, C.POINTER(MemOpt), C.POINTER(BatchIn), C.POINTER(C.POINTER(BatchOut))]
+        L.arachne_batch_free.argtypes = [C.POINTER(BatchOut)]
+        L.arachne_occ_batch.argtypes = [C.c_void_p, C.c_int64, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+        L.arachne_sa_batch.argtypes = [C.c_void_p, C.c_int64, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+        L.arachne_seed_batch.argtypes = [C.c_void_p, C.POINTER(MemOpt), C.c_int64, C.POINTER(C.c_uint8), C.POINTER(C.c_int64),
+                                         C.POINTER(C.c_int64), C.POINTER(C.c_uint64), C.c_int64]
+        L.arachne_ksw_extend_batch.argtypes = [C.c_int, C.POINTER(MemOpt), C.c_int64, C.POINTER(C.c_uint8), C.POINTER(C.c_int64),
+                                               C.POINTER(C.c_uint8), C.POINTER(C.c_int64), C.POINTER(C.c_int32), C.POINTER(C.c_int32),
+                                               C.c_int, C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_uint64), C.POINTER(C.c_float), C.c_int]
+        L.arachne_ksw_global_batch.argtypes = [C.c_int, C.POINTER(MemOpt), C.c_int64, C.POINTER(C.c_uint8), C.POINTER(C.c_int64),
+                                               C.POINTER(C.c_uint8), C.POINTER(C.c_int64), C.POINTER(C.c_int32), C.POINTER(C.c_int32),
+                                               C.POINTER(C.c_int64), C.POINTER(C.c_uint32), C.c_int64]
+        self.opt = MemOpt()
+        self._ck(L.arachne_opts_default(C.byref(self.opt)))
+        self.idx = C.c_void_p(None)
+        self.device = 0
+
+    def _ck(self, rc: int):
+        if rc != 0:
+            raise ArachneError(f"libarachne_cuda error {rc}: {self.lib.arachne_last_error().decode()}")
+
+    def device_count(self) -> int:
+        return self.lib.arachne_device_count()
+
+    # ---- index (GoBwaLoadReference, gobwa.go:128-147) ----
+    def load_index(self, prefix: str, device: int = 0):
+        self.close()
+        self.device = device
+        self._ck(self.lib.arachne_index_load(prefix.encode(), device, C.byref(self.idx)))
+        return self
+
+    def close(self):
+        if self.idx:
+            self.lib.arachne_index_free(self.idx)
+            self.idx = C.c_void_p(None)
+
+    @property
+    def l_pac(self) -> int:
+        return self.lib.arachne_index_l_pac(self.idx)
+
+    def contigs(self):
+        out = []
+        for i in range(self.lib.arachne_index_n_seqs(self.idx)):
+            name = C.c_char_p(); off = C.c_int64(); ln = C.c_int32()
+            self._ck(self.lib.arachne_index_contig(self.idx, i, C.byref(name), C.byref(off), C.byref(ln)))
+            out.append((name.value.decode(), off.value, ln.value))
+        return out
+
+    # ---- stage entry points ----
+    def occ(self, k, l):
+        k = np.ascontiguousarray(k, dtype=np.uint64); l = np.ascontiguousarray(l, dtype=np.uint64)
+        out = np.zeros((len(k), 8), dtype=np.uint64)
+        self._ck(self.lib.arachne_occ_batch(self.idx, len(k), _p(k, C.c_uint64), _p(l, C.c_uint64), _p(out, C.c_uint64)))
+        return out
+
+    def sa(self, k):
+        k = np.ascontiguousarray(k, dtype=np.uint64); out = np.zeros(len(k), dtype=np.uint64)
+        self._ck(self.lib.arachne_sa_batch(self.idx, len(k), _p(k, C.c_uint64), _p(out, C.c_uint64)))
+        return out
+
+    def seed(self, seq, off, cap_per_read=64):
+        seq = np.ascontiguousarray(seq, dtype=np.uint8); off = np.ascontiguousarray(off, dtype=np.int64)
+        n = len(off) - 1
+        ioff = np.zeros(n + 1, dtype=np.int64); cap = n * cap_per_read + 1024
+        intv = np.zeros((cap, 4), dtype=np.uint64)
+        self._ck(self.lib.arachne_seed_batch(self.idx, C.byref(self.opt), n, _p(seq, C.c_uint8), _p(off, C.c_int64), _p(ioff, C.c_int64),
+                                             _p(intv, C.c_uint64), cap))
+        return ioff, intv[:ioff[-1]]
+
+    def ksw_extend(self, q, q_off, t, t_off, h0, w, end_bonus=5, zdrop=100, repeat=1, device=None):
+        q = np.ascontiguousarray(q, dtype=np.uint8); t = np.ascontiguousarray(t, dtype=np.uint8)
+        q_off = np.ascontiguousarray(q_off, dtype=np.int64); t_off = np.ascontiguousarray(t_off, dtype=np.int64)
+        h0 = np.ascontiguousarray(h0, dtype=np.int32); w = np.ascontiguousarray(w, dtype=np.int32)
+        n = len(h0); out = np.zeros((n, 6), dtype=np.int32); cells = C.c_uint64(0); ms = C.c_float(0)
+        self._ck(self.lib.arachne_ksw_extend_batch(self.device if device is None else device, C.byref(self.opt), n, _p(q, C.c_uint8),
+                                                   _p(q_off, C.c_int64), _p(t, C.c_uint8), _p(t_off, C.c_int64), _p(h0, C.c_int32),
+                                                   _p(w, C.c_int32), end_bonus, zdrop, _p(out, C.c_int32), C.byref(cells), C.byref(ms), repeat))
+        return out, cells.value, ms.value
+
+    def ksw_global(self, q, q_off, t, t_off, w, want_cigar=True, device=None):
+        q = np.ascontiguousarray(q, dtype=np.uint8); t = np.ascontiguousarray(t, dtype=np.uint8)
+        q_off = np.ascontiguousarray(q_off, dtype=np.int64); t_off = np.ascontiguousarray(t_off, dtype=np.int64)
+        w = np.ascontiguousarray(w, dtype=np.int32); n = len(w)
+        sc = np.zeros(n, dtype=np.int32); coff = np.zeros(n + 1, dtype=np.int64); cap = int(q_off[-1] + t_off[-1] + 8 * n + 8)
+        cig = np.zeros(cap, dtype=np.uint32)
+        self._ck(self.lib.arachne_ksw_global_batch(self.device if device is None else device, C.byref(self.opt), n, _p(q, C.c_uint8),
+                                                   _p(q_off, C.c_int64), _p(t, C.c_uint8), _p(t_off, C.c_int64), _p(w, C.c_int32),
+                                                   _p(sc, C.c_int32), _p(coff, C.c_int64) if want_cigar else None, _p(cig, C.c_uint32), cap))
+        return sc, coff, cig[:coff[-1]]
+
+    # ---- batch hot path ----
+    def align_batch(self, seq, off, bc_off=None, score_delta=25, stages=0):
+        seq = np.ascontiguousarray(seq, dtype=np.uint8); off = np.ascontiguousarray(off, dtype=np.int64)
+        n_pairs = (len(off) - 1) // 2
+        bi = BatchIn(); bi.n_pairs = n_pairs; bi.seq = _p(seq, C.c_uint8); bi.seq_off = _p(off, C.c_int64)
+        if bc_off is not None:
+            bc_off = np.ascontiguousarray(bc_off, dtype=np.int64)
+            bi.n_barcodes = len(bc_off) - 1; bi.barcode_off = _p(bc_off, C.c_int64)
+        bi.score_delta = score_delta; bi.stages = stages
+        po = C.POINTER(BatchOut)()
+        self._ck(self.lib.arachne_align_batch(self.idx, C.byref(self.opt), C.byref(bi), C.byref(po)))
+        try:
+            o = po.contents
+            res = dict(reg_off=np.ctypeslib.as_array(o.reg_off, shape=(o.n_reads + 1,)).copy(),
+                       regs=(np.frombuffer(C.string_at(o.regs, o.n_regs * 88), dtype=ALNREG).copy() if o.n_regs else np.zeros(0, ALNREG)),
+                       counters={k: getattr(o, k) for k in ("n_occ_lookups", "n_sa_lookups", "n_lf_steps", "n_ext_calls", "n_ext_cells", "n_glb_cells")},
+                       ms={k: getattr(o, "ms_" + k) for k in ("seed", "sa", "chain", "extend", "rescue", "cigar", "place", "total")})
+            if o.alns and o.n_regs:
+                res["alns"] = np.frombuffer(C.string_at(o.alns, o.n_regs * 72), dtype=ALN).copy()
+                res["cigar"] = np.ctypeslib.as_array(o.cigar, shape=(max(1, o.n_cigar),))[:o.n_cigar].copy()
+                res["mm"] = np.ctypeslib.as_array(o.mm, shape=(max(1, o.n_mm),))[:o.n_mm].copy()
+        finally:
+            self.lib.arachne_batch_free(po)
+        return res

@@ -1,0 +1,183 @@
+/* libarachne_cuda -- C ABI of the B200-native candidate-alignment / read-placement hot path.
+ *
+ * This is the seam the reference crosses through cgo in src/gobwa/gobwa.go (it links `-lbwa` there,
+ * gobwa.go:7).  Everything below is plain C: pointers and sizes, int status returns, no aborts.
+ * A call made without a usable CUDA device fails with ARACHNE_ERR_CUDA -- there is no CPU fallback.
+ *
+ * Two layers:
+ *   (1) batch API (new): one call per batch of barcodes instead of one cgo call per read pair / candidate;
+ *   (2) stage entry points: the individual kernels on caller-supplied problems -- these are what the parity
+ *       tests and the config-5 ksw_extend2 microbench drive.
+ * The per-pair compat shims with BWA's own symbol names are declared in arachne_bwa_compat.h.
+ */
+#ifndef ARACHNE_CUDA_H_
+#define ARACHNE_CUDA_H_
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum {
+    ARACHNE_OK = 0,
+    ARACHNE_ERR_ARG = -1,      /* bad argument (null pointer, read longer than ARACHNE_MAX_READ_LEN, ...) */
+    ARACHNE_ERR_IO = -2,       /* index files missing / unreadable / inconsistent (replaces bwa_idx_load -> NULL, gobwa.go:130-135) */
+    ARACHNE_ERR_CUDA = -3,     /* no device, launch failure, out of device memory */
+    ARACHNE_ERR_OVERFLOW = -4, /* an internal arena stayed too small after the automatic retries */
+    ARACHNE_ERR_OPTS = -5      /* option values the kernels do not implement (non bwa_fill_scmat matrix, ...) */
+};
+
+#define ARACHNE_MAX_READ_LEN 255
+
+/* Options: field-for-field the reference's mem_opt_t (bwa/bwamem.h:27-66; defaults mem_opt_init, bwamem.c:48-84),
+ * so GoBwaAllocSettings (gobwa.go:149-153) can keep handing an opaque pointer around. */
+typedef struct {
+    int a, b;
+    int o_del, e_del;
+    int o_ins, e_ins;
+    int pen_unpaired;
+    int pen_clip5, pen_clip3;
+    int w;
+    int zdrop;
+    uint64_t max_mem_intv;
+    int T;
+    int flag;
+    int min_seed_len;
+    int min_chain_weight;
+    int max_chain_extend;
+    float split_factor;
+    int split_width;
+    int max_occ;
+    int max_chain_gap;
+    int n_threads;
+    int chunk_size;
+    float mask_level;
+    float drop_ratio;
+    float XA_drop_ratio;
+    float mask_level_redun;
+    float mapQ_coef_len;
+    int mapQ_coef_fac;
+    int max_ins;
+    int max_matesw;
+    int max_XA_hits, max_XA_hits_alt;
+    int8_t mat[25];
+} arachne_mem_opt_t;
+
+/* Alignment region: byte-for-byte mem_alnreg_t (bwa/bwamem.h:86-104, 88 bytes); the fields gobwa.go dereferences
+ * (rb re qb qe rid score secondary secondary_all, gobwa.go:352-369) sit at the same offsets. */
+typedef struct {
+    int64_t rb, re;
+    int qb, qe;
+    int rid;
+    int score;
+    int truesc;
+    int sub;
+    int alt_sc;
+    int csub;
+    int sub_n;
+    int w;
+    int seedcov;
+    int secondary;
+    int secondary_all;
+    int seedlen0;
+    int n_comp_is_alt; /* n_comp:30, is_alt:2 */
+    float frac_rep;
+    uint64_t hash;
+} arachne_alnreg_t;
+
+/* Per-region alignment record: what mem_reg2aln (bwamem.c:1086-1156) + InterpretSingleReadAlignment
+ * (gobwa.go:449-488) + the CIGAR/reference walk of GetAlignments (aligner.go:1505-1569) produce. */
+typedef struct {
+    int64_t pos;          /* 0-based leftmost forward-strand position within the contig (mem_aln_t.pos) */
+    int32_t rid;
+    int32_t is_rev;
+    int32_t nm;           /* edit distance (mem_aln_t.NM) */
+    int32_t n_cigar;
+    int64_t cigar_off;    /* into the batch CIGAR pool; words are len<<4|op, MIDSH = 01234 */
+    int32_t score, sub;
+    int32_t matches, mismatches, indels, soft_clipped, soft_clipped_length; /* aligner.go:1505-1569 */
+    int32_t n_mm;         /* number of mismatch loci */
+    int64_t mm_off;       /* into the batch mismatch pool: n_mm reference loci then n_mm read offsets */
+} arachne_aln_t;
+
+typedef struct arachne_index arachne_index_t;
+
+typedef struct {
+    int64_t n_pairs;
+    const uint8_t *seq;        /* concatenated reads as codes 0..4 (SequenceConvert, gobwa.go:159-167): R1,R2 of pair 0, ... */
+    const int64_t *seq_off;    /* 2*n_pairs+1 offsets into seq */
+    int64_t n_barcodes;        /* work units (fastqreader.ReadBarcodeSet, reader.go:208-291); may be 0 => one unit */
+    const int64_t *barcode_off;/* n_barcodes+1 pair indices */
+    int32_t score_delta;       /* GetChains passes 25 (aligner.go:454) */
+    int32_t stages;            /* bitmask of ARACHNE_STAGE_*; 0 = all */
+} arachne_batch_in_t;
+
+enum {
+    ARACHNE_STAGE_REGIONS = 1, /* seeding, chaining, extension, dedup (mem_align1_core) */
+    ARACHNE_STAGE_RESCUE = 2,  /* mem_matesw as driven by GoBwaMemMateSW */
+    ARACHNE_STAGE_CIGAR = 4,   /* mem_reg2aln + GetAlignments walk */
+    ARACHNE_STAGE_PLACE = 8    /* tagBestAlignments .. estimateMapQualities */
+};
+
+typedef struct {
+    int64_t n_reads, n_regs, n_cigar, n_mm;
+    int64_t *reg_off;          /* n_reads+1 */
+    arachne_alnreg_t *regs;    /* n_regs */
+    arachne_aln_t *alns;       /* n_regs (ARACHNE_STAGE_CIGAR) */
+    uint32_t *cigar;           /* n_cigar */
+    int32_t *mm;               /* mismatch pool */
+    /* counters for roofline accounting: */
+    uint64_t n_occ_lookups;    /* bwt_2occ4-equivalent calls in seeding */
+    uint64_t n_sa_lookups, n_lf_steps;
+    uint64_t n_ext_calls, n_ext_cells;  /* ksw_extend2 calls and in-band cells exactly as ksw.c:424-448 visits them */
+    uint64_t n_glb_cells;
+    float ms_seed, ms_sa, ms_chain, ms_extend, ms_rescue, ms_cigar, ms_place, ms_total; /* CUDA-event stage times */
+    void *priv;
+} arachne_batch_out_t;
+
+/* ---- library ---- */
+const char *arachne_last_error(void);
+int arachne_device_count(void);
+
+/* ---- index: replaces bwa_idx_load(path, BWA_IDX_ALL) (gobwa.go:130; bwa/bwa.c:262-294).  Reads
+ * <prefix>.bwt .sa .pac .ann .amb as written by `bwa index` and keeps the FM-index, the sampled SA and the
+ * packed reference resident in HBM of `device`. */
+int arachne_index_load(const char *prefix, int device, arachne_index_t **out);
+void arachne_index_free(arachne_index_t *idx);
+int64_t arachne_index_l_pac(const arachne_index_t *idx);
+int32_t arachne_index_n_seqs(const arachne_index_t *idx);
+int arachne_index_contig(const arachne_index_t *idx, int32_t rid, const char **name, int64_t *offset, int32_t *len);
+size_t arachne_index_device_bytes(const arachne_index_t *idx);
+
+/* ---- options: mem_opt_init defaults (gobwa.go:151) ---- */
+int arachne_opts_default(arachne_mem_opt_t *opt);
+
+/* ---- batch hot path: replaces the per-pair GoBwaMemMateSW loop of GetChains (aligner.go:1637-1638) and the
+ * per-candidate GoBwaSmithWaterman / GetSeq calls of GetAlignments (aligner.go:1500,1519). */
+int arachne_align_batch(arachne_index_t *idx, const arachne_mem_opt_t *opt, const arachne_batch_in_t *in, arachne_batch_out_t **out);
+void arachne_batch_free(arachne_batch_out_t *out);
+
+/* ---- stage entry points (device kernels on caller problems) ---- */
+/* ksw_extend2 (bwa/ksw.c:380-479) on n independent problems; query i = q[q_off[i]..q_off[i+1]), same for t.
+ * out: n x 6 ints {score, qle, tle, gtle, gscore, max_off}.  *cells receives the in-band cell count;
+ * *kernel_ms the CUDA-event time of `repeat` back-to-back launches divided by repeat. */
+int arachne_ksw_extend_batch(int device, const arachne_mem_opt_t *opt, int64_t n, const uint8_t *q, const int64_t *q_off, const uint8_t *t,
+                             const int64_t *t_off, const int32_t *h0, const int32_t *w, int end_bonus, int zdrop, int32_t *out,
+                             uint64_t *cells, float *kernel_ms, int repeat);
+/* ksw_global2 (bwa/ksw.c:504-606): out scores[n]; cigars as CSR (cigar_off n+1, pool of cap words) when cigar_off != NULL */
+int arachne_ksw_global_batch(int device, const arachne_mem_opt_t *opt, int64_t n, const uint8_t *q, const int64_t *q_off, const uint8_t *t,
+                             const int64_t *t_off, const int32_t *w, int32_t *scores, int64_t *cigar_off, uint32_t *cigar, int64_t cigar_cap);
+/* bwt_2occ4 (bwa/bwt.c:189-220): cnt is n x 8 (cntk[4], cntl[4]) */
+int arachne_occ_batch(arachne_index_t *idx, int64_t n, const uint64_t *k, const uint64_t *l, uint64_t *cnt);
+/* bwt_sa (bwa/bwt.c:86-96) */
+int arachne_sa_batch(arachne_index_t *idx, int64_t n, const uint64_t *k, uint64_t *sa);
+/* mem_collect_intv (bwa/bwamem.c:114-162) per read: CSR of {x0,x1,x2,info} */
+int arachne_seed_batch(arachne_index_t *idx, const arachne_mem_opt_t *opt, int64_t n_reads, const uint8_t *seq, const int64_t *seq_off,
+                       int64_t *intv_off, uint64_t *intv, int64_t intv_cap);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
