@@ -21,6 +21,7 @@
 #include "index.cuh"
 #include "smem.cuh"
 #include "warp_ctx.cuh"
+#include "cigar.cuh"
 
 namespace arachne {
 
@@ -202,6 +203,139 @@ __global__ void k_gather_regs(int n_reads, const unsigned long long* __restrict_
     }
 }
 
+// ------------------------------------------------------------------------------------------------ k_rescue
+// Warp per pair.  Most pairs already hold a consistent hit for every anchor, in which case mem_matesw returns before
+// touching anything (bwamem_pair.c:118-124) and the lists stay where k_extend left them.  Only pairs that really run
+// a rescue SW get private copies with room to grow (each mem_matesw call adds at most one region).
+constexpr unsigned long long RESC_FLAG = 1ull << 63;
+
+__device__ __forceinline__ bool matesw_would_run(const RefView& ref, const PeStat pes[4], const AlnReg& a, const AlnReg* ma, int n_ma) {
+    int skip[4];
+    for (int r = 0; r < 4; ++r) skip[r] = pes[r].failed ? 1 : 0;
+    for (int i = 0; i < n_ma; ++i) {
+        int64_t dist;
+        int r = infer_dir(ref.l_pac, a.rb, ma[i].rb, &dist);
+        if (dist >= pes[r].low && dist <= pes[r].high) skip[r] = 1;
+    }
+    return skip[0] + skip[1] + skip[2] + skip[3] != 4;
+}
+
+__global__ void __launch_bounds__(EXT_WARPS * 32) k_rescue(MemOpt opt, RefView ref, int score_delta, const uint8_t* __restrict__ seq,
+                                                           const int64_t* __restrict__ off, int n_pairs, const unsigned long long* __restrict__ sa_off,
+                                                           AlnReg* regs, int* n_regs, unsigned long long* reg_loc, AlnReg* resc,
+                                                           unsigned long long resc_cap, unsigned long long* resc_used, uint8_t* win, int win_cap,
+                                                           uint64_t* blists, int bcap, unsigned int* next, Counters* cnt) {
+    const int lane = threadIdx.x & 31;
+    const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    WarpCtx ctx;
+    ctx.lane = lane; ctx.cells = nullptr; ctx.z = nullptr; ctx.z_cap = 0; ctx.blist = blists + (size_t)gw * bcap; ctx.bcap = bcap;
+    uint8_t* rbuf = win + (size_t)gw * win_cap;
+    PeStat pes[4];
+    gobwa_pestat(pes);
+    for (;;) {
+        int p = 0;
+        if (lane == 0) p = (int)atomicAdd(next, 1u);
+        p = __shfl_sync(FULL, p, 0);
+        if (p >= n_pairs) break;
+        const int ra = 2 * p, rb = 2 * p + 1;
+        const int l1 = (int)(off[ra + 1] - off[ra]), l2 = (int)(off[rb + 1] - off[rb]);
+        AlnReg* r1 = regs + sa_off[ra];
+        AlnReg* r2 = regs + sa_off[rb];
+        int n1 = n_regs[ra], n2 = n_regs[rb];
+        if (lane == 0) { reg_loc[ra] = sa_off[ra]; reg_loc[rb] = sa_off[rb]; }
+        // would any mem_matesw call get past its early return?  (lanes split the anchors)
+        int best1 = 0, best2 = 0;
+        for (int i = 0; i < n1; ++i) best1 = best1 > r1[i].score ? best1 : r1[i].score;
+        for (int i = 0; i < n2; ++i) best2 = best2 > r2[i].score ? best2 : r2[i].score;
+        bool need = false;
+        if (l1 > 0)
+            for (int i = 0, num = 0; i < n2 && num < 50 && !need; ++i)
+                if (r2[i].score >= best2 - score_delta) { ++num; need = matesw_would_run(ref, pes, r2[i], r1, n1); }
+        if (l2 > 0)
+            for (int i = 0, num = 0; i < n1 && num < 50 && !need; ++i)
+                if (r1[i].score >= best1 - score_delta) { ++num; need = matesw_would_run(ref, pes, r1[i], r2, n2); }
+        if (!need) continue;
+        const int cap1 = n1 + 50, cap2 = n2 + 50;
+        unsigned long long pos = 0;
+        if (lane == 0) pos = atomicAdd(resc_used, (unsigned long long)(cap1 + cap2));
+        pos = __shfl_sync(FULL, pos, 0);
+        if (pos + cap1 + cap2 > resc_cap) { if (lane == 0) raise(cnt, -100, p); continue; }
+        AlnReg* c1 = resc + pos;
+        AlnReg* c2 = c1 + cap1;
+        for (int i = lane; i < n1; i += 32) c1[i] = r1[i];
+        for (int i = lane; i < n2; i += 32) c2[i] = r2[i];
+        __syncwarp();
+        ctx.lsw_err = 0;
+        int rc = pair_rescue(ctx, opt, ref, score_delta, l1, seq + off[ra], l2, seq + off[rb], c1, &n1, cap1, c2, &n2, cap2, rbuf, win_cap);
+        if (rc < 0 || ctx.lsw_err) { if (lane == 0) raise(cnt, ARACHNE_ERR_OVERFLOW, p); continue; }
+        if (lane == 0) {
+            n_regs[ra] = n1; n_regs[rb] = n2;
+            reg_loc[ra] = RESC_FLAG | pos; reg_loc[rb] = RESC_FLAG | (pos + cap1);
+        }
+    }
+}
+
+__global__ void k_gather_regs2(int n_reads, const unsigned long long* __restrict__ reg_loc, const unsigned long long* __restrict__ reg_off,
+                               const AlnReg* __restrict__ regs, const AlnReg* __restrict__ resc, AlnReg* out, int* reg_read) {
+    const int lane = threadIdx.x & 31;
+    for (int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; r < n_reads; r += (gridDim.x * blockDim.x) >> 5) {
+        unsigned long long loc = reg_loc[r];
+        const AlnReg* sp = (loc & RESC_FLAG) ? resc + (loc & ~RESC_FLAG) : regs + loc;
+        const uint32_t* src = reinterpret_cast<const uint32_t*>(sp);
+        uint32_t* dst = reinterpret_cast<uint32_t*>(out + reg_off[r]);
+        int nr = (int)(reg_off[r + 1] - reg_off[r]);
+        int nw = nr * (int)(sizeof(AlnReg) / 4);
+        for (int k = lane; k < nw; k += 32) dst[k] = src[k];
+        for (int k = lane; k < nr; k += 32) reg_read[reg_off[r] + k] = r;
+    }
+}
+
+__global__ void k_init_loc(int n_reads, const unsigned long long* __restrict__ sa_off, unsigned long long* reg_loc) {
+    for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < n_reads; r += gridDim.x * blockDim.x) reg_loc[r] = sa_off[r];
+}
+
+// ------------------------------------------------------------------------------------------------ k_cigar
+__global__ void __launch_bounds__(EXT_WARPS * 32) k_cigar(MemOpt opt, RefView ref, const uint8_t* __restrict__ seq, const int64_t* __restrict__ off,
+                                                          long n_regs, const AlnReg* __restrict__ regs, const int* __restrict__ reg_read, AlnRec* alns,
+                                                          uint32_t* cig_pool, unsigned long long cig_cap, int32_t* mm_pool, unsigned long long mm_cap,
+                                                          unsigned long long* used /*[0]=cigar [1]=mm*/, uint8_t* win, int win_cap, uint8_t* zbuf,
+                                                          long z_cap, uint32_t* cig_scr, int cig_scr_cap, int32_t* mm_scr, int mm_scr_cap,
+                                                          unsigned int* next, Counters* cnt) {
+    const int lane = threadIdx.x & 31;
+    const long gw = (blockIdx.x * (long)blockDim.x + threadIdx.x) >> 5;
+    WarpCtx ctx;
+    ctx.lane = lane; ctx.cells = nullptr; ctx.z = zbuf + gw * z_cap; ctx.z_cap = z_cap;
+    uint8_t* rbuf = win + gw * (long)win_cap;
+    uint32_t* cig = cig_scr + gw * (long)cig_scr_cap;
+    int32_t* mm = mm_scr + gw * (long)mm_scr_cap;
+    for (;;) {
+        long g = 0;
+        if (lane == 0) g = (long)atomicAdd(next, 1u);
+        g = __shfl_sync(FULL, g, 0);
+        if (g >= n_regs) break;
+        const int r = reg_read[g];
+        const int len = (int)(off[r + 1] - off[r]);
+        const AlnReg ar = regs[g];
+        AlnRec a;
+        // traceback matrix must fit: n_col * tlen with n_col <= qlen
+        if ((long)(ar.qe - ar.qb) * (ar.re - ar.rb) > z_cap || 2 * len > mm_scr_cap) { if (lane == 0) raise(cnt, ARACHNE_ERR_OVERFLOW, r); continue; }
+        int rc = reg2aln(ctx, opt, ref, len, seq + off[r], ar, &a, cig, cig_scr_cap, mm, rbuf, win_cap);
+        if (rc < 0) { if (lane == 0) raise(cnt, ARACHNE_ERR_OVERFLOW, r); continue; }
+        unsigned long long co = 0, mo = 0;
+        if (lane == 0) {
+            co = atomicAdd(&used[0], (unsigned long long)a.n_cigar);
+            mo = atomicAdd(&used[1], (unsigned long long)(2 * a.n_mm));
+        }
+        co = __shfl_sync(FULL, co, 0); mo = __shfl_sync(FULL, mo, 0);
+        if (co + a.n_cigar > cig_cap || mo + 2 * a.n_mm > mm_cap) { if (lane == 0) raise(cnt, -101, r); continue; }
+        for (int k = lane; k < a.n_cigar; k += 32) cig_pool[co + k] = cig[k];
+        for (int k = lane; k < a.n_mm; k += 32) { mm_pool[mo + k] = mm[k]; mm_pool[mo + a.n_mm + k] = mm[len + k]; }
+        a.cigar_off = (int64_t)co; a.mm_off = (int64_t)mo;
+        if (lane == 0) alns[g] = a;
+        __syncwarp();
+    }
+}
+
 // ------------------------------------------------------------------------------------------------ stage kernels
 __global__ void k_occ(FMIndex fm, long n, const uint64_t* k, const uint64_t* l, uint64_t* cnt) {
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x)
@@ -363,7 +497,7 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
     const int sms = sm_count(idx->device);
     cudaStream_t st;
     AR_CUDA(cudaStreamCreate(&st));
-    cudaEvent_t ev[8];
+    cudaEvent_t ev[8];  // seed | sa | chain | extend | rescue | gather | cigar
     for (auto& e : ev) cudaEventCreate(&e);
 
     auto* out = new arachne_batch_out_t();
@@ -375,9 +509,10 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
 
     DevBuf d_seq, d_off, d_scratch, d_arena, d_misc, d_intv_off, d_intv_n, d_nsa, d_sa_off, d_rows, d_cnt, d_tmp;
     DevBuf d_seeds, d_kseeds, d_chains, d_nodes, d_order, d_kept, d_nchain, d_nkseed, d_srt, d_regs, d_nregs, d_win, d_reg_off, d_out;
+    DevBuf d_nregs_bak, d_reg_loc, d_blist, d_resc, d_reg_read, d_z, d_cig_scr, d_mm_scr, d_alns, d_cig, d_mm;
     std::vector<DevBuf*> all = {&d_seq, &d_off, &d_scratch, &d_arena, &d_misc, &d_intv_off, &d_intv_n, &d_nsa, &d_sa_off, &d_rows, &d_cnt, &d_tmp,
                                 &d_seeds, &d_kseeds, &d_chains, &d_nodes, &d_order, &d_kept, &d_nchain, &d_nkseed, &d_srt, &d_regs, &d_nregs,
-                                &d_win, &d_reg_off, &d_out};
+                                &d_win, &d_reg_off, &d_out, &d_nregs_bak, &d_reg_loc, &d_blist, &d_resc, &d_reg_read, &d_z, &d_cig_scr, &d_mm_scr, &d_alns, &d_cig, &d_mm};
     auto cleanup = [&]() {
         for (auto* b : all) b->release();
         for (auto& e : ev) cudaEventDestroy(e);
@@ -471,6 +606,41 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
                                                     d_misc.as<unsigned int>(), d_cnt.as<Counters>());
     AR_TRY(cudaGetLastError());
     cudaEventRecord(ev[4], st);
+    int stages = in->stages ? in->stages : (ARACHNE_STAGE_REGIONS | ARACHNE_STAGE_RESCUE | ARACHNE_STAGE_CIGAR);
+    // ---- mate rescue ----
+    AR_ALLOC(d_reg_loc, (n_reads + 1) * 8);
+    k_init_loc<<<sms * 2, 256, 0, st>>>((int)n_reads, d_sa_off.as<unsigned long long>(), d_reg_loc.as<unsigned long long>());
+    AR_TRY(cudaGetLastError());
+    if (stages & ARACHNE_STAGE_RESCUE) {
+        const int bcap = win_cap;  // one row-maximum entry per target row at most
+        AR_ALLOC(d_blist, (size_t)ext_blocks * EXT_WARPS * bcap * 8);
+        unsigned long long resc_cap = (unsigned long long)n_reads * (getenv("ARACHNE_RESC_MULT") ? atoi(getenv("ARACHNE_RESC_MULT")) : 4) + 4096;
+        AR_TRY(cudaMemcpyAsync(&hc, d_cnt.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
+        AR_TRY(cudaStreamSynchronize(st));
+        if (hc.err != 0) { set_error("internal scratch overflow (code %d) at read %d", hc.err, hc.err_read); return fail(ARACHNE_ERR_OVERFLOW); }
+        AR_ALLOC(d_nregs_bak, (n_reads + 1) * 4);
+        AR_TRY(cudaMemcpyAsync(d_nregs_bak.p, d_nregs.p, (n_reads + 1) * 4, cudaMemcpyDeviceToDevice, st));
+        for (int attempt = 0;; ++attempt) {
+            AR_ALLOC(d_resc, resc_cap * sizeof(AlnReg));
+            AR_TRY(cudaMemsetAsync(d_misc.p, 0, 64, st));
+            k_rescue<<<ext_blocks, EXT_WARPS * 32, 0, st>>>(opt, idx->ref, in->score_delta, d_seq.as<uint8_t>(), d_off.as<int64_t>(), (int)in->n_pairs,
+                                                            d_sa_off.as<unsigned long long>(), d_regs.as<AlnReg>(), d_nregs.as<int>(),
+                                                            d_reg_loc.as<unsigned long long>(), d_resc.as<AlnReg>(), resc_cap,
+                                                            d_misc.as<unsigned long long>() + 1, d_win.as<uint8_t>(), win_cap, d_blist.as<uint64_t>(), bcap,
+                                                            d_misc.as<unsigned int>(), d_cnt.as<Counters>());
+            AR_TRY(cudaGetLastError());
+            AR_TRY(cudaMemcpyAsync(&hc, d_cnt.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
+            AR_TRY(cudaStreamSynchronize(st));
+            if (hc.err == 0) break;
+            if (hc.err != -100 || attempt >= 4) { set_error("rescue: scratch overflow (code %d) at pair %d", hc.err, hc.err_read); return fail(ARACHNE_ERR_OVERFLOW); }
+            // the rescue arena was too small: regions in place are untouched (copy-on-write), so the stage can simply be re-run
+            resc_cap *= 8;
+            AR_TRY(cudaMemcpyAsync(d_nregs.p, d_nregs_bak.p, (n_reads + 1) * 4, cudaMemcpyDeviceToDevice, st));
+            AR_TRY(cudaMemsetAsync(d_cnt.as<char>() + offsetof(Counters, err), 0, 8, st));
+            k_init_loc<<<sms * 2, 256, 0, st>>>((int)n_reads, d_sa_off.as<unsigned long long>(), d_reg_loc.as<unsigned long long>());
+        }
+    }
+    cudaEventRecord(ev[5], st);
     // ---- compact regions ----
     cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, d_nregs.as<int>(), d_reg_off.as<unsigned long long>(), (int)n_reads + 1, st);
     AR_ALLOC(d_tmp, tmp_bytes + 16);
@@ -481,14 +651,55 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
     AR_TRY(cudaStreamSynchronize(st));
     if (hc.err != 0) { set_error("internal scratch overflow (code %d) at read %d", hc.err, hc.err_read); return fail(ARACHNE_ERR_OVERFLOW); }
     AR_ALLOC(d_out, (total_regs + 1) * sizeof(AlnReg));
-    k_gather_regs<<<sms * 4, 256, 0, st>>>((int)n_reads, d_sa_off.as<unsigned long long>(), d_reg_off.as<unsigned long long>(), d_regs.as<AlnReg>(),
-                                            d_out.as<AlnReg>());
+    AR_ALLOC(d_reg_read, (total_regs + 1) * 4);
+    k_gather_regs2<<<sms * 4, 256, 0, st>>>((int)n_reads, d_reg_loc.as<unsigned long long>(), d_reg_off.as<unsigned long long>(), d_regs.as<AlnReg>(),
+                                             d_resc.as<AlnReg>(), d_out.as<AlnReg>(), d_reg_read.as<int>());
     AR_TRY(cudaGetLastError());
     priv->regs.resize(total_regs);
     static_assert(sizeof(unsigned long long) == sizeof(int64_t), "");
     AR_TRY(cudaMemcpyAsync(priv->reg_off.data(), d_reg_off.p, (n_reads + 1) * 8, cudaMemcpyDeviceToHost, st));
     if (total_regs) AR_TRY(cudaMemcpyAsync(priv->regs.data(), d_out.p, total_regs * sizeof(AlnReg), cudaMemcpyDeviceToHost, st));
-    cudaEventRecord(ev[5], st);
+    cudaEventRecord(ev[6], st);
+    // ---- CIGAR + candidate statistics ----
+    if ((stages & ARACHNE_STAGE_CIGAR) && total_regs) {
+        const int cg_blocks = sms * 4;
+        const long nw = (long)cg_blocks * EXT_WARPS;
+        const long z_cap = (long)maxlen * (maxlen + 1024);
+        const int cig_scr_cap = 2 * maxlen + 64, mm_scr_cap = 2 * maxlen + 8;
+        AR_ALLOC(d_z, (size_t)nw * z_cap);
+        AR_ALLOC(d_cig_scr, (size_t)nw * cig_scr_cap * 4);
+        AR_ALLOC(d_mm_scr, (size_t)nw * mm_scr_cap * 4);
+        AR_ALLOC(d_win, (size_t)std::max<long>(nw, (long)ext_blocks * EXT_WARPS) * win_cap);
+        AR_ALLOC(d_alns, (total_regs + 1) * sizeof(AlnRec));
+        unsigned long long cig_cap = total_regs * 4 + 4096, mm_cap = total_regs * 12 + 4096;
+        for (int attempt = 0;; ++attempt) {
+            AR_ALLOC(d_cig, cig_cap * 4);
+            AR_ALLOC(d_mm, mm_cap * 4);
+            AR_TRY(cudaMemsetAsync(d_misc.p, 0, 64, st));
+            k_cigar<<<cg_blocks, EXT_WARPS * 32, 0, st>>>(opt, idx->ref, d_seq.as<uint8_t>(), d_off.as<int64_t>(), (long)total_regs, d_out.as<AlnReg>(),
+                                                          d_reg_read.as<int>(), d_alns.as<AlnRec>(), d_cig.as<uint32_t>(), cig_cap, d_mm.as<int32_t>(), mm_cap,
+                                                          d_misc.as<unsigned long long>() + 1, d_win.as<uint8_t>(), win_cap, d_z.as<uint8_t>(), z_cap,
+                                                          d_cig_scr.as<uint32_t>(), cig_scr_cap, d_mm_scr.as<int32_t>(), mm_scr_cap,
+                                                          d_misc.as<unsigned int>(), d_cnt.as<Counters>());
+            AR_TRY(cudaGetLastError());
+            AR_TRY(cudaMemcpyAsync(&hc, d_cnt.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
+            AR_TRY(cudaStreamSynchronize(st));
+            if (hc.err == 0) break;
+            if (hc.err != -101 || attempt >= 4) { set_error("cigar: scratch overflow (code %d) at read %d", hc.err, hc.err_read); return fail(ARACHNE_ERR_OVERFLOW); }
+            cig_cap *= 4; mm_cap *= 4;
+            AR_TRY(cudaMemsetAsync(d_cnt.as<char>() + offsetof(Counters, err), 0, 8, st));
+        }
+        unsigned long long used[2] = {0, 0};
+        AR_TRY(cudaMemcpyAsync(used, d_misc.as<unsigned long long>() + 1, 16, cudaMemcpyDeviceToHost, st));
+        AR_TRY(cudaStreamSynchronize(st));
+        priv->alns.resize(total_regs); priv->cigar.resize(used[0] + 1); priv->mm.resize(used[1] + 1);
+        AR_TRY(cudaMemcpyAsync(priv->alns.data(), d_alns.p, total_regs * sizeof(AlnRec), cudaMemcpyDeviceToHost, st));
+        if (used[0]) AR_TRY(cudaMemcpyAsync(priv->cigar.data(), d_cig.p, used[0] * 4, cudaMemcpyDeviceToHost, st));
+        if (used[1]) AR_TRY(cudaMemcpyAsync(priv->mm.data(), d_mm.p, used[1] * 4, cudaMemcpyDeviceToHost, st));
+        out->n_cigar = (int64_t)used[0]; out->n_mm = (int64_t)used[1];
+        out->alns = priv->alns.data(); out->cigar = priv->cigar.data(); out->mm = priv->mm.data();
+    }
+    cudaEventRecord(ev[7], st);
     AR_TRY(cudaStreamSynchronize(st));
 
     out->n_regs = (int64_t)total_regs;
@@ -502,7 +713,9 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
     cudaEventElapsedTime(&out->ms_sa, ev[1], ev[2]);
     cudaEventElapsedTime(&out->ms_chain, ev[2], ev[3]);
     cudaEventElapsedTime(&out->ms_extend, ev[3], ev[4]);
-    cudaEventElapsedTime(&out->ms_total, ev[0], ev[5]);
+    cudaEventElapsedTime(&out->ms_rescue, ev[4], ev[5]);
+    cudaEventElapsedTime(&out->ms_cigar, ev[6], ev[7]);
+    cudaEventElapsedTime(&out->ms_total, ev[0], ev[7]);
     cleanup();
     *out_ = out;
     return ARACHNE_OK;

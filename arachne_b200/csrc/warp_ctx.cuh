@@ -15,6 +15,7 @@
 // reference's direction byte per cell for the traceback.
 #pragma once
 #include "extend.cuh"
+#include "rescue.cuh"
 
 namespace arachne {
 
@@ -240,6 +241,125 @@ __device__ __noinline__ int ksw_global_warp(const MemOpt& opt, int qlen, const u
     return __shfl_sync(FULL, mine, qlen / CPL);
 }
 
+
+// ---- local SW with the reference's striped-SIMD semantics (ksw_u8 / ksw_i16 / ksw_align2, bwa/ksw.c:111-365) ----
+// Lane k of the first P lanes plays element k of the SSE2 vector (P = 16 for u8, 8 for i16); vector j, element k holds
+// query position j + k*slen.  The recurrence, the saturation, the lazy-F rounds (with their early exit), the row-maximum
+// list `b` and the query-end tie-break are the reference's, so scores, ends, score2 and starts are bit-identical.
+constexpr int LSW_MAXSEG = 32;  // slen <= 32 for qlen <= 255 at P = 8
+
+struct LswOut { int score, te, qe, score2, te2; };
+
+template <class QF, class TF>
+__device__ __noinline__ LswOut striped_pass_warp(const MemOpt& opt, int bytes, int qlen, QF qf, int tlen, TF tf, int xtra, uint64_t* blist,
+                                                 int bcap, int* err) {
+    const int lane = threadIdx.x & 31;
+    const int P = bytes == 1 ? 16 : 8, HI = bytes == 1 ? 255 : 32767;
+    const unsigned pmask = bytes == 1 ? 0xffffu : 0xffu;
+    const bool on = lane < P;
+    const int slen = (qlen + P - 1) / P;
+    const int mb = opt.b > 1 ? opt.b : 1;
+    const int shift = bytes == 1 ? (mb > -opt.a ? mb : -opt.a) : 0;
+    int top = opt.a > -opt.b ? opt.a : -opt.b; top = top > -1 ? top : -1;
+    const int e_del = opt.e_del, e_ins = opt.e_ins, oe_del = opt.o_del + opt.e_del, oe_ins = opt.o_ins + opt.e_ins;
+    const int sa = opt.a, snb = -opt.b;
+    short H[2][LSW_MAXSEG], E[LSW_MAXSEG], Hm[LSW_MAXSEG];
+    unsigned char qb[LSW_MAXSEG];
+    for (int j = 0; j < slen; ++j) {
+        int pos = j + lane * slen;
+        H[0][j] = H[1][j] = 0; E[j] = 0; Hm[j] = 0;
+        qb[j] = (on && pos < qlen) ? (unsigned char)qf(pos) : (unsigned char)255;
+    }
+    const int minsc = (xtra & KSW_XSUBO) ? xtra & 0xffff : 0x10000, endsc = (xtra & KSW_XSTOP) ? xtra & 0xffff : 0x10000;
+    int gmax = 0, te = -1, n_b = 0, cur = 0;
+    auto sat = [HI](int v) { return v < 0 ? 0 : (v > HI ? HI : v); };
+    for (int i = 0; i < tlen; ++i) {
+        const int tb = tf(i);
+        short* H0 = H[cur];
+        short* H1 = H[cur ^ 1];
+        int F = 0, mx = 0;
+        int hv = __shfl_up_sync(FULL, (int)H0[slen - 1], 1);
+        if (lane == 0) hv = 0;
+        for (int j = 0; j < slen; ++j) {
+            int q = qb[j];
+            int sc = q == 255 ? 0 : sw_score(sa, snb, tb, q);
+            int h;
+            if (bytes == 1) h = sat(sat(hv + sc + shift) - shift);
+            else { h = hv + sc; h = h > 32767 ? 32767 : (h < -32768 ? -32768 : h); }
+            int e = E[j];
+            h = __vimax3_s32(h, e, F);
+            mx = mx > h ? mx : h;
+            H1[j] = (short)h;
+            int x = sat(h - oe_del);
+            e = sat(e - e_del); e = e > x ? e : x;
+            E[j] = (short)e;
+            x = sat(h - oe_ins);
+            F = sat(F - e_ins); F = F > x ? F : x;
+            hv = H0[j];
+        }
+        bool done = false;
+        for (int kk = 0; kk < 16 && !done; ++kk) {  // lazy F
+            F = __shfl_up_sync(FULL, F, 1);
+            if (lane == 0) F = 0;
+            for (int j = 0; j < slen; ++j) {
+                int h = H1[j];
+                h = h > F ? h : F;
+                H1[j] = (short)h;
+                h = sat(h - oe_ins);
+                F = sat(F - e_ins);
+                unsigned any = __ballot_sync(FULL, on && F > h) & pmask;
+                if (!any) { done = true; break; }
+            }
+        }
+        int rowmax = __reduce_max_sync(FULL, on ? mx : 0);
+        if (rowmax >= minsc) {
+            if (lane == 0) {
+                if (n_b == 0 || (int32_t)blist[n_b - 1] + 1 != i) {
+                    if (n_b < bcap) blist[n_b] = (uint64_t)rowmax << 32 | (uint32_t)i;
+                    else *err = 1;
+                    ++n_b;
+                } else if ((int)(blist[n_b - 1] >> 32) < rowmax) blist[n_b - 1] = (uint64_t)rowmax << 32 | (uint32_t)i;
+            }
+            n_b = __shfl_sync(FULL, n_b, 0);
+        }
+        bool brk = false;
+        if (rowmax > gmax) {
+            gmax = rowmax; te = i;
+            for (int j = 0; j < slen; ++j) Hm[j] = H1[j];
+            if ((bytes == 1 && gmax + shift >= 255) || gmax >= endsc) brk = true;
+        }
+        if (brk) break;
+        cur ^= 1;
+    }
+    LswOut r;
+    r.score = (bytes == 1 && gmax + shift >= 255) ? 255 : gmax;
+    r.te = te; r.qe = -1; r.score2 = -1; r.te2 = -1;
+    if (bytes == 2 || r.score != 255) {
+        int best = -1, bpos = 0x7fffffff;
+        if (on)
+            for (int j = 0; j < slen; ++j) {
+                int v = Hm[j], pos = j + lane * slen;
+                if (v > best || (v == best && pos < bpos)) { best = v; bpos = pos; }
+            }
+        int gbest = __reduce_max_sync(FULL, best);
+        int gpos = __reduce_min_sync(FULL, best == gbest ? bpos : 0x7fffffff);
+        r.qe = gpos;
+        __syncwarp();
+        if (n_b > 0) {
+            int k = (r.score + top - 1) / top, low = te - k, high = te + k, s2 = -1, t2 = -1;
+            if (lane == 0)
+                for (int i = 0; i < n_b && i < bcap; ++i) {
+                    int e = (int32_t)blist[i];
+                    if ((e < low || e > high) && (int)(blist[i] >> 32) > s2) { s2 = (int)(blist[i] >> 32); t2 = e; }
+                }
+            r.score2 = __shfl_sync(FULL, s2, 0);
+            r.te2 = __shfl_sync(FULL, t2, 0);
+        }
+    }
+    __syncwarp();
+    return r;
+}
+
 #define AR_CPL_DISPATCH(ncols, CALL)                 \
     switch (((ncols) + 31) >> 5) {                   \
         case 0: case 1: { constexpr int CPL_ = 1; CALL; } break; \
@@ -259,6 +379,9 @@ struct WarpCtx {
     unsigned long long* cells;  // per-warp DP cell counter (roofline accounting), may be null
     uint8_t* z;                 // traceback scratch for ksw_global (n_col * tlen bytes), may be null
     long z_cap;
+    uint64_t* blist = nullptr;  // row-maximum list scratch for ksw_local
+    int bcap = 0;
+    int lsw_err = 0;
 
     AR_D bool leader() const { return lane == 0; }
     AR_D void sync() const { __syncwarp(); }
@@ -276,6 +399,24 @@ struct WarpCtx {
         AR_CPL_DISPATCH(qlen + 1, r = ksw_extend_warp<CPL_>(opt, qlen, q, qs, tlen, t, ts, w, end_bonus, zdrop, h0, qle, tle, gtle, gscore,
                                                             max_off, lane == 0 ? cells : nullptr));
         return r;
+    }
+
+
+    // ksw_align2 with the mate optionally reverse-complemented on the fly (bwamem_pair.c:131-135)
+    AR_D void ksw_local(const MemOpt& opt, int qlen, const uint8_t* ms, int is_rev, int tlen, const uint8_t* t, int xtra, LocalAln* out) {
+        const int bytes = (xtra & KSW_XBYTE) ? 1 : 2;
+        auto qf = [=](int p) -> int { if (!is_rev) return ms[p]; int c = ms[qlen - 1 - p]; return c < 4 ? 3 - c : 4; };
+        auto tf = [=](int i) -> int { return t[i]; };
+        LswOut r = striped_pass_warp(opt, bytes, qlen, qf, tlen, tf, xtra, blist, bcap, &lsw_err);
+        out->score = r.score; out->te = r.te; out->qe = r.qe; out->score2 = r.score2; out->te2 = r.te2; out->tb = -1; out->qb = -1;
+        if ((xtra & KSW_XSTART) == 0 || ((xtra & KSW_XSUBO) && r.score < (xtra & 0xffff))) return;
+        // start coordinates: same recurrence over the reversed prefixes; the target keeps its full length with only
+        // its first te+1 symbols reversed (ksw.c:357-360)
+        const int qe = r.qe, te = r.te;
+        auto qf2 = [=](int p) -> int { return qf(qe - p); };
+        auto tf2 = [=](int i) -> int { return i <= te ? t[te - i] : t[i]; };
+        LswOut rr = striped_pass_warp(opt, bytes, qe + 1, qf2, tlen, tf2, KSW_XSTOP | r.score, blist, bcap, &lsw_err);
+        if (r.score == rr.score) { out->tb = r.te - rr.te; out->qb = r.qe - rr.qe; }
     }
 
     // score only when cigar == nullptr; otherwise also backtracks into cigar (len<<4|op, already in forward order)

@@ -9,12 +9,15 @@
 #include <vector>
 #include "../../arachne_b200/csrc/smem.cuh"
 #include "../../arachne_b200/csrc/extend.cuh"
+#include "../../arachne_b200/csrc/rescue.cuh"
+#include "../../arachne_b200/csrc/cigar.cuh"
 #include "../../include/arachne_cuda.h"
 
 extern "C" {
 typedef struct { int a, b, o_del, e_del, o_ins, e_ins; } orc_sc_t;
 int orc_extend(const orc_sc_t*, int, const uint8_t*, int, const uint8_t*, int, int, int, int, int*, uint64_t*);
 int orc_global(const orc_sc_t*, int, const uint8_t*, int, const uint8_t*, int, uint32_t*, int, int*);
+void orc_local(const orc_sc_t*, int, const uint8_t*, int, const uint8_t*, int, int*);
 int arachne_opts_default_host(arachne_mem_opt_t* o);
 }
 
@@ -57,7 +60,18 @@ struct HostCtx {
         for (int i = 0; i < qlen; ++i) qq[i] = q[(long)i * qs];
         for (int i = 0; i < tlen; ++i) tt[i] = t[(long)i * ts];
         orc_sc_t s = {o.a, o.b, o.o_del, o.e_del, o.o_ins, o.e_ins};
-        return orc_global(&s, qlen, qq.data(), tlen, tt.data(), w, cigar, cap, nc);
+        int n = 0;
+        int r = orc_global(&s, qlen, qq.data(), tlen, tt.data(), w, cigar, cap, &n);
+        if (nc) *nc = n;
+        return r;
+    }
+    void ksw_local(const MemOpt& o, int qlen, const uint8_t* ms, int is_rev, int tlen, const uint8_t* t, int xtra, LocalAln* out) {
+        std::vector<uint8_t> qq(qlen + 1);
+        for (int i = 0; i < qlen; ++i) qq[i] = is_rev ? (ms[qlen - 1 - i] < 4 ? 3 - ms[qlen - 1 - i] : 4) : ms[i];
+        orc_sc_t s = {o.a, o.b, o.o_del, o.e_del, o.o_ins, o.e_ins};
+        int o7[7];
+        orc_local(&s, qlen, qq.data(), tlen, t, xtra, o7);
+        out->score = o7[0]; out->te = o7[1]; out->qe = o7[2]; out->score2 = o7[3]; out->te2 = o7[4]; out->tb = o7[5]; out->qb = o7[6];
     }
 };
 
@@ -185,5 +199,37 @@ int hs_align1(void* h_, int len, const uint8_t* seq, arachne_alnreg_t* out, int 
     for (int i = 0; i < m && i < cap_out; ++i) memcpy(&out[i], &av[i], sizeof(AlnReg));
     if (counters) { counters[0] = ctx.calls; counters[1] = ctx.cells; counters[2] = nsa; }
     return m;
+}
+
+// GoBwaMemMateSW: regions of both reads after rescue
+int hs_pair(void* h_, int l1, const uint8_t* s1, int l2, const uint8_t* s2, int score_delta, arachne_alnreg_t* o1, int* n1_, arachne_alnreg_t* o2, int* n2_, int cap) {
+    HostIndex* h = (HostIndex*)h_; MemOpt opt; default_opts(opt);
+    std::vector<AlnReg> r1(cap + 64), r2(cap + 64);
+    int n1 = l1 > 0 ? hs_align1(h_, l1, s1, (arachne_alnreg_t*)r1.data(), cap, nullptr) : 0;
+    int n2 = l2 > 0 ? hs_align1(h_, l2, s2, (arachne_alnreg_t*)r2.data(), cap, nullptr) : 0;
+    if (n1 < 0 || n2 < 0) return -1;
+    HostCtx ctx;
+    int win_cap = 2 * (l1 > l2 ? l1 : l2) + 1024 + 4 * opt.w;
+    std::vector<uint8_t> win(win_cap);
+    int rc = pair_rescue(ctx, opt, h->ref, score_delta, l1, s1, l2, s2, r1.data(), &n1, cap + 64, r2.data(), &n2, cap + 64, win.data(), win_cap);
+    if (rc < 0) return rc;
+    memcpy(o1, r1.data(), (size_t)n1 * sizeof(AlnReg)); memcpy(o2, r2.data(), (size_t)n2 * sizeof(AlnReg));
+    *n1_ = n1; *n2_ = n2;
+    return 0;
+}
+
+// mem_reg2aln + GetAlignments walk; mm gets n_mm ref loci then n_mm read offsets
+int hs_reg2aln(void* h_, int len, const uint8_t* seq, const arachne_alnreg_t* reg, arachne_aln_t* out, uint32_t* cigar, int cap, int32_t* mm) {
+    HostIndex* h = (HostIndex*)h_; MemOpt opt; default_opts(opt);
+    HostCtx ctx;
+    int win_cap = 2 * len + 1024 + 4 * opt.w;
+    std::vector<uint8_t> win(win_cap);
+    std::vector<int32_t> m(2 * len + 8);
+    AlnRec a;
+    int rc = reg2aln(ctx, opt, h->ref, len, seq, *(const AlnReg*)reg, &a, cigar, cap, m.data(), win.data(), win_cap);
+    if (rc < 0) return rc;
+    memcpy(out, &a, sizeof(a));
+    for (int i = 0; i < a.n_mm; ++i) { mm[i] = m[i]; mm[a.n_mm + i] = m[len + i]; }
+    return 0;
 }
 }

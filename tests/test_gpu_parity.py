@@ -88,3 +88,24 @@ def test_index_and_regions_parity(A, R, workdir, name):
     assert np.array_equal(res["reg_off"], ref["reg_off"])
     assert res["regs"].tobytes() == ref["regs"].tobytes()
     assert res["counters"]["n_ext_cells"] > 0 and res["counters"]["n_lf_steps"] > 0
+
+
+@pytest.mark.parametrize("name", ["rand1m", "rep600k"])
+def test_rescue_and_cigar_parity(A, R, workdir, name):
+    """GoBwaMemMateSW (with mate rescue) + GoBwaSmithWaterman for every candidate, against the reference's own code."""
+    fa, ctg, rs = util.make_dataset(name, workdir, damaged=True)
+    R.load(fa); A.load_index(fa)
+    res = A.align_batch(rs.seq, rs.off, rs.bc_off, stages=7)
+    ref = R.batch(rs.seq, rs.off, rescue=True, cigar=True, threads=8)
+    norescue = R.batch(rs.seq, rs.off, rescue=False, cigar=False, threads=8)
+    assert ref["regs"].tobytes() != norescue["regs"].tobytes(), "dataset does not exercise rescue"
+    assert np.array_equal(res["reg_off"], ref["reg_off"])
+    assert res["regs"].tobytes() == ref["regs"].tobytes()
+    a, e = res["alns"], ref["aln"]  # e: pos rid is_rev NM n_cigar cigar_off score sub
+    assert np.array_equal(a["pos"], e[:, 0]) and np.array_equal(a["rid"], e[:, 1]) and np.array_equal(a["is_rev"], e[:, 2])
+    assert np.array_equal(a["nm"], e[:, 3]) and np.array_equal(a["n_cigar"], e[:, 4])
+    assert np.array_equal(a["score"], e[:, 6]) and np.array_equal(a["sub"], e[:, 7])
+    for i in range(len(a)):
+        got = res["cigar"][a["cigar_off"][i]:a["cigar_off"][i] + a["n_cigar"][i]]
+        exp = ref["cigar"][e[i, 5]:e[i, 5] + e[i, 4]]
+        assert np.array_equal(got, exp), i

@@ -84,6 +84,18 @@ def pack(seqs):
     return (np.concatenate(seqs).astype(np.uint8) if len(seqs) and off[-1] else np.zeros(0, np.uint8)), off
 
 
+def damage(rs, frac, sub, seed):
+    """Wreck one mate of a fraction of pairs so that only mate rescue can place it."""
+    g = np.random.default_rng(seed); seq = rs.seq.copy()
+    for p in range(rs.n_pairs):
+        if g.random() < frac:
+            i = 2 * p + int(g.integers(0, 2)); a, b = rs.off[i], rs.off[i + 1]
+            m = g.random(b - a) < sub
+            seq[a:b][m] = (seq[a:b][m] + g.integers(1, 4, int(m.sum()))) & 3
+    rs.seq = seq
+    return rs
+
+
 DATASETS = {
     # name: (reference kwargs, read kwargs)
     "rand1m": (dict(total_len=1_000_000, n_contigs=1, seed=1), dict(n_barcodes=60, seed=11)),
@@ -92,7 +104,7 @@ DATASETS = {
 }
 
 
-def make_dataset(name, workdir):
+def make_dataset(name, workdir, damaged=False):
     """Reference FASTA + BWA index (built with the reference's own `bwa index` code from oracle/_ref) + simulated reads."""
     from oracle.refbwa import RefBwa
     rk, qk = DATASETS[name]
@@ -102,4 +114,6 @@ def make_dataset(name, workdir):
         S.write_fasta(fa, ctg)
         RefBwa().build_index(fa)
     rs = S.simulate_linked_reads(ctg, **qk)
+    if damaged:
+        rs = damage(rs, 0.3, 0.11, 5)
     return fa, ctg, rs
