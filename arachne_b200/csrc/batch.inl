@@ -1,0 +1,308 @@
+// Host orchestration of one batch (included inside pipeline.cu's extern "C" block).
+// All device arenas live in the index handle's Workspace and are reused by later batches; results are copied into
+// pinned host buffers recycled through arachne_batch_free.
+
+static Workspace* get_ws(arachne_index_t* idx) {
+    if (!idx->ws) {
+        auto* w = new Workspace();
+        if (w->init()) { w->destroy(); delete w; return nullptr; }
+        idx->ws = w;
+    }
+    return reinterpret_cast<Workspace*>(idx->ws);
+}
+
+int arachne_index_set_stream(arachne_index_t* idx, void* cuda_stream, int use) {
+    if (!idx) { set_error("arachne_index_set_stream: null index"); return ARACHNE_ERR_ARG; }
+    std::lock_guard<std::mutex> g(idx->mu);
+    idx->user_stream = cuda_stream;
+    idx->has_user_stream = use != 0;
+    return ARACHNE_OK;
+}
+
+int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, const arachne_batch_in_t* in, arachne_batch_out_t** out_) {
+    if (!idx || !in || !out_ || !in->seq_off || (!in->seq && in->n_pairs > 0)) { set_error("arachne_align_batch: null argument"); return ARACHNE_ERR_ARG; }
+    int rc = validate_opts(opt_);
+    if (rc) return rc;
+    MemOpt opt;
+    memcpy(&opt, opt_, sizeof(opt));
+    const bool in_dev = (in->flags & ARACHNE_IN_DEVICE) != 0, out_dev = (in->flags & ARACHNE_OUT_DEVICE) != 0;
+    const int64_t n_reads = in->n_pairs * 2;
+    if (n_reads < 0 || n_reads > 0x7fffffff / 2) { set_error("batch too large"); return ARACHNE_ERR_ARG; }
+    int64_t n_bases = 0;
+    int maxlen = 0;
+    if (in_dev) {  // device-resident input: lengths cannot be checked on the host; the caller states the bounds
+        if (in->max_read_len <= 0 || in->max_read_len > ARACHNE_MAX_READ_LEN || in->n_bases < 0) {
+            set_error("ARACHNE_IN_DEVICE needs max_read_len in 1..%d and n_bases", ARACHNE_MAX_READ_LEN); return ARACHNE_ERR_ARG;
+        }
+        maxlen = in->max_read_len; n_bases = in->n_bases;
+    } else {
+        n_bases = n_reads ? in->seq_off[n_reads] : 0;
+        for (int64_t i = 0; i < n_reads; ++i) {
+            int64_t l = in->seq_off[i + 1] - in->seq_off[i];
+            if (l < 0 || l > ARACHNE_MAX_READ_LEN) { set_error("read %lld has length %lld; supported 0..%d", (long long)i, (long long)l, ARACHNE_MAX_READ_LEN); return ARACHNE_ERR_ARG; }
+            if (l > maxlen) maxlen = (int)l;
+        }
+    }
+    std::lock_guard<std::mutex> guard(idx->mu);
+    AR_CUDA(cudaSetDevice(idx->device));
+    Workspace* wsp = get_ws(idx);
+    if (!wsp) { set_error("cannot create the batch workspace (stream/events/pinned memory)"); return ARACHNE_ERR_CUDA; }
+    Workspace& W = *wsp;
+    const int sms = sm_count(idx->device);
+    cudaStream_t st = idx->has_user_stream ? reinterpret_cast<cudaStream_t>(idx->user_stream) : W.own_stream;
+    cudaEvent_t* ev = W.ev;  // seed | sa | chain | extend | rescue | gather | cigar | end
+
+    auto* out = new arachne_batch_out_t();
+    memset(out, 0, sizeof(*out));
+    BatchPriv* priv = nullptr;
+    if (!W.pool.empty()) { priv = W.pool.back(); W.pool.pop_back(); } else priv = new BatchPriv();
+    priv->owner = idx;
+    out->priv = priv;
+    out->n_reads = n_reads;
+    auto fail = [&](int code) { W.pool.push_back(priv); delete out; return code; };
+#define AR_TRY(x) do { if ((x) != cudaSuccess) { set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #x, cudaGetErrorString(cudaGetLastError())); return fail(ARACHNE_ERR_CUDA); } } while (0)
+#define AR_ALLOC(buf, bytes) do { if ((buf).ensure(bytes)) { set_error("out of device memory allocating %zu bytes (%s)", (size_t)(bytes), #buf); return fail(ARACHNE_ERR_CUDA); } } while (0)
+#define AR_PIN(buf, bytes) do { if ((buf).ensure(bytes)) { set_error("out of pinned host memory allocating %zu bytes (%s)", (size_t)(bytes), #buf); return fail(ARACHNE_ERR_CUDA); } } while (0)
+
+    AR_PIN(priv->reg_off, (n_reads + 1) * 8);
+    if (n_reads == 0) { priv->reg_off.as<int64_t>()[0] = 0; out->reg_off = priv->reg_off.as<int64_t>(); *out_ = out; return ARACHNE_OK; }
+
+    const int L1 = maxlen + 1;
+    const int seed_threads = sms * 512;
+    const uint8_t* d_seq; const int64_t* d_off;
+    if (in_dev) { d_seq = in->seq; d_off = in->seq_off; }
+    else {
+        AR_ALLOC(W.d_seq, n_bases + 16);
+        AR_ALLOC(W.d_off, (n_reads + 1) * 8);
+        AR_TRY(cudaMemcpyAsync(W.d_seq.p, in->seq, n_bases, cudaMemcpyHostToDevice, st));
+        AR_TRY(cudaMemcpyAsync(W.d_off.p, in->seq_off, (n_reads + 1) * 8, cudaMemcpyHostToDevice, st));
+        d_seq = W.d_seq.as<uint8_t>(); d_off = W.d_off.as<int64_t>();
+    }
+    AR_ALLOC(W.d_scratch, (size_t)seed_threads * 7 * L1 * sizeof(Intv));
+    AR_ALLOC(W.d_misc, 64);
+    AR_ALLOC(W.d_intv_off, n_reads * 8);
+    AR_ALLOC(W.d_intv_n, n_reads * 4);
+    AR_ALLOC(W.d_nsa, (n_reads + 1) * 4);
+    AR_ALLOC(W.d_sa_off, (n_reads + 1) * 8);
+    AR_ALLOC(W.d_cnt, sizeof(Counters));
+    AR_ALLOC(W.d_nchain, n_reads * 4);
+    AR_ALLOC(W.d_nkseed, n_reads * 4);
+    AR_ALLOC(W.d_nregs, (n_reads + 1) * 4);
+    AR_ALLOC(W.d_reg_off, (n_reads + 1) * 8);
+    AR_TRY(cudaMemsetAsync(W.d_cnt.p, 0, sizeof(Counters), st));
+    AR_TRY(cudaMemsetAsync(W.d_nsa.p, 0, (n_reads + 1) * 4, st));
+    AR_TRY(cudaMemsetAsync(W.d_nregs.p, 0, (n_reads + 1) * 4, st));
+
+    int nl = 0;  // kernels launched by this batch
+    Counters& hc = *W.h_cnt;
+    unsigned long long* hs = W.h_scalars;
+    unsigned long long arena_cap = (unsigned long long)n_reads * 24 + 1024;
+    // ---- seeding (retry with a larger interval arena if it overflows) ----
+    cudaEventRecord(ev[0], st);
+    for (int attempt = 0;; ++attempt) {
+        AR_ALLOC(W.d_arena, arena_cap * sizeof(Intv));
+        AR_TRY(cudaMemsetAsync(W.d_misc.p, 0, 64, st));
+        ++nl;
+        k_seed<<<seed_threads / 128, 128, 0, st>>>(idx->fm, opt, d_seq, d_off, (int)n_reads, maxlen, W.d_scratch.as<Intv>(), L1,
+                                                    W.d_arena.as<Intv>(), arena_cap, W.d_misc.as<unsigned long long>(), W.d_intv_off.as<unsigned long long>(),
+                                                    W.d_intv_n.as<int>(), W.d_nsa.as<unsigned int>(), W.d_cnt.as<Counters>());
+        AR_TRY(cudaGetLastError());
+        AR_TRY(cudaMemcpyAsync(&hc, W.d_cnt.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
+        AR_TRY(cudaStreamSynchronize(st));
+        if (hc.err == 0) break;
+        if (hc.err == ARACHNE_ERR_ARG) { set_error("read %d is longer than the stated max_read_len %d", hc.err_read, maxlen); return fail(ARACHNE_ERR_ARG); }
+        if (attempt >= 3) { set_error("seeding: interval arena/scratch overflow at read %d", hc.err_read); return fail(ARACHNE_ERR_OVERFLOW); }
+        arena_cap *= 4;
+        AR_TRY(cudaMemsetAsync(W.d_cnt.p, 0, sizeof(Counters), st));
+    }
+    cudaEventRecord(ev[1], st);
+    // ---- seeds per read -> offsets ----
+    size_t tmp_bytes = 0;
+    cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, W.d_nsa.as<unsigned int>(), W.d_sa_off.as<unsigned long long>(), (int)n_reads + 1, st);
+    AR_ALLOC(W.d_tmp, tmp_bytes + 16);
+    nl += 2;  // cub scan = init + scan kernels
+    AR_TRY(cub::DeviceScan::ExclusiveSum(W.d_tmp.p, tmp_bytes, W.d_nsa.as<unsigned int>(), W.d_sa_off.as<unsigned long long>(), (int)n_reads + 1, st));
+    AR_TRY(cudaMemcpyAsync(&hs[0], W.d_sa_off.as<unsigned long long>() + n_reads, 8, cudaMemcpyDeviceToHost, st));
+    AR_TRY(cudaStreamSynchronize(st));
+    const unsigned long long total_sa = hs[0];
+    const size_t tsa = (size_t)total_sa + 8;
+    AR_ALLOC(W.d_rows, tsa * 8);
+    AR_ALLOC(W.d_seeds, tsa * sizeof(Seed));
+    AR_ALLOC(W.d_kseeds, tsa * sizeof(Seed));
+    AR_ALLOC(W.d_chains, tsa * sizeof(Chain));
+    AR_ALLOC(W.d_nodes, (tsa / 4 + 4 * (size_t)n_reads + 8) * sizeof(BNode));
+    AR_ALLOC(W.d_order, tsa * 4);
+    AR_ALLOC(W.d_kept, tsa * 4);
+    AR_ALLOC(W.d_srt, tsa * 8);
+    AR_ALLOC(W.d_regs, tsa * sizeof(AlnReg));
+    ++nl;
+    k_expand<<<sms * 4, 256, 0, st>>>(opt, (int)n_reads, W.d_arena.as<Intv>(), W.d_intv_off.as<unsigned long long>(), W.d_intv_n.as<int>(),
+                                       W.d_sa_off.as<unsigned long long>(), W.d_rows.as<uint64_t>());
+    AR_TRY(cudaGetLastError());
+    ++nl;
+    k_sa<<<sms * 8, 256, 0, st>>>(idx->fm, total_sa, W.d_rows.as<uint64_t>(), W.d_cnt.as<Counters>());
+    AR_TRY(cudaGetLastError());
+    cudaEventRecord(ev[2], st);
+    // ---- chaining ----
+    ChainBufs cb;
+    cb.seeds = W.d_seeds.as<Seed>(); cb.kseeds = W.d_kseeds.as<Seed>(); cb.chains = W.d_chains.as<Chain>(); cb.nodes = W.d_nodes.as<BNode>();
+    cb.order = W.d_order.as<int32_t>(); cb.kept = W.d_kept.as<int32_t>(); cb.n_chain = W.d_nchain.as<int>(); cb.n_kseed = W.d_nkseed.as<int>();
+    ++nl;
+    k_chain<<<sms * 8, 128, 0, st>>>(opt, idx->ref, d_off, (int)n_reads, W.d_arena.as<Intv>(), W.d_intv_off.as<unsigned long long>(),
+                                      W.d_intv_n.as<int>(), W.d_sa_off.as<unsigned long long>(), W.d_rows.as<uint64_t>(), cb, W.d_cnt.as<Counters>());
+    AR_TRY(cudaGetLastError());
+    cudaEventRecord(ev[3], st);
+    // ---- extension + dedup ----
+    const int ext_blocks = sms * 8;
+    const int win_cap = 2 * maxlen + 1024 + 4 * opt.w;
+    const long cg_warps = (long)sms * 4 * EXT_WARPS;
+    AR_ALLOC(W.d_win, (size_t)std::max<long>(cg_warps, (long)ext_blocks * EXT_WARPS) * win_cap);
+    AR_TRY(cudaMemsetAsync(W.d_misc.p, 0, 64, st));
+    ++nl;
+    k_extend<<<ext_blocks, EXT_WARPS * 32, 0, st>>>(opt, idx->ref, d_seq, d_off, (int)n_reads, W.d_sa_off.as<unsigned long long>(),
+                                                    cb, W.d_srt.as<uint64_t>(), W.d_regs.as<AlnReg>(), W.d_nregs.as<int>(), W.d_win.as<uint8_t>(), win_cap,
+                                                    W.d_misc.as<unsigned int>(), W.d_cnt.as<Counters>());
+    AR_TRY(cudaGetLastError());
+    cudaEventRecord(ev[4], st);
+    int stages = in->stages ? in->stages : (ARACHNE_STAGE_REGIONS | ARACHNE_STAGE_RESCUE | ARACHNE_STAGE_CIGAR);
+    // ---- mate rescue ----
+    AR_ALLOC(W.d_reg_loc, (n_reads + 1) * 8);
+    ++nl;
+    k_init_loc<<<sms * 2, 256, 0, st>>>((int)n_reads, W.d_sa_off.as<unsigned long long>(), W.d_reg_loc.as<unsigned long long>());
+    AR_TRY(cudaGetLastError());
+    if (stages & ARACHNE_STAGE_RESCUE) {
+        const int bcap = win_cap;  // one row-maximum entry per target row at most
+        AR_ALLOC(W.d_blist, (size_t)ext_blocks * EXT_WARPS * bcap * 8);
+        unsigned long long resc_cap = (unsigned long long)n_reads * (getenv("ARACHNE_RESC_MULT") ? atoi(getenv("ARACHNE_RESC_MULT")) : 4) + 4096;
+        AR_TRY(cudaMemcpyAsync(&hc, W.d_cnt.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
+        AR_TRY(cudaStreamSynchronize(st));
+        if (hc.err != 0) { set_error("internal scratch overflow (code %d) at read %d", hc.err, hc.err_read); return fail(ARACHNE_ERR_OVERFLOW); }
+        AR_ALLOC(W.d_nregs_bak, (n_reads + 1) * 4);
+        AR_TRY(cudaMemcpyAsync(W.d_nregs_bak.p, W.d_nregs.p, (n_reads + 1) * 4, cudaMemcpyDeviceToDevice, st));
+        for (int attempt = 0;; ++attempt) {
+            AR_ALLOC(W.d_resc, resc_cap * sizeof(AlnReg));
+            AR_TRY(cudaMemsetAsync(W.d_misc.p, 0, 64, st));
+            ++nl;
+            k_rescue<<<ext_blocks, EXT_WARPS * 32, 0, st>>>(opt, idx->ref, in->score_delta, d_seq, d_off, (int)in->n_pairs,
+                                                            W.d_sa_off.as<unsigned long long>(), W.d_regs.as<AlnReg>(), W.d_nregs.as<int>(),
+                                                            W.d_reg_loc.as<unsigned long long>(), W.d_resc.as<AlnReg>(), resc_cap,
+                                                            W.d_misc.as<unsigned long long>() + 1, W.d_win.as<uint8_t>(), win_cap, W.d_blist.as<uint64_t>(), bcap,
+                                                            W.d_misc.as<unsigned int>(), W.d_cnt.as<Counters>());
+            AR_TRY(cudaGetLastError());
+            AR_TRY(cudaMemcpyAsync(&hc, W.d_cnt.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
+            AR_TRY(cudaStreamSynchronize(st));
+            if (hc.err == 0) break;
+            if (hc.err != -100 || attempt >= 4) { set_error("rescue: scratch overflow (code %d) at pair %d", hc.err, hc.err_read); return fail(ARACHNE_ERR_OVERFLOW); }
+            // the rescue arena was too small: regions in place are untouched (copy-on-write), so the stage can simply be re-run
+            resc_cap *= 8;
+            AR_TRY(cudaMemcpyAsync(W.d_nregs.p, W.d_nregs_bak.p, (n_reads + 1) * 4, cudaMemcpyDeviceToDevice, st));
+            AR_TRY(cudaMemsetAsync(W.d_cnt.as<char>() + offsetof(Counters, err), 0, 8, st));
+            ++nl;
+            k_init_loc<<<sms * 2, 256, 0, st>>>((int)n_reads, W.d_sa_off.as<unsigned long long>(), W.d_reg_loc.as<unsigned long long>());
+        }
+    }
+    cudaEventRecord(ev[5], st);
+    // ---- compact regions ----
+    cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, W.d_nregs.as<int>(), W.d_reg_off.as<unsigned long long>(), (int)n_reads + 1, st);
+    AR_ALLOC(W.d_tmp, tmp_bytes + 16);
+    nl += 2;  // cub scan = init + scan kernels
+    AR_TRY(cub::DeviceScan::ExclusiveSum(W.d_tmp.p, tmp_bytes, W.d_nregs.as<int>(), W.d_reg_off.as<unsigned long long>(), (int)n_reads + 1, st));
+    AR_TRY(cudaMemcpyAsync(&hs[1], W.d_reg_off.as<unsigned long long>() + n_reads, 8, cudaMemcpyDeviceToHost, st));
+    AR_TRY(cudaMemcpyAsync(&hc, W.d_cnt.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
+    AR_TRY(cudaStreamSynchronize(st));
+    const unsigned long long total_regs = hs[1];
+    if (hc.err != 0) { set_error("internal scratch overflow (code %d) at read %d", hc.err, hc.err_read); return fail(ARACHNE_ERR_OVERFLOW); }
+    AR_ALLOC(W.d_out, (total_regs + 1) * sizeof(AlnReg));
+    AR_ALLOC(W.d_reg_read, (total_regs + 1) * 4);
+    ++nl;
+    k_gather_regs2<<<sms * 4, 256, 0, st>>>((int)n_reads, W.d_reg_loc.as<unsigned long long>(), W.d_reg_off.as<unsigned long long>(), W.d_regs.as<AlnReg>(),
+                                             W.d_resc.as<AlnReg>(), W.d_out.as<AlnReg>(), W.d_reg_read.as<int>());
+    AR_TRY(cudaGetLastError());
+    static_assert(sizeof(unsigned long long) == sizeof(int64_t), "");
+    if (!out_dev) {
+        AR_PIN(priv->regs, (total_regs + 1) * sizeof(AlnReg));
+        AR_TRY(cudaMemcpyAsync(priv->reg_off.p, W.d_reg_off.p, (n_reads + 1) * 8, cudaMemcpyDeviceToHost, st));
+        if (total_regs) AR_TRY(cudaMemcpyAsync(priv->regs.p, W.d_out.p, total_regs * sizeof(AlnReg), cudaMemcpyDeviceToHost, st));
+    }
+    cudaEventRecord(ev[6], st);
+    // ---- CIGAR + candidate statistics ----
+    if ((stages & ARACHNE_STAGE_CIGAR) && total_regs) {
+        const int cg_blocks = sms * 4;
+        const long nw = (long)cg_blocks * EXT_WARPS;
+        const long z_cap = (long)maxlen * (maxlen + 1024);
+        const int cig_scr_cap = 2 * maxlen + 64, mm_scr_cap = 2 * maxlen + 8;
+        AR_ALLOC(W.d_z, (size_t)nw * z_cap);
+        AR_ALLOC(W.d_cig_scr, (size_t)nw * cig_scr_cap * 4);
+        AR_ALLOC(W.d_mm_scr, (size_t)nw * mm_scr_cap * 4);
+        AR_ALLOC(W.d_alns, (total_regs + 1) * sizeof(AlnRec));
+        unsigned long long cig_cap = total_regs * 4 + 4096, mm_cap = total_regs * 12 + 4096;
+        for (int attempt = 0;; ++attempt) {
+            AR_ALLOC(W.d_cig, cig_cap * 4);
+            AR_ALLOC(W.d_mm, mm_cap * 4);
+            AR_TRY(cudaMemsetAsync(W.d_misc.p, 0, 64, st));
+            ++nl;
+            k_cigar<<<cg_blocks, EXT_WARPS * 32, 0, st>>>(opt, idx->ref, d_seq, d_off, (long)total_regs, W.d_out.as<AlnReg>(),
+                                                          W.d_reg_read.as<int>(), W.d_alns.as<AlnRec>(), W.d_cig.as<uint32_t>(), cig_cap, W.d_mm.as<int32_t>(), mm_cap,
+                                                          W.d_misc.as<unsigned long long>() + 1, W.d_win.as<uint8_t>(), win_cap, W.d_z.as<uint8_t>(), z_cap,
+                                                          W.d_cig_scr.as<uint32_t>(), cig_scr_cap, W.d_mm_scr.as<int32_t>(), mm_scr_cap,
+                                                          W.d_misc.as<unsigned int>(), W.d_cnt.as<Counters>());
+            AR_TRY(cudaGetLastError());
+            AR_TRY(cudaMemcpyAsync(&hc, W.d_cnt.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
+            AR_TRY(cudaMemcpyAsync(&hs[2], W.d_misc.as<unsigned long long>() + 1, 16, cudaMemcpyDeviceToHost, st));
+            AR_TRY(cudaStreamSynchronize(st));
+            if (hc.err == 0) break;
+            if (hc.err != -101 || attempt >= 4) { set_error("cigar: scratch overflow (code %d) at read %d", hc.err, hc.err_read); return fail(ARACHNE_ERR_OVERFLOW); }
+            cig_cap *= 4; mm_cap *= 4;
+            AR_TRY(cudaMemsetAsync(W.d_cnt.as<char>() + offsetof(Counters, err), 0, 8, st));
+        }
+        const unsigned long long used0 = hs[2], used1 = hs[3];
+        out->n_cigar = (int64_t)used0; out->n_mm = (int64_t)used1;
+        if (!out_dev) {
+            AR_PIN(priv->alns, (total_regs + 1) * sizeof(AlnRec)); AR_PIN(priv->cigar, (used0 + 1) * 4); AR_PIN(priv->mm, (used1 + 1) * 4);
+            AR_TRY(cudaMemcpyAsync(priv->alns.p, W.d_alns.p, total_regs * sizeof(AlnRec), cudaMemcpyDeviceToHost, st));
+            if (used0) AR_TRY(cudaMemcpyAsync(priv->cigar.p, W.d_cig.p, used0 * 4, cudaMemcpyDeviceToHost, st));
+            if (used1) AR_TRY(cudaMemcpyAsync(priv->mm.p, W.d_mm.p, used1 * 4, cudaMemcpyDeviceToHost, st));
+            out->alns = priv->alns.as<arachne_aln_t>(); out->cigar = priv->cigar.as<uint32_t>(); out->mm = priv->mm.as<int32_t>();
+        }
+    }
+    cudaEventRecord(ev[7], st);
+    AR_TRY(cudaStreamSynchronize(st));
+
+    out->n_regs = (int64_t)total_regs;
+    if (!out_dev) { out->reg_off = priv->reg_off.as<int64_t>(); out->regs = priv->regs.as<arachne_alnreg_t>(); }
+    out->n_occ_lookups = hc.occ;
+    out->n_occ_blocks = hc.occ_blocks;
+    out->n_sa_lookups = total_sa;
+    out->n_lf_steps = hc.lf_steps;
+    out->n_ext_calls = hc.ext_calls;
+    out->n_ext_cells = hc.ext_cells;
+    out->n_glb_cells = hc.glb_cells;
+    out->n_kernel_launches = nl;
+    cudaEventElapsedTime(&out->ms_seed, ev[0], ev[1]);
+    cudaEventElapsedTime(&out->ms_sa, ev[1], ev[2]);
+    cudaEventElapsedTime(&out->ms_chain, ev[2], ev[3]);
+    cudaEventElapsedTime(&out->ms_extend, ev[3], ev[4]);
+    cudaEventElapsedTime(&out->ms_rescue, ev[4], ev[5]);
+    cudaEventElapsedTime(&out->ms_cigar, ev[6], ev[7]);
+    cudaEventElapsedTime(&out->ms_total, ev[0], ev[7]);
+    *out_ = out;
+    return ARACHNE_OK;
+#undef AR_TRY
+#undef AR_ALLOC
+#undef AR_PIN
+}
+
+void arachne_batch_free(arachne_batch_out_t* out) {
+    if (!out) return;
+    auto* priv = reinterpret_cast<BatchPriv*>(out->priv);
+    if (priv) {
+        arachne_index_t* idx = priv->owner;
+        bool pooled = false;
+        if (idx) {
+            std::lock_guard<std::mutex> g(idx->mu);
+            if (idx->ws) { reinterpret_cast<Workspace*>(idx->ws)->pool.push_back(priv); pooled = true; }
+        }
+        if (!pooled) { priv->release(); delete priv; }
+    }
+    delete out;
+}

@@ -85,8 +85,13 @@ AR_HD void fm_occ4(const FMIndex& fm, uint64_t k, uint64_t cnt[4]) {
 }
 
 // bwt_2occ4, bwa/bwt.c:189-220.  *n_blocks receives the number of 64-byte lines touched (roofline accounting).
-AR_HD void fm_2occ4(const FMIndex& fm, uint64_t k, uint64_t l, uint64_t ck[4], uint64_t cl[4]) {
+struct OccStat {  // roofline accounting: bwt_2occ4 calls and the 64-byte blocks they touch
+    unsigned calls = 0, blocks = 0;
+};
+
+AR_HD void fm_2occ4(const FMIndex& fm, uint64_t k, uint64_t l, uint64_t ck[4], uint64_t cl[4], OccStat* st = nullptr) {
     uint64_t k_ = k - (k >= fm.primary), l_ = l - (l >= fm.primary);
+    if (st) { ++st->calls; st->blocks += (k == (uint64_t)-1 || l == (uint64_t)-1) ? (k != l ? 1 : 0) : ((l_ >> 7) != (k_ >> 7) ? 2 : 1); }
     if ((l_ >> 7) != (k_ >> 7) || k == (uint64_t)-1 || l == (uint64_t)-1) {
         fm_occ4(fm, k, ck);
         fm_occ4(fm, l, cl);
@@ -107,11 +112,11 @@ AR_HD void fm_set_intv(const FMIndex& fm, int c, Intv& ik) {
 
 // bwt_extend, bwa/bwt.c:262-275.  is_back=1 extends to the left of the match (prepends a base), 0 appends the
 // complement on the reverse strand.  x(!is_back) is the coordinate that is looked up.
-AR_HD void fm_extend(const FMIndex& fm, const Intv& ik, Intv ok[4], int is_back) {
+AR_HD void fm_extend(const FMIndex& fm, const Intv& ik, Intv ok[4], int is_back, OccStat* st = nullptr) {
     uint64_t tk[4], tl[4];
     uint64_t xa = is_back ? ik.x0 : ik.x1;  // x[!is_back]
     uint64_t xb = is_back ? ik.x1 : ik.x0;  // x[is_back]
-    fm_2occ4(fm, xa - 1, xa - 1 + ik.x2, tk, tl);
+    fm_2occ4(fm, xa - 1, xa - 1 + ik.x2, tk, tl, st);
     uint64_t na[4], nb[4], ns[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {

@@ -7,6 +7,7 @@
 #include <vector>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include "fmindex.cuh"
 #include "../../include/arachne_cuda.h"
 
@@ -25,6 +26,13 @@ struct arachne_index {
     int64_t l_pac = 0;
     // host copy of the packed reference (GetSeq-style host queries, compat shims)
     std::vector<uint8_t> h_pac;
+    // per-index batch workspace (device arenas, pinned result pools, stream, events): created on first use, reused by
+    // every later batch; calls on one handle serialise on `mu` (the reference's workers share one read-only index and
+    // bring their own scratch, gobwa.go passes buf=NULL -- here the scratch is the handle's, so batches queue up)
+    std::mutex mu;
+    void* ws = nullptr;
+    void* user_stream = nullptr;
+    bool has_user_stream = false;
 };
 
 namespace arachne {
@@ -77,7 +85,10 @@ inline int index_load(const char* prefix_, int device, arachne_index** out) {
     fm.seq_len = fm.L2[4];
     size_t bwt_bytes = bwt.size() - 40;
     size_t n_blocks = (fm.seq_len + 127) / 128 + 1;  // bwt_bwtupdate_core writes one trailing count block
-    if (bwt_bytes < (n_blocks - 1) * 64 + 32) { delete idx; set_error("%s.bwt is not an occ-interleaved BWT (run `bwa index`)", prefix.c_str()); return ARACHNE_ERR_IO; }
+    // bwt_bwtupdate_core (bwtindex.c:151-173): 32 bytes of counts per started 128-symbol block, 4 bytes per started
+    // 16-symbol word, one trailing 32-byte count record
+    const size_t want_bytes = ((fm.seq_len + 127) / 128) * 32 + ((fm.seq_len + 15) / 16) * 4 + 32;
+    if (bwt_bytes < want_bytes) { delete idx; set_error("%s.bwt is not an occ-interleaved BWT (run `bwa index`)", prefix.c_str()); return ARACHNE_ERR_IO; }
     const uint64_t* sh = reinterpret_cast<const uint64_t*>(sa.data());
     if (sh[0] != fm.primary || sh[6] != fm.seq_len) { delete idx; set_error("SA-BWT inconsistency in %s", prefix.c_str()); return ARACHNE_ERR_IO; }
     fm.sa_intv = (int)sh[5];

@@ -37,7 +37,7 @@ static_assert(sizeof(MemOpt) == sizeof(arachne_mem_opt_t), "MemOpt layout");
 static_assert(sizeof(AlnReg) == sizeof(arachne_alnreg_t), "AlnReg layout");
 
 struct Counters {
-    unsigned long long occ, sa_lookups, lf_steps, ext_calls, ext_cells, glb_cells;
+    unsigned long long occ, occ_blocks, sa_lookups, lf_steps, ext_calls, ext_cells, glb_cells;
     int err;       // first internal error code (negative) raised by a kernel
     int err_read;
 };
@@ -48,18 +48,20 @@ __device__ __forceinline__ void raise(Counters* c, int code, int read) {
 
 // ------------------------------------------------------------------------------------------------ k_seed
 __global__ void __launch_bounds__(128) k_seed(FMIndex fm, MemOpt opt, const uint8_t* __restrict__ seq, const int64_t* __restrict__ off,
-                                              int n_reads, Intv* scratch, int L1, Intv* arena, unsigned long long arena_cap,
+                                              int n_reads, int maxlen, Intv* scratch, int L1, Intv* arena, unsigned long long arena_cap,
                                               unsigned long long* arena_used, unsigned long long* intv_off, int* intv_n,
                                               unsigned int* n_sa, Counters* cnt) {
     const int tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
     Intv* sc = scratch + (size_t)tid * 7 * L1;
     Intv* out = sc + 3 * L1;
     const int cap = 4 * L1;
+    OccStat ost;
     for (int r = tid; r < n_reads; r += nth) {
         const int len = (int)(off[r + 1] - off[r]);
         const uint8_t* s = seq + off[r];
         int n = 0;
-        if (len >= opt.min_seed_len) n = collect_intv(opt, fm, len, s, out, cap, sc);
+        if (len > maxlen) { raise(cnt, ARACHNE_ERR_ARG, r); intv_off[r] = 0; intv_n[r] = 0; n_sa[r] = 0; continue; }
+        if (len >= opt.min_seed_len) n = collect_intv(opt, fm, len, s, out, cap, sc, &ost);
         if (n < 0) { raise(cnt, ARACHNE_ERR_OVERFLOW, r); n = 0; }
         unsigned long long pos = 0;
         unsigned int nsa = 0;
@@ -73,6 +75,8 @@ __global__ void __launch_bounds__(128) k_seed(FMIndex fm, MemOpt opt, const uint
         }
         intv_off[r] = pos; intv_n[r] = n; n_sa[r] = nsa;
     }
+    unsigned c = __reduce_add_sync(0xffffffffu, ost.calls), b = __reduce_add_sync(0xffffffffu, ost.blocks);
+    if ((threadIdx.x & 31) == 0 && c) { atomicAdd(&cnt->occ, (unsigned long long)c); atomicAdd(&cnt->occ_blocks, (unsigned long long)b); }
 }
 
 // ------------------------------------------------------------------------------------------------ k_expand / k_sa
@@ -416,12 +420,60 @@ static int sm_count(int device) {
 
 using namespace arachne;
 
+// pinned host buffer (results land here so the device->host copies are true async DMA)
+struct PinBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    int ensure(size_t bytes) {
+        if (bytes <= cap) return 0;
+        if (p) cudaFreeHost(p);
+        p = nullptr; cap = 0;
+        size_t want = bytes + bytes / 4 + 4096;
+        if (cudaMallocHost(&p, want) != cudaSuccess) { p = nullptr; return -1; }
+        cap = want;
+        return 0;
+    }
+    void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
 struct BatchPriv {
-    std::vector<int64_t> reg_off;
-    std::vector<arachne_alnreg_t> regs;
-    std::vector<arachne_aln_t> alns;
-    std::vector<uint32_t> cigar;
-    std::vector<int32_t> mm;
+    PinBuf reg_off, regs, alns, cigar, mm;
+    arachne_index_t* owner = nullptr;
+    void release() { reg_off.release(); regs.release(); alns.release(); cigar.release(); mm.release(); }
+};
+
+// Per-index workspace: every device arena of the batch pipeline, grown on demand and kept between batches.
+struct Workspace {
+    DevBuf d_seq, d_off, d_scratch, d_arena, d_misc, d_intv_off, d_intv_n, d_nsa, d_sa_off, d_rows, d_cnt, d_tmp;
+    DevBuf d_seeds, d_kseeds, d_chains, d_nodes, d_order, d_kept, d_nchain, d_nkseed, d_srt, d_regs, d_nregs, d_win, d_reg_off, d_out;
+    DevBuf d_nregs_bak, d_reg_loc, d_blist, d_resc, d_reg_read, d_z, d_cig_scr, d_mm_scr, d_alns, d_cig, d_mm;
+    cudaStream_t own_stream = nullptr;
+    cudaEvent_t ev[8] = {};
+    Counters* h_cnt = nullptr;              // pinned
+    unsigned long long* h_scalars = nullptr;  // pinned, 8 slots
+    std::vector<BatchPriv*> pool;           // recycled pinned result sets
+    std::vector<DevBuf*> all() {
+        return {&d_seq, &d_off, &d_scratch, &d_arena, &d_misc, &d_intv_off, &d_intv_n, &d_nsa, &d_sa_off, &d_rows, &d_cnt, &d_tmp,
+                &d_seeds, &d_kseeds, &d_chains, &d_nodes, &d_order, &d_kept, &d_nchain, &d_nkseed, &d_srt, &d_regs, &d_nregs,
+                &d_win, &d_reg_off, &d_out, &d_nregs_bak, &d_reg_loc, &d_blist, &d_resc, &d_reg_read, &d_z, &d_cig_scr, &d_mm_scr, &d_alns, &d_cig, &d_mm};
+    }
+    int init() {
+        if (cudaStreamCreateWithFlags(&own_stream, cudaStreamNonBlocking) != cudaSuccess) return -1;
+        for (auto& e : ev) if (cudaEventCreate(&e) != cudaSuccess) return -1;
+        if (cudaMallocHost((void**)&h_cnt, sizeof(Counters)) != cudaSuccess) return -1;
+        if (cudaMallocHost((void**)&h_scalars, 64) != cudaSuccess) return -1;
+        return 0;
+    }
+    void destroy() {
+        for (auto* b : all()) b->release();
+        for (auto* p : pool) { p->release(); delete p; }
+        pool.clear();
+        for (auto& e : ev) if (e) cudaEventDestroy(e);
+        if (own_stream) cudaStreamDestroy(own_stream);
+        if (h_cnt) cudaFreeHost(h_cnt);
+        if (h_scalars) cudaFreeHost(h_scalars);
+    }
 };
 
 extern "C" {
@@ -439,6 +491,7 @@ int arachne_index_load(const char* prefix, int device, arachne_index_t** out) { 
 void arachne_index_free(arachne_index_t* idx) {
     if (!idx) return;
     cudaSetDevice(idx->device);
+    if (idx->ws) { auto* w = reinterpret_cast<Workspace*>(idx->ws); w->destroy(); delete w; idx->ws = nullptr; }
     cudaFree(idx->d_bwt); cudaFree(idx->d_sa); cudaFree(idx->d_pac); cudaFree(idx->d_contigs);
     delete idx;
 }
@@ -478,254 +531,7 @@ int arachne_opts_default(arachne_mem_opt_t* o) {  // mem_opt_init, bwa/bwamem.c:
 }
 
 // ---------------------------------------------------------------------------------------------- batch
-int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, const arachne_batch_in_t* in, arachne_batch_out_t** out_) {
-    if (!idx || !in || !out_ || !in->seq_off || (!in->seq && in->n_pairs > 0)) { set_error("arachne_align_batch: null argument"); return ARACHNE_ERR_ARG; }
-    int rc = validate_opts(opt_);
-    if (rc) return rc;
-    MemOpt opt;
-    memcpy(&opt, opt_, sizeof(opt));
-    const int64_t n_reads = in->n_pairs * 2;
-    const int64_t n_bases = n_reads ? in->seq_off[n_reads] : 0;
-    int maxlen = 0;
-    for (int64_t i = 0; i < n_reads; ++i) {
-        int64_t l = in->seq_off[i + 1] - in->seq_off[i];
-        if (l < 0 || l > ARACHNE_MAX_READ_LEN) { set_error("read %lld has length %lld; supported 0..%d", (long long)i, (long long)l, ARACHNE_MAX_READ_LEN); return ARACHNE_ERR_ARG; }
-        if (l > maxlen) maxlen = (int)l;
-    }
-    if (n_reads > 0x7fffffff / 2) { set_error("batch too large"); return ARACHNE_ERR_ARG; }
-    AR_CUDA(cudaSetDevice(idx->device));
-    const int sms = sm_count(idx->device);
-    cudaStream_t st;
-    AR_CUDA(cudaStreamCreate(&st));
-    cudaEvent_t ev[8];  // seed | sa | chain | extend | rescue | gather | cigar
-    for (auto& e : ev) cudaEventCreate(&e);
-
-    auto* out = new arachne_batch_out_t();
-    memset(out, 0, sizeof(*out));
-    auto* priv = new BatchPriv();
-    out->priv = priv;
-    out->n_reads = n_reads;
-    priv->reg_off.assign(n_reads + 1, 0);
-
-    DevBuf d_seq, d_off, d_scratch, d_arena, d_misc, d_intv_off, d_intv_n, d_nsa, d_sa_off, d_rows, d_cnt, d_tmp;
-    DevBuf d_seeds, d_kseeds, d_chains, d_nodes, d_order, d_kept, d_nchain, d_nkseed, d_srt, d_regs, d_nregs, d_win, d_reg_off, d_out;
-    DevBuf d_nregs_bak, d_reg_loc, d_blist, d_resc, d_reg_read, d_z, d_cig_scr, d_mm_scr, d_alns, d_cig, d_mm;
-    std::vector<DevBuf*> all = {&d_seq, &d_off, &d_scratch, &d_arena, &d_misc, &d_intv_off, &d_intv_n, &d_nsa, &d_sa_off, &d_rows, &d_cnt, &d_tmp,
-                                &d_seeds, &d_kseeds, &d_chains, &d_nodes, &d_order, &d_kept, &d_nchain, &d_nkseed, &d_srt, &d_regs, &d_nregs,
-                                &d_win, &d_reg_off, &d_out, &d_nregs_bak, &d_reg_loc, &d_blist, &d_resc, &d_reg_read, &d_z, &d_cig_scr, &d_mm_scr, &d_alns, &d_cig, &d_mm};
-    auto cleanup = [&]() {
-        for (auto* b : all) b->release();
-        for (auto& e : ev) cudaEventDestroy(e);
-        cudaStreamDestroy(st);
-    };
-    auto fail = [&](int code) { cleanup(); arachne_batch_free(out); return code; };
-#define AR_TRY(x) do { if ((x) != cudaSuccess) { set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #x, cudaGetErrorString(cudaGetLastError())); return fail(ARACHNE_ERR_CUDA); } } while (0)
-#define AR_ALLOC(buf, bytes) do { if ((buf).ensure(bytes)) { set_error("out of device memory allocating %zu bytes (%s)", (size_t)(bytes), #buf); return fail(ARACHNE_ERR_CUDA); } } while (0)
-
-    if (n_reads == 0) { cleanup(); out->reg_off = priv->reg_off.data(); *out_ = out; return ARACHNE_OK; }
-
-    const int L1 = maxlen + 1;
-    const int seed_threads = sms * 512;
-    AR_ALLOC(d_seq, n_bases + 16);
-    AR_ALLOC(d_off, (n_reads + 1) * 8);
-    AR_ALLOC(d_scratch, (size_t)seed_threads * 7 * L1 * sizeof(Intv));
-    AR_ALLOC(d_misc, 64);
-    AR_ALLOC(d_intv_off, n_reads * 8);
-    AR_ALLOC(d_intv_n, n_reads * 4);
-    AR_ALLOC(d_nsa, (n_reads + 1) * 4);
-    AR_ALLOC(d_sa_off, (n_reads + 1) * 8);
-    AR_ALLOC(d_cnt, sizeof(Counters));
-    AR_ALLOC(d_nchain, n_reads * 4);
-    AR_ALLOC(d_nkseed, n_reads * 4);
-    AR_ALLOC(d_nregs, (n_reads + 1) * 4);
-    AR_ALLOC(d_reg_off, (n_reads + 1) * 8);
-    AR_TRY(cudaMemcpyAsync(d_seq.p, in->seq, n_bases, cudaMemcpyHostToDevice, st));
-    AR_TRY(cudaMemcpyAsync(d_off.p, in->seq_off, (n_reads + 1) * 8, cudaMemcpyHostToDevice, st));
-    AR_TRY(cudaMemsetAsync(d_cnt.p, 0, sizeof(Counters), st));
-    AR_TRY(cudaMemsetAsync(d_nsa.p, 0, (n_reads + 1) * 4, st));
-    AR_TRY(cudaMemsetAsync(d_nregs.p, 0, (n_reads + 1) * 4, st));
-
-    Counters hc;
-    unsigned long long arena_cap = (unsigned long long)n_reads * 24 + 1024;
-    // ---- seeding (retry with a larger interval arena if it overflows) ----
-    cudaEventRecord(ev[0], st);
-    for (int attempt = 0;; ++attempt) {
-        AR_ALLOC(d_arena, arena_cap * sizeof(Intv));
-        AR_TRY(cudaMemsetAsync(d_misc.p, 0, 64, st));
-        k_seed<<<seed_threads / 128, 128, 0, st>>>(idx->fm, opt, d_seq.as<uint8_t>(), d_off.as<int64_t>(), (int)n_reads, d_scratch.as<Intv>(), L1,
-                                                    d_arena.as<Intv>(), arena_cap, d_misc.as<unsigned long long>(), d_intv_off.as<unsigned long long>(),
-                                                    d_intv_n.as<int>(), d_nsa.as<unsigned int>(), d_cnt.as<Counters>());
-        AR_TRY(cudaGetLastError());
-        AR_TRY(cudaMemcpyAsync(&hc, d_cnt.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
-        AR_TRY(cudaStreamSynchronize(st));
-        if (hc.err == 0) break;
-        if (attempt >= 3) { set_error("seeding: interval arena/scratch overflow at read %d", hc.err_read); return fail(ARACHNE_ERR_OVERFLOW); }
-        arena_cap *= 4;
-        AR_TRY(cudaMemsetAsync(d_cnt.p, 0, sizeof(Counters), st));
-    }
-    cudaEventRecord(ev[1], st);
-    // ---- seeds per read -> offsets ----
-    size_t tmp_bytes = 0;
-    cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, d_nsa.as<unsigned int>(), d_sa_off.as<unsigned long long>(), (int)n_reads + 1, st);
-    AR_ALLOC(d_tmp, tmp_bytes + 16);
-    AR_TRY(cub::DeviceScan::ExclusiveSum(d_tmp.p, tmp_bytes, d_nsa.as<unsigned int>(), d_sa_off.as<unsigned long long>(), (int)n_reads + 1, st));
-    unsigned long long total_sa = 0;
-    AR_TRY(cudaMemcpyAsync(&total_sa, d_sa_off.as<unsigned long long>() + n_reads, 8, cudaMemcpyDeviceToHost, st));
-    AR_TRY(cudaStreamSynchronize(st));
-    const size_t tsa = (size_t)total_sa + 8;
-    AR_ALLOC(d_rows, tsa * 8);
-    AR_ALLOC(d_seeds, tsa * sizeof(Seed));
-    AR_ALLOC(d_kseeds, tsa * sizeof(Seed));
-    AR_ALLOC(d_chains, tsa * sizeof(Chain));
-    AR_ALLOC(d_nodes, (tsa / 4 + 4 * (size_t)n_reads + 8) * sizeof(BNode));
-    AR_ALLOC(d_order, tsa * 4);
-    AR_ALLOC(d_kept, tsa * 4);
-    AR_ALLOC(d_srt, tsa * 8);
-    AR_ALLOC(d_regs, tsa * sizeof(AlnReg));
-    k_expand<<<sms * 4, 256, 0, st>>>(opt, (int)n_reads, d_arena.as<Intv>(), d_intv_off.as<unsigned long long>(), d_intv_n.as<int>(),
-                                       d_sa_off.as<unsigned long long>(), d_rows.as<uint64_t>());
-    AR_TRY(cudaGetLastError());
-    k_sa<<<sms * 8, 256, 0, st>>>(idx->fm, total_sa, d_rows.as<uint64_t>(), d_cnt.as<Counters>());
-    AR_TRY(cudaGetLastError());
-    cudaEventRecord(ev[2], st);
-    // ---- chaining ----
-    ChainBufs cb;
-    cb.seeds = d_seeds.as<Seed>(); cb.kseeds = d_kseeds.as<Seed>(); cb.chains = d_chains.as<Chain>(); cb.nodes = d_nodes.as<BNode>();
-    cb.order = d_order.as<int32_t>(); cb.kept = d_kept.as<int32_t>(); cb.n_chain = d_nchain.as<int>(); cb.n_kseed = d_nkseed.as<int>();
-    k_chain<<<sms * 8, 128, 0, st>>>(opt, idx->ref, d_off.as<int64_t>(), (int)n_reads, d_arena.as<Intv>(), d_intv_off.as<unsigned long long>(),
-                                      d_intv_n.as<int>(), d_sa_off.as<unsigned long long>(), d_rows.as<uint64_t>(), cb, d_cnt.as<Counters>());
-    AR_TRY(cudaGetLastError());
-    cudaEventRecord(ev[3], st);
-    // ---- extension + dedup ----
-    const int ext_blocks = sms * 8;
-    const int win_cap = 2 * maxlen + 1024 + 4 * opt.w;
-    AR_ALLOC(d_win, (size_t)ext_blocks * EXT_WARPS * win_cap);
-    AR_TRY(cudaMemsetAsync(d_misc.p, 0, 64, st));
-    k_extend<<<ext_blocks, EXT_WARPS * 32, 0, st>>>(opt, idx->ref, d_seq.as<uint8_t>(), d_off.as<int64_t>(), (int)n_reads, d_sa_off.as<unsigned long long>(),
-                                                    cb, d_srt.as<uint64_t>(), d_regs.as<AlnReg>(), d_nregs.as<int>(), d_win.as<uint8_t>(), win_cap,
-                                                    d_misc.as<unsigned int>(), d_cnt.as<Counters>());
-    AR_TRY(cudaGetLastError());
-    cudaEventRecord(ev[4], st);
-    int stages = in->stages ? in->stages : (ARACHNE_STAGE_REGIONS | ARACHNE_STAGE_RESCUE | ARACHNE_STAGE_CIGAR);
-    // ---- mate rescue ----
-    AR_ALLOC(d_reg_loc, (n_reads + 1) * 8);
-    k_init_loc<<<sms * 2, 256, 0, st>>>((int)n_reads, d_sa_off.as<unsigned long long>(), d_reg_loc.as<unsigned long long>());
-    AR_TRY(cudaGetLastError());
-    if (stages & ARACHNE_STAGE_RESCUE) {
-        const int bcap = win_cap;  // one row-maximum entry per target row at most
-        AR_ALLOC(d_blist, (size_t)ext_blocks * EXT_WARPS * bcap * 8);
-        unsigned long long resc_cap = (unsigned long long)n_reads * (getenv("ARACHNE_RESC_MULT") ? atoi(getenv("ARACHNE_RESC_MULT")) : 4) + 4096;
-        AR_TRY(cudaMemcpyAsync(&hc, d_cnt.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
-        AR_TRY(cudaStreamSynchronize(st));
-        if (hc.err != 0) { set_error("internal scratch overflow (code %d) at read %d", hc.err, hc.err_read); return fail(ARACHNE_ERR_OVERFLOW); }
-        AR_ALLOC(d_nregs_bak, (n_reads + 1) * 4);
-        AR_TRY(cudaMemcpyAsync(d_nregs_bak.p, d_nregs.p, (n_reads + 1) * 4, cudaMemcpyDeviceToDevice, st));
-        for (int attempt = 0;; ++attempt) {
-            AR_ALLOC(d_resc, resc_cap * sizeof(AlnReg));
-            AR_TRY(cudaMemsetAsync(d_misc.p, 0, 64, st));
-            k_rescue<<<ext_blocks, EXT_WARPS * 32, 0, st>>>(opt, idx->ref, in->score_delta, d_seq.as<uint8_t>(), d_off.as<int64_t>(), (int)in->n_pairs,
-                                                            d_sa_off.as<unsigned long long>(), d_regs.as<AlnReg>(), d_nregs.as<int>(),
-                                                            d_reg_loc.as<unsigned long long>(), d_resc.as<AlnReg>(), resc_cap,
-                                                            d_misc.as<unsigned long long>() + 1, d_win.as<uint8_t>(), win_cap, d_blist.as<uint64_t>(), bcap,
-                                                            d_misc.as<unsigned int>(), d_cnt.as<Counters>());
-            AR_TRY(cudaGetLastError());
-            AR_TRY(cudaMemcpyAsync(&hc, d_cnt.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
-            AR_TRY(cudaStreamSynchronize(st));
-            if (hc.err == 0) break;
-            if (hc.err != -100 || attempt >= 4) { set_error("rescue: scratch overflow (code %d) at pair %d", hc.err, hc.err_read); return fail(ARACHNE_ERR_OVERFLOW); }
-            // the rescue arena was too small: regions in place are untouched (copy-on-write), so the stage can simply be re-run
-            resc_cap *= 8;
-            AR_TRY(cudaMemcpyAsync(d_nregs.p, d_nregs_bak.p, (n_reads + 1) * 4, cudaMemcpyDeviceToDevice, st));
-            AR_TRY(cudaMemsetAsync(d_cnt.as<char>() + offsetof(Counters, err), 0, 8, st));
-            k_init_loc<<<sms * 2, 256, 0, st>>>((int)n_reads, d_sa_off.as<unsigned long long>(), d_reg_loc.as<unsigned long long>());
-        }
-    }
-    cudaEventRecord(ev[5], st);
-    // ---- compact regions ----
-    cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, d_nregs.as<int>(), d_reg_off.as<unsigned long long>(), (int)n_reads + 1, st);
-    AR_ALLOC(d_tmp, tmp_bytes + 16);
-    AR_TRY(cub::DeviceScan::ExclusiveSum(d_tmp.p, tmp_bytes, d_nregs.as<int>(), d_reg_off.as<unsigned long long>(), (int)n_reads + 1, st));
-    unsigned long long total_regs = 0;
-    AR_TRY(cudaMemcpyAsync(&total_regs, d_reg_off.as<unsigned long long>() + n_reads, 8, cudaMemcpyDeviceToHost, st));
-    AR_TRY(cudaMemcpyAsync(&hc, d_cnt.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
-    AR_TRY(cudaStreamSynchronize(st));
-    if (hc.err != 0) { set_error("internal scratch overflow (code %d) at read %d", hc.err, hc.err_read); return fail(ARACHNE_ERR_OVERFLOW); }
-    AR_ALLOC(d_out, (total_regs + 1) * sizeof(AlnReg));
-    AR_ALLOC(d_reg_read, (total_regs + 1) * 4);
-    k_gather_regs2<<<sms * 4, 256, 0, st>>>((int)n_reads, d_reg_loc.as<unsigned long long>(), d_reg_off.as<unsigned long long>(), d_regs.as<AlnReg>(),
-                                             d_resc.as<AlnReg>(), d_out.as<AlnReg>(), d_reg_read.as<int>());
-    AR_TRY(cudaGetLastError());
-    priv->regs.resize(total_regs);
-    static_assert(sizeof(unsigned long long) == sizeof(int64_t), "");
-    AR_TRY(cudaMemcpyAsync(priv->reg_off.data(), d_reg_off.p, (n_reads + 1) * 8, cudaMemcpyDeviceToHost, st));
-    if (total_regs) AR_TRY(cudaMemcpyAsync(priv->regs.data(), d_out.p, total_regs * sizeof(AlnReg), cudaMemcpyDeviceToHost, st));
-    cudaEventRecord(ev[6], st);
-    // ---- CIGAR + candidate statistics ----
-    if ((stages & ARACHNE_STAGE_CIGAR) && total_regs) {
-        const int cg_blocks = sms * 4;
-        const long nw = (long)cg_blocks * EXT_WARPS;
-        const long z_cap = (long)maxlen * (maxlen + 1024);
-        const int cig_scr_cap = 2 * maxlen + 64, mm_scr_cap = 2 * maxlen + 8;
-        AR_ALLOC(d_z, (size_t)nw * z_cap);
-        AR_ALLOC(d_cig_scr, (size_t)nw * cig_scr_cap * 4);
-        AR_ALLOC(d_mm_scr, (size_t)nw * mm_scr_cap * 4);
-        AR_ALLOC(d_win, (size_t)std::max<long>(nw, (long)ext_blocks * EXT_WARPS) * win_cap);
-        AR_ALLOC(d_alns, (total_regs + 1) * sizeof(AlnRec));
-        unsigned long long cig_cap = total_regs * 4 + 4096, mm_cap = total_regs * 12 + 4096;
-        for (int attempt = 0;; ++attempt) {
-            AR_ALLOC(d_cig, cig_cap * 4);
-            AR_ALLOC(d_mm, mm_cap * 4);
-            AR_TRY(cudaMemsetAsync(d_misc.p, 0, 64, st));
-            k_cigar<<<cg_blocks, EXT_WARPS * 32, 0, st>>>(opt, idx->ref, d_seq.as<uint8_t>(), d_off.as<int64_t>(), (long)total_regs, d_out.as<AlnReg>(),
-                                                          d_reg_read.as<int>(), d_alns.as<AlnRec>(), d_cig.as<uint32_t>(), cig_cap, d_mm.as<int32_t>(), mm_cap,
-                                                          d_misc.as<unsigned long long>() + 1, d_win.as<uint8_t>(), win_cap, d_z.as<uint8_t>(), z_cap,
-                                                          d_cig_scr.as<uint32_t>(), cig_scr_cap, d_mm_scr.as<int32_t>(), mm_scr_cap,
-                                                          d_misc.as<unsigned int>(), d_cnt.as<Counters>());
-            AR_TRY(cudaGetLastError());
-            AR_TRY(cudaMemcpyAsync(&hc, d_cnt.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
-            AR_TRY(cudaStreamSynchronize(st));
-            if (hc.err == 0) break;
-            if (hc.err != -101 || attempt >= 4) { set_error("cigar: scratch overflow (code %d) at read %d", hc.err, hc.err_read); return fail(ARACHNE_ERR_OVERFLOW); }
-            cig_cap *= 4; mm_cap *= 4;
-            AR_TRY(cudaMemsetAsync(d_cnt.as<char>() + offsetof(Counters, err), 0, 8, st));
-        }
-        unsigned long long used[2] = {0, 0};
-        AR_TRY(cudaMemcpyAsync(used, d_misc.as<unsigned long long>() + 1, 16, cudaMemcpyDeviceToHost, st));
-        AR_TRY(cudaStreamSynchronize(st));
-        priv->alns.resize(total_regs); priv->cigar.resize(used[0] + 1); priv->mm.resize(used[1] + 1);
-        AR_TRY(cudaMemcpyAsync(priv->alns.data(), d_alns.p, total_regs * sizeof(AlnRec), cudaMemcpyDeviceToHost, st));
-        if (used[0]) AR_TRY(cudaMemcpyAsync(priv->cigar.data(), d_cig.p, used[0] * 4, cudaMemcpyDeviceToHost, st));
-        if (used[1]) AR_TRY(cudaMemcpyAsync(priv->mm.data(), d_mm.p, used[1] * 4, cudaMemcpyDeviceToHost, st));
-        out->n_cigar = (int64_t)used[0]; out->n_mm = (int64_t)used[1];
-        out->alns = priv->alns.data(); out->cigar = priv->cigar.data(); out->mm = priv->mm.data();
-    }
-    cudaEventRecord(ev[7], st);
-    AR_TRY(cudaStreamSynchronize(st));
-
-    out->n_regs = (int64_t)total_regs;
-    out->reg_off = priv->reg_off.data();
-    out->regs = priv->regs.data();
-    out->n_sa_lookups = total_sa;
-    out->n_lf_steps = hc.lf_steps;
-    out->n_ext_calls = hc.ext_calls;
-    out->n_ext_cells = hc.ext_cells;
-    cudaEventElapsedTime(&out->ms_seed, ev[0], ev[1]);
-    cudaEventElapsedTime(&out->ms_sa, ev[1], ev[2]);
-    cudaEventElapsedTime(&out->ms_chain, ev[2], ev[3]);
-    cudaEventElapsedTime(&out->ms_extend, ev[3], ev[4]);
-    cudaEventElapsedTime(&out->ms_rescue, ev[4], ev[5]);
-    cudaEventElapsedTime(&out->ms_cigar, ev[6], ev[7]);
-    cudaEventElapsedTime(&out->ms_total, ev[0], ev[7]);
-    cleanup();
-    *out_ = out;
-    return ARACHNE_OK;
-}
-
-void arachne_batch_free(arachne_batch_out_t* out) {
-    if (!out) return;
-    delete reinterpret_cast<BatchPriv*>(out->priv);
-    delete out;
-}
+#include "batch.inl"
 
 // ---------------------------------------------------------------------------------------------- stage entry points
 int arachne_occ_batch(arachne_index_t* idx, int64_t n, const uint64_t* k, const uint64_t* l, uint64_t* cnt) {
@@ -775,7 +581,7 @@ int arachne_seed_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, int6
     AR_CUDA(cudaMemcpy(d_seq.p, seq, nb, cudaMemcpyHostToDevice));
     AR_CUDA(cudaMemcpy(d_off.p, seq_off, (n_reads + 1) * 8, cudaMemcpyHostToDevice));
     AR_CUDA(cudaMemset(d_used.p, 0, 64)); AR_CUDA(cudaMemset(d_cnt.p, 0, sizeof(Counters)));
-    k_seed<<<threads / 128, 128>>>(idx->fm, opt, d_seq.as<uint8_t>(), d_off.as<int64_t>(), (int)n_reads, d_scr.as<Intv>(), L1, d_arena.as<Intv>(),
+    k_seed<<<threads / 128, 128>>>(idx->fm, opt, d_seq.as<uint8_t>(), d_off.as<int64_t>(), (int)n_reads, maxlen, d_scr.as<Intv>(), L1, d_arena.as<Intv>(),
                                     (unsigned long long)intv_cap, d_used.as<unsigned long long>(), d_ioff.as<unsigned long long>(), d_in.as<int>(),
                                     d_nsa.as<unsigned int>(), d_cnt.as<Counters>());
     AR_CUDA(cudaGetLastError());

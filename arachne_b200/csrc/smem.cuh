@@ -13,7 +13,7 @@ AR_HD void intv_reverse(Intv* a, int n) {
 
 // All SMEMs through position x.  mem receives them sorted by start; buf0/buf1 are scratch of >= len+1 entries.
 // Returns the position to continue from.  max_intv is 0 on the path Arachne takes (bwt_smem1).
-AR_HD int smem1(const FMIndex& fm, int len, const uint8_t* q, int x, int min_intv, Intv* mem, int* n_mem, Intv* buf0, Intv* buf1) {
+AR_HD int smem1(const FMIndex& fm, int len, const uint8_t* q, int x, int min_intv, Intv* mem, int* n_mem, Intv* buf0, Intv* buf1, OccStat* st = nullptr) {
     Intv ik, ok[4];
     Intv *prev = buf0, *curr = buf1, *swap;
     int i, j, c, ret, n_curr = 0, n_prev, nm = 0;
@@ -25,7 +25,7 @@ AR_HD int smem1(const FMIndex& fm, int len, const uint8_t* q, int x, int min_int
     for (i = x + 1; i < len; ++i) {  // forward search
         if (q[i] < 4) {
             c = 3 - q[i];
-            fm_extend(fm, ik, ok, 0);
+            fm_extend(fm, ik, ok, 0, st);
             if (ok[c].x2 != ik.x2) {  // change of the interval size
                 curr[n_curr++] = ik;
                 if (ok[c].x2 < (uint64_t)min_intv) break;
@@ -45,7 +45,7 @@ AR_HD int smem1(const FMIndex& fm, int len, const uint8_t* q, int x, int min_int
         c = i < 0 ? -1 : q[i] < 4 ? q[i] : -1;
         for (j = 0, n_curr = 0; j < n_prev; ++j) {
             const Intv p = prev[j];
-            if (c >= 0) fm_extend(fm, p, ok, 1);
+            if (c >= 0) fm_extend(fm, p, ok, 1, st);
             if (c < 0 || ok[c].x2 < (uint64_t)min_intv) {
                 if (n_curr == 0) {  // no longer match has survived this step
                     if (nm == 0 || (uint64_t)(i + 1) < (mem[nm - 1].info >> 32)) {  // skip contained matches
@@ -67,7 +67,7 @@ AR_HD int smem1(const FMIndex& fm, int len, const uint8_t* q, int x, int min_int
 }
 
 // LAST-like seeding: first extension whose interval drops below max_intv once >= min_len long
-AR_HD int seed_strategy1(const FMIndex& fm, int len, const uint8_t* q, int x, int min_len, int max_intv, Intv* mem) {
+AR_HD int seed_strategy1(const FMIndex& fm, int len, const uint8_t* q, int x, int min_len, int max_intv, Intv* mem, OccStat* st = nullptr) {
     Intv ik, ok[4];
     mem->x0 = mem->x1 = mem->x2 = mem->info = 0;
     if (q[x] > 3) return x + 1;
@@ -75,7 +75,7 @@ AR_HD int seed_strategy1(const FMIndex& fm, int len, const uint8_t* q, int x, in
     for (int i = x + 1; i < len; ++i) {
         if (q[i] < 4) {
             int c = 3 - q[i];
-            fm_extend(fm, ik, ok, 0);
+            fm_extend(fm, ik, ok, 0, st);
             if (ok[c].x2 < (uint64_t)max_intv && i - x >= min_len) {
                 *mem = ok[c];
                 mem->info = (uint64_t)x << 32 | (uint32_t)(i + 1);
@@ -88,7 +88,7 @@ AR_HD int seed_strategy1(const FMIndex& fm, int len, const uint8_t* q, int x, in
 }
 
 // mem_collect_intv.  out: capacity cap; scratch: 3*(len+1) Intv.  Returns the number of intervals, or -1 on overflow.
-AR_HD int collect_intv(const MemOpt& opt, const FMIndex& fm, int len, const uint8_t* seq, Intv* out, int cap, Intv* scratch) {
+AR_HD int collect_intv(const MemOpt& opt, const FMIndex& fm, int len, const uint8_t* seq, Intv* out, int cap, Intv* scratch, OccStat* st = nullptr) {
     Intv* mem1 = scratch;
     Intv* b0 = scratch + (len + 1);
     Intv* b1 = scratch + 2 * (len + 1);
@@ -96,7 +96,7 @@ AR_HD int collect_intv(const MemOpt& opt, const FMIndex& fm, int len, const uint
     int split_len = (int)(opt.min_seed_len * opt.split_factor + .499);
     while (x < len) {  // pass 1: all SMEMs
         if (seq[x] < 4) {
-            x = smem1(fm, len, seq, x, 1, mem1, &n1, b0, b1);
+            x = smem1(fm, len, seq, x, 1, mem1, &n1, b0, b1, st);
             for (i = 0; i < n1; ++i) {
                 int slen = (int)((uint32_t)mem1[i].info - (uint32_t)(mem1[i].info >> 32));
                 if (slen >= opt.min_seed_len) {
@@ -110,7 +110,7 @@ AR_HD int collect_intv(const MemOpt& opt, const FMIndex& fm, int len, const uint
     for (k = 0; k < old_n; ++k) {  // pass 2: re-seed inside long, rare SMEMs
         int start = (int)(out[k].info >> 32), end = (int32_t)out[k].info;
         if (end - start < split_len || out[k].x2 > (uint64_t)opt.split_width) continue;
-        smem1(fm, len, seq, (start + end) >> 1, (int)(out[k].x2 + 1), mem1, &n1, b0, b1);
+        smem1(fm, len, seq, (start + end) >> 1, (int)(out[k].x2 + 1), mem1, &n1, b0, b1, st);
         for (i = 0; i < n1; ++i)
             if ((int)((uint32_t)mem1[i].info - (uint32_t)(mem1[i].info >> 32)) >= opt.min_seed_len) {
                 if (n >= cap) return -1;
@@ -122,7 +122,7 @@ AR_HD int collect_intv(const MemOpt& opt, const FMIndex& fm, int len, const uint
         while (x < len) {
             if (seq[x] < 4) {
                 Intv m;
-                x = seed_strategy1(fm, len, seq, x, opt.min_seed_len, (int)opt.max_mem_intv, &m);
+                x = seed_strategy1(fm, len, seq, x, opt.min_seed_len, (int)opt.max_mem_intv, &m, st);
                 if (m.x2 > 0) {
                     if (n >= cap) return -1;
                     out[n++] = m;

@@ -17,6 +17,9 @@ ALN = np.dtype([("pos", "<i8"), ("rid", "<i4"), ("is_rev", "<i4"), ("nm", "<i4")
 assert ALNREG.itemsize == 88 and ALN.itemsize == 72
 
 STAGE_REGIONS, STAGE_RESCUE, STAGE_CIGAR, STAGE_PLACE = 1, 2, 4, 8
+IN_DEVICE, OUT_DEVICE = 1, 2
+COUNTERS = ("n_occ_lookups", "n_occ_blocks", "n_sa_lookups", "n_lf_steps", "n_ext_calls", "n_ext_cells", "n_glb_cells", "n_kernel_launches")
+STAGE_MS = ("seed", "sa", "chain", "extend", "rescue", "cigar", "place", "total")
 
 
 class ArachneError(RuntimeError):
@@ -40,15 +43,16 @@ class MemOpt(C.Structure):  # arachne_mem_opt_t == mem_opt_t (bwa/bwamem.h:27-66
 
 class BatchIn(C.Structure):
     _fields_ = [("n_pairs", C.c_int64), ("seq", C.POINTER(C.c_uint8)), ("seq_off", C.POINTER(C.c_int64)), ("n_barcodes", C.c_int64),
-                ("barcode_off", C.POINTER(C.c_int64)), ("score_delta", C.c_int32), ("stages", C.c_int32)]
+                ("barcode_off", C.POINTER(C.c_int64)), ("score_delta", C.c_int32), ("stages", C.c_int32),
+                ("flags", C.c_int32), ("max_read_len", C.c_int32), ("n_bases", C.c_int64)]
 
 
 class BatchOut(C.Structure):
     _fields_ = [("n_reads", C.c_int64), ("n_regs", C.c_int64), ("n_cigar", C.c_int64), ("n_mm", C.c_int64),
                 ("reg_off", C.POINTER(C.c_int64)), ("regs", C.c_void_p), ("alns", C.c_void_p), ("cigar", C.POINTER(C.c_uint32)),
                 ("mm", C.POINTER(C.c_int32)),
-                ("n_occ_lookups", C.c_uint64), ("n_sa_lookups", C.c_uint64), ("n_lf_steps", C.c_uint64), ("n_ext_calls", C.c_uint64),
-                ("n_ext_cells", C.c_uint64), ("n_glb_cells", C.c_uint64),
+                ("n_occ_lookups", C.c_uint64), ("n_occ_blocks", C.c_uint64), ("n_sa_lookups", C.c_uint64), ("n_lf_steps", C.c_uint64), ("n_ext_calls", C.c_uint64),
+                ("n_ext_cells", C.c_uint64), ("n_glb_cells", C.c_uint64), ("n_kernel_launches", C.c_uint64),
                 ("ms_seed", C.c_float), ("ms_sa", C.c_float), ("ms_chain", C.c_float), ("ms_extend", C.c_float), ("ms_rescue", C.c_float),
                 ("ms_cigar", C.c_float), ("ms_place", C.c_float), ("ms_total", C.c_float), ("priv", C.c_void_p)]
 
@@ -73,6 +77,7 @@ class ArachneCuda:
         L.arachne_index_n_seqs.argtypes = [C.c_void_p]
         L.arachne_index_device_bytes.restype = C.c_size_t; L.arachne_index_device_bytes.argtypes = [C.c_void_p]
         L.arachne_index_contig.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_char_p), C.POINTER(C.c_int64), C.POINTER(C.c_int32)]
+        L.arachne_index_set_stream.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
         L.arachne_opts_default.argtypes = [C.POINTER(MemOpt)]
         L.arachne_align_batch.argtypes = [C.c_void_p, C.POINTER(MemOpt), C.POINTER(BatchIn), C.POINTER(C.POINTER(BatchOut))]
         L.arachne_batch_free.argtypes = [C.POINTER(BatchOut)]
@@ -164,6 +169,42 @@ class ArachneCuda:
                                                    _p(sc, C.c_int32), _p(coff, C.c_int64) if want_cigar else None, _p(cig, C.c_uint32), cap))
         return sc, coff, cig[:coff[-1]]
 
+    def set_stream(self, cuda_stream: int | None):
+        """Run batches on the caller's stream (e.g. torch.cuda.current_stream().cuda_stream); None = the handle's own."""
+        self._ck(self.lib.arachne_index_set_stream(self.idx, C.c_void_p(cuda_stream or 0), 0 if cuda_stream is None else 1))
+
+    def align_batch_device(self, d_seq_ptr: int, d_off_ptr: int, n_pairs: int, n_bases: int, max_read_len: int, score_delta=25, stages=0):
+        """Inputs already resident in HBM, results left in the device workspace: returns counts, counters and stage times."""
+        bi = BatchIn(); bi.n_pairs = n_pairs
+        bi.seq = C.cast(C.c_void_p(d_seq_ptr), C.POINTER(C.c_uint8)); bi.seq_off = C.cast(C.c_void_p(d_off_ptr), C.POINTER(C.c_int64))
+        bi.score_delta = score_delta; bi.stages = stages; bi.flags = IN_DEVICE | OUT_DEVICE
+        bi.max_read_len = max_read_len; bi.n_bases = n_bases
+        po = C.POINTER(BatchOut)()
+        self._ck(self.lib.arachne_align_batch(self.idx, C.byref(self.opt), C.byref(bi), C.byref(po)))
+        try:
+            o = po.contents
+            return dict(n_regs=o.n_regs, n_cigar=o.n_cigar, n_mm=o.n_mm, counters={k: getattr(o, k) for k in COUNTERS},
+                        ms={k: getattr(o, "ms_" + k) for k in STAGE_MS})
+        finally:
+            self.lib.arachne_batch_free(po)
+
+    def align_batch_host(self, seq, off, score_delta=25, stages=0):
+        """The C-ABI call exactly as a host makes it (host buffers in, pinned host results out), without converting the
+        results to numpy: returns counts, the bytes that crossed PCIe in each direction, counters and stage times."""
+        n_pairs = (len(off) - 1) // 2
+        bi = BatchIn(); bi.n_pairs = n_pairs; bi.seq = _p(seq, C.c_uint8); bi.seq_off = _p(off, C.c_int64)
+        bi.score_delta = score_delta; bi.stages = stages
+        po = C.POINTER(BatchOut)()
+        self._ck(self.lib.arachne_align_batch(self.idx, C.byref(self.opt), C.byref(bi), C.byref(po)))
+        try:
+            o = po.contents
+            d2h = (o.n_reads + 1) * 8 + o.n_regs * 88 + (o.n_regs * 72 + o.n_cigar * 4 + o.n_mm * 4 if o.alns else 0)
+            return dict(n_regs=o.n_regs, n_cigar=o.n_cigar, n_mm=o.n_mm, h2d_bytes=seq.nbytes + off.nbytes, d2h_bytes=d2h,
+                        first_score=(int(np.frombuffer(C.string_at(o.regs, 88), dtype=ALNREG)["score"][0]) if o.n_regs else -1),
+                        counters={k: getattr(o, k) for k in COUNTERS}, ms={k: getattr(o, "ms_" + k) for k in STAGE_MS})
+        finally:
+            self.lib.arachne_batch_free(po)
+
     # ---- batch hot path ----
     def align_batch(self, seq, off, bc_off=None, score_delta=25, stages=0):
         seq = np.ascontiguousarray(seq, dtype=np.uint8); off = np.ascontiguousarray(off, dtype=np.int64)
@@ -179,8 +220,7 @@ class ArachneCuda:
             o = po.contents
             res = dict(reg_off=np.ctypeslib.as_array(o.reg_off, shape=(o.n_reads + 1,)).copy(),
                        regs=(np.frombuffer(C.string_at(o.regs, o.n_regs * 88), dtype=ALNREG).copy() if o.n_regs else np.zeros(0, ALNREG)),
-                       counters={k: getattr(o, k) for k in ("n_occ_lookups", "n_sa_lookups", "n_lf_steps", "n_ext_calls", "n_ext_cells", "n_glb_cells")},
-                       ms={k: getattr(o, "ms_" + k) for k in ("seed", "sa", "chain", "extend", "rescue", "cigar", "place", "total")})
+                       counters={k: getattr(o, k) for k in COUNTERS}, ms={k: getattr(o, "ms_" + k) for k in STAGE_MS})
             if o.alns and o.n_regs:
                 res["alns"] = np.frombuffer(C.string_at(o.alns, o.n_regs * 72), dtype=ALN).copy()
                 res["cigar"] = np.ctypeslib.as_array(o.cigar, shape=(max(1, o.n_cigar),))[:o.n_cigar].copy()

@@ -1,0 +1,268 @@
+#!/usr/bin/env python
+"""bench.py -- read pairs/s of the candidate-alignment hot path (seeding -> chaining -> extension -> mate rescue ->
+CIGAR) through libarachne_cuda, with the reference's own CPU code (oracle/_ref) timed beside it.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+  torchrun --nproc-per-node N ... bench.py --gpus N ...        (one rank per GPU, barcode-sharded, no collective)
+
+A step = one pass of the hot path over one batch of `--pairs` simulated 2x150 read pairs grouped by barcode.
+`value`   : pairs/s with the batch already resident in HBM and the results left in HBM (CUDA events, max over ranks).
+`e2e`     : pairs/s through the C-ABI call a host makes: pinned host buffers in, H2D + kernels + D2H of every result.
+`roofline`: the seeding kernel's algorithmic occ-block bytes / its CUDA-event time against the measured HBM copy peak.
+`cpu_baseline`: the reference's C code (GoBwaMemMateSW + GoBwaSmithWaterman per candidate, oracle/_ref) on the host cores.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from arachne_b200 import simulate as S  # noqa: E402
+
+STAGES = 7  # regions + rescue + cigar (placement is reported separately once it is on the device)
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=8)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="arachne_b200", choices=["arachne_b200", "reference"])
+    ap.add_argument("--ref-mb", type=float, default=float(os.environ.get("ARACHNE_BENCH_REF_MB", "32")), help="synthetic reference size, Mbp")
+    ap.add_argument("--pairs", type=int, default=int(os.environ.get("ARACHNE_BENCH_PAIRS", "500000")), help="read pairs per step per GPU")
+    ap.add_argument("--batches", type=int, default=2, help="distinct input batches cycled over the steps")
+    ap.add_argument("--cpu-sample", type=int, default=150000, help="pairs in the bounded CPU-baseline sample")
+    ap.add_argument("--workdir", default=os.environ.get("ARACHNE_BENCH_DIR", "/tmp/arachne_bench"))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+# ---------------------------------------------------------------------------------------------- dataset
+def dataset(args, rank: int, world: int, need_index_files: bool = True):
+    """Reference (seed 2, human-like contig proportions) + its index + per-rank read batches (seed 12 + rank)."""
+    os.makedirs(args.workdir, exist_ok=True)
+    L = int(args.ref_mb * 1e6)
+    n_ctg = 24 if L >= 24_000_000 else 1
+    ctg = S.make_reference(L, n_ctg, seed=2)
+    fa = os.path.join(args.workdir, f"ref{L}.fa")
+    done = fa + ".done"
+    if rank == 0 and not os.path.exists(done):
+        t = time.time()
+        S.write_fasta(fa, ctg)
+        build_index(fa)
+        open(done, "w").write("ok")
+        log(f"index built in {time.time() - t:.1f}s")
+    return fa, ctg
+
+
+def build_index(fa: str):
+    """Data preparation, not the measured path: `bwa index` as the reference ships it (oracle/_ref), SURVEY.md section 2 #18."""
+    from oracle.refbwa import RefBwa
+    RefBwa().build_index(fa)
+
+
+def make_batches(ctg, args, rank):
+    return [S.simulate_pairs_fast(ctg, args.pairs, seed=12 + 1000 * rank + b) for b in range(args.batches)]
+
+
+def log(msg):
+    print(f"[bench] {msg}", file=sys.stderr, flush=True)
+
+
+# ---------------------------------------------------------------------------------------------- clocks
+class ClockSampler:
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, dev: int):
+        self.dev, self.rows, self.p = dev, [], None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.dev), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                                      stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True); self.t.start()
+        except OSError:
+            self.p = None
+
+    def _read(self):
+        for line in self.p.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.p:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+        sm = [int(r[0]) for r in self.rows if r and r[0].isdigit()]
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": float(max(mx)) if mx else None, "reasons": reasons, "samples": len(sm)}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return json.load(open(p))["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+# ---------------------------------------------------------------------------------------------- reference arm / cpu baseline
+_REF_CACHE = {}
+
+
+def cpu_reference(fa, rs, n_sample, threads):
+    """The reference's own C code for the path (oracle/_ref: unmodified bwa sources driven as gobwa.go drives them)."""
+    from oracle.refbwa import RefBwa
+    if fa not in _REF_CACHE:
+        _REF_CACHE[fa] = RefBwa().load(fa)
+    R = _REF_CACHE[fa]
+    n_bc = int(np.searchsorted(rs.bc_off, min(n_sample, rs.n_pairs), side="left"))
+    sub = rs.subset(0, max(1, n_bc))
+    t = time.perf_counter()
+    R.batch(sub.seq, sub.off, rescue=True, cigar=True, threads=threads)
+    dt = time.perf_counter() - t
+    return sub.n_pairs, dt
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's CPU implementation on this box's host cores, same workload/metric.  Rank 0 only."""
+    if rank != 0:
+        return
+    fa, ctg = dataset(args, 0, 1)
+    threads = os.cpu_count() or 1
+    n = max(1000, min(args.cpu_sample, args.pairs))
+    batches = [S.simulate_pairs_fast(ctg, n, seed=12 + b) for b in range(min(args.batches, 2))]
+    times = []
+    for it in range(args.warmup + args.steps):
+        npairs, dt = cpu_reference(fa, batches[it % len(batches)], n, threads)
+        if it >= args.warmup:
+            times.append(dt)
+    ms = 1e3 * sum(times) / len(times)
+    val = npairs / (ms / 1e3)
+    line = base_line(args, 1, val, ms)
+    line.update({"impl": "reference", "dtype": "int32", "n_gpus": args.gpus,
+                 "cpu_baseline": {"value": val, "unit": "pairs/s", "cores": threads, "kind": "reference",
+                                  "sample": f"{npairs} pairs per step of the same workload (oracle/_ref: the reference's BWA C sources, gobwa.go call sequence, {threads} pthreads over pairs)"},
+                 "e2e": {"value": val, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                 "gpu_launches": 0, "roofline": None})
+    print(json.dumps(line), flush=True)
+
+
+def base_line(args, world, value, ms):
+    return {"metric": "read pairs/sec aligned", "value": value, "unit": "pairs/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32", "data": "synthetic",
+            "config": {"workload": f"configs[1] scaled to what one bench run can index: synthetic {args.ref_mb:g} Mb iid reference (24 human-like contigs, seed 2), "
+                                   f"simulated haplotagging 2x150 bp pairs (1% subs, 14% reads with a 1-3 bp indel, 0.2% N, 30 pairs/barcode), "
+                                   f"{args.pairs} pairs per step per GPU; stages: seeding+SA+chaining+extension+mate rescue+CIGAR/NM",
+                       "ref_mb": args.ref_mb, "pairs_per_step_per_gpu": args.pairs, "read_len": 150, "parallelism": f"barcode-sharded x{world}, index replicated, no collective",
+                       "l2_policy": "inputs+index+per-batch arenas exceed L2 (>126 MB touched per step); distinct batches are cycled"}}
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        return run_reference(args, rank, world)
+    import torch
+    import torch.distributed as dist
+    from arachne_b200 import ArachneCuda
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: libarachne_cuda has no CPU path")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    barrier = (lambda: dist.barrier()) if world > 1 else (lambda: None)
+
+    fa, ctg = dataset(args, rank, world)
+    barrier()
+    batches = make_batches(ctg, args, rank)
+    A = ArachneCuda().load_index(fa, device=local)
+    stream = torch.cuda.Stream()
+    A.set_stream(stream.cuda_stream)
+    # resident inputs
+    dev = [(torch.from_numpy(b.seq).cuda(), torch.from_numpy(b.off).cuda(), b) for b in batches]
+    pinned = [(torch.from_numpy(b.seq).pin_memory(), torch.from_numpy(b.off).pin_memory()) for b in batches]
+    torch.cuda.synchronize()
+
+    def step_resident(i):
+        s, o, b = dev[i % len(dev)]
+        return A.align_batch_device(s.data_ptr(), o.data_ptr(), b.n_pairs, int(b.off[-1]), 150, stages=STAGES)
+
+    def step_host(i):
+        s, o = pinned[i % len(pinned)]
+        return A.align_batch_host(s.numpy(), o.numpy(), stages=STAGES)
+
+    # ---- device-resident timing (value) ----
+    with torch.cuda.stream(stream):
+        for i in range(args.warmup):
+            step_resident(i)
+        torch.cuda.synchronize(); barrier()
+        clk = ClockSampler(local); clk.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        acc = {}
+        e0.record(stream)
+        for i in range(args.steps):
+            r = step_resident(i)
+            for k, v in {**r["ms"], **r["counters"]}.items():
+                acc[k] = acc.get(k, 0) + v
+        e1.record(stream)
+        torch.cuda.synchronize(); barrier()
+        ms_total = e0.elapsed_time(e1)
+        # ---- end to end through the host C-ABI (e2e) ----
+        for i in range(min(2, args.warmup)):
+            step_host(i)
+        torch.cuda.synchronize(); barrier()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record(stream); t0 = time.perf_counter()
+        h2d = d2h = 0
+        for i in range(args.steps):
+            r = step_host(i); h2d += r["h2d_bytes"]; d2h += r["d2h_bytes"]
+        f1.record(stream)
+        torch.cuda.synchronize(); wall_e2e = (time.perf_counter() - t0) * 1e3; barrier()
+        ms_e2e = max(f0.elapsed_time(f1), wall_e2e)
+        clocks = clk.stop()
+    t = torch.tensor([ms_total, ms_e2e], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total, ms_e2e = float(t[0]), float(t[1])
+    if rank == 0:
+        pairs = args.pairs * args.steps * world
+        value = pairs / (ms_total / 1e3)
+        line = base_line(args, world, value, ms_total / args.steps)
+        peak, how = peaks()
+        seed_ms = acc["seed"] / args.steps
+        blocks = acc["n_occ_blocks"] / args.steps
+        achieved = blocks * 64 / (seed_ms / 1e3) / 1e9
+        line["roofline"] = {"kernel": "k_seed (FM-index SMEM seeding: bwt_2occ4 block reads)", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                            "frac": achieved / peak, "traffic": None, "peak_source": how,
+                            "algorithmic_bytes_per_launch": blocks * 64, "kernel_ms": seed_ms,
+                            "stage_ms_per_step": {k: acc[k] / args.steps for k in ("seed", "sa", "chain", "extend", "rescue", "cigar", "total")},
+                            "ext_gcups": acc["n_ext_cells"] / (acc["extend"] / 1e3) / 1e9 if acc["extend"] else None}
+        line["e2e"] = {"value": pairs / (ms_e2e / 1e3), "unit": "pairs/s", "h2d_bytes_per_step": h2d // args.steps, "d2h_bytes_per_step": d2h // args.steps}
+        line["gpu_launches"] = int(acc["n_kernel_launches"])
+        line["clocks"] = clocks
+        if world == 1 and not args.no_cpu_baseline:
+            threads = os.cpu_count() or 1
+            n, dt = cpu_reference(fa, batches[0], args.cpu_sample, threads)
+            line["cpu_baseline"] = {"value": n / dt, "unit": "pairs/s", "cores": threads, "kind": "reference",
+                                    "sample": f"first {n} pairs of batch 0 (whole barcodes), oracle/_ref = the reference's BWA C sources driven as gobwa.go drives them, {threads} pthreads"}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -112,7 +112,15 @@ typedef struct {
     const int64_t *barcode_off;/* n_barcodes+1 pair indices */
     int32_t score_delta;       /* GetChains passes 25 (aligner.go:454) */
     int32_t stages;            /* bitmask of ARACHNE_STAGE_*; 0 = all */
+    int32_t flags;             /* ARACHNE_IN_DEVICE | ARACHNE_OUT_DEVICE */
+    int32_t max_read_len;      /* ARACHNE_IN_DEVICE only: upper bound of the read lengths (checked on the device) */
+    int64_t n_bases;           /* ARACHNE_IN_DEVICE only: seq_off[2*n_pairs] */
 } arachne_batch_in_t;
+
+enum {
+    ARACHNE_IN_DEVICE = 1,     /* seq / seq_off are device pointers on the index's device (inputs already resident in HBM) */
+    ARACHNE_OUT_DEVICE = 2     /* leave the results in the handle's device workspace: only counts, counters and stage times come back */
+};
 
 enum {
     ARACHNE_STAGE_REGIONS = 1, /* seeding, chaining, extension, dedup (mem_align1_core) */
@@ -130,9 +138,11 @@ typedef struct {
     int32_t *mm;               /* mismatch pool */
     /* counters for roofline accounting: */
     uint64_t n_occ_lookups;    /* bwt_2occ4-equivalent calls in seeding */
+    uint64_t n_occ_blocks;     /* distinct 64-byte occ blocks those calls touch (1 if k>>7 == l>>7 else 2; bwt.c:194-196) */
     uint64_t n_sa_lookups, n_lf_steps;
     uint64_t n_ext_calls, n_ext_cells;  /* ksw_extend2 calls and in-band cells exactly as ksw.c:424-448 visits them */
     uint64_t n_glb_cells;
+    uint64_t n_kernel_launches; /* kernels this batch launched (bench.py reports it as gpu_launches) */
     float ms_seed, ms_sa, ms_chain, ms_extend, ms_rescue, ms_cigar, ms_place, ms_total; /* CUDA-event stage times */
     void *priv;
 } arachne_batch_out_t;
@@ -150,6 +160,9 @@ int64_t arachne_index_l_pac(const arachne_index_t *idx);
 int32_t arachne_index_n_seqs(const arachne_index_t *idx);
 int arachne_index_contig(const arachne_index_t *idx, int32_t rid, const char **name, int64_t *offset, int32_t *len);
 size_t arachne_index_device_bytes(const arachne_index_t *idx);
+/* Run this handle's batches on the caller's CUDA stream (a cudaStream_t; use != 0) or on the handle's own stream (use == 0,
+ * the default), so that a caller can bracket batches with its own CUDA events. */
+int arachne_index_set_stream(arachne_index_t *idx, void *cuda_stream, int use);
 
 /* ---- options: mem_opt_init defaults (gobwa.go:151) ---- */
 int arachne_opts_default(arachne_mem_opt_t *opt);
