@@ -68,7 +68,6 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
     if (n_reads == 0) { priv->reg_off.as<int64_t>()[0] = 0; out->reg_off = priv->reg_off.as<int64_t>(); *out_ = out; return ARACHNE_OK; }
 
     const int L1 = maxlen + 1;
-    const int seed_threads = sms * 512;
     const uint8_t* d_seq; const int64_t* d_off;
     if (in_dev) { d_seq = in->seq; d_off = in->seq_off; }
     else {
@@ -78,7 +77,6 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
         AR_TRY(cudaMemcpyAsync(W.d_off.p, in->seq_off, (n_reads + 1) * 8, cudaMemcpyHostToDevice, st));
         d_seq = W.d_seq.as<uint8_t>(); d_off = W.d_off.as<int64_t>();
     }
-    AR_ALLOC(W.d_scratch, (size_t)seed_threads * 7 * L1 * sizeof(Intv));
     AR_ALLOC(W.d_misc, 64);
     AR_ALLOC(W.d_intv_off, n_reads * 8);
     AR_ALLOC(W.d_intv_n, n_reads * 4);
@@ -96,25 +94,33 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
     int nl = 0;  // kernels launched by this batch
     Counters& hc = *W.h_cnt;
     unsigned long long* hs = W.h_scalars;
-    unsigned long long arena_cap = (unsigned long long)n_reads * 24 + 1024;
-    // ---- seeding (retry with a larger interval arena if it overflows) ----
+    // ---- seeding (retry with a larger per-read interval capacity if a read overflows it) ----
+    if (idx->fm.seq_len >= (1ull << 40) - 2) { set_error("reference too long for the packed interval lists (2*l_pac must stay below 2^40)"); return fail(ARACHNE_ERR_ARG); }
+    const int seed_blocks = sms * 3, seed_T = seed_blocks * 256, list_rows = 2 * L1;
+    AR_ALLOC(W.d_scratch, (size_t)seed_T * list_rows * sizeof(uint4));
+    int intv_cap = 32;
     cudaEventRecord(ev[0], st);
     for (int attempt = 0;; ++attempt) {
-        AR_ALLOC(W.d_arena, arena_cap * sizeof(Intv));
+        AR_ALLOC(W.d_arena, (size_t)n_reads * intv_cap * sizeof(Intv));
         AR_TRY(cudaMemsetAsync(W.d_misc.p, 0, 64, st));
+        AR_TRY(cudaMemsetAsync(W.d_intv_n.p, 0, n_reads * 4, st));
+        AR_TRY(cudaMemsetAsync(W.d_nsa.p, 0, (n_reads + 1) * 4, st));
+        SeedOut so; so.intv = W.d_arena.as<Intv>(); so.intv_n = W.d_intv_n.as<int>(); so.n_sa = W.d_nsa.as<unsigned int>(); so.cap = intv_cap;
         ++nl;
-        k_seed<<<seed_threads / 128, 128, 0, st>>>(idx->fm, opt, d_seq, d_off, (int)n_reads, maxlen, W.d_scratch.as<Intv>(), L1,
-                                                    W.d_arena.as<Intv>(), arena_cap, W.d_misc.as<unsigned long long>(), W.d_intv_off.as<unsigned long long>(),
-                                                    W.d_intv_n.as<int>(), W.d_nsa.as<unsigned int>(), W.d_cnt.as<Counters>());
+        k_seed2<<<seed_blocks, 256, 0, st>>>(idx->fm, opt, d_seq, d_off, (int)n_reads, maxlen, W.d_scratch.as<uint4>(), list_rows, so,
+                                              W.d_misc.as<unsigned int>(), W.d_cnt.as<Counters>());
         AR_TRY(cudaGetLastError());
         AR_TRY(cudaMemcpyAsync(&hc, W.d_cnt.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
         AR_TRY(cudaStreamSynchronize(st));
         if (hc.err == 0) break;
         if (hc.err == ARACHNE_ERR_ARG) { set_error("read %d is longer than the stated max_read_len %d", hc.err_read, maxlen); return fail(ARACHNE_ERR_ARG); }
-        if (attempt >= 3) { set_error("seeding: interval arena/scratch overflow at read %d", hc.err_read); return fail(ARACHNE_ERR_OVERFLOW); }
-        arena_cap *= 4;
+        if (attempt >= 3) { set_error("seeding: more than %d intervals at read %d", intv_cap, hc.err_read); return fail(ARACHNE_ERR_OVERFLOW); }
+        intv_cap *= 4;
         AR_TRY(cudaMemsetAsync(W.d_cnt.p, 0, sizeof(Counters), st));
     }
+    ++nl;
+    k_sort_intv<<<sms * 8, 128, 0, st>>>((int)n_reads, W.d_arena.as<Intv>(), W.d_intv_n.as<int>(), intv_cap);
+    AR_TRY(cudaGetLastError());
     cudaEventRecord(ev[1], st);
     // ---- seeds per read -> offsets ----
     size_t tmp_bytes = 0;
@@ -136,11 +142,12 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
     AR_ALLOC(W.d_srt, tsa * 8);
     AR_ALLOC(W.d_regs, tsa * sizeof(AlnReg));
     ++nl;
-    k_expand<<<sms * 4, 256, 0, st>>>(opt, (int)n_reads, W.d_arena.as<Intv>(), W.d_intv_off.as<unsigned long long>(), W.d_intv_n.as<int>(),
+    k_expand<<<sms * 4, 256, 0, st>>>(opt, (int)n_reads, W.d_arena.as<Intv>(), W.d_intv_off.as<unsigned long long>(), intv_cap, W.d_intv_n.as<int>(),
                                        W.d_sa_off.as<unsigned long long>(), W.d_rows.as<uint64_t>());
     AR_TRY(cudaGetLastError());
     ++nl;
-    k_sa<<<sms * 8, 256, 0, st>>>(idx->fm, total_sa, W.d_rows.as<uint64_t>(), W.d_cnt.as<Counters>());
+    AR_TRY(cudaMemsetAsync(W.d_misc.p, 0, 64, st));
+    k_sa<<<sms * 8, 256, 0, st>>>(idx->fm, total_sa, W.d_rows.as<uint64_t>(), W.d_misc.as<unsigned long long>(), W.d_cnt.as<Counters>());
     AR_TRY(cudaGetLastError());
     cudaEventRecord(ev[2], st);
     // ---- chaining ----

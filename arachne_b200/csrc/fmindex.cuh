@@ -1,47 +1,38 @@
-// FM-index primitives over the reference's on-disk layout, resident in HBM.
+// FM-index primitives, B200 layout.
 //
-// Layout (bwa/bwtindex.c:151-173, bwa/bwt.h:72-78): the .bwt payload is a sequence of 64-byte blocks, one per
-// 128 BWT symbols: 4 x u64 cumulative A/C/G/T counts followed by 8 x u32 words of 16 two-bit symbols
-// (symbol i of a word at bits (15-i)*2).  We keep exactly that image, 64-byte aligned, so one occ query is one
-// aligned 64-byte line: four 128-bit loads (ld.global.nc.v4) per touched block.  The '$' is not stored:
-// k -= (k >= primary) (bwa/bwt.c:114,177).
+// The reference keeps the BWT as 64-byte blocks of 128 symbols: 4 x u64 cumulative A/C/G/T counts + 8 x u32 words of
+// 16 two-bit symbols (bwa/bwtindex.c:151-173, bwa/bwt.h:72-78), so one rank query reads one 64-byte block = two 32-byte
+// DRAM sectors.  In HBM we keep the same information re-cut to the sector size: one 32-byte block per 64 symbols,
+// 4 x u32 cumulative counts + 4 x u32 symbol words (same bit order: symbol i of a word at bits (15-i)*2).  A rank query
+// is then exactly ONE 32-byte sector (one 256-bit access), half the DRAM traffic per query at the same index size
+// (seq_len/2 bytes).  u32 counts hold for every base count < 2^32 (seq_len up to ~1.6e10 on uniform text; checked at load).
+// The '$' is not stored: k -= (k >= primary) (bwa/bwt.c:114,177).
 //
-// Functions mirror bwa/bwt.c: occ4/2occ4 (:169-220), occ (:107-129), invPsi (:53-59), sa (:86-96),
-// extend (:262-275), set_intv (bwt.h:80).  Counting uses popcount on 64-bit lanes instead of the reference's
-// 256-entry byte LUT; results are identical integers.
+// Functions mirror bwa/bwt.c: occ4/2occ4 (:169-220), occ (:107-129), invPsi (:53-59), sa (:86-96), extend (:262-275),
+// set_intv (bwt.h:80).  Counting uses popcount on 64-bit lanes instead of the reference's 256-entry byte LUT; the
+// integers are identical.
 #pragma once
 #include "common.cuh"
 
 namespace arachne {
 
-struct OccBlock {  // 64 bytes
-    uint64_t cnt[4];
-    uint32_t w[8];
+struct Blk32 {  // 32 bytes = one DRAM sector: 64 BWT symbols
+    uint32_t cnt[4];
+    uint32_t w[4];
 };
-static_assert(sizeof(OccBlock) == 64, "occ block must be one 64-byte line");
+static_assert(sizeof(Blk32) == 32, "occ block must be one 32-byte sector");
 
 struct FMIndex {
-    const OccBlock* blocks;
+    const Blk32* blocks;
     const uint64_t* sa;  // sa[0] == (uint64_t)-1, sampled every sa_intv rows (bwa/bwt.c:62-84)
     uint64_t primary, seq_len, n_sa;
     uint64_t L2[5];
     int sa_intv;
 };
 
-AR_HD OccBlock fm_load_block(const FMIndex& fm, uint64_t b) {
-#if defined(__CUDA_ARCH__)
-    const uint4* p = reinterpret_cast<const uint4*>(fm.blocks + b);
-    uint4 v0 = __ldg(p), v1 = __ldg(p + 1), v2 = __ldg(p + 2), v3 = __ldg(p + 3);
-    OccBlock o;
-    o.cnt[0] = (uint64_t)v0.y << 32 | v0.x; o.cnt[1] = (uint64_t)v0.w << 32 | v0.z;
-    o.cnt[2] = (uint64_t)v1.y << 32 | v1.x; o.cnt[3] = (uint64_t)v1.w << 32 | v1.z;
-    o.w[0] = v2.x; o.w[1] = v2.y; o.w[2] = v2.z; o.w[3] = v2.w;
-    o.w[4] = v3.x; o.w[5] = v3.y; o.w[6] = v3.z; o.w[7] = v3.w;
-    return o;
-#else
-    return fm.blocks[b];
-#endif
-}
+struct OccStat {  // roofline accounting in the reference's own units: bwt_2occ4 calls and the 64-byte blocks they touch
+    unsigned calls = 0, blocks = 0;
+};
 
 AR_HD int ar_popc64(uint64_t x) {
 #if defined(__CUDA_ARCH__)
@@ -51,12 +42,41 @@ AR_HD int ar_popc64(uint64_t x) {
 #endif
 }
 
-// symbols [0, nvalid) of the block, nvalid in 1..128 -> per-base counts
-AR_HD void fm_block_count(const OccBlock& o, int nvalid, uint32_t c[4]) {
+// Re-cut one reference block (4 x u64 counts + 8 words, given as 16 little-endian u32) into two sector blocks.
+AR_HD void fm_recut_block(const uint32_t* raw16, Blk32* out2) {
+    uint64_t c[4];
+    for (int i = 0; i < 4; ++i) c[i] = (uint64_t)raw16[2 * i + 1] << 32 | raw16[2 * i];
+    for (int i = 0; i < 4; ++i) { out2[0].cnt[i] = (uint32_t)c[i]; out2[0].w[i] = raw16[8 + i]; out2[1].w[i] = raw16[12 + i]; }
+    const uint64_t M = 0x5555555555555555ull;
+    uint32_t cc = 0, cg = 0, ct = 0;
+    for (int i = 0; i < 2; ++i) {
+        uint64_t x = (uint64_t)raw16[8 + 2 * i] << 32 | raw16[9 + 2 * i];
+        uint64_t lo = x & M, hi = (x >> 1) & M;
+        ct += ar_popc64(hi & lo); cg += ar_popc64(hi & ~lo); cc += ar_popc64(~hi & lo);
+    }
+    out2[1].cnt[0] = (uint32_t)c[0] + (64 - cc - cg - ct);
+    out2[1].cnt[1] = (uint32_t)c[1] + cc; out2[1].cnt[2] = (uint32_t)c[2] + cg; out2[1].cnt[3] = (uint32_t)c[3] + ct;
+}
+
+AR_HD Blk32 fm_load_block(const FMIndex& fm, uint64_t b) {
+#if defined(__CUDA_ARCH__)
+    const uint4* p = reinterpret_cast<const uint4*>(fm.blocks + b);
+    uint4 v0 = __ldg(p), v1 = __ldg(p + 1);
+    Blk32 o;
+    o.cnt[0] = v0.x; o.cnt[1] = v0.y; o.cnt[2] = v0.z; o.cnt[3] = v0.w;
+    o.w[0] = v1.x; o.w[1] = v1.y; o.w[2] = v1.z; o.w[3] = v1.w;
+    return o;
+#else
+    return fm.blocks[b];
+#endif
+}
+
+// symbols [0, nvalid) of the block, nvalid in 1..64 -> per-base counts
+AR_HD void fm_block_count(const Blk32& o, int nvalid, uint32_t c[4]) {
     const uint64_t M = 0x5555555555555555ull;
     uint32_t cc = 0, cg = 0, ct = 0;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
+    for (int i = 0; i < 2; ++i) {
         int v = nvalid - 32 * i;
         v = v < 0 ? 0 : (v > 32 ? 32 : v);
         uint64_t m = v == 0 ? 0ull : (M << ((32 - v) << 1)) & M;  // the v leading symbols of this 64-bit lane
@@ -70,43 +90,52 @@ AR_HD void fm_block_count(const OccBlock& o, int nvalid, uint32_t c[4]) {
     c[0] = (uint32_t)nvalid - cc - cg - ct;
 }
 
-AR_HD void fm_occ4_blk(const OccBlock& o, uint64_t kk, uint64_t cnt[4]) {
+AR_HD void fm_occ4_blk(const Blk32& o, uint64_t kk, uint64_t cnt[4]) {
     uint32_t c[4];
-    fm_block_count(o, (int)(kk & 127) + 1, c);
-    cnt[0] = o.cnt[0] + c[0]; cnt[1] = o.cnt[1] + c[1]; cnt[2] = o.cnt[2] + c[2]; cnt[3] = o.cnt[3] + c[3];
+    fm_block_count(o, (int)(kk & 63) + 1, c);
+    cnt[0] = (uint64_t)o.cnt[0] + c[0]; cnt[1] = (uint64_t)o.cnt[1] + c[1]; cnt[2] = (uint64_t)o.cnt[2] + c[2]; cnt[3] = (uint64_t)o.cnt[3] + c[3];
 }
 
 // bwt_occ4, bwa/bwt.c:169-186
 AR_HD void fm_occ4(const FMIndex& fm, uint64_t k, uint64_t cnt[4]) {
     if (k == (uint64_t)-1) { cnt[0] = cnt[1] = cnt[2] = cnt[3] = 0; return; }
     k -= (k >= fm.primary);
-    OccBlock o = fm_load_block(fm, k >> 7);
+    Blk32 o = fm_load_block(fm, k >> 6);
     fm_occ4_blk(o, k, cnt);
 }
 
-// bwt_2occ4, bwa/bwt.c:189-220.  *n_blocks receives the number of 64-byte lines touched (roofline accounting).
-struct OccStat {  // roofline accounting: bwt_2occ4 calls and the 64-byte blocks they touch
-    unsigned calls = 0, blocks = 0;
-};
+// blocks of the reference layout (64 bytes / 128 symbols) that bwt_2occ4(k, l) touches, bwa/bwt.c:189-220
+AR_HD unsigned fm_ref_blocks(const FMIndex& fm, uint64_t k, uint64_t l) {
+    if (k == (uint64_t)-1 || l == (uint64_t)-1) return (k != (uint64_t)-1) + (l != (uint64_t)-1);
+    uint64_t k_ = k - (k >= fm.primary), l_ = l - (l >= fm.primary);
+    return (l_ >> 7) != (k_ >> 7) ? 2 : 1;
+}
 
+// bwt_2occ4, bwa/bwt.c:189-220
 AR_HD void fm_2occ4(const FMIndex& fm, uint64_t k, uint64_t l, uint64_t ck[4], uint64_t cl[4], OccStat* st = nullptr) {
     uint64_t k_ = k - (k >= fm.primary), l_ = l - (l >= fm.primary);
-    if (st) { ++st->calls; st->blocks += (k == (uint64_t)-1 || l == (uint64_t)-1) ? (k != l ? 1 : 0) : ((l_ >> 7) != (k_ >> 7) ? 2 : 1); }
-    if ((l_ >> 7) != (k_ >> 7) || k == (uint64_t)-1 || l == (uint64_t)-1) {
+    if (st) { ++st->calls; st->blocks += fm_ref_blocks(fm, k, l); }
+    if ((l_ >> 6) != (k_ >> 6) || k == (uint64_t)-1 || l == (uint64_t)-1) {
         fm_occ4(fm, k, ck);
         fm_occ4(fm, l, cl);
     } else {
-        OccBlock o = fm_load_block(fm, k_ >> 7);
+        Blk32 o = fm_load_block(fm, k_ >> 6);
         fm_occ4_blk(o, k_, ck);
         fm_occ4_blk(o, l_, cl);
     }
 }
 
+// register-friendly selects (dynamic indexing of kernel-parameter or register arrays would spill to local memory)
+AR_HD uint64_t fm_L2(const FMIndex& fm, int c) {
+    return c == 0 ? fm.L2[0] : c == 1 ? fm.L2[1] : c == 2 ? fm.L2[2] : c == 3 ? fm.L2[3] : fm.L2[4];
+}
+template <class T> AR_HD T sel4(const T a[4], int c) { return c == 0 ? a[0] : c == 1 ? a[1] : c == 2 ? a[2] : a[3]; }
+
 // bwt_set_intv, bwa/bwt.h:80
 AR_HD void fm_set_intv(const FMIndex& fm, int c, Intv& ik) {
-    ik.x0 = fm.L2[c] + 1;
-    ik.x2 = fm.L2[c + 1] - fm.L2[c];
-    ik.x1 = fm.L2[3 - c] + 1;
+    ik.x0 = fm_L2(fm, c) + 1;
+    ik.x2 = fm_L2(fm, c + 1) - fm_L2(fm, c);
+    ik.x1 = fm_L2(fm, 3 - c) + 1;
     ik.info = 0;
 }
 
@@ -135,17 +164,15 @@ AR_HD void fm_extend(const FMIndex& fm, const Intv& ik, Intv ok[4], int is_back,
     }
 }
 
-// one LF step: bwt_invPsi, bwa/bwt.c:53-59 (B0 and occ come from the same 64-byte line)
+// one LF step: bwt_invPsi, bwa/bwt.c:53-59 (B0 and occ come from the same sector)
 AR_HD uint64_t fm_inv_psi(const FMIndex& fm, uint64_t k) {
     if (k == fm.primary) return 0;
     uint64_t x = k - (k > fm.primary);
-    OccBlock o = fm_load_block(fm, x >> 7);
-    int c = (o.w[(x & 127) >> 4] >> ((~x & 15) << 1)) & 3;
+    Blk32 o = fm_load_block(fm, x >> 6);
+    int c = (sel4(o.w, (int)(x & 63) >> 4) >> ((~x & 15) << 1)) & 3;
     uint32_t cnt[4];
-    fm_block_count(o, (int)(x & 127) + 1, cnt);
-    // bwt_occ(k, c): k == seq_len cannot reach here with k != primary unless k is the last row; handled identically
-    // because x = k - 1 then addresses the last stored symbol.
-    return fm.L2[c] + o.cnt[c] + cnt[c];
+    fm_block_count(o, (int)(x & 63) + 1, cnt);
+    return fm_L2(fm, c) + sel4(o.cnt, c) + sel4(cnt, c);
 }
 
 // bwt_sa, bwa/bwt.c:86-96.  Row-sampled SA: geometric walk length (mean ~ sa_intv-1).

@@ -9,6 +9,7 @@
 #include <cstring>
 #include <mutex>
 #include "fmindex.cuh"
+#include "bwt_image.h"
 #include "../../include/arachne_cuda.h"
 
 namespace arachne {
@@ -84,7 +85,6 @@ inline int index_load(const char* prefix_, int device, arachne_index** out) {
     for (int i = 1; i <= 4; ++i) fm.L2[i] = bh[i];
     fm.seq_len = fm.L2[4];
     size_t bwt_bytes = bwt.size() - 40;
-    size_t n_blocks = (fm.seq_len + 127) / 128 + 1;  // bwt_bwtupdate_core writes one trailing count block
     // bwt_bwtupdate_core (bwtindex.c:151-173): 32 bytes of counts per started 128-symbol block, 4 bytes per started
     // 16-symbol word, one trailing 32-byte count record
     const size_t want_bytes = ((fm.seq_len + 127) / 128) * 32 + ((fm.seq_len + 15) / 16) * 4 + 32;
@@ -123,11 +123,13 @@ inline int index_load(const char* prefix_, int device, arachne_index** out) {
         }
     }
     if ((uint64_t)idx->l_pac * 2 != fm.seq_len || pac.size() < (size_t)(idx->l_pac / 4 + 1)) { delete idx; set_error("inconsistent .pac/.ann/.bwt for %s", prefix.c_str()); return ARACHNE_ERR_IO; }
-    // upload
+    // re-cut the reference's 64-byte / 128-symbol blocks into 32-byte sector blocks (fmindex.cuh) and upload
+    for (int i = 0; i < 4; ++i)
+        if (fm.L2[i + 1] - fm.L2[i] >= 0xffffffffull) { delete idx; set_error("%s: a base count exceeds 2^32-1 (sector layout keeps u32 counts)", prefix.c_str()); return ARACHNE_ERR_IO; }
     cudaError_t e = cudaSetDevice(device);
-    size_t img = n_blocks * 64, sab = fm.n_sa * 8, pacb = (size_t)(idx->l_pac / 4 + 1);
-    std::vector<uint8_t> image(img, 0);
-    memcpy(image.data(), bwt.data() + 40, bwt_bytes < img ? bwt_bytes : img);
+    std::vector<uint8_t> image;
+    if (!bwt_recut_image(bwt.data() + 40, bwt_bytes, fm.seq_len, image)) { delete idx; set_error("%s.bwt is truncated", prefix.c_str()); return ARACHNE_ERR_IO; }
+    size_t img = image.size(), sab = fm.n_sa * 8, pacb = (size_t)(idx->l_pac / 4 + 1);
     std::vector<uint64_t> sav(fm.n_sa);
     sav[0] = (uint64_t)-1;
     memcpy(sav.data() + 1, sa.data() + 56, (fm.n_sa - 1) * 8);
@@ -146,7 +148,7 @@ inline int index_load(const char* prefix_, int device, arachne_index** out) {
         delete idx;
         return ARACHNE_ERR_CUDA;
     }
-    fm.blocks = reinterpret_cast<const OccBlock*>(idx->d_bwt);
+    fm.blocks = reinterpret_cast<const Blk32*>(idx->d_bwt);
     fm.sa = reinterpret_cast<const uint64_t*>(idx->d_sa);
     idx->ref.pac = reinterpret_cast<const uint8_t*>(idx->d_pac);
     idx->ref.contigs = reinterpret_cast<const Contig*>(idx->d_contigs);

@@ -46,44 +46,17 @@ __device__ __forceinline__ void raise(Counters* c, int code, int read) {
     if (atomicCAS(&c->err, 0, code) == 0) c->err_read = read;
 }
 
-// ------------------------------------------------------------------------------------------------ k_seed
-__global__ void __launch_bounds__(128) k_seed(FMIndex fm, MemOpt opt, const uint8_t* __restrict__ seq, const int64_t* __restrict__ off,
-                                              int n_reads, int maxlen, Intv* scratch, int L1, Intv* arena, unsigned long long arena_cap,
-                                              unsigned long long* arena_used, unsigned long long* intv_off, int* intv_n,
-                                              unsigned int* n_sa, Counters* cnt) {
-    const int tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
-    Intv* sc = scratch + (size_t)tid * 7 * L1;
-    Intv* out = sc + 3 * L1;
-    const int cap = 4 * L1;
-    OccStat ost;
-    for (int r = tid; r < n_reads; r += nth) {
-        const int len = (int)(off[r + 1] - off[r]);
-        const uint8_t* s = seq + off[r];
-        int n = 0;
-        if (len > maxlen) { raise(cnt, ARACHNE_ERR_ARG, r); intv_off[r] = 0; intv_n[r] = 0; n_sa[r] = 0; continue; }
-        if (len >= opt.min_seed_len) n = collect_intv(opt, fm, len, s, out, cap, sc, &ost);
-        if (n < 0) { raise(cnt, ARACHNE_ERR_OVERFLOW, r); n = 0; }
-        unsigned long long pos = 0;
-        unsigned int nsa = 0;
-        if (n > 0) {
-            pos = atomicAdd(arena_used, (unsigned long long)n);
-            if (pos + n > arena_cap) { raise(cnt, ARACHNE_ERR_OVERFLOW, r); n = 0; }
-        }
-        for (int i = 0; i < n; ++i) {
-            arena[pos + i] = out[i];
-            nsa += out[i].x2 > (uint64_t)opt.max_occ ? (unsigned)opt.max_occ : (unsigned)out[i].x2;
-        }
-        intv_off[r] = pos; intv_n[r] = n; n_sa[r] = nsa;
-    }
-    unsigned c = __reduce_add_sync(0xffffffffu, ost.calls), b = __reduce_add_sync(0xffffffffu, ost.blocks);
-    if ((threadIdx.x & 31) == 0 && c) { atomicAdd(&cnt->occ, (unsigned long long)c); atomicAdd(&cnt->occ_blocks, (unsigned long long)b); }
-}
+// ------------------------------------------------------------------------------------------------ k_seed2
+}  // namespace arachne
+#include "seed_kernel.cuh"
+namespace arachne {
 
 // ------------------------------------------------------------------------------------------------ k_expand / k_sa
-__global__ void k_expand(MemOpt opt, int n_reads, const Intv* __restrict__ arena, const unsigned long long* __restrict__ intv_off,
+__global__ void k_expand(MemOpt opt, int n_reads, const Intv* __restrict__ arena, unsigned long long* __restrict__ intv_off, int cap,
                          const int* __restrict__ intv_n, const unsigned long long* __restrict__ sa_off, uint64_t* rows) {
     for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < n_reads; r += gridDim.x * blockDim.x) {
-        const Intv* iv = arena + intv_off[r];
+        intv_off[r] = (unsigned long long)r * cap;
+        const Intv* iv = arena + (size_t)r * cap;
         unsigned long long o = sa_off[r];
         for (int i = 0; i < intv_n[r]; ++i) {
             const Intv p = iv[i];
@@ -94,13 +67,26 @@ __global__ void k_expand(MemOpt opt, int n_reads, const Intv* __restrict__ arena
     }
 }
 
-__global__ void __launch_bounds__(256) k_sa(FMIndex fm, unsigned long long n, uint64_t* rows, Counters* cnt) {
-    unsigned long long steps = 0;
-    for (unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; i < n; i += (unsigned long long)gridDim.x * blockDim.x) {
-        uint64_t k = rows[i], sa = 0, mask = (uint64_t)fm.sa_intv - 1;
-        while (k & mask) { ++sa; k = fm_inv_psi(fm, k); }
-        rows[i] = sa + fm.sa[k / fm.sa_intv];
-        steps += sa;
+// bwt_sa for every SA row of the batch.  Walk lengths are geometric (rows, not text positions, are sampled), so lanes
+// are persistent: a lane that reaches a sampled row stores its result and pulls the next row from the queue, and every
+// loop iteration is one LF step (one 32-byte sector) for every live lane.
+__global__ void __launch_bounds__(256) k_sa(FMIndex fm, unsigned long long n, uint64_t* rows, unsigned long long* next, Counters* cnt) {
+    const uint64_t mask = (uint64_t)fm.sa_intv - 1;
+    unsigned long long steps = 0, idx = 0;
+    uint64_t k = 0, sa = 0;
+    bool live = false, done = false;
+    for (;;) {
+        if (!live && !done) {
+            idx = atomicAdd(next, 1ull);
+            if (idx >= n) done = true;
+            else { k = rows[idx]; sa = 0; live = true; }
+        }
+        __syncwarp();
+        if (live) {
+            if (k & mask) { ++sa; k = fm_inv_psi(fm, k); }
+            else { rows[idx] = sa + fm.sa[k / fm.sa_intv]; steps += sa; live = false; }
+        }
+        if (__all_sync(FULL, done)) break;
     }
     steps = __reduce_add_sync(FULL, (unsigned)steps);  // per-thread totals stay far below 2^32 / 32
     if ((threadIdx.x & 31) == 0 && steps) atomicAdd(&cnt->lf_steps, steps);
@@ -552,10 +538,10 @@ int arachne_sa_batch(arachne_index_t* idx, int64_t n, const uint64_t* k, uint64_
     if (!idx || !k || !sa || n < 0) { set_error("arachne_sa_batch: bad argument"); return ARACHNE_ERR_ARG; }
     AR_CUDA(cudaSetDevice(idx->device));
     uint64_t* dk = nullptr; Counters* dc = nullptr;
-    AR_CUDA(cudaMalloc(&dk, n * 8 + 8)); AR_CUDA(cudaMalloc(&dc, sizeof(Counters)));
-    AR_CUDA(cudaMemset(dc, 0, sizeof(Counters)));
+    AR_CUDA(cudaMalloc(&dk, n * 8 + 8)); AR_CUDA(cudaMalloc(&dc, sizeof(Counters) + 8));
+    AR_CUDA(cudaMemset(dc, 0, sizeof(Counters) + 8));
     AR_CUDA(cudaMemcpy(dk, k, n * 8, cudaMemcpyHostToDevice));
-    k_sa<<<256, 256>>>(idx->fm, (unsigned long long)n, dk, dc);
+    k_sa<<<256, 256>>>(idx->fm, (unsigned long long)n, dk, reinterpret_cast<unsigned long long*>(dc + 1), dc);
     AR_CUDA(cudaGetLastError());
     AR_CUDA(cudaMemcpy(sa, dk, n * 8, cudaMemcpyDeviceToHost));
     cudaFree(dk); cudaFree(dc);
@@ -572,37 +558,44 @@ int arachne_seed_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, int6
     int maxlen = 0;
     for (int64_t i = 0; i < n_reads; ++i) maxlen = std::max<int>(maxlen, (int)(seq_off[i + 1] - seq_off[i]));
     if (maxlen > ARACHNE_MAX_READ_LEN) { set_error("read longer than %d", ARACHNE_MAX_READ_LEN); return ARACHNE_ERR_ARG; }
-    const int L1 = maxlen + 1, threads = 148 * 128;
-    DevBuf d_seq, d_off, d_scr, d_arena, d_used, d_ioff, d_in, d_nsa, d_cnt;
+    const int L1 = maxlen + 1, blocks = sm_count(idx->device) * 3, T = blocks * 256, rows = 2 * L1;
+    int cap = 32;
+    DevBuf d_seq, d_off, d_scr, d_arena, d_next, d_in, d_nsa, d_cnt;
     int64_t nb = seq_off[n_reads];
-    if (d_seq.ensure(nb + 16) || d_off.ensure((n_reads + 1) * 8) || d_scr.ensure((size_t)threads * 7 * L1 * sizeof(Intv)) ||
-        d_arena.ensure((size_t)intv_cap * sizeof(Intv) + 32) || d_used.ensure(64) || d_ioff.ensure(n_reads * 8 + 8) || d_in.ensure(n_reads * 4 + 4) ||
-        d_nsa.ensure(n_reads * 4 + 4) || d_cnt.ensure(sizeof(Counters))) { set_error("out of device memory"); return ARACHNE_ERR_CUDA; }
+    auto rel = [&]() { for (DevBuf* b : {&d_seq, &d_off, &d_scr, &d_arena, &d_next, &d_in, &d_nsa, &d_cnt}) b->release(); };
+    if (d_seq.ensure(nb + 16) || d_off.ensure((n_reads + 1) * 8) || d_scr.ensure((size_t)T * rows * sizeof(uint4)) || d_next.ensure(64) ||
+        d_in.ensure(n_reads * 4 + 4) || d_nsa.ensure(n_reads * 4 + 4) || d_cnt.ensure(sizeof(Counters))) { rel(); set_error("out of device memory"); return ARACHNE_ERR_CUDA; }
     AR_CUDA(cudaMemcpy(d_seq.p, seq, nb, cudaMemcpyHostToDevice));
     AR_CUDA(cudaMemcpy(d_off.p, seq_off, (n_reads + 1) * 8, cudaMemcpyHostToDevice));
-    AR_CUDA(cudaMemset(d_used.p, 0, 64)); AR_CUDA(cudaMemset(d_cnt.p, 0, sizeof(Counters)));
-    k_seed<<<threads / 128, 128>>>(idx->fm, opt, d_seq.as<uint8_t>(), d_off.as<int64_t>(), (int)n_reads, maxlen, d_scr.as<Intv>(), L1, d_arena.as<Intv>(),
-                                    (unsigned long long)intv_cap, d_used.as<unsigned long long>(), d_ioff.as<unsigned long long>(), d_in.as<int>(),
-                                    d_nsa.as<unsigned int>(), d_cnt.as<Counters>());
-    AR_CUDA(cudaGetLastError());
     Counters hc;
-    AR_CUDA(cudaMemcpy(&hc, d_cnt.p, sizeof(hc), cudaMemcpyDeviceToHost));
-    if (hc.err) { set_error("interval capacity too small"); return ARACHNE_ERR_OVERFLOW; }
-    std::vector<unsigned long long> ioff(n_reads); std::vector<int> in_(n_reads);
-    unsigned long long used = 0;
-    AR_CUDA(cudaMemcpy(ioff.data(), d_ioff.p, n_reads * 8, cudaMemcpyDeviceToHost));
+    for (int attempt = 0;; ++attempt) {
+        if (d_arena.ensure((size_t)n_reads * cap * sizeof(Intv) + 32)) { rel(); set_error("out of device memory"); return ARACHNE_ERR_CUDA; }
+        AR_CUDA(cudaMemset(d_next.p, 0, 64)); AR_CUDA(cudaMemset(d_cnt.p, 0, sizeof(Counters)));
+        AR_CUDA(cudaMemset(d_in.p, 0, n_reads * 4 + 4)); AR_CUDA(cudaMemset(d_nsa.p, 0, n_reads * 4 + 4));
+        SeedOut so; so.intv = d_arena.as<Intv>(); so.intv_n = d_in.as<int>(); so.n_sa = d_nsa.as<unsigned int>(); so.cap = cap;
+        k_seed2<<<blocks, 256>>>(idx->fm, opt, d_seq.as<uint8_t>(), d_off.as<int64_t>(), (int)n_reads, maxlen, d_scr.as<uint4>(), rows, so,
+                                 d_next.as<unsigned int>(), d_cnt.as<Counters>());
+        AR_CUDA(cudaGetLastError());
+        AR_CUDA(cudaMemcpy(&hc, d_cnt.p, sizeof(hc), cudaMemcpyDeviceToHost));
+        if (!hc.err) break;
+        if (attempt >= 3) { rel(); set_error("more than %d intervals at read %d", cap, hc.err_read); return ARACHNE_ERR_OVERFLOW; }
+        cap *= 4;
+    }
+    k_sort_intv<<<256, 128>>>((int)n_reads, d_arena.as<Intv>(), d_in.as<int>(), cap);
+    AR_CUDA(cudaGetLastError());
+    std::vector<int> in_(n_reads);
     AR_CUDA(cudaMemcpy(in_.data(), d_in.p, n_reads * 4, cudaMemcpyDeviceToHost));
-    AR_CUDA(cudaMemcpy(&used, d_used.p, 8, cudaMemcpyDeviceToHost));
-    std::vector<Intv> a(used + 1);
-    AR_CUDA(cudaMemcpy(a.data(), d_arena.p, used * sizeof(Intv), cudaMemcpyDeviceToHost));
+    std::vector<Intv> a((size_t)n_reads * cap + 1);
+    AR_CUDA(cudaMemcpy(a.data(), d_arena.p, (size_t)n_reads * cap * sizeof(Intv), cudaMemcpyDeviceToHost));
     int64_t o = 0;
-    for (int64_t r = 0; r < n_reads; ++r) {  // arena slots are handed out in completion order; re-pack in read order
+    for (int64_t r = 0; r < n_reads; ++r) {
         intv_off[r] = o;
-        memcpy(intv + 4 * o, a.data() + ioff[r], (size_t)in_[r] * sizeof(Intv));
+        if (o + in_[r] > intv_cap) { rel(); set_error("interval capacity too small"); return ARACHNE_ERR_OVERFLOW; }
+        memcpy(intv + 4 * o, a.data() + (size_t)r * cap, (size_t)in_[r] * sizeof(Intv));
         o += in_[r];
     }
     intv_off[n_reads] = o;
-    for (DevBuf* b : {&d_seq, &d_off, &d_scr, &d_arena, &d_used, &d_ioff, &d_in, &d_nsa, &d_cnt}) b->release();
+    rel();
     return ARACHNE_OK;
 }
 

@@ -7,6 +7,7 @@
 #include <cstring>
 #include <string>
 #include <vector>
+#include "../../arachne_b200/csrc/bwt_image.h"
 #include "../../arachne_b200/csrc/smem.cuh"
 #include "../../arachne_b200/csrc/extend.cuh"
 #include "../../arachne_b200/csrc/rescue.cuh"
@@ -24,7 +25,7 @@ int arachne_opts_default_host(arachne_mem_opt_t* o);
 using namespace arachne;
 
 struct HostIndex {
-    std::vector<uint8_t> bwt, sa_raw, pac;
+    std::vector<uint8_t> bwt, sa_raw, pac, image;
     std::vector<uint64_t> sa;
     std::vector<Contig> contigs;
     FMIndex fm;
@@ -96,7 +97,8 @@ void* hs_load(const char* prefix_) {
     FMIndex& fm = h->fm;
     fm.primary = bh[0]; fm.L2[0] = 0; for (int i = 1; i <= 4; ++i) fm.L2[i] = bh[i];
     fm.seq_len = fm.L2[4];
-    fm.blocks = (const OccBlock*)(h->bwt.data() + 40);
+    if (!bwt_recut_image(h->bwt.data() + 40, h->bwt.size() - 40, fm.seq_len, h->image)) { delete h; return nullptr; }
+    fm.blocks = (const Blk32*)h->image.data();
     const uint64_t* sh = (const uint64_t*)h->sa_raw.data();
     fm.sa_intv = (int)sh[5]; fm.n_sa = (fm.seq_len + fm.sa_intv) / fm.sa_intv;
     h->sa.resize(fm.n_sa); h->sa[0] = (uint64_t)-1; memcpy(h->sa.data() + 1, h->sa_raw.data() + 56, (fm.n_sa - 1) * 8);
