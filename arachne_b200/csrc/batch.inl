@@ -166,9 +166,24 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
     AR_ALLOC(W.d_win, (size_t)std::max<long>(cg_warps, (long)ext_blocks * EXT_WARPS) * win_cap);
     AR_TRY(cudaMemsetAsync(W.d_misc.p, 0, 64, st));
     ++nl;
-    k_extend<<<ext_blocks, EXT_WARPS * 32, 0, st>>>(opt, idx->ref, d_seq, d_off, (int)n_reads, W.d_sa_off.as<unsigned long long>(),
-                                                    cb, W.d_srt.as<uint64_t>(), W.d_regs.as<AlnReg>(), W.d_nregs.as<int>(), W.d_win.as<uint8_t>(), win_cap,
-                                                    W.d_misc.as<unsigned int>(), W.d_cnt.as<Counters>());
+    {
+        const size_t smem = (size_t)(maxlen + 1 + EXT_CHUNK) * EXT_BLOCK * sizeof(uint32_t);
+        if (smem > 200 * 1024) { set_error("read length %d does not fit the extension kernel's shared-memory columns", maxlen); return fail(ARACHNE_ERR_ARG); }
+        AR_TRY(cudaFuncSetAttribute(k_extend2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        int per_sm = 0;
+        AR_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_extend2, EXT_BLOCK, smem));
+        if (per_sm < 1) per_sm = 1;
+        const int xblocks = sms * per_sm;
+        const size_t xT = (size_t)xblocks * EXT_BLOCK;
+        AR_ALLOC(W.d_hscr, xT * 2 * (maxlen + 2) * sizeof(int));
+        AR_ALLOC(W.d_rscr, xT * win_cap);
+        ExtArgs xa;
+        xa.seq = d_seq; xa.off = d_off; xa.n_reads = (int)n_reads; xa.sa_off = W.d_sa_off.as<unsigned long long>(); xa.b = cb;
+        xa.srt = W.d_srt.as<uint64_t>(); xa.regs = W.d_regs.as<AlnReg>(); xa.n_regs = W.d_nregs.as<int>();
+        xa.hscr = W.d_hscr.as<int>(); xa.rscr = W.d_rscr.as<uint8_t>(); xa.rcap = win_cap; xa.maxlen = maxlen;
+        xa.next = W.d_misc.as<unsigned int>(); xa.cnt = W.d_cnt.as<Counters>();
+        k_extend2<<<xblocks, EXT_BLOCK, smem, st>>>(opt, idx->ref, xa);
+    }
     AR_TRY(cudaGetLastError());
     cudaEventRecord(ev[4], st);
     int stages = in->stages ? in->stages : (ARACHNE_STAGE_REGIONS | ARACHNE_STAGE_RESCUE | ARACHNE_STAGE_CIGAR);

@@ -134,7 +134,12 @@ __global__ void __launch_bounds__(128) k_chain(MemOpt opt, RefView ref, const in
     }
 }
 
-// ------------------------------------------------------------------------------------------------ k_extend
+// ------------------------------------------------------------------------------------------------ k_extend2
+}  // namespace arachne
+#include "extend_kernel.cuh"
+namespace arachne {
+
+// ------------------------------------------------------------------------------------------------ k_extend (warp per read; kept for the stage entry points)
 constexpr int EXT_WARPS = 4;
 
 __global__ void __launch_bounds__(EXT_WARPS * 32) k_extend(MemOpt opt, RefView ref, const uint8_t* __restrict__ seq, const int64_t* __restrict__ off,
@@ -433,7 +438,7 @@ struct BatchPriv {
 struct Workspace {
     DevBuf d_seq, d_off, d_scratch, d_arena, d_misc, d_intv_off, d_intv_n, d_nsa, d_sa_off, d_rows, d_cnt, d_tmp;
     DevBuf d_seeds, d_kseeds, d_chains, d_nodes, d_order, d_kept, d_nchain, d_nkseed, d_srt, d_regs, d_nregs, d_win, d_reg_off, d_out;
-    DevBuf d_nregs_bak, d_reg_loc, d_blist, d_resc, d_reg_read, d_z, d_cig_scr, d_mm_scr, d_alns, d_cig, d_mm;
+    DevBuf d_nregs_bak, d_reg_loc, d_blist, d_resc, d_reg_read, d_z, d_cig_scr, d_mm_scr, d_alns, d_cig, d_mm, d_hscr, d_rscr;
     cudaStream_t own_stream = nullptr;
     cudaEvent_t ev[8] = {};
     Counters* h_cnt = nullptr;              // pinned
@@ -442,7 +447,7 @@ struct Workspace {
     std::vector<DevBuf*> all() {
         return {&d_seq, &d_off, &d_scratch, &d_arena, &d_misc, &d_intv_off, &d_intv_n, &d_nsa, &d_sa_off, &d_rows, &d_cnt, &d_tmp,
                 &d_seeds, &d_kseeds, &d_chains, &d_nodes, &d_order, &d_kept, &d_nchain, &d_nkseed, &d_srt, &d_regs, &d_nregs,
-                &d_win, &d_reg_off, &d_out, &d_nregs_bak, &d_reg_loc, &d_blist, &d_resc, &d_reg_read, &d_z, &d_cig_scr, &d_mm_scr, &d_alns, &d_cig, &d_mm};
+                &d_win, &d_reg_off, &d_out, &d_nregs_bak, &d_reg_loc, &d_blist, &d_resc, &d_reg_read, &d_z, &d_cig_scr, &d_mm_scr, &d_alns, &d_cig, &d_mm, &d_hscr, &d_rscr};
     }
     int init() {
         if (cudaStreamCreateWithFlags(&own_stream, cudaStreamNonBlocking) != cudaSuccess) return -1;
