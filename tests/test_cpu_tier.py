@@ -1,0 +1,239 @@
+"""CPU tier (pytest -m "not gpu"): the oracle against the golden vectors (outputs of the reference's own code,
+scripts/make_golden.py) and, where it is built, against oracle/_ref directly; the host-side logic (host simulation of
+the thread-sequential device code, barcode sharding under gloo with world_size 2); and the C ABI surface."""
+import ctypes as C
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from tests import util
+
+ROOT = util.ROOT
+
+
+@pytest.fixture(scope="module")
+def O():
+    return util.oracle_lib()
+
+
+@pytest.fixture(scope="module")
+def HS():
+    return util.HostSim()
+
+
+def _problems(d, p):
+    qo, to = d[p + "_qo"], d[p + "_to"]
+    return [(d[p + "_q"][qo[i]:qo[i + 1]], d[p + "_t"][to[i]:to[i + 1]]) for i in range(len(qo) - 1)]
+
+
+# ---- oracle restatement (oracle/restate_ksw.c) vs golden known answers from the reference ----
+def test_oracle_ksw_extend_golden(O):
+    d = util.load_golden("ksw_kat")
+    pr = _problems(d, "ext"); n = len(pr)
+    for s, (zd, eb) in enumerate(((100, 5), (0, 0), (20, 5))):
+        for i, (q, t) in enumerate(pr):
+            got, _ = util.orc_extend(O, q, t, int(d["ext_w"][i]), eb, zd, int(d["ext_h0"][i]))
+            assert got == tuple(d["ext_out"][s * n + i]), (s, i)
+
+
+def test_oracle_ksw_global_golden(O):
+    d = util.load_golden("ksw_kat")
+    co = np.zeros(len(d["glb_w"]) + 1, dtype=np.int64)
+    pr = _problems(d, "glb")
+    pos = 0
+    for i, (q, t) in enumerate(pr):
+        sc, cig = util.orc_global(O, q, t, int(d["glb_w"][i]))
+        assert sc == d["glb_score"][i], i
+        assert cig == list(d["glb_cig"][pos:pos + len(cig)]), i
+        pos += len(cig)
+    assert pos == len(d["glb_cig"])
+
+
+def test_oracle_ksw_local_golden(O):
+    d = util.load_golden("ksw_kat")
+    for i, (q, t) in enumerate(_problems(d, "loc")):
+        assert util.orc_local(O, q, t, int(d["loc_x"][i])) == tuple(d["loc_out"][i]), i
+
+
+def test_oracle_vs_reference_live(O):
+    """Fresh random problems against the reference's compiled sources (skipped where oracle/_ref is absent)."""
+    from oracle.refbwa import RefBwa, available
+    if not available():
+        pytest.skip("oracle/_ref not built (no /root/reference here)")
+    R = RefBwa()
+    qs, ts, h0, w = util.extension_problems(int.from_bytes(os.urandom(2), "little"), 800)
+    for i in range(len(qs)):
+        for zd, eb in ((100, 5), (0, 0)):
+            got, _ = util.orc_extend(O, qs[i], ts[i], int(w[i]), eb, zd, int(h0[i]))
+            assert got == R.ksw_extend2(qs[i], ts[i], int(w[i]), eb, zd, int(h0[i])), i
+        if len(ts[i]) and len(qs[i]):
+            ww = max(abs(len(ts[i]) - len(qs[i])) + 3, int(w[i]))
+            assert util.orc_global(O, qs[i], ts[i], ww) == R.ksw_global2(qs[i], ts[i], ww), i
+
+
+# ---- host simulation of the device logic vs golden pipeline outputs ----
+@pytest.mark.parametrize("name", ["tiny_rand", "tiny_rep"])
+def test_hostsim_pipeline_golden(HS, workdir, name):
+    from arachne_b200.lib import ALNREG
+    d, prefix = util.load_golden(name, workdir)
+    HS.load(prefix)
+    for i in range(len(d["occ_k"])):
+        assert HS.occ(d["occ_k"][i], d["occ_l"][i]) == list(d["occ_out"][i])
+        assert HS.occ(int(d["occ_k"][i]) - 1, d["occ_l"][i]) == list(d["occ_out_km1"][i])
+        assert HS.sa(d["occ_k"][i]) == d["sa_out"][i]
+    seq, off = d["seq"], d["off"]
+    n_pairs = (len(off) - 1) // 2
+    s1 = d["s1_regs"].view(ALNREG); s7 = d["s7_regs"].view(ALNREG)
+    assert d["s1_regs"].tobytes() != d["s7_regs"].tobytes(), "fixture does not exercise mate rescue"
+    n_cig = 0
+    for p in range(n_pairs):
+        r1, r2 = seq[off[2 * p]:off[2 * p + 1]], seq[off[2 * p + 1]:off[2 * p + 2]]
+        for k, q in ((2 * p, r1), (2 * p + 1, r2)):
+            exp = s1[d["s1_reg_off"][k]:d["s1_reg_off"][k + 1]]
+            assert HS.align1(q).tobytes() == exp.tobytes(), ("align1", k)
+        o1, o2 = HS.pair(r1, r2)
+        for k, q, got in ((2 * p, r1, o1), (2 * p + 1, r2, o2)):
+            lo, hi = d["s7_reg_off"][k], d["s7_reg_off"][k + 1]
+            assert got.tobytes() == s7[lo:hi].tobytes(), ("pair", k)
+            if p % 3 == 0:  # CIGAR / NM / pos for every third pair keeps the tier fast
+                for j in range(lo, hi):
+                    a, cig, _mm = HS.reg2aln(q, s7[j:j + 1])
+                    e = d["s7_aln"][j]
+                    assert (a["pos"], a["rid"], a["is_rev"], a["nm"], a["n_cigar"], a["score"], a["sub"]) == (e[0], e[1], e[2], e[3], e[4], e[6], e[7]), j
+                    assert np.array_equal(cig, d["s7_cigar"][e[5]:e[5] + e[4]]), j
+                    n_cig += 1
+    assert n_cig > 50
+
+
+def test_hostsim_seed_intervals_live(HS, workdir):
+    """mem_collect_intv restated from bwt_smem1 / bwt_seed_strategy1 calls on the reference's code (needs oracle/_ref)."""
+    from oracle.refbwa import RefBwa, available
+    if not available():
+        pytest.skip("oracle/_ref not built")
+    d, prefix = util.load_golden("tiny_rep", workdir)
+    R = RefBwa().load(prefix); HS.load(prefix)
+    seq, off = d["seq"], d["off"]
+    for r in range(0, 120):
+        q = seq[off[r]:off[r + 1]]
+        got = HS.seed(q)
+        # mem_collect_intv (bwamem.c:114-162) composed from the reference's own primitives
+        L = len(q); exp = []
+        x = 0
+        while x < L:
+            if q[x] < 4:
+                x, iv = R.smem1(q, x)
+                exp += [tuple(int(v) for v in a) for a in iv if (int(a[3]) & 0xffffffff) - (int(a[3]) >> 32) >= 19]
+            else:
+                x += 1
+        first = list(exp)
+        for a in first:
+            s, e = a[3] >> 32, a[3] & 0xffffffff
+            if e - s < 28 or a[2] > 10:
+                continue
+            _, iv = R.smem1(q, (s + e) >> 1, a[2] + 1)
+            exp += [tuple(int(v) for v in b) for b in iv if (int(b[3]) & 0xffffffff) - (int(b[3]) >> 32) >= 19]
+        x = 0
+        while x < L:
+            if q[x] < 4:
+                x, m = R.seed_strategy1(q, x, 19, 20)
+                if m[2] > 0:
+                    exp.append(tuple(m))
+            else:
+                x += 1
+        exp.sort(key=lambda a: a[3])
+        assert sorted(map(tuple, got.tolist()), key=lambda a: a[3]) == exp or [tuple(a) for a in got.tolist()] == exp, r
+        assert [a[3] for a in got.tolist()] == [a[3] for a in exp], r
+
+
+# ---- C ABI surface ----
+def test_abi_exports_every_declared_symbol():
+    from arachne_b200.lib import lib_path
+    assert os.path.exists(lib_path()), "libarachne_cuda.so missing: run __graft_entry__.build()"
+    lib = C.CDLL(lib_path())
+    declared = []
+    for h in sorted(os.listdir(os.path.join(ROOT, "include"))):
+        src = open(os.path.join(ROOT, "include", h)).read()
+        src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+        declared += re.findall(r"\b((?:arachne|mem|bwa|bns|bwt)_[a-z0-9_]+)\s*\(", src)
+    declared = sorted(set(declared))
+    assert len(declared) >= 15
+    missing = [s for s in declared if not hasattr(lib, s)]
+    assert not missing, missing
+
+
+def test_abi_defaults_and_errors_without_device():
+    """Host-only entry points work without a GPU; compute entry points fail loudly (no CPU fallback)."""
+    from arachne_b200 import ArachneCuda, ArachneError
+    A = ArachneCuda()
+    o = A.opt
+    assert (o.a, o.b, o.o_del, o.e_del, o.o_ins, o.e_ins, o.w, o.zdrop, o.T, o.min_seed_len, o.max_occ, o.max_chain_gap) == (1, 4, 6, 1, 6, 1, 100, 100, 30, 19, 500, 10000)
+    assert (o.pen_clip5, o.pen_clip3, o.max_mem_intv, o.split_width, o.max_matesw) == (5, 5, 20, 10, 50)
+    assert abs(o.split_factor - 1.5) < 1e-6 and abs(o.mask_level_redun - 0.95) < 1e-6 and abs(o.drop_ratio - 0.5) < 1e-6
+    assert list(o.mat) == [1, -4, -4, -4, -1, -4, 1, -4, -4, -1, -4, -4, 1, -4, -1, -4, -4, -4, 1, -1, -1, -1, -1, -1, -1]
+    from oracle.refbwa import RefBwa, available
+    if available():
+        assert bytes(o)[:C.sizeof(o)] == RefBwa().opt_default()[:C.sizeof(o)], "arachne_mem_opt_t differs from mem_opt_init()"
+    if A.device_count() == 0:
+        q = np.zeros(10, np.uint8); qo = np.array([0, 10], np.int64)
+        with pytest.raises(ArachneError):
+            A.ksw_extend(q, qo, q, qo, np.array([10], np.int32), np.array([10], np.int32))
+        with pytest.raises(ArachneError):
+            A.load_index("/nonexistent/prefix")
+
+
+# ---- barcode sharding: host logic, world_size 2 over gloo ----
+def test_shard_barcodes_properties():
+    from arachne_b200.shard import shard_barcodes
+    g = np.random.default_rng(0)
+    for _ in range(50):
+        n = int(g.integers(0, 40)); sizes = g.integers(1, 400, n)
+        bc = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
+        for w in (1, 2, 3, 4, 8):
+            sh = shard_barcodes(bc, w)
+            assert len(sh) == w and sh[0][0] == 0 and sh[-1][1] == n
+            assert all(sh[i][1] == sh[i + 1][0] for i in range(w - 1)) and all(a <= b for a, b in sh)
+            if n >= 4 * w:
+                loads = [int(bc[b] - bc[a]) for a, b in sh]
+                assert max(loads) - min(loads) <= 2 * int(sizes.max())
+
+
+_GLOO_WORKER = r"""
+import os, sys, pickle
+sys.path.insert(0, {root!r})
+import numpy as np, torch.distributed as dist
+from tests import util
+from arachne_b200.shard import shard_barcodes, shard_view, merge_results
+rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+dist.init_process_group("gloo")
+d, prefix = util.load_golden("tiny_rand", {wd!r} + "/r%d" % rank) if os.makedirs({wd!r} + "/r%d" % rank, exist_ok=True) is None else None
+HS = util.HostSim().load(prefix)
+lo, hi = shard_barcodes(d["bc_off"], world)[rank]
+seq, off, bc = shard_view(d["seq"], d["off"], d["bc_off"], lo, hi)
+regs, reg_off = [], [0]
+for p in range((len(off) - 1) // 2):
+    o1, o2 = HS.pair(seq[off[2*p]:off[2*p+1]], seq[off[2*p+1]:off[2*p+2]])
+    for o in (o1, o2):
+        regs.append(o); reg_off.append(reg_off[-1] + len(o))
+part = dict(reg_off=np.array(reg_off, dtype=np.int64), regs=np.concatenate(regs) if regs else np.zeros(0, dtype=util.ALNREG_DT()))
+out = [None] * world
+dist.gather_object(part, out if rank == 0 else None, dst=0)
+if rank == 0:
+    m = merge_results(out)
+    from arachne_b200.lib import ALNREG
+    ok = np.array_equal(m["reg_off"], d["s7_reg_off"]) and m["regs"].tobytes() == d["s7_regs"].tobytes()
+    print("SHARD_MERGE_OK" if ok else "SHARD_MERGE_MISMATCH", flush=True)
+dist.destroy_process_group()
+"""
+
+
+def test_sharded_two_ranks_gloo_matches_unsharded(workdir):
+    util.HostSim()  # build once before the ranks race on make
+    script = os.path.join(workdir, "gloo_worker.py")
+    open(script, "w").write(_GLOO_WORKER.format(root=ROOT, wd=workdir))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+                        "--master-port", str(29500 + os.getpid() % 2000), script], capture_output=True, text=True, timeout=600)
+    assert "SHARD_MERGE_OK" in r.stdout, (r.stdout[-2000:], r.stderr[-2000:])

@@ -117,3 +117,97 @@ def make_dataset(name, workdir, damaged=False):
     if damaged:
         rs = damage(rs, 0.3, 0.11, 5)
     return fa, ctg, rs
+
+
+# ------------------------------------------------------------------------------------------------ golden fixtures
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def load_golden(name, workdir=None):
+    """tests/golden/<name>.npz (made by scripts/make_golden.py from the reference's own code).  With workdir, the BWA
+    index files the fixture carries are written to <workdir>/<name>.fa.{bwt,sa,pac,ann,amb} and the prefix returned."""
+    d = dict(np.load(os.path.join(GOLDEN, name + ".npz")))
+    if workdir is None:
+        return d
+    prefix = os.path.join(workdir, name + ".fa")
+    for ext in ("bwt", "sa", "pac", "ann", "amb"):
+        p = prefix + "." + ext
+        if not os.path.exists(p):
+            with open(p, "wb") as f:
+                f.write(d["idx_" + ext].tobytes())
+    return d, prefix
+
+
+# ------------------------------------------------------------------------------------------------ host simulation
+class HostSim:
+    """tests/hostsim/libhostsim.so: the product's thread-sequential device logic (csrc/*.cuh) compiled for the host."""
+
+    def __init__(self):
+        d = os.path.join(ROOT, "tests", "hostsim")
+        subprocess.run(["make", "-s", "-C", d], check=True, stdout=subprocess.DEVNULL)
+        L = self.lib = C.CDLL(os.path.join(d, "libhostsim.so"))
+        L.hs_load.restype = C.c_void_p; L.hs_load.argtypes = [C.c_char_p]
+        L.hs_free.argtypes = [C.c_void_p]
+        L.hs_occ.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+        L.hs_sa.restype = C.c_uint64; L.hs_sa.argtypes = [C.c_void_p, C.c_uint64]
+        L.hs_seed.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint8), C.POINTER(C.c_uint64), C.c_int]
+        L.hs_align1.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint8), C.c_void_p, C.c_int, C.POINTER(C.c_uint64)]
+        L.hs_pair.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint8), C.c_int, C.POINTER(C.c_uint8), C.c_int, C.c_void_p, C.POINTER(C.c_int),
+                              C.c_void_p, C.POINTER(C.c_int), C.c_int]
+        L.hs_reg2aln.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint8), C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32), C.c_int, C.POINTER(C.c_int32)]
+        self.h = None
+
+    def load(self, prefix):
+        self.h = L = self.lib.hs_load(prefix.encode())
+        if not L:
+            raise RuntimeError("hs_load failed: " + prefix)
+        return self
+
+    def occ(self, k, l):
+        a = (C.c_uint64 * 4)(); b = (C.c_uint64 * 4)()
+        self.lib.hs_occ(self.h, C.c_uint64(int(k) & (2**64 - 1)), C.c_uint64(int(l) & (2**64 - 1)), a, b)
+        return list(a) + list(b)
+
+    def sa(self, k):
+        return self.lib.hs_sa(self.h, int(k))
+
+    def seed(self, q, cap=1024):
+        q, qp = u8p(q); out = (C.c_uint64 * (4 * cap))()
+        n = self.lib.hs_seed(self.h, len(q), qp, out, cap)
+        return np.array(out[:4 * max(n, 0)], dtype=np.uint64).reshape(-1, 4)
+
+    def pair(self, r1, r2, score_delta=25, cap=512):
+        from arachne_b200.lib import ALNREG
+        r1, p1 = u8p(r1); r2, p2 = u8p(r2)
+        o1 = np.zeros(cap, dtype=ALNREG); o2 = np.zeros(cap, dtype=ALNREG); n1 = C.c_int(0); n2 = C.c_int(0)
+        rc = self.lib.hs_pair(self.h, len(r1), p1, len(r2), p2, score_delta, o1.ctypes.data_as(C.c_void_p), C.byref(n1),
+                              o2.ctypes.data_as(C.c_void_p), C.byref(n2), cap)
+        assert rc == 0, rc
+        return o1[:n1.value], o2[:n2.value]
+
+    def align1(self, q, cap=512):
+        from arachne_b200.lib import ALNREG
+        q, qp = u8p(q); out = np.zeros(cap, dtype=ALNREG); cnt = (C.c_uint64 * 3)()
+        n = self.lib.hs_align1(self.h, len(q), qp, out.ctypes.data_as(C.c_void_p), cap, cnt)
+        assert n >= 0, n
+        return out[:n]
+
+    def reg2aln(self, q, reg):
+        from arachne_b200.lib import ALN
+        q, qp = u8p(q); out = np.zeros(1, dtype=ALN); cap = 2 * len(q) + 64; cig = (C.c_uint32 * cap)(); mm = (C.c_int32 * (2 * len(q) + 8))()
+        r = np.ascontiguousarray(reg)
+        rc = self.lib.hs_reg2aln(self.h, len(q), qp, r.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p), cig, cap, mm)
+        assert rc == 0, rc
+        a = out[0]
+        return a, np.array(cig[:a["n_cigar"]], dtype=np.uint32), np.array(mm[:2 * a["n_mm"]], dtype=np.int32)
+
+
+def orc_local(O, q, t, xtra):
+    q, qp = u8p(q); t, tp = u8p(t); out = (C.c_int * 7)()
+    O.orc_local(C.byref(DEFAULT_SC), len(q), qp, len(t), tp, xtra, out)
+    return tuple(out)
+
+
+def ALNREG_DT():
+    from arachne_b200.lib import ALNREG
+    return ALNREG
