@@ -1,0 +1,63 @@
+/* TEST INFRASTRUCTURE ONLY -- CPU restatement of the reference's Go placement code.
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may use anything under oracle/.
+ *
+ * PARITY UNPINNED against Go execution: this box has no Go toolchain and the reference tree does not compile as shipped
+ * (SURVEY.md "facts").  What is pinned: Go's math/rand source (gorand_table.h, checked against Go's published known
+ * outputs) and MD5 (RFC 1321 vectors).  sort.Sort's pdqsort tie order on equal positions is NOT reproduced (stable order used).
+ */
+#ifndef ORACLE_RESTATE_PLACE_H_
+#define ORACLE_RESTATE_PLACE_H_
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* one record per entry of Go's `alignments [][]*Alignment` (src/aligner/aligner.go:65-114), CSR by read */
+typedef struct {
+    int32_t reg;          /* index into the batch region array, -1 = unmapped placeholder (aligner.go:1664-1676) */
+    int32_t read;         /* batch-global read index */
+    int32_t id;           /* hit_id */
+    int32_t active, is_proper, bwa_pick;
+    int32_t mapq;
+    int32_t molecule_id;  /* within the barcode, after scrapMolecules; -1 none */
+    int32_t active_molecule;
+    int32_t second_best;  /* mapq_data.second_best as a batch-global candidate index, -1 nil (active alignments only) */
+    int32_t mate;         /* mate_alignment as a batch-global candidate index, -1 nil */
+    int32_t duplicate;
+    int64_t pos, aend;
+    double log_alignment_probability;
+    double as_score;      /* mapq_data.score */
+    double xs_score;      /* mapq_data.second_best_score */
+    double molecule_difference;
+    double sum_move_probability_change;
+    double molecule_confidence;
+    double raw_mapq;      /* the float before int() truncation (tolerance checks) */
+} orc_cand_t;
+
+typedef struct {
+    int64_t l_pac;
+    int32_t n_seqs;
+    const int64_t *ctg_off;   /* n_seqs */
+    const int32_t *ctg_len;
+    const uint8_t *pac;
+    const int64_t *centro_start, *centro_end; /* per rid, or NULL: -1,-1 (aligner.go:906-916) */
+} orc_ref_t;
+
+/* regs: 88-byte mem_alnreg_t records; aln: 8 int64 per region {pos rid is_rev NM n_cigar cigar_off score sub} as oracle/ref_shim.c emits */
+int orc_place(const orc_ref_t *ref, int64_t n_pairs, const uint8_t *seq, const int64_t *off, int64_t n_bc, const int64_t *bc_off,
+              const uint8_t *run_rfa, const int64_t *rand_seed, const int64_t *reg_off, const void *regs, const int64_t *aln,
+              const uint32_t *cigar, double improper_penalty, int delta, int64_t *cand_off /* 2*n_pairs+1 */, orc_cand_t *cands, int64_t cap,
+              double *log_molecule_penalty /* per barcode, may be NULL */);
+
+/* GetAlignments walk for one region (aligner.go:1505-1569): out5 = matches mismatches indels soft_clipped soft_clipped_length;
+ * mm receives n ref loci then n read offsets; returns n */
+int orc_walk(const orc_ref_t *ref, int l_query, const uint8_t *query, const void *reg, const int64_t *aln8, const uint32_t *cigar, int *out5, int32_t *mm);
+
+int64_t orc_name_seed(const char *name, int len);        /* int64(LittleEndian.Uint64(md5(name)[0:8])) */
+void orc_md5(const uint8_t *msg, int64_t len, uint8_t out[16]);
+void orc_gorand_float64(int64_t seed, int n, double *out); /* first n Float64() of rand.New(rand.NewSource(seed)) */
+
+#ifdef __cplusplus
+}
+#endif
+#endif

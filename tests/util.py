@@ -211,3 +211,61 @@ def orc_local(O, q, t, xtra):
 def ALNREG_DT():
     from arachne_b200.lib import ALNREG
     return ALNREG
+
+
+# ------------------------------------------------------------------------------------------------ placement oracle
+class OrcRef(C.Structure):
+    _fields_ = [("l_pac", C.c_int64), ("n_seqs", C.c_int32), ("ctg_off", C.POINTER(C.c_int64)), ("ctg_len", C.POINTER(C.c_int32)),
+                ("pac", C.POINTER(C.c_uint8)), ("centro_start", C.POINTER(C.c_int64)), ("centro_end", C.POINTER(C.c_int64))]
+
+
+CAND = np.dtype([("reg", "<i4"), ("read", "<i4"), ("id", "<i4"), ("active", "<i4"), ("is_proper", "<i4"), ("bwa_pick", "<i4"), ("mapq", "<i4"),
+                 ("molecule_id", "<i4"), ("active_molecule", "<i4"), ("second_best", "<i4"), ("mate", "<i4"), ("duplicate", "<i4"),
+                 ("pos", "<i8"), ("aend", "<i8"), ("lap", "<f8"), ("as_score", "<f8"), ("xs_score", "<f8"), ("molecule_difference", "<f8"),
+                 ("sum_move", "<f8"), ("molecule_confidence", "<f8"), ("raw_mapq", "<f8")])
+assert CAND.itemsize == 120
+
+
+def read_ann(prefix):
+    """(l_pac, [(name, offset, len)]) from a bwa .ann file (bntseq.c:93-130)."""
+    with open(prefix + ".ann") as f:
+        l_pac, n, _ = f.readline().split()
+        ctg = []
+        for _ in range(int(n)):
+            name = f.readline().split()[1]
+            off, ln, _na = f.readline().split()
+            ctg.append((name, int(off), int(ln)))
+    return int(l_pac), ctg
+
+
+class PlaceOracle:
+    def __init__(self, prefix, centromeres=None):
+        self.O = oracle_lib()
+        self.l_pac, self.ctg = read_ann(prefix)
+        self.pac = np.fromfile(prefix + ".pac", dtype=np.uint8)
+        self.coff = np.array([c[1] for c in self.ctg], dtype=np.int64); self.clen = np.array([c[2] for c in self.ctg], dtype=np.int32)
+        self.ref = OrcRef(self.l_pac, len(self.ctg), self.coff.ctypes.data_as(C.POINTER(C.c_int64)), self.clen.ctypes.data_as(C.POINTER(C.c_int32)),
+                          self.pac.ctypes.data_as(C.POINTER(C.c_uint8)), None, None)
+        if centromeres is not None:
+            self.cs = np.ascontiguousarray(centromeres[0], dtype=np.int64); self.ce = np.ascontiguousarray(centromeres[1], dtype=np.int64)
+            self.ref.centro_start = self.cs.ctypes.data_as(C.POINTER(C.c_int64)); self.ref.centro_end = self.ce.ctypes.data_as(C.POINTER(C.c_int64))
+        self.O.orc_place.argtypes = [C.POINTER(OrcRef), C.c_int64, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                     C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
+        self.O.orc_name_seed.restype = C.c_int64; self.O.orc_name_seed.argtypes = [C.c_char_p, C.c_int]
+
+    def name_seed(self, name: str) -> int:
+        b = name.encode()
+        return self.O.orc_name_seed(b, len(b))
+
+    def place(self, seq, off, bc_off, run_rfa, seeds, reg_off, regs, aln8, cigar, improper=-4.0, delta=17):
+        seq = np.ascontiguousarray(seq, np.uint8); off = np.ascontiguousarray(off, np.int64); bc_off = np.ascontiguousarray(bc_off, np.int64)
+        run_rfa = np.ascontiguousarray(run_rfa, np.uint8); seeds = np.ascontiguousarray(seeds, np.int64)
+        reg_off = np.ascontiguousarray(reg_off, np.int64); regs = np.ascontiguousarray(regs); aln8 = np.ascontiguousarray(aln8, np.int64)
+        cigar = np.ascontiguousarray(cigar, np.uint32)
+        n_pairs = (len(off) - 1) // 2; cap = len(regs) + 2 * n_pairs + 8
+        cand_off = np.zeros(2 * n_pairs + 1, np.int64); cands = np.zeros(cap, CAND); lmp = np.zeros(max(1, len(bc_off) - 1))
+        vp = lambda a: a.ctypes.data_as(C.c_void_p)
+        rc = self.O.orc_place(C.byref(self.ref), n_pairs, vp(seq), vp(off), len(bc_off) - 1, vp(bc_off), vp(run_rfa), vp(seeds), vp(reg_off), vp(regs),
+                              vp(aln8), vp(cigar), improper, delta, vp(cand_off), vp(cands), cap, vp(lmp))
+        assert rc == 0, rc
+        return cand_off, cands[:cand_off[-1]], lmp
