@@ -187,6 +187,7 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
     AR_TRY(cudaGetLastError());
     cudaEventRecord(ev[4], st);
     int stages = in->stages ? in->stages : (ARACHNE_STAGE_REGIONS | ARACHNE_STAGE_RESCUE | ARACHNE_STAGE_CIGAR);
+    if (stages & ARACHNE_STAGE_PLACE) stages |= ARACHNE_STAGE_CIGAR;  // placement scores the candidates' CIGAR statistics
     // ---- mate rescue ----
     AR_ALLOC(W.d_reg_loc, (n_reads + 1) * 8);
     ++nl;
@@ -288,6 +289,11 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
         }
     }
     cudaEventRecord(ev[7], st);
+    // ---- placement: tagBestAlignments .. optimizer .. MAPQ ----
+    if (stages & ARACHNE_STAGE_PLACE) {
+#include "place_host.inl"
+    }
+    cudaEventRecord(ev[8], st);
     AR_TRY(cudaStreamSynchronize(st));
 
     out->n_regs = (int64_t)total_regs;
@@ -306,7 +312,8 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
     cudaEventElapsedTime(&out->ms_extend, ev[3], ev[4]);
     cudaEventElapsedTime(&out->ms_rescue, ev[4], ev[5]);
     cudaEventElapsedTime(&out->ms_cigar, ev[6], ev[7]);
-    cudaEventElapsedTime(&out->ms_total, ev[0], ev[7]);
+    cudaEventElapsedTime(&out->ms_place, ev[7], ev[8]);
+    cudaEventElapsedTime(&out->ms_total, ev[0], ev[8]);
     *out_ = out;
     return ARACHNE_OK;
 #undef AR_TRY

@@ -11,6 +11,7 @@
 // The index is read-only and shared; all per-batch state lives in one device workspace that is reused.
 #include <cuda_runtime.h>
 #include <cub/device/device_scan.cuh>
+#include <cub/device/device_radix_sort.cuh>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -48,6 +49,7 @@ __device__ __forceinline__ void raise(Counters* c, int code, int read) {
 
 // ------------------------------------------------------------------------------------------------ k_seed2
 }  // namespace arachne
+#include "place.cuh"
 #include "seed_kernel.cuh"
 namespace arachne {
 
@@ -429,9 +431,9 @@ struct PinBuf {
 };
 
 struct BatchPriv {
-    PinBuf reg_off, regs, alns, cigar, mm;
+    PinBuf reg_off, regs, alns, cigar, mm, cand_off, cands, lmp;
     arachne_index_t* owner = nullptr;
-    void release() { reg_off.release(); regs.release(); alns.release(); cigar.release(); mm.release(); }
+    void release() { reg_off.release(); regs.release(); alns.release(); cigar.release(); mm.release(); cand_off.release(); cands.release(); lmp.release(); }
 };
 
 // Per-index workspace: every device arena of the batch pipeline, grown on demand and kept between batches.
@@ -439,15 +441,19 @@ struct Workspace {
     DevBuf d_seq, d_off, d_scratch, d_arena, d_misc, d_intv_off, d_intv_n, d_nsa, d_sa_off, d_rows, d_cnt, d_tmp;
     DevBuf d_seeds, d_kseeds, d_chains, d_nodes, d_order, d_kept, d_nchain, d_nkseed, d_srt, d_regs, d_nregs, d_win, d_reg_off, d_out;
     DevBuf d_nregs_bak, d_reg_loc, d_blist, d_resc, d_reg_read, d_z, d_cig_scr, d_mm_scr, d_alns, d_cig, d_mm, d_hscr, d_rscr;
+    DevBuf d_bc_off, d_run_rfa, d_rand_seed, d_centro, d_pl_cnt, d_pl_scan, d_cand_off, d_lmp, d_cands, d_hot, d_aux, d_slow, d_slot_of_bc, d_bc_of_slot,
+        d_first, d_keys_a, d_keys_b, d_vals_a, d_vals_b, d_seg_off, d_mol;
     cudaStream_t own_stream = nullptr;
-    cudaEvent_t ev[8] = {};
+    cudaEvent_t ev[10] = {};
     Counters* h_cnt = nullptr;              // pinned
     unsigned long long* h_scalars = nullptr;  // pinned, 8 slots
     std::vector<BatchPriv*> pool;           // recycled pinned result sets
     std::vector<DevBuf*> all() {
         return {&d_seq, &d_off, &d_scratch, &d_arena, &d_misc, &d_intv_off, &d_intv_n, &d_nsa, &d_sa_off, &d_rows, &d_cnt, &d_tmp,
                 &d_seeds, &d_kseeds, &d_chains, &d_nodes, &d_order, &d_kept, &d_nchain, &d_nkseed, &d_srt, &d_regs, &d_nregs,
-                &d_win, &d_reg_off, &d_out, &d_nregs_bak, &d_reg_loc, &d_blist, &d_resc, &d_reg_read, &d_z, &d_cig_scr, &d_mm_scr, &d_alns, &d_cig, &d_mm, &d_hscr, &d_rscr};
+                &d_win, &d_reg_off, &d_out, &d_nregs_bak, &d_reg_loc, &d_blist, &d_resc, &d_reg_read, &d_z, &d_cig_scr, &d_mm_scr, &d_alns, &d_cig, &d_mm, &d_hscr, &d_rscr,
+                &d_bc_off, &d_run_rfa, &d_rand_seed, &d_centro, &d_pl_cnt, &d_pl_scan, &d_cand_off, &d_lmp, &d_cands, &d_hot, &d_aux, &d_slow, &d_slot_of_bc,
+                &d_bc_of_slot, &d_first, &d_keys_a, &d_keys_b, &d_vals_a, &d_vals_b, &d_seg_off, &d_mol};
     }
     int init() {
         if (cudaStreamCreateWithFlags(&own_stream, cudaStreamNonBlocking) != cudaSuccess) return -1;
@@ -519,6 +525,48 @@ int arachne_opts_default(arachne_mem_opt_t* o) {  // mem_opt_init, bwa/bwamem.c:
     }
     for (int j = 0; j < 5; ++j) o->mat[20 + j] = -1;
     return ARACHNE_OK;
+}
+
+// md5(name)[0:8] little-endian as int64: the seed tagBestAlignments hands to rand.NewSource (aligner.go:1413-1416).  RFC 1321.
+int64_t arachne_name_seed(const char* name, int32_t len) {
+    static const uint32_t K[64] = {
+        0xd76aa478, 0xe8c7b756, 0x242070db, 0xc1bdceee, 0xf57c0faf, 0x4787c62a, 0xa8304613, 0xfd469501, 0x698098d8, 0x8b44f7af, 0xffff5bb1, 0x895cd7be,
+        0x6b901122, 0xfd987193, 0xa679438e, 0x49b40821, 0xf61e2562, 0xc040b340, 0x265e5a51, 0xe9b6c7aa, 0xd62f105d, 0x02441453, 0xd8a1e681, 0xe7d3fbc8,
+        0x21e1cde6, 0xc33707d6, 0xf4d50d87, 0x455a14ed, 0xa9e3e905, 0xfcefa3f8, 0x676f02d9, 0x8d2a4c8a, 0xfffa3942, 0x8771f681, 0x6d9d6122, 0xfde5380c,
+        0xa4beea44, 0x4bdecfa9, 0xf6bb4b60, 0xbebfbc70, 0x289b7ec6, 0xeaa127fa, 0xd4ef3085, 0x04881d05, 0xd9d4d039, 0xe6db99e5, 0x1fa27cf8, 0xc4ac5665,
+        0xf4292244, 0x432aff97, 0xab9423a7, 0xfc93a039, 0x655b59c3, 0x8f0ccc92, 0xffeff47d, 0x85845dd1, 0x6fa87e4f, 0xfe2ce6e0, 0xa3014314, 0x4e0811a1,
+        0xf7537e82, 0xbd3af235, 0x2ad7d2bb, 0xeb86d391};
+    static const uint8_t S[16] = {7, 12, 17, 22, 5, 9, 14, 20, 4, 11, 16, 23, 6, 10, 15, 21};
+    if (!name || len < 0) return 1;
+    uint32_t h[4] = {0x67452301u, 0xefcdab89u, 0x98badcfeu, 0x10325476u};
+    const uint64_t n = (uint64_t)len, padded = ((n + 8) / 64 + 1) * 64;
+    for (uint64_t base = 0; base < padded; base += 64) {
+        uint32_t w[16];
+        for (int i = 0; i < 16; ++i) {
+            uint32_t v = 0;
+            for (int k = 0; k < 4; ++k) {
+                const uint64_t pos = base + 4 * i + k;
+                uint8_t byte = pos < n ? (uint8_t)name[pos] : (pos == n ? 0x80 : 0);
+                if (pos >= padded - 8) byte = (uint8_t)((n * 8) >> (8 * (pos - (padded - 8))));
+                v |= (uint32_t)byte << (8 * k);
+            }
+            w[i] = v;
+        }
+        uint32_t a = h[0], b = h[1], c = h[2], d = h[3];
+        for (int i = 0; i < 64; ++i) {
+            uint32_t f; int g;
+            switch (i >> 4) {
+                case 0: f = (b & c) | (~b & d); g = i; break;
+                case 1: f = (d & b) | (~d & c); g = (5 * i + 1) & 15; break;
+                case 2: f = b ^ c ^ d; g = (3 * i + 5) & 15; break;
+                default: f = c ^ (b | ~d); g = (7 * i) & 15;
+            }
+            const uint32_t t = a + f + K[i] + w[g]; const int r = S[(i >> 4) * 4 + (i & 3)];
+            a = d; d = c; c = b; b += (t << r) | (t >> (32 - r));
+        }
+        h[0] += a; h[1] += b; h[2] += c; h[3] += d;
+    }
+    return (int64_t)((uint64_t)h[1] << 32 | h[0]);
 }
 
 // ---------------------------------------------------------------------------------------------- batch

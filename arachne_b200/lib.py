@@ -14,7 +14,11 @@ ALNREG = np.dtype([("rb", "<i8"), ("re", "<i8"), ("qb", "<i4"), ("qe", "<i4"), (
 ALN = np.dtype([("pos", "<i8"), ("rid", "<i4"), ("is_rev", "<i4"), ("nm", "<i4"), ("n_cigar", "<i4"), ("cigar_off", "<i8"),
                 ("score", "<i4"), ("sub", "<i4"), ("matches", "<i4"), ("mismatches", "<i4"), ("indels", "<i4"),
                 ("soft_clipped", "<i4"), ("soft_clipped_length", "<i4"), ("n_mm", "<i4"), ("mm_off", "<i8")])
-assert ALNREG.itemsize == 88 and ALN.itemsize == 72
+CAND = np.dtype([("reg", "<i4"), ("read", "<i4"), ("id", "<i4"), ("active", "<i4"), ("is_proper", "<i4"), ("bwa_pick", "<i4"), ("mapq", "<i4"),
+                 ("molecule_id", "<i4"), ("active_molecule", "<i4"), ("second_best", "<i4"), ("mate", "<i4"), ("duplicate", "<i4"),
+                 ("pos", "<i8"), ("aend", "<i8"), ("lap", "<f8"), ("as_score", "<f8"), ("xs_score", "<f8"), ("molecule_difference", "<f8"),
+                 ("sum_move", "<f8"), ("molecule_confidence", "<f8"), ("raw_mapq", "<f8")])  # arachne_cand_t
+assert ALNREG.itemsize == 88 and ALN.itemsize == 72 and CAND.itemsize == 120
 
 STAGE_REGIONS, STAGE_RESCUE, STAGE_CIGAR, STAGE_PLACE = 1, 2, 4, 8
 IN_DEVICE, OUT_DEVICE = 1, 2
@@ -44,7 +48,9 @@ class MemOpt(C.Structure):  # arachne_mem_opt_t == mem_opt_t (bwa/bwamem.h:27-66
 class BatchIn(C.Structure):
     _fields_ = [("n_pairs", C.c_int64), ("seq", C.POINTER(C.c_uint8)), ("seq_off", C.POINTER(C.c_int64)), ("n_barcodes", C.c_int64),
                 ("barcode_off", C.POINTER(C.c_int64)), ("score_delta", C.c_int32), ("stages", C.c_int32),
-                ("flags", C.c_int32), ("max_read_len", C.c_int32), ("n_bases", C.c_int64)]
+                ("flags", C.c_int32), ("max_read_len", C.c_int32), ("n_bases", C.c_int64),
+                ("run_rfa", C.POINTER(C.c_uint8)), ("rand_seed", C.POINTER(C.c_int64)), ("improper_penalty", C.c_double), ("delta", C.c_int32),
+                ("place_flags", C.c_int32), ("centro_start", C.POINTER(C.c_int64)), ("centro_end", C.POINTER(C.c_int64))]
 
 
 class BatchOut(C.Structure):
@@ -54,7 +60,9 @@ class BatchOut(C.Structure):
                 ("n_occ_lookups", C.c_uint64), ("n_occ_blocks", C.c_uint64), ("n_sa_lookups", C.c_uint64), ("n_lf_steps", C.c_uint64), ("n_ext_calls", C.c_uint64),
                 ("n_ext_cells", C.c_uint64), ("n_glb_cells", C.c_uint64), ("n_kernel_launches", C.c_uint64),
                 ("ms_seed", C.c_float), ("ms_sa", C.c_float), ("ms_chain", C.c_float), ("ms_extend", C.c_float), ("ms_rescue", C.c_float),
-                ("ms_cigar", C.c_float), ("ms_place", C.c_float), ("ms_total", C.c_float), ("priv", C.c_void_p)]
+                ("ms_cigar", C.c_float), ("ms_place", C.c_float), ("ms_total", C.c_float),
+                ("n_cands", C.c_int64), ("cand_off", C.POINTER(C.c_int64)), ("cands", C.c_void_p), ("log_molecule_penalty", C.POINTER(C.c_double)),
+                ("priv", C.c_void_p)]
 
 
 def _p(a, t):
@@ -91,6 +99,7 @@ class ArachneCuda:
         L.arachne_ksw_global_batch.argtypes = [C.c_int, C.POINTER(MemOpt), C.c_int64, C.POINTER(C.c_uint8), C.POINTER(C.c_int64),
                                                C.POINTER(C.c_uint8), C.POINTER(C.c_int64), C.POINTER(C.c_int32), C.POINTER(C.c_int32),
                                                C.POINTER(C.c_int64), C.POINTER(C.c_uint32), C.c_int64]
+        L.arachne_name_seed.restype = C.c_int64; L.arachne_name_seed.argtypes = [C.c_char_p, C.c_int32]
         self.opt = MemOpt()
         self._ck(L.arachne_opts_default(C.byref(self.opt)))
         self.idx = C.c_void_p(None)
@@ -205,15 +214,26 @@ class ArachneCuda:
         finally:
             self.lib.arachne_batch_free(po)
 
+    def name_seed(self, name: str) -> int:
+        b = name.encode()
+        return self.lib.arachne_name_seed(b, len(b))
+
     # ---- batch hot path ----
-    def align_batch(self, seq, off, bc_off=None, score_delta=25, stages=0):
+    def align_batch(self, seq, off, bc_off=None, score_delta=25, stages=0, run_rfa=None, rand_seed=None, improper_penalty=-4.0, centromeres=None):
         seq = np.ascontiguousarray(seq, dtype=np.uint8); off = np.ascontiguousarray(off, dtype=np.int64)
         n_pairs = (len(off) - 1) // 2
         bi = BatchIn(); bi.n_pairs = n_pairs; bi.seq = _p(seq, C.c_uint8); bi.seq_off = _p(off, C.c_int64)
         if bc_off is not None:
             bc_off = np.ascontiguousarray(bc_off, dtype=np.int64)
             bi.n_barcodes = len(bc_off) - 1; bi.barcode_off = _p(bc_off, C.c_int64)
-        bi.score_delta = score_delta; bi.stages = stages
+        bi.score_delta = score_delta; bi.stages = stages; bi.improper_penalty = improper_penalty; bi.delta = 17
+        if run_rfa is not None:
+            run_rfa = np.ascontiguousarray(run_rfa, dtype=np.uint8); bi.run_rfa = _p(run_rfa, C.c_uint8)
+        if rand_seed is not None:
+            rand_seed = np.ascontiguousarray(rand_seed, dtype=np.int64); bi.rand_seed = _p(rand_seed, C.c_int64)
+        if centromeres is not None:
+            cs = np.ascontiguousarray(centromeres[0], dtype=np.int64); ce = np.ascontiguousarray(centromeres[1], dtype=np.int64)
+            bi.centro_start = _p(cs, C.c_int64); bi.centro_end = _p(ce, C.c_int64)
         po = C.POINTER(BatchOut)()
         self._ck(self.lib.arachne_align_batch(self.idx, C.byref(self.opt), C.byref(bi), C.byref(po)))
         try:
@@ -225,6 +245,11 @@ class ArachneCuda:
                 res["alns"] = np.frombuffer(C.string_at(o.alns, o.n_regs * 72), dtype=ALN).copy()
                 res["cigar"] = np.ctypeslib.as_array(o.cigar, shape=(max(1, o.n_cigar),))[:o.n_cigar].copy()
                 res["mm"] = np.ctypeslib.as_array(o.mm, shape=(max(1, o.n_mm),))[:o.n_mm].copy()
+            if o.cand_off:
+                res["cand_off"] = np.ctypeslib.as_array(o.cand_off, shape=(o.n_reads + 1,)).copy()
+                res["cands"] = np.frombuffer(C.string_at(o.cands, o.n_cands * 120), dtype=CAND).copy() if o.n_cands else np.zeros(0, CAND)
+                nb = bi.n_barcodes if bi.n_barcodes > 0 else 1
+                res["lmp"] = np.ctypeslib.as_array(o.log_molecule_penalty, shape=(nb,)).copy()
         finally:
             self.lib.arachne_batch_free(po)
         return res

@@ -102,6 +102,31 @@ typedef struct {
     int64_t mm_off;       /* into the batch mismatch pool: n_mm reference loci then n_mm read offsets */
 } arachne_aln_t;
 
+/* One entry of Go's `alignments [][]*Alignment` after DoRFAForOneBarcode (aligner.go:65-114,440-501): the candidates of a
+ * read that survived `score >= best - delta`, or its single unmapped placeholder; CSR by read (cand_off). */
+typedef struct {
+    int32_t reg;          /* index into the batch region array; -1 = unmapped placeholder (aligner.go:1664-1676) */
+    int32_t read;         /* batch-global read index (2*pair + mate) */
+    int32_t id;           /* hit_id within the barcode (aligner.go:1645-1712) */
+    int32_t active;       /* the alignment selected for this read */
+    int32_t is_proper;
+    int32_t bwa_pick;
+    int32_t mapq;         /* int(min(method 1, method 2, 60)) (aligner.go:901-919) */
+    int32_t molecule_id;  /* candidate molecule within the barcode after scrapMolecules; -1 = none */
+    int32_t active_molecule;
+    int32_t second_best;  /* mapq_data.second_best as a batch-global candidate index; -1 = nil (set on active alignments) */
+    int32_t mate;         /* mate_alignment as a batch-global candidate index; -1 = nil */
+    int32_t duplicate;    /* markDuplicates (aligner.go:611-641) */
+    int64_t pos, aend;    /* Alignment.pos / aend (aligner.go:1582-1587) */
+    double log_alignment_probability;
+    double as_score;      /* mapq_data.score -> AS tag */
+    double xs_score;      /* mapq_data.second_best_score -> XS tag */
+    double molecule_difference;          /* DM tag */
+    double sum_move_probability_change;
+    double molecule_confidence;
+    double raw_mapq;      /* the value before int() truncation */
+} arachne_cand_t;
+
 typedef struct arachne_index arachne_index_t;
 
 typedef struct {
@@ -115,7 +140,18 @@ typedef struct {
     int32_t flags;             /* ARACHNE_IN_DEVICE | ARACHNE_OUT_DEVICE */
     int32_t max_read_len;      /* ARACHNE_IN_DEVICE only: upper bound of the read lengths (checked on the device) */
     int64_t n_bases;           /* ARACHNE_IN_DEVICE only: seq_off[2*n_pairs] */
+    /* ---- ARACHNE_STAGE_PLACE inputs (device pointers under ARACHNE_IN_DEVICE, like seq / seq_off / barcode_off) ---- */
+    const uint8_t *run_rfa;    /* n_barcodes flags = worthRunningRFA (aligner.go:1018-1030); NULL => no barcode runs the optimizer */
+    const int64_t *rand_seed;  /* n_pairs: arachne_name_seed(read name) = first 8 bytes of md5(ReadInfo) (aligner.go:1413-1416); NULL => seed 1 */
+    double improper_penalty;   /* -i / --improper-pair-penalty, default -4.0 (main.go:29); 0 in a zeroed struct means "use -4.0" only with ARACHNE_PLACE_DEFAULTS */
+    int32_t delta;             /* GetAlignments keeps score >= best - delta; DoRFAForOneBarcode passes 17 (aligner.go:455); 0 => 17 */
+    int32_t place_flags;       /* ARACHNE_PLACE_* */
+    const int64_t *centro_start, *centro_end; /* per contig id, HOST pointers, or NULL (-c / --centromeres, aligner.go:906-916) */
 } arachne_batch_in_t;
+
+enum {
+    ARACHNE_PLACE_DEFAULTS = 1 /* ignore improper_penalty and use the reference's default -4.0 */
+};
 
 enum {
     ARACHNE_IN_DEVICE = 1,     /* seq / seq_off are device pointers on the index's device (inputs already resident in HBM) */
@@ -144,6 +180,11 @@ typedef struct {
     uint64_t n_glb_cells;
     uint64_t n_kernel_launches; /* kernels this batch launched (bench.py reports it as gpu_launches) */
     float ms_seed, ms_sa, ms_chain, ms_extend, ms_rescue, ms_cigar, ms_place, ms_total; /* CUDA-event stage times */
+    /* ---- ARACHNE_STAGE_PLACE outputs ---- */
+    int64_t n_cands;
+    int64_t *cand_off;         /* n_reads+1 */
+    arachne_cand_t *cands;     /* n_cands */
+    double *log_molecule_penalty; /* n_barcodes (calculateLogMoleculePenalty, aligner.go:722-755) */
     void *priv;
 } arachne_batch_out_t;
 
@@ -163,6 +204,9 @@ size_t arachne_index_device_bytes(const arachne_index_t *idx);
 /* Run this handle's batches on the caller's CUDA stream (a cudaStream_t; use != 0) or on the handle's own stream (use == 0,
  * the default), so that a caller can bracket batches with its own CUDA events. */
 int arachne_index_set_stream(arachne_index_t *idx, void *cuda_stream, int use);
+
+/* int64(binary.LittleEndian.Uint64(md5(name)[0:8])): the per-read PRNG seed of tagBestAlignments (aligner.go:1413-1416). Host only. */
+int64_t arachne_name_seed(const char *name, int32_t len);
 
 /* ---- options: mem_opt_init defaults (gobwa.go:151) ---- */
 int arachne_opts_default(arachne_mem_opt_t *opt);

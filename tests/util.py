@@ -269,3 +269,17 @@ class PlaceOracle:
                               vp(aln8), vp(cigar), improper, delta, vp(cand_off), vp(cands), cap, vp(lmp))
         assert rc == 0, rc
         return cand_off, cands[:cand_off[-1]], lmp
+
+
+def exact_repeat_reference(total_len=300_000, n_contigs=4, seed=9, families=6, copies=24, rep_len=700):
+    """Random contigs with families of EXACT repeat copies: reads inside a copy get many equal-score candidates, so
+    tagBestAlignments' PRNG tie-break decides, pairs need hundreds of PRNG outputs, and the optimizer has moves to make."""
+    ctg = S.make_reference(total_len=total_len, n_contigs=n_contigs, seed=seed)
+    g = np.random.default_rng(seed + 1000)
+    for _ in range(families):
+        ci = int(g.integers(0, len(ctg))); s = ctg[ci][1]
+        a = int(g.integers(0, len(s) - rep_len)); seg = s[a:a + rep_len].copy()
+        for _ in range(copies):
+            cj = int(g.integers(0, len(ctg))); t = ctg[cj][1]
+            b = int(g.integers(0, len(t) - rep_len)); t[b:b + rep_len] = seg
+    return ctg
