@@ -182,34 +182,51 @@ class ArachneCuda:
         """Run batches on the caller's stream (e.g. torch.cuda.current_stream().cuda_stream); None = the handle's own."""
         self._ck(self.lib.arachne_index_set_stream(self.idx, C.c_void_p(cuda_stream or 0), 0 if cuda_stream is None else 1))
 
-    def align_batch_device(self, d_seq_ptr: int, d_off_ptr: int, n_pairs: int, n_bases: int, max_read_len: int, score_delta=25, stages=0):
+    def align_batch_device(self, d_seq_ptr: int, d_off_ptr: int, n_pairs: int, n_bases: int, max_read_len: int, score_delta=25, stages=0,
+                           d_bc_off_ptr: int = 0, n_barcodes: int = 0, d_run_rfa_ptr: int = 0, d_rand_seed_ptr: int = 0, improper_penalty=-4.0):
         """Inputs already resident in HBM, results left in the device workspace: returns counts, counters and stage times."""
         bi = BatchIn(); bi.n_pairs = n_pairs
         bi.seq = C.cast(C.c_void_p(d_seq_ptr), C.POINTER(C.c_uint8)); bi.seq_off = C.cast(C.c_void_p(d_off_ptr), C.POINTER(C.c_int64))
         bi.score_delta = score_delta; bi.stages = stages; bi.flags = IN_DEVICE | OUT_DEVICE
-        bi.max_read_len = max_read_len; bi.n_bases = n_bases
+        bi.max_read_len = max_read_len; bi.n_bases = n_bases; bi.improper_penalty = improper_penalty; bi.delta = 17
+        if d_bc_off_ptr:
+            bi.n_barcodes = n_barcodes; bi.barcode_off = C.cast(C.c_void_p(d_bc_off_ptr), C.POINTER(C.c_int64))
+        if d_run_rfa_ptr:
+            bi.run_rfa = C.cast(C.c_void_p(d_run_rfa_ptr), C.POINTER(C.c_uint8))
+        if d_rand_seed_ptr:
+            bi.rand_seed = C.cast(C.c_void_p(d_rand_seed_ptr), C.POINTER(C.c_int64))
         po = C.POINTER(BatchOut)()
         self._ck(self.lib.arachne_align_batch(self.idx, C.byref(self.opt), C.byref(bi), C.byref(po)))
         try:
             o = po.contents
-            return dict(n_regs=o.n_regs, n_cigar=o.n_cigar, n_mm=o.n_mm, counters={k: getattr(o, k) for k in COUNTERS},
+            return dict(n_regs=o.n_regs, n_cigar=o.n_cigar, n_mm=o.n_mm, n_cands=o.n_cands, counters={k: getattr(o, k) for k in COUNTERS},
                         ms={k: getattr(o, "ms_" + k) for k in STAGE_MS})
         finally:
             self.lib.arachne_batch_free(po)
 
-    def align_batch_host(self, seq, off, score_delta=25, stages=0):
+    def align_batch_host(self, seq, off, score_delta=25, stages=0, bc_off=None, run_rfa=None, rand_seed=None, improper_penalty=-4.0):
         """The C-ABI call exactly as a host makes it (host buffers in, pinned host results out), without converting the
         results to numpy: returns counts, the bytes that crossed PCIe in each direction, counters and stage times."""
         n_pairs = (len(off) - 1) // 2
         bi = BatchIn(); bi.n_pairs = n_pairs; bi.seq = _p(seq, C.c_uint8); bi.seq_off = _p(off, C.c_int64)
-        bi.score_delta = score_delta; bi.stages = stages
+        bi.score_delta = score_delta; bi.stages = stages; bi.improper_penalty = improper_penalty; bi.delta = 17
+        h2d = seq.nbytes + off.nbytes
+        if bc_off is not None:
+            bi.n_barcodes = len(bc_off) - 1; bi.barcode_off = _p(bc_off, C.c_int64); h2d += bc_off.nbytes
+        if run_rfa is not None:
+            bi.run_rfa = _p(run_rfa, C.c_uint8); h2d += run_rfa.nbytes
+        if rand_seed is not None:
+            bi.rand_seed = _p(rand_seed, C.c_int64); h2d += rand_seed.nbytes
         po = C.POINTER(BatchOut)()
         self._ck(self.lib.arachne_align_batch(self.idx, C.byref(self.opt), C.byref(bi), C.byref(po)))
         try:
             o = po.contents
             d2h = (o.n_reads + 1) * 8 + o.n_regs * 88 + (o.n_regs * 72 + o.n_cigar * 4 + o.n_mm * 4 if o.alns else 0)
-            return dict(n_regs=o.n_regs, n_cigar=o.n_cigar, n_mm=o.n_mm, h2d_bytes=seq.nbytes + off.nbytes, d2h_bytes=d2h,
-                        first_score=(int(np.frombuffer(C.string_at(o.regs, 88), dtype=ALNREG)["score"][0]) if o.n_regs else -1),
+            if o.cands:
+                d2h += (o.n_reads + 1) * 8 + o.n_cands * 120 + max(1, bi.n_barcodes) * 8
+            mapq_sum = int(np.frombuffer(C.string_at(o.cands, min(o.n_cands, 64) * 120), dtype=CAND)["mapq"].sum()) if o.cands and o.n_cands else -1
+            return dict(n_regs=o.n_regs, n_cigar=o.n_cigar, n_mm=o.n_mm, n_cands=o.n_cands, h2d_bytes=h2d, d2h_bytes=d2h,
+                        first_score=(int(np.frombuffer(C.string_at(o.regs, 88), dtype=ALNREG)["score"][0]) if o.n_regs else -1), mapq_probe=mapq_sum,
                         counters={k: getattr(o, k) for k in COUNTERS}, ms={k: getattr(o, "ms_" + k) for k in STAGE_MS})
         finally:
             self.lib.arachne_batch_free(po)

@@ -28,7 +28,7 @@ sys.path.insert(0, ROOT)
 
 from arachne_b200 import simulate as S  # noqa: E402
 
-STAGES = 7  # regions + rescue + cigar (placement is reported separately once it is on the device)
+STAGES = 15  # regions + rescue + cigar + placement (tagBestAlignments .. optimizer .. MAPQ)
 
 
 def parse_args():
@@ -43,6 +43,7 @@ def parse_args():
     ap.add_argument("--cpu-sample", type=int, default=150000, help="pairs in the bounded CPU-baseline sample")
     ap.add_argument("--workdir", default=os.environ.get("ARACHNE_BENCH_DIR", "/tmp/arachne_bench"))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--plain-barcodes", action="store_true", help="barcodes without the '-1' suffix: worthRunningRFA is false, the optimizer is skipped (what the reference does with haplotagging barcodes as shipped)")
     return ap.parse_args()
 
 
@@ -72,6 +73,15 @@ def build_index(fa: str):
 
 def make_batches(ctg, args, rank):
     return [S.simulate_pairs_fast(ctg, args.pairs, seed=12 + 1000 * rank + b) for b in range(args.batches)]
+
+
+def place_inputs(b, args):
+    """Per-batch inputs of the placement stage: PRNG seeds = md5(read name)[0:8] (aligner.go:1413-1416) and the
+    worthRunningRFA flag per barcode (aligner.go:1018-1030: unique barcode with a '-', >= 5 pairs)."""
+    import hashlib
+    seeds = np.fromiter((int.from_bytes(hashlib.md5(n.encode()).digest()[:8], "little", signed=True) for n in b.names), dtype=np.int64, count=b.n_pairs)
+    rfa = ((np.diff(b.bc_off) >= 5) & (not args.plain_barcodes)).astype(np.uint8)
+    return seeds, rfa
 
 
 def log(msg):
@@ -123,17 +133,40 @@ def peaks():
 _REF_CACHE = {}
 
 
-def cpu_reference(fa, rs, n_sample, threads):
-    """The reference's own C code for the path (oracle/_ref: unmodified bwa sources driven as gobwa.go drives them)."""
+def cpu_reference(fa, rs, n_sample, threads, args):
+    """The reference's CPU implementation of the path on `threads` host threads: the C part is the reference's own code
+    (oracle/_ref: unmodified bwa sources driven as gobwa.go drives them, pthreads over pairs); the Go part (GetAlignments
+    walk, tagBestAlignments .. optimizer .. MAPQ) cannot be built here (no Go toolchain) and is timed as the oracle's C++
+    restatement, one worker thread per chunk of barcodes like aligner.WorkerThread (aligner.go:405-419)."""
+    from concurrent.futures import ThreadPoolExecutor
     from oracle.refbwa import RefBwa
+    from tests import util
     if fa not in _REF_CACHE:
-        _REF_CACHE[fa] = RefBwa().load(fa)
-    R = _REF_CACHE[fa]
+        _REF_CACHE[fa] = (RefBwa().load(fa), util.PlaceOracle(fa))
+    R, P = _REF_CACHE[fa]
     n_bc = int(np.searchsorted(rs.bc_off, min(n_sample, rs.n_pairs), side="left"))
     sub = rs.subset(0, max(1, n_bc))
+    seeds, rfa = place_inputs(sub, args)
     t = time.perf_counter()
-    R.batch(sub.seq, sub.off, rescue=True, cigar=True, threads=threads)
+    ref = R.batch(sub.seq, sub.off, rescue=True, cigar=True, threads=threads)
+    t1 = time.perf_counter()
+    nb = len(sub.bc_off) - 1
+    cuts = [nb * k // threads for k in range(threads + 1)]
+
+    def work(k):
+        lo, hi = cuts[k], cuts[k + 1]
+        if hi <= lo:
+            return 0
+        p0, p1 = int(sub.bc_off[lo]), int(sub.bc_off[hi])
+        o = sub.off[2 * p0:2 * p1 + 1]; ro = ref["reg_off"][2 * p0:2 * p1 + 1]
+        aln = ref["aln"][ro[0]:ro[-1]].copy(); c0 = int(aln[0, 5]) if len(aln) else 0
+        aln[:, 5] -= c0
+        P.place(sub.seq[o[0]:o[-1]], o - o[0], sub.bc_off[lo:hi + 1] - p0, rfa[lo:hi], seeds[p0:p1], ro - ro[0], ref["regs"][ro[0]:ro[-1]], aln, ref["cigar"][c0:])
+        return p1 - p0
+    with ThreadPoolExecutor(threads) as ex:
+        list(ex.map(work, range(threads)))
     dt = time.perf_counter() - t
+    log(f"cpu reference: {sub.n_pairs} pairs, C part {t1 - t:.2f}s + placement port {dt - (t1 - t):.2f}s on {threads} threads")
     return sub.n_pairs, dt
 
 
@@ -147,7 +180,7 @@ def run_reference(args, rank, world):
     batches = [S.simulate_pairs_fast(ctg, n, seed=12 + b) for b in range(min(args.batches, 2))]
     times = []
     for it in range(args.warmup + args.steps):
-        npairs, dt = cpu_reference(fa, batches[it % len(batches)], n, threads)
+        npairs, dt = cpu_reference(fa, batches[it % len(batches)], n, threads, args)
         if it >= args.warmup:
             times.append(dt)
     ms = 1e3 * sum(times) / len(times)
@@ -166,7 +199,7 @@ def base_line(args, world, value, ms):
             "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32", "data": "synthetic",
             "config": {"workload": f"configs[1] scaled to what one bench run can index: synthetic {args.ref_mb:g} Mb iid reference (24 human-like contigs, seed 2), "
                                    f"simulated haplotagging 2x150 bp pairs (1% subs, 14% reads with a 1-3 bp indel, 0.2% N, 30 pairs/barcode), "
-                                   f"{args.pairs} pairs per step per GPU; stages: seeding+SA+chaining+extension+mate rescue+CIGAR/NM",
+                                   f"{args.pairs} pairs per step per GPU; stages: seeding+SA+chaining+extension+mate rescue+CIGAR/NM+placement (tagBestAlignments, molecules, optimizer, MAPQ; " + ("plain barcodes: no RFA" if args.plain_barcodes else "'-1' barcodes: RFA on") + ")",
                        "ref_mb": args.ref_mb, "pairs_per_step_per_gpu": args.pairs, "read_len": 150, "parallelism": f"barcode-sharded x{world}, index replicated, no collective",
                        "l2_policy": "inputs+index+per-batch arenas exceed L2 (>126 MB touched per step); distinct batches are cycled"}}
 
@@ -193,17 +226,20 @@ def main():
     stream = torch.cuda.Stream()
     A.set_stream(stream.cuda_stream)
     # resident inputs
-    dev = [(torch.from_numpy(b.seq).cuda(), torch.from_numpy(b.off).cuda(), b) for b in batches]
-    pinned = [(torch.from_numpy(b.seq).pin_memory(), torch.from_numpy(b.off).pin_memory()) for b in batches]
+    pl = [place_inputs(b, args) for b in batches]
+    dev = [(torch.from_numpy(b.seq).cuda(), torch.from_numpy(b.off).cuda(), b, torch.from_numpy(b.bc_off).cuda(), torch.from_numpy(rfa).cuda(),
+            torch.from_numpy(sd).cuda()) for b, (sd, rfa) in zip(batches, pl)]
+    pinned = [tuple(torch.from_numpy(x).pin_memory() for x in (b.seq, b.off, b.bc_off, rfa, sd)) for b, (sd, rfa) in zip(batches, pl)]
     torch.cuda.synchronize()
 
     def step_resident(i):
-        s, o, b = dev[i % len(dev)]
-        return A.align_batch_device(s.data_ptr(), o.data_ptr(), b.n_pairs, int(b.off[-1]), 150, stages=STAGES)
+        s, o, b, bc, rfa, sd = dev[i % len(dev)]
+        return A.align_batch_device(s.data_ptr(), o.data_ptr(), b.n_pairs, int(b.off[-1]), 150, stages=STAGES, d_bc_off_ptr=bc.data_ptr(),
+                                    n_barcodes=len(b.bc_off) - 1, d_run_rfa_ptr=rfa.data_ptr(), d_rand_seed_ptr=sd.data_ptr())
 
     def step_host(i):
-        s, o = pinned[i % len(pinned)]
-        return A.align_batch_host(s.numpy(), o.numpy(), stages=STAGES)
+        s, o, bc, rfa, sd = pinned[i % len(pinned)]
+        return A.align_batch_host(s.numpy(), o.numpy(), stages=STAGES, bc_off=bc.numpy(), run_rfa=rfa.numpy(), rand_seed=sd.numpy())
 
     # ---- device-resident timing (value) ----
     with torch.cuda.stream(stream):
@@ -249,14 +285,14 @@ def main():
         line["roofline"] = {"kernel": "k_seed (FM-index SMEM seeding: bwt_2occ4 block reads)", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                             "frac": achieved / peak, "traffic": None, "peak_source": how,
                             "algorithmic_bytes_per_launch": blocks * 64, "kernel_ms": seed_ms,
-                            "stage_ms_per_step": {k: acc[k] / args.steps for k in ("seed", "sa", "chain", "extend", "rescue", "cigar", "total")},
+                            "stage_ms_per_step": {k: acc[k] / args.steps for k in ("seed", "sa", "chain", "extend", "rescue", "cigar", "place", "total")},
                             "ext_gcups": acc["n_ext_cells"] / (acc["extend"] / 1e3) / 1e9 if acc["extend"] else None}
         line["e2e"] = {"value": pairs / (ms_e2e / 1e3), "unit": "pairs/s", "h2d_bytes_per_step": h2d // args.steps, "d2h_bytes_per_step": d2h // args.steps}
         line["gpu_launches"] = int(acc["n_kernel_launches"])
         line["clocks"] = clocks
         if world == 1 and not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
-            n, dt = cpu_reference(fa, batches[0], args.cpu_sample, threads)
+            n, dt = cpu_reference(fa, batches[0], args.cpu_sample, threads, args)
             line["cpu_baseline"] = {"value": n / dt, "unit": "pairs/s", "cores": threads, "kind": "reference",
                                     "sample": f"first {n} pairs of batch 0 (whole barcodes), oracle/_ref = the reference's BWA C sources driven as gobwa.go drives them, {threads} pthreads"}
         print(json.dumps(line), flush=True)
