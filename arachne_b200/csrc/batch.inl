@@ -259,16 +259,39 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
         AR_ALLOC(W.d_mm_scr, (size_t)nw * mm_scr_cap * 4);
         AR_ALLOC(W.d_alns, (total_regs + 1) * sizeof(AlnRec));
         unsigned long long cig_cap = total_regs * 4 + 4096, mm_cap = total_regs * 12 + 4096;
+        // thread-per-region tiers (cigar_kernel.cuh); ARACHNE_CIGAR_TIERS=0 sends every region to the warp tier
+        const bool cigar_tiers = !(getenv("ARACHNE_CIGAR_TIERS") && atoi(getenv("ARACHNE_CIGAR_TIERS")) == 0);
+        const int band_blocks = sms * 4;
+        const long zband_stride = (long)maxlen * (2 * BAND_WMAX + 1);
+        if (cigar_tiers) {
+            AR_ALLOC(W.d_list2, (total_regs + 1) * 4);
+            AR_ALLOC(W.d_list3, (total_regs + 1) * 4);
+            AR_ALLOC(W.d_zband, (size_t)band_blocks * CIG_BLOCK * zband_stride);
+        }
         for (int attempt = 0;; ++attempt) {
             AR_ALLOC(W.d_cig, cig_cap * 4);
             AR_ALLOC(W.d_mm, mm_cap * 4);
             AR_TRY(cudaMemsetAsync(W.d_misc.p, 0, 64, st));
+            // misc words: u32[0] queue head of the warp tier, u64[1..2] pool use, u32[8] / u32[9] lengths of the tier-2 / tier-3 lists
+            CigArgs CA;
+            CA.seq = d_seq; CA.off = d_off; CA.n_regs = (long)total_regs; CA.regs = W.d_out.as<AlnReg>(); CA.reg_read = W.d_reg_read.as<int>();
+            CA.alns = W.d_alns.as<AlnRec>(); CA.cig_pool = W.d_cig.as<uint32_t>(); CA.cig_cap = cig_cap; CA.mm_pool = W.d_mm.as<int32_t>(); CA.mm_cap = mm_cap;
+            CA.used = W.d_misc.as<unsigned long long>() + 1; CA.list2 = W.d_list2.as<unsigned>(); CA.n2 = W.d_misc.as<unsigned>() + 8;
+            CA.list3 = W.d_list3.as<unsigned>(); CA.n3 = W.d_misc.as<unsigned>() + 9; CA.z = W.d_zband.as<uint8_t>(); CA.z_stride = zband_stride;
+            CA.cnt = W.d_cnt.as<Counters>();
+            const unsigned* l3 = nullptr; const unsigned* n3 = nullptr;
+            if (cigar_tiers) {
+                nl += 2;
+                k_cigar_fast<<<band_blocks * 2, CIG_BLOCK, 0, st>>>(opt, idx->ref, CA);
+                k_cigar_band<<<band_blocks, CIG_BLOCK, 0, st>>>(opt, idx->ref, CA);
+                l3 = CA.list3; n3 = CA.n3;
+            }
             ++nl;
             k_cigar<<<cg_blocks, EXT_WARPS * 32, 0, st>>>(opt, idx->ref, d_seq, d_off, (long)total_regs, W.d_out.as<AlnReg>(),
                                                           W.d_reg_read.as<int>(), W.d_alns.as<AlnRec>(), W.d_cig.as<uint32_t>(), cig_cap, W.d_mm.as<int32_t>(), mm_cap,
                                                           W.d_misc.as<unsigned long long>() + 1, W.d_win.as<uint8_t>(), win_cap, W.d_z.as<uint8_t>(), z_cap,
                                                           W.d_cig_scr.as<uint32_t>(), cig_scr_cap, W.d_mm_scr.as<int32_t>(), mm_scr_cap,
-                                                          W.d_misc.as<unsigned int>(), W.d_cnt.as<Counters>());
+                                                          W.d_misc.as<unsigned int>(), W.d_cnt.as<Counters>(), l3, n3);
             AR_TRY(cudaGetLastError());
             AR_TRY(cudaMemcpyAsync(&hc, W.d_cnt.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
             AR_TRY(cudaMemcpyAsync(&hs[2], W.d_misc.as<unsigned long long>() + 1, 16, cudaMemcpyDeviceToHost, st));

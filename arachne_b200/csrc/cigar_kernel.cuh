@@ -1,0 +1,290 @@
+// Region -> alignment record, thread-per-region kernels (the warp-cooperative version in cigar.cuh/k_cigar stays as the
+// wide-band tier).  Same reference functions as cigar.cuh:
+//   mem_reg2aln bwa/bwamem.c:1086-1156, bwa_gen_cigar2 bwa/bwa.c:121-207, ksw_global2 bwa/ksw.c:504-606,
+//   GetAlignments walk src/aligner/aligner.go:1505-1569, InterpretAlign src/gobwa/gobwa.go:339-371.
+//
+// Why three tiers.  ncu (profiles/r1b): the one-warp-per-region kernel spent 13.6 k warp instructions per region because
+// (a) 32 lanes ran the gap-free path's 150-base loops redundantly and (b) the banded NW filled all qlen columns of every
+// row although the inferred band is a few cells wide.  On the bench workload 86 % of regions are gap-free
+// (bwa.c:141-149) and nearly all others need w <= 8.
+//   tier 1  k_cigar_fast   one lane per region: band inference; the gap-free case is finished here (score, NM, clips, walk)
+//   tier 2  k_cigar_band   one lane per queued region: exact ksw_global2 with the band in a 32-slot shared-memory ring
+//                          (w <= 14), direction bytes in a per-lane global slice, the up-to-3 band doublings of mem_reg2aln
+//   tier 3  k_cigar        (cigar.cuh) one warp per region for whatever needs a wider band or a long CIGAR
+// Sequences are read where they lie: the read from the batch buffer, the reference straight from the 2-bit .pac.
+#pragma once
+#include "cigar.cuh"
+
+namespace arachne {
+
+constexpr int CIG_LOCAL = 24;     // CIGAR ops a lane keeps locally; longer ones go to tier 3
+constexpr int BAND_RING = 32;     // ring slots per lane: covers band half-width w <= 14 (2w+3 <= 31)
+constexpr int BAND_WMAX = 14;
+constexpr int CIG_BLOCK = 128;
+
+struct CigArgs {
+    const uint8_t* seq; const int64_t* off;
+    long n_regs; const AlnReg* regs; const int* reg_read; AlnRec* alns;
+    uint32_t* cig_pool; unsigned long long cig_cap; int32_t* mm_pool; unsigned long long mm_cap;
+    unsigned long long* used;          // [0] CIGAR words, [1] mismatch ints
+    unsigned* list2; unsigned* n2;     // regions for tier 2
+    unsigned* list3; unsigned* n3;     // regions for tier 3
+    uint8_t* z; long z_stride;         // tier-2 direction bytes, one slice per lane
+    Counters* cnt;
+};
+
+// view of one region's two sequences in the orientation bwa_gen_cigar2 aligns them in (both reversed on the reverse
+// strand so that indels are left-aligned on the forward strand, bwa.c:135-140)
+struct RegView {
+    const uint8_t* q; const uint8_t* pac;
+    int64_t tpos;   // forward-strand coordinate of target base 0
+    int lq, rlen, qb, qe, rev;
+    __device__ __forceinline__ int Q(int i) const { return rev ? q[qe - 1 - i] : q[qb + i]; }
+    __device__ __forceinline__ int T(int i) const {
+        const int64_t p = tpos + i;
+        const int b = (__ldg(pac + (p >> 2)) >> ((~p & 3) << 1)) & 3;
+        return rev ? 3 - b : b;
+    }
+};
+
+__device__ __forceinline__ RegView make_view(const RefView& ref, const uint8_t* query, const AlnReg& ar) {
+    RegView v;
+    v.q = query; v.pac = ref.pac; v.qb = ar.qb; v.qe = ar.qe; v.lq = ar.qe - ar.qb; v.rlen = (int)(ar.re - ar.rb);
+    v.rev = ar.rb >= ref.l_pac;
+    v.tpos = v.rev ? (ref.l_pac << 1) - ar.re : ar.rb;
+    return v;
+}
+
+// NM as bwa_gen_cigar2 computes it (bwa.c:171-198)
+__device__ __forceinline__ int cig_nm(const RegView& v, const uint32_t* c, int n) {
+    int x = 0, y = 0, n_mm = 0, n_gap = 0;
+    for (int k = 0; k < n; ++k) {
+        const int op = c[k] & 0xf, len = (int)(c[k] >> 4);
+        if (op == 0) { for (int i = 0; i < len; ++i) n_mm += v.Q(x + i) != v.T(y + i); x += len; y += len; }
+        else if (op == 2) { if (k > 0 && k < n - 1) n_gap += len; y += len; }
+        else if (op == 1) { x += len; n_gap += len; }
+    }
+    return n_mm + n_gap;
+}
+
+// Everything mem_reg2aln does after the CIGAR loop (bwamem.c:1120-1155) + the GetAlignments walk + pool output.
+// c[0..n) is the CIGAR of the aligned part in forward-strand order; c must have room for two more words.
+__device__ __forceinline__ bool cig_finish(const CigArgs& A, const RefView& ref, long g, int r, int l_query, const uint8_t* query, const AlnReg& ar,
+                                           const RegView& v, uint32_t* c, int n, int score, int NM) {
+    AlnRec a;
+    int is_rev;
+    int64_t pos = bns_depos(ref, ar.rb < ref.l_pac ? ar.rb : ar.re - 1, &is_rev);
+    a.is_rev = is_rev; a.nm = NM;
+    int c0 = 0;
+    if (n > 0) {  // squeeze out a leading, else a trailing, deletion (:1124-1133)
+        if ((c[0] & 0xf) == 2) { pos += c[0] >> 4; --n; c0 = 1; }
+        else if ((c[n - 1] & 0xf) == 2) --n;
+    }
+    int clip5 = 0, clip3 = 0;
+    if (ar.qb != 0 || ar.qe != l_query) { clip5 = is_rev ? l_query - ar.qe : ar.qb; clip3 = is_rev ? ar.qb : l_query - ar.qe; }
+    const int n_out = n + (clip5 ? 1 : 0) + (clip3 ? 1 : 0);
+    a.n_cigar = n_out;
+    a.rid = bns_pos2rid(ref, pos);
+    a.pos = pos - ref.contigs[a.rid].offset;
+    a.score = ar.score; a.sub = ar.sub > ar.csub ? ar.sub : ar.csub;
+    // ---- GetAlignments walk (aligner.go:1505-1569): final CIGAR against the reference in read orientation ----
+    const int64_t coff = ref.contigs[ar.rid].offset;
+    const int64_t ch_pos = ar.rb < ref.l_pac ? ar.rb - coff : ref.l_pac * 2 - 1 - ar.rb - coff;
+    const int64_t ch_aend = ar.re < ref.l_pac ? ar.re - coff : ref.l_pac * 2 - 1 - ar.re - coff;
+    int64_t refStart = ch_pos, refEnd = ch_aend;
+    if (is_rev) { refStart = ch_aend + 1; refEnd = ch_pos + 1; }
+    const int ref_len = v.rlen;
+    int matches = 0, indels = 0, indel_len = 0, sclip = 0, sclip_len = 0, n_mm = 0;
+    unsigned long long mo = 0;
+    // op k of the final CIGAR: [clip5] c[c0 .. c0+n) [clip3]
+    auto op_at = [&](int k) -> uint32_t {
+        if (clip5) { if (k == 0) return (uint32_t)clip5 << 4 | 3; --k; }
+        return k < n ? c[c0 + k] : ((uint32_t)clip3 << 4 | 3);
+    };
+    for (int pass = 0; pass < 2; ++pass) {  // pass 0 counts the mismatch loci, pass 1 writes them
+        int refOff = 0, readOff = 0, w = 0;
+        for (int kk = 0; kk < n_out; ++kk) {
+            const uint32_t cw = op_at(is_rev ? n_out - 1 - kk : kk);
+            const int op = cw & 0xf, len = (int)(cw >> 4);
+            if (op == 0) {
+                for (int m = 0; m < len; ++m) {
+                    if (refOff + m >= ref_len) continue;
+                    // reference base k of the region in read orientation == target base (rev ? rlen-1-k : k) of the view
+                    const int k = refOff + m;
+                    if (readOff + m < l_query && v.T(v.rev ? v.rlen - 1 - k : k) != query[readOff + m]) {
+                        if (pass) {
+                            A.mm_pool[mo + w] = is_rev ? (int32_t)(refEnd - k) : (int32_t)(k + refStart);
+                            A.mm_pool[mo + n_mm + w] = readOff + m;
+                        }
+                        ++w;
+                    }
+                }
+                if (!pass) matches += len;
+                refOff += len; readOff += len;
+            } else if (op == 1) { if (!pass) { ++indels; indel_len += len; } readOff += len; }
+            else if (op == 2) { if (!pass) { ++indels; indel_len += len; } refOff += len; }
+            else if (op == 3) { if (!pass) { ++sclip; sclip_len += len; } readOff += len; }
+        }
+        if (!pass) {
+            n_mm = w;
+            if (n_mm == 0) break;
+            mo = atomicAdd(&A.used[1], (unsigned long long)(2 * n_mm));
+            if (mo + 2 * n_mm > A.mm_cap) { raise(A.cnt, -101, r); return false; }
+        }
+    }
+    int mismatches = NM - indel_len;
+    matches -= mismatches;
+    if (mismatches < 0) mismatches = 0;
+    a.matches = matches; a.mismatches = mismatches; a.indels = indels; a.soft_clipped = sclip; a.soft_clipped_length = sclip_len;
+    a.n_mm = n_mm; a.mm_off = (int64_t)mo;
+    const unsigned long long co = atomicAdd(&A.used[0], (unsigned long long)n_out);
+    if (co + n_out > A.cig_cap) { raise(A.cnt, -101, r); return false; }
+    for (int k = 0; k < n_out; ++k) A.cig_pool[co + k] = op_at(k);
+    a.cigar_off = (int64_t)co;
+    A.alns[g] = a;
+    return true;
+}
+
+// band half-width mem_reg2aln starts from (bwamem.c:1105-1110)
+__device__ __forceinline__ int cig_first_w(const MemOpt& opt, const AlnReg& ar) {
+    const int l1 = ar.qe - ar.qb, l2 = (int)(ar.re - ar.rb);
+    int tmp = infer_bw(l1, l2, ar.truesc, opt.a, opt.o_del, opt.e_del);
+    int w2 = infer_bw(l1, l2, ar.truesc, opt.a, opt.o_ins, opt.e_ins);
+    w2 = w2 > tmp ? w2 : tmp;
+    if (w2 > opt.w) w2 = w2 < ar.w ? w2 : ar.w;
+    return w2;
+}
+
+// ------------------------------------------------------------------------------------------------ tier 1
+__global__ void __launch_bounds__(CIG_BLOCK) k_cigar_fast(MemOpt opt, RefView ref, CigArgs A) {
+    for (long g = blockIdx.x * (long)blockDim.x + threadIdx.x; g < A.n_regs; g += (long)gridDim.x * blockDim.x) {
+        const AlnReg ar = A.regs[g];
+        const int r = A.reg_read[g];
+        const int l_query = (int)(A.off[r + 1] - A.off[r]);
+        const uint8_t* query = A.seq + A.off[r];
+        const int lq = ar.qe - ar.qb;
+        // anything bwa_gen_cigar2 answers without an alignment (bwa.c:133-135), or that looks unusual, is the wide tier's
+        const bool odd = ar.rb < 0 || ar.re < 0 || lq <= 0 || ar.rb >= ar.re || (ar.rb < ref.l_pac && ar.re > ref.l_pac) || ar.re > (ref.l_pac << 1);
+        if (odd) { A.list3[atomicAdd(A.n3, 1u)] = (unsigned)g; continue; }
+        int w2 = cig_first_w(opt, ar);
+        w2 = w2 < opt.w << 2 ? w2 : opt.w << 2;
+        const RegView v = make_view(ref, query, ar);
+        if (!(lq == v.rlen && w2 == 0)) { A.list2[atomicAdd(A.n2, 1u)] = (unsigned)g; continue; }
+        // gap-free (bwa.c:141-149).  The band-doubling loop of mem_reg2aln re-runs this with w2 = 0 << 1 = 0 and stops on
+        // the unchanged score, so this is the final answer.
+        int score = 0, nm = 0;
+        for (int i = 0; i < lq; ++i) {
+            const int qb = v.Q(i), tb = v.T(i);
+            score += qb > 3 ? -1 : (qb == tb ? opt.a : -opt.b);
+            nm += qb != tb;
+        }
+        uint32_t c[3];
+        c[0] = (uint32_t)lq << 4;
+        cig_finish(A, ref, g, r, l_query, query, ar, v, c, 1, score, nm);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ tier 2
+// One bwa_gen_cigar2 call for band parameter w_ (bwa.c:121-207) on the lane's ring.  Returns n_cigar >= 0 with the CIGAR
+// in c (forward-strand order), or -1 when this lane cannot do it (band or CIGAR too large -> tier 3).
+__device__ __forceinline__ int band_gen_cigar(const MemOpt& opt, const RegView& v, int w_, int2 (*ring)[CIG_BLOCK], uint8_t* z, long z_cap,
+                                              int* score, uint32_t* c, unsigned long long* cells) {
+    const int lq = v.lq, rlen = v.rlen, tid = threadIdx.x;
+    if (lq == rlen && w_ == 0) {
+        int s = 0;
+        for (int i = 0; i < lq; ++i) { const int qb = v.Q(i), tb = v.T(i); s += qb > 3 ? -1 : (qb == tb ? opt.a : -opt.b); }
+        *score = s; c[0] = (uint32_t)lq << 4;
+        return 1;
+    }
+    int max_ins = (int)((double)(((lq + 1) >> 1) * opt.mat[0] - opt.o_ins) / opt.e_ins + 1.);
+    int max_del = (int)((double)(((lq + 1) >> 1) * opt.mat[0] - opt.o_del) / opt.e_del + 1.);
+    int max_gap = max_ins > max_del ? max_ins : max_del;
+    max_gap = max_gap > 1 ? max_gap : 1;
+    int dl = rlen - lq; dl = dl < 0 ? -dl : dl;
+    int w = (max_gap + dl + 1) >> 1;
+    w = w < w_ ? w : w_;
+    w = w > dl + 3 ? w : dl + 3;
+    if (w > BAND_WMAX) return -1;
+    const int n_col = lq < 2 * w + 1 ? lq : 2 * w + 1;
+    if ((long)n_col * rlen > z_cap) return -1;
+    // ksw_global2 (ksw.c:504-606): eh[j] = {H(i-1,j-1), E(i,j)} lives in ring slot j & 31
+    const int e_del = opt.e_del, e_ins = opt.e_ins, oe_del = opt.o_del + opt.e_del, oe_ins = opt.o_ins + opt.e_ins;
+    for (int j = 0; j <= lq && j <= w + 1; ++j) ring[j & (BAND_RING - 1)][tid] = make_int2(j == 0 ? 0 : (j <= w ? -(opt.o_ins + e_ins * j) : KSW_MINUS_INF), KSW_MINUS_INF);
+    for (int i = 0; i < rlen; ++i) {
+        const int tb = v.T(i);
+        const int beg = i > w ? i - w : 0, end = i + w + 1 < lq ? i + w + 1 : lq;
+        int f = KSW_MINUS_INF, left = beg == 0 ? -(opt.o_del + e_del * (i + 1)) : KSW_MINUS_INF;
+        uint8_t* zi = z + (long)i * n_col - beg;
+        for (int j = beg; j < end; ++j) {
+            const int2 he = ring[j & (BAND_RING - 1)][tid];
+            const int qb = v.Q(j);
+            const int m = he.x + ((qb > 3) ? -1 : (qb == tb ? opt.a : -opt.b));
+            int e = he.y, h, d, x;
+            d = m >= e ? 0 : 1; h = m >= e ? m : e;
+            if (h < f) { d = 2; h = f; }
+            x = m - oe_del; e -= e_del;
+            if (e > x) d |= 1 << 2; else e = x;
+            ring[j & (BAND_RING - 1)][tid] = make_int2(left, e);
+            left = h;
+            x = m - oe_ins; f -= e_ins;
+            if (f > x) d |= 2 << 4; else f = x;
+            zi[j] = (uint8_t)d;
+        }
+        ring[end & (BAND_RING - 1)][tid] = make_int2(left, KSW_MINUS_INF);
+        *cells += end > beg ? end - beg : 0;
+    }
+    *score = ring[lq & (BAND_RING - 1)][tid].x;
+    // backtrack (ksw.c:585-603): ops are produced last-to-first
+    int n = 0, state = 0, i = rlen - 1, k = (i + w + 1 < lq ? i + w + 1 : lq) - 1;
+    auto push = [&](int op, int len) -> bool {
+        if (n > 0 && (int)(c[n - 1] & 0xf) == op) { c[n - 1] += (uint32_t)len << 4; return true; }
+        if (n >= CIG_LOCAL - 2) return false;
+        c[n++] = (uint32_t)len << 4 | op;
+        return true;
+    };
+    bool ok = true;
+    while (i >= 0 && k >= 0 && ok) {
+        const int beg = i > w ? i - w : 0;
+        state = z[(long)i * n_col + (k - beg)] >> (state << 1) & 3;
+        if (state == 0) { ok = push(0, 1); --i; --k; }
+        else if (state == 1) { ok = push(2, 1); --i; }
+        else { ok = push(1, 1); --k; }
+    }
+    if (ok && i >= 0) ok = push(2, i + 1);
+    if (ok && k >= 0) ok = push(1, k + 1);
+    if (!ok) return -1;
+    for (int a = 0; a < n >> 1; ++a) { const uint32_t t = c[a]; c[a] = c[n - 1 - a]; c[n - 1 - a] = t; }
+    return n;
+}
+
+__global__ void __launch_bounds__(CIG_BLOCK) k_cigar_band(MemOpt opt, RefView ref, CigArgs A) {
+    __shared__ int2 ring[BAND_RING][CIG_BLOCK];
+    const unsigned n2 = *A.n2;
+    uint8_t* z = A.z + (blockIdx.x * (long)blockDim.x + threadIdx.x) * A.z_stride;
+    unsigned long long cells = 0;
+    for (unsigned t = blockIdx.x * blockDim.x + threadIdx.x; t < n2; t += gridDim.x * blockDim.x) {
+        const long g = A.list2[t];
+        const AlnReg ar = A.regs[g];
+        const int r = A.reg_read[g];
+        const int l_query = (int)(A.off[r + 1] - A.off[r]);
+        const uint8_t* query = A.seq + A.off[r];
+        const RegView v = make_view(ref, query, ar);
+        uint32_t c[CIG_LOCAL];
+        // the band-doubling loop of mem_reg2aln (bwamem.c:1111-1119)
+        int w2 = cig_first_w(opt, ar), i = 0, score = 0, n = 0, last_sc = -(1 << 30);
+        bool bail = false;
+        do {
+            w2 = w2 < opt.w << 2 ? w2 : opt.w << 2;
+            n = band_gen_cigar(opt, v, w2, ring, z, A.z_stride, &score, c, &cells);
+            if (n < 0) { bail = true; break; }
+            if (score == last_sc || w2 == opt.w << 2) break;
+            last_sc = score;
+            w2 <<= 1;
+        } while (++i < 3 && score < ar.truesc - opt.a);
+        if (bail) { A.list3[atomicAdd(A.n3, 1u)] = (unsigned)g; continue; }
+        cig_finish(A, ref, g, r, l_query, query, ar, v, c, n, score, cig_nm(v, c, n));
+    }
+    if (cells) atomicAdd(&A.cnt->glb_cells, cells);
+}
+
+}  // namespace arachne

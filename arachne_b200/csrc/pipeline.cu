@@ -50,6 +50,7 @@ __device__ __forceinline__ void raise(Counters* c, int code, int read) {
 // ------------------------------------------------------------------------------------------------ k_seed2
 }  // namespace arachne
 #include "place.cuh"
+#include "cigar_kernel.cuh"
 #include "seed_kernel.cuh"
 namespace arachne {
 
@@ -297,7 +298,8 @@ __global__ void __launch_bounds__(EXT_WARPS * 32) k_cigar(MemOpt opt, RefView re
                                                           uint32_t* cig_pool, unsigned long long cig_cap, int32_t* mm_pool, unsigned long long mm_cap,
                                                           unsigned long long* used /*[0]=cigar [1]=mm*/, uint8_t* win, int win_cap, uint8_t* zbuf,
                                                           long z_cap, uint32_t* cig_scr, int cig_scr_cap, int32_t* mm_scr, int mm_scr_cap,
-                                                          unsigned int* next, Counters* cnt) {
+                                                          unsigned int* next, Counters* cnt, const unsigned* list, const unsigned* n_list) {
+    if (list) n_regs = (long)*n_list;  // wide-band tier: only the regions the thread-per-region tiers handed over
     const int lane = threadIdx.x & 31;
     const long gw = (blockIdx.x * (long)blockDim.x + threadIdx.x) >> 5;
     WarpCtx ctx;
@@ -310,6 +312,7 @@ __global__ void __launch_bounds__(EXT_WARPS * 32) k_cigar(MemOpt opt, RefView re
         if (lane == 0) g = (long)atomicAdd(next, 1u);
         g = __shfl_sync(FULL, g, 0);
         if (g >= n_regs) break;
+        if (list) g = (long)list[g];
         const int r = reg_read[g];
         const int len = (int)(off[r + 1] - off[r]);
         const AlnReg ar = regs[g];
@@ -442,7 +445,7 @@ struct Workspace {
     DevBuf d_seeds, d_kseeds, d_chains, d_nodes, d_order, d_kept, d_nchain, d_nkseed, d_srt, d_regs, d_nregs, d_win, d_reg_off, d_out;
     DevBuf d_nregs_bak, d_reg_loc, d_blist, d_resc, d_reg_read, d_z, d_cig_scr, d_mm_scr, d_alns, d_cig, d_mm, d_hscr, d_rscr;
     DevBuf d_bc_off, d_run_rfa, d_rand_seed, d_centro, d_pl_cnt, d_pl_scan, d_cand_off, d_lmp, d_cands, d_hot, d_aux, d_slow, d_slot_of_bc, d_bc_of_slot,
-        d_first, d_keys_a, d_keys_b, d_vals_a, d_vals_b, d_seg_off, d_mol;
+        d_first, d_keys_a, d_keys_b, d_vals_a, d_vals_b, d_seg_off, d_mol, d_list2, d_list3, d_zband;
     cudaStream_t own_stream = nullptr;
     cudaEvent_t ev[10] = {};
     Counters* h_cnt = nullptr;              // pinned
@@ -453,7 +456,7 @@ struct Workspace {
                 &d_seeds, &d_kseeds, &d_chains, &d_nodes, &d_order, &d_kept, &d_nchain, &d_nkseed, &d_srt, &d_regs, &d_nregs,
                 &d_win, &d_reg_off, &d_out, &d_nregs_bak, &d_reg_loc, &d_blist, &d_resc, &d_reg_read, &d_z, &d_cig_scr, &d_mm_scr, &d_alns, &d_cig, &d_mm, &d_hscr, &d_rscr,
                 &d_bc_off, &d_run_rfa, &d_rand_seed, &d_centro, &d_pl_cnt, &d_pl_scan, &d_cand_off, &d_lmp, &d_cands, &d_hot, &d_aux, &d_slow, &d_slot_of_bc,
-                &d_bc_of_slot, &d_first, &d_keys_a, &d_keys_b, &d_vals_a, &d_vals_b, &d_seg_off, &d_mol};
+                &d_bc_of_slot, &d_first, &d_keys_a, &d_keys_b, &d_vals_a, &d_vals_b, &d_seg_off, &d_mol, &d_list2, &d_list3, &d_zband};
     }
     int init() {
         if (cudaStreamCreateWithFlags(&own_stream, cudaStreamNonBlocking) != cudaSuccess) return -1;
