@@ -261,12 +261,19 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
         unsigned long long cig_cap = total_regs * 4 + 4096, mm_cap = total_regs * 12 + 4096;
         // thread-per-region tiers (cigar_kernel.cuh); ARACHNE_CIGAR_TIERS=0 sends every region to the warp tier
         const bool cigar_tiers = !(getenv("ARACHNE_CIGAR_TIERS") && atoi(getenv("ARACHNE_CIGAR_TIERS")) == 0);
-        const int band_blocks = sms * 4;
-        const long zband_stride = (long)maxlen * (2 * BAND_WMAX + 1);
+        const size_t band_smem = (size_t)BAND_RING * CIG_BLOCK * sizeof(int2);
+        int band_per_sm = 1;
+        if (cigar_tiers) {
+            AR_TRY(cudaFuncSetAttribute(k_cigar_band, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)band_smem));
+            AR_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&band_per_sm, k_cigar_band, CIG_BLOCK, band_smem));
+            if (band_per_sm < 1) band_per_sm = 1;
+        }
+        const int band_blocks = sms * band_per_sm;
+        const int zband_rows = maxlen + 2 * BAND_WMAX + 4;  // rlen <= l_query + band
         if (cigar_tiers) {
             AR_ALLOC(W.d_list2, (total_regs + 1) * 4);
             AR_ALLOC(W.d_list3, (total_regs + 1) * 4);
-            AR_ALLOC(W.d_zband, (size_t)band_blocks * CIG_BLOCK * zband_stride);
+            AR_ALLOC(W.d_zband, (size_t)band_blocks * CIG_BLOCK * zband_rows * BAND_ZCHUNK * 8);
         }
         for (int attempt = 0;; ++attempt) {
             AR_ALLOC(W.d_cig, cig_cap * 4);
@@ -277,13 +284,13 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
             CA.seq = d_seq; CA.off = d_off; CA.n_regs = (long)total_regs; CA.regs = W.d_out.as<AlnReg>(); CA.reg_read = W.d_reg_read.as<int>();
             CA.alns = W.d_alns.as<AlnRec>(); CA.cig_pool = W.d_cig.as<uint32_t>(); CA.cig_cap = cig_cap; CA.mm_pool = W.d_mm.as<int32_t>(); CA.mm_cap = mm_cap;
             CA.used = W.d_misc.as<unsigned long long>() + 1; CA.list2 = W.d_list2.as<unsigned>(); CA.n2 = W.d_misc.as<unsigned>() + 8;
-            CA.list3 = W.d_list3.as<unsigned>(); CA.n3 = W.d_misc.as<unsigned>() + 9; CA.z = W.d_zband.as<uint8_t>(); CA.z_stride = zband_stride;
+            CA.list3 = W.d_list3.as<unsigned>(); CA.n3 = W.d_misc.as<unsigned>() + 9; CA.z = W.d_zband.as<unsigned long long>(); CA.z_rows = zband_rows;
             CA.cnt = W.d_cnt.as<Counters>();
             const unsigned* l3 = nullptr; const unsigned* n3 = nullptr;
             if (cigar_tiers) {
                 nl += 2;
-                k_cigar_fast<<<band_blocks * 2, CIG_BLOCK, 0, st>>>(opt, idx->ref, CA);
-                k_cigar_band<<<band_blocks, CIG_BLOCK, 0, st>>>(opt, idx->ref, CA);
+                k_cigar_fast<<<sms * 8, CIG_BLOCK, 0, st>>>(opt, idx->ref, CA);
+                k_cigar_band<<<band_blocks, CIG_BLOCK, band_smem, st>>>(opt, idx->ref, CA);
                 l3 = CA.list3; n3 = CA.n3;
             }
             ++nl;

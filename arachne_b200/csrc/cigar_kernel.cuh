@@ -8,8 +8,11 @@
 // row although the inferred band is a few cells wide.  On the bench workload 86 % of regions are gap-free
 // (bwa.c:141-149) and nearly all others need w <= 8.
 //   tier 1  k_cigar_fast   one lane per region: band inference; the gap-free case is finished here (score, NM, clips, walk)
-//   tier 2  k_cigar_band   one lane per queued region: exact ksw_global2 with the band in a 32-slot shared-memory ring
-//                          (w <= 14), direction bytes in a per-lane global slice, the up-to-3 band doublings of mem_reg2aln
+//   tier 2  k_cigar_band   one lane per queued region: exact ksw_global2 with the band in a 64-slot shared-memory ring
+//                          (w <= 30); the traceback matrix is 4 bits per cell, accumulated in a register and stored 16 cells at
+//                          a time, interleaved across lanes so that a warp's stores coalesce (byte-per-cell stores into
+//                          per-lane slices made this kernel L2-transaction bound: 4.8 ms, profiles/r1d); the up-to-3 band
+//                          doublings of mem_reg2aln
 //   tier 3  k_cigar        (cigar.cuh) one warp per region for whatever needs a wider band or a long CIGAR
 // Sequences are read where they lie: the read from the batch buffer, the reference straight from the 2-bit .pac.
 #pragma once
@@ -18,8 +21,9 @@
 namespace arachne {
 
 constexpr int CIG_LOCAL = 24;     // CIGAR ops a lane keeps locally; longer ones go to tier 3
-constexpr int BAND_RING = 32;     // ring slots per lane: covers band half-width w <= 14 (2w+3 <= 31)
-constexpr int BAND_WMAX = 14;
+constexpr int BAND_RING = 64;     // ring slots per lane: covers band half-width w <= 30 (2w+3 <= 63)
+constexpr int BAND_WMAX = 30;
+constexpr int BAND_ZCHUNK = 4;    // 64-bit words of 4-bit direction codes per row: 16 cells each, 2w+1 <= 61 cells
 constexpr int CIG_BLOCK = 128;
 
 struct CigArgs {
@@ -29,7 +33,7 @@ struct CigArgs {
     unsigned long long* used;          // [0] CIGAR words, [1] mismatch ints
     unsigned* list2; unsigned* n2;     // regions for tier 2
     unsigned* list3; unsigned* n3;     // regions for tier 3
-    uint8_t* z; long z_stride;         // tier-2 direction bytes, one slice per lane
+    unsigned long long* z; int z_rows; // tier-2 direction codes: word (row, chunk) of lane t at z[(row*BAND_ZCHUNK + chunk)*T + t]
     Counters* cnt;
 };
 
@@ -187,8 +191,10 @@ __global__ void __launch_bounds__(CIG_BLOCK) k_cigar_fast(MemOpt opt, RefView re
 // ------------------------------------------------------------------------------------------------ tier 2
 // One bwa_gen_cigar2 call for band parameter w_ (bwa.c:121-207) on the lane's ring.  Returns n_cigar >= 0 with the CIGAR
 // in c (forward-strand order), or -1 when this lane cannot do it (band or CIGAR too large -> tier 3).
-__device__ __forceinline__ int band_gen_cigar(const MemOpt& opt, const RegView& v, int w_, int2 (*ring)[CIG_BLOCK], uint8_t* z, long z_cap,
-                                              int* score, uint32_t* c, unsigned long long* cells) {
+// Direction code per cell (ksw.c:551-563 keeps a byte d = h | e<<2 | f<<4 with e in {0,1}, f in {0,2}):
+// nibble = h | e<<2 | (f>>1)<<3.
+__device__ __forceinline__ int band_gen_cigar(const MemOpt& opt, const RegView& v, int w_, int2 (*ring)[CIG_BLOCK], unsigned long long* z, long T,
+                                              int z_rows, int* score, uint32_t* c, unsigned long long* cells) {
     const int lq = v.lq, rlen = v.rlen, tid = threadIdx.x;
     if (lq == rlen && w_ == 0) {
         int s = 0;
@@ -204,32 +210,33 @@ __device__ __forceinline__ int band_gen_cigar(const MemOpt& opt, const RegView& 
     int w = (max_gap + dl + 1) >> 1;
     w = w < w_ ? w : w_;
     w = w > dl + 3 ? w : dl + 3;
-    if (w > BAND_WMAX) return -1;
-    const int n_col = lq < 2 * w + 1 ? lq : 2 * w + 1;
-    if ((long)n_col * rlen > z_cap) return -1;
-    // ksw_global2 (ksw.c:504-606): eh[j] = {H(i-1,j-1), E(i,j)} lives in ring slot j & 31
+    if (w > BAND_WMAX || rlen > z_rows) return -1;
+    // ksw_global2 (ksw.c:504-606): eh[j] = {H(i-1,j-1), E(i,j)} lives in ring slot j & 63
     const int e_del = opt.e_del, e_ins = opt.e_ins, oe_del = opt.o_del + opt.e_del, oe_ins = opt.o_ins + opt.e_ins;
     for (int j = 0; j <= lq && j <= w + 1; ++j) ring[j & (BAND_RING - 1)][tid] = make_int2(j == 0 ? 0 : (j <= w ? -(opt.o_ins + e_ins * j) : KSW_MINUS_INF), KSW_MINUS_INF);
     for (int i = 0; i < rlen; ++i) {
         const int tb = v.T(i);
         const int beg = i > w ? i - w : 0, end = i + w + 1 < lq ? i + w + 1 : lq;
         int f = KSW_MINUS_INF, left = beg == 0 ? -(opt.o_del + e_del * (i + 1)) : KSW_MINUS_INF;
-        uint8_t* zi = z + (long)i * n_col - beg;
+        unsigned long long acc = 0, *zi = z + (long)i * BAND_ZCHUNK * T;
         for (int j = beg; j < end; ++j) {
             const int2 he = ring[j & (BAND_RING - 1)][tid];
             const int qb = v.Q(j);
             const int m = he.x + ((qb > 3) ? -1 : (qb == tb ? opt.a : -opt.b));
-            int e = he.y, h, d, x;
-            d = m >= e ? 0 : 1; h = m >= e ? m : e;
-            if (h < f) { d = 2; h = f; }
+            int e = he.y, h, x;
+            unsigned d = m >= e ? 0u : 1u; h = m >= e ? m : e;
+            if (h < f) { d = 2u; h = f; }
             x = m - oe_del; e -= e_del;
-            if (e > x) d |= 1 << 2; else e = x;
+            if (e > x) d |= 4u; else e = x;
             ring[j & (BAND_RING - 1)][tid] = make_int2(left, e);
             left = h;
             x = m - oe_ins; f -= e_ins;
-            if (f > x) d |= 2 << 4; else f = x;
-            zi[j] = (uint8_t)d;
+            if (f > x) d |= 8u; else f = x;
+            const int ci = j - beg;
+            acc |= (unsigned long long)d << ((ci & 15) << 2);
+            if ((ci & 15) == 15) { zi[(long)(ci >> 4) * T] = acc; acc = 0; }
         }
+        if ((end - beg) & 15) zi[(long)((end - beg) >> 4) * T] = acc;
         ring[end & (BAND_RING - 1)][tid] = make_int2(left, KSW_MINUS_INF);
         *cells += end > beg ? end - beg : 0;
     }
@@ -244,8 +251,10 @@ __device__ __forceinline__ int band_gen_cigar(const MemOpt& opt, const RegView& 
     };
     bool ok = true;
     while (i >= 0 && k >= 0 && ok) {
-        const int beg = i > w ? i - w : 0;
-        state = z[(long)i * n_col + (k - beg)] >> (state << 1) & 3;
+        const int ci = k - (i > w ? i - w : 0);
+        if (ci < 0 || k >= (i + w + 1 < lq ? i + w + 1 : lq)) return -1;  // the path left the band: the reference reads a neighbouring row's byte here
+        const unsigned nib = (unsigned)(z[((long)i * BAND_ZCHUNK + (ci >> 4)) * T] >> ((ci & 15) << 2)) & 15u;
+        state = state == 0 ? (int)(nib & 3u) : (state == 1 ? (int)((nib >> 2) & 1u) : (int)((nib >> 3) & 1u) << 1);
         if (state == 0) { ok = push(0, 1); --i; --k; }
         else if (state == 1) { ok = push(2, 1); --i; }
         else { ok = push(1, 1); --k; }
@@ -258,9 +267,11 @@ __device__ __forceinline__ int band_gen_cigar(const MemOpt& opt, const RegView& 
 }
 
 __global__ void __launch_bounds__(CIG_BLOCK) k_cigar_band(MemOpt opt, RefView ref, CigArgs A) {
-    __shared__ int2 ring[BAND_RING][CIG_BLOCK];
+    extern __shared__ int2 ring_raw[];
+    int2 (*ring)[CIG_BLOCK] = reinterpret_cast<int2 (*)[CIG_BLOCK]>(ring_raw);
     const unsigned n2 = *A.n2;
-    uint8_t* z = A.z + (blockIdx.x * (long)blockDim.x + threadIdx.x) * A.z_stride;
+    const long T = (long)gridDim.x * blockDim.x;
+    unsigned long long* z = A.z + (blockIdx.x * (long)blockDim.x + threadIdx.x);
     unsigned long long cells = 0;
     for (unsigned t = blockIdx.x * blockDim.x + threadIdx.x; t < n2; t += gridDim.x * blockDim.x) {
         const long g = A.list2[t];
@@ -275,7 +286,7 @@ __global__ void __launch_bounds__(CIG_BLOCK) k_cigar_band(MemOpt opt, RefView re
         bool bail = false;
         do {
             w2 = w2 < opt.w << 2 ? w2 : opt.w << 2;
-            n = band_gen_cigar(opt, v, w2, ring, z, A.z_stride, &score, c, &cells);
+            n = band_gen_cigar(opt, v, w2, ring, z, T, A.z_rows, &score, c, &cells);
             if (n < 0) { bail = true; break; }
             if (score == last_sc || w2 == opt.w << 2) break;
             last_sc = score;
