@@ -271,7 +271,7 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
         const int band_blocks = sms * band_per_sm;
         const int zband_rows = maxlen + 2 * BAND_WMAX + 4;  // rlen <= l_query + band
         if (cigar_tiers) {
-            AR_ALLOC(W.d_list2, (total_regs + 1) * 4);
+            AR_ALLOC(W.d_list2, (total_regs + 1) * 4 * 4);  // list, sorted list, keys, sorted keys
             AR_ALLOC(W.d_list3, (total_regs + 1) * 4);
             AR_ALLOC(W.d_zband, (size_t)band_blocks * CIG_BLOCK * zband_rows * BAND_ZCHUNK * 8);
         }
@@ -289,7 +289,17 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
             const unsigned* l3 = nullptr; const unsigned* n3 = nullptr;
             if (cigar_tiers) {
                 nl += 2;
+                unsigned* l2 = W.d_list2.as<unsigned>(); const size_t nr1 = (size_t)total_regs + 1;
+                CA.list2 = l2; CA.key2 = l2 + 2 * nr1;
+                AR_TRY(cudaMemsetAsync(CA.key2, 0xff, nr1 * 4, st));
                 k_cigar_fast<<<sms * 8, CIG_BLOCK, 0, st>>>(opt, idx->ref, CA);
+                size_t sbytes = 0;
+                cub::DeviceRadixSort::SortPairs(nullptr, sbytes, CA.key2, l2 + 3 * nr1, l2, l2 + nr1, (int)total_regs, 0, 16, st);
+                AR_ALLOC(W.d_tmp, sbytes + 16);
+                sbytes = W.d_tmp.cap;
+                AR_TRY(cub::DeviceRadixSort::SortPairs(W.d_tmp.p, sbytes, CA.key2, l2 + 3 * nr1, l2, l2 + nr1, (int)total_regs, 0, 16, st));
+                nl += 3;
+                CA.list2 = l2 + nr1;
                 k_cigar_band<<<band_blocks, CIG_BLOCK, band_smem, st>>>(opt, idx->ref, CA);
                 l3 = CA.list3; n3 = CA.n3;
             }

@@ -23,7 +23,7 @@ namespace arachne {
 constexpr int CIG_LOCAL = 24;     // CIGAR ops a lane keeps locally; longer ones go to tier 3
 constexpr int BAND_RING = 64;     // ring slots per lane: covers band half-width w <= 30 (2w+3 <= 63)
 constexpr int BAND_WMAX = 30;
-constexpr int BAND_ZCHUNK = 4;    // 64-bit words of 4-bit direction codes per row: 16 cells each, 2w+1 <= 61 cells
+constexpr int BAND_ZCHUNK = 4;    // 64 bits x 4 of 4-bit direction codes per row (stored as 8 32-bit words of 8 cells), 2w+1 <= 61 cells
 constexpr int CIG_BLOCK = 128;
 
 struct CigArgs {
@@ -31,7 +31,8 @@ struct CigArgs {
     long n_regs; const AlnReg* regs; const int* reg_read; AlnRec* alns;
     uint32_t* cig_pool; unsigned long long cig_cap; int32_t* mm_pool; unsigned long long mm_cap;
     unsigned long long* used;          // [0] CIGAR words, [1] mismatch ints
-    unsigned* list2; unsigned* n2;     // regions for tier 2
+    unsigned* list2; unsigned* n2;     // regions for tier 2 (k_cigar_fast appends, the host sorts by key2, k_cigar_band reads)
+    unsigned* key2;
     unsigned* list3; unsigned* n3;     // regions for tier 3
     unsigned long long* z; int z_rows; // tier-2 direction codes: word (row, chunk) of lane t at z[(row*BAND_ZCHUNK + chunk)*T + t]
     Counters* cnt;
@@ -159,6 +160,18 @@ __device__ __forceinline__ int cig_first_w(const MemOpt& opt, const AlnReg& ar) 
     return w2;
 }
 
+// the band half-width ksw_global2 is really called with (bwa.c:151-163)
+__device__ __forceinline__ int cig_eff_w(const MemOpt& opt, int lq, int rlen, int w_) {
+    int max_ins = (int)((double)(((lq + 1) >> 1) * opt.mat[0] - opt.o_ins) / opt.e_ins + 1.);
+    int max_del = (int)((double)(((lq + 1) >> 1) * opt.mat[0] - opt.o_del) / opt.e_del + 1.);
+    int max_gap = max_ins > max_del ? max_ins : max_del;
+    max_gap = max_gap > 1 ? max_gap : 1;
+    int dl = rlen - lq; dl = dl < 0 ? -dl : dl;
+    int w = (max_gap + dl + 1) >> 1;
+    w = w < w_ ? w : w_;
+    return w > dl + 3 ? w : dl + 3;
+}
+
 // ------------------------------------------------------------------------------------------------ tier 1
 __global__ void __launch_bounds__(CIG_BLOCK) k_cigar_fast(MemOpt opt, RefView ref, CigArgs A) {
     for (long g = blockIdx.x * (long)blockDim.x + threadIdx.x; g < A.n_regs; g += (long)gridDim.x * blockDim.x) {
@@ -173,7 +186,15 @@ __global__ void __launch_bounds__(CIG_BLOCK) k_cigar_fast(MemOpt opt, RefView re
         int w2 = cig_first_w(opt, ar);
         w2 = w2 < opt.w << 2 ? w2 : opt.w << 2;
         const RegView v = make_view(ref, query, ar);
-        if (!(lq == v.rlen && w2 == 0)) { A.list2[atomicAdd(A.n2, 1u)] = (unsigned)g; continue; }
+        if (!(lq == v.rlen && w2 == 0)) {
+            // banded: tier 2 takes it when the first band fits its ring; the key lets the host sort tier 2's work so that
+            // the lanes of a warp get regions with the same band width and similar length
+            const int w = cig_eff_w(opt, lq, v.rlen, w2);
+            if (w > BAND_WMAX) { A.list3[atomicAdd(A.n3, 1u)] = (unsigned)g; continue; }
+            const unsigned t = atomicAdd(A.n2, 1u);
+            A.list2[t] = (unsigned)g; A.key2[t] = (unsigned)w << 10 | (unsigned)(v.rlen < 1023 ? v.rlen : 1023);
+            continue;
+        }
         // gap-free (bwa.c:141-149).  The band-doubling loop of mem_reg2aln re-runs this with w2 = 0 << 1 = 0 and stops on
         // the unchanged score, so this is the final answer.
         int score = 0, nm = 0;
@@ -193,7 +214,7 @@ __global__ void __launch_bounds__(CIG_BLOCK) k_cigar_fast(MemOpt opt, RefView re
 // in c (forward-strand order), or -1 when this lane cannot do it (band or CIGAR too large -> tier 3).
 // Direction code per cell (ksw.c:551-563 keeps a byte d = h | e<<2 | f<<4 with e in {0,1}, f in {0,2}):
 // nibble = h | e<<2 | (f>>1)<<3.
-__device__ __forceinline__ int band_gen_cigar(const MemOpt& opt, const RegView& v, int w_, int2 (*ring)[CIG_BLOCK], unsigned long long* z, long T,
+__device__ __forceinline__ int band_gen_cigar(const MemOpt& opt, const RegView& v, int w_, int2 (*ring)[CIG_BLOCK], unsigned* z32, long T,
                                               int z_rows, int* score, uint32_t* c, unsigned long long* cells) {
     const int lq = v.lq, rlen = v.rlen, tid = threadIdx.x;
     if (lq == rlen && w_ == 0) {
@@ -202,42 +223,52 @@ __device__ __forceinline__ int band_gen_cigar(const MemOpt& opt, const RegView& 
         *score = s; c[0] = (uint32_t)lq << 4;
         return 1;
     }
-    int max_ins = (int)((double)(((lq + 1) >> 1) * opt.mat[0] - opt.o_ins) / opt.e_ins + 1.);
-    int max_del = (int)((double)(((lq + 1) >> 1) * opt.mat[0] - opt.o_del) / opt.e_del + 1.);
-    int max_gap = max_ins > max_del ? max_ins : max_del;
-    max_gap = max_gap > 1 ? max_gap : 1;
-    int dl = rlen - lq; dl = dl < 0 ? -dl : dl;
-    int w = (max_gap + dl + 1) >> 1;
-    w = w < w_ ? w : w_;
-    w = w > dl + 3 ? w : dl + 3;
+    const int w = cig_eff_w(opt, lq, rlen, w_);
     if (w > BAND_WMAX || rlen > z_rows) return -1;
-    // ksw_global2 (ksw.c:504-606): eh[j] = {H(i-1,j-1), E(i,j)} lives in ring slot j & 63
+    // ksw_global2 (ksw.c:504-606): eh[j] = {H(i-1,j-1), E(i,j)} lives in ring slot j & 63.  The slot also carries the
+    // query base of column j (low 3 bits of .y, E above them), so the cell loop has no global load: a column's base is
+    // fetched once, when the sliding band first reaches it.  "-infinity" is -2^26 here instead of the reference's -2^30
+    // so that E survives the 3-bit shift; only differences between sentinel-derived values and the order between those and
+    // real scores (|score| < 2^12) ever matter, and both are unchanged.
+    constexpr int NEG = -(1 << 26);
     const int e_del = opt.e_del, e_ins = opt.e_ins, oe_del = opt.o_del + opt.e_del, oe_ins = opt.o_ins + opt.e_ins;
-    for (int j = 0; j <= lq && j <= w + 1; ++j) ring[j & (BAND_RING - 1)][tid] = make_int2(j == 0 ? 0 : (j <= w ? -(opt.o_ins + e_ins * j) : KSW_MINUS_INF), KSW_MINUS_INF);
+    const uint8_t* qp = v.rev ? v.q + v.qe - 1 : v.q + v.qb;
+    const int qs = v.rev ? -1 : 1;
+    for (int j = 0; j <= lq && j <= w + 1; ++j) {
+        const int qb = j < lq ? qp[j * qs] : 0;
+        ring[j & (BAND_RING - 1)][tid] = make_int2(j == 0 ? 0 : (j <= w ? -(opt.o_ins + e_ins * j) : NEG), (NEG << 3) | qb);
+    }
+    // direction codes: 8 cells per 32-bit word, lane-interleaved: word k of row i of lane t at z32[(i*8 + k)*T] (z32 already offset by t)
     for (int i = 0; i < rlen; ++i) {
         const int tb = v.T(i);
         const int beg = i > w ? i - w : 0, end = i + w + 1 < lq ? i + w + 1 : lq;
-        int f = KSW_MINUS_INF, left = beg == 0 ? -(opt.o_del + e_del * (i + 1)) : KSW_MINUS_INF;
-        unsigned long long acc = 0, *zi = z + (long)i * BAND_ZCHUNK * T;
-        for (int j = beg; j < end; ++j) {
-            const int2 he = ring[j & (BAND_RING - 1)][tid];
-            const int qb = v.Q(j);
-            const int m = he.x + ((qb > 3) ? -1 : (qb == tb ? opt.a : -opt.b));
-            int e = he.y, h, x;
-            unsigned d = m >= e ? 0u : 1u; h = m >= e ? m : e;
-            if (h < f) { d = 2u; h = f; }
-            x = m - oe_del; e -= e_del;
-            if (e > x) d |= 4u; else e = x;
-            ring[j & (BAND_RING - 1)][tid] = make_int2(left, e);
-            left = h;
-            x = m - oe_ins; f -= e_ins;
-            if (f > x) d |= 8u; else f = x;
-            const int ci = j - beg;
-            acc |= (unsigned long long)d << ((ci & 15) << 2);
-            if ((ci & 15) == 15) { zi[(long)(ci >> 4) * T] = acc; acc = 0; }
+        const int qnext = end < lq ? qp[end * qs] : 0;  // base of the column the band reaches in the next row
+        int f = NEG, left = beg == 0 ? -(opt.o_del + e_del * (i + 1)) : NEG;
+        unsigned* zi = z32 + (long)i * (2 * BAND_ZCHUNK) * T;
+        for (int j0 = beg; j0 < end; j0 += 8) {
+            unsigned acc = 0;
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const int j = j0 + u;
+                if (j < end) {
+                    const int2 he = ring[j & (BAND_RING - 1)][tid];
+                    const int qb = he.y & 7;
+                    const int m = he.x + ((qb > 3) ? -1 : (qb == tb ? opt.a : -opt.b));
+                    int e = he.y >> 3, h, x;
+                    unsigned d = m >= e ? 0u : 1u; h = m >= e ? m : e;
+                    if (h < f) { d = 2u; h = f; }
+                    x = m - oe_del; e -= e_del;
+                    if (e > x) d |= 4u; else e = x;
+                    ring[j & (BAND_RING - 1)][tid] = make_int2(left, (e << 3) | qb);
+                    left = h;
+                    x = m - oe_ins; f -= e_ins;
+                    if (f > x) d |= 8u; else f = x;
+                    acc |= d << (4 * u);
+                }
+            }
+            zi[(long)((j0 - beg) >> 3) * T] = acc;
         }
-        if ((end - beg) & 15) zi[(long)((end - beg) >> 4) * T] = acc;
-        ring[end & (BAND_RING - 1)][tid] = make_int2(left, KSW_MINUS_INF);
+        ring[end & (BAND_RING - 1)][tid] = make_int2(left, (NEG << 3) | qnext);
         *cells += end > beg ? end - beg : 0;
     }
     *score = ring[lq & (BAND_RING - 1)][tid].x;
@@ -253,7 +284,7 @@ __device__ __forceinline__ int band_gen_cigar(const MemOpt& opt, const RegView& 
     while (i >= 0 && k >= 0 && ok) {
         const int ci = k - (i > w ? i - w : 0);
         if (ci < 0 || k >= (i + w + 1 < lq ? i + w + 1 : lq)) return -1;  // the path left the band: the reference reads a neighbouring row's byte here
-        const unsigned nib = (unsigned)(z[((long)i * BAND_ZCHUNK + (ci >> 4)) * T] >> ((ci & 15) << 2)) & 15u;
+        const unsigned nib = (z32[((long)i * (2 * BAND_ZCHUNK) + (ci >> 3)) * T] >> ((ci & 7) << 2)) & 15u;
         state = state == 0 ? (int)(nib & 3u) : (state == 1 ? (int)((nib >> 2) & 1u) : (int)((nib >> 3) & 1u) << 1);
         if (state == 0) { ok = push(0, 1); --i; --k; }
         else if (state == 1) { ok = push(2, 1); --i; }
@@ -271,7 +302,7 @@ __global__ void __launch_bounds__(CIG_BLOCK) k_cigar_band(MemOpt opt, RefView re
     int2 (*ring)[CIG_BLOCK] = reinterpret_cast<int2 (*)[CIG_BLOCK]>(ring_raw);
     const unsigned n2 = *A.n2;
     const long T = (long)gridDim.x * blockDim.x;
-    unsigned long long* z = A.z + (blockIdx.x * (long)blockDim.x + threadIdx.x);
+    unsigned* z = reinterpret_cast<unsigned*>(A.z) + (blockIdx.x * (long)blockDim.x + threadIdx.x);
     unsigned long long cells = 0;
     for (unsigned t = blockIdx.x * blockDim.x + threadIdx.x; t < n2; t += gridDim.x * blockDim.x) {
         const long g = A.list2[t];
