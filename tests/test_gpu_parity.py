@@ -200,3 +200,70 @@ def test_place_moves_and_ties(A, R, workdir):
     assert (ocands["mapq"][act] < 60).sum() > 10
     ncomb = np.diff(oc)[0::2] * np.diff(oc)[1::2]
     assert ncomb.max() > 273, "no pair exercises the stateful PRNG path"
+
+
+def _edge_readset(ctg, seed):
+    """Ragged / degenerate reads on top of a simulated set: 1-base reads, reads shorter than min_seed_len, all-N reads,
+    N-rich reads, 250-base reads (the i16 mate-rescue kernel, l_ms >= 250 is never reached at 250 but 249/250 straddle the
+    u8/i16 switch), homopolymers, reads hanging over a contig end, and single-pair barcodes."""
+    g = np.random.default_rng(seed)
+    base = S.simulate_linked_reads(ctg, n_barcodes=12, seed=seed, read_len=250, sub=0.02, ins=0.003, dele=0.003)
+    seqs = [base.read(i).copy() for i in range(2 * base.n_pairs)]
+    ref0 = ctg[0][1]
+    def rc(s):
+        r = s[::-1].copy(); m = r < 4; r[m] = 3 - r[m]; return r
+    for p in range(0, base.n_pairs, 5):
+        kind = (p // 5) % 9
+        i = 2 * p + int(g.integers(0, 2))
+        if kind == 0: seqs[i] = seqs[i][:1]
+        elif kind == 1: seqs[i] = seqs[i][:int(g.integers(2, 19))]
+        elif kind == 2: seqs[i] = np.full(int(g.integers(20, 120)), 4, np.uint8)
+        elif kind == 3:
+            s = seqs[i].copy(); s[g.random(len(s)) < 0.15] = 4; seqs[i] = s
+        elif kind == 4: seqs[i] = np.full(150, int(g.integers(0, 4)), np.uint8)
+        elif kind == 5: seqs[i] = seqs[i][:249]
+        elif kind == 6: seqs[i] = np.concatenate([ref0[-90:], g.integers(0, 4, 60).astype(np.uint8)])      # runs off the contig end
+        elif kind == 7: seqs[i] = rc(np.concatenate([g.integers(0, 4, 40).astype(np.uint8), ref0[:110]]))  # ... and off its start
+        else: seqs[i] = seqs[i][:int(g.integers(19, 40))]
+    off = np.zeros(len(seqs) + 1, np.int64); np.cumsum([len(s) for s in seqs], out=off[1:])
+    bc = list(base.bc_off)
+    extra = sorted(set(int(x) for x in g.integers(1, base.n_pairs, 6)) - set(bc))  # cut a few barcodes into 1..few-pair units
+    bc_off = np.array(sorted(set(bc) | set(extra)), dtype=np.int64)
+    return np.concatenate(seqs).astype(np.uint8), off, bc_off, base.names
+
+
+@pytest.mark.parametrize("name", ["rand1m", "rep600k"])
+def test_edge_inputs_all_stages(A, R, workdir, name):
+    fa, ctg, _ = util.make_dataset(name, workdir)
+    R.load(fa); A.load_index(fa)
+    seq, off, bc_off, names = _edge_readset(ctg, 41)
+    seeds = np.array([A.name_seed(n) for n in names], dtype=np.int64)
+    run_rfa = (np.arange(len(bc_off) - 1) % 3 != 0).astype(np.uint8)
+    res = A.align_batch(seq, off, bc_off, stages=15, run_rfa=run_rfa, rand_seed=seeds)
+    ref = R.batch(seq, off, rescue=True, cigar=True, threads=8)
+    assert np.array_equal(res["reg_off"], ref["reg_off"]) and res["regs"].tobytes() == ref["regs"].tobytes()
+    a, e = res["alns"], ref["aln"]
+    for k, f in enumerate(("pos", "rid", "is_rev", "nm", "n_cigar")):
+        assert np.array_equal(a[f], e[:, k]), f
+    for i in range(len(a)):
+        assert np.array_equal(res["cigar"][a["cigar_off"][i]:a["cigar_off"][i] + a["n_cigar"][i]], ref["cigar"][e[i, 5]:e[i, 5] + e[i, 4]]), i
+    P = util.PlaceOracle(fa)
+    oc, ocands, olmp = P.place(seq, off, bc_off, run_rfa, seeds, ref["reg_off"], ref["regs"], ref["aln"], ref["cigar"])
+    _check_place(res, oc, ocands, olmp, ("edge", name))
+    assert (ocands["reg"] == -1).sum() > 5, "no unmapped placeholders exercised"
+
+
+def test_empty_and_tiny_batches(A, R, workdir):
+    fa, ctg, rs = util.make_dataset("rand1m", workdir)
+    A.load_index(fa); R.load(fa)
+    res = A.align_batch(np.zeros(0, np.uint8), np.zeros(1, np.int64), None, stages=15)
+    assert len(res["reg_off"]) == 1 and len(res["regs"]) == 0
+    one = rs.subset(0, 1)
+    seq, off = one.seq[:one.off[2]], one.off[:3]
+    res = A.align_batch(seq, off, None, stages=15)   # one pair, no barcode table, no seeds
+    ref = R.batch(seq, off, rescue=True, cigar=True, threads=1)
+    assert res["regs"].tobytes() == ref["regs"].tobytes()
+    assert res["cands"]["active"].sum() == 2 and len(res["cand_off"]) == 3
+    from arachne_b200 import ArachneError
+    with pytest.raises(ArachneError):  # reads longer than ARACHNE_MAX_READ_LEN are refused, not truncated
+        A.align_batch(np.zeros(600, np.uint8), np.array([0, 300, 600], np.int64), None, stages=7)
