@@ -140,6 +140,7 @@ __global__ void __launch_bounds__(128) k_chain(MemOpt opt, RefView ref, const in
 // ------------------------------------------------------------------------------------------------ k_extend2
 }  // namespace arachne
 #include "extend_kernel.cuh"
+#include "extend_stage.cuh"
 namespace arachne {
 
 // ------------------------------------------------------------------------------------------------ k_extend (warp per read; kept for the stage entry points)
@@ -337,6 +338,18 @@ __global__ void __launch_bounds__(EXT_WARPS * 32) k_cigar(MemOpt opt, RefView re
 }
 
 // ------------------------------------------------------------------------------------------------ stage kernels
+__global__ void k_dpx_peak(int* out, int iters, int seed) {
+    int a0 = threadIdx.x + seed, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
+    const int d = -(seed | 1), z = blockIdx.x & 7;
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            a0 = __viaddmax_s32(a0, d, z); a1 = __viaddmax_s32(a1, d, z); a2 = __viaddmax_s32(a2, d, z); a3 = __viaddmax_s32(a3, d, z);
+            a4 = __viaddmax_s32(a4, d, z); a5 = __viaddmax_s32(a5, d, z); a6 = __viaddmax_s32(a6, d, z); a7 = __viaddmax_s32(a7, d, z);
+        }
+    }
+    if ((a0 ^ a1 ^ a2 ^ a3 ^ a4 ^ a5 ^ a6 ^ a7) == 0x7fffffff) out[0] = a0;
+}
 __global__ void k_occ(FMIndex fm, long n, const uint64_t* k, const uint64_t* l, uint64_t* cnt) {
     for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x)
         fm_2occ4(fm, k[i], l[i], cnt + 8 * i, cnt + 8 * i + 4);
@@ -576,6 +589,27 @@ int64_t arachne_name_seed(const char* name, int32_t len) {
 #include "batch.inl"
 
 // ---------------------------------------------------------------------------------------------- stage entry points
+// DPX issue peak: a register-resident chain-free stream of VIADDMNMX (the max-plus instruction the DP kernels are built on).
+// 8 independent accumulators per thread, 1024 threads per SM resident.  Returns giga-ops/s (one op = one 32-bit viaddmax).
+int arachne_dpx_peak(int device, double* gops, float* ms_out) {
+    if (!gops) { set_error("arachne_dpx_peak: null argument"); return ARACHNE_ERR_ARG; }
+    if (arachne_device_count() <= device) { set_error("no CUDA device %d (no CPU path)", device); return ARACHNE_ERR_CUDA; }
+    AR_CUDA(cudaSetDevice(device));
+    int* d = nullptr; AR_CUDA(cudaMalloc(&d, 4096));
+    const int iters = 4096, blocks = sm_count(device) * 4, threads = 256;
+    cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    k_dpx_peak<<<blocks, threads>>>(d, iters, 1);
+    cudaEventRecord(e0);
+    for (int r = 0; r < 5; ++r) k_dpx_peak<<<blocks, threads>>>(d, iters, r + 2);
+    cudaEventRecord(e1);
+    AR_CUDA(cudaDeviceSynchronize());
+    float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
+    *gops = 5.0 * (double)blocks * threads * iters * 16 / (ms * 1e-3) / 1e9;
+    if (ms_out) *ms_out = ms / 5;
+    cudaFree(d); cudaEventDestroy(e0); cudaEventDestroy(e1);
+    return ARACHNE_OK;
+}
+
 int arachne_occ_batch(arachne_index_t* idx, int64_t n, const uint64_t* k, const uint64_t* l, uint64_t* cnt) {
     if (!idx || !k || !l || !cnt || n < 0) { set_error("arachne_occ_batch: bad argument"); return ARACHNE_ERR_ARG; }
     AR_CUDA(cudaSetDevice(idx->device));
@@ -671,19 +705,39 @@ int arachne_ksw_extend_batch(int device, const arachne_mem_opt_t* opt_, int64_t 
     AR_CUDA(cudaSetDevice(device));
     DevBuf dq, dqo, dt, dto, dh, dw, dout, dc;
     if (dq.ensure(q_off[n] + 16) || dqo.ensure((n + 1) * 8) || dt.ensure(t_off[n] + 16) || dto.ensure((n + 1) * 8) || dh.ensure(n * 4 + 4) ||
-        dw.ensure(n * 4 + 4) || dout.ensure(n * 24 + 8) || dc.ensure(8)) { set_error("out of device memory"); return ARACHNE_ERR_CUDA; }
+        dw.ensure(n * 4 + 4) || dout.ensure(n * 24 + 8) || dc.ensure(16)) { set_error("out of device memory"); return ARACHNE_ERR_CUDA; }
     AR_CUDA(cudaMemcpy(dq.p, q, q_off[n], cudaMemcpyHostToDevice)); AR_CUDA(cudaMemcpy(dqo.p, q_off, (n + 1) * 8, cudaMemcpyHostToDevice));
     AR_CUDA(cudaMemcpy(dt.p, t, t_off[n], cudaMemcpyHostToDevice)); AR_CUDA(cudaMemcpy(dto.p, t_off, (n + 1) * 8, cudaMemcpyHostToDevice));
     AR_CUDA(cudaMemcpy(dh.p, h0, n * 4, cudaMemcpyHostToDevice)); AR_CUDA(cudaMemcpy(dw.p, w, n * 4, cudaMemcpyHostToDevice));
     cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
     if (repeat < 1) repeat = 1;
-    const int blocks = sm_count(device) * 8;
+    // the lane-per-problem DPX kernel (extend_stage.cuh, same DP core as the pipeline's k_extend2); ARACHNE_KSW_WARP=1 selects the
+    // warp-cooperative kernel instead
+    const bool warp_kernel = getenv("ARACHNE_KSW_WARP") && atoi(getenv("ARACHNE_KSW_WARP")) != 0;
+    int maxq = 1;
+    for (int64_t i = 0; i < n; ++i) maxq = std::max<int>(maxq, (int)(q_off[i + 1] - q_off[i]));
+    const size_t smem = (size_t)(maxq + 1 + EXT_CHUNK) * EXT_BLOCK * sizeof(uint32_t);
+    int per_sm = 1;
+    if (!warp_kernel) {
+        AR_CUDA(cudaFuncSetAttribute(k_ksw_extend_lane, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        AR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_ksw_extend_lane, EXT_BLOCK, smem));
+        if (per_sm < 1) per_sm = 1;
+    }
+    const int blocks = warp_kernel ? sm_count(device) * 8 : sm_count(device) * per_sm;
     // one untimed launch, then `repeat` timed ones
     for (int it = 0; it <= repeat; ++it) {
         if (it == 1) cudaEventRecord(e0);
-        AR_CUDA(cudaMemsetAsync(dc.p, 0, 8));
-        k_ksw_extend<<<blocks, EXT_WARPS * 32>>>(opt, (long)n, dq.as<uint8_t>(), dqo.as<int64_t>(), dt.as<uint8_t>(), dto.as<int64_t>(), dh.as<int>(),
-                                                 dw.as<int>(), end_bonus, zdrop, dout.as<int>(), dc.as<unsigned long long>());
+        AR_CUDA(cudaMemsetAsync(dc.p, 0, 16));
+        if (warp_kernel) {
+            k_ksw_extend<<<blocks, EXT_WARPS * 32>>>(opt, (long)n, dq.as<uint8_t>(), dqo.as<int64_t>(), dt.as<uint8_t>(), dto.as<int64_t>(), dh.as<int>(),
+                                                     dw.as<int>(), end_bonus, zdrop, dout.as<int>(), dc.as<unsigned long long>());
+        } else {
+            KswStageArgs KA;
+            KA.n = (long)n; KA.q = dq.as<uint8_t>(); KA.q_off = dqo.as<int64_t>(); KA.t = dt.as<uint8_t>(); KA.t_off = dto.as<int64_t>();
+            KA.h0 = dh.as<int>(); KA.w = dw.as<int>(); KA.end_bonus = end_bonus; KA.zdrop = zdrop; KA.out = dout.as<int>();
+            KA.cells_out = dc.as<unsigned long long>(); KA.next = dc.as<unsigned>() + 2; KA.maxq = maxq;
+            k_ksw_extend_lane<<<blocks, EXT_BLOCK, smem>>>(opt, KA);
+        }
         AR_CUDA(cudaGetLastError());
     }
     cudaEventRecord(e1);

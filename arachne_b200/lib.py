@@ -99,6 +99,7 @@ class ArachneCuda:
         L.arachne_ksw_global_batch.argtypes = [C.c_int, C.POINTER(MemOpt), C.c_int64, C.POINTER(C.c_uint8), C.POINTER(C.c_int64),
                                                C.POINTER(C.c_uint8), C.POINTER(C.c_int64), C.POINTER(C.c_int32), C.POINTER(C.c_int32),
                                                C.POINTER(C.c_int64), C.POINTER(C.c_uint32), C.c_int64]
+        L.arachne_dpx_peak.argtypes = [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_float)]
         L.arachne_name_seed.restype = C.c_int64; L.arachne_name_seed.argtypes = [C.c_char_p, C.c_int32]
         self.opt = MemOpt()
         self._ck(L.arachne_opts_default(C.byref(self.opt)))
@@ -230,6 +231,12 @@ class ArachneCuda:
                         counters={k: getattr(o, k) for k in COUNTERS}, ms={k: getattr(o, "ms_" + k) for k in STAGE_MS})
         finally:
             self.lib.arachne_batch_free(po)
+
+    def dpx_peak(self, device=None) -> float:
+        """Measured DPX (VIADDMNMX) issue peak in giga-ops/s."""
+        g = C.c_double(0); ms = C.c_float(0)
+        self._ck(self.lib.arachne_dpx_peak(self.device if device is None else device, C.byref(g), C.byref(ms)))
+        return g.value
 
     def name_seed(self, name: str) -> int:
         b = name.encode()

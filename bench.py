@@ -282,8 +282,20 @@ def main():
         seed_ms = acc["seed"] / args.steps
         blocks = acc["n_occ_blocks"] / args.steps
         achieved = blocks * 64 / (seed_ms / 1e3) / 1e9
-        line["roofline"] = {"kernel": "k_seed (FM-index SMEM seeding: bwt_2occ4 block reads)", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                            "frac": achieved / peak, "traffic": None, "peak_source": how,
+        traffic, traffic_note = None, "no ncu capture committed for this workload"
+        tp = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+        if os.path.exists(tp):  # dram bytes of ONE k_seed2 launch from `ncu --set full` on this same command (scripts/gpu_round.sh)
+            tj = json.load(open(tp))
+            if tj.get("pairs_per_step") == args.pairs and tj.get("ref_mb") == args.ref_mb:
+                traffic, traffic_note = tj["dram_bytes_per_launch"], tj.get("note", "")
+        dpx = A.dpx_peak()
+        ext_ops = 3 * acc["n_ext_cells"] / args.steps  # DPX-class ops per in-band cell in k_extend2's SASS: VIMNMX3 + 2 x VIADDMNMX.RELU
+        line["roofline"] = {"kernel": "k_seed2 (FM-index SMEM seeding: bwt_2occ4 block reads)", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                            "frac": achieved / peak, "traffic": traffic, "traffic_note": traffic_note, "peak_source": how,
+                            "extension": {"kernel": "k_extend2 (ksw_extend2)", "bound": "dpx issue", "gcups": acc["n_ext_cells"] / (acc["extend"] / 1e3) / 1e9 if acc["extend"] else None,
+                                          "dpx_ops_per_cell": 3, "achieved_gops": ext_ops / (acc["extend"] / args.steps / 1e3) / 1e9 if acc["extend"] else None,
+                                          "peak_gops": dpx, "frac": (ext_ops / (acc["extend"] / args.steps / 1e3) / 1e9) / dpx if acc["extend"] and dpx else None,
+                                          "peak_source": "measured in this run: independent VIADDMNMX streams (arachne_dpx_peak)"},
                             "algorithmic_bytes_per_launch": blocks * 64, "kernel_ms": seed_ms,
                             "stage_ms_per_step": {k: acc[k] / args.steps for k in ("seed", "sa", "chain", "extend", "rescue", "cigar", "place", "total")},
                             "ext_gcups": acc["n_ext_cells"] / (acc["extend"] / 1e3) / 1e9 if acc["extend"] else None}

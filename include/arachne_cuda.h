@@ -223,6 +223,9 @@ void arachne_batch_free(arachne_batch_out_t *out);
 int arachne_ksw_extend_batch(int device, const arachne_mem_opt_t *opt, int64_t n, const uint8_t *q, const int64_t *q_off, const uint8_t *t,
                              const int64_t *t_off, const int32_t *h0, const int32_t *w, int end_bonus, int zdrop, int32_t *out,
                              uint64_t *cells, float *kernel_ms, int repeat);
+/* Measured DPX issue peak of the device (independent 32-bit VIADDMNMX streams): the denominator of the extension kernel's roofline
+ * (not in MEASURED_PEAKS.json).  gops = 1e9 viaddmax per second. */
+int arachne_dpx_peak(int device, double *gops, float *kernel_ms);
 /* ksw_global2 (bwa/ksw.c:504-606): out scores[n]; cigars as CSR (cigar_off n+1, pool of cap words) when cigar_off != NULL */
 int arachne_ksw_global_batch(int device, const arachne_mem_opt_t *opt, int64_t n, const uint8_t *q, const int64_t *q_off, const uint8_t *t,
                              const int64_t *t_off, const int32_t *w, int32_t *scores, int64_t *cigar_off, uint32_t *cigar, int64_t cigar_cap);
