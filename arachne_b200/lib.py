@@ -45,6 +45,11 @@ class MemOpt(C.Structure):  # arachne_mem_opt_t == mem_opt_t (bwa/bwamem.h:27-66
                 ("max_XA_hits", C.c_int), ("max_XA_hits_alt", C.c_int), ("mat", C.c_int8 * 25)]
 
 
+class IndexBuildInfo(C.Structure):  # arachne_index_build_info_t
+    _fields_ = [(n, C.c_int64) for n in ("seq_len", "primary", "n_batches", "max_batch", "tied_suffixes", "max_rounds", "device_peak_bytes")] + \
+               [(n, C.c_double) for n in ("seconds_read", "seconds_build", "seconds_write")]
+
+
 class BatchIn(C.Structure):
     _fields_ = [("n_pairs", C.c_int64), ("seq", C.POINTER(C.c_uint8)), ("seq_off", C.POINTER(C.c_int64)), ("n_barcodes", C.c_int64),
                 ("barcode_off", C.POINTER(C.c_int64)), ("score_delta", C.c_int32), ("stages", C.c_int32),
@@ -81,6 +86,7 @@ class ArachneCuda:
         L.arachne_last_error.restype = C.c_char_p
         L.arachne_index_load.argtypes = [C.c_char_p, C.c_int, C.POINTER(C.c_void_p)]
         L.arachne_index_free.argtypes = [C.c_void_p]
+        L.arachne_index_build.argtypes = [C.c_char_p, C.c_int, C.c_int64, C.POINTER(IndexBuildInfo)]
         L.arachne_index_l_pac.restype = C.c_int64; L.arachne_index_l_pac.argtypes = [C.c_void_p]
         L.arachne_index_n_seqs.argtypes = [C.c_void_p]
         L.arachne_index_device_bytes.restype = C.c_size_t; L.arachne_index_device_bytes.argtypes = [C.c_void_p]
@@ -112,6 +118,13 @@ class ArachneCuda:
 
     def device_count(self) -> int:
         return self.lib.arachne_device_count()
+
+    # ---- index construction (the BWT/SA half of `bwa index`, bwtindex.c:244-300) ----
+    def build_index(self, prefix: str, device: int = 0, batch_cap: int = 0) -> dict:
+        """<prefix>.pac/.ann -> <prefix>.bwt/.sa on the device, byte-identical to `bwa index`."""
+        info = IndexBuildInfo()
+        self._ck(self.lib.arachne_index_build(prefix.encode(), device, batch_cap, C.byref(info)))
+        return {n: getattr(info, n) for n, _ in IndexBuildInfo._fields_}
 
     # ---- index (GoBwaLoadReference, gobwa.go:128-147) ----
     def load_index(self, prefix: str, device: int = 0):

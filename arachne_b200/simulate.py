@@ -67,6 +67,41 @@ def write_fasta(path: str, contigs, width: int = 60) -> None:
                 f.write(a[n:].tobytes() + b"\n")
 
 
+def write_bns(prefix: str, contigs) -> int:
+    """<prefix>.pac/.ann/.amb exactly as the reference's pack step leaves them after `bwa index`
+    (bns_fasta2bntseq(for_only=1) + bns_dump, bwa/bntseq.c:66-96,275-328) for contigs without N: forward strand, 4 bases
+    per byte with the first base in the top bits, a zero byte when l_pac % 4 == 0, then the byte l_pac % 4; .ann carries
+    seed 11 and "(null)" annotations, .amb no holes.  Skips FASTA text for references too large to round-trip through it."""
+    l_pac = int(sum(len(s) for _, s in contigs))
+    with open(prefix + ".pac", "wb") as f:
+        carry = np.zeros(0, np.uint8)
+        for _, s in contigs:
+            if (s > 3).any():
+                raise ValueError("write_bns: N bases need the reference's own pack step (lrand48 replacement, bntseq.c:261)")
+            a = np.concatenate([carry, s]) if len(carry) else s
+            k = len(a) // 4 * 4
+            q = a[:k].reshape(-1, 4)
+            f.write((q[:, 0] << 6 | q[:, 1] << 4 | q[:, 2] << 2 | q[:, 3]).astype(np.uint8).tobytes())
+            carry = a[k:].copy()
+        if len(carry):
+            v = 0
+            for i, c in enumerate(carry):
+                v |= int(c) << (6 - 2 * i)
+            f.write(bytes([v]))
+        else:
+            f.write(b"\0")
+        f.write(bytes([l_pac % 4]))
+    with open(prefix + ".ann", "w") as f:
+        f.write(f"{l_pac} {len(contigs)} 11\n")
+        off = 0
+        for name, s in contigs:
+            f.write(f"0 {name} (null)\n{off} {len(s)} 0\n")
+            off += len(s)
+    with open(prefix + ".amb", "w") as f:
+        f.write(f"{l_pac} {len(contigs)} 0\n")
+    return l_pac
+
+
 @dataclasses.dataclass
 class ReadSet:
     """Barcode-sorted read pairs. seq is the concatenation of all reads (R1 of pair 0, R2 of pair 0, ...),

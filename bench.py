@@ -37,10 +37,12 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=8)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="arachne_b200", choices=["arachne_b200", "reference"])
-    ap.add_argument("--ref-mb", type=float, default=float(os.environ.get("ARACHNE_BENCH_REF_MB", "32")), help="synthetic reference size, Mbp")
-    ap.add_argument("--pairs", type=int, default=int(os.environ.get("ARACHNE_BENCH_PAIRS", "500000")), help="read pairs per step per GPU")
+    ap.add_argument("--ref-mb", type=float, default=float(os.environ.get("ARACHNE_BENCH_REF_MB", "3100")), help="synthetic reference size, Mbp (configs[1]: 3100)")
+    ap.add_argument("--pairs", type=int, default=int(os.environ.get("ARACHNE_BENCH_PAIRS", "1000000")), help="read pairs per step per GPU")
     ap.add_argument("--batches", type=int, default=2, help="distinct input batches cycled over the steps")
-    ap.add_argument("--cpu-sample", type=int, default=150000, help="pairs in the bounded CPU-baseline sample")
+    ap.add_argument("--cpu-sample", type=int, default=300000, help="pairs in the bounded CPU-baseline sample")
+    ap.add_argument("--index-builder", default="device", choices=["device", "reference"],
+                    help="data preparation: arachne_index_build on the GPU (byte-identical files, tests/test_gpu_parity.py::test_index_build_parity) or the reference's single-threaded `bwa index`")
     ap.add_argument("--workdir", default=os.environ.get("ARACHNE_BENCH_DIR", "/tmp/arachne_bench"))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--plain-barcodes", action="store_true", help="barcodes without the '-1' suffix: worthRunningRFA is false, the optimizer is skipped (what the reference does with haplotagging barcodes as shipped)")
@@ -49,26 +51,41 @@ def parse_args():
 
 # ---------------------------------------------------------------------------------------------- dataset
 def dataset(args, rank: int, world: int, need_index_files: bool = True):
-    """Reference (seed 2, human-like contig proportions) + its index + per-rank read batches (seed 12 + rank)."""
+    """Reference (seed 2, human-like contig proportions) + its index + per-rank read batches (seed 12 + rank).
+    Data preparation, outside every timed region.  Rank 0 writes the index files once per box (a marker file lets the
+    reference arm and the N = 1, 2, 4, 8 runs of one round share them); the other ranks wait on the marker."""
     os.makedirs(args.workdir, exist_ok=True)
     L = int(args.ref_mb * 1e6)
     n_ctg = 24 if L >= 24_000_000 else 1
+    t = time.time()
     ctg = S.make_reference(L, n_ctg, seed=2)
-    fa = os.path.join(args.workdir, f"ref{L}.fa")
-    done = fa + ".done"
+    log(f"rank {rank}: reference of {L} bases generated in {time.time() - t:.1f}s")
+    prefix = os.path.join(args.workdir, f"ref{L}")
+    done = prefix + ".done"
     if rank == 0 and not os.path.exists(done):
         t = time.time()
-        S.write_fasta(fa, ctg)
-        build_index(fa)
+        build_index(prefix, ctg, args)
         open(done, "w").write("ok")
-        log(f"index built in {time.time() - t:.1f}s")
-    return fa, ctg
+        log(f"index files written in {time.time() - t:.1f}s")
+    while not os.path.exists(done):
+        time.sleep(0.5)
+    return prefix, ctg
 
 
-def build_index(fa: str):
-    """Data preparation, not the measured path: `bwa index` as the reference ships it (oracle/_ref), SURVEY.md section 2 #18."""
-    from oracle.refbwa import RefBwa
-    RefBwa().build_index(fa)
+def build_index(prefix: str, ctg, args):
+    """Data preparation, not the measured path.  `device`: the packed reference is written as the reference's pack step
+    writes it (simulate.write_bns, pinned to bns_fasta2bntseq in the CPU tests) and the BWT + sampled SA come from
+    arachne_index_build (bwtindex.c:61-173 + bwt.c:62-84 on the GPU; byte-identical files).  `reference`: FASTA through the
+    reference's own `bwa index` (oracle/_ref), single-threaded -- minutes per 100 Mb, hours at 3.1 Gb."""
+    if args.index_builder == "reference":
+        from oracle.refbwa import RefBwa
+        S.write_fasta(prefix, ctg)
+        RefBwa().build_index(prefix)
+        return
+    from arachne_b200 import ArachneCuda
+    S.write_bns(prefix, ctg)
+    info = ArachneCuda().build_index(prefix, int(os.environ.get("LOCAL_RANK", "0")), 0)
+    log("arachne_index_build: " + json.dumps(info))
 
 
 def make_batches(ctg, args, rank):

@@ -201,6 +201,21 @@ int64_t arachne_index_l_pac(const arachne_index_t *idx);
 int32_t arachne_index_n_seqs(const arachne_index_t *idx);
 int arachne_index_contig(const arachne_index_t *idx, int32_t rid, const char **name, int64_t *offset, int32_t *len);
 size_t arachne_index_device_bytes(const arachne_index_t *idx);
+/* ---- index construction: replaces the BWT/SA half of `bwa index` = bwa_idx_build steps 2, 3 and 5 (bwa/bwtindex.c:244-300:
+ * bwt_pac2bwt :61-123, bwt_bwtupdate_core :151-173, bwt_cal_sa bwa/bwt.c:62-84) on the device.  Reads <prefix>.pac (forward
+ * strand, as bns_fasta2bntseq(for_only=1) leaves it, bwa/bntseq.c:275-328) and <prefix>.ann, writes <prefix>.bwt and
+ * <prefix>.sa byte-identical to the reference's (bwt_dump_bwt / bwt_dump_sa, bwa/bwt.c:385-409).  batch_cap = suffixes
+ * sorted per radix-sort batch (0: 2^28).  info may be NULL. */
+typedef struct {
+    int64_t seq_len, primary;      /* bwt_t.seq_len (= 2 * l_pac), bwt_t.primary */
+    int64_t n_batches, max_batch;  /* suffix-sort batches and the largest one */
+    int64_t tied_suffixes;         /* suffixes still tied after the first 29 bases */
+    int64_t max_rounds;            /* deepest refinement (29 bases per round) any batch needed */
+    int64_t device_peak_bytes;
+    double seconds_read, seconds_build, seconds_write;
+} arachne_index_build_info_t;
+int arachne_index_build(const char *prefix, int device, int64_t batch_cap, arachne_index_build_info_t *info);
+
 /* Run this handle's batches on the caller's CUDA stream (a cudaStream_t; use != 0) or on the handle's own stream (use == 0,
  * the default), so that a caller can bracket batches with its own CUDA events. */
 int arachne_index_set_stream(arachne_index_t *idx, void *cuda_stream, int use);

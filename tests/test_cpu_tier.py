@@ -150,6 +150,38 @@ def test_hostsim_seed_intervals_live(HS, workdir):
 
 
 # ---- C ABI surface ----
+# ---- index construction (csrc/index_build.cuh on the host backend) vs the reference's own `bwa index` output ----
+@pytest.mark.parametrize("name", ["tiny_rand", "tiny_rep"])
+def test_hostsim_index_build_golden(name):
+    """The fixture carries the .pac/.bwt/.sa files the reference's bwa_idx_build wrote: ours must be byte-identical."""
+    d = util.load_golden(name)
+    for cap in (0, 4000):
+        bwt, sa, st = util.hostsim_index_build(d["idx_pac"].tobytes(), int(d["l_pac"]), cap)
+        assert bwt == d["idx_bwt"].tobytes(), (name, cap, "bwt")
+        assert sa == d["idx_sa"].tobytes(), (name, cap, "sa")
+        assert st["n_batches"] >= (1 if cap == 0 else 2)
+
+
+def test_hostsim_index_build_live(tmp_path):
+    """Stress references against oracle/_ref's bwa_idx_build run here; also pins simulate.write_bns to the reference's pack step."""
+    from oracle.refbwa import RefBwa, available
+    if not available():
+        pytest.skip("oracle/_ref not built")
+    deep = 0
+    for name, ctg, cap in util.index_build_cases():
+        fa = str(tmp_path / (name + ".fa"))
+        util.S.write_fasta(fa, ctg)
+        RefBwa().build_index(fa)
+        l_pac = util.S.write_bns(str(tmp_path / (name + ".mine")), ctg)
+        for ext in (".pac", ".ann", ".amb"):
+            assert open(fa + ext, "rb").read() == open(str(tmp_path / (name + ".mine")) + ext, "rb").read(), (name, ext)
+        bwt, sa, st = util.hostsim_index_build(open(fa + ".pac", "rb").read(), l_pac, cap)
+        assert bwt == open(fa + ".bwt", "rb").read(), (name, "bwt")
+        assert sa == open(fa + ".sa", "rb").read(), (name, "sa")
+        deep = max(deep, st["rounds"])
+    assert deep >= 10  # the homopolymer / tandem cases really went through many refinement rounds
+
+
 def test_abi_exports_every_declared_symbol():
     from arachne_b200.lib import lib_path
     assert os.path.exists(lib_path()), "libarachne_cuda.so missing: run __graft_entry__.build()"

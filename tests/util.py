@@ -283,3 +283,44 @@ def exact_repeat_reference(total_len=300_000, n_contigs=4, seed=9, families=6, c
             cj = int(g.integers(0, len(ctg))); t = ctg[cj][1]
             b = int(g.integers(0, len(t) - rep_len)); t[b:b + rep_len] = seg
     return ctg
+
+
+# ------------------------------------------------------------------------------------------------ index construction
+def bwt_payload_words(n):
+    return (n + 15) // 16 + ((n + 127) // 128 + 1) * 8
+
+
+def hostsim_index_build(pac_bytes, l_pac, batch_cap=0):
+    """The product's index-construction driver (csrc/index_build.cuh) on the TEST-ONLY host backend -> the bytes of
+    <prefix>.bwt and <prefix>.sa as bwt_dump_bwt / bwt_dump_sa lay them out (bwa/bwt.c:385-409) + driver statistics."""
+    HostSim()  # builds libhostsim.so
+    H = C.CDLL(os.path.join(ROOT, "tests", "hostsim", "libhostsim.so"))
+    H.hostsim_index_build.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]
+    n = 2 * l_pac
+    buf = np.zeros(l_pac // 4 + 16, np.uint8)
+    k = min(len(pac_bytes), l_pac // 4 + 1)
+    buf[:k] = np.frombuffer(bytes(pac_bytes[:k]), np.uint8)
+    out = np.zeros(bwt_payload_words(n), np.uint32); sa = np.zeros((n + 32) // 32, np.uint64); meta = np.zeros(8, np.uint64)
+    rc = H.hostsim_index_build(buf.ctypes.data, l_pac, batch_cap, out.ctypes.data, sa.ctypes.data, meta.ctypes.data)
+    assert rc == 0
+    bwt = meta[:5].tobytes() + out.tobytes()
+    saf = meta[:5].tobytes() + np.array([32, n], np.uint64).tobytes() + sa[1:].tobytes()
+    return bwt, saf, dict(n_batches=int(meta[5]), tied=int(meta[6]), rounds=int(meta[7]))
+
+
+def index_build_cases():
+    """(name, contigs, batch_cap): references that stress the suffix sorter -- iid text, batches forced small, diverged and
+    exact repeats, homopolymer runs (deep tie refinement, the '$'-is-smallest rule at the text end), tandem repeats,
+    lengths around every packing boundary (4 / 16 / 32 / 128 bases), single-letter texts."""
+    g = np.random.default_rng(5)
+    cases = [("rand10k", S.make_reference(10007, 1, seed=1), 0), ("rand10k-cap500", S.make_reference(10007, 1, seed=1), 500),
+             ("rep60k", S.make_reference(60000, 1, seed=2, repeat_frac=0.3), 3000), ("multi100k", S.make_reference(100000, 3, seed=3), 0),
+             ("exactrep", exact_repeat_reference(120_000, 2, 9, 3, 8, 700), 20000)]
+    s = g.integers(0, 4, 5000, dtype=np.uint8); s[1000:1400] = 0; s[-50:] = 0; s[:37] = 3
+    cases.append(("polyA", [("c", s)], 0))
+    cases.append(("tandem", [("c", np.tile(g.integers(0, 4, 7, dtype=np.uint8), 300))], 0))
+    for L in (1, 2, 3, 4, 5, 15, 16, 17, 31, 32, 33, 63, 64, 65, 127, 128, 129, 255, 256, 257):
+        cases.append((f"L{L}", [("c", g.integers(0, 4, L, dtype=np.uint8))], 0))
+    cases.append(("allA", [("c", np.zeros(300, np.uint8))], 0))
+    cases.append(("allT", [("c", np.full(300, 3, np.uint8))], 0))
+    return cases
