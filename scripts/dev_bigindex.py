@@ -16,6 +16,7 @@ p = os.path.join(wd, f"ref{L}")
 t = time.time(); S.write_bns(p, ctg); print("write_bns %.1fs" % (time.time() - t), flush=True)
 A = ArachneCuda()
 t = time.time(); info = A.build_index(p, 0, 0); print("build_index %.1fs" % (time.time() - t), json.dumps(info), flush=True)
+open(p + ".done", "w").write("ok")
 t = time.time(); A.load_index(p); print("load_index %.1fs, device bytes %d" % (time.time() - t, A.lib.arachne_index_device_bytes(A.idx)), flush=True)
 rs = S.simulate_pairs_fast(ctg, npairs, seed=12)
 t = time.time(); res = A.align_batch(rs.seq, rs.off, rs.bc_off, stages=7); print("gpu batch %.2fs" % (time.time() - t), flush=True)
