@@ -144,6 +144,15 @@ __global__ void __launch_bounds__(EXT_BLOCK, 5) k_extend2(MemOpt opt, RefView re
                     else rmax0 = l_pac;
                 }
                 fetch_window(ref, &rmax0, seeds[0].rbeg, &rmax1);
+                {   // the chain's reference window (~100 bytes of .pac) is read 16 bases at a time, one dependent load per 16
+                    // rows; on an HBM-resident reference each would be a DRAM round trip: pull its lines into L2 now
+                    int64_t b = rmax0, e = rmax1 - 1;
+                    if (b >= l_pac) { const int64_t t = (l_pac << 1) - 1 - e; e = (l_pac << 1) - 1 - b; b = t; }
+                    if (e >= b) {
+                        const uintptr_t p0 = (uintptr_t)(ref.pac + (b >> 2)) & ~(uintptr_t)127, p1 = (uintptr_t)(ref.pac + (e >> 2));
+                        for (uintptr_t p = p0; p <= p1; p += 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+                    }
+                }
                 for (int x = 0; x < cn; ++x) srt[x] = (uint64_t)seeds[x].score << 32 | (uint32_t)x;
                 ks_introsort((size_t)cn, srt, [](uint64_t a, uint64_t b) { return a < b; });
                 k = cn - 1;

@@ -71,28 +71,45 @@ __global__ void k_expand(MemOpt opt, int n_reads, const Intv* __restrict__ arena
 }
 
 // bwt_sa for every SA row of the batch.  Walk lengths are geometric (rows, not text positions, are sampled), so lanes
-// are persistent: a lane that reaches a sampled row stores its result and pulls the next row from the queue, and every
-// loop iteration is one LF step (one 32-byte sector) for every live lane.
+// are persistent: a lane that reaches a sampled row stores its result and takes the next row, and every loop iteration
+// is one LF step (one 32-byte sector) for every live lane.  Rows are claimed from the global queue a warp-chunk at a
+// time (one atomic per SA_CLAIM rows) and dealt to idle lanes by ballot rank: a per-lane atomic on the single queue
+// counter serialises in L2 and was the kernel's bound on the 3.1 Gb index (15 M same-address atomics per 1 M pairs).
+constexpr unsigned SA_CLAIM = 128;
 __global__ void __launch_bounds__(256) k_sa(FMIndex fm, unsigned long long n, uint64_t* rows, unsigned long long* next, Counters* cnt) {
     const uint64_t mask = (uint64_t)fm.sa_intv - 1;
+    const unsigned lane = threadIdx.x & 31;
     unsigned long long steps = 0, idx = 0;
+    unsigned long long wbase = 0, wend = 0;  // warp-uniform: the claimed rows not yet dealt
+    bool exhausted = false;                  // warp-uniform: the queue is empty
     uint64_t k = 0, sa = 0;
-    bool live = false, done = false;
+    bool live = false;
     for (;;) {
-        if (!live && !done) {
-            idx = atomicAdd(next, 1ull);
-            if (idx >= n) done = true;
-            else { k = rows[idx]; sa = 0; live = true; }
+        const unsigned idle = __ballot_sync(FULL, !live);
+        if (idle && !exhausted) {
+            if (wbase == wend) {
+                unsigned long long b = 0;
+                if (lane == 0) b = atomicAdd(next, (unsigned long long)SA_CLAIM);
+                b = __shfl_sync(FULL, b, 0);
+                if (b >= n) exhausted = true;
+                else { wbase = b; wend = b + SA_CLAIM < n ? b + SA_CLAIM : n; }
+            }
+            if (!exhausted) {
+                const unsigned rank = __popc(idle & ((1u << lane) - 1u));
+                const unsigned long long avail = wend - wbase;
+                if (!live && rank < avail) { idx = wbase + rank; k = rows[idx]; sa = 0; live = true; }
+                const unsigned want = __popc(idle);
+                wbase += want < avail ? want : avail;
+            }
         }
-        __syncwarp();
         if (live) {
             if (k & mask) { ++sa; k = fm_inv_psi(fm, k); }
             else { rows[idx] = sa + fm.sa[k / fm.sa_intv]; steps += sa; live = false; }
         }
-        if (__all_sync(FULL, done)) break;
+        if (exhausted && __ballot_sync(FULL, live) == 0) break;
     }
     steps = __reduce_add_sync(FULL, (unsigned)steps);  // per-thread totals stay far below 2^32 / 32
-    if ((threadIdx.x & 31) == 0 && steps) atomicAdd(&cnt->lf_steps, steps);
+    if (lane == 0 && steps) atomicAdd(&cnt->lf_steps, steps);
 }
 
 // ------------------------------------------------------------------------------------------------ k_chain

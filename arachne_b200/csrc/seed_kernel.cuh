@@ -8,7 +8,8 @@
 //
 //   * work item = (read, kind): kind 0 = passes 1+2 (SMEMs, re-seeding), kind 1 = pass 3 (bwt_seed_strategy1); the
 //     three passes only meet in the final sort by `info`, and equal info means an identical interval, so the order in
-//     which they emit is not observable.  Lanes are persistent and pull the next item from a global counter.
+//     which they emit is not observable.  Lanes are persistent and pull the next item from a global counter per kind
+//     (next[0], next[1]); a warp stays on one kind while its queue lasts.
 //   * interval lists: bwt_smem1a's prev/curr swap is an in-place compaction (curr never outruns prev), so one list per
 //     lane suffices; entries are packed to 16 bytes (x0,x1,x2 40 bits each + the 8-bit query end) and stored
 //     row-interleaved across lanes (entry j of every lane of a warp is one 512-byte line).
@@ -45,7 +46,8 @@ __global__ void __launch_bounds__(256, 3) k_seed2(FMIndex fm, MemOpt opt, const 
     uint4* list = lists + tid;                       // entry j at list[j * T]
     uint4* recs = lists + (size_t)(rows >> 1) * T + tid;  // re-seed records in the upper half
     const int split_len = (int)(opt.min_seed_len * opt.split_factor + .499f);
-    const unsigned n_tasks = 2u * (unsigned)n_reads;
+    // task kinds cost about 2:1 in bwt_extend calls (passes 1+2 vs pass 3): every third warp starts on the LAST-like queue
+    const int pref_kind = (opt.max_mem_intv > 0 && (tid >> 5) % 3 == 2) ? 1 : 0;
 
     int phase = SP_IDLE, r = 0, len = 0, x = 0, i = 0, pass = 1;
     const uint8_t* q = seq;
@@ -76,15 +78,22 @@ __global__ void __launch_bounds__(256, 3) k_seed2(FMIndex fm, MemOpt opt, const 
         do {
             if (phase == SP_DONE) break;
             if (phase == SP_IDLE) {
-                unsigned t = atomicAdd(next, 1u);
-                if (t >= n_tasks) { phase = SP_DONE; break; }
-                r = (int)(t >> 1);
+                // one queue per task kind; a warp keeps to its own kind until that queue is empty, so its lanes walk the
+                // same automaton states (a warp mixing SMEM and LAST-like tasks pays for both code paths every trip)
+                int kind = pref_kind;
+                unsigned t = atomicAdd(next + kind, 1u);
+                if (t >= (unsigned)n_reads) {
+                    kind ^= 1;
+                    t = atomicAdd(next + kind, 1u);
+                    if (t >= (unsigned)n_reads) { phase = SP_DONE; break; }
+                }
+                r = (int)t;
                 len = (int)(off[r + 1] - off[r]);
                 q = seq + off[r];
-                if (len > maxlen) { if ((t & 1) == 0) raise(cnt, ARACHNE_ERR_ARG, r); break; }
+                if (len > maxlen) { if (kind == 0) raise(cnt, ARACHNE_ERR_ARG, r); break; }
                 if (len < opt.min_seed_len) break;
                 x = 0; pass = 1; n_rec = 0; rec_i = 0;
-                phase = (t & 1) ? ((opt.max_mem_intv > 0) ? SP_P3_SCAN : SP_IDLE) : SP_P1_SCAN;
+                phase = kind ? ((opt.max_mem_intv > 0) ? SP_P3_SCAN : SP_IDLE) : SP_P1_SCAN;
                 if (phase == SP_IDLE) break;
             }
             if (phase == SP_P2_NEXT) {
