@@ -15,8 +15,10 @@
 namespace arachne {
 
 AR_HD int cal_max_gap(const MemOpt& opt, int qlen) {
-    int l_del = (int)((double)(qlen * opt.a - opt.o_del) / opt.e_del + 1.);
-    int l_ins = (int)((double)(qlen * opt.a - opt.o_ins) / opt.e_ins + 1.);
+    // bwamem.c:621-628 computes (int)((double)x / e + 1.); (x + e) / e in C integer division truncates the same real number
+    // toward zero (no FP64 on the device path)
+    int l_del = (qlen * opt.a - opt.o_del + opt.e_del) / opt.e_del;
+    int l_ins = (qlen * opt.a - opt.o_ins + opt.e_ins) / opt.e_ins;
     int l = l_del > l_ins ? l_del : l_ins;
     l = l > 1 ? l : 1;
     return l < opt.w << 1 ? l : opt.w << 1;

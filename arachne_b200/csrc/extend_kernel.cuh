@@ -62,7 +62,7 @@ struct ThreadCtx {
     }
 };
 
-enum { XS_FETCH = 0, XS_CHAIN, XS_SEED, XS_SETUP, XS_ROWSTART, XS_CELLS, XS_ROWEND, XS_POST, XS_REGION, XS_FINISH, XS_DONE };
+enum { XS_FETCH = 0, XS_CHAIN, XS_SEED, XS_SETUP, XS_INIT, XS_ROWSTART, XS_CELLS, XS_ROWEND, XS_POST, XS_REGION, XS_FINISH, XS_DONE };
 
 struct ExtArgs {
     const uint8_t* seq; const int64_t* off; int n_reads;
@@ -105,10 +105,11 @@ __global__ void __launch_bounds__(EXT_BLOCK, 5) k_extend2(MemOpt opt, RefView re
     int64_t tfp = 0, tw_idx = -1; int tfstep = 1; bool tcomp = false; uint32_t tw = 0;
     unsigned long long cells = 0, calls = 0;
     int err = 0;
+    const uint8_t* iq = A.seq; int iqs = 1;  // first-row fill request (XS_INIT): query pointer and stride of this ksw_extend2 call
 
     for (;;) {
         // ------------------------------------------------------------ divergent driver: advance until this lane has cells to compute
-        while (st != XS_DONE && !(st == XS_CELLS && j < end)) {
+        while (st != XS_DONE && st != XS_INIT && !(st == XS_CELLS && j < end)) {
             switch (st) {
             case XS_FETCH: {
                 unsigned t = atomicAdd(A.next, 1u);
@@ -144,15 +145,6 @@ __global__ void __launch_bounds__(EXT_BLOCK, 5) k_extend2(MemOpt opt, RefView re
                     else rmax0 = l_pac;
                 }
                 fetch_window(ref, &rmax0, seeds[0].rbeg, &rmax1);
-                {   // the chain's reference window (~100 bytes of .pac) is read 16 bases at a time, one dependent load per 16
-                    // rows; on an HBM-resident reference each would be a DRAM round trip: pull its lines into L2 now
-                    int64_t b = rmax0, e = rmax1 - 1;
-                    if (b >= l_pac) { const int64_t t = (l_pac << 1) - 1 - e; e = (l_pac << 1) - 1 - b; b = t; }
-                    if (e >= b) {
-                        const uintptr_t p0 = (uintptr_t)(ref.pac + (b >> 2)) & ~(uintptr_t)127, p1 = (uintptr_t)(ref.pac + (e >> 2));
-                        for (uintptr_t p = p0; p <= p1; p += 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
-                    }
-                }
                 for (int x = 0; x < cn; ++x) srt[x] = (uint64_t)seeds[x].score << 32 | (uint32_t)x;
                 ks_introsort((size_t)cn, srt, [](uint64_t a, uint64_t b) { return a < b; });
                 k = cn - 1;
@@ -214,21 +206,16 @@ __global__ void __launch_bounds__(EXT_BLOCK, 5) k_extend2(MemOpt opt, RefView re
                     tfstep = tcomp ? -tstep : tstep;
                     tw_idx = -1;
                 }
-                int hv = h0;
-                for (int x = 0; x <= qlen; ++x) {
-                    if (x == 1) hv = h0 > oe_ins ? h0 - oe_ins : 0;
-                    else if (x > 1) hv = hv > e_ins ? hv - e_ins : 0;
-                    uint32_t qb = x < qlen ? (uint32_t)__ldg(q + (long)x * qs) : 0u;
-                    COL(x) = (uint32_t)hv | qb << 26;
-                }
+                iq = q; iqs = qs;  // the first row itself (ksw.c:395-397) is filled by the whole warp below
                 int top = sa > snb ? sa : snb; top = top > -1 ? top : -1;
-                int lim = (int)((double)(qlen * top + end_bonus - opt.o_ins) / e_ins + 1.);
+                // (int)((double)x / e + 1.) == (x + e) / e in C integer division (both truncate the same real number toward zero)
+                int lim = (qlen * top + end_bonus - opt.o_ins + e_ins) / e_ins;
                 lim = lim > 1 ? lim : 1; w = w < lim ? w : lim;
-                lim = (int)((double)(qlen * top + end_bonus - opt.o_del) / e_del + 1.);
+                lim = (qlen * top + end_bonus - opt.o_del + e_del) / e_del;
                 lim = lim > 1 ? lim : 1; w = w < lim ? w : lim;
                 mx = h0; max_i = max_j = max_ie = -1; gscore = -1; max_off = 0;
                 beg = 0; end = qlen; i = 0;
-                st = XS_ROWSTART;
+                st = XS_INIT;
             } break;
             case XS_ROWSTART: {
                 if (i >= tlen) { st = XS_POST; break; }
@@ -321,6 +308,29 @@ __global__ void __launch_bounds__(EXT_BLOCK, 5) k_extend2(MemOpt opt, RefView re
             }
         }
         __syncwarp();
+        // ------------------------------------------------------------ convergent: first rows (ksw.c:395-397) of the lanes that asked for one
+        // A lane filling its own qlen+1 columns runs a ~10-instruction loop body 100+ times alone (15 % of the kernel's warp
+        // instructions at 1.1 active lanes); here the warp fills them together, 32 columns per trip: h(0) = h0,
+        // h(x) = max(h0 - o_ins - x*e_ins, 0), e = 0, query base in the top bits.
+        {
+            unsigned want = __ballot_sync(0xffffffffu, st == XS_INIT);
+            const int lane = tix & 31;
+            while (want) {
+                const int src = __ffs(want) - 1;
+                want &= want - 1;
+                const uint8_t* bq = reinterpret_cast<const uint8_t*>(__shfl_sync(0xffffffffu, (unsigned long long)iq, src));
+                const int bqs = __shfl_sync(0xffffffffu, iqs, src), bqlen = __shfl_sync(0xffffffffu, qlen, src), bh0 = __shfl_sync(0xffffffffu, h0, src);
+                uint32_t* bcol = cols + (tix & ~31) + src;
+                for (int x = lane; x <= bqlen; x += 32) {
+                    int hv = bh0 - opt.o_ins - x * e_ins;
+                    hv = x == 0 ? bh0 : (hv > 0 ? hv : 0);
+                    const uint32_t qb = x < bqlen ? (uint32_t)__ldg(bq + (long)x * bqs) : 0u;
+                    bcol[x * EXT_BLOCK] = (uint32_t)hv | qb << 26;
+                }
+            }
+            __syncwarp();
+            if (st == XS_INIT) st = XS_ROWSTART;
+        }
         // ------------------------------------------------------------ convergent: up to EXT_CHUNK cells of the current row (ksw.c:424-448)
         // Straight-line: the chunk's column words are loaded up front (the column array is padded by EXT_CHUNK words, so
         // reading past `end` is harmless), every cell is computed, and cells at or beyond `end` are simply not committed.

@@ -6,6 +6,7 @@
 #include <string>
 #include <vector>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include "fmindex.cuh"
@@ -46,6 +47,25 @@ namespace arachne {
             return ARACHNE_ERR_CUDA;                                                       \
         }                                                                                  \
     } while (0)
+
+// HBM-resident SA at a denser sampling than the file's (bwtindex.c:309 samples every 32nd row; 180 GB of HBM hold every
+// row of a 3.1 Gb index in 50 GB): bwt_sa (bwt.c:86-96) then needs (d-1)/2 LF steps on average instead of 15.5 -- none at
+// d = 1 -- and returns the same integers.  The rows between two file samples form one LF chain (bwt_cal_sa, bwt.c:62-84,
+// walks them in this order), so one lane per file sample fills its chain: seq_len LF steps in total.
+__global__ void __launch_bounds__(256) k_sa_densify(FMIndex fm, uint64_t* dense, int d) {
+    const uint64_t n_file = fm.n_sa, mask = (uint64_t)fm.sa_intv - 1, dmask = (uint64_t)d - 1;
+    for (uint64_t j = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; j < n_file; j += (uint64_t)gridDim.x * blockDim.x) {
+        uint64_t k = j * (uint64_t)fm.sa_intv;
+        uint64_t v = j == 0 ? fm.seq_len : fm.sa[j];  // row 0 is the empty suffix; its stored value stays the reference's -1 (bwt.c:83)
+        if ((k & dmask) == 0) dense[k / d] = j == 0 ? (uint64_t)-1 : v;
+        for (;;) {
+            k = fm_inv_psi(fm, k);
+            if ((k & mask) == 0) break;
+            --v;
+            if ((k & dmask) == 0) dense[k / d] = v;
+        }
+    }
+}
 
 inline bool read_file(const std::string& path, std::vector<uint8_t>& out) {
     FILE* fp = fopen(path.c_str(), "rb");
@@ -155,6 +175,36 @@ inline int index_load(const char* prefix_, int device, arachne_index** out) {
     idx->ref.l_pac = idx->l_pac;
     idx->ref.n_seqs = (int)idx->contigs.size();
     idx->device_bytes = img + sab + pacb + sizeof(Contig) * idx->contigs.size();
+    {   // densify the sampled SA when HBM has the room (ARACHNE_SA_INTV=1|2|4|8|16|32 overrides; 32 keeps the file's sampling)
+        int d = 0;
+        if (const char* ev = getenv("ARACHNE_SA_INTV")) d = atoi(ev);
+        size_t free_b = 0, total_b = 0;
+        cudaMemGetInfo(&free_b, &total_b);
+        if (d <= 0 || (d & (d - 1)) || d > fm.sa_intv)
+            for (d = 1; d < fm.sa_intv && ((fm.seq_len + d) / d) * 8 > free_b * 2 / 5; d <<= 1) {}
+        if (d < fm.sa_intv) {
+            const uint64_t n_dense = (fm.seq_len + d) / d;
+            void* dd = nullptr;
+            e = cudaMalloc(&dd, n_dense * 8);
+            if (e == cudaSuccess) {
+                cudaDeviceProp prop;
+                int sms = cudaGetDeviceProperties(&prop, device) == cudaSuccess ? prop.multiProcessorCount : 148;
+                k_sa_densify<<<sms * 8, 256>>>(fm, reinterpret_cast<uint64_t*>(dd), d);
+                e = cudaGetLastError();
+                if (e == cudaSuccess) e = cudaDeviceSynchronize();
+            }
+            if (e == cudaSuccess) {
+                cudaFree(idx->d_sa);
+                idx->d_sa = dd;
+                fm.sa = reinterpret_cast<const uint64_t*>(dd);
+                fm.sa_intv = d; fm.n_sa = n_dense;
+                idx->device_bytes += n_dense * 8 - sab;
+            } else {  // keep the file's sampling: slower, same answers
+                if (dd) cudaFree(dd);
+                (void)cudaGetLastError();
+            }
+        }
+    }
     idx->h_pac.assign(pac.begin(), pac.begin() + pacb);
     *out = idx;
     return ARACHNE_OK;
