@@ -11,6 +11,15 @@ static Workspace* get_ws(arachne_index_t* idx) {
     return reinterpret_cast<Workspace*>(idx->ws);
 }
 
+int arachne_index_set_option(arachne_index_t* idx, const char* name, int64_t value) {
+    if (!idx || !name) { set_error("arachne_index_set_option: null argument"); return ARACHNE_ERR_ARG; }
+    std::lock_guard<std::mutex> lk(idx->mu);
+    if (!strcmp(name, "seed_kmer")) idx->opt_seed_kmer = value != 0;
+    else if (!strcmp(name, "seed_blocks_per_sm") && (value == 3 || value == 4)) idx->opt_seed_blocks = (int)value;
+    else { set_error("arachne_index_set_option: unknown option or value: %s=%lld", name, (long long)value); return ARACHNE_ERR_ARG; }
+    return ARACHNE_OK;
+}
+
 int arachne_index_set_stream(arachne_index_t* idx, void* cuda_stream, int use) {
     if (!idx) { set_error("arachne_index_set_stream: null index"); return ARACHNE_ERR_ARG; }
     std::lock_guard<std::mutex> g(idx->mu);
@@ -96,7 +105,7 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
     unsigned long long* hs = W.h_scalars;
     // ---- seeding (retry with a larger per-read interval capacity if a read overflows it) ----
     if (idx->fm.seq_len >= (1ull << 40) - 2) { set_error("reference too long for the packed interval lists (2*l_pac must stay below 2^40)"); return fail(ARACHNE_ERR_ARG); }
-    const int seed_blocks = sms * 3, seed_T = seed_blocks * 256, list_rows = 2 * L1;
+    const int seed_bpsm = idx->opt_seed_blocks == 4 ? 4 : 3, seed_blocks = sms * seed_bpsm, seed_T = seed_blocks * 256, list_rows = 2 * L1;
     AR_ALLOC(W.d_scratch, (size_t)seed_T * list_rows * sizeof(uint4));
     int intv_cap = 32;
     cudaEventRecord(ev[0], st);
@@ -107,8 +116,12 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
         AR_TRY(cudaMemsetAsync(W.d_nsa.p, 0, (n_reads + 1) * 4, st));
         SeedOut so; so.intv = W.d_arena.as<Intv>(); so.intv_n = W.d_intv_n.as<int>(); so.n_sa = W.d_nsa.as<unsigned int>(); so.cap = intv_cap;
         ++nl;
-        k_seed2<<<seed_blocks, 256, 0, st>>>(idx->fm, opt, d_seq, d_off, (int)n_reads, maxlen, W.d_scratch.as<uint4>(), list_rows, so,
-                                              W.d_misc.as<unsigned int>(), W.d_cnt.as<Counters>());
+        if (seed_bpsm == 4)
+            k_seed2<4><<<seed_blocks, 256, 0, st>>>(idx->fm, opt, d_seq, d_off, (int)n_reads, maxlen, W.d_scratch.as<uint4>(), list_rows, so,
+                                                     W.d_misc.as<unsigned int>(), W.d_cnt.as<Counters>(), idx->opt_seed_kmer);
+        else
+            k_seed2<3><<<seed_blocks, 256, 0, st>>>(idx->fm, opt, d_seq, d_off, (int)n_reads, maxlen, W.d_scratch.as<uint4>(), list_rows, so,
+                                                     W.d_misc.as<unsigned int>(), W.d_cnt.as<Counters>(), idx->opt_seed_kmer);
         AR_TRY(cudaGetLastError());
         AR_TRY(cudaMemcpyAsync(&hc, W.d_cnt.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
         AR_TRY(cudaStreamSynchronize(st));
@@ -167,7 +180,9 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
     AR_TRY(cudaMemsetAsync(W.d_misc.p, 0, 64, st));
     ++nl;
     {
-        const size_t smem = (size_t)(maxlen + 1 + EXT_CHUNK) * EXT_BLOCK * sizeof(uint32_t);
+        // columns 0..qlen plus the chunk's read-ahead; qlen <= len - min_seed_len (every seed is at least that long)
+        const int ncols = std::max(1, maxlen - opt.min_seed_len) + EXT_CHUNK;
+        const size_t smem = (size_t)ncols * EXT_BLOCK * sizeof(uint32_t);
         if (smem > 200 * 1024) { set_error("read length %d does not fit the extension kernel's shared-memory columns", maxlen); return fail(ARACHNE_ERR_ARG); }
         AR_TRY(cudaFuncSetAttribute(k_extend2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         int per_sm = 0;
@@ -180,7 +195,7 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
         ExtArgs xa;
         xa.seq = d_seq; xa.off = d_off; xa.n_reads = (int)n_reads; xa.sa_off = W.d_sa_off.as<unsigned long long>(); xa.b = cb;
         xa.srt = W.d_srt.as<uint64_t>(); xa.regs = W.d_regs.as<AlnReg>(); xa.n_regs = W.d_nregs.as<int>();
-        xa.hscr = W.d_hscr.as<int>(); xa.rscr = W.d_rscr.as<uint8_t>(); xa.rcap = win_cap; xa.maxlen = maxlen;
+        xa.hscr = W.d_hscr.as<int>(); xa.rscr = W.d_rscr.as<uint8_t>(); xa.rcap = win_cap; xa.maxlen = maxlen; xa.ncols = ncols;
         xa.next = W.d_misc.as<unsigned int>(); xa.cnt = W.d_cnt.as<Counters>();
         k_extend2<<<xblocks, EXT_BLOCK, smem, st>>>(opt, idx->ref, xa);
     }

@@ -70,11 +70,12 @@ struct ExtArgs {
     ChainBufs b;
     uint64_t* srt; AlnReg* regs; int* n_regs;
     int* hscr; uint8_t* rscr; int rcap; int maxlen;
+    int ncols;  // shared-memory column words per lane: (maxlen - min_seed_len) + EXT_CHUNK, a flank is never longer than len - seed
     unsigned int* next; Counters* cnt;
 };
 
-__global__ void __launch_bounds__(EXT_BLOCK, 5) k_extend2(MemOpt opt, RefView ref, ExtArgs A) {
-    extern __shared__ uint32_t cols[];  // [(maxlen+1+EXT_CHUNK)][EXT_BLOCK]
+__global__ void __launch_bounds__(EXT_BLOCK, 6) k_extend2(MemOpt opt, RefView ref, ExtArgs A) {
+    extern __shared__ uint32_t cols[];  // [ncols][EXT_BLOCK]
     const int tix = threadIdx.x;
     const long gtid = (long)blockIdx.x * blockDim.x + tix;
     uint32_t* col = cols + tix;
@@ -105,6 +106,7 @@ __global__ void __launch_bounds__(EXT_BLOCK, 5) k_extend2(MemOpt opt, RefView re
     int64_t tfp = 0, tw_idx = -1; int tfstep = 1; bool tcomp = false; uint32_t tw = 0;
     unsigned long long cells = 0, calls = 0;
     int err = 0;
+    int firstnz = 0x7fffffff, lastnz = -1;  // first / last column of the current row whose stored (h, e) is non-zero
     const uint8_t* iq = A.seq; int iqs = 1;  // first-row fill request (XS_INIT): query pointer and stride of this ksw_extend2 call
 
     for (;;) {
@@ -199,6 +201,7 @@ __global__ void __launch_bounds__(EXT_BLOCK, 5) k_extend2(MemOpt opt, RefView re
                     qlen = len - qe; tlen = (int)(rmax1 - (s_rbeg + s_len)); w = opt.w << tr; aw1 = w; end_bonus = opt.pen_clip3; h0 = sc0;
                     tpos = s_rbeg + s_len; tstep = 1; q = query + qe; qs = 1;
                 }
+                if (qlen + EXT_CHUNK > A.ncols) { err = -3; st = XS_FINISH; break; }  // cannot happen with seeds >= min_seed_len
                 ++calls;
                 {   // forward-strand coordinate of row 0 and its step: the window never crosses l_pac (fetch_window)
                     tcomp = tpos >= ref.l_pac;
@@ -231,6 +234,7 @@ __global__ void __launch_bounds__(EXT_BLOCK, 5) k_extend2(MemOpt opt, RefView re
                 h1 = 0;
                 if (beg == 0) { h1 = h0 - (opt.o_del + e_del * (i + 1)); if (h1 < 0) h1 = 0; }
                 f = 0; m = 0; mj = -1; j = beg;
+                firstnz = 0x7fffffff; lastnz = -1;
                 cells += end > beg ? end - beg : 0;
                 st = XS_CELLS;
             } break;
@@ -252,10 +256,10 @@ __global__ void __launch_bounds__(EXT_BLOCK, 5) k_extend2(MemOpt opt, RefView re
                     else drop = mx - m - ((mj - max_j) - (i - max_i)) * e_ins > opt.zdrop;
                     if (drop) { st = XS_POST; break; }
                 }
-                int x;
-                for (x = beg; x < end && (COL(x) & 0x3ffffffu) == 0; ++x) {}
-                beg = x;
-                for (x = end; x >= beg && (COL(x) & 0x3ffffffu) == 0; --x) {}
+                // band trimming (ksw.c:465-468) without re-reading the row: the cell loop recorded the first and last column
+                // it stored a non-zero (h, e) into, and column `end` holds (h1, 0)
+                beg = firstnz < end ? firstnz : end;
+                const int x = h1 ? end : (lastnz >= beg ? lastnz : beg - 1);
                 end = x + 2 < qlen ? x + 2 : qlen;
                 ++i;
                 st = XS_ROWSTART;
@@ -341,6 +345,7 @@ __global__ void __launch_bounds__(EXT_BLOCK, 5) k_extend2(MemOpt opt, RefView re
 #pragma unroll
             for (int u = 0; u < EXT_CHUNK; ++u) cw[u] = p[u * EXT_BLOCK];
             int mkey = m << 8 | (mj & 0xff);  // row maximum and its column in one key: ties go to the larger column (:437)
+            unsigned nzm = 0;                  // bit u: the (h, e) stored into column j+u is non-zero
 #pragma unroll
             for (int u = 0; u < EXT_CHUNK; ++u) {
                 const bool on = u < nc;
@@ -350,11 +355,18 @@ __global__ void __launch_bounds__(EXT_BLOCK, 5) k_extend2(MemOpt opt, RefView re
                 const int h = __vimax3_s32(M, e, f);
                 const int e2 = __viaddmax_s32_relu(M, -oe_del, e - e_del);
                 const int f2 = __viaddmax_s32_relu(M, -oe_ins, f - e_ins);
-                if (on) p[u * EXT_BLOCK] = (uint32_t)h1 | (uint32_t)e2 << 13 | (cw[u] & (7u << 26));
+                const uint32_t he = (uint32_t)h1 | (uint32_t)e2 << 13;
+                nzm |= he ? 1u << u : 0u;
+                if (on) p[u * EXT_BLOCK] = he | (cw[u] & (7u << 26));
                 const int key = on ? (h << 8 | (j + u)) : 0;
                 mkey = mkey > key ? mkey : key;
                 f = on ? f2 : f;
                 h1 = on ? h : h1;
+            }
+            nzm &= nc >= EXT_CHUNK ? 0xffffu : (1u << nc) - 1u;
+            if (nzm) {
+                if (firstnz == 0x7fffffff) firstnz = j + __ffs(nzm) - 1;
+                lastnz = j + 31 - __clz(nzm);
             }
             m = mkey >> 8;
             if (m > 0) mj = mkey & 0xff;  // with m == 0 the column is never read (ksw.c:454)

@@ -28,6 +28,10 @@ struct FMIndex {
     uint64_t primary, seq_len, n_sa;
     uint64_t L2[5];
     int sa_intv;
+    // bi-interval of every kmer_k-mer (16 bytes each, packed like the seeding kernel's list entries), or null: lets the
+    // LAST-like pass (bwt_seed_strategy1) start kmer_k bases in instead of kmer_k-1 dependent bwt_extend calls (index.cuh)
+    const void* kmer;
+    int kmer_k;
 };
 
 struct OccStat {  // roofline accounting in the reference's own units: bwt_2occ4 calls and the 64-byte blocks they touch
@@ -60,11 +64,11 @@ AR_HD void fm_recut_block(const uint32_t* raw16, Blk32* out2) {
 
 AR_HD Blk32 fm_load_block(const FMIndex& fm, uint64_t b) {
 #if defined(__CUDA_ARCH__)
-    const uint4* p = reinterpret_cast<const uint4*>(fm.blocks + b);
-    uint4 v0 = __ldg(p), v1 = __ldg(p + 1);
+    // one 256-bit load (LDG.E.256 on sm_100): the whole sector in a single L1/L2 request instead of two 128-bit ones
     Blk32 o;
-    o.cnt[0] = v0.x; o.cnt[1] = v0.y; o.cnt[2] = v0.z; o.cnt[3] = v0.w;
-    o.w[0] = v1.x; o.w[1] = v1.y; o.w[2] = v1.z; o.w[3] = v1.w;
+    asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(o.cnt[0]), "=r"(o.cnt[1]), "=r"(o.cnt[2]), "=r"(o.cnt[3]), "=r"(o.w[0]), "=r"(o.w[1]), "=r"(o.w[2]), "=r"(o.w[3])
+                 : "l"(fm.blocks + b));
     return o;
 #else
     return fm.blocks[b];

@@ -21,7 +21,9 @@ struct arachne_index {
     int device = 0;
     arachne::FMIndex fm{};   // device pointers
     arachne::RefView ref{};  // device pointers
-    void *d_bwt = nullptr, *d_sa = nullptr, *d_pac = nullptr, *d_contigs = nullptr;
+    void *d_bwt = nullptr, *d_sa = nullptr, *d_pac = nullptr, *d_contigs = nullptr, *d_kmer = nullptr;
+    // runtime knobs (arachne_index_set_option): use the k-mer table in seeding; resident seeding blocks per SM
+    int opt_seed_kmer = 1, opt_seed_blocks = 3;
     size_t device_bytes = 0;
     std::vector<arachne::Contig> contigs;
     std::vector<std::string> names;
@@ -63,6 +65,28 @@ __global__ void __launch_bounds__(256) k_sa_densify(FMIndex fm, uint64_t* dense,
             if ((k & mask) == 0) break;
             --v;
             if ((k & dmask) == 0) dense[k / d] = v;
+        }
+    }
+}
+
+// Bi-interval of every K-mer: one thread per (K-1)-mer walks K-2 forward extensions from the single-base interval
+// (bwt_set_intv, bwt.h:80; forward = bwt_extend(.., is_back = 0) with the complement, bwt.c:304-307) and writes the four
+// children of the last one.  Entry = the seeding kernel's packed list entry (x0, x1, x2: 40 bits each).
+__global__ void __launch_bounds__(256) k_kmer_table(FMIndex fm, uint4* tab, int K) {
+    const uint64_t n_pre = 1ull << (2 * (K - 1));
+    for (uint64_t p = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; p < n_pre; p += (uint64_t)gridDim.x * blockDim.x) {
+        Intv ik, ok[4];
+        fm_set_intv(fm, (int)(p >> (2 * (K - 2))) & 3, ik);
+        for (int t = 1; t < K - 1; ++t) {
+            const int b = (int)(p >> (2 * (K - 2 - t))) & 3;
+            fm_extend(fm, ik, ok, 0);
+            ik = b == 0 ? ok[3] : b == 1 ? ok[2] : b == 2 ? ok[1] : ok[0];
+        }
+        fm_extend(fm, ik, ok, 0);
+        for (int b = 0; b < 4; ++b) {
+            const Intv& o = ok[3 - b];
+            const uint64_t lo = o.x0 | (o.x1 << 40), hi = (o.x1 >> 24) | (o.x2 << 16);
+            tab[p * 4 + b] = make_uint4((unsigned)lo, (unsigned)(lo >> 32), (unsigned)hi, (unsigned)(hi >> 32));
         }
     }
 }
@@ -175,6 +199,27 @@ inline int index_load(const char* prefix_, int device, arachne_index** out) {
     idx->ref.l_pac = idx->l_pac;
     idx->ref.n_seqs = (int)idx->contigs.size();
     idx->device_bytes = img + sab + pacb + sizeof(Contig) * idx->contigs.size();
+    fm.kmer = nullptr; fm.kmer_k = 0;
+    {   // k-mer table for the LAST-like seeding pass: K = min(14, log4(seq_len) - 1), off below 8 (ARACHNE_SEED_KMER=0 disables, =K forces)
+        int K = 0;
+        for (uint64_t v = fm.seq_len; v > 3; v >>= 2) ++K;
+        K = K - 1 < 14 ? K - 1 : 14;
+        if (const char* ev = getenv("ARACHNE_SEED_KMER")) K = atoi(ev);
+        size_t free_b = 0, total_b = 0;
+        cudaMemGetInfo(&free_b, &total_b);
+        if (K >= 8 && K <= 15 && (16ull << (2 * K)) < free_b / 4 && fm.seq_len < (1ull << 40) - 2) {
+            void* dk = nullptr;
+            e = cudaMalloc(&dk, 16ull << (2 * K));
+            if (e == cudaSuccess) {
+                FMIndex f2 = fm;  // the table is filled with the file's SA sampling still in place (the SA is not used)
+                k_kmer_table<<<148 * 8, 256>>>(f2, reinterpret_cast<uint4*>(dk), K);
+                e = cudaGetLastError();
+                if (e == cudaSuccess) e = cudaDeviceSynchronize();
+            }
+            if (e == cudaSuccess) { idx->d_kmer = dk; fm.kmer = dk; fm.kmer_k = K; idx->device_bytes += 16ull << (2 * K); }
+            else { if (dk) cudaFree(dk); (void)cudaGetLastError(); }
+        }
+    }
     {   // densify the sampled SA when HBM has the room (ARACHNE_SA_INTV=1|2|4|8|16|32 overrides; 32 keeps the file's sampling)
         int d = 0;
         if (const char* ev = getenv("ARACHNE_SA_INTV")) d = atoi(ev);

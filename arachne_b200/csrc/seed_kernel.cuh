@@ -40,14 +40,18 @@ __device__ __forceinline__ void pk_unpack(uint4 v, uint64_t& x0, uint64_t& x1, u
 
 enum { SP_IDLE = 0, SP_P1_SCAN, SP_FWD, SP_BWD, SP_P2_NEXT, SP_P3_SCAN, SP_P3, SP_DONE };
 
-__global__ void __launch_bounds__(256, 3) k_seed2(FMIndex fm, MemOpt opt, const uint8_t* __restrict__ seq, const int64_t* __restrict__ off,
-                                                  int n_reads, int maxlen, uint4* lists, int rows, SeedOut out, unsigned int* next, Counters* cnt) {
+template <int MIN_BLOCKS>
+__global__ void __launch_bounds__(256, MIN_BLOCKS) k_seed2(FMIndex fm, MemOpt opt, const uint8_t* __restrict__ seq, const int64_t* __restrict__ off,
+                                                  int n_reads, int maxlen, uint4* lists, int rows, SeedOut out, unsigned int* next, Counters* cnt,
+                                                  int use_kmer) {
     const unsigned T = gridDim.x * blockDim.x, tid = blockIdx.x * blockDim.x + threadIdx.x;
     uint4* list = lists + tid;                       // entry j at list[j * T]
     uint4* recs = lists + (size_t)(rows >> 1) * T + tid;  // re-seed records in the upper half
     const int split_len = (int)(opt.min_seed_len * opt.split_factor + .499f);
     // task kinds cost about 2:1 in bwt_extend calls (passes 1+2 vs pass 3): every third warp starts on the LAST-like queue
-    const int pref_kind = (opt.max_mem_intv > 0 && (tid >> 5) % 3 == 2) ? 1 : 0;
+    // (1:5 when pass 3 starts from the k-mer table)
+    const int kmer_k = (use_kmer && fm.kmer && fm.kmer_k <= opt.min_seed_len) ? fm.kmer_k : 0;
+    const int pref_kind = (opt.max_mem_intv > 0 && (tid >> 5) % (kmer_k ? 6 : 3) == 2) ? 1 : 0;
 
     int phase = SP_IDLE, r = 0, len = 0, x = 0, i = 0, pass = 1;
     const uint8_t* q = seq;
@@ -119,12 +123,30 @@ __global__ void __launch_bounds__(256, 3) k_seed2(FMIndex fm, MemOpt opt, const 
                 phase = SP_FWD;
             }
             if (phase == SP_P3_SCAN) {
-                while (x < len && __ldg(q + x) > 3) ++x;
-                if (x >= len) { phase = SP_IDLE; break; }
-                int b = __ldg(q + x);
-                kx0 = fm_L2(fm, b) + 1; kx2 = fm_L2(fm, b + 1) - fm_L2(fm, b); kx1 = fm_L2(fm, 3 - b) + 1;
-                i = x + 1;
-                phase = SP_P3;
+                // bwt_seed_strategy1 (bwt.c:358-379) from x: nothing is tested before the match is min_seed_len + 1 long, so
+                // (a) a start with fewer bases left cannot seed, (b) the first kmer_k bases need no stepping: their bi-interval
+                // is one table entry (an ambiguous base among them ends the call without a seed, as in the reference).
+                for (;;) {
+                    while (x < len && __ldg(q + x) > 3) ++x;
+                    if (len - x <= opt.min_seed_len) { phase = SP_IDLE; break; }
+                    int b = __ldg(q + x);
+                    if (kmer_k) {
+                        uint32_t km = (uint32_t)b;
+                        int p = x + 1;
+                        for (; p < x + kmer_k; ++p) { const int bb = __ldg(q + p); if (bb > 3) break; km = km << 2 | (uint32_t)bb; }
+                        if (p < x + kmer_k) { x = p + 1; continue; }
+                        unsigned spare;
+                        pk_unpack(__ldg(reinterpret_cast<const uint4*>(fm.kmer) + km), kx0, kx1, kx2, spare);
+                        i = x + kmer_k;
+                        st_calls += kmer_k - 1; st_blocks += 2 * (kmer_k - 1);  // the skipped calls; intervals this large span two blocks
+                    } else {
+                        kx0 = fm_L2(fm, b) + 1; kx2 = fm_L2(fm, b + 1) - fm_L2(fm, b); kx1 = fm_L2(fm, 3 - b) + 1;
+                        i = x + 1;
+                    }
+                    phase = SP_P3;
+                    break;
+                }
+                if (phase == SP_IDLE) break;
             }
             if (phase == SP_FWD) {
                 int b = i < len ? (int)__ldg(q + i) : 4;

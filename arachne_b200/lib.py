@@ -92,6 +92,7 @@ class ArachneCuda:
         L.arachne_index_device_bytes.restype = C.c_size_t; L.arachne_index_device_bytes.argtypes = [C.c_void_p]
         L.arachne_index_contig.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_char_p), C.POINTER(C.c_int64), C.POINTER(C.c_int32)]
         L.arachne_index_set_stream.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+        L.arachne_index_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_int64]
         L.arachne_opts_default.argtypes = [C.POINTER(MemOpt)]
         L.arachne_align_batch.argtypes = [C.c_void_p, C.POINTER(MemOpt), C.POINTER(BatchIn), C.POINTER(C.POINTER(BatchOut))]
         L.arachne_batch_free.argtypes = [C.POINTER(BatchOut)]
@@ -191,6 +192,9 @@ class ArachneCuda:
                                                    _p(q_off, C.c_int64), _p(t, C.c_uint8), _p(t_off, C.c_int64), _p(w, C.c_int32),
                                                    _p(sc, C.c_int32), _p(coff, C.c_int64) if want_cigar else None, _p(cig, C.c_uint32), cap))
         return sc, coff, cig[:coff[-1]]
+
+    def set_option(self, name: str, value: int):
+        self._ck(self.lib.arachne_index_set_option(self.idx, name.encode(), int(value)))
 
     def set_stream(self, cuda_stream: int | None):
         """Run batches on the caller's stream (e.g. torch.cuda.current_stream().cuda_stream); None = the handle's own."""
