@@ -2,18 +2,30 @@
 // All device arenas live in the index handle's Workspace and are reused by later batches; results are copied into
 // pinned host buffers recycled through arachne_batch_free.
 
-static Workspace* get_ws(arachne_index_t* idx) {
-    if (!idx->ws) {
+static Workspace* get_ws(arachne_index_t* idx, int slot) {
+    if (!idx->ws[slot]) {
         auto* w = new Workspace();
         if (w->init()) { w->destroy(); delete w; return nullptr; }
-        idx->ws = w;
+        idx->ws[slot] = w;
     }
-    return reinterpret_cast<Workspace*>(idx->ws);
+    return reinterpret_cast<Workspace*>(idx->ws[slot]);
+}
+
+// Take a free workspace slot (first one that is idle, else wait on them in turn).
+static std::unique_lock<std::mutex> take_ws(arachne_index_t* idx, int* slot) {
+    for (int k = 0; k < arachne_index::N_WS; ++k) {
+        std::unique_lock<std::mutex> l(idx->ws_mu[k], std::try_to_lock);
+        if (l.owns_lock()) { *slot = k; return l; }
+    }
+    unsigned k;
+    { std::lock_guard<std::mutex> g(idx->mu); k = idx->ws_rr++ % arachne_index::N_WS; }
+    *slot = (int)k;
+    return std::unique_lock<std::mutex>(idx->ws_mu[k]);
 }
 
 int arachne_index_set_option(arachne_index_t* idx, const char* name, int64_t value) {
     if (!idx || !name) { set_error("arachne_index_set_option: null argument"); return ARACHNE_ERR_ARG; }
-    std::lock_guard<std::mutex> lk(idx->mu);
+    std::lock_guard<std::mutex> lk(idx->mu);  // takes effect with the next batch that starts
     if (!strcmp(name, "seed_kmer")) idx->opt_seed_kmer = value != 0;
     else if (!strcmp(name, "seed_blocks_per_sm") && (value == 3 || value == 4)) idx->opt_seed_blocks = (int)value;
     else { set_error("arachne_index_set_option: unknown option or value: %s=%lld", name, (long long)value); return ARACHNE_ERR_ARG; }
@@ -52,23 +64,31 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
             if (l > maxlen) maxlen = (int)l;
         }
     }
-    std::lock_guard<std::mutex> guard(idx->mu);
+    int ws_slot = 0;
+    std::unique_lock<std::mutex> guard = take_ws(idx, &ws_slot);
     AR_CUDA(cudaSetDevice(idx->device));
-    Workspace* wsp = get_ws(idx);
+    Workspace* wsp = get_ws(idx, ws_slot);
     if (!wsp) { set_error("cannot create the batch workspace (stream/events/pinned memory)"); return ARACHNE_ERR_CUDA; }
     Workspace& W = *wsp;
     const int sms = sm_count(idx->device);
-    cudaStream_t st = idx->has_user_stream ? reinterpret_cast<cudaStream_t>(idx->user_stream) : W.own_stream;
+    cudaStream_t st;
+    int use_seed_kmer, seed_bpsm_opt;
+    BatchPriv* priv = nullptr;
+    {
+        std::lock_guard<std::mutex> g(idx->mu);
+        st = idx->has_user_stream ? reinterpret_cast<cudaStream_t>(idx->user_stream) : W.own_stream;
+        use_seed_kmer = idx->opt_seed_kmer; seed_bpsm_opt = idx->opt_seed_blocks;
+        if (!idx->priv_pool.empty()) { priv = reinterpret_cast<BatchPriv*>(idx->priv_pool.back()); idx->priv_pool.pop_back(); }
+    }
     cudaEvent_t* ev = W.ev;  // seed | sa | chain | extend | rescue | gather | cigar | end
 
     auto* out = new arachne_batch_out_t();
     memset(out, 0, sizeof(*out));
-    BatchPriv* priv = nullptr;
-    if (!W.pool.empty()) { priv = W.pool.back(); W.pool.pop_back(); } else priv = new BatchPriv();
+    if (!priv) priv = new BatchPriv();
     priv->owner = idx;
     out->priv = priv;
     out->n_reads = n_reads;
-    auto fail = [&](int code) { W.pool.push_back(priv); delete out; return code; };
+    auto fail = [&](int code) { { std::lock_guard<std::mutex> g(idx->mu); idx->priv_pool.push_back(priv); } delete out; return code; };
 #define AR_TRY(x) do { if ((x) != cudaSuccess) { set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #x, cudaGetErrorString(cudaGetLastError())); return fail(ARACHNE_ERR_CUDA); } } while (0)
 #define AR_ALLOC(buf, bytes) do { if ((buf).ensure(bytes)) { set_error("out of device memory allocating %zu bytes (%s)", (size_t)(bytes), #buf); return fail(ARACHNE_ERR_CUDA); } } while (0)
 #define AR_PIN(buf, bytes) do { if ((buf).ensure(bytes)) { set_error("out of pinned host memory allocating %zu bytes (%s)", (size_t)(bytes), #buf); return fail(ARACHNE_ERR_CUDA); } } while (0)
@@ -105,7 +125,7 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
     unsigned long long* hs = W.h_scalars;
     // ---- seeding (retry with a larger per-read interval capacity if a read overflows it) ----
     if (idx->fm.seq_len >= (1ull << 40) - 2) { set_error("reference too long for the packed interval lists (2*l_pac must stay below 2^40)"); return fail(ARACHNE_ERR_ARG); }
-    const int seed_bpsm = idx->opt_seed_blocks == 4 ? 4 : 3, seed_blocks = sms * seed_bpsm, seed_T = seed_blocks * 256, list_rows = 2 * L1;
+    const int seed_bpsm = seed_bpsm_opt == 4 ? 4 : 3, seed_blocks = sms * seed_bpsm, seed_T = seed_blocks * 256, list_rows = 2 * L1;
     AR_ALLOC(W.d_scratch, (size_t)seed_T * list_rows * sizeof(uint4));
     int intv_cap = 32;
     cudaEventRecord(ev[0], st);
@@ -118,10 +138,10 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
         ++nl;
         if (seed_bpsm == 4)
             k_seed2<4><<<seed_blocks, 256, 0, st>>>(idx->fm, opt, d_seq, d_off, (int)n_reads, maxlen, W.d_scratch.as<uint4>(), list_rows, so,
-                                                     W.d_misc.as<unsigned int>(), W.d_cnt.as<Counters>(), idx->opt_seed_kmer);
+                                                     W.d_misc.as<unsigned int>(), W.d_cnt.as<Counters>(), use_seed_kmer);
         else
             k_seed2<3><<<seed_blocks, 256, 0, st>>>(idx->fm, opt, d_seq, d_off, (int)n_reads, maxlen, W.d_scratch.as<uint4>(), list_rows, so,
-                                                     W.d_misc.as<unsigned int>(), W.d_cnt.as<Counters>(), idx->opt_seed_kmer);
+                                                     W.d_misc.as<unsigned int>(), W.d_cnt.as<Counters>(), use_seed_kmer);
         AR_TRY(cudaGetLastError());
         AR_TRY(cudaMemcpyAsync(&hc, W.d_cnt.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
         AR_TRY(cudaStreamSynchronize(st));
@@ -384,7 +404,7 @@ void arachne_batch_free(arachne_batch_out_t* out) {
         bool pooled = false;
         if (idx) {
             std::lock_guard<std::mutex> g(idx->mu);
-            if (idx->ws) { reinterpret_cast<Workspace*>(idx->ws)->pool.push_back(priv); pooled = true; }
+            if (idx->priv_pool.size() < 8) { idx->priv_pool.push_back(priv); pooled = true; }
         }
         if (!pooled) { priv->release(); delete priv; }
     }

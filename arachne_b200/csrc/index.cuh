@@ -30,11 +30,17 @@ struct arachne_index {
     int64_t l_pac = 0;
     // host copy of the packed reference (GetSeq-style host queries, compat shims)
     std::vector<uint8_t> h_pac;
-    // per-index batch workspace (device arenas, pinned result pools, stream, events): created on first use, reused by
-    // every later batch; calls on one handle serialise on `mu` (the reference's workers share one read-only index and
-    // bring their own scratch, gobwa.go passes buf=NULL -- here the scratch is the handle's, so batches queue up)
+    // per-index batch workspaces (device arenas, pinned scalars, stream, events): created on first use and reused by
+    // every later batch.  The reference's workers share one read-only index and bring their own scratch (gobwa.go passes
+    // buf=NULL); here the scratch is the handle's: N_WS slots, so that two host threads can be in flight on one handle and
+    // one batch's host<->device copies overlap the other's kernels; further callers queue.  `mu` guards the small
+    // shared state (options, stream choice, the pool of recycled pinned result sets).
+    static constexpr int N_WS = 2;
     std::mutex mu;
-    void* ws = nullptr;
+    std::mutex ws_mu[N_WS];
+    void* ws[N_WS] = {nullptr, nullptr};
+    unsigned ws_rr = 0;
+    std::vector<void*> priv_pool;
     void* user_stream = nullptr;
     bool has_user_stream = false;
 };

@@ -480,7 +480,6 @@ struct Workspace {
     cudaEvent_t ev[10] = {};
     Counters* h_cnt = nullptr;              // pinned
     unsigned long long* h_scalars = nullptr;  // pinned, 8 slots
-    std::vector<BatchPriv*> pool;           // recycled pinned result sets
     std::vector<DevBuf*> all() {
         return {&d_seq, &d_off, &d_scratch, &d_arena, &d_misc, &d_intv_off, &d_intv_n, &d_nsa, &d_sa_off, &d_rows, &d_cnt, &d_tmp,
                 &d_seeds, &d_kseeds, &d_chains, &d_nodes, &d_order, &d_kept, &d_nchain, &d_nkseed, &d_srt, &d_regs, &d_nregs,
@@ -497,8 +496,6 @@ struct Workspace {
     }
     void destroy() {
         for (auto* b : all()) b->release();
-        for (auto* p : pool) { p->release(); delete p; }
-        pool.clear();
         for (auto& e : ev) if (e) cudaEventDestroy(e);
         if (own_stream) cudaStreamDestroy(own_stream);
         if (h_cnt) cudaFreeHost(h_cnt);
@@ -521,7 +518,10 @@ int arachne_index_load(const char* prefix, int device, arachne_index_t** out) { 
 void arachne_index_free(arachne_index_t* idx) {
     if (!idx) return;
     cudaSetDevice(idx->device);
-    if (idx->ws) { auto* w = reinterpret_cast<Workspace*>(idx->ws); w->destroy(); delete w; idx->ws = nullptr; }
+    for (int k = 0; k < arachne_index::N_WS; ++k)
+        if (idx->ws[k]) { auto* w = reinterpret_cast<Workspace*>(idx->ws[k]); w->destroy(); delete w; idx->ws[k] = nullptr; }
+    for (void* p : idx->priv_pool) { auto* bp = reinterpret_cast<BatchPriv*>(p); bp->release(); delete bp; }
+    idx->priv_pool.clear();
     cudaFree(idx->d_bwt); cudaFree(idx->d_sa); cudaFree(idx->d_pac); cudaFree(idx->d_contigs); cudaFree(idx->d_kmer);
     delete idx;
 }

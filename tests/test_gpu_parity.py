@@ -287,6 +287,24 @@ def test_edge_inputs_all_stages(A, R, workdir, name):
     assert (ocands["reg"] == -1).sum() > 5, "no unmapped placeholders exercised"
 
 
+def test_concurrent_batches_on_one_handle(A, R, workdir):
+    """Two host threads in flight on one handle (the reference's worker goroutines share one index, aligner.go:335-337):
+    each call gets its own workspace; results equal the sequential ones and the reference's."""
+    from concurrent.futures import ThreadPoolExecutor
+    fa, ctg, rs = util.make_dataset("rand1m", workdir, damaged=True)
+    R.load(fa); A.load_index(fa)
+    nb = len(rs.bc_off) - 1
+    parts = [rs.subset(nb * k // 6, nb * (k + 1) // 6) for k in range(6)]
+    seq = [A.align_batch(p.seq, p.off, p.bc_off, stages=7) for p in parts]
+    with ThreadPoolExecutor(3) as ex:
+        par = list(ex.map(lambda p: A.align_batch(p.seq, p.off, p.bc_off, stages=7), parts * 2))
+    for k, p in enumerate(parts):
+        ref = R.batch(p.seq, p.off, rescue=True, cigar=True, threads=4)
+        for res in (seq[k], par[k], par[k + 6]):
+            assert np.array_equal(res["reg_off"], ref["reg_off"]) and res["regs"].tobytes() == ref["regs"].tobytes(), k
+            assert np.array_equal(res["cigar"], seq[k]["cigar"]) and res["alns"].tobytes() == seq[k]["alns"].tobytes(), k
+
+
 def test_empty_and_tiny_batches(A, R, workdir):
     fa, ctg, rs = util.make_dataset("rand1m", workdir)
     A.load_index(fa); R.load(fa)
