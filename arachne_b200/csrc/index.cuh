@@ -23,7 +23,7 @@ struct arachne_index {
     arachne::RefView ref{};  // device pointers
     void *d_bwt = nullptr, *d_sa = nullptr, *d_pac = nullptr, *d_contigs = nullptr, *d_kmer = nullptr;
     // runtime knobs (arachne_index_set_option): use the k-mer table in seeding; resident seeding blocks per SM
-    int opt_seed_kmer = 1, opt_seed_blocks = 3;
+    int opt_seed_kmer = 1, opt_seed_blocks = 3, opt_seed_slist = -1;
     size_t device_bytes = 0;
     std::vector<arachne::Contig> contigs;
     std::vector<std::string> names;

@@ -680,8 +680,9 @@ int arachne_seed_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, int6
         AR_CUDA(cudaMemset(d_next.p, 0, 64)); AR_CUDA(cudaMemset(d_cnt.p, 0, sizeof(Counters)));
         AR_CUDA(cudaMemset(d_in.p, 0, n_reads * 4 + 4)); AR_CUDA(cudaMemset(d_nsa.p, 0, n_reads * 4 + 4));
         SeedOut so; so.intv = d_arena.as<Intv>(); so.intv_n = d_in.as<int>(); so.n_sa = d_nsa.as<unsigned int>(); so.cap = cap;
-        k_seed2<3><<<blocks, 256>>>(idx->fm, opt, d_seq.as<uint8_t>(), d_off.as<int64_t>(), (int)n_reads, maxlen, d_scr.as<uint4>(), rows, so,
-                                    d_next.as<unsigned int>(), d_cnt.as<Counters>(), idx->opt_seed_kmer);
+        AR_CUDA(cudaFuncSetAttribute(k_seed2<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16 * 256 * (int)sizeof(uint4)));
+        k_seed2<3><<<blocks, 256, 16 * 256 * sizeof(uint4)>>>(idx->fm, opt, d_seq.as<uint8_t>(), d_off.as<int64_t>(), (int)n_reads, maxlen, d_scr.as<uint4>(), rows, so,
+                                    d_next.as<unsigned int>(), d_cnt.as<Counters>(), idx->opt_seed_kmer, 16);
         AR_CUDA(cudaGetLastError());
         AR_CUDA(cudaMemcpy(&hc, d_cnt.p, sizeof(hc), cudaMemcpyDeviceToHost));
         if (!hc.err) break;

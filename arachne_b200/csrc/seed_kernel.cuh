@@ -43,9 +43,16 @@ enum { SP_IDLE = 0, SP_P1_SCAN, SP_FWD, SP_BWD, SP_P2_NEXT, SP_P3_SCAN, SP_P3, S
 template <int MIN_BLOCKS>
 __global__ void __launch_bounds__(256, MIN_BLOCKS) k_seed2(FMIndex fm, MemOpt opt, const uint8_t* __restrict__ seq, const int64_t* __restrict__ off,
                                                   int n_reads, int maxlen, uint4* lists, int rows, SeedOut out, unsigned int* next, Counters* cnt,
-                                                  int use_kmer) {
+                                                  int use_kmer, int slist_n) {
     const unsigned T = gridDim.x * blockDim.x, tid = blockIdx.x * blockDim.x + threadIdx.x;
-    uint4* list = lists + tid;                       // entry j at list[j * T]
+    uint4* list = lists + tid;                       // entry j (j >= slist_n) at list[j * T]
+    // the first slist_n entries of every lane's list live in shared memory ([entry][lane], 16 bytes each: the bank depends
+    // on the lane only, so lanes at different entries never conflict): with ~17 entries per forward pass the lists of the
+    // SM's lanes (0.3 MB) do not fit L1, and every backward step would otherwise start with an L2 round trip
+    extern __shared__ uint4 slist[];
+    uint4* sl = slist + threadIdx.x;
+    auto lput = [&](int e, uint4 v) { if (e < slist_n) sl[e * 256] = v; else list[(size_t)e * T] = v; };
+    auto lget = [&](int e) -> uint4 { return e < slist_n ? sl[e * 256] : list[(size_t)e * T]; };
     uint4* recs = lists + (size_t)(rows >> 1) * T + tid;  // re-seed records in the upper half
     const int split_len = (int)(opt.min_seed_len * opt.split_factor + .499f);
     // task kinds cost about 2:1 in bwt_extend calls (passes 1+2 vs pass 3): every third warp starts on the LAST-like queue
@@ -152,7 +159,7 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) k_seed2(FMIndex fm, MemOpt op
                 int b = i < len ? (int)__ldg(q + i) : 4;
                 if (b < 4) { need = true; is_back = 0; c = 3 - b; sx0 = kx0; sx1 = kx1; sx2 = kx2; }
                 else {  // ambiguous base or end of read: close the forward pass (bwt.c:311-316)
-                    list[(size_t)(n++) * T] = pk_pack(kx0, kx1, kx2, kend);
+                    lput(n++, pk_pack(kx0, kx1, kx2, kend));
                     ret = (int)kend;
                     hi = n; lo = 0; j = hi - 1; ncur = 0; i = x - 1;
                     phase = SP_BWD;
@@ -160,7 +167,7 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) k_seed2(FMIndex fm, MemOpt op
             }
             if (phase == SP_BWD && !need) {
                 int b = i < 0 ? 4 : (int)__ldg(q + i);
-                pk_unpack(list[(size_t)j * T], px0, px1, px2, pend);
+                pk_unpack(lget(j), px0, px1, px2, pend);
                 if (b > 3) {
                     // no extension possible: only the longest survivor can be a new SMEM (bwt.c:331-341), then the call ends
                     if (ncur == 0 && j == hi - 1 && i + 1 < last_start) emit(px0, px1, px2, i + 1, (int)pend, true);
@@ -212,7 +219,7 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) k_seed2(FMIndex fm, MemOpt op
             // forward extension: ok.x1 = looked-up coordinate, ok.x0 = the other
             bool stop = false;
             if (ox2 != kx2) {
-                list[(size_t)(n++) * T] = pk_pack(kx0, kx1, kx2, kend);
+                lput(n++, pk_pack(kx0, kx1, kx2, kend));
                 if (ox2 < min_intv) stop = true;
             }
             if (stop) {
@@ -228,7 +235,7 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) k_seed2(FMIndex fm, MemOpt op
             if (ox2 < min_intv) {
                 if (ncur == 0 && i + 1 < last_start) { emit(px0, px1, px2, i + 1, (int)pend, true); last_start = i + 1; }
             } else if (ncur == 0 || ox2 != lastcur_x2) {
-                list[(size_t)(hi - 1 - ncur) * T] = pk_pack(ox_a, ox_b, ox2, pend);
+                lput(hi - 1 - ncur, pk_pack(ox_a, ox_b, ox2, pend));
                 ++ncur; lastcur_x2 = ox2;
             }
             if (--j < lo) {

@@ -222,7 +222,8 @@ int arachne_index_set_stream(arachne_index_t *idx, void *cuda_stream, int use);
 
 /* Runtime knobs of a handle; results never depend on them.  "seed_kmer" 0|1: let the LAST-like seeding pass start from the
  * HBM k-mer table built at load (default 1; 0 makes every bwt_extend call of the reference, which is how bench.py counts the
- * algorithmic occ-block bytes).  "seed_blocks_per_sm" 3|4: resident seeding blocks per SM. */
+ * algorithmic occ-block bytes).  "seed_blocks_per_sm" 3|4: resident seeding blocks per SM.
+ * "seed_shared_list" -1..16: interval-list entries per lane kept in shared memory (-1: as many as fit). */
 int arachne_index_set_option(arachne_index_t *idx, const char *name, int64_t value);
 
 /* int64(binary.LittleEndian.Uint64(md5(name)[0:8])): the per-read PRNG seed of tagBestAlignments (aligner.go:1413-1416). Host only. */
