@@ -20,6 +20,7 @@
 namespace arachne {
 
 constexpr int EXT_CHUNK = 16;
+constexpr int EXT_GROUP = 4;
 constexpr int EXT_BLOCK = 64;
 constexpr int COL_HMASK = 0x1fff;
 
@@ -61,6 +62,11 @@ struct ThreadCtx {
         return H[qlen];
     }
 };
+
+// mem_sort_dedup_patch once per read, kept out of line: the kernel's hot loop should not share instruction-cache lines with it
+__device__ __noinline__ int sort_dedup_patch_cold(ThreadCtx tctx, const MemOpt& opt, const RefView& ref, const uint8_t* query, int n_av, AlnReg* av, int rcap) {
+    return sort_dedup_patch(tctx, opt, ref, query, n_av, av, tctx.rbuf, rcap);
+}
 
 enum { XS_FETCH = 0, XS_CHAIN, XS_SEED, XS_SETUP, XS_INIT, XS_ROWSTART, XS_CELLS, XS_ROWEND, XS_POST, XS_REGION, XS_FINISH, XS_DONE };
 
@@ -299,7 +305,7 @@ __global__ void __launch_bounds__(EXT_BLOCK, 6) k_extend2(MemOpt opt, RefView re
             case XS_FINISH: {
                 int rc = err;
                 if (rc == 0) {
-                    int nn = sort_dedup_patch(tctx, opt, ref, query, n_av, av, tctx.rbuf, A.rcap);
+                    int nn = sort_dedup_patch_cold(tctx, opt, ref, query, n_av, av, A.rcap);
                     if (nn < 0) rc = nn; else n_av = nn;
                 }
                 if (rc != 0) { raise(A.cnt, ARACHNE_ERR_OVERFLOW, r); n_av = 0; }
@@ -336,41 +342,49 @@ __global__ void __launch_bounds__(EXT_BLOCK, 6) k_extend2(MemOpt opt, RefView re
             if (st == XS_INIT) st = XS_ROWSTART;
         }
         // ------------------------------------------------------------ convergent: up to EXT_CHUNK cells of the current row (ksw.c:424-448)
-        // Straight-line: the chunk's column words are loaded up front (the column array is padded by EXT_CHUNK words, so
-        // reading past `end` is harmless), every cell is computed, and cells at or beyond `end` are simply not committed.
-        if (st == XS_CELLS) {
-            uint32_t* p = &COL(j);
-            const int nc = end - j;  // >= 1
-            uint32_t cw[EXT_CHUNK];
-#pragma unroll
-            for (int u = 0; u < EXT_CHUNK; ++u) cw[u] = p[u * EXT_BLOCK];
+        // In groups of EXT_GROUP cells: a group's column words are loaded up front (the column array is padded by EXT_CHUNK
+        // words, so reading past `end` is harmless), every cell of the group is computed, and cells at or beyond `end` are
+        // simply not committed.  The group loop is rolled (the fully unrolled 16-cell block was 5.6 KB of code and the
+        // kernel's top stall was instruction fetch) and stops at the longest remaining run in the warp.
+        {
+            const int nc = st == XS_CELLS ? (end - j < EXT_CHUNK ? end - j : EXT_CHUNK) : 0;  // >= 1 for a lane in XS_CELLS
+            const int nc_warp = __reduce_max_sync(0xffffffffu, nc);
             int mkey = m << 8 | (mj & 0xff);  // row maximum and its column in one key: ties go to the larger column (:437)
             unsigned nzm = 0;                  // bit u: the (h, e) stored into column j+u is non-zero
+            uint32_t* p = &COL(j);
+#pragma unroll 1
+            for (int g = 0; g < nc_warp; g += EXT_GROUP, p += EXT_GROUP * EXT_BLOCK) {
+                if (g >= nc) continue;
+                uint32_t cw[EXT_GROUP];
 #pragma unroll
-            for (int u = 0; u < EXT_CHUNK; ++u) {
-                const bool on = u < nc;
-                const int hd = (int)(cw[u] & COL_HMASK), e = (int)((cw[u] >> 13) & COL_HMASK), qb = (int)(cw[u] >> 26);
-                const int sc = qb == tbv ? sa : ((qb | tbv) > 3 ? -1 : snb);
-                const int M = hd ? hd + sc : 0;
-                const int h = __vimax3_s32(M, e, f);
-                const int e2 = __viaddmax_s32_relu(M, -oe_del, e - e_del);
-                const int f2 = __viaddmax_s32_relu(M, -oe_ins, f - e_ins);
-                const uint32_t he = (uint32_t)h1 | (uint32_t)e2 << 13;
-                nzm |= he ? 1u << u : 0u;
-                if (on) p[u * EXT_BLOCK] = he | (cw[u] & (7u << 26));
-                const int key = on ? (h << 8 | (j + u)) : 0;
-                mkey = mkey > key ? mkey : key;
-                f = on ? f2 : f;
-                h1 = on ? h : h1;
+                for (int u = 0; u < EXT_GROUP; ++u) cw[u] = p[u * EXT_BLOCK];
+#pragma unroll
+                for (int u = 0; u < EXT_GROUP; ++u) {
+                    const bool on = g + u < nc;
+                    const int hd = (int)(cw[u] & COL_HMASK), e = (int)((cw[u] >> 13) & COL_HMASK), qb = (int)(cw[u] >> 26);
+                    const int sc = qb == tbv ? sa : ((qb | tbv) > 3 ? -1 : snb);
+                    const int M = hd ? hd + sc : 0;
+                    const int h = __vimax3_s32(M, e, f);
+                    const int e2 = __viaddmax_s32_relu(M, -oe_del, e - e_del);
+                    const int f2 = __viaddmax_s32_relu(M, -oe_ins, f - e_ins);
+                    const uint32_t he = (uint32_t)h1 | (uint32_t)e2 << 13;
+                    nzm |= (on && he) ? 1u << (g + u) : 0u;
+                    if (on) p[u * EXT_BLOCK] = he | (cw[u] & (7u << 26));
+                    const int key = on ? (h << 8 | (j + g + u)) : 0;
+                    mkey = mkey > key ? mkey : key;
+                    f = on ? f2 : f;
+                    h1 = on ? h : h1;
+                }
             }
-            nzm &= nc >= EXT_CHUNK ? 0xffffu : (1u << nc) - 1u;
-            if (nzm) {
-                if (firstnz == 0x7fffffff) firstnz = j + __ffs(nzm) - 1;
-                lastnz = j + 31 - __clz(nzm);
+            if (nc) {
+                if (nzm) {
+                    if (firstnz == 0x7fffffff) firstnz = j + __ffs(nzm) - 1;
+                    lastnz = j + 31 - __clz(nzm);
+                }
+                m = mkey >> 8;
+                if (m > 0) mj = mkey & 0xff;  // with m == 0 the column is never read (ksw.c:454)
+                j += nc;
             }
-            m = mkey >> 8;
-            if (m > 0) mj = mkey & 0xff;  // with m == 0 the column is never read (ksw.c:454)
-            j += nc < EXT_CHUNK ? nc : EXT_CHUNK;
         }
         if (__all_sync(0xffffffffu, st == XS_DONE)) break;
     }
