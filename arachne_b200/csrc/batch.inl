@@ -56,6 +56,7 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
         if (in->max_read_len <= 0 || in->max_read_len > ARACHNE_MAX_READ_LEN || in->n_bases < 0) {
             set_error("ARACHNE_IN_DEVICE needs max_read_len in 1..%d and n_bases", ARACHNE_MAX_READ_LEN); return ARACHNE_ERR_ARG;
         }
+        if (reinterpret_cast<uintptr_t>(in->seq) & 7) { set_error("ARACHNE_IN_DEVICE: seq must be 8-byte aligned"); return ARACHNE_ERR_ARG; }
         maxlen = in->max_read_len; n_bases = in->n_bases;
     } else {
         n_bases = n_reads ? in->seq_off[n_reads] : 0;

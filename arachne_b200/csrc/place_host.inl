@@ -144,7 +144,7 @@
         AR_TRY(cudaMemsetAsync(W.d_misc.p, 0, 64, st));
         RA.next = W.d_misc.as<unsigned>();
         ++nl;
-        k_place_rfa<<<std::min(n_slots, sms * 4), PLACE_T, 0, st>>>(PA, RA);
+        k_place_rfa<<<std::min(n_slots, sms * (1024 / PLACE_T)), PLACE_T, 0, st>>>(PA, RA);
         AR_TRY(cudaGetLastError());
     }
     // ---- MAPQ ----

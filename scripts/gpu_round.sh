@@ -6,6 +6,6 @@ python bench.py --steps 6 --warmup 3 > gpurun_out/${TAG}_bench.json 2> gpurun_ou
 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/${TAG}_bench_ref.json 2>> gpurun_out/${TAG}_bench.err
 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/${TAG}_launches.csv python bench.py --steps 2 --warmup 1 --pairs 200000 --no-cpu-baseline > gpurun_out/${TAG}_ncu1.log 2>&1
 for k in $KERNELS; do
-ncu --set full --clock-control none --import-source on -k regex:$k -s 1 -c 1 -o gpurun_out/${TAG}_$k -f python bench.py --steps 1 --warmup 1 --pairs 200000 --no-cpu-baseline > gpurun_out/${TAG}_ncu_$k.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:$k -s 1 -c 1 -o gpurun_out/${TAG}_$k -f python bench.py --steps 1 --warmup 1 --pairs ${NCU_PAIRS:-200000} --no-cpu-baseline > gpurun_out/${TAG}_ncu_$k.log 2>&1
 done
 tail -3 gpurun_out/${TAG}_pytest.log; tail -2 gpurun_out/${TAG}_smoke.log; cat gpurun_out/${TAG}_bench.json; cat gpurun_out/${TAG}_bench_ref.json; tail -5 gpurun_out/${TAG}_bench.err

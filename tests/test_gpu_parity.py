@@ -287,6 +287,38 @@ def test_edge_inputs_all_stages(A, R, workdir, name):
     assert (ocands["reg"] == -1).sum() > 5, "no unmapped placeholders exercised"
 
 
+@pytest.mark.parametrize("cfg", ["stlfr", "tellseq", "len100", "len250"])
+def test_config_flavours_all_stages(A, R, workdir, cfg):
+    """BASELINE.json configs[2..4] as parity cases: stLFR-style barcodes (hundreds of pairs per barcode: long candidate lists,
+    many molecules per barcode in the optimizer), TELLseq-style with 30 % invalid barcodes (unbarcoded path: run_rfa = 0 for
+    those, aligner.go:1018-1030), and the microbench read lengths 100 / 250."""
+    fa, ctg, _ = util.make_dataset("rep600k", workdir)
+    R.load(fa); A.load_index(fa)
+    if cfg == "stlfr":
+        rs = S.simulate_linked_reads(ctg, n_barcodes=4, seed=31, style="stlfr", dash_suffix=True, mol_per_bc=14.0, pairs_per_mol=22.0, sub=0.015)
+        assert np.diff(rs.bc_off).max() > 250
+        run_rfa = np.ones(len(rs.bc_off) - 1, np.uint8)
+    elif cfg == "tellseq":
+        rs = S.simulate_linked_reads(ctg, n_barcodes=60, seed=32, style="tellseq", invalid_frac=0.3, sub=0.015)
+        g = np.random.default_rng(32)
+        run_rfa = (g.random(len(rs.bc_off) - 1) >= 0.3).astype(np.uint8)  # VX:i:0 barcodes are not molecule-grouped
+        assert 0 < run_rfa.sum() < len(run_rfa)
+    else:
+        rs = S.simulate_linked_reads(ctg, n_barcodes=25, seed=33, read_len=int(cfg[3:]), sub=0.02, ins=0.002, dele=0.002)
+        run_rfa = np.ones(len(rs.bc_off) - 1, np.uint8)
+    seeds = np.array([A.name_seed(n) for n in rs.names], dtype=np.int64)
+    res = A.align_batch(rs.seq, rs.off, rs.bc_off, stages=15, run_rfa=run_rfa, rand_seed=seeds)
+    ref = R.batch(rs.seq, rs.off, rescue=True, cigar=True, threads=8)
+    assert np.array_equal(res["reg_off"], ref["reg_off"]) and res["regs"].tobytes() == ref["regs"].tobytes(), cfg
+    a, e = res["alns"], ref["aln"]
+    for f, jx in (("pos", 0), ("rid", 1), ("is_rev", 2), ("nm", 3), ("n_cigar", 4), ("score", 6), ("sub", 7)):
+        assert np.array_equal(a[f], e[:, jx]), (cfg, f)
+    for i in range(len(a)):
+        assert np.array_equal(res["cigar"][a["cigar_off"][i]:a["cigar_off"][i] + a["n_cigar"][i]], ref["cigar"][e[i, 5]:e[i, 5] + e[i, 4]]), (cfg, i)
+    oc, ocands, olmp = util.PlaceOracle(fa).place(rs.seq, rs.off, rs.bc_off, run_rfa, seeds, ref["reg_off"], ref["regs"], ref["aln"], ref["cigar"])
+    _check_place(res, oc, ocands, olmp, cfg)
+
+
 def test_concurrent_batches_on_one_handle(A, R, workdir):
     """Two host threads in flight on one handle (the reference's worker goroutines share one index, aligner.go:335-337):
     each call gets its own workspace; results equal the sequential ones and the reference's."""
