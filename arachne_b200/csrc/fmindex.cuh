@@ -30,7 +30,8 @@ struct FMIndex {
     int sa_intv;
     // bi-interval of every kmer_k-mer (16 bytes each, packed like the seeding kernel's list entries), or null: lets the
     // LAST-like pass (bwt_seed_strategy1) start kmer_k bases in instead of kmer_k-1 dependent bwt_extend calls (index.cuh)
-    const void* kmer;
+    const void* kmer;      // level kmer_k
+    const void* kmer_all;  // levels 1..kmer_k back to back: level L (4^L entries) starts at entry (4^L - 4) / 3
     int kmer_k;
 };
 

@@ -75,25 +75,29 @@ __global__ void __launch_bounds__(256) k_sa_densify(FMIndex fm, uint64_t* dense,
     }
 }
 
-// Bi-interval of every K-mer: one thread per (K-1)-mer walks K-2 forward extensions from the single-base interval
-// (bwt_set_intv, bwt.h:80; forward = bwt_extend(.., is_back = 0) with the complement, bwt.c:304-307) and writes the four
-// children of the last one.  Entry = the seeding kernel's packed list entry (x0, x1, x2: 40 bits each).
-__global__ void __launch_bounds__(256) k_kmer_table(FMIndex fm, uint4* tab, int K) {
-    const uint64_t n_pre = 1ull << (2 * (K - 1));
-    for (uint64_t p = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; p < n_pre; p += (uint64_t)gridDim.x * blockDim.x) {
+// Bi-intervals of every L-mer, L = 1..K, level by level: level 1 is bwt_set_intv (bwt.h:80); an entry of level L+1 is one
+// forward extension (bwt_extend(.., is_back = 0) with the complement base, bwt.c:304-307) of its level-L prefix -- the
+// chain the reference's seeding would walk.  Entry = the seeding kernel's packed list entry (x0, x1, x2: 40 bits each).
+__device__ __forceinline__ uint4 kmer_pack(const Intv& o) {
+    const uint64_t lo = o.x0 | (o.x1 << 40), hi = (o.x1 >> 24) | (o.x2 << 16);
+    return make_uint4((unsigned)lo, (unsigned)(lo >> 32), (unsigned)hi, (unsigned)(hi >> 32));
+}
+__host__ __device__ inline uint64_t kmer_level_off(int L) { return ((1ull << (2 * L)) - 4) / 3; }
+__global__ void __launch_bounds__(256) k_kmer_level(FMIndex fm, uint4* all, int L) {  // fills level L+1 from level L (L = 0: level 1)
+    if (L == 0) {
+        if (blockIdx.x == 0 && threadIdx.x < 4) { Intv ik; fm_set_intv(fm, (int)threadIdx.x, ik); all[threadIdx.x] = kmer_pack(ik); }
+        return;
+    }
+    const uint64_t n = 1ull << (2 * L);
+    const uint4* src = all + kmer_level_off(L);
+    uint4* dst = all + kmer_level_off(L + 1);
+    for (uint64_t p = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; p < n; p += (uint64_t)gridDim.x * blockDim.x) {
+        const uint4 v = src[p];
+        const uint64_t lo = (uint64_t)v.y << 32 | v.x, hi = (uint64_t)v.w << 32 | v.z;
         Intv ik, ok[4];
-        fm_set_intv(fm, (int)(p >> (2 * (K - 2))) & 3, ik);
-        for (int t = 1; t < K - 1; ++t) {
-            const int b = (int)(p >> (2 * (K - 2 - t))) & 3;
-            fm_extend(fm, ik, ok, 0);
-            ik = b == 0 ? ok[3] : b == 1 ? ok[2] : b == 2 ? ok[1] : ok[0];
-        }
+        ik.x0 = lo & 0xffffffffffull; ik.x1 = (lo >> 40) | ((hi & 0xffffull) << 24); ik.x2 = (hi >> 16) & 0xffffffffffull; ik.info = 0;
         fm_extend(fm, ik, ok, 0);
-        for (int b = 0; b < 4; ++b) {
-            const Intv& o = ok[3 - b];
-            const uint64_t lo = o.x0 | (o.x1 << 40), hi = (o.x1 >> 24) | (o.x2 << 16);
-            tab[p * 4 + b] = make_uint4((unsigned)lo, (unsigned)(lo >> 32), (unsigned)hi, (unsigned)(hi >> 32));
-        }
+        for (int b = 0; b < 4; ++b) dst[p * 4 + b] = kmer_pack(ok[3 - b]);
     }
 }
 
@@ -205,7 +209,7 @@ inline int index_load(const char* prefix_, int device, arachne_index** out) {
     idx->ref.l_pac = idx->l_pac;
     idx->ref.n_seqs = (int)idx->contigs.size();
     idx->device_bytes = img + sab + pacb + sizeof(Contig) * idx->contigs.size();
-    fm.kmer = nullptr; fm.kmer_k = 0;
+    fm.kmer = nullptr; fm.kmer_all = nullptr; fm.kmer_k = 0;
     {   // k-mer table for the LAST-like seeding pass: K = min(14, log4(seq_len) - 1), off below 8 (ARACHNE_SEED_KMER=0 disables, =K forces)
         int K = 0;
         for (uint64_t v = fm.seq_len; v > 3; v >>= 2) ++K;
@@ -213,17 +217,22 @@ inline int index_load(const char* prefix_, int device, arachne_index** out) {
         if (const char* ev = getenv("ARACHNE_SEED_KMER")) K = atoi(ev);
         size_t free_b = 0, total_b = 0;
         cudaMemGetInfo(&free_b, &total_b);
-        if (K >= 8 && K <= 15 && (16ull << (2 * K)) < free_b / 4 && fm.seq_len < (1ull << 40) - 2) {
+        const uint64_t n_ent = K >= 1 ? kmer_level_off(K + 1) : 0;
+        if (K >= 8 && K <= 15 && n_ent * 16 < free_b / 4 && fm.seq_len < (1ull << 40) - 2) {
             void* dk = nullptr;
-            e = cudaMalloc(&dk, 16ull << (2 * K));
+            e = cudaMalloc(&dk, n_ent * 16);
             if (e == cudaSuccess) {
-                FMIndex f2 = fm;  // the table is filled with the file's SA sampling still in place (the SA is not used)
-                k_kmer_table<<<148 * 8, 256>>>(f2, reinterpret_cast<uint4*>(dk), K);
-                e = cudaGetLastError();
+                FMIndex f2 = fm;  // the SA is not used here
+                for (int L = 0; L < K && e == cudaSuccess; ++L) {
+                    k_kmer_level<<<148 * 8, 256>>>(f2, reinterpret_cast<uint4*>(dk), L);
+                    e = cudaGetLastError();
+                }
                 if (e == cudaSuccess) e = cudaDeviceSynchronize();
             }
-            if (e == cudaSuccess) { idx->d_kmer = dk; fm.kmer = dk; fm.kmer_k = K; idx->device_bytes += 16ull << (2 * K); }
-            else { if (dk) cudaFree(dk); (void)cudaGetLastError(); }
+            if (e == cudaSuccess) {
+                idx->d_kmer = dk; fm.kmer_all = dk; fm.kmer = reinterpret_cast<const uint4*>(dk) + kmer_level_off(K); fm.kmer_k = K;
+                idx->device_bytes += n_ent * 16;
+            } else { if (dk) cudaFree(dk); (void)cudaGetLastError(); }
         }
     }
     {   // densify the sampled SA when HBM has the room (ARACHNE_SA_INTV=1|2|4|8|16|32 overrides; 32 keeps the file's sampling)

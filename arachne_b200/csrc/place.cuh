@@ -226,7 +226,7 @@ struct RfaArgs {
     unsigned* next;
 };
 
-constexpr int PLACE_T = 64;  // threads per barcode block: a 30-pair barcode has ~100 candidates; small blocks keep more barcodes in flight and barriers cheap
+constexpr int PLACE_T = 32;  // threads per barcode block: a 30-pair barcode has ~100 candidates; small blocks keep more barcodes in flight and barriers cheap
 
 __device__ __forceinline__ int place_block_scan_excl(int v, int* total, int* sh /* PLACE_T/32 + 1 ints */) {
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;

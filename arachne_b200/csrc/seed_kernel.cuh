@@ -38,6 +38,12 @@ __device__ __forceinline__ void pk_unpack(uint4 v, uint64_t& x0, uint64_t& x1, u
     end = (unsigned)(hi >> 56);
 }
 
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+    const unsigned a = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(a), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory"); }
+
 enum { SP_IDLE = 0, SP_P1_SCAN, SP_FWD, SP_BWD, SP_P2_NEXT, SP_P3_SCAN, SP_P3, SP_DONE };
 
 template <int MIN_BLOCKS>
@@ -58,6 +64,10 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) k_seed2(FMIndex fm, MemOpt op
     // task kinds cost about 2:1 in bwt_extend calls (passes 1+2 vs pass 3): every third warp starts on the LAST-like queue
     // (1:5 when pass 3 starts from the k-mer table)
     const int kmer_k = (use_kmer && fm.kmer && fm.kmer_k <= opt.min_seed_len) ? fm.kmer_k : 0;
+    // the SMEM passes' forward extension starts from the table too (all levels 1..K, fetched with K independent copies into
+    // the lane's shared list slots) when those slots can hold them
+    const bool kmer_fwd = kmer_k && fm.kmer_all && slist_n >= kmer_k;
+    bool fresh = false;  // a forward pass was just set up at x
     const int pref_kind = (opt.max_mem_intv > 0 && (tid >> 5) % (kmer_k ? 6 : 3) == 2) ? 1 : 0;
 
     int phase = SP_IDLE, r = 0, len = 0, x = 0, i = 0, pass = 1;
@@ -117,7 +127,7 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) k_seed2(FMIndex fm, MemOpt op
                     if (b > 3) break;  // bwt_smem1a returns at once on an ambiguous base (cannot happen inside a match)
                     kx0 = fm_L2(fm, b) + 1; kx2 = fm_L2(fm, b + 1) - fm_L2(fm, b); kx1 = fm_L2(fm, 3 - b) + 1; kend = x + 1;
                     i = x + 1; n = 0; last_start = 0x7fffffff;
-                    phase = SP_FWD;
+                    phase = SP_FWD; fresh = true;
                 } else { phase = SP_IDLE; break; }
             }
             if (phase == SP_P1_SCAN) {
@@ -127,7 +137,7 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) k_seed2(FMIndex fm, MemOpt op
                 kx0 = fm_L2(fm, b) + 1; kx2 = fm_L2(fm, b + 1) - fm_L2(fm, b); kx1 = fm_L2(fm, 3 - b) + 1; kend = x + 1;
                 min_intv = 1;
                 i = x + 1; n = 0; last_start = 0x7fffffff;
-                phase = SP_FWD;
+                phase = SP_FWD; fresh = true;
             }
             if (phase == SP_P3_SCAN) {
                 // bwt_seed_strategy1 (bwt.c:358-379) from x: nothing is tested before the match is min_seed_len + 1 long, so
@@ -154,6 +164,43 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) k_seed2(FMIndex fm, MemOpt op
                     break;
                 }
                 if (phase == SP_IDLE) break;
+            }
+            if (fresh) {
+                // bwt_smem1a's forward loop (bwt.c:300-316) over the first m <= K bases without stepping: the interval after
+                // each base is a table entry; what the loop does with them (push on a size change, stop below min_intv) is
+                // replayed from shared memory.  An ambiguous base or the read end inside the window ends the window there and
+                // the ordinary stepping takes over (and closes the pass).
+                fresh = false;
+                if (kmer_fwd) {
+                    uint32_t km = 0;
+                    int m = 0;
+                    const int lim = len - x < kmer_k ? len - x : kmer_k;
+                    for (; m < lim; ++m) { const int bb = __ldg(q + x + m); if (bb > 3) break; km = km << 2 | (uint32_t)bb; }
+                    if (m >= 2) {
+                        const uint4* all = reinterpret_cast<const uint4*>(fm.kmer_all);
+                        for (int L = 1; L <= m; ++L) cp_async16(&sl[(L - 1) * 256], all + ((1ull << (2 * L)) - 4) / 3 + (km >> (2 * (m - L))));
+                        cp_async_wait_all();
+                        unsigned spare;
+                        pk_unpack(sl[0], kx0, kx1, kx2, spare);
+                        bool stop = false;
+                        int L = 1;
+                        for (; L < m; ++L) {
+                            uint64_t a0, a1, a2;
+                            pk_unpack(sl[L * 256], a0, a1, a2, spare);
+                            if (a2 != kx2) {
+                                lput(n++, pk_pack(kx0, kx1, kx2, (unsigned)(x + L)));
+                                if (a2 < min_intv) { stop = true; break; }
+                            }
+                            kx0 = a0; kx1 = a1; kx2 = a2;
+                        }
+                        st_calls += (unsigned)(stop ? L : L - 1); st_blocks += 2u * (unsigned)(stop ? L : L - 1);
+                        if (stop) {
+                            kend = (unsigned)(x + L); ret = (int)kend;
+                            hi = n; lo = 0; j = hi - 1; ncur = 0; i = x - 1;
+                            phase = SP_BWD;
+                        } else { kend = (unsigned)(x + m); i = x + m; }
+                    }
+                }
             }
             if (phase == SP_FWD) {
                 int b = i < len ? (int)__ldg(q + i) : 4;
