@@ -27,7 +27,7 @@ int arachne_index_set_option(arachne_index_t* idx, const char* name, int64_t val
     if (!idx || !name) { set_error("arachne_index_set_option: null argument"); return ARACHNE_ERR_ARG; }
     std::lock_guard<std::mutex> lk(idx->mu);  // takes effect with the next batch that starts
     if (!strcmp(name, "seed_kmer")) idx->opt_seed_kmer = value != 0;
-    else if (!strcmp(name, "seed_blocks_per_sm") && (value == 3 || value == 4)) idx->opt_seed_blocks = (int)value;
+    else if (!strcmp(name, "seed_blocks_per_sm") && value >= 1 && value <= 4) idx->opt_seed_blocks = (int)value;
     else if (!strcmp(name, "seed_shared_list") && value >= -1 && value <= 16) idx->opt_seed_slist = (int)value;
     else { set_error("arachne_index_set_option: unknown option or value: %s=%lld", name, (long long)value); return ARACHNE_ERR_ARG; }
     return ARACHNE_OK;
@@ -127,7 +127,7 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
     unsigned long long* hs = W.h_scalars;
     // ---- seeding (retry with a larger per-read interval capacity if a read overflows it) ----
     if (idx->fm.seq_len >= (1ull << 40) - 2) { set_error("reference too long for the packed interval lists (2*l_pac must stay below 2^40)"); return fail(ARACHNE_ERR_ARG); }
-    const int seed_bpsm = seed_bpsm_opt == 4 ? 4 : 3, seed_blocks = sms * seed_bpsm, seed_T = seed_blocks * 256, list_rows = 2 * L1;
+    const int seed_bpsm = seed_bpsm_opt >= 1 && seed_bpsm_opt <= 4 ? seed_bpsm_opt : 3, seed_blocks = sms * seed_bpsm, seed_T = seed_blocks * 256, list_rows = 2 * L1;
     AR_ALLOC(W.d_scratch, (size_t)seed_T * list_rows * sizeof(uint4));
     int intv_cap = 32;
     cudaEventRecord(ev[0], st);
