@@ -11,16 +11,15 @@ static Workspace* get_ws(arachne_index_t* idx, int slot) {
     return reinterpret_cast<Workspace*>(idx->ws[slot]);
 }
 
-// Take a free workspace slot (first one that is idle, else wait on them in turn).
+// Take a free workspace slot: the first idle one; when all are busy, poll (a batch lasts ~100 ms, the poll 100 us).
 static std::unique_lock<std::mutex> take_ws(arachne_index_t* idx, int* slot) {
-    for (int k = 0; k < arachne_index::N_WS; ++k) {
-        std::unique_lock<std::mutex> l(idx->ws_mu[k], std::try_to_lock);
-        if (l.owns_lock()) { *slot = k; return l; }
+    for (;;) {
+        for (int k = 0; k < arachne_index::N_WS; ++k) {
+            std::unique_lock<std::mutex> l(idx->ws_mu[k], std::try_to_lock);
+            if (l.owns_lock()) { *slot = k; return l; }
+        }
+        std::this_thread::sleep_for(std::chrono::microseconds(100));
     }
-    unsigned k;
-    { std::lock_guard<std::mutex> g(idx->mu); k = idx->ws_rr++ % arachne_index::N_WS; }
-    *slot = (int)k;
-    return std::unique_lock<std::mutex>(idx->ws_mu[k]);
 }
 
 int arachne_index_set_option(arachne_index_t* idx, const char* name, int64_t value) {

@@ -9,6 +9,8 @@
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
+#include <thread>
+#include <chrono>
 #include "fmindex.cuh"
 #include "bwt_image.h"
 #include "../../include/arachne_cuda.h"
@@ -35,11 +37,10 @@ struct arachne_index {
     // buf=NULL); here the scratch is the handle's: N_WS slots, so that two host threads can be in flight on one handle and
     // one batch's host<->device copies overlap the other's kernels; further callers queue.  `mu` guards the small
     // shared state (options, stream choice, the pool of recycled pinned result sets).
-    static constexpr int N_WS = 2;
+    static constexpr int N_WS = 3;
     std::mutex mu;
     std::mutex ws_mu[N_WS];
-    void* ws[N_WS] = {nullptr, nullptr};
-    unsigned ws_rr = 0;
+    void* ws[N_WS] = {};
     std::vector<void*> priv_pool;
     void* user_stream = nullptr;
     bool has_user_stream = false;
