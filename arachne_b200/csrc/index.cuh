@@ -37,7 +37,7 @@ struct arachne_index {
     // buf=NULL); here the scratch is the handle's: N_WS slots, so that two host threads can be in flight on one handle and
     // one batch's host<->device copies overlap the other's kernels; further callers queue.  `mu` guards the small
     // shared state (options, stream choice, the pool of recycled pinned result sets).
-    static constexpr int N_WS = 3;
+    static constexpr int N_WS = 2;  // 3 in flight measured slower (persistent kernels of three batches oversubscribe the SMs)
     std::mutex mu;
     std::mutex ws_mu[N_WS];
     void* ws[N_WS] = {};
