@@ -224,7 +224,7 @@ def run_reference(args, rank, world):
                                   "sample": f"{npairs} pairs per step of the same workload (oracle/_ref: the reference's BWA C sources, gobwa.go call sequence, {threads} pthreads over pairs)"},
                  "e2e": {"value": val, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                  "gpu_launches": 0, "roofline": None})
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def base_line(args, world, value, ms):
@@ -240,8 +240,25 @@ def base_line(args, world, value, ms):
                        "l2_policy": "index (3.1 GB BWT + 1.55 GB SA + 0.78 GB pac at 3.1 Gb) and per-batch arenas exceed the 126 MB L2; distinct batches are cycled"}}
 
 
+_REAL_STDOUT = None
+
+
+def emit(line: dict):
+    """The ONE JSON line goes to the process's real stdout; everything else that writes to fd 1 during the run (NCCL
+    prints its version banner there) has been pointed at stderr."""
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def main():
+    global _REAL_STDOUT
     args = parse_args()
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
         return run_reference(args, rank, world)
@@ -355,7 +372,7 @@ def main():
             line["cpu_baseline"] = {"value": n / dt, "unit": "pairs/s", "cores": threads, "kind": "reference",
                                     "sample": f"first {n} pairs of batch 0 (whole barcodes), oracle/_ref = the reference's BWA C sources driven as gobwa.go drives them, {threads} pthreads"}
             line["parity_sample"] = parity_sample(A)
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
