@@ -528,6 +528,35 @@ void arachne_index_free(arachne_index_t* idx) {
 int64_t arachne_index_l_pac(const arachne_index_t* idx) { return idx ? idx->l_pac : -1; }
 int32_t arachne_index_n_seqs(const arachne_index_t* idx) { return idx ? (int32_t)idx->contigs.size() : -1; }
 size_t arachne_index_device_bytes(const arachne_index_t* idx) { return idx ? idx->device_bytes : 0; }
+int64_t arachne_index_fetch_seq(const arachne_index_t* idx, int64_t* beg, int64_t mid, int64_t* end, int32_t* rid, uint8_t* out) {
+    if (!idx || !beg || !end || !out) { set_error("arachne_index_fetch_seq: null argument"); return ARACHNE_ERR_ARG; }
+    if (*end < *beg) { const int64_t t = *beg; *beg = *end; *end = t; }
+    const int64_t l_pac = idx->l_pac;
+    if (!(*beg <= mid && mid < *end) || mid < 0 || mid >= 2 * l_pac) {  // the reference asserts here (bntseq.c:427)
+        set_error("arachne_index_fetch_seq: mid %lld outside [%lld, %lld) or the reference", (long long)mid, (long long)*beg, (long long)*end);
+        return ARACHNE_ERR_ARG;
+    }
+    const bool is_rev = mid >= l_pac;                        // bns_depos, bntseq.h
+    const int64_t pos_f = is_rev ? 2 * l_pac - 1 - mid : mid;
+    int lo = 0, hi = (int)idx->contigs.size(), r = 0;        // bns_pos2rid, bntseq.c:346-363
+    while (lo < hi) {
+        const int m = (lo + hi) >> 1;
+        if (pos_f >= idx->contigs[m].offset) { r = m; lo = m + 1; } else hi = m;
+    }
+    int64_t far_beg = idx->contigs[r].offset, far_end = far_beg + idx->contigs[r].len;
+    if (is_rev) { const int64_t t = far_beg; far_beg = 2 * l_pac - far_end; far_end = 2 * l_pac - t; }
+    if (*beg < far_beg) *beg = far_beg;
+    if (*end > far_end) *end = far_end;
+    if (rid) *rid = r;
+    const uint8_t* pac = idx->h_pac.data();
+    int64_t n = 0;
+    for (int64_t p = *beg; p < *end; ++p) {                  // bns_get_seq, bntseq.c:398-419
+        const int64_t f = p >= l_pac ? 2 * l_pac - 1 - p : p;
+        const int b = pac[f >> 2] >> ((~f & 3) << 1) & 3;
+        out[n++] = (uint8_t)(p >= l_pac ? 3 - b : b);
+    }
+    return n;
+}
 int arachne_index_contig(const arachne_index_t* idx, int32_t rid, const char** name, int64_t* offset, int32_t* len) {
     if (!idx || rid < 0 || rid >= (int32_t)idx->contigs.size()) { set_error("contig id out of range"); return ARACHNE_ERR_ARG; }
     if (name) *name = idx->names[rid].c_str();

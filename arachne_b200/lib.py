@@ -92,6 +92,8 @@ class ArachneCuda:
         L.arachne_index_device_bytes.restype = C.c_size_t; L.arachne_index_device_bytes.argtypes = [C.c_void_p]
         L.arachne_index_contig.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_char_p), C.POINTER(C.c_int64), C.POINTER(C.c_int32)]
         L.arachne_index_set_stream.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+        L.arachne_index_fetch_seq.restype = C.c_int64
+        L.arachne_index_fetch_seq.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.c_int64, C.POINTER(C.c_int64), C.POINTER(C.c_int32), C.POINTER(C.c_uint8)]
         L.arachne_index_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_int64]
         L.arachne_opts_default.argtypes = [C.POINTER(MemOpt)]
         L.arachne_align_batch.argtypes = [C.c_void_p, C.POINTER(MemOpt), C.POINTER(BatchIn), C.POINTER(C.POINTER(BatchOut))]
@@ -192,6 +194,15 @@ class ArachneCuda:
                                                    _p(q_off, C.c_int64), _p(t, C.c_uint8), _p(t_off, C.c_int64), _p(w, C.c_int32),
                                                    _p(sc, C.c_int32), _p(coff, C.c_int64) if want_cigar else None, _p(cig, C.c_uint32), cap))
         return sc, coff, cig[:coff[-1]]
+
+    def fetch_seq(self, beg: int, mid: int, end: int):
+        """bns_fetch_seq as GetSeq uses it (gobwa.go:59): (bases, clamped beg, clamped end, rid)."""
+        b, e, rid = C.c_int64(beg), C.c_int64(end), C.c_int32(-1)
+        out = np.zeros(max(1, abs(end - beg)), np.uint8)
+        n = self.lib.arachne_index_fetch_seq(self.idx, C.byref(b), mid, C.byref(e), C.byref(rid), _p(out, C.c_uint8))
+        if n < 0:
+            self._ck(int(n))
+        return out[:n].copy(), b.value, e.value, rid.value
 
     def set_option(self, name: str, value: int):
         self._ck(self.lib.arachne_index_set_option(self.idx, name.encode(), int(value)))

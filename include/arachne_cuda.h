@@ -8,7 +8,8 @@
  *   (1) batch API (new): one call per batch of barcodes instead of one cgo call per read pair / candidate;
  *   (2) stage entry points: the individual kernels on caller-supplied problems -- these are what the parity
  *       tests and the config-5 ksw_extend2 microbench drive.
- * The per-pair compat shims with BWA's own symbol names are declared in arachne_bwa_compat.h.
+ * The per-pair Go entry points (GoBwaMemMateSW / GoBwaSmithWaterman / GetSeq) are kept on the Go side as thin shims over
+ * this batch ABI (INTEGRATION.md sections 2 and 4); BWA's own C symbol names are not re-exported.
  */
 #ifndef ARACHNE_CUDA_H_
 #define ARACHNE_CUDA_H_
@@ -201,6 +202,11 @@ int64_t arachne_index_l_pac(const arachne_index_t *idx);
 int32_t arachne_index_n_seqs(const arachne_index_t *idx);
 int arachne_index_contig(const arachne_index_t *idx, int32_t rid, const char **name, int64_t *offset, int32_t *len);
 size_t arachne_index_device_bytes(const arachne_index_t *idx);
+/* bns_fetch_seq (bwa/bntseq.c:421-446) as GoBwaReference.GetSeq calls it (gobwa.go:50-80): bases (codes 0..3) of the
+ * forward-reverse coordinate range [*beg, *end) clamped to the contig (and strand) that holds `mid`; the clamped range is
+ * written back, *rid receives the contig.  `out` must hold the unclamped end - beg bytes.  Host only: served from the
+ * handle's host copy of the packed reference.  Returns the number of bases or a negative ARACHNE_ERR_*. */
+int64_t arachne_index_fetch_seq(const arachne_index_t *idx, int64_t *beg, int64_t mid, int64_t *end, int32_t *rid, uint8_t *out);
 /* ---- index construction: replaces the BWT/SA half of `bwa index` = bwa_idx_build steps 2, 3 and 5 (bwa/bwtindex.c:244-300:
  * bwt_pac2bwt :61-123, bwt_bwtupdate_core :151-173, bwt_cal_sa bwa/bwt.c:62-84) on the device.  Reads <prefix>.pac (forward
  * strand, as bns_fasta2bntseq(for_only=1) leaves it, bwa/bntseq.c:275-328) and <prefix>.ann, writes <prefix>.bwt and

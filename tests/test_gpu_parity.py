@@ -319,6 +319,35 @@ def test_config_flavours_all_stages(A, R, workdir, cfg):
     _check_place(res, oc, ocands, olmp, cfg)
 
 
+def test_fetch_seq_matches_reference_text(A, workdir):
+    """arachne_index_fetch_seq = bns_fetch_seq as GetSeq calls it: forward ranges read the contig, reverse ranges its
+    reverse complement, both clamped to the contig that holds `mid`."""
+    from arachne_b200.lib import ArachneError
+    fa, ctg, _ = util.make_dataset("rep600k", workdir)
+    A.load_index(fa)
+    ann = util.read_ann(fa)
+    l_pac = A.l_pac
+    genome = np.concatenate([s for _, s in ctg])
+    nmask = genome > 3  # N became a random base in the .pac (bntseq.c:261): compare elsewhere
+    g = np.random.default_rng(8)
+    offs = np.cumsum([0] + [len(s) for _, s in ctg])
+    for _ in range(300):
+        ci = int(g.integers(0, len(ctg))); L = len(ctg[ci][1])
+        a = int(g.integers(-50, L - 10)); b = a + int(g.integers(1, 400))
+        beg, end = offs[ci] + a, offs[ci] + b          # may hang over either contig end
+        mid = int(np.clip((beg + end) >> 1, offs[ci], offs[ci] + L - 1))
+        seq, cb, ce, rid = A.fetch_seq(int(beg), mid, int(end))
+        assert rid == ci and cb == max(beg, offs[ci]) and ce == min(end, offs[ci] + L) and len(seq) == ce - cb
+        ok = ~nmask[cb:ce]
+        assert np.array_equal(seq[ok], genome[cb:ce][ok])
+        rb, re_, rmid = 2 * l_pac - ce, 2 * l_pac - cb, 2 * l_pac - 1 - mid  # the same bases on the reverse strand
+        rseq, rcb, rce, rrid = A.fetch_seq(int(rb), int(rmid), int(re_))
+        assert rrid == ci and (rcb, rce) == (rb, re_)
+        assert np.array_equal((3 - rseq[::-1])[ok], genome[cb:ce][ok])
+    with pytest.raises(ArachneError):
+        A.fetch_seq(10, 500, 20)  # mid outside the range
+
+
 def test_concurrent_batches_on_one_handle(A, R, workdir):
     """Two host threads in flight on one handle (the reference's worker goroutines share one index, aligner.go:335-337):
     each call gets its own workspace; results equal the sequential ones and the reference's."""
