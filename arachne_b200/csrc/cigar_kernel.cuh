@@ -45,9 +45,14 @@ struct RegView {
     int64_t tpos;   // forward-strand coordinate of target base 0
     int lq, rlen, qb, qe, rev;
     __device__ __forceinline__ int Q(int i) const { return rev ? q[qe - 1 - i] : q[qb + i]; }
+    // 16 target bases per 32-bit load of the packed reference, kept across calls: the DP reads one target base per row and
+    // the walks move along the region, so a load (a DRAM round trip on a 3.1 Gb reference) is needed every 16th base only
+    mutable uint32_t tw = 0;
+    mutable int64_t tw_at = -1;
     __device__ __forceinline__ int T(int i) const {
         const int64_t p = tpos + i;
-        const int b = (__ldg(pac + (p >> 2)) >> ((~p & 3) << 1)) & 3;
+        if ((p >> 4) != tw_at) { tw_at = p >> 4; tw = __ldg(reinterpret_cast<const uint32_t*>(pac) + tw_at); }
+        const int b = (int)(tw >> ((((unsigned)p >> 2) & 3u) << 3) >> ((~(unsigned)p & 3u) << 1)) & 3;
         return rev ? 3 - b : b;
     }
 };
