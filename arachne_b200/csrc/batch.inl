@@ -27,6 +27,7 @@ int arachne_index_set_option(arachne_index_t* idx, const char* name, int64_t val
     std::lock_guard<std::mutex> lk(idx->mu);  // takes effect with the next batch that starts
     if (!strcmp(name, "seed_kmer")) idx->opt_seed_kmer = value != 0;
     else if (!strcmp(name, "seed_blocks_per_sm") && value >= 1 && value <= 4) idx->opt_seed_blocks = (int)value;
+    else if (!strcmp(name, "seed_direct")) idx->opt_seed_direct = value != 0;
     else if (!strcmp(name, "seed_shared_list") && value >= -1 && value <= 16) idx->opt_seed_slist = (int)value;
     else { set_error("arachne_index_set_option: unknown option or value: %s=%lld", name, (long long)value); return ARACHNE_ERR_ARG; }
     return ARACHNE_OK;
@@ -73,12 +74,12 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
     Workspace& W = *wsp;
     const int sms = sm_count(idx->device);
     cudaStream_t st;
-    int use_seed_kmer, seed_bpsm_opt, seed_slist;
+    int use_seed_kmer, seed_bpsm_opt, seed_slist, use_seed_direct;
     BatchPriv* priv = nullptr;
     {
         std::lock_guard<std::mutex> g(idx->mu);
         st = idx->has_user_stream ? reinterpret_cast<cudaStream_t>(idx->user_stream) : W.own_stream;
-        use_seed_kmer = idx->opt_seed_kmer; seed_bpsm_opt = idx->opt_seed_blocks; seed_slist = idx->opt_seed_slist;
+        use_seed_kmer = idx->opt_seed_kmer; seed_bpsm_opt = idx->opt_seed_blocks; seed_slist = idx->opt_seed_slist; use_seed_direct = idx->opt_seed_direct;
         if (!idx->priv_pool.empty()) { priv = reinterpret_cast<BatchPriv*>(idx->priv_pool.back()); idx->priv_pool.pop_back(); }
     }
     cudaEvent_t* ev = W.ev;  // seed | sa | chain | extend | rescue | gather | cigar | end
@@ -130,6 +131,17 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
     AR_ALLOC(W.d_scratch, (size_t)seed_T * list_rows * sizeof(uint4));
     int intv_cap = 32;
     cudaEventRecord(ev[0], st);
+    // the reads 2-bit packed with their masks: what the seeding lanes keep in shared memory (seed_kernel.cuh)
+    const ulonglong2* d_qpk = nullptr;
+    const int qstride = seed_qstride(maxlen);
+    const int seed_direct = use_seed_direct && idx->fm.isa && idx->fm.text;
+    {
+        AR_ALLOC(W.d_qpk, (size_t)n_reads * qstride * sizeof(ulonglong2));
+        k_pack_reads<<<sms * 8, 256, 0, st>>>(d_seq, d_off, (int)n_reads, qstride, W.d_qpk.as<ulonglong2>());
+        AR_TRY(cudaGetLastError());
+        d_qpk = W.d_qpk.as<ulonglong2>();
+        ++nl;
+    }
     for (int attempt = 0;; ++attempt) {
         AR_ALLOC(W.d_arena, (size_t)n_reads * intv_cap * sizeof(Intv));
         AR_TRY(cudaMemsetAsync(W.d_misc.p, 0, 64, st));
@@ -138,16 +150,16 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
         SeedOut so; so.intv = W.d_arena.as<Intv>(); so.intv_n = W.d_intv_n.as<int>(); so.n_sa = W.d_nsa.as<unsigned int>(); so.cap = intv_cap;
         ++nl;
         // shared-memory head of the interval lists: as many entries as fit next to the resident blocks (16 at 3 blocks/SM)
-        const int slist_n = seed_slist >= 0 ? seed_slist : (seed_bpsm == 4 ? 12 : 16);
-        const size_t seed_smem = (size_t)slist_n * 256 * sizeof(uint4);
+        int slist_n = 0, nwq = 0;
+        const size_t seed_smem = seed_smem_plan(maxlen, seed_bpsm, seed_slist, &slist_n, &nwq);
         if (seed_bpsm == 4) {
             AR_TRY(cudaFuncSetAttribute(k_seed2<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)seed_smem));
-            k_seed2<4><<<seed_blocks, 256, seed_smem, st>>>(idx->fm, opt, d_seq, d_off, (int)n_reads, maxlen, W.d_scratch.as<uint4>(), list_rows, so,
-                                                             W.d_misc.as<unsigned int>(), W.d_cnt.as<Counters>(), use_seed_kmer, slist_n);
+            k_seed2<4><<<seed_blocks, 256, seed_smem, st>>>(idx->fm, opt, d_off, (int)n_reads, maxlen, W.d_scratch.as<uint4>(), list_rows, so,
+                                                             W.d_misc.as<unsigned int>(), W.d_cnt.as<Counters>(), use_seed_kmer, slist_n, d_qpk, qstride, nwq, seed_direct);
         } else {
             AR_TRY(cudaFuncSetAttribute(k_seed2<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)seed_smem));
-            k_seed2<3><<<seed_blocks, 256, seed_smem, st>>>(idx->fm, opt, d_seq, d_off, (int)n_reads, maxlen, W.d_scratch.as<uint4>(), list_rows, so,
-                                                             W.d_misc.as<unsigned int>(), W.d_cnt.as<Counters>(), use_seed_kmer, slist_n);
+            k_seed2<3><<<seed_blocks, 256, seed_smem, st>>>(idx->fm, opt, d_off, (int)n_reads, maxlen, W.d_scratch.as<uint4>(), list_rows, so,
+                                                             W.d_misc.as<unsigned int>(), W.d_cnt.as<Counters>(), use_seed_kmer, slist_n, d_qpk, qstride, nwq, seed_direct);
         }
         AR_TRY(cudaGetLastError());
         AR_TRY(cudaMemcpyAsync(&hc, W.d_cnt.p, sizeof(hc), cudaMemcpyDeviceToHost, st));

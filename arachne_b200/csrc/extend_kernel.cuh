@@ -20,7 +20,10 @@
 namespace arachne {
 
 constexpr int EXT_CHUNK = 16;
-constexpr int EXT_GROUP = 4;
+#ifndef ARACHNE_EXT_GROUP
+#define ARACHNE_EXT_GROUP 4
+#endif
+constexpr int EXT_GROUP = ARACHNE_EXT_GROUP;  // cells per rolled group of the DP block (2 / 4 / 8 measured: see profiles)
 constexpr int EXT_BLOCK = 64;
 constexpr int COL_HMASK = 0x1fff;
 

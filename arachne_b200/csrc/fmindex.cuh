@@ -33,6 +33,10 @@ struct FMIndex {
     const void* kmer;      // level kmer_k
     const void* kmer_all;  // levels 1..kmer_k back to back: level L (4^L entries) starts at entry (4^L - 4) / 3
     int kmer_k;
+    // direct forward extension of unique matches (seed_kernel.cuh): inverse SA (row of every text position) and the text
+    // T.revcomp(T) itself, 32 bases per u64 (base p at bits 62 - 2*(p & 31) of word p >> 5); both null when HBM is short
+    const uint64_t* isa;
+    const uint64_t* text;
 };
 
 struct OccStat {  // roofline accounting in the reference's own units: bwt_2occ4 calls and the 64-byte blocks they touch

@@ -23,9 +23,9 @@ struct arachne_index {
     int device = 0;
     arachne::FMIndex fm{};   // device pointers
     arachne::RefView ref{};  // device pointers
-    void *d_bwt = nullptr, *d_sa = nullptr, *d_pac = nullptr, *d_contigs = nullptr, *d_kmer = nullptr;
+    void *d_bwt = nullptr, *d_sa = nullptr, *d_pac = nullptr, *d_contigs = nullptr, *d_kmer = nullptr, *d_isa = nullptr, *d_text = nullptr;
     // runtime knobs (arachne_index_set_option): use the k-mer table in seeding; resident seeding blocks per SM
-    int opt_seed_kmer = 1, opt_seed_blocks = 3, opt_seed_slist = -1;
+    int opt_seed_kmer = 1, opt_seed_blocks = 3, opt_seed_slist = -1, opt_seed_direct = 1;
     size_t device_bytes = 0;
     std::vector<arachne::Contig> contigs;
     std::vector<std::string> names;
@@ -99,6 +99,28 @@ __global__ void __launch_bounds__(256) k_kmer_level(FMIndex fm, uint4* all, int 
         ik.x0 = lo & 0xffffffffffull; ik.x1 = (lo >> 40) | ((hi & 0xffffull) << 24); ik.x2 = (hi >> 16) & 0xffffffffffull; ik.info = 0;
         fm_extend(fm, ik, ok, 0);
         for (int b = 0; b < 4; ++b) dst[p * 4 + b] = kmer_pack(ok[3 - b]);
+    }
+}
+
+// Inverse of the dense SA and the 2-bit text of both strands (FMIndex::isa / ::text): once a match is unique, its forward
+// extension (bwt.c:300-316) is a comparison against the text at SA[row], and the reverse-strand row the bi-interval
+// carries is ISA[n - pos - len] (the text equals its own reverse complement).
+__global__ void __launch_bounds__(256) k_isa_fill(const uint64_t* __restrict__ sa, uint64_t n_rows, uint64_t* isa) {
+    for (uint64_t k = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x + 1; k < n_rows; k += (uint64_t)gridDim.x * blockDim.x) isa[sa[k]] = k;
+}
+__global__ void __launch_bounds__(256) k_text_both(const uint8_t* __restrict__ pac, uint64_t l_pac, uint64_t n_words, uint64_t* text) {
+    const uint64_t n = 2 * l_pac;
+    for (uint64_t w = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; w < n_words; w += (uint64_t)gridDim.x * blockDim.x) {
+        uint64_t v = 0;
+        for (int b = 0; b < 32; ++b) {
+            const uint64_t p = w * 32 + b;
+            if (p >= n) break;
+            const uint64_t f = p < l_pac ? p : n - 1 - p;
+            unsigned c = (pac[f >> 2] >> ((~f & 3) << 1)) & 3;
+            if (p >= l_pac) c = 3 - c;
+            v |= (uint64_t)c << (62 - 2 * b);
+        }
+        text[w] = v;
     }
 }
 
@@ -264,6 +286,31 @@ inline int index_load(const char* prefix_, int device, arachne_index** out) {
                 if (dd) cudaFree(dd);
                 (void)cudaGetLastError();
             }
+        }
+    }
+    fm.isa = nullptr; fm.text = nullptr;
+    {   // inverse SA + both-strand text for the direct extension of unique matches (ARACHNE_SEED_DIRECT=0 disables): needs every
+        // SA row in HBM and room for another 8 bytes per row next to ~48 GB kept free for the batch workspaces
+        const char* ev = getenv("ARACHNE_SEED_DIRECT");
+        size_t free_b = 0, total_b = 0;
+        cudaMemGetInfo(&free_b, &total_b);
+        const uint64_t n_words = fm.seq_len / 32 + 8;
+        const size_t reserve = total_b / 4 < ((size_t)48 << 30) ? total_b / 4 : ((size_t)48 << 30);
+        if (!(ev && atoi(ev) == 0) && fm.sa_intv == 1 && (fm.seq_len + 1) * 8 + n_words * 8 + reserve < free_b) {
+            void *di = nullptr, *dt = nullptr;
+            e = cudaMalloc(&di, (fm.seq_len + 1) * 8);
+            if (e == cudaSuccess) e = cudaMalloc(&dt, n_words * 8);
+            if (e == cudaSuccess) {
+                k_isa_fill<<<148 * 8, 256>>>(fm.sa, fm.seq_len + 1, reinterpret_cast<uint64_t*>(di));
+                k_text_both<<<148 * 8, 256>>>(idx->ref.pac, (uint64_t)idx->l_pac, n_words, reinterpret_cast<uint64_t*>(dt));
+                e = cudaGetLastError();
+                if (e == cudaSuccess) e = cudaDeviceSynchronize();
+            }
+            if (e == cudaSuccess) {
+                idx->d_isa = di; idx->d_text = dt;
+                fm.isa = reinterpret_cast<const uint64_t*>(di); fm.text = reinterpret_cast<const uint64_t*>(dt);
+                idx->device_bytes += (fm.seq_len + 1) * 8 + n_words * 8;
+            } else { if (di) cudaFree(di); if (dt) cudaFree(dt); (void)cudaGetLastError(); }
         }
     }
     idx->h_pac.assign(pac.begin(), pac.begin() + pacb);

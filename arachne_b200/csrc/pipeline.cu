@@ -471,7 +471,7 @@ struct BatchPriv {
 
 // Per-index workspace: every device arena of the batch pipeline, grown on demand and kept between batches.
 struct Workspace {
-    DevBuf d_seq, d_off, d_scratch, d_arena, d_misc, d_intv_off, d_intv_n, d_nsa, d_sa_off, d_rows, d_cnt, d_tmp;
+    DevBuf d_qpk, d_seq, d_off, d_scratch, d_arena, d_misc, d_intv_off, d_intv_n, d_nsa, d_sa_off, d_rows, d_cnt, d_tmp;
     DevBuf d_seeds, d_kseeds, d_chains, d_nodes, d_order, d_kept, d_nchain, d_nkseed, d_srt, d_regs, d_nregs, d_win, d_reg_off, d_out;
     DevBuf d_nregs_bak, d_reg_loc, d_blist, d_resc, d_reg_read, d_z, d_cig_scr, d_mm_scr, d_alns, d_cig, d_mm, d_hscr, d_rscr;
     DevBuf d_bc_off, d_run_rfa, d_rand_seed, d_centro, d_pl_cnt, d_pl_scan, d_cand_off, d_lmp, d_cands, d_hot, d_aux, d_slow, d_slot_of_bc, d_bc_of_slot,
@@ -481,7 +481,7 @@ struct Workspace {
     Counters* h_cnt = nullptr;              // pinned
     unsigned long long* h_scalars = nullptr;  // pinned, 8 slots
     std::vector<DevBuf*> all() {
-        return {&d_seq, &d_off, &d_scratch, &d_arena, &d_misc, &d_intv_off, &d_intv_n, &d_nsa, &d_sa_off, &d_rows, &d_cnt, &d_tmp,
+        return {&d_qpk, &d_seq, &d_off, &d_scratch, &d_arena, &d_misc, &d_intv_off, &d_intv_n, &d_nsa, &d_sa_off, &d_rows, &d_cnt, &d_tmp,
                 &d_seeds, &d_kseeds, &d_chains, &d_nodes, &d_order, &d_kept, &d_nchain, &d_nkseed, &d_srt, &d_regs, &d_nregs,
                 &d_win, &d_reg_off, &d_out, &d_nregs_bak, &d_reg_loc, &d_blist, &d_resc, &d_reg_read, &d_z, &d_cig_scr, &d_mm_scr, &d_alns, &d_cig, &d_mm, &d_hscr, &d_rscr,
                 &d_bc_off, &d_run_rfa, &d_rand_seed, &d_centro, &d_pl_cnt, &d_pl_scan, &d_cand_off, &d_lmp, &d_cands, &d_hot, &d_aux, &d_slow, &d_slot_of_bc,
@@ -522,7 +522,7 @@ void arachne_index_free(arachne_index_t* idx) {
         if (idx->ws[k]) { auto* w = reinterpret_cast<Workspace*>(idx->ws[k]); w->destroy(); delete w; idx->ws[k] = nullptr; }
     for (void* p : idx->priv_pool) { auto* bp = reinterpret_cast<BatchPriv*>(p); bp->release(); delete bp; }
     idx->priv_pool.clear();
-    cudaFree(idx->d_bwt); cudaFree(idx->d_sa); cudaFree(idx->d_pac); cudaFree(idx->d_contigs); cudaFree(idx->d_kmer);
+    cudaFree(idx->d_bwt); cudaFree(idx->d_sa); cudaFree(idx->d_pac); cudaFree(idx->d_contigs); cudaFree(idx->d_kmer); cudaFree(idx->d_isa); cudaFree(idx->d_text);
     delete idx;
 }
 int64_t arachne_index_l_pac(const arachne_index_t* idx) { return idx ? idx->l_pac : -1; }
@@ -698,20 +698,32 @@ int arachne_seed_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, int6
     int cap = 32;
     DevBuf d_seq, d_off, d_scr, d_arena, d_next, d_in, d_nsa, d_cnt;
     int64_t nb = seq_off[n_reads];
-    auto rel = [&]() { for (DevBuf* b : {&d_seq, &d_off, &d_scr, &d_arena, &d_next, &d_in, &d_nsa, &d_cnt}) b->release(); };
+    DevBuf d_q;
+    auto rel = [&]() { for (DevBuf* b : {&d_seq, &d_off, &d_scr, &d_arena, &d_next, &d_in, &d_nsa, &d_cnt, &d_q}) b->release(); };
     if (d_seq.ensure(nb + 16) || d_off.ensure((n_reads + 1) * 8) || d_scr.ensure((size_t)T * rows * sizeof(uint4)) || d_next.ensure(64) ||
         d_in.ensure(n_reads * 4 + 4) || d_nsa.ensure(n_reads * 4 + 4) || d_cnt.ensure(sizeof(Counters))) { rel(); set_error("out of device memory"); return ARACHNE_ERR_CUDA; }
     AR_CUDA(cudaMemcpy(d_seq.p, seq, nb, cudaMemcpyHostToDevice));
     AR_CUDA(cudaMemcpy(d_off.p, seq_off, (n_reads + 1) * 8, cudaMemcpyHostToDevice));
     Counters hc;
+    const ulonglong2* d_qpk = nullptr;
+    const int qstride = seed_qstride(maxlen);
+    const int seed_direct = idx->opt_seed_direct && idx->fm.isa && idx->fm.text;
+    int slist_n = 0, nwq = 0;
+    const size_t seed_smem = seed_smem_plan(maxlen, 3, -1, &slist_n, &nwq);
+    {
+        if (d_q.ensure((size_t)n_reads * qstride * sizeof(ulonglong2))) { rel(); set_error("out of device memory"); return ARACHNE_ERR_CUDA; }
+        k_pack_reads<<<148 * 8, 256>>>(d_seq.as<uint8_t>(), d_off.as<int64_t>(), (int)n_reads, qstride, d_q.as<ulonglong2>());
+        AR_CUDA(cudaGetLastError());
+        d_qpk = d_q.as<ulonglong2>();
+    }
     for (int attempt = 0;; ++attempt) {
         if (d_arena.ensure((size_t)n_reads * cap * sizeof(Intv) + 32)) { rel(); set_error("out of device memory"); return ARACHNE_ERR_CUDA; }
         AR_CUDA(cudaMemset(d_next.p, 0, 64)); AR_CUDA(cudaMemset(d_cnt.p, 0, sizeof(Counters)));
         AR_CUDA(cudaMemset(d_in.p, 0, n_reads * 4 + 4)); AR_CUDA(cudaMemset(d_nsa.p, 0, n_reads * 4 + 4));
         SeedOut so; so.intv = d_arena.as<Intv>(); so.intv_n = d_in.as<int>(); so.n_sa = d_nsa.as<unsigned int>(); so.cap = cap;
-        AR_CUDA(cudaFuncSetAttribute(k_seed2<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16 * 256 * (int)sizeof(uint4)));
-        k_seed2<3><<<blocks, 256, 16 * 256 * sizeof(uint4)>>>(idx->fm, opt, d_seq.as<uint8_t>(), d_off.as<int64_t>(), (int)n_reads, maxlen, d_scr.as<uint4>(), rows, so,
-                                    d_next.as<unsigned int>(), d_cnt.as<Counters>(), idx->opt_seed_kmer, 16);
+        AR_CUDA(cudaFuncSetAttribute(k_seed2<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)seed_smem));
+        k_seed2<3><<<blocks, 256, seed_smem>>>(idx->fm, opt, d_off.as<int64_t>(), (int)n_reads, maxlen, d_scr.as<uint4>(), rows, so,
+                                    d_next.as<unsigned int>(), d_cnt.as<Counters>(), idx->opt_seed_kmer, slist_n, d_qpk, qstride, nwq, seed_direct);
         AR_CUDA(cudaGetLastError());
         AR_CUDA(cudaMemcpy(&hc, d_cnt.p, sizeof(hc), cudaMemcpyDeviceToHost));
         if (!hc.err) break;

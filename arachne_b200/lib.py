@@ -31,6 +31,8 @@ class ArachneError(RuntimeError):
 
 
 def lib_path() -> str:
+    if os.environ.get("ARACHNE_LIB"):  # tuning builds (scripts/): same ABI, different compile-time constants
+        return os.environ["ARACHNE_LIB"]
     return os.path.join(HERE, "libarachne_cuda.so")
 
 

@@ -297,10 +297,11 @@ def main():
     # ---- device-resident timing (value) ----
     with torch.cuda.stream(stream):
         # algorithmic occ-block touches of each distinct batch = what the reference's bwt_2occ4 calls touch: counted once,
-        # untimed, with every bwt_extend call made (the k-mer table of the LAST-like pass skips some of them in the timed steps)
-        A.set_option("seed_kmer", 0)
+        # untimed, with every bwt_extend call made (the k-mer tables and the direct extension of unique matches skip some of them in the timed steps)
+        A.set_option("seed_kmer", 0); A.set_option("seed_direct", 0)
         algo_blocks = [step_resident(i)["counters"]["n_occ_blocks"] for i in range(len(dev))]
         A.set_option("seed_kmer", int(os.environ.get("ARACHNE_BENCH_SEED_KMER", "1")))
+        A.set_option("seed_direct", int(os.environ.get("ARACHNE_BENCH_SEED_DIRECT", "1")))
         A.set_option("seed_blocks_per_sm", int(os.environ.get("ARACHNE_BENCH_SEED_BLOCKS", "3")))
         A.set_option("seed_shared_list", int(os.environ.get("ARACHNE_BENCH_SEED_SLIST", "-1")))
         for i in range(args.warmup):
