@@ -25,7 +25,7 @@ static std::unique_lock<std::mutex> take_ws(arachne_index_t* idx, int* slot) {
 int arachne_index_set_option(arachne_index_t* idx, const char* name, int64_t value) {
     if (!idx || !name) { set_error("arachne_index_set_option: null argument"); return ARACHNE_ERR_ARG; }
     std::lock_guard<std::mutex> lk(idx->mu);  // takes effect with the next batch that starts
-    if (!strcmp(name, "seed_kmer")) idx->opt_seed_kmer = value != 0;
+    if (!strcmp(name, "seed_kmer")) idx->opt_seed_kmer = (int)(value & 7);  // bit 0: tables on; bit 2: the forward window's table copies complete in a trip of their own
     else if (!strcmp(name, "seed_blocks_per_sm") && value >= 1 && value <= 4) idx->opt_seed_blocks = (int)value;
     else if (!strcmp(name, "seed_direct")) idx->opt_seed_direct = value != 0;
     else if (!strcmp(name, "seed_shared_list") && value >= -1 && value <= 16) idx->opt_seed_slist = (int)value;
@@ -111,6 +111,7 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
     AR_ALLOC(W.d_misc, 64);
     AR_ALLOC(W.d_intv_off, n_reads * 8);
     AR_ALLOC(W.d_intv_n, n_reads * 4);
+    AR_ALLOC(W.d_intv_cnt2, n_reads * 8);
     AR_ALLOC(W.d_nsa, (n_reads + 1) * 4);
     AR_ALLOC(W.d_sa_off, (n_reads + 1) * 8);
     AR_ALLOC(W.d_cnt, sizeof(Counters));
@@ -145,9 +146,9 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
     for (int attempt = 0;; ++attempt) {
         AR_ALLOC(W.d_arena, (size_t)n_reads * intv_cap * sizeof(Intv));
         AR_TRY(cudaMemsetAsync(W.d_misc.p, 0, 64, st));
-        AR_TRY(cudaMemsetAsync(W.d_intv_n.p, 0, n_reads * 4, st));
+        AR_TRY(cudaMemsetAsync(W.d_intv_cnt2.p, 0, n_reads * 8, st));
         AR_TRY(cudaMemsetAsync(W.d_nsa.p, 0, (n_reads + 1) * 4, st));
-        SeedOut so; so.intv = W.d_arena.as<Intv>(); so.intv_n = W.d_intv_n.as<int>(); so.n_sa = W.d_nsa.as<unsigned int>(); so.cap = intv_cap;
+        SeedOut so; so.intv = W.d_arena.as<Intv>(); so.cnt2 = W.d_intv_cnt2.as<int>(); so.cap = intv_cap;
         ++nl;
         // shared-memory head of the interval lists: as many entries as fit next to the resident blocks (16 at 3 blocks/SM)
         int slist_n = 0, nwq = 0;
@@ -171,7 +172,7 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
         AR_TRY(cudaMemsetAsync(W.d_cnt.p, 0, sizeof(Counters), st));
     }
     ++nl;
-    k_sort_intv<<<sms * 8, 128, 0, st>>>((int)n_reads, W.d_arena.as<Intv>(), W.d_intv_n.as<int>(), intv_cap);
+    k_sort_intv<<<sms * 8, 128, 0, st>>>((int)n_reads, W.d_arena.as<Intv>(), W.d_intv_cnt2.as<int>(), intv_cap, opt.max_occ, W.d_intv_n.as<int>(), W.d_nsa.as<unsigned int>());
     AR_TRY(cudaGetLastError());
     cudaEventRecord(ev[1], st);
     // ---- seeds per read -> offsets ----

@@ -471,7 +471,7 @@ struct BatchPriv {
 
 // Per-index workspace: every device arena of the batch pipeline, grown on demand and kept between batches.
 struct Workspace {
-    DevBuf d_qpk, d_seq, d_off, d_scratch, d_arena, d_misc, d_intv_off, d_intv_n, d_nsa, d_sa_off, d_rows, d_cnt, d_tmp;
+    DevBuf d_qpk, d_intv_cnt2, d_seq, d_off, d_scratch, d_arena, d_misc, d_intv_off, d_intv_n, d_nsa, d_sa_off, d_rows, d_cnt, d_tmp;
     DevBuf d_seeds, d_kseeds, d_chains, d_nodes, d_order, d_kept, d_nchain, d_nkseed, d_srt, d_regs, d_nregs, d_win, d_reg_off, d_out;
     DevBuf d_nregs_bak, d_reg_loc, d_blist, d_resc, d_reg_read, d_z, d_cig_scr, d_mm_scr, d_alns, d_cig, d_mm, d_hscr, d_rscr;
     DevBuf d_bc_off, d_run_rfa, d_rand_seed, d_centro, d_pl_cnt, d_pl_scan, d_cand_off, d_lmp, d_cands, d_hot, d_aux, d_slow, d_slot_of_bc, d_bc_of_slot,
@@ -481,7 +481,7 @@ struct Workspace {
     Counters* h_cnt = nullptr;              // pinned
     unsigned long long* h_scalars = nullptr;  // pinned, 8 slots
     std::vector<DevBuf*> all() {
-        return {&d_qpk, &d_seq, &d_off, &d_scratch, &d_arena, &d_misc, &d_intv_off, &d_intv_n, &d_nsa, &d_sa_off, &d_rows, &d_cnt, &d_tmp,
+        return {&d_qpk, &d_intv_cnt2, &d_seq, &d_off, &d_scratch, &d_arena, &d_misc, &d_intv_off, &d_intv_n, &d_nsa, &d_sa_off, &d_rows, &d_cnt, &d_tmp,
                 &d_seeds, &d_kseeds, &d_chains, &d_nodes, &d_order, &d_kept, &d_nchain, &d_nkseed, &d_srt, &d_regs, &d_nregs,
                 &d_win, &d_reg_off, &d_out, &d_nregs_bak, &d_reg_loc, &d_blist, &d_resc, &d_reg_read, &d_z, &d_cig_scr, &d_mm_scr, &d_alns, &d_cig, &d_mm, &d_hscr, &d_rscr,
                 &d_bc_off, &d_run_rfa, &d_rand_seed, &d_centro, &d_pl_cnt, &d_pl_scan, &d_cand_off, &d_lmp, &d_cands, &d_hot, &d_aux, &d_slow, &d_slot_of_bc,
@@ -698,8 +698,8 @@ int arachne_seed_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, int6
     int cap = 32;
     DevBuf d_seq, d_off, d_scr, d_arena, d_next, d_in, d_nsa, d_cnt;
     int64_t nb = seq_off[n_reads];
-    DevBuf d_q;
-    auto rel = [&]() { for (DevBuf* b : {&d_seq, &d_off, &d_scr, &d_arena, &d_next, &d_in, &d_nsa, &d_cnt, &d_q}) b->release(); };
+    DevBuf d_q, d_c2;
+    auto rel = [&]() { for (DevBuf* b : {&d_seq, &d_off, &d_scr, &d_arena, &d_next, &d_in, &d_nsa, &d_cnt, &d_q, &d_c2}) b->release(); };
     if (d_seq.ensure(nb + 16) || d_off.ensure((n_reads + 1) * 8) || d_scr.ensure((size_t)T * rows * sizeof(uint4)) || d_next.ensure(64) ||
         d_in.ensure(n_reads * 4 + 4) || d_nsa.ensure(n_reads * 4 + 4) || d_cnt.ensure(sizeof(Counters))) { rel(); set_error("out of device memory"); return ARACHNE_ERR_CUDA; }
     AR_CUDA(cudaMemcpy(d_seq.p, seq, nb, cudaMemcpyHostToDevice));
@@ -720,7 +720,9 @@ int arachne_seed_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, int6
         if (d_arena.ensure((size_t)n_reads * cap * sizeof(Intv) + 32)) { rel(); set_error("out of device memory"); return ARACHNE_ERR_CUDA; }
         AR_CUDA(cudaMemset(d_next.p, 0, 64)); AR_CUDA(cudaMemset(d_cnt.p, 0, sizeof(Counters)));
         AR_CUDA(cudaMemset(d_in.p, 0, n_reads * 4 + 4)); AR_CUDA(cudaMemset(d_nsa.p, 0, n_reads * 4 + 4));
-        SeedOut so; so.intv = d_arena.as<Intv>(); so.intv_n = d_in.as<int>(); so.n_sa = d_nsa.as<unsigned int>(); so.cap = cap;
+        if (d_c2.ensure(n_reads * 8 + 8)) { rel(); set_error("out of device memory"); return ARACHNE_ERR_CUDA; }
+        AR_CUDA(cudaMemset(d_c2.p, 0, n_reads * 8 + 8));
+        SeedOut so; so.intv = d_arena.as<Intv>(); so.cnt2 = d_c2.as<int>(); so.cap = cap;
         AR_CUDA(cudaFuncSetAttribute(k_seed2<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)seed_smem));
         k_seed2<3><<<blocks, 256, seed_smem>>>(idx->fm, opt, d_off.as<int64_t>(), (int)n_reads, maxlen, d_scr.as<uint4>(), rows, so,
                                     d_next.as<unsigned int>(), d_cnt.as<Counters>(), idx->opt_seed_kmer, slist_n, d_qpk, qstride, nwq, seed_direct);
@@ -730,7 +732,7 @@ int arachne_seed_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, int6
         if (attempt >= 3) { rel(); set_error("more than %d intervals at read %d", cap, hc.err_read); return ARACHNE_ERR_OVERFLOW; }
         cap *= 4;
     }
-    k_sort_intv<<<256, 128>>>((int)n_reads, d_arena.as<Intv>(), d_in.as<int>(), cap);
+    k_sort_intv<<<256, 128>>>((int)n_reads, d_arena.as<Intv>(), d_c2.as<int>(), cap, opt.max_occ, d_in.as<int>(), d_nsa.as<unsigned int>());
     AR_CUDA(cudaGetLastError());
     std::vector<int> in_(n_reads);
     AR_CUDA(cudaMemcpy(in_.data(), d_in.p, n_reads * 4, cudaMemcpyDeviceToHost));

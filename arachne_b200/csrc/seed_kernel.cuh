@@ -20,9 +20,8 @@
 namespace arachne {
 
 struct SeedOut {
-    Intv* intv;            // [n_reads * cap]
-    int* intv_n;           // [n_reads], zeroed before launch
-    unsigned int* n_sa;    // [n_reads], zeroed before launch
+    Intv* intv;            // [n_reads * cap]: the SMEM passes fill a read's slots from 0, the LAST-like pass from cap / 2
+    int* cnt2;             // [n_reads * 2], zeroed before launch: intervals written by each of the two (one lane per read and kind)
     int cap;
 };
 
@@ -51,7 +50,7 @@ __device__ __forceinline__ void ld_sector(uint32_t* o, const void* p) {  // one 
 // bits [s, s + 64) of the 128-bit string a.b (s even, 0..62)
 __device__ __forceinline__ uint64_t fsh64(uint64_t a, uint64_t b, int s) { return (a << s) | ((b >> 1) >> (63 - s)); }
 
-enum { SP_IDLE = 0, SP_P1_SCAN, SP_FWD, SP_BWD, SP_P2_NEXT, SP_P3_SCAN, SP_P3, SP_DONE, SP_FSA, SP_FTXT, SP_FISA };
+enum { SP_IDLE = 0, SP_P1_SCAN, SP_FWD, SP_BWD, SP_P2_NEXT, SP_P3_SCAN, SP_P3, SP_DONE, SP_FSA, SP_FTXT, SP_FISA, SP_FTAB };
 
 // Reads as 2-bit words for the direct extension (below): per read `stride` pairs (bases, mask), 32 bases per u64 with base p
 // at bits 62 - 2*(p & 31); the mask (one bit per base, base p at bit 31 - (p & 31)) is set at every ambiguous base and at every
@@ -62,7 +61,7 @@ __host__ __device__ inline int seed_qstride(int maxlen) { return (maxlen + 31) /
 // Dynamic shared memory of k_seed2 at `bpsm` resident blocks per SM: the read cache (nwq words + masks per lane) and as many
 // interval-list entries per lane as fit beside it (at most 16, or `want` when >= 0).
 inline size_t seed_smem_plan(int maxlen, int bpsm, int want, int* slist_n, int* nwq) {
-    const int budget = (228 * 1024) / bpsm - 1024 - 2048;  // per-block reserve and the static counters
+    const int budget = (228 * 1024) / bpsm - 1024 - 3072;  // per-block reserve and the static counters
     *nwq = (maxlen > 0 ? (maxlen - 1) / 32 : 0) + 2;
     int sn = (budget - *nwq * 256 * 12) / (256 * 16);
     sn = sn > 16 ? 16 : sn < 0 ? 0 : sn;
@@ -138,19 +137,47 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) k_seed2(FMIndex fm, MemOpt op
     uint64_t& dpos = lastcur_x2;  // direct extension: text position of the match (the backward pass's register, idle until then)
     // bwt_extend calls / reference occ blocks (made or replaced), per lane in shared memory: two registers less in the loop
     __shared__ uint2 s_stat[256];
+    __shared__ int s_emit[256];  // intervals the lane's current work item has written
     s_stat[threadIdx.x] = make_uint2(0u, 0u);
     auto stat = [&](unsigned calls, unsigned blocks) { uint2 t = s_stat[threadIdx.x]; t.x += calls; t.y += blocks; s_stat[threadIdx.x] = t; };
 
     auto emit = [&](uint64_t e0, uint64_t e1, uint64_t e2, int start, int end, bool filter) {
         const int slen = end - start;
         if (filter && slen < opt.min_seed_len) return;
-        int slot = atomicAdd(&out.intv_n[r], 1);
-        if (slot >= out.cap) { raise(cnt, ARACHNE_ERR_OVERFLOW, r); return; }
+        // no atomics: a read's two work items write disjoint halves, counted by their own lanes (k_sort_intv joins the halves)
+        const int kind = filter ? 0 : 1, slot = s_emit[threadIdx.x];
+        if (slot >= (out.cap >> 1)) { raise(cnt, ARACHNE_ERR_OVERFLOW, r); return; }
+        s_emit[threadIdx.x] = slot + 1;
+        out.cnt2[2 * r + kind] = slot + 1;
         Intv v; v.x0 = e0; v.x1 = e1; v.x2 = e2; v.info = (uint64_t)start << 32 | (unsigned)end;
-        out.intv[(size_t)r * out.cap + slot] = v;
-        atomicAdd(&out.n_sa[r], e2 > (uint64_t)opt.max_occ ? (unsigned)opt.max_occ : (unsigned)e2);
+        out.intv[(size_t)r * out.cap + kind * (out.cap >> 1) + slot] = v;
         if (rec_i == 0 && filter && slen >= split_len && e2 <= (uint64_t)opt.split_width)
             recs[(size_t)(n_rec++) * T] = make_uint4((unsigned)start, (unsigned)end, (unsigned)e2, 0u);
+    };
+
+    // the table window of a forward pass: intervals of q[x, x + L), L = 1..m, are in the lane's first list slots
+    auto replay = [&]() {
+        int m = __clz((int)mwin(x));
+        m = m < kf ? m : kf;
+        unsigned spare;
+        pk_unpack(sl[0], kx0, kx1, kx2, spare);
+        bool stop = false;
+        int L = 1;
+        for (; L < m; ++L) {
+            uint64_t a0, a1, a2;
+            pk_unpack(sl[L * 256], a0, a1, a2, spare);
+            if (a2 != kx2) {
+                lput(n++, pk_pack(kx0, kx1, kx2, (unsigned)(x + L)));
+                if (a2 < min_intv) { stop = true; break; }
+            }
+            kx0 = a0; kx1 = a1; kx2 = a2;
+        }
+        stat((unsigned)(stop ? L : L - 1), 2u * (unsigned)(stop ? L : L - 1));
+        if (stop) {
+            ret = x + L;
+            hi = n; lo = 0; j = hi - 1; ncur = 0; i = x - 1;
+            phase = SP_BWD;
+        } else { i = x + m; phase = SP_FWD; }
     };
 
     for (;;) {
@@ -159,7 +186,7 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) k_seed2(FMIndex fm, MemOpt op
         int c = 0;  // base of the extension; it is a backward one (is_back) exactly in SP_BWD
         uint64_t tabp = 0;  // need == 4: address of the table entry
         do {
-            if (phase >= SP_DONE) { need = phase == SP_DONE ? 0 : phase == SP_FTXT ? 3 : 2; break; }
+            if (phase >= SP_DONE) { need = phase == SP_DONE ? 0 : phase == SP_FTXT ? 3 : 2; break; }  // (SP_FTAB never lasts into a trip)
             if (phase == SP_IDLE) {
                 // one queue per task kind; a warp keeps to its own kind until that queue is empty, so its lanes walk the
                 // same automaton states (a warp mixing SMEM and LAST-like tasks pays for both code paths every trip)
@@ -178,7 +205,7 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) k_seed2(FMIndex fm, MemOpt op
                     const ulonglong2 pw = __ldg(qpk + (size_t)r * qstride + w);
                     qv[w * 256] = pw.x; qm[w * 256] = (uint32_t)pw.y;
                 }
-                x = 0; n_rec = 0; rec_i = 0;
+                x = 0; n_rec = 0; rec_i = 0; s_emit[threadIdx.x] = 0;
                 phase = kind ? ((opt.max_mem_intv > 0) ? SP_P3_SCAN : SP_IDLE) : SP_P1_SCAN;
                 if (phase == SP_IDLE) break;
             }
@@ -241,26 +268,11 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) k_seed2(FMIndex fm, MemOpt op
                         const uint32_t km = (uint32_t)(qwin(x) >> (64 - 2 * m));
                         const uint4* all = reinterpret_cast<const uint4*>(fm.kmer_all);
                         for (int L = 1; L <= m; ++L) cp_async16(&sl[(L - 1) * 256], all + ((1ull << (2 * L)) - 4) / 3 + (km >> (2 * (m - L))));
-                        cp_async_wait_all();
-                        unsigned spare;
-                        pk_unpack(sl[0], kx0, kx1, kx2, spare);
-                        bool stop = false;
-                        int L = 1;
-                        for (; L < m; ++L) {
-                            uint64_t a0, a1, a2;
-                            pk_unpack(sl[L * 256], a0, a1, a2, spare);
-                            if (a2 != kx2) {
-                                lput(n++, pk_pack(kx0, kx1, kx2, (unsigned)(x + L)));
-                                if (a2 < min_intv) { stop = true; break; }
-                            }
-                            kx0 = a0; kx1 = a1; kx2 = a2;
-                        }
-                        stat((unsigned)(stop ? L : L - 1), 2u * (unsigned)(stop ? L : L - 1));
-                        if (stop) {
-                            ret = x + L;
-                            hi = n; lo = 0; j = hi - 1; ncur = 0; i = x - 1;
-                            phase = SP_BWD;
-                        } else i = x + m;
+                        // the copies land while the other lanes' loads of this trip are in flight; replayed in POST
+                        // waiting here costs the warp one table round trip; handing the window to the next trip (SP_FTAB, use_kmer
+                        // bit 2) costs every forward pass a trip of its own and measured slower (57-60 vs 55 ms per 1 M pairs)
+                        if (use_kmer & 4) { phase = SP_FTAB; need = 8; break; }
+                        cp_async_wait_all(); replay();
                     }
                 }
             }
@@ -375,6 +387,8 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) k_seed2(FMIndex fm, MemOpt op
             ox2 = c == 0 ? ns0 : c == 1 ? ns1 : c == 2 ? ns2 : ns3;
         } else if (need == 2) {
             got = (uint64_t)R[1] << 32 | R[0];
+        } else if (need == 8) {
+            cp_async_wait_all();
         } else if (need == 4) {
             ox2 = ((uint64_t)R[3] << 32 | R[2]) >> 16 & 0xffffffffffull;
         }
@@ -418,6 +432,8 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) k_seed2(FMIndex fm, MemOpt op
                 if (ox2 > 0) emit(ox_b, ox_a, ox2, x, i + 1, false);
                 x = i + 1; phase = SP_P3_SCAN;
             } else { kx0 = ox_b; kx1 = ox_a; kx2 = ox2; ++i; }
+        } else if (phase == SP_FTAB) {
+            replay();
         } else if (phase == SP_FSA) {
             dpos = got;  // text position of the unique match q[x, i)
             phase = SP_FTXT;
@@ -440,19 +456,26 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) k_seed2(FMIndex fm, MemOpt op
     if (st.x) { atomicAdd(&cnt->occ, (unsigned long long)st.x); atomicAdd(&cnt->occ_blocks, (unsigned long long)st.y); }
 }
 
-// Sort each read's intervals by info (bwamem.c:161; equal info => identical interval, so any sort gives the same
-// array) and expand them into SA rows (bwamem.c:278-283).  Thread per read.
-__global__ void k_sort_intv(int n_reads, Intv* intv, const int* __restrict__ intv_n, int cap) {
+// Join the two halves of each read's intervals, sort them by info (bwamem.c:161; equal info => identical interval, so any
+// sort gives the same array), and count the SA rows they expand into (bwamem.c:278-283).  Thread per read.
+__global__ void k_sort_intv(int n_reads, Intv* intv, const int* __restrict__ cnt2, int cap, int max_occ, int* intv_n, unsigned int* n_sa) {
     for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < n_reads; r += gridDim.x * blockDim.x) {
         Intv* a = intv + (size_t)r * cap;
-        int n = intv_n[r];
-        n = n < cap ? n : cap;
-        for (int i = 1; i < n; ++i) {
+        const int h = cap >> 1;
+        int n0 = cnt2[2 * r], n1 = cnt2[2 * r + 1];
+        n0 = n0 < h ? n0 : h; n1 = n1 < h ? n1 : h;
+        if (n0 < h) for (int t = 0; t < n1; ++t) a[n0 + t] = a[h + t];
+        const int n = n0 + n1;
+        unsigned rows = 0;
+        for (int i = 0; i < n; ++i) {
             Intv v = a[i];
+            rows += v.x2 > (uint64_t)max_occ ? (unsigned)max_occ : (unsigned)v.x2;
             int k = i - 1;
             while (k >= 0 && a[k].info > v.info) { a[k + 1] = a[k]; --k; }
             a[k + 1] = v;
         }
+        intv_n[r] = n;
+        n_sa[r] = rows;
     }
 }
 

@@ -386,3 +386,44 @@ def test_empty_and_tiny_batches(A, R, workdir):
     from arachne_b200 import ArachneError
     with pytest.raises(ArachneError):  # reads longer than ARACHNE_MAX_READ_LEN are refused, not truncated
         A.align_batch(np.zeros(600, np.uint8), np.array([0, 300, 600], np.int64), None, stages=7)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["rand1m", "rep600k"])
+def test_seed_intervals_every_shortcut(A, R, workdir, name):
+    """k_seed2's shortcuts -- k-mer tables (LAST-like pass, forward windows, short backward extensions), direct text comparison
+    of unique forward matches (SA / inverse SA / both-strand text), the forward window in a trip of its own -- against the
+    reference's own bwt_smem1 / bwt_seed_strategy1 composed into mem_collect_intv, and against plain stepping: identical
+    interval arrays (x0, x1, x2, info) for every read, including exact reference substrings of both strands (direct comparison
+    running into the read's end), reads with an N inside an exact match, all-N and too-short reads."""
+    fa, ctg, rs = util.make_dataset(name, workdir)
+    R.load(fa); A.load_index(fa)
+    g = np.random.default_rng(11)
+    ref = np.concatenate([np.asarray(c[1], dtype=np.uint8) for c in ctg])
+    reads = [rs.seq[rs.off[r]:rs.off[r + 1]] for r in range(0, min(len(rs.off) - 1, 240))]
+    for k in range(24):
+        p = int(g.integers(0, len(ref) - 260)); L = int(g.choice([30, 100, 150, 250]))
+        s = ref[p:p + L].copy()
+        if s.max() > 3:
+            continue
+        if k % 3 == 1:
+            s = (3 - s)[::-1].copy()
+        if k % 3 == 2:
+            s[int(g.integers(20, L - 5))] = 4
+        reads.append(s)
+    reads += [np.full(40, 4, dtype=np.uint8), np.zeros(12, dtype=np.uint8), np.array([0, 1, 2, 3] * 30, dtype=np.uint8)]
+    seq, off = util.pack(reads)
+    base = None
+    try:
+        for kmer, direct in [(0, 0), (1, 0), (0, 1), (1, 1), (5, 1)]:
+            A.set_option("seed_kmer", kmer); A.set_option("seed_direct", direct)
+            ioff, iv = A.seed(seq, off)
+            if base is None:
+                base = (ioff.copy(), iv.copy())
+                for r, q in enumerate(reads):
+                    got = [tuple(int(v) for v in a) for a in iv[ioff[r]:ioff[r + 1]]]
+                    assert got == util.ref_collect_intv(R, q), (name, r)
+            else:
+                assert np.array_equal(ioff, base[0]) and np.array_equal(iv, base[1]), (name, kmer, direct)
+    finally:
+        A.set_option("seed_kmer", 1); A.set_option("seed_direct", 1)

@@ -324,3 +324,32 @@ def index_build_cases():
     cases.append(("allA", [("c", np.zeros(300, np.uint8))], 0))
     cases.append(("allT", [("c", np.full(300, 3, np.uint8))], 0))
     return cases
+
+
+def ref_collect_intv(R, q, min_seed_len=19, split_len=28, split_width=10, max_mem_intv=20):
+    """mem_collect_intv (bwamem.c:114-162) composed from the reference's own bwt_smem1 / bwt_seed_strategy1 (oracle/_ref),
+    sorted by info: the array k_seed2 + k_sort_intv must produce for the read."""
+    L = len(q); exp = []
+    x = 0
+    while x < L:
+        if q[x] < 4:
+            x, iv = R.smem1(q, x)
+            exp += [tuple(int(v) for v in a) for a in iv if (int(a[3]) & 0xffffffff) - (int(a[3]) >> 32) >= min_seed_len]
+        else:
+            x += 1
+    for a in list(exp):
+        s, e = a[3] >> 32, a[3] & 0xffffffff
+        if e - s < split_len or a[2] > split_width:
+            continue
+        _, iv = R.smem1(q, (s + e) >> 1, a[2] + 1)
+        exp += [tuple(int(v) for v in b) for b in iv if (int(b[3]) & 0xffffffff) - (int(b[3]) >> 32) >= min_seed_len]
+    x = 0
+    while x < L:
+        if q[x] < 4:
+            x, m = R.seed_strategy1(q, x, min_seed_len, max_mem_intv)
+            if m[2] > 0:
+                exp.append(tuple(int(v) for v in m))
+        else:
+            x += 1
+    exp.sort(key=lambda a: a[3])
+    return exp
