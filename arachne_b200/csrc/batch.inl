@@ -25,8 +25,9 @@ static std::unique_lock<std::mutex> take_ws(arachne_index_t* idx, int* slot) {
 int arachne_index_set_option(arachne_index_t* idx, const char* name, int64_t value) {
     if (!idx || !name) { set_error("arachne_index_set_option: null argument"); return ARACHNE_ERR_ARG; }
     std::lock_guard<std::mutex> lk(idx->mu);  // takes effect with the next batch that starts
-    if (!strcmp(name, "seed_kmer")) idx->opt_seed_kmer = (int)(value & 7);  // bit 0: tables on; bit 2: the forward window's table copies complete in a trip of their own
+    if (!strcmp(name, "seed_kmer")) idx->opt_seed_kmer = (idx->opt_seed_kmer & ~0xff) | (int)(value & 7);  // bit 0: tables on; bit 2: the forward window's table copies complete in a trip of their own
     else if (!strcmp(name, "seed_blocks_per_sm") && value >= 1 && value <= 4) idx->opt_seed_blocks = (int)value;
+    else if (!strcmp(name, "seed_fwd_levels") && value >= 0 && value <= 15) idx->opt_seed_kmer = (idx->opt_seed_kmer & 0xff) | (int)value << 8;
     else if (!strcmp(name, "seed_direct")) idx->opt_seed_direct = value != 0;
     else if (!strcmp(name, "seed_shared_list") && value >= -1 && value <= 16) idx->opt_seed_slist = (int)value;
     else { set_error("arachne_index_set_option: unknown option or value: %s=%lld", name, (long long)value); return ARACHNE_ERR_ARG; }

@@ -44,7 +44,7 @@ __device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory"); }
 
 __device__ __forceinline__ void ld_sector(uint32_t* o, const void* p) {  // one 32-byte sector, LDG.E.256
-    asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+    asm volatile("ld.global.nc.L1::no_allocate.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                  : "=r"(o[0]), "=r"(o[1]), "=r"(o[2]), "=r"(o[3]), "=r"(o[4]), "=r"(o[5]), "=r"(o[6]), "=r"(o[7]) : "l"(p));
 }
 // bits [s, s + 64) of the 128-bit string a.b (s even, 0..62)
@@ -59,13 +59,14 @@ constexpr int DIRECT_WORDS = 3;    // 64-bit words compared per trip (96 bases)
 constexpr int DIRECT_MIN_LEFT = 8; // bases left in the read below which stepping is kept (the switch costs three trips)
 __host__ __device__ inline int seed_qstride(int maxlen) { return (maxlen + 31) / 32 + DIRECT_WORDS + 1; }
 // Dynamic shared memory of k_seed2 at `bpsm` resident blocks per SM: the read cache (nwq words + masks per lane) and as many
-// interval-list entries per lane as fit beside it (at most 16, or `want` when >= 0).
+// interval-list entries per lane as fit beside it (at most 10, or `want` when >= 0).
 inline size_t seed_smem_plan(int maxlen, int bpsm, int want, int* slist_n, int* nwq) {
     const int budget = (228 * 1024) / bpsm - 1024 - 3072;  // per-block reserve and the static counters
     *nwq = (maxlen > 0 ? (maxlen - 1) / 32 : 0) + 2;
     int sn = (budget - *nwq * 256 * 12) / (256 * 16);
     sn = sn > 16 ? 16 : sn < 0 ? 0 : sn;
-    if (want >= 0 && want < sn) sn = want;
+    const int dflt = 10;  // more entries measured slower: the shared memory they take is L1 the list tails lose
+    sn = want >= 0 ? (want < sn ? want : sn) : (dflt < sn ? dflt : sn);
     *slist_n = sn;
     return (size_t)sn * 256 * 16 + (size_t)*nwq * 256 * 12;
 }
@@ -112,10 +113,13 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) k_seed2(FMIndex fm, MemOpt op
     const int split_len = (int)(opt.min_seed_len * opt.split_factor + .499f);
     // task kinds cost about 2:1 in bwt_extend calls (passes 1+2 vs pass 3): every third warp starts on the LAST-like queue
     // (1:5 when pass 3 starts from the k-mer table)
-    const int kmer_k = (use_kmer && fm.kmer && fm.kmer_k <= opt.min_seed_len) ? fm.kmer_k : 0;
+    const int kmer_k = ((use_kmer & 1) && fm.kmer && fm.kmer_k <= opt.min_seed_len) ? fm.kmer_k : 0;
     // the SMEM passes' forward extension starts from the table too (all levels 1..K, fetched with K independent copies into
     // the lane's shared list slots) when those slots can hold them
-    const int kf = kmer_k < slist_n ? kmer_k : slist_n;  // levels the forward window replays
+    // levels the forward window replays: at most the shared slots, and use_kmer bits 8..11 when set (the deep levels are HBM
+    // round trips the warp waits for; the shallow ones stay in L2)
+    const int kf_cap = (use_kmer >> 8) & 15;
+    const int kf = min(min(kmer_k, slist_n), kf_cap ? kf_cap : 8);
     const bool kmer_fwd = kmer_k && fm.kmer_all && kf >= 4;
     // a backward extension whose result is at most kmer_k long is a table entry too: bwt_smem1a's backward pass extends every
     // interval of the forward list base by base (bwt.c:320-347), and most of those patterns are short
@@ -336,15 +340,15 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) k_seed2(FMIndex fm, MemOpt op
             if (!same) ld_sector(R + 8, fm.blocks + lb);
         } else if (need == 2) {
             const uint64_t* a = phase == SP_FSA ? fm.sa + kx0 : fm.isa + (fm.seq_len - dpos - (uint64_t)(i - x));
-            asm volatile("ld.global.nc.v2.u32 {%0,%1}, [%2];" : "=r"(R[0]), "=r"(R[1]) : "l"(a));
+            asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(R[0]), "=r"(R[1]) : "l"(a));
         } else if (need == 3) {
             const uint64_t* tp = fm.text + ((dpos + (uint64_t)(i - x)) >> 5);
 #pragma unroll
             for (int d = 0; d <= DIRECT_WORDS; ++d)
-                asm volatile("ld.global.nc.v2.u32 {%0,%1}, [%2];" : "=r"(R[2 * d]), "=r"(R[2 * d + 1]) : "l"(tp + d));
+                asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(R[2 * d]), "=r"(R[2 * d + 1]) : "l"(tp + d));
         } else if (need == 4) {
             stat(1u, 2u);
-            asm volatile("ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(R[0]), "=r"(R[1]), "=r"(R[2]), "=r"(R[3]) : "l"(tabp));
+            asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(R[0]), "=r"(R[1]), "=r"(R[2]), "=r"(R[3]) : "l"(tabp));
         }
         __syncwarp();
         // ------------------------------------------------------------------ CONSUME: bwt_extend on (sx, is_back), base c / the loaded entry

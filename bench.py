@@ -302,6 +302,8 @@ def main():
         algo_blocks = [step_resident(i)["counters"]["n_occ_blocks"] for i in range(len(dev))]
         A.set_option("seed_kmer", int(os.environ.get("ARACHNE_BENCH_SEED_KMER", "1")))
         A.set_option("seed_direct", int(os.environ.get("ARACHNE_BENCH_SEED_DIRECT", "1")))
+        if os.environ.get("ARACHNE_BENCH_SEED_FWD_LEVELS"):
+            A.set_option("seed_fwd_levels", int(os.environ["ARACHNE_BENCH_SEED_FWD_LEVELS"]))
         A.set_option("seed_blocks_per_sm", int(os.environ.get("ARACHNE_BENCH_SEED_BLOCKS", "3")))
         A.set_option("seed_shared_list", int(os.environ.get("ARACHNE_BENCH_SEED_SLIST", "-1")))
         for i in range(args.warmup):
