@@ -226,10 +226,14 @@ int arachne_index_build(const char *prefix, int device, int64_t batch_cap, arach
  * the default), so that a caller can bracket batches with its own CUDA events. */
 int arachne_index_set_stream(arachne_index_t *idx, void *cuda_stream, int use);
 
-/* Runtime knobs of a handle; results never depend on them.  "seed_kmer" 0|1: let the LAST-like seeding pass start from the
- * HBM k-mer table built at load (default 1; 0 makes every bwt_extend call of the reference, which is how bench.py counts the
- * algorithmic occ-block bytes).  "seed_blocks_per_sm" 3|4: resident seeding blocks per SM.
- * "seed_shared_list" -1..16: interval-list entries per lane kept in shared memory (-1: as many as fit). */
+/* Runtime knobs of a handle; results never depend on them.  "seed_kmer" 0|1 (+4): use the HBM k-mer tables built at load in
+ * seeding -- LAST-like pass, forward windows and short backward extensions of the SMEM passes (default 1; 0 together with
+ * "seed_direct" 0 makes every bwt_extend call of the reference, which is how bench.py counts the algorithmic occ-block
+ * bytes; +4 completes a forward window's table copies in a loop trip of its own).  "seed_direct" 0|1: extend unique forward
+ * matches by comparing read and text (needs the inverse SA the loader builds when HBM has room; default 1).
+ * "seed_blocks_per_sm" 1..4: resident seeding blocks per SM (default 3).  "seed_shared_list" -1..16: interval-list entries
+ * per lane kept in shared memory (-1: the default, 10 or as many as fit).  "seed_fwd_levels" 0..15: table levels a forward
+ * window replays (0: the default, 8). */
 int arachne_index_set_option(arachne_index_t *idx, const char *name, int64_t value);
 
 /* int64(binary.LittleEndian.Uint64(md5(name)[0:8])): the per-read PRNG seed of tagBestAlignments (aligner.go:1413-1416). Host only. */
