@@ -14,6 +14,13 @@
 //     lane suffices; entries are packed to 16 bytes (x0,x1,x2 40 bits each + the 8-bit query end) and stored
 //     row-interleaved across lanes (entry j of every lane of a warp is one 512-byte line).
 //   * occ blocks are the 32-byte sectors of fmindex.cuh: k and l cost one sector each (the same one when they share it).
+//   * a trip is PRE (per-lane bookkeeping, shared memory only) -> ISSUE (every lane's loads of the trip, of whatever kind:
+//     occ sectors, a k-mer table entry, an SA / inverse-SA entry, text words) -> warp barrier -> CONSUME -> POST.  The kernel
+//     is bound by the dependent chain inside a trip (profiles/r1h_summary.md), so nothing global is read in PRE: the lane's
+//     read is kept 2-bit packed with its N / end mask in shared memory (k_pack_reads packs the batch once).
+//   * shortcuts that return the integers the stepping would (tests/test_gpu_parity.py::test_seed_intervals_every_shortcut):
+//     k-mer tables (FMIndex::kmer_all) for the LAST-like pass, the first levels of every forward pass and every backward
+//     extension whose result is at most K long; direct text comparison once a forward match is unique (FMIndex::isa / text).
 #pragma once
 #include "fmindex.cuh"
 
