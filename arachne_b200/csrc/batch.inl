@@ -92,7 +92,7 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
     out->priv = priv;
     out->n_reads = n_reads;
     auto fail = [&](int code) { { std::lock_guard<std::mutex> g(idx->mu); idx->priv_pool.push_back(priv); } delete out; return code; };
-#define AR_TRY(x) do { if ((x) != cudaSuccess) { set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #x, cudaGetErrorString(cudaGetLastError())); return fail(ARACHNE_ERR_CUDA); } } while (0)
+#define AR_TRY(x) do { const cudaError_t e_ = (x); if (e_ != cudaSuccess) { set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #x, cudaGetErrorString(e_)); return fail(ARACHNE_ERR_CUDA); } } while (0)
 #define AR_ALLOC(buf, bytes) do { if ((buf).ensure(bytes)) { set_error("out of device memory allocating %zu bytes (%s)", (size_t)(bytes), #buf); return fail(ARACHNE_ERR_CUDA); } } while (0)
 #define AR_PIN(buf, bytes) do { if ((buf).ensure(bytes)) { set_error("out of pinned host memory allocating %zu bytes (%s)", (size_t)(bytes), #buf); return fail(ARACHNE_ERR_CUDA); } } while (0)
 

@@ -286,3 +286,126 @@ def simulate_pairs_fast(contigs, n_pairs: int, seed: int, *, read_len: int = 150
     names = [f"f{seed}_{i}" for i in range(n_pairs)] if n_pairs <= 2_000_000 else []
     truth = np.stack([ci, fs, isz, flip.astype(np.int64)], axis=1)
     return ReadSet(seq.reshape(-1), off, bc_off, bcs, names, truth)
+
+
+# ---------------------------------------------------------------------------------------------- bench-scale workloads
+def _barcode_plan(g, n_pairs: int, style: str, oversize_pairs: int = 0):
+    """Pairs per molecule for every barcode until n_pairs are covered.  Returns (bc_sizes, mol_sizes, mol_bc).
+    haplotagging / tellseq: molecules per barcode ~ Poisson(3) + 1, pairs per molecule ~ max(1, Poisson(8)).
+    stlfr: pairs per barcode ~ lognormal(mean 200, sigma 1), one molecule per ~20 pairs; `oversize_pairs` > 0 puts one
+    barcode of that many pairs first, so that the reader's 30000-record cap and 201-record continuation chunks
+    (src/fastqreader/reader.go:236,266-270) are exercised."""
+    bc_sizes, mol_sizes, mol_bc = [], [], []
+    tot = 0
+    est = 36 if style != "stlfr" else 200
+    while tot < n_pairs:
+        nb = max(16, int((n_pairs - tot) / est * 1.1) + 1)
+        if style == "stlfr":
+            sz = np.maximum(1, g.lognormal(np.log(200.0) - 0.5, 1.0, size=nb)).astype(np.int64)
+            if oversize_pairs and not bc_sizes:
+                sz[0] = oversize_pairs
+            nm = np.maximum(1, np.rint(sz / 20.0)).astype(np.int64)
+            for b in range(nb):
+                cuts = np.sort(g.integers(0, sz[b] + 1, size=nm[b] - 1)) if nm[b] > 1 else np.zeros(0, np.int64)
+                ms = np.diff(np.concatenate([[0], cuts, [sz[b]]]))
+                ms = ms[ms > 0]
+                mol_sizes.append(ms); mol_bc.append(np.full(len(ms), len(bc_sizes), np.int64)); bc_sizes.append(int(sz[b]))
+                tot += int(sz[b])
+                if tot >= n_pairs:
+                    break
+        else:
+            nm = g.poisson(3.0, size=nb) + 1
+            ms_all = np.maximum(1, g.poisson(8.0, size=int(nm.sum())))
+            o = 0
+            for b in range(nb):
+                ms = ms_all[o:o + nm[b]]; o += nm[b]
+                mol_sizes.append(ms); mol_bc.append(np.full(len(ms), len(bc_sizes), np.int64)); bc_sizes.append(int(ms.sum()))
+                tot += int(ms.sum())
+                if tot >= n_pairs:
+                    break
+    return np.array(bc_sizes, np.int64), np.concatenate(mol_sizes).astype(np.int64), np.concatenate(mol_bc)
+
+
+def simulate_workload(contigs, n_pairs: int, seed: int, *, style: str = "haplotagging", read_len: int = 150, dash_suffix: bool = True,
+                      sub: float = 0.01, ins: float = 0.0005, dele: float = 0.0005, nrate: float = 0.002, invalid_frac: float = 0.0,
+                      oversize_pairs: int = 0, want_names: bool = True) -> ReadSet:
+    """Vectorised molecule-structured generator for bench-scale inputs: per-base substitution / insertion /
+    deletion rates (indels 1-3 bp), insert ~ N(300, 50) clipped to [max(160, L + 10), 500], FR pairs, R1 strand random.
+    style: haplotagging (AxxCxxBxxDxx), stlfr (i_j_k, lognormal pairs per barcode), tellseq (18-mer; `invalid_frac` of the
+    barcodes carry an N, are not molecule-grouped and never run RFA).  The last barcode is cut so that exactly n_pairs come out.
+    `barcodes` holds one string per barcode with the '-1' suffix when dash_suffix (worthRunningRFA needs a '-', aligner.go:1022)."""
+    g = rng(seed)
+    L = read_len
+    slack = 16
+    clen = np.array([len(s) for _, s in contigs], dtype=np.int64)
+    cstart = np.concatenate([[0], np.cumsum(clen)])
+    genome = np.concatenate([s for _, s in contigs]) if len(contigs) > 1 else contigs[0][1]
+    bc_sizes, mol_sizes, mol_bc = _barcode_plan(g, n_pairs, style, oversize_pairs)
+    n_mol = len(mol_sizes)
+    pair_mol = np.repeat(np.arange(n_mol), mol_sizes)[:n_pairs]
+    pair_bc = mol_bc[pair_mol]
+    n_bc = int(pair_bc[-1]) + 1
+    bc_off = np.concatenate([[0], np.cumsum(bc_sizes[:n_bc])]).astype(np.int64)
+    bc_off[-1] = n_pairs
+    mol_c = g.choice(len(contigs), size=n_mol, p=clen / clen.sum())
+    mol_len = np.clip(g.exponential(40000, size=n_mol), 5000, 150000).astype(np.int64)
+    mol_len = np.minimum(mol_len, clen[mol_c] - 600)
+    mol_start = (g.random(n_mol) * (clen[mol_c] - mol_len - 600)).astype(np.int64)
+    isz = np.clip(g.normal(300, 50, size=n_pairs), max(160, L + 10), 500).astype(np.int64)
+    ci = mol_c[pair_mol]
+    fs = mol_start[pair_mol] + (g.random(n_pairs) * np.maximum(1, mol_len[pair_mol] - isz)).astype(np.int64)
+    bc_invalid = np.zeros(n_bc, bool)
+    if style == "tellseq" and invalid_frac > 0:  # unbarcoded pairs: random positions, no molecule structure
+        bc_invalid = g.random(n_bc) < invalid_frac
+        inv = bc_invalid[pair_bc]
+        k = int(inv.sum())
+        ci2 = g.choice(len(contigs), size=k, p=clen / clen.sum())
+        ci = ci.copy(); fs = fs.copy()
+        ci[inv] = ci2
+        fs[inv] = (g.random(k) * (clen[ci2] - 600)).astype(np.int64)
+    gpos = cstart[ci] + fs
+    ar = np.arange(L + slack, dtype=np.int64)
+    fwd = genome[gpos[:, None] + ar[None, :]]
+    rvt = genome[(gpos + isz - 1)[:, None] - ar[None, :]]
+    rv = np.where(rvt < 4, 3 - rvt, rvt).astype(np.uint8)
+
+    def mutate(a):
+        m = g.random(a.shape) < sub
+        a = np.where(m, (a + g.integers(1, 4, size=a.shape, dtype=np.uint8)) & 3, a).astype(np.uint8)
+        n_ev = g.poisson((ins + dele) * L, size=a.shape[0])
+        rows = np.nonzero(n_ev)[0]
+        W = L + slack
+        for r in rows.tolist():
+            row = a[r]
+            for _ in range(int(n_ev[r])):
+                p = int(g.integers(5, L - 5)); ln = int(g.integers(1, 4))
+                if g.random() < dele / (ins + dele):
+                    row[p:W - ln] = row[p + ln:W].copy()
+                else:
+                    tmp = row[p:W - ln].copy()
+                    row[p:p + ln] = g.integers(0, 4, size=ln, dtype=np.uint8)
+                    row[p + ln:W] = tmp
+        a = a[:, :L]
+        if nrate > 0:
+            a = np.where(g.random(a.shape) < nrate, 4, a).astype(np.uint8)
+        return np.ascontiguousarray(a)
+
+    fwd = mutate(fwd); rv = mutate(rv)
+    flip = g.random(n_pairs) < 0.5
+    seq = np.empty((n_pairs, 2, L), dtype=np.uint8)
+    seq[:, 0] = np.where(flip[:, None], rv, fwd)
+    seq[:, 1] = np.where(flip[:, None], fwd, rv)
+    off = np.arange(2 * n_pairs + 1, dtype=np.int64) * L
+    sfx = "-1" if dash_suffix else ""
+    if style == "stlfr":
+        ijk = g.integers(1, 1537, size=(n_bc, 3))
+        bcs = [f"{a}_{b}_{c}{sfx}" for a, b, c in ijk.tolist()]
+    elif style == "tellseq":
+        codes = g.integers(0, 4, size=(n_bc, 18))
+        bcs = ["".join("ACGT"[x] for x in row) for row in codes.tolist()]
+        bcs = [(b[:7] + "N" + b[8:]) if bad else b + sfx for b, bad in zip(bcs, bc_invalid.tolist())]
+    else:
+        bcs = [f"A{(i % 96) + 1:02d}C{(i // 96 % 96) + 1:02d}B{(i // 9216 % 96) + 1:02d}D{(i // 884736 % 96) + 1:02d}{sfx}" for i in range(n_bc)]
+    names = [f"w{seed}_{i}" for i in range(n_pairs)] if want_names else []
+    truth = np.stack([ci, fs, isz, flip.astype(np.int64)], axis=1)
+    return ReadSet(seq.reshape(-1), off, bc_off, bcs, names, truth)

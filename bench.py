@@ -37,6 +37,10 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=8)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="arachne_b200", choices=["arachne_b200", "reference"])
+    ap.add_argument("--config", default="haplotag", choices=["haplotag", "stlfr", "tellseq", "ksw"],
+                    help="workload (BASELINE.json configs): haplotag = configs[1] (default, what BENCH/SCALE record), stlfr = configs[2] "
+                         "(lognormal pairs per barcode, mean 200, one over-cap barcode per batch), tellseq = configs[3] (30 %% invalid barcodes), "
+                         "ksw = configs[4] (ksw_extend2 microbench grid, GCUPS)")
     ap.add_argument("--ref-mb", type=float, default=float(os.environ.get("ARACHNE_BENCH_REF_MB", "3100")), help="synthetic reference size, Mbp (configs[1]: 3100)")
     ap.add_argument("--pairs", type=int, default=int(os.environ.get("ARACHNE_BENCH_PAIRS", "1000000")), help="read pairs per step per GPU")
     ap.add_argument("--batches", type=int, default=2, help="distinct input batches cycled over the steps")
@@ -88,17 +92,46 @@ def build_index(prefix: str, ctg, args):
     log("arachne_index_build: " + json.dumps(info))
 
 
+WORKLOADS = {
+    # --config: (simulate_workload style, seed base (12 / 13 / 14), extra kwargs, description)
+    "haplotag": ("haplotagging", 12, {}, "simulated haplotagging 2x150 bp pairs: molecules/barcode ~ Poisson(3)+1, pairs/molecule ~ Poisson(8), "
+                                         "1% subs, 0.05%/base ins, 0.05%/base del (1-3 bp), 0.2% N"),
+    "stlfr": ("stlfr", 13, {"oversize_pairs": 30500}, "simulated stLFR 2x150 bp pairs: pairs/barcode ~ lognormal(mean 200, sigma 1), one molecule per ~20 pairs, "
+                                                      "one 30500-pair barcode per batch (reader cap 30000 + 201-record continuation units), same error model"),
+    "tellseq": ("tellseq", 14, {"invalid_frac": 0.3}, "simulated TELLseq 2x150 bp pairs: 18-mer barcodes, 30% of barcodes invalid (N, VX:i:0: random positions, no RFA), "
+                                                      "same molecule and error model as haplotagging"),
+}
+
+
+def make_batch(ctg, args, seed, n_pairs):
+    """One batch of the --config workload, cut into the reference reader's work units (reader.go:208-291): ReadSet.bc_off
+    becomes the work-unit offsets, .unique / .run_rfa the per-unit flags (aligner.go:1018-1030)."""
+    from arachne_b200 import workunits as W
+    style, seed0, kw, _ = WORKLOADS[args.config]
+    rs = S.simulate_workload(ctg, n_pairs, seed=seed0 + seed, style=style, dash_suffix=not args.plain_barcodes, **kw)
+    uo, uq, ub = W.work_units(rs.bc_off, rs.barcodes)
+    rs.run_rfa = W.worth_running_rfa(uo, uq, ub, rs.barcodes)
+    rs.barcodes = [rs.barcodes[b] for b in ub.tolist()]
+    rs.bc_off = uo
+    return rs
+
+
 def make_batches(ctg, args, rank):
-    return [S.simulate_pairs_fast(ctg, args.pairs, seed=12 + 1000 * rank + b) for b in range(args.batches)]
+    return [make_batch(ctg, args, 1000 * rank + b, args.pairs) for b in range(args.batches)]
+
+
+def subset_units(rs, lo, hi):
+    sub = rs.subset(lo, hi)
+    sub.run_rfa = rs.run_rfa[lo:hi].copy()
+    return sub
 
 
 def place_inputs(b, args):
     """Per-batch inputs of the placement stage: PRNG seeds = md5(read name)[0:8] (aligner.go:1413-1416) and the
-    worthRunningRFA flag per barcode (aligner.go:1018-1030: unique barcode with a '-', >= 5 pairs)."""
+    worthRunningRFA flag per work unit (aligner.go:1018-1030: unique barcode with a '-', >= 5 pairs)."""
     import hashlib
     seeds = np.fromiter((int.from_bytes(hashlib.md5(n.encode()).digest()[:8], "little", signed=True) for n in b.names), dtype=np.int64, count=b.n_pairs)
-    rfa = ((np.diff(b.bc_off) >= 5) & (not args.plain_barcodes)).astype(np.uint8)
-    return seeds, rfa
+    return seeds, b.run_rfa
 
 
 def log(msg):
@@ -162,37 +195,76 @@ def cpu_reference(fa, rs, n_sample, threads, args):
         _REF_CACHE[fa] = (RefBwa().load(fa), util.PlaceOracle(fa))
     R, P = _REF_CACHE[fa]
     n_bc = int(np.searchsorted(rs.bc_off, min(n_sample, rs.n_pairs), side="left"))
-    sub = rs.subset(0, max(1, n_bc))
+    sub = subset_units(rs, 0, max(1, n_bc))
     seeds, rfa = place_inputs(sub, args)
     t = time.perf_counter()
     ref = R.batch(sub.seq, sub.off, rescue=True, cigar=True, threads=threads)
     t1 = time.perf_counter()
     nb = len(sub.bc_off) - 1
-    cuts = [nb * k // threads for k in range(threads + 1)]
+    # chunks of work units balanced by pair count (a 30000-pair unit must not drag a whole thread's share behind it)
+    tgt = [sub.n_pairs * k // threads for k in range(threads + 1)]
+    cuts = sorted(set(int(np.searchsorted(sub.bc_off, x, side="left")) for x in tgt) | {0, nb})
 
     def work(k):
         lo, hi = cuts[k], cuts[k + 1]
-        if hi <= lo:
-            return 0
         p0, p1 = int(sub.bc_off[lo]), int(sub.bc_off[hi])
         o = sub.off[2 * p0:2 * p1 + 1]; ro = ref["reg_off"][2 * p0:2 * p1 + 1]
         aln = ref["aln"][ro[0]:ro[-1]].copy(); c0 = int(aln[0, 5]) if len(aln) else 0
         aln[:, 5] -= c0
-        P.place(sub.seq[o[0]:o[-1]], o - o[0], sub.bc_off[lo:hi + 1] - p0, rfa[lo:hi], seeds[p0:p1], ro - ro[0], ref["regs"][ro[0]:ro[-1]], aln, ref["cigar"][c0:])
-        return p1 - p0
+        return P.place(sub.seq[o[0]:o[-1]], o - o[0], sub.bc_off[lo:hi + 1] - p0, rfa[lo:hi], seeds[p0:p1], ro - ro[0], ref["regs"][ro[0]:ro[-1]], aln, ref["cigar"][c0:])
     with ThreadPoolExecutor(threads) as ex:
-        list(ex.map(work, range(threads)))
+        parts = list(ex.map(work, range(len(cuts) - 1)))
     dt = time.perf_counter() - t
     log(f"cpu reference: {sub.n_pairs} pairs, C part {t1 - t:.2f}s + placement port {dt - (t1 - t):.2f}s on {threads} threads")
-    _REF_CACHE["last"] = (sub, ref)
+    _REF_CACHE["last"] = (sub, ref, parts, seeds, rfa)
     return sub.n_pairs, dt
 
 
+def merge_place_parts(sub, ref, parts, cuts_pairs):
+    """Concatenate the placement oracle's per-chunk outputs into batch-global arrays (indices re-based)."""
+    offs, cands, lmps = [np.zeros(1, np.int64)], [], []
+    cb = 0
+    for (oc, ca, lmp), p0 in zip(parts, cuts_pairs):
+        ca = ca.copy()
+        rb = int(ref["reg_off"][2 * p0])
+        ca["reg"][ca["reg"] >= 0] += rb
+        ca["read"] += 2 * p0
+        for f in ("second_best", "mate"):
+            ca[f][ca[f] >= 0] += cb
+        offs.append(oc[1:] + cb); cands.append(ca); lmps.append(lmp)
+        cb += int(oc[-1])
+    return np.concatenate(offs), np.concatenate(cands), np.concatenate(lmps)
+
+
+def mapping_truth(sub, cand_off, cands, rid, is_rev, tol=20):
+    """Fraction of the sample's reads whose selected (active) alignment sits on the simulated contig / strand within `tol`
+    bases of the simulated position (ReadSet.truth): pins the index and the whole path independently of either arm."""
+    act = np.nonzero(cands["active"] == 1)[0]
+    read = cands["read"][act]
+    assert len(np.unique(read)) == len(read) == 2 * sub.n_pairs, "not exactly one active alignment per read"
+    order = np.argsort(read); act = act[order]
+    reg = cands["reg"][act]
+    L = np.diff(sub.off)
+    t = sub.truth
+    pair = np.arange(2 * sub.n_pairs) // 2; mate = np.arange(2 * sub.n_pairs) & 1
+    # R1 is the reverse-strand read of the fragment when flip (simulate.py): read 2p is reverse iff flip, read 2p+1 iff not flip
+    rev = (t[pair, 3] == 1) ^ (mate == 1)
+    exp_pos = np.where(rev, t[pair, 1] + t[pair, 2] - L, t[pair, 1])
+    ok = reg >= 0
+    r = np.where(ok, reg, 0)
+    good = ok & (rid[r] == t[pair, 0]) & ((is_rev[r] != 0) == rev) & (np.abs(cands["pos"][act] - exp_pos) <= tol)
+    return float(good.mean())
+
+
 def parity_sample(A):
-    """Not a test, a tripwire: the CPU-baseline sample's regions / alignments from the reference's own code against the
-    library's on the same pairs (the index sizes of configs[1] are only reachable inside a bench run)."""
-    sub, ref = _REF_CACHE["last"]
-    res = A.align_batch(sub.seq, sub.off, sub.bc_off, stages=7)
+    """The CPU-baseline sample (whole work units of batch 0) through ALL stages of the library against the reference arm on
+    the same pairs: regions / alignments / CIGARs from the reference's own C code (oracle/_ref), placement (candidates,
+    active picks, molecules, MAPQ) from the oracle's restatement of the Go code with the tolerances of
+    tests/test_gpu_parity.py, and both arms against the simulation truth.  Any false flag makes bench.py exit non-zero.
+    Reference coordinates beyond 2^32 only exist at the configs[1] index size, which no pytest case reaches."""
+    from tests import util
+    sub, ref, parts, seeds, rfa = _REF_CACHE["last"]
+    res = A.align_batch(sub.seq, sub.off, sub.bc_off, stages=15, run_rfa=rfa, rand_seed=seeds)
     regs = bool(np.array_equal(res["reg_off"], ref["reg_off"]) and res["regs"].tobytes() == ref["regs"].tobytes())
     a, e = res["alns"], ref["aln"]
     alns = regs and all(np.array_equal(a[f], e[:, j]) for f, j in (("pos", 0), ("rid", 1), ("is_rev", 2), ("nm", 3), ("n_cigar", 4), ("score", 6), ("sub", 7)))
@@ -200,7 +272,23 @@ def parity_sample(A):
         idx_g = np.concatenate([np.arange(o, o + n) for o, n in zip(a["cigar_off"].tolist(), a["n_cigar"].tolist())]) if len(a) else np.zeros(0, np.int64)
         idx_r = np.concatenate([np.arange(o, o + n) for o, n in zip(e[:, 5].tolist(), e[:, 4].tolist())]) if len(a) else np.zeros(0, np.int64)
         alns = bool(np.array_equal(res["cigar"][idx_g], ref["cigar"][idx_r]))
-    return {"pairs": int(sub.n_pairs), "regions_identical": regs, "alignments_and_cigars_identical": bool(alns), "n_regions": int(ref["reg_off"][-1])}
+    nb = len(sub.bc_off) - 1
+    # the chunk boundaries cpu_reference used (same formula)
+    threads = len(parts)
+    tgt = [sub.n_pairs * k // (os.cpu_count() or 1) for k in range((os.cpu_count() or 1) + 1)]
+    cuts = sorted(set(int(np.searchsorted(sub.bc_off, x, side="left")) for x in tgt) | {0, nb})
+    assert len(cuts) - 1 == threads
+    oc, ocands, olmp = merge_place_parts(sub, ref, parts, [int(sub.bc_off[c]) for c in cuts[:-1]])
+    bad = util.place_mismatches(res, oc, ocands, olmp) if regs else ["regions differ"]
+    out = {"pairs": int(sub.n_pairs), "work_units": nb, "regions_identical": regs, "alignments_and_cigars_identical": bool(alns),
+           "placement_identical": not bad, "placement_mismatches": bad[:6], "n_regions": int(ref["reg_off"][-1]), "n_candidates": int(oc[-1]),
+           "placement_tolerance": "integers exact; scores 1e-9 rel; MAPQ equal or +-1 where the untruncated value is within 1e-6 of an integer"}
+    out["mapping_truth"] = {"library": mapping_truth(sub, res["cand_off"], res["cands"], a["rid"], a["is_rev"]) if regs else None,
+                            "reference": mapping_truth(sub, oc, ocands, e[:, 1], e[:, 2]),
+                            "rule": "active alignment on the simulated contig and strand, |pos - simulated pos| <= 20"}
+    out["ok"] = bool(regs and alns and not bad and out["mapping_truth"]["library"] is not None and out["mapping_truth"]["library"] > 0.97
+                     and out["mapping_truth"]["reference"] > 0.97)
+    return out
 
 
 def run_reference(args, rank, world):
@@ -210,7 +298,7 @@ def run_reference(args, rank, world):
     fa, ctg = dataset(args, 0, 1)
     threads = os.cpu_count() or 1
     n = max(1000, min(args.cpu_sample, args.pairs))
-    batches = [S.simulate_pairs_fast(ctg, n, seed=12 + b) for b in range(min(args.batches, 2))]
+    batches = [make_batch(ctg, args, b, n) for b in range(min(args.batches, 2))]
     times = []
     for it in range(args.warmup + args.steps):
         npairs, dt = cpu_reference(fa, batches[it % len(batches)], n, threads, args)
@@ -219,6 +307,7 @@ def run_reference(args, rank, world):
     ms = 1e3 * sum(times) / len(times)
     val = npairs / (ms / 1e3)
     line = base_line(args, 1, val, ms)
+    line["config"]["reference_arm_step"] = f"{npairs} pairs per step (a bounded sample of the arm's {args.pairs}-pair step: same generator, same work-unit rule)"
     line.update({"impl": "reference", "dtype": "int32", "n_gpus": args.gpus,
                  "cpu_baseline": {"value": val, "unit": "pairs/s", "cores": threads, "kind": "reference",
                                   "sample": f"{npairs} pairs per step of the same workload (oracle/_ref: the reference's BWA C sources, gobwa.go call sequence, {threads} pthreads over pairs)"},
@@ -229,14 +318,15 @@ def run_reference(args, rank, world):
 
 def base_line(args, world, value, ms):
     big = args.ref_mb >= 3000
-    what = ("configs[1]: synthetic 3.1 Gb human-scale reference" if big else f"configs[1] scaled down to a synthetic {args.ref_mb:g} Mb reference") + \
+    cfgno = {"haplotag": 1, "stlfr": 2, "tellseq": 3}[args.config]
+    what = (f"configs[{cfgno}]: synthetic 3.1 Gb human-scale reference" if big else f"configs[{cfgno}] scaled down to a synthetic {args.ref_mb:g} Mb reference") + \
            " (24 human-like contigs, iid, seed 2; index built by arachne_index_build, byte-identical to bwa index)"
     return {"metric": "read pairs/sec aligned", "value": value, "unit": "pairs/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32", "data": "synthetic",
-            "config": {"workload": f"{what}, simulated haplotagging 2x150 bp pairs (1% subs, 14% reads with a 1-3 bp indel, 0.2% N, 30 pairs/barcode), "
-                                   f"{args.pairs} pairs per step per GPU ({args.steps} timed steps = {args.pairs * args.steps * world} pairs of the 20M-pair job); "
+            "config": {"workload": f"{what}, {WORKLOADS[args.config][3]}; work units cut by the reference reader's rule (reader.go:208-291); "
+                                   f"{args.pairs} pairs per step per GPU ({args.steps} timed steps = {args.pairs * args.steps * world} pairs); "
                                    f"stages: seeding+SA+chaining+extension+mate rescue+CIGAR/NM+placement (tagBestAlignments, molecules, optimizer, MAPQ; " + ("plain barcodes: no RFA" if args.plain_barcodes else "'-1' barcodes: RFA on") + ")",
-                       "ref_mb": args.ref_mb, "pairs_per_step_per_gpu": args.pairs, "read_len": 150, "parallelism": f"barcode-sharded x{world}, index replicated, no collective",
+                       "name": args.config, "ref_mb": args.ref_mb, "pairs_per_step_per_gpu": args.pairs, "read_len": 150, "parallelism": f"barcode-sharded x{world}, index replicated, no collective",
                        "l2_policy": "index (3.1 GB BWT + 1.55 GB SA + 0.78 GB pac at 3.1 Gb) and per-batch arenas exceed the 126 MB L2; distinct batches are cycled"}}
 
 
@@ -272,6 +362,7 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     barrier = (lambda: dist.barrier()) if world > 1 else (lambda: None)
 
+    rc = 0
     fa, ctg = dataset(args, rank, world)
     barrier()
     batches = make_batches(ctg, args, rank)
@@ -352,12 +443,15 @@ def main():
         tp = os.path.join(ROOT, "profiles", "roofline_traffic.json")
         if os.path.exists(tp):  # dram bytes of ONE k_seed2 launch from `ncu --set full` on this same command (scripts/gpu_round.sh)
             tj = json.load(open(tp))
-            if tj.get("pairs_per_step") == args.pairs and tj.get("ref_mb") == args.ref_mb:
+            if tj.get("pairs_per_step") == args.pairs and tj.get("ref_mb") == args.ref_mb and tj.get("config", "haplotag") == args.config:
                 traffic, traffic_note = tj["dram_bytes_per_launch"], tj.get("note", "")
         dpx = A.dpx_peak()
         ext_ops = 3 * acc["n_ext_cells"] / args.steps  # DPX-class ops per in-band cell in k_extend2's SASS: VIMNMX3 + 2 x VIADDMNMX.RELU
         line["roofline"] = {"kernel": "k_seed2 (FM-index SMEM seeding: bwt_2occ4 block reads)", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                             "frac": achieved / peak, "traffic": traffic, "traffic_note": traffic_note, "peak_source": how,
+                            # what the DRAM really delivered: ncu dram bytes of one launch / this run's kernel time (null without a matching capture)
+                            "delivered": traffic / (seed_ms / 1e3) / 1e9 if traffic else None, "frac_delivered": traffic / (seed_ms / 1e3) / 1e9 / peak if traffic else None,
+                            "frac_definition": "frac = ALGORITHMIC bytes (64 B per occ block the reference's bwt_2occ4 calls touch, SURVEY 8d) / kernel time / peak; frac_delivered = ncu dram bytes / kernel time / peak",
                             "extension": {"kernel": "k_extend2 (ksw_extend2)", "bound": "dpx issue", "gcups": acc["n_ext_cells"] / (acc["extend"] / 1e3) / 1e9 if acc["extend"] else None,
                                           "dpx_ops_per_cell": 3, "achieved_gops": ext_ops / (acc["extend"] / args.steps / 1e3) / 1e9 if acc["extend"] else None,
                                           "peak_gops": dpx, "frac": (ext_ops / (acc["extend"] / args.steps / 1e3) / 1e9) / dpx if acc["extend"] and dpx else None,
@@ -376,9 +470,13 @@ def main():
                                     "sample": f"first {n} pairs of batch 0 (whole barcodes), oracle/_ref = the reference's BWA C sources driven as gobwa.go drives them, {threads} pthreads"}
             line["parity_sample"] = parity_sample(A)
         emit(line)
+        if "parity_sample" in line and not line["parity_sample"]["ok"]:
+            log("PARITY FAILURE at the bench size: " + json.dumps(line["parity_sample"]))
+            rc = 3
     if world > 1:
         dist.destroy_process_group()
+    return rc
 
 
 if __name__ == "__main__":
-    main()
+    sys.exit(main() or 0)

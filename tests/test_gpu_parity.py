@@ -156,28 +156,8 @@ def _place_inputs(A, rs, rfa):
 
 
 def _check_place(res, oc, ocands, olmp, what):
-    g = res["cands"]
-    assert np.array_equal(res["cand_off"], oc), what
-    assert len(g) == len(ocands)
-    for f in ("reg", "read", "id", "pos", "aend", "active", "is_proper", "bwa_pick", "molecule_id", "active_molecule"):
-        bad = np.nonzero(g[f] != ocands[f])[0]
-        assert len(bad) == 0, (what, f, bad[:5], g[f][bad[:5]], ocands[f][bad[:5]])
-    assert np.array_equal(g["lap"], ocands["lap"]), what
-    act = ocands["active"] == 1
-    for f in ("second_best", "mate"):
-        assert np.array_equal(g[f][act], ocands[f][act]), (what, f)
-    # floating point: pair scores are sums of dyadic rationals (exact); the molecule penalty goes through log10 and MAPQ
-    # through pow/log10, which differ from the host libm in the last bits.  Tolerance: 1e-9 relative on scores,
-    # MAPQ equal unless the un-truncated value sits within 1e-6 of an integer (then +-1).
-    for f in ("as_score", "xs_score", "molecule_difference", "molecule_confidence"):
-        assert np.allclose(g[f][act], ocands[f][act], rtol=1e-9, atol=1e-9), (what, f)
-    assert np.allclose(g["sum_move"][act], ocands["sum_move"][act], rtol=1e-9), what
-    assert np.allclose(res["lmp"], olmp, rtol=1e-12, atol=1e-12), what
-    dm = g["mapq"][act] != ocands["mapq"][act]
-    if dm.any():
-        raw = ocands["raw_mapq"][act][dm]
-        assert np.all(np.abs(raw - np.round(raw)) < 1e-6) and np.all(np.abs(g["mapq"][act][dm] - ocands["mapq"][act][dm]) <= 1), (what, raw[:5])
-    assert np.allclose(g["raw_mapq"][act], ocands["raw_mapq"][act], rtol=1e-9, atol=1e-9, equal_nan=True), what
+    bad = util.place_mismatches(res, oc, ocands, olmp)  # tolerances stated there
+    assert not bad, (what, bad)
 
 
 @pytest.mark.parametrize("name", ["rand1m", "rep600k"])

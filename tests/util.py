@@ -271,6 +271,42 @@ class PlaceOracle:
         return cand_off, cands[:cand_off[-1]], lmp
 
 
+def place_mismatches(res, oc, ocands, olmp):
+    """Compare the library's placement outputs with the oracle's.  Integers exactly; floating point: pair scores are sums of
+    dyadic rationals (exact), the molecule penalty goes through log10 and MAPQ through pow/log10, which differ from the host
+    libm in the last bits -> 1e-9 relative on scores, MAPQ equal unless the un-truncated value sits within 1e-6 of an
+    integer (then +-1).  Returns a list of human-readable mismatches (empty = parity)."""
+    bad = []
+    g = res["cands"]
+    if not np.array_equal(res["cand_off"], oc) or len(g) != len(ocands):
+        return ["candidate lists differ (%d vs %d)" % (len(g), len(ocands))]
+    for f in ("reg", "read", "id", "pos", "aend", "active", "is_proper", "bwa_pick", "molecule_id", "active_molecule", "duplicate"):
+        d = np.nonzero(g[f] != ocands[f])[0]
+        if len(d):
+            bad.append("%s: %d differ, first at %d (%s vs %s)" % (f, len(d), d[0], g[f][d[0]], ocands[f][d[0]]))
+    if not np.array_equal(g["lap"], ocands["lap"]):
+        bad.append("log_alignment_probability differs")
+    act = ocands["active"] == 1
+    for f in ("second_best", "mate"):
+        if not np.array_equal(g[f][act], ocands[f][act]):
+            bad.append(f + " differs")
+    for f in ("as_score", "xs_score", "molecule_difference", "molecule_confidence"):
+        if not np.allclose(g[f][act], ocands[f][act], rtol=1e-9, atol=1e-9):
+            bad.append(f + " beyond 1e-9")
+    if not np.allclose(g["sum_move"][act], ocands["sum_move"][act], rtol=1e-9):
+        bad.append("sum_move beyond 1e-9")
+    if not np.allclose(res["lmp"], olmp, rtol=1e-12, atol=1e-12):
+        bad.append("log_molecule_penalty beyond 1e-12")
+    dm = g["mapq"][act] != ocands["mapq"][act]
+    if dm.any():
+        raw = ocands["raw_mapq"][act][dm]
+        if not (np.all(np.abs(raw - np.round(raw)) < 1e-6) and np.all(np.abs(g["mapq"][act][dm] - ocands["mapq"][act][dm]) <= 1)):
+            bad.append("mapq: %d differ beyond the integer-boundary tolerance" % int(dm.sum()))
+    if not np.allclose(g["raw_mapq"][act], ocands["raw_mapq"][act], rtol=1e-9, atol=1e-9, equal_nan=True):
+        bad.append("raw_mapq beyond 1e-9")
+    return bad
+
+
 def exact_repeat_reference(total_len=300_000, n_contigs=4, seed=9, families=6, copies=24, rep_len=700):
     """Random contigs with families of EXACT repeat copies: reads inside a copy get many equal-score candidates, so
     tagBestAlignments' PRNG tie-break decides, pairs need hundreds of PRNG outputs, and the optimizer has moves to make."""
