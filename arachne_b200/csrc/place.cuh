@@ -302,7 +302,7 @@ __device__ double place_fast_score(const PlaceArgs& A, const RfaArgs& R, long ob
 // One barcode per block (slots pulled from a queue).  Steps follow DoRFAForOneBarcode (aligner.go:479-496).
 __global__ void __launch_bounds__(PLACE_T) k_place_rfa(PlaceArgs A, RfaArgs R) {
     __shared__ int sh_scan[PLACE_T / 32 + 1];
-    __shared__ int sh_slot, sh_best_idx, sh_accept;
+    __shared__ int sh_slot, sh_best_idx, sh_accept, sh_ntouch;
     __shared__ double sh_wscore[PLACE_T / 32];
     __shared__ int sh_wlen[PLACE_T / 32], sh_widx[PLACE_T / 32];
     __shared__ long long sh_dna;
@@ -396,19 +396,55 @@ __global__ void __launch_bounds__(PLACE_T) k_place_rfa(PlaceArgs A, RfaArgs R) {
             for (int j = R.k_beg[ob + m]; j < R.k_end[ob + m]; ++j) { const long c = R.ord[ob + j]; if (A.hot[c].active) A.cands[c].molecule_difference = d; }
         }
         __syncthreads();
+        // ---- which molecules can ever be the source of a move: one of their reads has a best alignment in another kept molecule.
+        // `best` and `molid` are fixed from here on (only `active` flips), so this is decided once; a GenerateMove step or a
+        // moleculeMapqProbabilitySums row of any other molecule finds num_moved == 0 for every sink and changes nothing.
+        // m_beg / m_end / m_nact are dead after scrapMolecules: reused as the sink stamps, the touched-sink list and this flag.
+        int* k_mark = R.m_beg + ob; int* k_list = R.m_end + ob; int* k_alt = R.m_nact + ob;
+        for (int m = tid; m < K; m += PLACE_T) { k_mark[m] = 0; k_alt[m] = 0; }
+        __syncthreads();
+        for (int j = tid; j < n; j += PLACE_T) {
+            const long c = R.ord[ob + j];
+            const Hot hc = A.hot[c];
+            if (hc.molid < 0 || k_alt[hc.molid]) continue;
+            for (long k = (long)A.cand_off[hc.read], e = (long)A.cand_off[hc.read + 1]; k < e; ++k) {
+                const Hot hk = A.hot[k];
+                if (hk.best && hk.molid >= 0 && hk.molid != hc.molid) { k_alt[hc.molid] = 1; break; }
+            }
+        }
+        __syncthreads();
+        // The sinks fastScore can report num_moved > 0 for = the molecules holding a best alignment of a read that is active in
+        // src.  They are collected first (a handful), and only they are scored: O(A*C) per step instead of O(K*A*C) -- at 200+
+        // pairs and 10+ molecules per barcode (stLFR) and 1500 molecules in a 30000-record work unit the dense sweep was 236 ms
+        // of a 359 ms step.  Each collected sink is still scored by the same sequential fastScore, so sums keep their order.
+        auto collect = [&](int src, int stamp) {
+            if (tid == 0) sh_ntouch = 0;
+            __syncthreads();
+            for (int j = R.k_beg[ob + src] + tid; j < R.k_end[ob + src]; j += PLACE_T) {
+                const Hot hc = A.hot[R.ord[ob + j]];
+                if (!hc.active) continue;
+                for (long k = (long)A.cand_off[hc.read], e = (long)A.cand_off[hc.read + 1]; k < e; ++k) {
+                    const Hot hk = A.hot[k];
+                    if (hk.best && hk.molid >= 0 && hk.molid != src && atomicExch(&k_mark[hk.molid], stamp) != stamp) k_list[atomicAdd(&sh_ntouch, 1)] = hk.molid;
+                }
+            }
+            __syncthreads();
+            return sh_ntouch;
+        };
         // ---- optimizer.Optimize(model, 1, 2, 4*K): 8*K GenerateMove steps (optimizer.go:15-27, aligner.go:1065-1097) ----
         int cur = 0;
         for (long step = 0; step < 8L * K; ++step) {
             const int src = cur;
             cur = (cur + 1) % K;
-            if (R.k_nact[ob + src] == 0) continue;  // uniform: every thread reads the same word after the barrier below
+            if (R.k_nact[ob + src] == 0 || !k_alt[src]) continue;  // uniform: every thread reads the same words after the barrier below
+            const int ntouch = collect(src, (int)step + 1);
             double bs = -DBL_MAX; int bl = -1, bi = 0x7fffffff;
-            for (int i = tid; i < K; i += PLACE_T) {
-                if (i == src) continue;
+            for (int t = tid; t < ntouch; t += PLACE_T) {
+                const int i = k_list[t];
                 int num;
                 const double sc = place_fast_score(A, R, ob, src, i, &num);
                 const int len = R.k_nact[ob + i];
-                if (num > 0 && (sc > bs || (sc == bs && len > bl))) { bs = sc; bl = len; bi = i; }
+                if (num > 0 && (bi == 0x7fffffff || sc > bs || (sc == bs && (len > bl || (len == bl && i < bi))))) { bs = sc; bl = len; bi = i; }
             }
             // lexicographic max of (score, sink size), smallest index on ties == the sequential rule of GenerateMove
 #pragma unroll
@@ -446,10 +482,12 @@ __global__ void __launch_bounds__(PLACE_T) k_place_rfa(PlaceArgs A, RfaArgs R) {
             }
             __syncthreads();
         }
-        // ---- moleculeMapqProbabilitySums (aligner.go:697-720) ----
+        // ---- moleculeMapqProbabilitySums (aligner.go:697-720): only sinks holding an alternative for an active read of src add anything ----
         for (int src = 0; src < K; ++src) {
-            for (int i = tid; i < K; i += PLACE_T) {
-                if (i == src) continue;
+            if (R.k_nact[ob + src] == 0 || !k_alt[src]) continue;
+            const int ntouch = collect(src, 8 * K + 1 + src);
+            for (int t = tid; t < ntouch; t += PLACE_T) {
+                const int i = k_list[t];
                 int num;
                 R.k_p[ob + i] = pow(10.0, place_fast_score(A, R, ob, src, i, &num));
             }
