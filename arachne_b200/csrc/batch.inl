@@ -213,34 +213,61 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
                                       W.d_intv_n.as<int>(), W.d_sa_off.as<unsigned long long>(), W.d_rows.as<uint64_t>(), cb, W.d_cnt.as<Counters>());
     AR_TRY(cudaGetLastError());
     cudaEventRecord(ev[3], st);
-    // ---- extension + dedup ----
+    // ---- extension + dedup: rounds of (driver -> sorted problem queue -> DP), ext_stage.cuh ----
     const int ext_blocks = sms * 8;
     const int win_cap = 2 * maxlen + 1024 + 4 * opt.w;
     const long cg_warps = (long)sms * 4 * EXT_WARPS;
     AR_ALLOC(W.d_win, (size_t)std::max<long>(cg_warps, (long)ext_blocks * EXT_WARPS) * win_cap);
-    AR_TRY(cudaMemsetAsync(W.d_misc.p, 0, 64, st));
-    ++nl;
     {
-        // columns 0..qlen plus the chunk's read-ahead; qlen <= len - min_seed_len (every seed is at least that long)
-        const int ncols = std::max(1, maxlen - opt.min_seed_len) + EXT_CHUNK;
-        const size_t smem = (size_t)ncols * EXT_BLOCK * sizeof(uint32_t);
+        const int drv_blocks = sms * 4, drv_T = drv_blocks * 128;
+        AR_ALLOC(W.d_hscr, (size_t)drv_T * 2 * (maxlen + 2) * sizeof(int));
+        AR_ALLOC(W.d_rscr, (size_t)drv_T * win_cap);
+        AR_ALLOC(W.d_xstate, (size_t)n_reads * sizeof(ExtState));
+        AR_ALLOC(W.d_xprob, (size_t)n_reads * sizeof(ExtProb));
+        AR_ALLOC(W.d_xres, (size_t)n_reads * sizeof(ExtRes));
+        AR_ALLOC(W.d_xrank, (size_t)n_reads * 4);
+        AR_ALLOC(W.d_xperm, (size_t)n_reads * 4 * 2);
+        AR_ALLOC(W.d_xctl, sizeof(ExtCtl));
+        AR_TRY(cudaMemsetAsync(W.d_xctl.p, 0, sizeof(ExtCtl), st));
+        ExtBufs XB;
+        XB.seq = d_seq; XB.off = d_off; XB.n_reads = (int)n_reads; XB.sa_off = W.d_sa_off.as<unsigned long long>(); XB.b = cb;
+        XB.srt = W.d_srt.as<uint64_t>(); XB.regs = W.d_regs.as<AlnReg>(); XB.n_regs = W.d_nregs.as<int>();
+        XB.hscr = W.d_hscr.as<int>(); XB.rscr = W.d_rscr.as<uint8_t>(); XB.rcap = win_cap; XB.maxlen = maxlen;
+        XB.state = W.d_xstate.as<ExtState>(); XB.prob = W.d_xprob.as<ExtProb>(); XB.res = W.d_xres.as<ExtRes>(); XB.rank = W.d_xrank.as<unsigned>();
+        XB.perm_cur = W.d_xperm.as<int>(); XB.perm_next = XB.perm_cur + n_reads;
+        XB.ctl = W.d_xctl.as<ExtCtl>(); XB.cnt = W.d_cnt.as<Counters>();
+        ExtDpArgs DA;
+        DA.seq = d_seq; DA.off = d_off; DA.tbytes = nullptr; DA.prob = XB.prob; DA.res = XB.res; DA.n_items = &XB.ctl->n_next; DA.head = &XB.ctl->head;
+        DA.ncols = std::max(1, maxlen - opt.min_seed_len) + 2;  // a flank is never longer than len - min_seed_len (every seed is at least that long)
+        DA.zdrop = opt.zdrop; DA.cnt = XB.cnt;
+        const size_t smem = (size_t)DA.ncols * XDP_BLOCK * sizeof(uint32_t);
         if (smem > 200 * 1024) { set_error("read length %d does not fit the extension kernel's shared-memory columns", maxlen); return fail(ARACHNE_ERR_ARG); }
-        AR_TRY(cudaFuncSetAttribute(k_extend2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        AR_TRY(cudaFuncSetAttribute(k_ext_dp<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         int per_sm = 0;
-        AR_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_extend2, EXT_BLOCK, smem));
+        AR_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_ext_dp<true>, XDP_BLOCK, smem));
         if (per_sm < 1) per_sm = 1;
-        const int xblocks = sms * per_sm;
-        const size_t xT = (size_t)xblocks * EXT_BLOCK;
-        AR_ALLOC(W.d_hscr, xT * 2 * (maxlen + 2) * sizeof(int));
-        AR_ALLOC(W.d_rscr, xT * win_cap);
-        ExtArgs xa;
-        xa.seq = d_seq; xa.off = d_off; xa.n_reads = (int)n_reads; xa.sa_off = W.d_sa_off.as<unsigned long long>(); xa.b = cb;
-        xa.srt = W.d_srt.as<uint64_t>(); xa.regs = W.d_regs.as<AlnReg>(); xa.n_regs = W.d_nregs.as<int>();
-        xa.hscr = W.d_hscr.as<int>(); xa.rscr = W.d_rscr.as<uint8_t>(); xa.rcap = win_cap; xa.maxlen = maxlen; xa.ncols = ncols;
-        xa.next = W.d_misc.as<unsigned int>(); xa.cnt = W.d_cnt.as<Counters>();
-        k_extend2<<<xblocks, EXT_BLOCK, smem, st>>>(opt, idx->ref, xa);
+        const int dp_blocks = sms * per_sm;
+        // A read needs one round per ksw_extend2 call it makes (two for most reads).  Rounds are launched four at a time without
+        // looking; the host reads the number of problems the last round emitted and stops at zero.
+        int round = 0;
+        for (;;) {
+            for (int k = 0; k < 4; ++k, ++round) {
+                k_ext_drive<<<drv_blocks, 128, 0, st>>>(opt, idx->ref, XB, round);
+                k_ext_binbase<<<1, 256, 0, st>>>(XB.ctl);
+                k_ext_scatter<<<sms * 4, 256, 0, st>>>(XB, round);
+                DA.perm = XB.perm_next;
+                k_ext_dp<true><<<dp_blocks, XDP_BLOCK, smem, st>>>(opt, idx->ref, DA);
+                k_ext_roll<<<1, 1, 0, st>>>(XB.ctl);
+                nl += 5;
+                std::swap(XB.perm_cur, XB.perm_next);
+            }
+            AR_TRY(cudaGetLastError());
+            AR_TRY(cudaMemcpyAsync(&hs[5], &XB.ctl->n_next, 4, cudaMemcpyDeviceToHost, st));
+            AR_TRY(cudaStreamSynchronize(st));
+            if ((unsigned)hs[5] == 0) break;
+            if (round > 4096) { set_error("extension rounds do not terminate"); return fail(ARACHNE_ERR_OVERFLOW); }
+        }
     }
-    AR_TRY(cudaGetLastError());
     cudaEventRecord(ev[4], st);
     int stages = in->stages ? in->stages : (ARACHNE_STAGE_REGIONS | ARACHNE_STAGE_RESCUE | ARACHNE_STAGE_CIGAR);
     if (stages & ARACHNE_STAGE_PLACE) stages |= ARACHNE_STAGE_CIGAR;  // placement scores the candidates' CIGAR statistics

@@ -1,14 +1,10 @@
-// Chain -> alignment regions: the extension *driver* and the region de-duplication, written once against a
-// cooperative context `Ctx`:
-//   * on the device Ctx is a warp (csrc/warp_ctx.cuh): every lane runs this scalar control flow redundantly
-//     (uniform branches, broadcast loads), global stores are done by the leader lane, and the DP primitives
-//     (ksw_extend / ksw_global) are warp-cooperative;
-//   * in tests/hostsim Ctx is a plain scalar implementation, which pins this control logic on the CPU tier.
-//
-//   mem_chain2aln        bwa/bwamem.c:632-786   cal_max_gap :621-628
-//   mem_sort_dedup_patch bwa/bwamem.c:437-489   mem_patch_reg :406-435
+// Region-level helpers shared by the extension driver, mate rescue and the CIGAR stage, written once against a cooperative
+// context `Ctx` (a warp on the device, csrc/warp_ctx.cuh; one thread in ext_stage.cuh's ThreadCtx; a scalar context in tests/hostsim):
+//   cal_max_gap          bwa/bwamem.c:621-628
 //   bns_fetch_seq        bwa/bntseq.c:421-446   (window clamp to the contig / strand)
+//   mem_sort_dedup_patch bwa/bwamem.c:437-489   mem_patch_reg :406-435
 //   bwa_gen_cigar2 (score-only use)  bwa/bwa.c:121-207
+// The mem_chain2aln driver itself is ext_driver.cuh.
 #pragma once
 #include "chain.cuh"
 
@@ -48,140 +44,6 @@ AR_HD uint8_t ref_base(const RefView& ref, int64_t pos) {
         return 3 - ((ref.pac[f >> 2] >> ((~f & 3) << 1)) & 3);
     }
     return (ref.pac[pos >> 2] >> ((~pos & 3) << 1)) & 3;
-}
-
-struct ExtScratch {
-    uint8_t* rseq;      // reference window buffer, >= win_cap bytes
-    int win_cap;
-    uint64_t* srt;      // >= seeds-in-chain entries
-};
-
-// mem_chain2aln.  seeds: the chain's seeds, contiguous [0,c.n).  av/n_av: the read's region list so far (shared by
-// all chains of the read, bwamem.c:1062-1068).  Returns 0, or a negative error (scratch exhausted).
-template <class Ctx>
-AR_HD int chain2aln(Ctx& ctx, const MemOpt& opt, const RefView& ref, int l_query, const uint8_t* query, const Chain& c,
-                    const Seed* seeds, AlnReg* av, int* n_av, int cap_av, ExtScratch& sc) {
-    int i, k, rid, max_off[2], aw[2];
-    int64_t l_pac = ref.l_pac, rmax[2], tmp, max = 0;
-    if (c.n == 0) return 0;
-    rmax[0] = l_pac << 1; rmax[1] = 0;
-    for (i = 0; i < c.n; ++i) {
-        const Seed& t = seeds[i];
-        int64_t b = t.rbeg - (t.qbeg + cal_max_gap(opt, t.qbeg));
-        int64_t e = t.rbeg + t.len + ((l_query - t.qbeg - t.len) + cal_max_gap(opt, l_query - t.qbeg - t.len));
-        rmax[0] = rmax[0] < b ? rmax[0] : b;
-        rmax[1] = rmax[1] > e ? rmax[1] : e;
-        if (t.len > max) max = t.len;
-    }
-    rmax[0] = rmax[0] > 0 ? rmax[0] : 0;
-    rmax[1] = rmax[1] < l_pac << 1 ? rmax[1] : l_pac << 1;
-    if (rmax[0] < l_pac && l_pac < rmax[1]) {
-        if (seeds[0].rbeg < l_pac) rmax[1] = l_pac;
-        else rmax[0] = l_pac;
-    }
-    rid = fetch_window(ref, &rmax[0], seeds[0].rbeg, &rmax[1]);
-    (void)rid;
-    if (rmax[1] - rmax[0] > sc.win_cap) return -2;
-    ctx.fetch_ref(ref, rmax[0], rmax[1], sc.rseq);
-    const uint8_t* rseq = sc.rseq;
-
-    if (ctx.leader()) {
-        for (i = 0; i < c.n; ++i) sc.srt[i] = (uint64_t)seeds[i].score << 32 | (uint32_t)i;
-        ks_introsort((size_t)c.n, sc.srt, [](uint64_t a, uint64_t b) { return a < b; });
-    }
-    ctx.sync();
-
-    for (k = c.n - 1; k >= 0; --k) {
-        const Seed& s = seeds[(uint32_t)sc.srt[k]];
-        int nav = *n_av;
-        for (i = 0; i < nav; ++i) {  // has this seed been covered by an earlier extension of this read?
-            const AlnReg& p = av[i];
-            int64_t rd;
-            int qd, w, max_gap;
-            if (s.rbeg < p.rb || s.rbeg + s.len > p.re || s.qbeg < p.qb || s.qbeg + s.len > p.qe) continue;
-            if (s.len - p.seedlen0 > .1 * l_query) continue;
-            qd = s.qbeg - p.qb; rd = s.rbeg - p.rb;
-            max_gap = cal_max_gap(opt, qd < rd ? qd : (int)rd);
-            w = max_gap < p.w ? max_gap : p.w;
-            if (qd - rd < w && rd - qd < w) break;
-            qd = p.qe - (s.qbeg + s.len); rd = p.re - (s.rbeg + s.len);
-            max_gap = cal_max_gap(opt, qd < rd ? qd : (int)rd);
-            w = max_gap < p.w ? max_gap : p.w;
-            if (qd - rd < w && rd - qd < w) break;
-        }
-        if (i < nav) {  // (almost) contained: extend only if an overlapping seed hints at a different alignment
-            for (i = k + 1; i < c.n; ++i) {
-                if (sc.srt[i] == 0) continue;
-                const Seed& t = seeds[(uint32_t)sc.srt[i]];
-                if (t.len < s.len * .95) continue;
-                if (s.qbeg <= t.qbeg && s.qbeg + s.len - t.qbeg >= s.len >> 2 && t.qbeg - s.qbeg != t.rbeg - s.rbeg) break;
-                if (t.qbeg <= s.qbeg && t.qbeg + t.len - s.qbeg >= s.len >> 2 && s.qbeg - t.qbeg != s.rbeg - t.rbeg) break;
-            }
-            if (i == c.n) {
-                if (ctx.leader()) sc.srt[k] = 0;
-                ctx.sync();
-                continue;
-            }
-        }
-        if (nav >= cap_av) return -3;
-        AlnReg a;
-        a.rb = a.re = 0; a.qb = a.qe = 0; a.sub = a.alt_sc = a.csub = a.sub_n = 0; a.seedcov = 0; a.secondary = a.secondary_all = 0;
-        a.seedlen0 = 0; a.n_comp_is_alt = 0; a.frac_rep = 0.f; a.hash = 0;
-        a.w = aw[0] = aw[1] = opt.w;
-        a.score = a.truesc = -1;
-        a.rid = c.rid;
-
-        if (s.qbeg) {  // left extension: both sequences reversed, read backwards from the seed
-            int qle = 0, tle = 0, gtle = 0, gscore = 0;
-            tmp = s.rbeg - rmax[0];
-            for (i = 0; i < 2; ++i) {  // MAX_BAND_TRY
-                int prev = a.score;
-                aw[0] = opt.w << i;
-                a.score = ctx.ksw_extend(opt, s.qbeg, query + s.qbeg - 1, -1, (int)tmp, rseq + tmp - 1, -1, aw[0], opt.pen_clip5,
-                                         opt.zdrop, s.len * opt.a, &qle, &tle, &gtle, &gscore, &max_off[0]);
-                if (a.score == prev || max_off[0] < (aw[0] >> 1) + (aw[0] >> 2)) break;
-            }
-            if (gscore <= 0 || gscore <= a.score - opt.pen_clip5) {
-                a.qb = s.qbeg - qle; a.rb = s.rbeg - tle;
-                a.truesc = a.score;
-            } else {
-                a.qb = 0; a.rb = s.rbeg - gtle;
-                a.truesc = gscore;
-            }
-        } else { a.score = a.truesc = s.len * opt.a; a.qb = 0; a.rb = s.rbeg; }
-
-        if (s.qbeg + s.len != l_query) {  // right extension
-            int qle = 0, tle = 0, gtle = 0, gscore = 0, sc0 = a.score;
-            int qe = s.qbeg + s.len;
-            int64_t re = s.rbeg + s.len - rmax[0];
-            for (i = 0; i < 2; ++i) {
-                int prev = a.score;
-                aw[1] = opt.w << i;
-                a.score = ctx.ksw_extend(opt, l_query - qe, query + qe, 1, (int)(rmax[1] - rmax[0] - re), rseq + re, 1, aw[1],
-                                         opt.pen_clip3, opt.zdrop, sc0, &qle, &tle, &gtle, &gscore, &max_off[1]);
-                if (a.score == prev || max_off[1] < (aw[1] >> 1) + (aw[1] >> 2)) break;
-            }
-            if (gscore <= 0 || gscore <= a.score - opt.pen_clip3) {
-                a.qe = qe + qle; a.re = rmax[0] + re + tle;
-                a.truesc += a.score - sc0;
-            } else {
-                a.qe = l_query; a.re = rmax[0] + re + gtle;
-                a.truesc += gscore - sc0;
-            }
-        } else { a.qe = l_query; a.re = s.rbeg + s.len; }
-
-        for (i = 0, a.seedcov = 0; i < c.n; ++i) {
-            const Seed& t = seeds[i];
-            if (t.qbeg >= a.qb && t.qbeg + t.len <= a.qe && t.rbeg >= a.rb && t.rbeg + t.len <= a.re) a.seedcov += t.len;
-        }
-        a.w = aw[0] > aw[1] ? aw[0] : aw[1];
-        a.seedlen0 = s.len;
-        a.frac_rep = c.frac_rep;
-        if (ctx.leader()) av[nav] = a;
-        *n_av = nav + 1;
-        ctx.sync();
-    }
-    return 0;
 }
 
 // bwa_gen_cigar2 used score-only by mem_patch_reg (n_cigar == NM == NULL): returns 1 and *score on success, 0 when the

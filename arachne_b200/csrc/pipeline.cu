@@ -1,14 +1,14 @@
-// libarachne_cuda: kernels and batch orchestration of the candidate-alignment hot path (sm_100a).
+// libarachne_cuda: kernels and batch orchestration of the candidate-alignment / read-placement hot path (sm_100a).
 //
-// Stages of one batch (reads = 2 x pairs), every stage a kernel over the whole batch:
-//   k_seed    thread / read   mem_collect_intv: SMEMs + re-seeding + LAST-like seeds -> SA intervals
-//   (scan)                    seeds per read -> offsets
-//   k_expand  thread / read   one SA row per seed occurrence (bwamem.c:278-283)
-//   k_sa      thread / row    bwt_sa LF walks (geometric length), each touching one 64-byte occ line per step
-//   k_chain   thread / read   B-tree chaining, chain weights, chain filter
-//   k_extend  warp   / read   mem_chain2aln (ksw_extend2 left/right, band retry) + mem_sort_dedup_patch
-//   ...       rescue, CIGAR, placement: see rescue.cuh / cigar.cuh / place.cuh
-// The index is read-only and shared; all per-batch state lives in one device workspace that is reused.
+// Stages of one batch (reads = 2 x pairs), every stage one or a few kernels over the whole batch:
+//   k_pack_reads, k_seed2, k_sort_intv   mem_collect_intv: SMEMs + re-seeding + LAST-like seeds -> SA intervals (seed_kernel.cuh)
+//   k_expand, k_sa                       one SA row per seed occurrence (bwamem.c:278-283), bwt_sa
+//   k_chain                              chaining, chain weights, chain filter (chain.cuh)
+//   k_ext_drive / k_ext_dp rounds        mem_chain2aln driver + ksw_extend2 as queues of uniform problems, region dedup (ext_stage.cuh)
+//   k_rescue                             mem_matesw as GoBwaMemMateSW drives it (rescue.cuh, warp_ctx.cuh)
+//   k_cigar_fast / _band / k_cigar       mem_reg2aln + the GetAlignments walk (cigar_kernel.cuh, cigar.cuh)
+//   k_place_*                            tagBestAlignments .. optimizer .. MAPQ (place.cuh)
+// The index is read-only and shared; all per-batch state lives in a device workspace that is reused (batch.inl).
 #include <cuda_runtime.h>
 #include <cub/device/device_scan.cuh>
 #include <cub/device/device_radix_sort.cuh>
@@ -20,7 +20,6 @@
 #include <vector>
 #include <algorithm>
 #include "index.cuh"
-#include "smem.cuh"
 #include "warp_ctx.cuh"
 #include "cigar.cuh"
 
@@ -154,70 +153,12 @@ __global__ void __launch_bounds__(128) k_chain(MemOpt opt, RefView ref, const in
     }
 }
 
-// ------------------------------------------------------------------------------------------------ k_extend2
+// ------------------------------------------------------------------------------------------------ extension rounds
 }  // namespace arachne
-#include "extend_kernel.cuh"
-#include "extend_stage.cuh"
+#include "ext_stage.cuh"
 namespace arachne {
 
-// ------------------------------------------------------------------------------------------------ k_extend (warp per read; kept for the stage entry points)
 constexpr int EXT_WARPS = 4;
-
-__global__ void __launch_bounds__(EXT_WARPS * 32) k_extend(MemOpt opt, RefView ref, const uint8_t* __restrict__ seq, const int64_t* __restrict__ off,
-                                                           int n_reads, const unsigned long long* __restrict__ sa_off, ChainBufs b, uint64_t* srt,
-                                                           AlnReg* regs, int* n_regs, uint8_t* win, int win_cap, unsigned int* next, Counters* cnt) {
-    const int lane = threadIdx.x & 31;
-    const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    WarpCtx ctx;
-    unsigned long long cells = 0, calls = 0;
-    ctx.lane = lane; ctx.cells = &cells; ctx.z = nullptr; ctx.z_cap = 0;
-    ExtScratch sc;
-    sc.rseq = win + (size_t)gw * win_cap; sc.win_cap = win_cap;
-    for (;;) {
-        int r = 0;
-        if (lane == 0) r = (int)atomicAdd(next, 1u);
-        r = __shfl_sync(FULL, r, 0);
-        if (r >= n_reads) break;
-        const int nk = b.n_chain[r];
-        int n_av = 0;
-        if (nk > 0) {
-            const unsigned long long o = sa_off[r];
-            const int len = (int)(off[r + 1] - off[r]);
-            const uint8_t* q = seq + off[r];
-            AlnReg* av = regs + o;
-            const int cap = b.n_kseed[r];
-            sc.srt = srt + o;
-            int rc = 0;
-            for (int i = 0; i < nk && rc == 0; ++i) {
-                const Chain c = b.chains[o + b.order[o + i]];
-                rc = chain2aln(ctx, opt, ref, len, q, c, b.kseeds + o + c.first_seed, av, &n_av, cap, sc);
-            }
-            if (rc == 0) {
-                calls += n_av;
-                int m = sort_dedup_patch(ctx, opt, ref, q, n_av, av, sc.rseq, win_cap);
-                if (m < 0) rc = m; else n_av = m;
-            }
-            if (rc != 0) { if (lane == 0) raise(cnt, ARACHNE_ERR_OVERFLOW, r); n_av = 0; }
-            if (lane == 0)
-                for (int i = 0; i < n_av; ++i)  // mem_align1_core tail, bwamem.c:1078-1082
-                    if (av[i].rid >= 0 && ref.contigs[av[i].rid].is_alt) av[i].n_comp_is_alt |= 1 << 30;
-            __syncwarp();
-        }
-        if (lane == 0) n_regs[r] = n_av;
-    }
-    if (lane == 0 && (cells || calls)) { atomicAdd(&cnt->ext_cells, cells); atomicAdd(&cnt->ext_calls, calls); }
-}
-
-__global__ void k_gather_regs(int n_reads, const unsigned long long* __restrict__ sa_off, const unsigned long long* __restrict__ reg_off,
-                              const AlnReg* __restrict__ regs, AlnReg* out) {
-    const int lane = threadIdx.x & 31;
-    for (int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; r < n_reads; r += (gridDim.x * blockDim.x) >> 5) {
-        const uint32_t* src = reinterpret_cast<const uint32_t*>(regs + sa_off[r]);
-        uint32_t* dst = reinterpret_cast<uint32_t*>(out + reg_off[r]);
-        int nw = (int)(reg_off[r + 1] - reg_off[r]) * (int)(sizeof(AlnReg) / 4);
-        for (int k = lane; k < nw; k += 32) dst[k] = src[k];
-    }
-}
 
 // ------------------------------------------------------------------------------------------------ k_rescue
 // Warp per pair.  Most pairs already hold a consistent hit for every anchor, in which case mem_matesw returns before
@@ -372,25 +313,6 @@ __global__ void k_occ(FMIndex fm, long n, const uint64_t* k, const uint64_t* l, 
         fm_2occ4(fm, k[i], l[i], cnt + 8 * i, cnt + 8 * i + 4);
 }
 
-__global__ void __launch_bounds__(EXT_WARPS * 32) k_ksw_extend(MemOpt opt, long n, const uint8_t* __restrict__ q, const int64_t* __restrict__ q_off,
-                                                               const uint8_t* __restrict__ t, const int64_t* __restrict__ t_off,
-                                                               const int* __restrict__ h0, const int* __restrict__ w, int end_bonus, int zdrop,
-                                                               int* out, unsigned long long* cells_out) {
-    const int lane = threadIdx.x & 31;
-    unsigned long long cells = 0;
-    WarpCtx ctx; ctx.lane = lane; ctx.cells = &cells; ctx.z = nullptr; ctx.z_cap = 0;
-    for (long i = (blockIdx.x * (long)blockDim.x + threadIdx.x) >> 5; i < n; i += ((long)gridDim.x * blockDim.x) >> 5) {
-        int qle, tle, gtle, gscore, max_off;
-        int qlen = (int)(q_off[i + 1] - q_off[i]), tlen = (int)(t_off[i + 1] - t_off[i]);
-        int sc = ctx.ksw_extend(opt, qlen, q + q_off[i], 1, tlen, t + t_off[i], 1, w[i], end_bonus, zdrop, h0[i], &qle, &tle, &gtle, &gscore, &max_off);
-        if (lane == 0) {
-            int* o = out + 6 * i;
-            o[0] = sc; o[1] = qle; o[2] = tle; o[3] = gtle; o[4] = gscore; o[5] = max_off;
-        }
-    }
-    if (lane == 0 && cells) atomicAdd(cells_out, cells);
-}
-
 __global__ void __launch_bounds__(EXT_WARPS * 32) k_ksw_global(MemOpt opt, long n, const uint8_t* __restrict__ q, const int64_t* __restrict__ q_off,
                                                                const uint8_t* __restrict__ t, const int64_t* __restrict__ t_off,
                                                                const int* __restrict__ w, int* scores, uint8_t* zbuf, long z_cap,
@@ -410,6 +332,10 @@ __global__ void __launch_bounds__(EXT_WARPS * 32) k_ksw_global(MemOpt opt, long 
 struct DevBuf {
     void* p = nullptr;
     size_t cap = 0;
+    DevBuf() = default;
+    DevBuf(const DevBuf&) = delete;
+    DevBuf& operator=(const DevBuf&) = delete;
+    ~DevBuf() { release(); }  // stage entry points return early on errors: nothing may leak
     int ensure(size_t bytes) {
         if (bytes <= cap) return 0;
         if (p) cudaFree(p);
@@ -427,6 +353,10 @@ static int validate_opts(const arachne_mem_opt_t* o) {
     if (!o) { set_error("null options"); return ARACHNE_ERR_ARG; }
     if (o->e_del <= 0 || o->e_ins <= 0 || o->a <= 0 || o->w <= 0 || o->max_occ <= 0 || o->min_seed_len <= 0) {
         set_error("options out of range"); return ARACHNE_ERR_OPTS;
+    }
+    // the DP kernels keep H and E in 13-bit fields (scores up to 8191) and the substitution scores x16 in signed bytes
+    if ((long)o->a * ARACHNE_MAX_READ_LEN > 8191 || o->a > 7 || o->b < 0 || o->b > 8 || o->o_del < 0 || o->o_ins < 0) {
+        set_error("scoring out of the kernels' range: need a <= 7, 0 <= b <= 8, a * %d <= 8191", ARACHNE_MAX_READ_LEN); return ARACHNE_ERR_OPTS;
     }
     for (int i = 0, k = 0; i < 5; ++i)
         for (int j = 0; j < 5; ++j, ++k) {
@@ -473,7 +403,7 @@ struct BatchPriv {
 struct Workspace {
     DevBuf d_qpk, d_intv_cnt2, d_seq, d_off, d_scratch, d_arena, d_misc, d_intv_off, d_intv_n, d_nsa, d_sa_off, d_rows, d_cnt, d_tmp;
     DevBuf d_seeds, d_kseeds, d_chains, d_nodes, d_order, d_kept, d_nchain, d_nkseed, d_srt, d_regs, d_nregs, d_win, d_reg_off, d_out;
-    DevBuf d_nregs_bak, d_reg_loc, d_blist, d_resc, d_reg_read, d_z, d_cig_scr, d_mm_scr, d_alns, d_cig, d_mm, d_hscr, d_rscr;
+    DevBuf d_nregs_bak, d_reg_loc, d_blist, d_resc, d_reg_read, d_z, d_cig_scr, d_mm_scr, d_alns, d_cig, d_mm, d_hscr, d_rscr, d_xstate, d_xprob, d_xres, d_xrank, d_xperm, d_xctl;
     DevBuf d_bc_off, d_run_rfa, d_rand_seed, d_centro, d_pl_cnt, d_pl_scan, d_cand_off, d_lmp, d_cands, d_hot, d_aux, d_slow, d_slot_of_bc, d_bc_of_slot,
         d_first, d_keys_a, d_keys_b, d_vals_a, d_vals_b, d_seg_off, d_mol, d_list2, d_list3, d_zband;
     cudaStream_t own_stream = nullptr;
@@ -483,7 +413,7 @@ struct Workspace {
     std::vector<DevBuf*> all() {
         return {&d_qpk, &d_intv_cnt2, &d_seq, &d_off, &d_scratch, &d_arena, &d_misc, &d_intv_off, &d_intv_n, &d_nsa, &d_sa_off, &d_rows, &d_cnt, &d_tmp,
                 &d_seeds, &d_kseeds, &d_chains, &d_nodes, &d_order, &d_kept, &d_nchain, &d_nkseed, &d_srt, &d_regs, &d_nregs,
-                &d_win, &d_reg_off, &d_out, &d_nregs_bak, &d_reg_loc, &d_blist, &d_resc, &d_reg_read, &d_z, &d_cig_scr, &d_mm_scr, &d_alns, &d_cig, &d_mm, &d_hscr, &d_rscr,
+                &d_win, &d_reg_off, &d_out, &d_nregs_bak, &d_reg_loc, &d_blist, &d_resc, &d_reg_read, &d_z, &d_cig_scr, &d_mm_scr, &d_alns, &d_cig, &d_mm, &d_hscr, &d_rscr, &d_xstate, &d_xprob, &d_xres, &d_xrank, &d_xperm, &d_xctl,
                 &d_bc_off, &d_run_rfa, &d_rand_seed, &d_centro, &d_pl_cnt, &d_pl_scan, &d_cand_off, &d_lmp, &d_cands, &d_hot, &d_aux, &d_slow, &d_slot_of_bc,
                 &d_bc_of_slot, &d_first, &d_keys_a, &d_keys_b, &d_vals_a, &d_vals_b, &d_seg_off, &d_mol, &d_list2, &d_list3, &d_zband};
     }
@@ -753,62 +683,72 @@ int arachne_seed_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, int6
 int arachne_ksw_extend_batch(int device, const arachne_mem_opt_t* opt_, int64_t n, const uint8_t* q, const int64_t* q_off, const uint8_t* t,
                              const int64_t* t_off, const int32_t* h0, const int32_t* w, int end_bonus, int zdrop, int32_t* out, uint64_t* cells,
                              float* kernel_ms, int repeat) {
-    if (!q || !q_off || !t || !t_off || !h0 || !w || !out || n < 0) { set_error("arachne_ksw_extend_batch: null argument"); return ARACHNE_ERR_ARG; }
+    if (!q || !q_off || !t || !t_off || !h0 || !w || !out || n < 0 || n > 0x7fffffff) { set_error("arachne_ksw_extend_batch: bad argument"); return ARACHNE_ERR_ARG; }
     int rc = validate_opts(opt_);
     if (rc) return rc;
+    int maxq = 1;
+    std::vector<ExtProb> probs((size_t)n);
+    std::vector<int> order((size_t)n);
     for (int64_t i = 0; i < n; ++i) {
-        if (q_off[i + 1] - q_off[i] > ARACHNE_MAX_READ_LEN || q_off[i + 1] - q_off[i] < 1 || h0[i] <= 0) {
+        const int64_t ql = q_off[i + 1] - q_off[i], tl = t_off[i + 1] - t_off[i];
+        if (ql > ARACHNE_MAX_READ_LEN || ql < 1 || h0[i] <= 0 || tl < 0 || tl > 0x7fffffff) {
             set_error("problem %lld: qlen must be 1..%d and h0 > 0 (ksw.c:385)", (long long)i, ARACHNE_MAX_READ_LEN); return ARACHNE_ERR_ARG;
         }
+        if ((long)h0[i] + ql * opt_->a > 8191) { set_error("problem %lld: h0 + qlen * a exceeds the kernel's 13-bit score fields", (long long)i); return ARACHNE_ERR_ARG; }
+        maxq = std::max<int>(maxq, (int)ql);
+        ExtProb& P = probs[(size_t)i];
+        P.read = (int32_t)i; P.q0 = 0; P.qlen = (int32_t)ql; P.tlen = (int32_t)tl; P.w = w[i]; P.h0 = h0[i]; P.end_bonus = end_bonus; P.dirs = 0; P.tpos = t_off[i];
+        order[(size_t)i] = (int)i;
     }
+    // the queue k_ext_dp consumes is sorted by query length, longest first (k_ext_binbase / k_ext_scatter do this in the pipeline)
+    std::stable_sort(order.begin(), order.end(), [&](int x, int y) { return probs[(size_t)x].qlen > probs[(size_t)y].qlen; });
     MemOpt opt; memcpy(&opt, opt_, sizeof(opt));
     if (arachne_device_count() <= device) { set_error("no CUDA device %d (no CPU path)", device); return ARACHNE_ERR_CUDA; }
     AR_CUDA(cudaSetDevice(device));
-    DevBuf dq, dqo, dt, dto, dh, dw, dout, dc;
-    if (dq.ensure(q_off[n] + 16) || dqo.ensure((n + 1) * 8) || dt.ensure(t_off[n] + 16) || dto.ensure((n + 1) * 8) || dh.ensure(n * 4 + 4) ||
-        dw.ensure(n * 4 + 4) || dout.ensure(n * 24 + 8) || dc.ensure(16)) { set_error("out of device memory"); return ARACHNE_ERR_CUDA; }
+    DevBuf dq, dqo, dt, dp, dperm, dres, dc, dctl;
+    if (dq.ensure(q_off[n] + 16) || dqo.ensure((n + 1) * 8) || dt.ensure(t_off[n] + 16) || dp.ensure(n * sizeof(ExtProb) + 8) || dperm.ensure(n * 4 + 4) ||
+        dres.ensure(n * sizeof(ExtRes) + 8) || dc.ensure(sizeof(Counters)) || dctl.ensure(16)) { set_error("out of device memory"); return ARACHNE_ERR_CUDA; }
     AR_CUDA(cudaMemcpy(dq.p, q, q_off[n], cudaMemcpyHostToDevice)); AR_CUDA(cudaMemcpy(dqo.p, q_off, (n + 1) * 8, cudaMemcpyHostToDevice));
-    AR_CUDA(cudaMemcpy(dt.p, t, t_off[n], cudaMemcpyHostToDevice)); AR_CUDA(cudaMemcpy(dto.p, t_off, (n + 1) * 8, cudaMemcpyHostToDevice));
-    AR_CUDA(cudaMemcpy(dh.p, h0, n * 4, cudaMemcpyHostToDevice)); AR_CUDA(cudaMemcpy(dw.p, w, n * 4, cudaMemcpyHostToDevice));
+    AR_CUDA(cudaMemcpy(dt.p, t, t_off[n], cudaMemcpyHostToDevice));
+    AR_CUDA(cudaMemcpy(dp.p, probs.data(), n * sizeof(ExtProb), cudaMemcpyHostToDevice));
+    AR_CUDA(cudaMemcpy(dperm.p, order.data(), n * 4, cudaMemcpyHostToDevice));
+    AR_CUDA(cudaMemset(dc.p, 0, sizeof(Counters)));
     cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
     if (repeat < 1) repeat = 1;
-    // the lane-per-problem DPX kernel (extend_stage.cuh, same DP core as the pipeline's k_extend2); ARACHNE_KSW_WARP=1 selects the
-    // warp-cooperative kernel instead
-    const bool warp_kernel = getenv("ARACHNE_KSW_WARP") && atoi(getenv("ARACHNE_KSW_WARP")) != 0;
-    int maxq = 1;
-    for (int64_t i = 0; i < n; ++i) maxq = std::max<int>(maxq, (int)(q_off[i + 1] - q_off[i]));
-    const size_t smem = (size_t)(maxq + 1 + EXT_CHUNK) * EXT_BLOCK * sizeof(uint32_t);
+    ExtDpArgs DA;
+    DA.seq = dq.as<uint8_t>(); DA.off = dqo.as<int64_t>(); DA.tbytes = dt.as<uint8_t>(); DA.prob = dp.as<ExtProb>(); DA.res = dres.as<ExtRes>();
+    DA.perm = dperm.as<int>(); DA.n_items = dctl.as<unsigned>(); DA.head = dctl.as<unsigned>() + 1; DA.ncols = maxq + 2; DA.zdrop = zdrop; DA.cnt = dc.as<Counters>();
+    const size_t smem = (size_t)DA.ncols * XDP_BLOCK * sizeof(uint32_t);
     int per_sm = 1;
-    if (!warp_kernel) {
-        AR_CUDA(cudaFuncSetAttribute(k_ksw_extend_lane, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        AR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_ksw_extend_lane, EXT_BLOCK, smem));
-        if (per_sm < 1) per_sm = 1;
-    }
-    const int blocks = warp_kernel ? sm_count(device) * 8 : sm_count(device) * per_sm;
-    // one untimed launch, then `repeat` timed ones
-    for (int it = 0; it <= repeat; ++it) {
-        if (it == 1) cudaEventRecord(e0);
-        AR_CUDA(cudaMemsetAsync(dc.p, 0, 16));
-        if (warp_kernel) {
-            k_ksw_extend<<<blocks, EXT_WARPS * 32>>>(opt, (long)n, dq.as<uint8_t>(), dqo.as<int64_t>(), dt.as<uint8_t>(), dto.as<int64_t>(), dh.as<int>(),
-                                                     dw.as<int>(), end_bonus, zdrop, dout.as<int>(), dc.as<unsigned long long>());
-        } else {
-            KswStageArgs KA;
-            KA.n = (long)n; KA.q = dq.as<uint8_t>(); KA.q_off = dqo.as<int64_t>(); KA.t = dt.as<uint8_t>(); KA.t_off = dto.as<int64_t>();
-            KA.h0 = dh.as<int>(); KA.w = dw.as<int>(); KA.end_bonus = end_bonus; KA.zdrop = zdrop; KA.out = dout.as<int>();
-            KA.cells_out = dc.as<unsigned long long>(); KA.next = dc.as<unsigned>() + 2; KA.maxq = maxq;
-            k_ksw_extend_lane<<<blocks, EXT_BLOCK, smem>>>(opt, KA);
-        }
+    AR_CUDA(cudaFuncSetAttribute(k_ext_dp<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    AR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_ext_dp<false>, XDP_BLOCK, smem));
+    if (per_sm < 1) per_sm = 1;
+    const int blocks = sm_count(device) * per_sm;
+    RefView no_ref; memset(&no_ref, 0, sizeof(no_ref));
+    const unsigned ctl0[2] = {(unsigned)n, 0u};
+    for (int it = 0; it <= repeat; ++it) {  // one untimed launch, then `repeat` timed ones
+        if (it == 1) { AR_CUDA(cudaMemset(dc.p, 0, sizeof(Counters))); cudaEventRecord(e0); }
+        AR_CUDA(cudaMemcpyAsync(dctl.p, ctl0, 8, cudaMemcpyHostToDevice));
+        k_ext_dp<false><<<blocks, XDP_BLOCK, smem>>>(opt, no_ref, DA);
         AR_CUDA(cudaGetLastError());
     }
     cudaEventRecord(e1);
     AR_CUDA(cudaDeviceSynchronize());
     float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
     if (kernel_ms) *kernel_ms = ms / repeat;
-    AR_CUDA(cudaMemcpy(out, dout.p, n * 24, cudaMemcpyDeviceToHost));
-    if (cells) AR_CUDA(cudaMemcpy(cells, dc.p, 8, cudaMemcpyDeviceToHost));
+    std::vector<ExtRes> res((size_t)n);
+    AR_CUDA(cudaMemcpy(res.data(), dres.p, n * sizeof(ExtRes), cudaMemcpyDeviceToHost));
+    for (int64_t i = 0; i < n; ++i) {
+        const ExtRes& R = res[(size_t)i];
+        int32_t* o = out + 6 * i;
+        o[0] = R.mx; o[1] = R.max_j + 1; o[2] = R.max_i + 1; o[3] = R.max_ie + 1; o[4] = R.gscore; o[5] = R.max_off;
+    }
+    if (cells) {
+        Counters hc;
+        AR_CUDA(cudaMemcpy(&hc, dc.p, sizeof(hc), cudaMemcpyDeviceToHost));
+        *cells = hc.ext_cells / (unsigned)repeat;
+    }
     cudaEventDestroy(e0); cudaEventDestroy(e1);
-    for (DevBuf* b : {&dq, &dqo, &dt, &dto, &dh, &dw, &dout, &dc}) b->release();
     return ARACHNE_OK;
 }
 

@@ -1,18 +1,11 @@
-// Warp-cooperative DP primitives for sm_100a: one warp per alignment problem, the DP row striped over the
-// lanes in registers (column j lives in lane j / CPL, slot j % CPL).
+// Warp-cooperative DP primitives for sm_100a used by mate rescue and the wide-band CIGAR tier: one warp per problem, the
+// DP row striped over the lanes in registers (column j lives in lane j / CPL, slot j % CPL).
 //
-// ksw_extend2 (bwa/ksw.c:380-479) is reproduced exactly, row-synchronously: the reference trims the band after
-// every row from the *complete* previous row (:465-469), so an anti-diagonal wavefront cannot know a row's
-// extent in time.  Two facts make a row cheap for a warp:
-//   (1) E and F derive from M (the diagonal term), not from H (:439-447), so the horizontal dependency
-//       F(i,j+1) = max(F(i,j) - e_ins, max(M(i,j) - oe_ins, 0)) is a max-plus prefix scan: CPL steps inside a
-//       lane plus a 5-step shuffle scan across lanes -- no lazy-F iteration;
-//   (2) the band bookkeeping (row max with last-index tie-break, first/last non-zero cell) are warp REDUX ops.
-// All max-plus steps use the DPX instructions (__viaddmax_s32 / __vimax3_s32 / _relu variants -> VIADDMNMX, VIMNMX3).
-// Stale eh[] entries beyond `end` are kept exactly as the reference leaves them (hard part 1).
-//
-// ksw_global2 (bwa/ksw.c:504-606) uses the same scan with a fixed band and -inf borders and writes the
-// reference's direction byte per cell for the traceback.
+// ksw_global2 (bwa/ksw.c:504-606): E and F derive from M (the diagonal term), not from H, so the horizontal dependency
+// F(i,j+1) = max(F(i,j) - e_ins, M(i,j) - oe_ins) is a max-plus prefix scan: CPL steps inside a lane plus a 5-step shuffle
+// scan across lanes -- no lazy-F iteration; fixed band, -inf borders, the reference's direction byte per cell for the
+// traceback.  All max-plus steps use the DPX instructions (__viaddmax_s32 / __vimax3_s32 -> VIADDMNMX, VIMNMX3).
+// (ksw_extend2 does not live here: it runs one problem per lane in ext_stage.cuh.)
 #pragma once
 #include "extend.cuh"
 #include "rescue.cuh"
@@ -24,138 +17,6 @@ constexpr unsigned FULL = 0xffffffffu;
 
 AR_D int sw_score(int a, int nb, int tb, int qb) {  // bwa_fill_scmat, bwa/bwa.c:109-118
     return (tb > 3 || qb > 3) ? -1 : (tb == qb ? a : nb);
-}
-
-template <int CPL>
-__device__ __noinline__ int ksw_extend_warp(const MemOpt& opt, int qlen, const uint8_t* q, int qs, int tlen, const uint8_t* t, int ts,
-                                            int w, int end_bonus, int zdrop, int h0, int* qle_, int* tle_, int* gtle_, int* gscore_,
-                                            int* max_off_, unsigned long long* cells_) {
-    const int lane = threadIdx.x & 31;
-    const int e_del = opt.e_del, e_ins = opt.e_ins, oe_del = opt.o_del + opt.e_del, oe_ins = opt.o_ins + opt.e_ins;
-    const int sa = opt.a, snb = -opt.b;
-    const int j0 = lane * CPL;
-    int hp[CPL], ep[CPL], qb[CPL];
-#pragma unroll
-    for (int c = 0; c < CPL; ++c) {
-        int j = j0 + c;
-        qb[c] = j < qlen ? q[(long)j * qs] : 4;
-        // first row: eh[0].h = h0, eh[j].h = max(0, h0 - oe_ins - (j-1) e_ins) while positive (:395-397)
-        int v = j == 0 ? h0 : h0 - oe_ins - (j - 1) * e_ins;
-        hp[c] = (j <= qlen && v > 0) ? v : 0;
-        ep[c] = 0;
-    }
-    int mx = sa > snb ? sa : snb; mx = mx > -1 ? mx : -1;
-    int max_ins = (int)((double)(qlen * mx + end_bonus - opt.o_ins) / e_ins + 1.);
-    max_ins = max_ins > 1 ? max_ins : 1;
-    w = w < max_ins ? w : max_ins;
-    int max_del = (int)((double)(qlen * mx + end_bonus - opt.o_del) / e_del + 1.);
-    max_del = max_del > 1 ? max_del : 1;
-    w = w < max_del ? w : max_del;
-    int max = h0, max_i = -1, max_j = -1, max_ie = -1, gscore = -1, max_off = 0;
-    int beg = 0, end = qlen;
-    unsigned long long cells = 0;
-    for (int i = 0; i < tlen; ++i) {
-        const int tb = t[(long)i * ts];
-        if (beg < i - w) beg = i - w;
-        if (end > i + w + 1) end = i + w + 1;
-        if (end > qlen) end = qlen;
-        int h1i;
-        if (beg == 0) { h1i = h0 - (opt.o_del + e_del * (i + 1)); if (h1i < 0) h1i = 0; }
-        else h1i = 0;
-        cells += end > beg ? end - beg : 0;
-        int M[CPL], g[CPL + 1], en[CPL];
-        g[0] = 0;
-#pragma unroll
-        for (int c = 0; c < CPL; ++c) {
-            int j = j0 + c;
-            bool act = j >= beg && j < end;
-            int m = hp[c] ? hp[c] + sw_score(sa, snb, tb, qb[c]) : 0;
-            M[c] = m;
-            en[c] = __viaddmax_s32(ep[c], -e_del, __viaddmax_s32(m, -oe_del, 0));  // E(i+1,j)
-            int tf = act ? __viaddmax_s32(m, -oe_ins, 0) : 0;
-            g[c + 1] = __viaddmax_s32(g[c], -e_ins, tf);                            // F(i,j+1) with zero carry-in
-        }
-        // carry of F across lanes: inclusive max-plus scan with per-lane decay CPL*e_ins
-        int V = g[CPL];
-        const int D = CPL * e_ins;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            int up = __shfl_up_sync(FULL, V, d);
-            if (lane >= d) V = __viaddmax_s32(up, -d * D, V);
-        }
-        int fin = __shfl_up_sync(FULL, V, 1);
-        if (lane == 0) fin = 0;
-        // H(i,j), row maximum (largest j on ties, :437-438)
-        int h[CPL];
-        unsigned key = 0;
-#pragma unroll
-        for (int c = 0; c < CPL; ++c) {
-            int j = j0 + c;
-            bool act = j >= beg && j < end;
-            int f = __viaddmax_s32(fin, -c * e_ins, g[c]);
-            int hh = __vimax3_s32(M[c], ep[c], f);
-            h[c] = hh;
-            unsigned kk = act ? ((unsigned)hh << 10 | (unsigned)j) : 0u;
-            key = key > kk ? key : kk;
-        }
-        key = __reduce_max_sync(FULL, key);
-        int m = (int)(key >> 10), mj = end > beg ? (int)(key & 1023) : -1;
-        // shift: eh[j+1].h = H(i,j); eh[beg].h = first-column value; eh[end] = {H(i,end-1), 0}
-        int hup = __shfl_up_sync(FULL, h[CPL - 1], 1);
-        if (end > beg) {
-#pragma unroll
-            for (int c = CPL - 1; c >= 0; --c) {
-                int j = j0 + c;
-                int left = c > 0 ? h[c - 1] : hup;
-                if (j > beg && j <= end) hp[c] = left;
-                else if (j == beg) hp[c] = h1i;
-                if (j >= beg && j < end) ep[c] = en[c];
-                else if (j == end) ep[c] = 0;
-            }
-        } else {  // empty row: the reference still writes eh[end] = {h1, 0}
-#pragma unroll
-            for (int c = 0; c < CPL; ++c) if (j0 + c == end) { hp[c] = h1i; ep[c] = 0; }
-        }
-        int jfin = end > beg ? end : beg;  // value of the loop variable after the row
-        if (jfin == qlen) {
-            int mine = 0;
-#pragma unroll
-            for (int c = 0; c < CPL; ++c) if (j0 + c == end) mine = hp[c];
-            int h1 = __shfl_sync(FULL, mine, end / CPL);
-            max_ie = gscore > h1 ? max_ie : i;
-            gscore = gscore > h1 ? gscore : h1;
-        }
-        if (m == 0) break;
-        if (m > max) {
-            max = m; max_i = i; max_j = mj;
-            int off = mj - i; off = off < 0 ? -off : off;
-            max_off = max_off > off ? max_off : off;
-        } else if (zdrop > 0) {
-            if (i - max_i > mj - max_j) {
-                if (max - m - ((i - max_i) - (mj - max_j)) * e_del > zdrop) break;
-            } else {
-                if (max - m - ((mj - max_j) - (i - max_i)) * e_ins > zdrop) break;
-            }
-        }
-        // next row's band: first / last non-zero {h,e} in [beg,end) / [beg,end]
-        int lo = 0x7fffffff, hi = -1;
-#pragma unroll
-        for (int c = 0; c < CPL; ++c) {
-            int j = j0 + c;
-            bool nz = (hp[c] | ep[c]) != 0;
-            if (nz && j >= beg && j < end) lo = lo < j ? lo : j;
-            if (nz && j >= beg && j <= end) hi = hi > j ? hi : j;
-        }
-        lo = __reduce_min_sync(FULL, lo);
-        hi = __reduce_max_sync(FULL, hi);
-        int nbeg = lo == 0x7fffffff ? end : lo;
-        int jl = hi >= nbeg ? hi : nbeg - 1;
-        beg = nbeg;
-        end = jl + 2 < qlen ? jl + 2 : qlen;
-    }
-    *qle_ = max_j + 1; *tle_ = max_i + 1; *gtle_ = max_ie + 1; *gscore_ = gscore; *max_off_ = max_off;
-    if (cells_) *cells_ += cells;
-    return max;
 }
 
 // ksw_global2.  z != nullptr records the direction bytes (row stride n_col) and the caller backtracks.
@@ -392,15 +253,6 @@ struct WarpCtx {
         for (int64_t k = lane; k < end - beg; k += 32) dst[k] = ref_base(ref, beg + k);
         __syncwarp();
     }
-
-    AR_D int ksw_extend(const MemOpt& opt, int qlen, const uint8_t* q, int qs, int tlen, const uint8_t* t, int ts, int w, int end_bonus,
-                        int zdrop, int h0, int* qle, int* tle, int* gtle, int* gscore, int* max_off) const {
-        int r = 0;
-        AR_CPL_DISPATCH(qlen + 1, r = ksw_extend_warp<CPL_>(opt, qlen, q, qs, tlen, t, ts, w, end_bonus, zdrop, h0, qle, tle, gtle, gscore,
-                                                            max_off, lane == 0 ? cells : nullptr));
-        return r;
-    }
-
 
     // ksw_align2 with the mate optionally reverse-complemented on the fly (bwamem_pair.c:131-135)
     AR_D void ksw_local(const MemOpt& opt, int qlen, const uint8_t* ms, int is_rev, int tlen, const uint8_t* t, int xtra, LocalAln* out) {

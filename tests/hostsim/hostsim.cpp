@@ -8,8 +8,8 @@
 #include <string>
 #include <vector>
 #include "../../arachne_b200/csrc/bwt_image.h"
-#include "../../arachne_b200/csrc/smem.cuh"
-#include "../../arachne_b200/csrc/extend.cuh"
+#include "smem.cuh"
+#include "../../arachne_b200/csrc/ext_driver.cuh"
 #include "../../arachne_b200/csrc/rescue.cuh"
 #include "../../arachne_b200/csrc/cigar.cuh"
 #include "../../include/arachne_cuda.h"
@@ -189,12 +189,23 @@ int hs_align1(void* h_, int len, const uint8_t* seq, arachne_alnreg_t* out, int 
     std::vector<AlnReg> av(nks + 1); std::vector<uint64_t> srt(nsa + 1);
     int win_cap = 2 * len + 1024 + 4 * opt.w;
     std::vector<uint8_t> win(win_cap);
-    ExtScratch sc; sc.rseq = win.data(); sc.win_cap = win_cap; sc.srt = srt.data();
     HostCtx ctx; int n_av = 0;
-    for (int i = 0; i < nk; ++i) {
-        const Chain c = chains[order[i]];
-        int rc = chain2aln(ctx, opt, h->ref, len, seq, c, ks.data() + c.first_seed, av.data(), &n_av, nks, sc);
-        if (rc) return -10 + rc;
+    {   // the shipped extension driver (csrc/ext_driver.cuh), its DP problems solved by the oracle's scalar ksw_extend2
+        ExtState S; ext_state_init(S);
+        ExtProb P; ExtRes R = {0, -1, -1, -1, -1, 0};
+        std::vector<uint8_t> qq, tt;
+        for (;;) {
+            int rc = ext_advance(opt, h->ref, 0, len, nk, chains.data(), order.data(), ks.data(), av.data(), nks, srt.data(), S, &R, &P);
+            if (rc < 0) return -10 + rc;
+            if (rc == 0) break;
+            qq.resize(P.qlen + 1); tt.resize(P.tlen + 1);
+            for (int i = 0; i < P.qlen; ++i) qq[i] = seq[P.q0 + ((P.dirs & 1) ? -i : i)];
+            for (int i = 0; i < P.tlen; ++i) tt[i] = ref_base(h->ref, P.tpos + ((P.dirs & 2) ? -(int64_t)i : (int64_t)i));
+            int qle, tle, gtle, gscore, max_off;
+            R.mx = ctx.ksw_extend(opt, P.qlen, qq.data(), 1, P.tlen, tt.data(), 1, P.w, P.end_bonus, opt.zdrop, P.h0, &qle, &tle, &gtle, &gscore, &max_off);
+            R.max_j = qle - 1; R.max_i = tle - 1; R.max_ie = gtle - 1; R.gscore = gscore; R.max_off = max_off;
+        }
+        n_av = S.n_regions;
     }
     int m = sort_dedup_patch(ctx, opt, h->ref, seq, n_av, av.data(), win.data(), win_cap);
     if (m < 0) return -20 + m;

@@ -1,7 +1,9 @@
-// SMEM seeding: bwt_smem1a (bwa/bwt.c:289-351), bwt_seed_strategy1 (:358-379) and the three-pass
-// mem_collect_intv (bwa/bwamem.c:114-162), thread-sequential per read.
+// TEST-ONLY (not part of libarachne_cuda): a thread-sequential restatement of bwt_smem1a (bwa/bwt.c:289-351),
+// bwt_seed_strategy1 (:358-379) and the three-pass mem_collect_intv (bwa/bwamem.c:114-162) over the product's FM-index
+// primitives (csrc/fmindex.cuh).  The host simulation uses it only as the SOURCE of seed intervals for the chaining /
+// extension-driver / dedup code it pins; the shipped seeding kernel is k_seed2 (csrc/seed_kernel.cuh), pinned on the GPU.
 #pragma once
-#include "fmindex.cuh"
+#include "../../arachne_b200/csrc/fmindex.cuh"
 
 namespace arachne {
 
