@@ -67,6 +67,7 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
             if (l > maxlen) maxlen = (int)l;
         }
     }
+    if ((long)opt.a * maxlen > 8191) { set_error("a * read length = %ld exceeds the extension kernel's 13-bit score fields", (long)opt.a * maxlen); return ARACHNE_ERR_OPTS; }
     int ws_slot = 0;
     std::unique_lock<std::mutex> guard = take_ws(idx, &ws_slot);
     AR_CUDA(cudaSetDevice(idx->device));
@@ -239,12 +240,14 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
         ExtDpArgs DA;
         DA.seq = d_seq; DA.off = d_off; DA.tbytes = nullptr; DA.prob = XB.prob; DA.res = XB.res; DA.n_items = &XB.ctl->n_next; DA.head = &XB.ctl->head;
         DA.ncols = std::max(1, maxlen - opt.min_seed_len) + 2;  // a flank is never longer than len - min_seed_len (every seed is at least that long)
-        DA.zdrop = opt.zdrop; DA.cnt = XB.cnt;
+        DA.zdrop = opt.zdrop; DA.one = 1; DA.cnt = XB.cnt;
         const size_t smem = (size_t)DA.ncols * XDP_BLOCK * sizeof(uint32_t);
         if (smem > 200 * 1024) { set_error("read length %d does not fit the extension kernel's shared-memory columns", maxlen); return fail(ARACHNE_ERR_ARG); }
-        AR_TRY(cudaFuncSetAttribute(k_ext_dp<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        // byte-wide score fields whenever no score can exceed 255 (a = 1: always); the 13-bit codec otherwise
+        auto dp_kernel = (long)opt.a * maxlen <= 255 ? k_ext_dp<true, false> : k_ext_dp<true, true>;
+        AR_TRY(cudaFuncSetAttribute(dp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         int per_sm = 0;
-        AR_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_ext_dp<true>, XDP_BLOCK, smem));
+        AR_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, dp_kernel, XDP_BLOCK, smem));
         if (per_sm < 1) per_sm = 1;
         const int dp_blocks = sms * per_sm;
         // A read needs one round per ksw_extend2 call it makes (two for most reads).  Rounds are launched four at a time without
@@ -256,7 +259,7 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
                 k_ext_binbase<<<1, 256, 0, st>>>(XB.ctl);
                 k_ext_scatter<<<sms * 4, 256, 0, st>>>(XB, round);
                 DA.perm = XB.perm_next;
-                k_ext_dp<true><<<dp_blocks, XDP_BLOCK, smem, st>>>(opt, idx->ref, DA);
+                dp_kernel<<<dp_blocks, XDP_BLOCK, smem, st>>>(opt, idx->ref, DA);
                 k_ext_roll<<<1, 1, 0, st>>>(XB.ctl);
                 nl += 5;
                 std::swap(XB.perm_cur, XB.perm_next);

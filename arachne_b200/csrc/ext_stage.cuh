@@ -12,9 +12,12 @@
 // DPX), 18 of 32 lanes active, 168 registers.  Here the DP kernel does nothing but rows:
 //   * row-synchronous lanes: one trip of the warp's loop = one row of every lane's problem; the queue is sorted by query
 //     length, so the lanes of a warp run rows of nearly the same width; row start / row end execute convergently;
-//   * a column is one 32-bit shared-memory word [column][lane] (bank = lane): q (3 bits) | 16*H << 0 | 16*E << 13.  Scores are
-//     kept multiplied by 16, so H needs no shift after the mask and the word's low nibble is directly the PRMT selector of the
-//     row's substitution-score byte table (one PRMT + sign extension instead of two compares and two selects);
+//   * a column is one 32-bit shared-memory word [column][lane] (bank = lane): E << 24 | H << 16 | selector.  The low half is
+//     a ready-made PRMT selector (q * 0x1111 + 0x8880: "byte q, sign-replicated") into the row's 5-entry substitution-score
+//     byte table, so a cell's score is ONE instruction; H and E are bytes (scores never exceed a * read length <= 255,
+//     checked by the callers) extracted and re-packed by PRMT as well.  The integer ALU pipe is what bounds this kernel
+//     (16 lanes per scheduler per clock, ncu: 70 % busy in the first version), so the cell is written for few ALU-pipe
+//     instructions (~9: 3 PRMT, 1 shift, 4 DPX, the row-maximum key) and the rest as IMADs, which issue to the FMA pipe;
 //   * max-plus steps on DPX (VIADDMNMX / VIMNMX3): M = max(min(H + s, H << 8), 0) reproduces `M ? M + s : 0` (a negative M and
 //     a zero M are indistinguishable downstream: every consumer clamps at zero), E and F are one add + one VIADDMNMX.RELU;
 //   * the band for the next row (ksw.c:465-468) is found by re-reading the few zero words at the row's two edges;
@@ -154,7 +157,6 @@ __global__ void k_ext_roll(ExtCtl* c) { c->n_cur = c->n_next; }
 
 // ------------------------------------------------------------------------------------------------ k_ext_dp
 constexpr int XDP_BLOCK = 128;
-constexpr unsigned XDP_QMASK = 7u, XDP_HMASK = 0x1fff0u;
 
 struct ExtDpArgs {
     const uint8_t* seq; const int64_t* off;  // queries: problem p reads seq[off[p.read] + p.q0 + x * (+1|-1)]
@@ -164,24 +166,51 @@ struct ExtDpArgs {
     const unsigned* n_items; unsigned* head;
     int ncols;                               // column words per lane, >= longest query + 2
     int zdrop;
+    int one;                                 // 1 (see k_ext_dp)
     Counters* cnt;
 };
 
-template <bool kPackedRef>
+// Column-word codecs.  Narrow (the pipeline's): E << 24 | H << 16 | PRMT selector, scores <= 255.  Wide: E << 17 | H << 4 | q,
+// 13-bit scores, plain mask-and-shift code -- only for callers of the stage entry point whose h0 + a * qlen exceeds a byte.
+template <bool kWide> struct XCol;
+template <> struct XCol<false> {
+    static __device__ __forceinline__ uint32_t init(int h, uint32_t q) { return (uint32_t)h << 16 | (q * 0x1111u + 0x8880u); }
+    static __device__ __forceinline__ int H(uint32_t w) { return (int)__byte_perm(w, 0u, 0x4442); }
+    static __device__ __forceinline__ int E(uint32_t w) { return (int)(w >> 24); }
+    static __device__ __forceinline__ int score(uint32_t lo, uint32_t hi, uint32_t w) { int s; asm("prmt.b32 %0, %1, %2, %3;" : "=r"(s) : "r"(lo), "r"(hi), "r"(w)); return s; }
+    static __device__ __forceinline__ uint32_t pack(uint32_t w, int h, int e, int c256) { return __byte_perm(w, (uint32_t)(e * c256 + h), 0x5410); }
+    static __device__ __forceinline__ uint32_t with_h(uint32_t w, int h) { return (w & 0xffffu) | (uint32_t)h << 16; }
+    static __device__ __forceinline__ bool zero(uint32_t w) { return (w >> 16) == 0; }
+    static constexpr int kMaxScore = 255;
+};
+template <> struct XCol<true> {
+    static __device__ __forceinline__ uint32_t init(int h, uint32_t q) { return (uint32_t)h << 4 | q; }
+    static __device__ __forceinline__ int H(uint32_t w) { return (int)((w >> 4) & 0x1fffu); }
+    static __device__ __forceinline__ int E(uint32_t w) { return (int)(w >> 17); }
+    static __device__ __forceinline__ int score(uint32_t lo, uint32_t hi, uint32_t w) { return (int)(int8_t)__byte_perm(lo, hi, w & 7u); }
+    static __device__ __forceinline__ uint32_t pack(uint32_t w, int h, int e, int) { return (w & 7u) | (uint32_t)h << 4 | (uint32_t)e << 17; }
+    static __device__ __forceinline__ uint32_t with_h(uint32_t w, int h) { return (w & 7u) | (uint32_t)h << 4; }
+    static __device__ __forceinline__ bool zero(uint32_t w) { return (w >> 4) == 0; }
+    static constexpr int kMaxScore = 8191;
+};
+
+template <bool kPackedRef, bool kWide>
 __global__ void __launch_bounds__(XDP_BLOCK) k_ext_dp(MemOpt opt, RefView ref, ExtDpArgs A) {
     extern __shared__ uint32_t xcols[];  // [ncols][XDP_BLOCK]
     uint32_t* col = xcols + threadIdx.x;
 #define XCOL(j) col[(j) * XDP_BLOCK]
     const unsigned lane = threadIdx.x & 31u;
     const unsigned n = *A.n_items;
-    // every score below is 16 x the reference's
-    const int e_del = opt.e_del << 4, e_ins = opt.e_ins << 4, o_del = opt.o_del << 4, o_ins = opt.o_ins << 4;
-    const int oe_del = o_del + e_del, oe_ins = o_ins + e_ins, zdrop = A.zdrop << 4;
-    const uint32_t mis4 = (uint32_t)((-opt.b * 16) & 0xff) * 0x01010101u, mat1 = (uint32_t)((opt.a * 16) & 0xff);
-    const uint32_t lut_hi = 0xf0f0f0f0u;  // query N scores -1
+    const int e_del = opt.e_del, e_ins = opt.e_ins, o_del = opt.o_del, o_ins = opt.o_ins;
+    const int oe_del = o_del + e_del, oe_ins = o_ins + e_ins, zdrop = A.zdrop;
+    const uint32_t mis4 = (uint32_t)(-opt.b & 0xff) * 0x01010101u, mat1 = (uint32_t)(opt.a & 0xff);
+    const uint32_t lut_hi = 0xffffffffu;  // query N scores -1
+    // multipliers the compiler cannot fold: `x * one + c` and `x * c256 + y` stay IMADs, which issue to the FMA pipe instead of the
+    // saturated integer ALU pipe (as plain adds / LEAs they were 3 of a cell's 12 ALU-pipe instructions)
+    const int one = A.one, c256 = A.one << 8;
     bool live = false, exhausted = false, need_init = false;
     int slot = 0, qlen = 0, tlen = 0, w = 0, h0 = 0, i = 0, beg = 0, end = 0;
-    int mx = 0, max_i = -1, max_j = -1, max_ie = -1, gscore = -16, max_off = 0;
+    int mx = 0, max_i = -1, max_j = -1, max_ie = -1, gscore = -1, max_off = 0;
     int64_t tfp = 0; int tfstep = 1; bool tcomp = false; int64_t tw_idx = -1; uint32_t tw = 0;
     const uint8_t* qptr = A.seq; int qstep = 1;
     unsigned long long cells = 0; unsigned calls = 0;
@@ -199,7 +228,7 @@ __global__ void __launch_bounds__(XDP_BLOCK) k_ext_dp(MemOpt opt, RefView ref, E
             if (!live && t < n) {
                 slot = A.perm ? A.perm[t] : (int)t;
                 const ExtProb P = A.prob[slot];
-                qlen = P.qlen; tlen = P.tlen; h0 = P.h0 << 4;
+                qlen = P.qlen; tlen = P.tlen; h0 = P.h0;
                 qptr = A.seq + A.off[P.read] + P.q0; qstep = (P.dirs & 1) ? -1 : 1;
                 ++calls;
                 {   // band limit (ksw.c:402-407): (int)((double)x / e + 1.) == (x + e) / e in C integer division
@@ -216,8 +245,8 @@ __global__ void __launch_bounds__(XDP_BLOCK) k_ext_dp(MemOpt opt, RefView ref, E
                     tfstep = tcomp ? -tstep : tstep;
                     tw_idx = -1;
                 } else tfp = P.tpos;
-                mx = h0; max_i = max_j = max_ie = -1; gscore = -16; max_off = 0; beg = 0; end = qlen; i = 0;
-                if (tlen <= 0 || qlen + 2 > A.ncols) {  // no row at all (ksw.c:409 never enters its loop) / caller sized the columns too small
+                mx = h0; max_i = max_j = max_ie = -1; gscore = -1; max_off = 0; beg = 0; end = qlen; i = 0;
+                if (tlen <= 0 || qlen + 2 > A.ncols || P.h0 + qlen * opt.a > XCol<kWide>::kMaxScore) {  // no row at all (ksw.c:409 never enters its loop) / caller sized the columns too small
                     ExtRes R; R.mx = tlen <= 0 ? P.h0 : -0x7fffffff; R.max_i = R.max_j = R.max_ie = -1; R.gscore = -1; R.max_off = 0;
                     A.res[slot] = R;
                 } else { live = true; need_init = true; }
@@ -236,7 +265,7 @@ __global__ void __launch_bounds__(XDP_BLOCK) k_ext_dp(MemOpt opt, RefView ref, E
                     int hv = bh0 - o_ins - x * e_ins;
                     hv = x == 0 ? bh0 : (hv > 0 ? hv : 0);
                     const uint32_t qb = x < bqlen ? (uint32_t)__ldg(bq + (long)x * bqs) : 0u;
-                    bcol[x * XDP_BLOCK] = (uint32_t)hv | (qb > 4u ? 4u : qb);
+                    bcol[x * XDP_BLOCK] = XCol<kWide>::init(hv, qb > 4u ? 4u : qb);
                 }
             }
             __syncwarp();
@@ -268,27 +297,26 @@ __global__ void __launch_bounds__(XDP_BLOCK) k_ext_dp(MemOpt opt, RefView ref, E
             const int nfull = nrow >> 2, nrem = nrow & 3;
             const int wfull = __reduce_max_sync(0xffffffffu, nfull);
             int jb = beg;
-#define XDP_CELL(cw_, u_)                                                                      \
-    {                                                                                          \
-        const int hd = (int)((cw_) & XDP_HMASK), e = (int)(((cw_) >> 13) & XDP_HMASK);         \
-        const int sc = (int)(int8_t)__byte_perm(lut_lo, lut_hi, (cw_));                        \
-        const int M = __viaddmin_s32_relu(hd, sc, hd << 8);                                    \
-        const int h = __vimax3_s32(M, e, f);                                                   \
-        const int e2 = __viaddmax_s32_relu(M, -oe_del, e - e_del);                             \
-        f = __viaddmax_s32_relu(M, -oe_ins, f - e_ins);                                        \
-        p[(u_) * XDP_BLOCK] = ((cw_) & XDP_QMASK) | (uint32_t)h1 | ((uint32_t)e2 << 13);       \
-        const int k_ = h * 16 + (u_);                                                          \
-        gk = gk > k_ ? gk : k_;                                                                \
-        h1 = h;                                                                                \
+#define XDP_CELL(cw_, u_)                                                              \
+    {                                                                                  \
+        const int hd = XCol<kWide>::H(cw_), e = XCol<kWide>::E(cw_);                   \
+        const int sc = XCol<kWide>::score(lut_lo, lut_hi, (cw_));                      \
+        const int M = __viaddmin_s32_relu(hd, sc, hd << 8);                            \
+        const int h = __vimax3_s32(M, e, f);                                           \
+        const int e2 = __viaddmax_s32_relu(M, -oe_del, e * one - e_del);               \
+        f = __viaddmax_s32_relu(M, -oe_ins, f * one - e_ins);                          \
+        p[(u_) * XDP_BLOCK] = XCol<kWide>::pack((cw_), h1, e2, c256);                  \
+        k##u_ = h * c256 + (u_);                                                       \
+        h1 = h;                                                                        \
     }
 #pragma unroll 1
             for (int g = 0; g < wfull; ++g) {
                 if (g < nfull) {
                     const uint32_t c0 = p[0], c1 = p[XDP_BLOCK], c2 = p[2 * XDP_BLOCK], c3 = p[3 * XDP_BLOCK];
-                    int gk = -1;
+                    int k0, k1, k2, k3;
                     XDP_CELL(c0, 0) XDP_CELL(c1, 1) XDP_CELL(c2, 2) XDP_CELL(c3, 3)
-                    gk += jb;
-                    key = key > gk ? key : gk;
+                    const int gk = __vimax3_s32(__vimax3_s32(k0, k1, k2), k3, -1);
+                    key = __viaddmax_s32(gk, jb, key);
                     p += 4 * XDP_BLOCK; jb += 4;
                 }
             }
@@ -297,10 +325,9 @@ __global__ void __launch_bounds__(XDP_BLOCK) k_ext_dp(MemOpt opt, RefView ref, E
             for (int u = 0; u < wrem; ++u) {
                 if (u < nrem) {
                     const uint32_t c0 = p[0];
-                    int gk = -1;
+                    int k0;
                     XDP_CELL(c0, 0)
-                    gk += jb;
-                    key = key > gk ? key : gk;
+                    key = __viaddmax_s32(k0, jb, key);
                     p += XDP_BLOCK; ++jb;
                 }
             }
@@ -310,9 +337,9 @@ __global__ void __launch_bounds__(XDP_BLOCK) k_ext_dp(MemOpt opt, RefView ref, E
         if (live) {
             bool done = false;
             const int jfin = end > beg ? end : beg;
-            XCOL(end) = (XCOL(end) & XDP_QMASK) | (uint32_t)h1;
+            XCOL(end) = XCol<kWide>::with_h(XCOL(end), h1);
             if (jfin == qlen) { max_ie = gscore > h1 ? max_ie : i; gscore = gscore > h1 ? gscore : h1; }
-            const int m = key >> 8 << 4, mj = key & 0xff;  // key = 16*H*16 + j: H (x16) is key >> 8 << 4
+            const int m = key >> 8, mj = key & 0xff;
             if (m == 0) done = true;
             else if (m > mx) {
                 mx = m; max_i = i; max_j = mj;
@@ -324,16 +351,16 @@ __global__ void __launch_bounds__(XDP_BLOCK) k_ext_dp(MemOpt opt, RefView ref, E
             }
             if (!done) {  // band for the next row: first and last column holding a non-zero H or E (ksw.c:465-468)
                 int j = beg;
-                while (j < end && (XCOL(j) & ~XDP_QMASK) == 0) ++j;
+                while (j < end && XCol<kWide>::zero(XCOL(j))) ++j;
                 beg = j;
                 j = end;
-                while (j >= beg && (XCOL(j) & ~XDP_QMASK) == 0) --j;
+                while (j >= beg && XCol<kWide>::zero(XCOL(j))) --j;
                 end = j + 2 < qlen ? j + 2 : qlen;
                 if (++i >= tlen) done = true;
             }
             if (done) {
                 ExtRes R;
-                R.mx = mx >> 4; R.max_i = max_i; R.max_j = max_j; R.max_ie = max_ie; R.gscore = gscore < 0 ? -1 : gscore >> 4; R.max_off = max_off;
+                R.mx = mx; R.max_i = max_i; R.max_j = max_j; R.max_ie = max_ie; R.gscore = gscore; R.max_off = max_off;
                 A.res[slot] = R;
                 live = false;
             }

@@ -354,9 +354,10 @@ static int validate_opts(const arachne_mem_opt_t* o) {
     if (o->e_del <= 0 || o->e_ins <= 0 || o->a <= 0 || o->w <= 0 || o->max_occ <= 0 || o->min_seed_len <= 0) {
         set_error("options out of range"); return ARACHNE_ERR_OPTS;
     }
-    // the DP kernels keep H and E in 13-bit fields (scores up to 8191) and the substitution scores x16 in signed bytes
-    if ((long)o->a * ARACHNE_MAX_READ_LEN > 8191 || o->a > 7 || o->b < 0 || o->b > 8 || o->o_del < 0 || o->o_ins < 0) {
-        set_error("scoring out of the kernels' range: need a <= 7, 0 <= b <= 8, a * %d <= 8191", ARACHNE_MAX_READ_LEN); return ARACHNE_ERR_OPTS;
+    // the extension kernel keeps H and E as bytes and the substitution scores as signed bytes (ext_stage.cuh); the callers
+    // check a * read length <= 255 per batch / problem
+    if (o->a > 127 || o->b < 0 || o->b > 128 || o->o_del < 0 || o->o_ins < 0) {
+        set_error("scoring out of the kernels' range: need a <= 127, 0 <= b <= 128, gap opens >= 0"); return ARACHNE_ERR_OPTS;
     }
     for (int i = 0, k = 0; i < 5; ++i)
         for (int j = 0; j < 5; ++j, ++k) {
@@ -687,6 +688,7 @@ int arachne_ksw_extend_batch(int device, const arachne_mem_opt_t* opt_, int64_t 
     int rc = validate_opts(opt_);
     if (rc) return rc;
     int maxq = 1;
+    bool wide = false;  // some problem's scores do not fit a byte: the 13-bit column codec
     std::vector<ExtProb> probs((size_t)n);
     std::vector<int> order((size_t)n);
     for (int64_t i = 0; i < n; ++i) {
@@ -694,7 +696,8 @@ int arachne_ksw_extend_batch(int device, const arachne_mem_opt_t* opt_, int64_t 
         if (ql > ARACHNE_MAX_READ_LEN || ql < 1 || h0[i] <= 0 || tl < 0 || tl > 0x7fffffff) {
             set_error("problem %lld: qlen must be 1..%d and h0 > 0 (ksw.c:385)", (long long)i, ARACHNE_MAX_READ_LEN); return ARACHNE_ERR_ARG;
         }
-        if ((long)h0[i] + ql * opt_->a > 8191) { set_error("problem %lld: h0 + qlen * a exceeds the kernel's 13-bit score fields", (long long)i); return ARACHNE_ERR_ARG; }
+        if ((long)h0[i] + ql * opt_->a > 8191) { set_error("problem %lld: h0 + qlen * a = %ld exceeds the kernel's 13-bit score fields", (long long)i, (long)h0[i] + ql * opt_->a); return ARACHNE_ERR_ARG; }
+        if ((long)h0[i] + ql * opt_->a > 255) wide = true;
         maxq = std::max<int>(maxq, (int)ql);
         ExtProb& P = probs[(size_t)i];
         P.read = (int32_t)i; P.q0 = 0; P.qlen = (int32_t)ql; P.tlen = (int32_t)tl; P.w = w[i]; P.h0 = h0[i]; P.end_bonus = end_bonus; P.dirs = 0; P.tpos = t_off[i];
@@ -717,11 +720,12 @@ int arachne_ksw_extend_batch(int device, const arachne_mem_opt_t* opt_, int64_t 
     if (repeat < 1) repeat = 1;
     ExtDpArgs DA;
     DA.seq = dq.as<uint8_t>(); DA.off = dqo.as<int64_t>(); DA.tbytes = dt.as<uint8_t>(); DA.prob = dp.as<ExtProb>(); DA.res = dres.as<ExtRes>();
-    DA.perm = dperm.as<int>(); DA.n_items = dctl.as<unsigned>(); DA.head = dctl.as<unsigned>() + 1; DA.ncols = maxq + 2; DA.zdrop = zdrop; DA.cnt = dc.as<Counters>();
+    DA.perm = dperm.as<int>(); DA.n_items = dctl.as<unsigned>(); DA.head = dctl.as<unsigned>() + 1; DA.ncols = maxq + 2; DA.zdrop = zdrop; DA.one = 1; DA.cnt = dc.as<Counters>();
     const size_t smem = (size_t)DA.ncols * XDP_BLOCK * sizeof(uint32_t);
     int per_sm = 1;
-    AR_CUDA(cudaFuncSetAttribute(k_ext_dp<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    AR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_ext_dp<false>, XDP_BLOCK, smem));
+    auto dp_kernel = wide ? k_ext_dp<false, true> : k_ext_dp<false, false>;
+    AR_CUDA(cudaFuncSetAttribute(dp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    AR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, dp_kernel, XDP_BLOCK, smem));
     if (per_sm < 1) per_sm = 1;
     const int blocks = sm_count(device) * per_sm;
     RefView no_ref; memset(&no_ref, 0, sizeof(no_ref));
@@ -729,7 +733,7 @@ int arachne_ksw_extend_batch(int device, const arachne_mem_opt_t* opt_, int64_t 
     for (int it = 0; it <= repeat; ++it) {  // one untimed launch, then `repeat` timed ones
         if (it == 1) { AR_CUDA(cudaMemset(dc.p, 0, sizeof(Counters))); cudaEventRecord(e0); }
         AR_CUDA(cudaMemcpyAsync(dctl.p, ctl0, 8, cudaMemcpyHostToDevice));
-        k_ext_dp<false><<<blocks, XDP_BLOCK, smem>>>(opt, no_ref, DA);
+        dp_kernel<<<blocks, XDP_BLOCK, smem>>>(opt, no_ref, DA);
         AR_CUDA(cudaGetLastError());
     }
     cudaEventRecord(e1);

@@ -32,8 +32,18 @@ def R():
     return RefBwa()
 
 
-def test_ksw_extend_parity(A, O):
+@pytest.mark.parametrize("codec", ["byte", "wide"])
+def test_ksw_extend_parity(A, O, codec):
+    """k_ext_dp against the oracle's ksw_extend2 (itself pinned to oracle/_ref).  "byte": every problem has h0 + qlen <= 255, the
+    column codec the pipeline runs (E<<24 | H<<16 | PRMT selector); "wide": unrestricted h0, the 13-bit codec of the stage entry."""
     qs, ts, h0, w = util.extension_problems(101, 4000)
+    if codec == "byte":
+        h0 = np.minimum(h0, 255 - np.array([len(x) for x in qs])).astype(np.int32)
+        keep = [i for i in range(len(qs)) if h0[i] > 0]
+        qs = [qs[i] for i in keep]; ts = [ts[i] for i in keep]; h0 = h0[keep]; w = w[keep]
+        assert len(qs) > 3000
+    else:
+        assert any(int(h0[i]) + len(qs[i]) > 255 for i in range(len(qs)))
     q, qo = util.pack(qs); t, to = util.pack(ts)
     for zdrop, eb in ((100, 5), (0, 0), (20, 5)):
         out, cells, _ = A.ksw_extend(q, qo, t, to, h0, w, end_bonus=eb, zdrop=zdrop)
