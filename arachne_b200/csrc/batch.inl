@@ -220,14 +220,14 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
     const long cg_warps = (long)sms * 4 * EXT_WARPS;
     AR_ALLOC(W.d_win, (size_t)std::max<long>(cg_warps, (long)ext_blocks * EXT_WARPS) * win_cap);
     {
-        const int drv_blocks = sms * 4, drv_T = drv_blocks * 128;
+        const int fin_blocks = sms * 4, drv_T = fin_blocks * 128, drv_blocks = (int)std::min<int64_t>((n_reads + 127) / 128, (int64_t)sms * 16);
         AR_ALLOC(W.d_hscr, (size_t)drv_T * 2 * (maxlen + 2) * sizeof(int));
         AR_ALLOC(W.d_rscr, (size_t)drv_T * win_cap);
         AR_ALLOC(W.d_xstate, (size_t)n_reads * sizeof(ExtState));
         AR_ALLOC(W.d_xprob, (size_t)n_reads * sizeof(ExtProb));
         AR_ALLOC(W.d_xres, (size_t)n_reads * sizeof(ExtRes));
         AR_ALLOC(W.d_xrank, (size_t)n_reads * 4);
-        AR_ALLOC(W.d_xperm, (size_t)n_reads * 4 * 2);
+        AR_ALLOC(W.d_xperm, (size_t)n_reads * sizeof(ExtProb) * 2);  // the sorted problem queues of two consecutive rounds
         AR_ALLOC(W.d_xctl, sizeof(ExtCtl));
         AR_TRY(cudaMemsetAsync(W.d_xctl.p, 0, sizeof(ExtCtl), st));
         ExtBufs XB;
@@ -235,10 +235,10 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
         XB.srt = W.d_srt.as<uint64_t>(); XB.regs = W.d_regs.as<AlnReg>(); XB.n_regs = W.d_nregs.as<int>();
         XB.hscr = W.d_hscr.as<int>(); XB.rscr = W.d_rscr.as<uint8_t>(); XB.rcap = win_cap; XB.maxlen = maxlen;
         XB.state = W.d_xstate.as<ExtState>(); XB.prob = W.d_xprob.as<ExtProb>(); XB.res = W.d_xres.as<ExtRes>(); XB.rank = W.d_xrank.as<unsigned>();
-        XB.perm_cur = W.d_xperm.as<int>(); XB.perm_next = XB.perm_cur + n_reads;
+        XB.queue_cur = W.d_xperm.as<ExtProb>(); XB.queue_next = XB.queue_cur + n_reads;
         XB.ctl = W.d_xctl.as<ExtCtl>(); XB.cnt = W.d_cnt.as<Counters>();
         ExtDpArgs DA;
-        DA.seq = d_seq; DA.off = d_off; DA.tbytes = nullptr; DA.prob = XB.prob; DA.res = XB.res; DA.n_items = &XB.ctl->n_next; DA.head = &XB.ctl->head;
+        DA.seq = d_seq; DA.tbytes = nullptr; DA.res = XB.res; DA.n_items = &XB.ctl->n_next; DA.head = &XB.ctl->head;
         DA.ncols = std::max(1, maxlen - opt.min_seed_len) + 2;  // a flank is never longer than len - min_seed_len (every seed is at least that long)
         DA.zdrop = opt.zdrop; DA.one = 1; DA.cnt = XB.cnt;
         const size_t smem = (size_t)DA.ncols * XDP_BLOCK * sizeof(uint32_t);
@@ -258,11 +258,11 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
                 k_ext_drive<<<drv_blocks, 128, 0, st>>>(opt, idx->ref, XB, round);
                 k_ext_binbase<<<1, 256, 0, st>>>(XB.ctl);
                 k_ext_scatter<<<sms * 4, 256, 0, st>>>(XB, round);
-                DA.perm = XB.perm_next;
+                DA.queue = XB.queue_next;
                 dp_kernel<<<dp_blocks, XDP_BLOCK, smem, st>>>(opt, idx->ref, DA);
                 k_ext_roll<<<1, 1, 0, st>>>(XB.ctl);
                 nl += 5;
-                std::swap(XB.perm_cur, XB.perm_next);
+                std::swap(XB.queue_cur, XB.queue_next);
             }
             AR_TRY(cudaGetLastError());
             AR_TRY(cudaMemcpyAsync(&hs[5], &XB.ctl->n_next, 4, cudaMemcpyDeviceToHost, st));
@@ -270,6 +270,8 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
             if ((unsigned)hs[5] == 0) break;
             if (round > 4096) { set_error("extension rounds do not terminate"); return fail(ARACHNE_ERR_OVERFLOW); }
         }
+        k_ext_finish<<<fin_blocks, 128, 0, st>>>(opt, idx->ref, XB);
+        ++nl;
     }
     cudaEventRecord(ev[4], st);
     int stages = in->stages ? in->stages : (ARACHNE_STAGE_REGIONS | ARACHNE_STAGE_RESCUE | ARACHNE_STAGE_CIGAR);

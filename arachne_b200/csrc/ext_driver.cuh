@@ -21,7 +21,9 @@ struct ExtProb {      // one ksw_extend2 call (bwa/ksw.c:380): query = read base
     int32_t w, h0, end_bonus;
     int32_t dirs;     // bit 0: query stride is -1; bit 1: target step is -1
     int64_t tpos;     // forward-reverse coordinate of the first target base
+    int64_t qoff;     // position of the first query base in the batch's base array (read offset + q0): filled by whoever queues the problem
 };
+static_assert(sizeof(ExtProb) == 48, "ExtProb is copied as three 16-byte words");
 
 struct ExtRes {       // what ksw_extend2 hands back: score, qle-1, tle-1, gtle-1, gscore, max_off
     int32_t mx, max_i, max_j, max_ie, gscore, max_off;

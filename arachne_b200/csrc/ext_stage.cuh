@@ -82,48 +82,56 @@ struct ExtBufs {
     uint64_t* srt; AlnReg* regs; int* n_regs;
     int* hscr; uint8_t* rscr; int rcap; int maxlen;
     ExtState* state; ExtProb* prob; ExtRes* res; unsigned* rank;
-    int* perm_cur; int* perm_next;
+    ExtProb* queue_cur; ExtProb* queue_next;  // the sorted problem queue of the previous round (= the reads this round visits) / of this round
     ExtCtl* ctl; Counters* cnt;
 };
 
 __global__ void __launch_bounds__(128) k_ext_drive(MemOpt opt, RefView ref, ExtBufs A, int round) {
     const unsigned n = round == 0 ? (unsigned)A.n_reads : A.ctl->n_cur;
-    const long gtid = (long)blockIdx.x * blockDim.x + threadIdx.x;
-    ThreadCtx tctx; tctx.hbuf = A.hscr + gtid * (2 * (A.maxlen + 2)); tctx.rbuf = A.rscr + gtid * A.rcap;
-    for (unsigned t = (unsigned)gtid; t < n; t += gridDim.x * blockDim.x) {
-        const int r = round == 0 ? (int)t : A.perm_cur[t];
+    for (unsigned t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
+        const int r = round == 0 ? (int)t : A.queue_cur[t].read;
         const int nk = A.b.n_chain[r];
         ExtState S;
         if (round == 0) {
-            if (nk == 0) { A.n_regs[r] = 0; A.state[r].phase = EXT_PH_DONE; continue; }
+            if (nk == 0) { A.state[r].phase = EXT_PH_DONE; A.state[r].n_regions = 0; continue; }
             ext_state_init(S);
         } else S = A.state[r];
         const unsigned long long o = A.sa_off[r];
-        const int len = (int)(A.off[r + 1] - A.off[r]);
-        AlnReg* av = A.regs + o;
+        const int64_t roff = A.off[r];
+        const int len = (int)(A.off[r + 1] - roff);
         ExtProb P;
         const ExtRes R = A.res[r];
-        int rc = ext_advance(opt, ref, r, len, nk, A.b.chains + o, A.b.order + o, A.b.kseeds + o, av, A.b.n_kseed[r], A.srt + o, S, &R, &P);
+        int rc = ext_advance(opt, ref, r, len, nk, A.b.chains + o, A.b.order + o, A.b.kseeds + o, A.regs + o, A.b.n_kseed[r], A.srt + o, S, &R, &P);
+        if (rc == 1 && (P.qlen > 255 || P.qlen <= 0)) rc = -3;  // cannot happen: a flank is shorter than the read
         if (rc == 1) {
-            if (P.qlen > 255 || P.qlen <= 0) rc = -3;  // cannot happen: a flank is shorter than the read
-            else {
-                A.prob[r] = P;
-                A.rank[r] = atomicAdd(&A.ctl->bin[P.qlen], 1u);
-                A.state[r] = S;
-                continue;
+            P.qoff = roff + P.q0;
+            A.prob[r] = P;
+            A.rank[r] = atomicAdd(&A.ctl->bin[P.qlen], 1u);
+        } else {
+            if (rc != 0) { raise(A.cnt, ARACHNE_ERR_OVERFLOW, r); S.n_regions = 0; }
+            S.phase = EXT_PH_DONE;
+        }
+        A.state[r] = S;
+    }
+}
+
+// mem_align1_core's tail (bwamem.c:1069-1082) once every read is through its rounds: region de-duplication / patching and the
+// ALT flag.  Kept out of k_ext_drive: only this kernel needs per-thread scratch (the rare patch re-alignment).
+__global__ void __launch_bounds__(128) k_ext_finish(MemOpt opt, RefView ref, ExtBufs A) {
+    const long gtid = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    ThreadCtx tctx; tctx.hbuf = A.hscr + gtid * (2 * (A.maxlen + 2)); tctx.rbuf = A.rscr + gtid * A.rcap;
+    for (int r = (int)gtid; r < A.n_reads; r += gridDim.x * blockDim.x) {
+        int n_av = A.state[r].n_regions;
+        if (n_av > 0) {
+            AlnReg* av = A.regs + A.sa_off[r];
+            if (n_av > 1) {
+                const int nn = sort_dedup_patch(tctx, opt, ref, A.seq + A.off[r], n_av, av, tctx.rbuf, A.rcap);
+                if (nn < 0) { raise(A.cnt, ARACHNE_ERR_OVERFLOW, r); n_av = 0; } else n_av = nn;
             }
+            for (int x = 0; x < n_av; ++x)
+                if (av[x].rid >= 0 && ref.contigs[av[x].rid].is_alt) av[x].n_comp_is_alt |= 1 << 30;
         }
-        int n_av = S.n_regions;
-        if (rc == 0) {  // mem_align1_core's tail (bwamem.c:1069-1082)
-            const int nn = sort_dedup_patch(tctx, opt, ref, A.seq + A.off[r], n_av, av, tctx.rbuf, A.rcap);
-            if (nn < 0) rc = nn; else n_av = nn;
-        }
-        if (rc != 0) { raise(A.cnt, ARACHNE_ERR_OVERFLOW, r); n_av = 0; }
-        for (int x = 0; x < n_av; ++x)
-            if (av[x].rid >= 0 && ref.contigs[av[x].rid].is_alt) av[x].n_comp_is_alt |= 1 << 30;
         A.n_regs[r] = n_av;
-        S.phase = EXT_PH_DONE;
-        A.state[r].phase = EXT_PH_DONE;
     }
 }
 
@@ -147,9 +155,12 @@ __global__ void __launch_bounds__(256) k_ext_binbase(ExtCtl* c) {
 __global__ void k_ext_scatter(ExtBufs A, int round) {
     const unsigned n = round == 0 ? (unsigned)A.n_reads : A.ctl->n_cur;
     for (unsigned t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
-        const int r = round == 0 ? (int)t : A.perm_cur[t];
+        const int r = round == 0 ? (int)t : A.queue_cur[t].read;
         if (A.state[r].phase == EXT_PH_DONE) continue;
-        A.perm_next[A.ctl->base[A.prob[r].qlen] + A.rank[r]] = r;
+        const uint4* src = reinterpret_cast<const uint4*>(A.prob + r);
+        const uint4 a = src[0], b = src[1], c = src[2];
+        uint4* dst = reinterpret_cast<uint4*>(A.queue_next + (A.ctl->base[a.z /* qlen */] + A.rank[r]));
+        dst[0] = a; dst[1] = b; dst[2] = c;
     }
 }
 
@@ -157,12 +168,13 @@ __global__ void k_ext_roll(ExtCtl* c) { c->n_cur = c->n_next; }
 
 // ------------------------------------------------------------------------------------------------ k_ext_dp
 constexpr int XDP_BLOCK = 128;
+constexpr int XDP_REFILL = 8;  // idle lanes of a warp that trigger a refill
 
 struct ExtDpArgs {
-    const uint8_t* seq; const int64_t* off;  // queries: problem p reads seq[off[p.read] + p.q0 + x * (+1|-1)]
+    const uint8_t* seq;                      // queries: problem p reads seq[p.qoff + x * (+1|-1)]
     const uint8_t* tbytes;                   // kPackedRef == false: targets as bytes, problem p reads tbytes[p.tpos + i]
-    const ExtProb* prob; ExtRes* res;        // both indexed by ExtProb::read's slot (the queue entry)
-    const int* perm;                         // queue: slot ids, longest query first (nullptr: identity)
+    const ExtProb* queue;                    // the problems, longest query first
+    ExtRes* res;                             // indexed by ExtProb::read
     const unsigned* n_items; unsigned* head;
     int ncols;                               // column words per lane, >= longest query + 2
     int zdrop;
@@ -209,27 +221,70 @@ __global__ void __launch_bounds__(XDP_BLOCK) k_ext_dp(MemOpt opt, RefView ref, E
     // saturated integer ALU pipe (as plain adds / LEAs they were 3 of a cell's 12 ALU-pipe instructions)
     const int one = A.one, c256 = A.one << 8;
     bool live = false, exhausted = false, need_init = false;
+    uint4 pool0 = make_uint4(0, 0, 0, 0), pool1 = pool0, pool2 = pool0;
+    int pool_n = 0, pool_pos = 0;
     int slot = 0, qlen = 0, tlen = 0, w = 0, h0 = 0, i = 0, beg = 0, end = 0;
     int mx = 0, max_i = -1, max_j = -1, max_ie = -1, gscore = -1, max_off = 0;
     int64_t tfp = 0; int tfstep = 1; bool tcomp = false; int64_t tw_idx = -1; uint32_t tw = 0;
     const uint8_t* qptr = A.seq; int qstep = 1;
     unsigned long long cells = 0; unsigned calls = 0;
 
+    int tb_next = 0;
+    // target base of row x: from a cached 16-base word of the packed reference (bns_get_seq, bntseq.c:398-419) or the caller's bytes.
+    // Always asked for one row ahead, so the (rare) word load is in flight while a row's cells are computed.
+    auto target_base = [&](int x) -> int {
+        if (kPackedRef) {
+            const int64_t fp = tfp + (int64_t)x * tfstep;
+            if ((fp >> 4) != tw_idx) { tw_idx = fp >> 4; tw = __ldg(reinterpret_cast<const uint32_t*>(ref.pac) + tw_idx); }
+            const int b = (int)(tw >> ((((unsigned)fp >> 2) & 3u) << 3) >> ((~(unsigned)fp & 3u) << 1)) & 3;
+            return tcomp ? 3 - b : b;
+        }
+        return (int)__ldg(A.tbytes + tfp + x);
+    };
     for (;;) {
-        // ---- idle lanes take the next problems of the queue (one atomic per warp) ----
+        // ---- idle lanes take the next problems ----
+        // The warp keeps a POOL of up to 32 descriptors in registers (lane k holds queue entry pool_base + k), loaded with one
+        // coalesced burst right after the previous pool ran out, i.e. long before anybody needs them: taking a problem is a
+        // handful of shuffles, not a dependent global load that stalls the 31 lanes still computing.  Lanes are refilled in
+        // batches (XDP_REFILL idle lanes, or nobody live): every refill event costs the warp one first-row fill per problem.
         const unsigned idle = __ballot_sync(0xffffffffu, !live);
-        if (idle && !exhausted) {
-            const unsigned want = __popc(idle);
+        const int n_idle = __popc(idle);
+        if (pool_pos >= pool_n && !exhausted) {  // (re)load the pool; the registers are first read at the next take
             unsigned base = 0;
-            if (lane == 0) base = atomicAdd(A.head, want);
+            if (lane == 0) base = atomicAdd(A.head, 32u);
             base = __shfl_sync(0xffffffffu, base, 0);
-            if (base + want >= n) exhausted = true;
-            const unsigned t = base + __popc(idle & ((1u << lane) - 1u));
-            if (!live && t < n) {
-                slot = A.perm ? A.perm[t] : (int)t;
-                const ExtProb P = A.prob[slot];
+            if (base >= n) { exhausted = true; pool_n = 0; }
+            else {
+                pool_n = n - base < 32u ? (int)(n - base) : 32;
+                if ((int)lane < pool_n) {
+                    const uint4* src = reinterpret_cast<const uint4*>(A.queue + base + lane);
+                    pool0 = __ldg(src); pool1 = __ldg(src + 1); pool2 = __ldg(src + 2);
+                }
+            }
+            pool_pos = 0;
+        }
+        if (n_idle && pool_pos < pool_n && (n_idle >= XDP_REFILL || n_idle == 32)) {
+            const int avail = pool_n - pool_pos, take = n_idle < avail ? n_idle : avail;
+            const int rank = __popc(idle & ((1u << lane) - 1u));
+            const bool mine = !live && rank < take;
+            const int from = mine ? pool_pos + rank : (int)lane;
+            uint4 d0, d1, d2;
+            d0.x = __shfl_sync(0xffffffffu, pool0.x, from); d0.y = __shfl_sync(0xffffffffu, pool0.y, from);
+            d0.z = __shfl_sync(0xffffffffu, pool0.z, from); d0.w = __shfl_sync(0xffffffffu, pool0.w, from);
+            d1.x = __shfl_sync(0xffffffffu, pool1.x, from); d1.y = __shfl_sync(0xffffffffu, pool1.y, from);
+            d1.z = __shfl_sync(0xffffffffu, pool1.z, from); d1.w = __shfl_sync(0xffffffffu, pool1.w, from);
+            d2.x = __shfl_sync(0xffffffffu, pool2.x, from); d2.y = __shfl_sync(0xffffffffu, pool2.y, from);
+            d2.z = __shfl_sync(0xffffffffu, pool2.z, from); d2.w = __shfl_sync(0xffffffffu, pool2.w, from);
+            pool_pos += take;
+            if (mine) {
+                ExtProb P;
+                {
+                    uint4* dst = reinterpret_cast<uint4*>(&P);
+                    dst[0] = d0; dst[1] = d1; dst[2] = d2;
+                }
+                slot = P.read;
                 qlen = P.qlen; tlen = P.tlen; h0 = P.h0;
-                qptr = A.seq + A.off[P.read] + P.q0; qstep = (P.dirs & 1) ? -1 : 1;
+                qptr = A.seq + P.qoff; qstep = (P.dirs & 1) ? -1 : 1;
                 ++calls;
                 {   // band limit (ksw.c:402-407): (int)((double)x / e + 1.) == (x + e) / e in C integer division
                     int top = opt.a > -opt.b ? opt.a : -opt.b; top = top > -1 ? top : -1;
@@ -249,7 +304,7 @@ __global__ void __launch_bounds__(XDP_BLOCK) k_ext_dp(MemOpt opt, RefView ref, E
                 if (tlen <= 0 || qlen + 2 > A.ncols || P.h0 + qlen * opt.a > XCol<kWide>::kMaxScore) {  // no row at all (ksw.c:409 never enters its loop) / caller sized the columns too small
                     ExtRes R; R.mx = tlen <= 0 ? P.h0 : -0x7fffffff; R.max_i = R.max_j = R.max_ie = -1; R.gscore = -1; R.max_off = 0;
                     A.res[slot] = R;
-                } else { live = true; need_init = true; }
+                } else { live = true; need_init = true; tb_next = target_base(0); }
             }
         }
         // ---- first row (ksw.c:395-397) of the lanes that just took a problem, filled by the whole warp, 32 columns per trip ----
@@ -261,11 +316,19 @@ __global__ void __launch_bounds__(XDP_BLOCK) k_ext_dp(MemOpt opt, RefView ref, E
                 const uint8_t* bq = reinterpret_cast<const uint8_t*>(__shfl_sync(0xffffffffu, (unsigned long long)qptr, src));
                 const int bqs = __shfl_sync(0xffffffffu, qstep, src), bqlen = __shfl_sync(0xffffffffu, qlen, src), bh0 = __shfl_sync(0xffffffffu, h0, src);
                 uint32_t* bcol = xcols + (threadIdx.x & ~31u) + src;
-                for (int x = (int)lane; x <= bqlen; x += 32) {
-                    int hv = bh0 - o_ins - x * e_ins;
-                    hv = x == 0 ? bh0 : (hv > 0 ? hv : 0);
-                    const uint32_t qb = x < bqlen ? (uint32_t)__ldg(bq + (long)x * bqs) : 0u;
-                    bcol[x * XDP_BLOCK] = XCol<kWide>::init(hv, qb > 4u ? 4u : qb);
+                for (int x0 = (int)lane; x0 <= bqlen; x0 += 128) {  // four independent loads in flight per trip
+                    uint32_t qb[4];
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) { const int x = x0 + 32 * k; qb[k] = x < bqlen ? (uint32_t)__ldg(bq + (long)x * bqs) : 0u; }
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const int x = x0 + 32 * k;
+                        if (x <= bqlen) {
+                            int hv = bh0 - o_ins - x * e_ins;
+                            hv = x == 0 ? bh0 : (hv > 0 ? hv : 0);
+                            bcol[x * XDP_BLOCK] = XCol<kWide>::init(hv, qb[k] > 4u ? 4u : qb[k]);
+                        }
+                    }
                 }
             }
             __syncwarp();
@@ -275,13 +338,7 @@ __global__ void __launch_bounds__(XDP_BLOCK) k_ext_dp(MemOpt opt, RefView ref, E
         int nrow = 0, h1 = 0, f = 0;
         uint32_t lut_lo = lut_hi;
         if (live) {
-            int tb;
-            if (kPackedRef) {  // target base of row i from a cached 16-base word of the packed reference (bns_get_seq, bntseq.c:398-419)
-                const int64_t fp = tfp + (int64_t)i * tfstep;
-                if ((fp >> 4) != tw_idx) { tw_idx = fp >> 4; tw = __ldg(reinterpret_cast<const uint32_t*>(ref.pac) + tw_idx); }
-                tb = (int)(tw >> ((((unsigned)fp >> 2) & 3u) << 3) >> ((~(unsigned)fp & 3u) << 1)) & 3;
-                tb = tcomp ? 3 - tb : tb;
-            } else tb = __ldg(A.tbytes + tfp + i);
+            const int tb = tb_next;  // fetched while the previous row was computed (row 0: at problem start)
             if (tb < 4) lut_lo = (mis4 & ~(0xffu << (tb << 3))) | (mat1 << (tb << 3));
             if (beg < i - w) beg = i - w;
             if (end > i + w + 1) end = i + w + 1;
@@ -289,6 +346,7 @@ __global__ void __launch_bounds__(XDP_BLOCK) k_ext_dp(MemOpt opt, RefView ref, E
             if (beg == 0) { h1 = h0 - (o_del + e_del * (i + 1)); h1 = h1 > 0 ? h1 : 0; }
             nrow = end > beg ? end - beg : 0;
             cells += nrow;
+            if (i + 1 < tlen) tb_next = target_base(i + 1);
         }
         // ---- the row's cells (ksw.c:424-448): groups of 4 to the warp's longest row, then up to 3 single cells ----
         int key = 0;  // 256 * (row maximum of H) + its column; ties go to the larger column (:437)
@@ -365,7 +423,7 @@ __global__ void __launch_bounds__(XDP_BLOCK) k_ext_dp(MemOpt opt, RefView ref, E
                 live = false;
             }
         }
-        if (exhausted && __ballot_sync(0xffffffffu, live) == 0) break;
+        if (exhausted && pool_pos >= pool_n && __ballot_sync(0xffffffffu, live) == 0) break;
     }
 #undef XCOL
     if (cells || calls) { atomicAdd(&A.cnt->ext_cells, cells); atomicAdd(&A.cnt->ext_calls, (unsigned long long)calls); }

@@ -700,7 +700,7 @@ int arachne_ksw_extend_batch(int device, const arachne_mem_opt_t* opt_, int64_t 
         if ((long)h0[i] + ql * opt_->a > 255) wide = true;
         maxq = std::max<int>(maxq, (int)ql);
         ExtProb& P = probs[(size_t)i];
-        P.read = (int32_t)i; P.q0 = 0; P.qlen = (int32_t)ql; P.tlen = (int32_t)tl; P.w = w[i]; P.h0 = h0[i]; P.end_bonus = end_bonus; P.dirs = 0; P.tpos = t_off[i];
+        P.read = (int32_t)i; P.q0 = 0; P.qlen = (int32_t)ql; P.tlen = (int32_t)tl; P.w = w[i]; P.h0 = h0[i]; P.end_bonus = end_bonus; P.dirs = 0; P.tpos = t_off[i]; P.qoff = q_off[i];
         order[(size_t)i] = (int)i;
     }
     // the queue k_ext_dp consumes is sorted by query length, longest first (k_ext_binbase / k_ext_scatter do this in the pipeline)
@@ -708,19 +708,20 @@ int arachne_ksw_extend_batch(int device, const arachne_mem_opt_t* opt_, int64_t 
     MemOpt opt; memcpy(&opt, opt_, sizeof(opt));
     if (arachne_device_count() <= device) { set_error("no CUDA device %d (no CPU path)", device); return ARACHNE_ERR_CUDA; }
     AR_CUDA(cudaSetDevice(device));
-    DevBuf dq, dqo, dt, dp, dperm, dres, dc, dctl;
-    if (dq.ensure(q_off[n] + 16) || dqo.ensure((n + 1) * 8) || dt.ensure(t_off[n] + 16) || dp.ensure(n * sizeof(ExtProb) + 8) || dperm.ensure(n * 4 + 4) ||
+    std::vector<ExtProb> queue((size_t)n);
+    for (int64_t i = 0; i < n; ++i) queue[(size_t)i] = probs[(size_t)order[(size_t)i]];
+    DevBuf dq, dt, dp, dres, dc, dctl;
+    if (dq.ensure(q_off[n] + 16) || dt.ensure(t_off[n] + 16) || dp.ensure(n * sizeof(ExtProb) + 8) ||
         dres.ensure(n * sizeof(ExtRes) + 8) || dc.ensure(sizeof(Counters)) || dctl.ensure(16)) { set_error("out of device memory"); return ARACHNE_ERR_CUDA; }
-    AR_CUDA(cudaMemcpy(dq.p, q, q_off[n], cudaMemcpyHostToDevice)); AR_CUDA(cudaMemcpy(dqo.p, q_off, (n + 1) * 8, cudaMemcpyHostToDevice));
+    AR_CUDA(cudaMemcpy(dq.p, q, q_off[n], cudaMemcpyHostToDevice));
     AR_CUDA(cudaMemcpy(dt.p, t, t_off[n], cudaMemcpyHostToDevice));
-    AR_CUDA(cudaMemcpy(dp.p, probs.data(), n * sizeof(ExtProb), cudaMemcpyHostToDevice));
-    AR_CUDA(cudaMemcpy(dperm.p, order.data(), n * 4, cudaMemcpyHostToDevice));
+    AR_CUDA(cudaMemcpy(dp.p, queue.data(), n * sizeof(ExtProb), cudaMemcpyHostToDevice));
     AR_CUDA(cudaMemset(dc.p, 0, sizeof(Counters)));
     cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
     if (repeat < 1) repeat = 1;
     ExtDpArgs DA;
-    DA.seq = dq.as<uint8_t>(); DA.off = dqo.as<int64_t>(); DA.tbytes = dt.as<uint8_t>(); DA.prob = dp.as<ExtProb>(); DA.res = dres.as<ExtRes>();
-    DA.perm = dperm.as<int>(); DA.n_items = dctl.as<unsigned>(); DA.head = dctl.as<unsigned>() + 1; DA.ncols = maxq + 2; DA.zdrop = zdrop; DA.one = 1; DA.cnt = dc.as<Counters>();
+    DA.seq = dq.as<uint8_t>(); DA.tbytes = dt.as<uint8_t>(); DA.queue = dp.as<ExtProb>(); DA.res = dres.as<ExtRes>();
+    DA.n_items = dctl.as<unsigned>(); DA.head = dctl.as<unsigned>() + 1; DA.ncols = maxq + 2; DA.zdrop = zdrop; DA.one = 1; DA.cnt = dc.as<Counters>();
     const size_t smem = (size_t)DA.ncols * XDP_BLOCK * sizeof(uint32_t);
     int per_sm = 1;
     auto dp_kernel = wide ? k_ext_dp<false, true> : k_ext_dp<false, false>;
