@@ -76,6 +76,76 @@ def _p(a, t):
     return a.ctypes.data_as(C.POINTER(t))
 
 
+class AlnRegV(C.Structure):  # mem_alnreg_v / arachne_alnreg_v
+    _fields_ = [("n", C.c_size_t), ("m", C.c_size_t), ("a", C.c_void_p)]
+
+
+class GoAln(C.Structure):  # GO_mem_aln_t / arachne_go_aln_t (bwa_bridge.h:19-29)
+    _fields_ = [("pos", C.c_int64), ("rid", C.c_int), ("flag", C.c_int), ("flag2", C.c_uint32), ("n_cigar", C.c_int),
+                ("cigar", C.POINTER(C.c_uint32)), ("XA", C.c_char_p), ("score", C.c_int), ("sub", C.c_int), ("alt_sc", C.c_int)]
+
+
+class CompatStats(C.Structure):
+    _fields_ = [("n_calls", C.c_uint64), ("n_batches", C.c_uint64), ("max_batch", C.c_uint64), ("n_live_blocks", C.c_uint64)]
+
+
+class Compat:
+    """ctypes mirror of include/arachne_compat.h: the per-pair / per-candidate calls gobwa makes, served from GPU batches formed
+    from the calls in flight (what integration/gobwa/gobwa_cuda.go binds).  Thread-safe: call it from many threads."""
+
+    def __init__(self, A: "ArachneCuda", max_batch_pairs: int = 0, max_wait_us: int = 0):
+        self.A, L = A, A.lib
+        L.arachne_compat_open.argtypes = [C.c_void_p, C.POINTER(MemOpt), C.c_int, C.c_int, C.POINTER(C.c_void_p)]
+        L.arachne_compat_close.argtypes = [C.c_void_p]
+        L.arachne_compat_mem_mate_sw.argtypes = [C.c_void_p, C.POINTER(C.c_uint8), C.c_int, C.POINTER(C.c_uint8), C.c_int, C.c_int,
+                                                 C.POINTER(AlnRegV), C.POINTER(AlnRegV), C.POINTER(C.c_void_p)]
+        L.arachne_compat_reg2aln.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(GoAln)]
+        L.arachne_compat_release.argtypes = [C.c_void_p, C.c_void_p]
+        L.arachne_compat_fetch_seq.restype = C.c_void_p
+        L.arachne_compat_fetch_seq.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.c_int64, C.POINTER(C.c_int64), C.POINTER(C.c_int)]
+        L.arachne_compat_stats.argtypes = [C.c_void_p, C.POINTER(CompatStats)]
+        self.h = C.c_void_p(None)
+        A._ck(L.arachne_compat_open(A.idx, C.byref(A.opt), max_batch_pairs, max_wait_us, C.byref(self.h)))
+
+    def mem_mate_sw(self, r1: np.ndarray, r2: np.ndarray, score_delta: int = 25):
+        """GoBwaMemMateSW for one pair -> (regions of read 1, regions of read 2, first-region addresses, owner).  Regions are
+        numpy copies of the 88-byte records; addr1/addr2 are the addresses GoBwaSmithWaterman would pass back."""
+        o1, o2, owner = AlnRegV(), AlnRegV(), C.c_void_p(None)
+        self.A._ck(self.A.lib.arachne_compat_mem_mate_sw(self.h, _p(r1, C.c_uint8), len(r1), _p(r2, C.c_uint8), len(r2), score_delta,
+                                                          C.byref(o1), C.byref(o2), C.byref(owner)))
+        def view(v):
+            return np.ctypeslib.as_array((C.c_uint8 * (88 * v.n)).from_address(v.a)).copy().view(ALNREG) if v.n else np.zeros(0, ALNREG)
+        return view(o1), view(o2), (o1.a or 0), (o2.a or 0), owner
+
+    def reg2aln(self, reg_addr: int):
+        g = GoAln()
+        self.A._ck(self.A.lib.arachne_compat_reg2aln(self.h, C.c_void_p(reg_addr), C.byref(g)))
+        cig = np.array([g.cigar[i] for i in range(g.n_cigar)], dtype=np.uint32)
+        return {"pos": g.pos, "rid": g.rid, "is_rev": g.flag2 & 1, "nm": g.flag2 >> 10, "n_cigar": g.n_cigar, "cigar": cig, "score": g.score, "sub": g.sub}
+
+    def release(self, owner):
+        self.A.lib.arachne_compat_release(self.h, owner)
+
+    def fetch_seq(self, beg: int, mid: int, end: int):
+        b, e, rid = C.c_int64(beg), C.c_int64(end), C.c_int(-1)
+        p = self.A.lib.arachne_compat_fetch_seq(self.A.idx, C.byref(b), mid, C.byref(e), C.byref(rid))
+        if not p:
+            raise ArachneError(self.A.lib.arachne_last_error().decode())
+        out = np.ctypeslib.as_array((C.c_uint8 * max(e.value - b.value, 0)).from_address(p)).copy()
+        C.CDLL(None).free(C.c_void_p(p))
+        return out, b.value, e.value, rid.value
+
+    def stats(self) -> dict:
+        s = CompatStats()
+        self.A.lib.arachne_compat_stats(self.h, C.byref(s))
+        return {n: getattr(s, n) for n, _ in CompatStats._fields_}
+
+    def close(self):
+        if self.h:
+            self.A.lib.arachne_compat_close(self.h)
+            self.h = C.c_void_p(None)
+
+
 class ArachneCuda:
     """One loaded index on one device + the kernel entry points."""
 

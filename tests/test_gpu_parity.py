@@ -417,3 +417,60 @@ def test_seed_intervals_every_shortcut(A, R, workdir, name):
                 assert np.array_equal(ioff, base[0]) and np.array_equal(iv, base[1]), (name, kmer, direct)
     finally:
         A.set_option("seed_kmer", 1); A.set_option("seed_direct", 1)
+
+
+# ---- row b: the gobwa-shaped layer (include/arachne_compat.h), what integration/gobwa/gobwa_cuda.go binds ----
+def test_compat_layer_per_pair_calls_batched(A, R, workdir):
+    """One barcode's worth of per-pair GoBwaMemMateSW calls + per-candidate GoBwaSmithWaterman calls, made from many threads the
+    way the reference's worker goroutines make them, against the reference's own C code driven in gobwa.go's call order
+    (oracle/ref_shim.c).  Also: the calls really were batched, region arrays stay valid until released, GetSeq = bns_fetch_seq."""
+    from concurrent.futures import ThreadPoolExecutor
+    from arachne_b200 import Compat
+    fa, ctg, rs = util.make_dataset("rep600k", workdir, damaged=True)
+    R.load(fa); A.load_index(fa)
+    ref = R.batch(rs.seq, rs.off, rescue=True, cigar=True, threads=8)
+    n = min(rs.n_pairs, 1500)
+    K = Compat(A, max_batch_pairs=256, max_wait_us=2000)
+    try:
+        def one(p):
+            r1 = np.ascontiguousarray(rs.seq[rs.off[2 * p]:rs.off[2 * p + 1]]); r2 = np.ascontiguousarray(rs.seq[rs.off[2 * p + 1]:rs.off[2 * p + 2]])
+            g1, g2, a1, a2, owner = K.mem_mate_sw(r1, r2, 25)
+            alns = [K.reg2aln(base + 88 * k) for base, g in ((a1, g1), (a2, g2)) for k in range(len(g))]
+            return p, g1, g2, alns, owner
+        with ThreadPoolExecutor(64) as ex:
+            out = list(ex.map(one, range(n)))
+        st = K.stats()
+        assert st["n_calls"] == n and st["n_batches"] < n // 4 and st["max_batch"] > 8, st  # dynamic batching happened
+        assert st["n_live_blocks"] == n
+        e = ref["aln"]
+        for p, g1, g2, alns, owner in out:
+            lo, mid, hi = (int(ref["reg_off"][2 * p + k]) for k in range(3))
+            assert g1.tobytes() == ref["regs"][lo:mid].tobytes() and g2.tobytes() == ref["regs"][mid:hi].tobytes(), p
+            assert len(alns) == hi - lo
+            for k, a in enumerate(alns):
+                x = e[lo + k]
+                assert (a["pos"], a["rid"], a["is_rev"], a["nm"], a["n_cigar"], a["score"], a["sub"]) == (x[0], x[1], x[2], x[3], x[4], x[6], x[7]), (p, k)
+                assert np.array_equal(a["cigar"], ref["cigar"][x[5]:x[5] + x[4]]), (p, k)
+        # a region handed out earlier is still addressable after every other call returned (gobwa's Arena lifetime) ...
+        first = next((o, a1 or a2) for o in out for a1, a2 in [(len(o[1]) > 0, len(o[2]) > 0)] if a1 or a2)[0]
+        r1 = np.ascontiguousarray(rs.seq[rs.off[2 * first[0]]:rs.off[2 * first[0] + 1]]); r2 = np.ascontiguousarray(rs.seq[rs.off[2 * first[0] + 1]:rs.off[2 * first[0] + 2]])
+        g1, g2, a1, a2, ow2 = K.mem_mate_sw(r1, r2, 25)
+        addr = a1 or a2
+        again = K.reg2aln(addr)
+        assert again["pos"] == first[3][0]["pos"] and np.array_equal(again["cigar"], first[3][0]["cigar"])
+        K.release(ow2)
+        # ... and not after its block is released
+        from arachne_b200 import ArachneError
+        with pytest.raises(ArachneError):
+            K.reg2aln(addr)
+        for _, _, _, _, ow in out:
+            K.release(ow)
+        assert K.stats()["n_live_blocks"] == 0
+        # GetSeq (gobwa.go:50-80): bns_fetch_seq with the clamp to the contig, both strands
+        l_pac = A.l_pac
+        for beg, end in ((100, 400), (l_pac - 50, l_pac + 70), (2 * l_pac - 300, 2 * l_pac - 20)):
+            got, b, en, rid = K.fetch_seq(beg, (beg + end) >> 1, end)
+            exp, eb, ee, erid = A.fetch_seq(beg, (beg + end) >> 1, end)  # pinned to the reference text in test_fetch_seq_matches_reference_text
+            assert (b, en, rid) == (eb, ee, erid) and np.array_equal(got, exp)
+    finally:
+        K.close()
