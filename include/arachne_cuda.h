@@ -9,7 +9,7 @@
  *   (2) stage entry points: the individual kernels on caller-supplied problems -- these are what the parity
  *       tests and the config-5 ksw_extend2 microbench drive.
  * The per-pair Go entry points (GoBwaMemMateSW / GoBwaSmithWaterman / GetSeq) are kept on the Go side as thin shims over
- * this batch ABI (INTEGRATION.md sections 2 and 4); BWA's own C symbol names are not re-exported.
+ * this batch ABI (INTEGRATION.md sections 2 and 4); BWA's own C symbol names are not re-exported; include/arachne_compat.h is the gobwa-shaped layer.
  */
 #ifndef ARACHNE_CUDA_H_
 #define ARACHNE_CUDA_H_
