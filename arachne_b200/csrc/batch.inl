@@ -275,6 +275,7 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
     }
     cudaEventRecord(ev[4], st);
     int stages = in->stages ? in->stages : (ARACHNE_STAGE_REGIONS | ARACHNE_STAGE_RESCUE | ARACHNE_STAGE_CIGAR);
+    if (stages & ARACHNE_STAGE_RECORDS) stages |= ARACHNE_STAGE_PLACE;
     if (stages & ARACHNE_STAGE_PLACE) stages |= ARACHNE_STAGE_CIGAR;  // placement scores the candidates' CIGAR statistics
     // ---- mate rescue ----
     AR_ALLOC(W.d_reg_loc, (n_reads + 1) * 8);
@@ -421,7 +422,7 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
     if (stages & ARACHNE_STAGE_PLACE) {
 #include "place_host.inl"
     }
-    cudaEventRecord(ev[8], st);
+    if (!(stages & ARACHNE_STAGE_PLACE)) { cudaEventRecord(ev[8], st); cudaEventRecord(ev[9], st); }
     AR_TRY(cudaStreamSynchronize(st));
 
     out->n_regs = (int64_t)total_regs;
@@ -441,7 +442,8 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
     cudaEventElapsedTime(&out->ms_rescue, ev[4], ev[5]);
     cudaEventElapsedTime(&out->ms_cigar, ev[6], ev[7]);
     cudaEventElapsedTime(&out->ms_place, ev[7], ev[8]);
-    cudaEventElapsedTime(&out->ms_total, ev[0], ev[8]);
+    cudaEventElapsedTime(&out->ms_records, ev[8], ev[9]);
+    cudaEventElapsedTime(&out->ms_total, ev[0], ev[9]);
     *out_ = out;
     return ARACHNE_OK;
 #undef AR_TRY

@@ -49,6 +49,7 @@ __device__ __forceinline__ void raise(Counters* c, int code, int read) {
 // ------------------------------------------------------------------------------------------------ k_seed2
 }  // namespace arachne
 #include "place.cuh"
+#include "records.cuh"
 #include "cigar_kernel.cuh"
 #include "seed_kernel.cuh"
 namespace arachne {
@@ -395,9 +396,9 @@ struct PinBuf {
 };
 
 struct BatchPriv {
-    PinBuf reg_off, regs, alns, cigar, mm, cand_off, cands, lmp;
+    PinBuf reg_off, regs, alns, cigar, mm, cand_off, cands, lmp, rec_off, recs;
     arachne_index_t* owner = nullptr;
-    void release() { reg_off.release(); regs.release(); alns.release(); cigar.release(); mm.release(); cand_off.release(); cands.release(); lmp.release(); }
+    void release() { reg_off.release(); regs.release(); alns.release(); cigar.release(); mm.release(); cand_off.release(); cands.release(); lmp.release(); rec_off.release(); recs.release(); }
 };
 
 // Per-index workspace: every device arena of the batch pipeline, grown on demand and kept between batches.
@@ -406,9 +407,9 @@ struct Workspace {
     DevBuf d_seeds, d_kseeds, d_chains, d_nodes, d_order, d_kept, d_nchain, d_nkseed, d_srt, d_regs, d_nregs, d_win, d_reg_off, d_out;
     DevBuf d_nregs_bak, d_reg_loc, d_blist, d_resc, d_reg_read, d_z, d_cig_scr, d_mm_scr, d_alns, d_cig, d_mm, d_hscr, d_rscr, d_xstate, d_xprob, d_xres, d_xrank, d_xperm, d_xctl;
     DevBuf d_bc_off, d_run_rfa, d_rand_seed, d_centro, d_pl_cnt, d_pl_scan, d_cand_off, d_lmp, d_cands, d_hot, d_aux, d_slow, d_slot_of_bc, d_bc_of_slot,
-        d_first, d_keys_a, d_keys_b, d_vals_a, d_vals_b, d_seg_off, d_mol, d_list2, d_list3, d_zband;
+        d_first, d_keys_a, d_keys_b, d_vals_a, d_vals_b, d_seg_off, d_mol, d_list2, d_list3, d_zband, d_attach, d_rec_i, d_rec_d, d_rec_cnt, d_recs;
     cudaStream_t own_stream = nullptr;
-    cudaEvent_t ev[10] = {};
+    cudaEvent_t ev[12] = {};
     Counters* h_cnt = nullptr;              // pinned
     unsigned long long* h_scalars = nullptr;  // pinned, 8 slots
     std::vector<DevBuf*> all() {
@@ -416,7 +417,8 @@ struct Workspace {
                 &d_seeds, &d_kseeds, &d_chains, &d_nodes, &d_order, &d_kept, &d_nchain, &d_nkseed, &d_srt, &d_regs, &d_nregs,
                 &d_win, &d_reg_off, &d_out, &d_nregs_bak, &d_reg_loc, &d_blist, &d_resc, &d_reg_read, &d_z, &d_cig_scr, &d_mm_scr, &d_alns, &d_cig, &d_mm, &d_hscr, &d_rscr, &d_xstate, &d_xprob, &d_xres, &d_xrank, &d_xperm, &d_xctl,
                 &d_bc_off, &d_run_rfa, &d_rand_seed, &d_centro, &d_pl_cnt, &d_pl_scan, &d_cand_off, &d_lmp, &d_cands, &d_hot, &d_aux, &d_slow, &d_slot_of_bc,
-                &d_bc_of_slot, &d_first, &d_keys_a, &d_keys_b, &d_vals_a, &d_vals_b, &d_seg_off, &d_mol, &d_list2, &d_list3, &d_zband};
+                &d_bc_of_slot, &d_first, &d_keys_a, &d_keys_b, &d_vals_a, &d_vals_b, &d_seg_off, &d_mol, &d_list2, &d_list3, &d_zband, &d_attach, &d_rec_i, &d_rec_d,
+                &d_rec_cnt, &d_recs};
     }
     int init() {
         if (cudaStreamCreateWithFlags(&own_stream, cudaStreamNonBlocking) != cudaSuccess) return -1;
@@ -564,6 +566,8 @@ int64_t arachne_name_seed(const char* name, int32_t len) {
 
 // ---------------------------------------------------------------------------------------------- batch
 #include "batch.inl"
+
+#include "records_host.inl"
 
 // ---------------------------------------------------------------------------------------------- stage entry points
 // DPX issue peak: a register-resident chain-free stream of VIADDMNMX (the max-plus instruction the DP kernels are built on).

@@ -151,6 +151,68 @@
     ++nl;
     k_place_mapq<<<sms * 4, 128, 0, st>>>(PA);
     AR_TRY(cudaGetLastError());
+    cudaEventRecord(ev[8], st);
+    // ---- record assembly: markDuplicates, CheckSplitReads, AppendBam's fields (records.cuh) ----
+    if (n_cands > 0) {
+        const bool want_records = (stages & ARACHNE_STAGE_RECORDS) != 0;
+        const uint8_t* d_attach = nullptr;
+        if (in->attach_bx && in->n_barcodes > 0) {
+            if (in_dev) d_attach = in->attach_bx;
+            else {
+                AR_ALLOC(W.d_attach, (size_t)n_bc + 8);
+                AR_TRY(cudaMemcpyAsync(W.d_attach.p, in->attach_bx, (size_t)n_bc, cudaMemcpyHostToDevice, st));
+                d_attach = W.d_attach.as<uint8_t>();
+            }
+        }
+        AR_ALLOC(W.d_rec_i, (size_t)(n_reads + 1) * 4 * 4);                  // act, split_reg, split_mapq, split_proper
+        AR_ALLOC(W.d_rec_d, (size_t)(n_reads + 1) * 8 * 2);                  // split_as, split_xs
+        AR_ALLOC(W.d_rec_cnt, (size_t)(n_reads + 2) * 8 * 2);                // counts, offsets
+        AR_ALLOC(W.d_keys_a, (size_t)(n_reads + 1) * 8); AR_ALLOC(W.d_keys_b, (size_t)(n_reads + 1) * 8);
+        AR_ALLOC(W.d_vals_a, (size_t)(n_reads + 1) * 4); AR_ALLOC(W.d_vals_b, (size_t)(n_reads + 1) * 4);
+        RecArgs RA2;
+        RA2.P = PA; RA2.attach_bx = d_attach;
+        int* ri = W.d_rec_i.as<int>(); const size_t nr1 = (size_t)n_reads + 1;
+        RA2.act = ri; RA2.split_reg = ri + nr1; RA2.split_mapq = ri + 2 * nr1; RA2.split_proper = ri + 3 * nr1;
+        RA2.split_as = W.d_rec_d.as<double>(); RA2.split_xs = RA2.split_as + nr1;
+        RA2.rec_cnt = W.d_rec_cnt.as<unsigned long long>(); RA2.rec_off = RA2.rec_cnt + (n_reads + 2); RA2.recs = nullptr;
+        k_rec_active<<<sms * 4, 256, 0, st>>>(PA, RA2.act);
+        k_rec_dup_keys<<<sms * 4, 256, 0, st>>>(PA, RA2.act, W.d_keys_a.as<unsigned long long>(), W.d_vals_a.as<unsigned>());
+        AR_TRY(cudaGetLastError());
+        size_t sbr = 0;
+        cub::DeviceRadixSort::SortPairs(nullptr, sbr, W.d_keys_a.as<unsigned long long>(), W.d_keys_b.as<unsigned long long>(), W.d_vals_a.as<unsigned>(),
+                                        W.d_vals_b.as<unsigned>(), (int)n_reads, 0, 64, st);
+        AR_ALLOC(W.d_tmp, sbr + 16);
+        sbr = W.d_tmp.cap;
+        AR_TRY(cub::DeviceRadixSort::SortPairs(W.d_tmp.p, sbr, W.d_keys_a.as<unsigned long long>(), W.d_keys_b.as<unsigned long long>(), W.d_vals_a.as<unsigned>(),
+                                               W.d_vals_b.as<unsigned>(), (int)n_reads, 0, 64, st));
+        k_rec_dup_mark<<<sms * 4, 256, 0, st>>>(PA, RA2.act, W.d_keys_b.as<unsigned long long>(), W.d_vals_b.as<unsigned>());  // markDuplicates closes DoRFAForOneBarcode (aligner.go:473,497)
+        AR_TRY(cudaGetLastError());
+        nl += 4 + 3;
+      if (want_records) {
+        k_rec_split<<<sms * 4, 256, 0, st>>>(RA2);
+        AR_TRY(cudaGetLastError());
+        cub::DeviceScan::ExclusiveSum(nullptr, tb, RA2.rec_cnt, const_cast<unsigned long long*>(RA2.rec_off), (int)n_reads + 1, st);
+        AR_ALLOC(W.d_tmp, tb + 16);
+        AR_TRY(cub::DeviceScan::ExclusiveSum(W.d_tmp.p, tb, RA2.rec_cnt, const_cast<unsigned long long*>(RA2.rec_off), (int)n_reads + 1, st));
+        nl += 1 + 2;
+        // at most two records per read: no size read-back before the last kernel
+        AR_ALLOC(W.d_recs, (size_t)(2 * n_reads + 1) * sizeof(Record));
+        RA2.recs = W.d_recs.as<Record>();
+        k_rec_emit<<<sms * 4, 128, 0, st>>>(RA2, W.d_cig.as<uint32_t>());
+        AR_TRY(cudaGetLastError());
+        ++nl;
+        AR_TRY(cudaMemcpyAsync(&hs[6], RA2.rec_off + n_reads, 8, cudaMemcpyDeviceToHost, st));
+        AR_TRY(cudaStreamSynchronize(st));
+        out->n_records = (int64_t)hs[6];
+        if (!out_dev) {
+            AR_PIN(priv->rec_off, (size_t)(n_reads + 1) * 8); AR_PIN(priv->recs, (size_t)(out->n_records + 1) * sizeof(Record));
+            AR_TRY(cudaMemcpyAsync(priv->rec_off.p, RA2.rec_off, (size_t)(n_reads + 1) * 8, cudaMemcpyDeviceToHost, st));
+            AR_TRY(cudaMemcpyAsync(priv->recs.p, W.d_recs.p, (size_t)out->n_records * sizeof(Record), cudaMemcpyDeviceToHost, st));
+            out->rec_off = priv->rec_off.as<int64_t>(); out->records = priv->recs.as<arachne_record_t>();
+        }
+      }
+    }
+    cudaEventRecord(ev[9], st);
     out->n_cands = n_cands;
     if (!out_dev) {
         AR_PIN(priv->cand_off, (size_t)(n_reads + 1) * 8); AR_PIN(priv->cands, (size_t)(n_cands + 1) * sizeof(Cand)); AR_PIN(priv->lmp, (size_t)n_bc * 8 + 8);

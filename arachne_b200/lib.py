@@ -57,7 +57,8 @@ class BatchIn(C.Structure):
                 ("barcode_off", C.POINTER(C.c_int64)), ("score_delta", C.c_int32), ("stages", C.c_int32),
                 ("flags", C.c_int32), ("max_read_len", C.c_int32), ("n_bases", C.c_int64),
                 ("run_rfa", C.POINTER(C.c_uint8)), ("rand_seed", C.POINTER(C.c_int64)), ("improper_penalty", C.c_double), ("delta", C.c_int32),
-                ("place_flags", C.c_int32), ("centro_start", C.POINTER(C.c_int64)), ("centro_end", C.POINTER(C.c_int64))]
+                ("place_flags", C.c_int32), ("centro_start", C.POINTER(C.c_int64)), ("centro_end", C.POINTER(C.c_int64)),
+                ("attach_bx", C.POINTER(C.c_uint8))]
 
 
 class BatchOut(C.Structure):
@@ -69,7 +70,16 @@ class BatchOut(C.Structure):
                 ("ms_seed", C.c_float), ("ms_sa", C.c_float), ("ms_chain", C.c_float), ("ms_extend", C.c_float), ("ms_rescue", C.c_float),
                 ("ms_cigar", C.c_float), ("ms_place", C.c_float), ("ms_total", C.c_float),
                 ("n_cands", C.c_int64), ("cand_off", C.POINTER(C.c_int64)), ("cands", C.c_void_p), ("log_molecule_penalty", C.POINTER(C.c_double)),
+                ("n_records", C.c_int64), ("rec_off", C.POINTER(C.c_int64)), ("records", C.c_void_p), ("ms_records", C.c_float),
                 ("priv", C.c_void_p)]
+
+
+RECORD = np.dtype([("read", "<i4"), ("reg", "<i4"), ("primary", "<i4"), ("flag", "<i4"), ("rid", "<i4"), ("mapq", "<i4"), ("mate_rid", "<i4"),
+                   ("duplicate", "<i4"), ("pos", "<i8"), ("mate_pos", "<i8"), ("tlen", "<i8"), ("reversed", "<i4"), ("clip_start", "<i4"),
+                   ("clip_end", "<i4"), ("hard", "<i4"), ("as", "<i4"), ("xs", "<i4"), ("has_xc", "<i4"), ("xc_reg", "<i4"), ("xm", "<i4"),
+                   ("am", "<i4"), ("xt", "<i4"), ("sa_reg", "<i4"), ("sa_rid", "<i4"), ("sa_rev", "<i4"), ("sa_hard", "<i4"), ("sa_mapq", "<i4"),
+                   ("sa_nm", "<i4"), ("_pad", "<i4"), ("sa_pos", "<i8"), ("attach_bx", "<i4"), ("has_dm", "<i4"), ("dm", "<f8")])
+assert RECORD.itemsize == 152
 
 
 def _p(a, t):
@@ -343,7 +353,10 @@ class ArachneCuda:
         return self.lib.arachne_name_seed(b, len(b))
 
     # ---- batch hot path ----
-    def align_batch(self, seq, off, bc_off=None, score_delta=25, stages=0, run_rfa=None, rand_seed=None, improper_penalty=-4.0, centromeres=None):
+    def align_batch(self, seq, off, bc_off=None, score_delta=25, stages=0, run_rfa=None, rand_seed=None, improper_penalty=-4.0, centromeres=None,
+                    attach_bx=None, sam=None):
+        """sam: dict(names=[...n_pairs], quals=[...2*n_pairs] or None, barcodes=[...n_barcodes] or None, read_group=str or None) -> res["sam"]
+        (needs stages & 16)."""
         seq = np.ascontiguousarray(seq, dtype=np.uint8); off = np.ascontiguousarray(off, dtype=np.int64)
         n_pairs = (len(off) - 1) // 2
         bi = BatchIn(); bi.n_pairs = n_pairs; bi.seq = _p(seq, C.c_uint8); bi.seq_off = _p(off, C.c_int64)
@@ -358,6 +371,8 @@ class ArachneCuda:
         if centromeres is not None:
             cs = np.ascontiguousarray(centromeres[0], dtype=np.int64); ce = np.ascontiguousarray(centromeres[1], dtype=np.int64)
             bi.centro_start = _p(cs, C.c_int64); bi.centro_end = _p(ce, C.c_int64)
+        if attach_bx is not None:
+            attach_bx = np.ascontiguousarray(attach_bx, dtype=np.uint8); bi.attach_bx = _p(attach_bx, C.c_uint8)
         po = C.POINTER(BatchOut)()
         self._ck(self.lib.arachne_align_batch(self.idx, C.byref(self.opt), C.byref(bi), C.byref(po)))
         try:
@@ -374,6 +389,19 @@ class ArachneCuda:
                 res["cands"] = np.frombuffer(C.string_at(o.cands, o.n_cands * 120), dtype=CAND).copy() if o.n_cands else np.zeros(0, CAND)
                 nb = bi.n_barcodes if bi.n_barcodes > 0 else 1
                 res["lmp"] = np.ctypeslib.as_array(o.log_molecule_penalty, shape=(nb,)).copy()
+            if o.rec_off:
+                res["rec_off"] = np.ctypeslib.as_array(o.rec_off, shape=(o.n_reads + 1,)).copy()
+                res["records"] = np.frombuffer(C.string_at(o.records, o.n_records * 152), dtype=RECORD).copy() if o.n_records else np.zeros(0, RECORD)
+                if sam is not None:
+                    arr = lambda xs: (C.c_char_p * len(xs))(*[x.encode() if isinstance(x, str) else x for x in xs]) if xs is not None else None
+                    txt, ln = C.c_void_p(None), C.c_size_t(0)
+                    self.lib.arachne_records_sam.argtypes = [C.c_void_p, C.POINTER(BatchIn), C.POINTER(BatchOut), C.c_void_p, C.c_void_p, C.c_void_p, C.c_char_p,
+                                                             C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]
+                    nm, ql, bcs = arr(sam["names"]), arr(sam.get("quals")), arr(sam.get("barcodes"))
+                    rg = sam.get("read_group")
+                    self._ck(self.lib.arachne_records_sam(self.idx, C.byref(bi), po, nm, ql, bcs, rg.encode() if rg else None, C.byref(txt), C.byref(ln)))
+                    res["sam"] = C.string_at(txt.value, ln.value).decode()
+                    C.CDLL(None).free(txt)
         finally:
             self.lib.arachne_batch_free(po)
         return res

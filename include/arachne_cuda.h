@@ -128,6 +128,34 @@ typedef struct {
     double raw_mapq;      /* the value before int() truncation */
 } arachne_cand_t;
 
+/* One SAM record as the reference's BAM writer assembles it (AppendBam, src/aligner/bamwriter.go:283-568; DoDumpToBam :635-658),
+ * fields only: ARACHNE_STAGE_RECORDS runs CheckSplitReads (split.go:31-160) and the flag /
+ * mate / TLEN / tag logic on the device; arachne_records_sam() turns the fields into SAM text on the host.  CSR by read
+ * (rec_off): the record of the read's active alignment, then its split alignment if one was chosen. */
+typedef struct {
+    int32_t read;          /* batch-global read index: QNAME, SEQ, QUAL source */
+    int32_t reg;           /* region of this record's alignment (CIGAR, AC:Z), -1 = unmapped placeholder */
+    int32_t primary;       /* 1: the read's active alignment; 0: its split alignment (flag 0x100) */
+    int32_t flag;          /* SAM FLAG */
+    int32_t rid;           /* RNAME contig, -1 = '*' */
+    int32_t mapq;
+    int32_t mate_rid;      /* RNEXT, -1 = '*' */
+    int32_t duplicate;
+    int64_t pos;           /* POS, 0-based, -1 unmapped */
+    int64_t mate_pos;      /* PNEXT, 0-based, -1 */
+    int64_t tlen;
+    int32_t reversed;      /* SEQ is reverse-complemented, QUAL reversed (bamwriter.go:371-374) */
+    int32_t clip_start, clip_end; /* SEQ / QUAL = oriented read [clip_start, clip_end): HardClip of split records (:664-689) */
+    int32_t hard;          /* leading / trailing S of the CIGAR are written as H */
+    int32_t as, xs;        /* AS:i, XS:i = int() of mapq_data.score / second_best_score (:416-418) */
+    int32_t has_xc, xc_reg;/* XC:Z lists the mismatch loci of region xc_reg (mapq_data.second_best); 0 / -1: empty string */
+    int32_t xm, am, xt;    /* XM:Z, AM:Z, XT:i */
+    int32_t sa_reg, sa_rid, sa_rev, sa_hard, sa_mapq, sa_nm; /* SA:Z (:459-492); sa_reg -1: no tag */
+    int64_t sa_pos;
+    int32_t attach_bx, has_dm; /* BX:Z + VX:i:1 (:556-565); DM:Z */
+    double dm;
+} arachne_record_t;
+
 typedef struct arachne_index arachne_index_t;
 
 typedef struct {
@@ -148,6 +176,8 @@ typedef struct {
     int32_t delta;             /* GetAlignments keeps score >= best - delta; DoRFAForOneBarcode passes 17 (aligner.go:455); 0 => 17 */
     int32_t place_flags;       /* ARACHNE_PLACE_* */
     const int64_t *centro_start, *centro_end; /* per contig id, HOST pointers, or NULL (-c / --centromeres, aligner.go:906-916) */
+    const uint8_t *attach_bx;  /* ARACHNE_STAGE_RECORDS: n_barcodes flags = WorkUnit.unique_barcode (aligner.go:474,498: BX/VX/DM are written);
+                                  NULL => run_rfa.  Device pointer under ARACHNE_IN_DEVICE */
 } arachne_batch_in_t;
 
 enum {
@@ -163,7 +193,8 @@ enum {
     ARACHNE_STAGE_REGIONS = 1, /* seeding, chaining, extension, dedup (mem_align1_core) */
     ARACHNE_STAGE_RESCUE = 2,  /* mem_matesw as driven by GoBwaMemMateSW */
     ARACHNE_STAGE_CIGAR = 4,   /* mem_reg2aln + GetAlignments walk */
-    ARACHNE_STAGE_PLACE = 8    /* tagBestAlignments .. estimateMapQualities */
+    ARACHNE_STAGE_PLACE = 8,   /* tagBestAlignments .. estimateMapQualities, markDuplicates */
+    ARACHNE_STAGE_RECORDS = 16 /* CheckSplitReads, the fields of every SAM record (implies PLACE) */
 };
 
 typedef struct {
@@ -186,6 +217,11 @@ typedef struct {
     int64_t *cand_off;         /* n_reads+1 */
     arachne_cand_t *cands;     /* n_cands */
     double *log_molecule_penalty; /* n_barcodes (calculateLogMoleculePenalty, aligner.go:722-755) */
+    /* ---- ARACHNE_STAGE_RECORDS outputs ---- */
+    int64_t n_records;
+    int64_t *rec_off;          /* n_reads+1 */
+    arachne_record_t *records; /* n_records */
+    float ms_records;
     void *priv;
 } arachne_batch_out_t;
 
@@ -246,6 +282,14 @@ int arachne_opts_default(arachne_mem_opt_t *opt);
  * per-candidate GoBwaSmithWaterman / GetSeq calls of GetAlignments (aligner.go:1500,1519). */
 int arachne_align_batch(arachne_index_t *idx, const arachne_mem_opt_t *opt, const arachne_batch_in_t *in, arachne_batch_out_t **out);
 void arachne_batch_free(arachne_batch_out_t *out);
+
+/* SAM text of every record of a batch that ran ARACHNE_STAGE_RECORDS with host outputs: one line per record, fields
+ * QNAME FLAG RNAME POS MAPQ CIGAR RNEXT PNEXT TLEN SEQ QUAL and the tags in AppendBam's order (RG XS XC AC AS XM AM XT SA BX VX DM;
+ * bamwriter.go:399-566).  `in` is the batch's input (host seq / seq_off / barcode_off).  names: n_pairs read names (FastQRecord.ReadInfo);
+ * quals: 2*n_pairs ASCII quality strings or NULL ('*'); barcodes: n_barcodes strings or NULL; read_group may be NULL.
+ * *sam is malloc'ed: release it with free().  BAM encoding itself (biogo/hts in the reference) stays with the host. */
+int arachne_records_sam(const arachne_index_t *idx, const arachne_batch_in_t *in, const arachne_batch_out_t *out, const char *const *names,
+                        const char *const *quals, const char *const *barcodes, const char *read_group, char **sam, size_t *sam_len);
 
 /* ---- stage entry points (device kernels on caller problems) ---- */
 /* ksw_extend2 (bwa/ksw.c:380-479) on n independent problems; query i = q[q_off[i]..q_off[i+1]), same for t.

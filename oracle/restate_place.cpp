@@ -18,6 +18,8 @@
 #include <string>
 #include <unordered_map>
 #include <vector>
+#include <set>
+#include <tuple>
 
 namespace {
 
@@ -155,6 +157,14 @@ struct Alignment {  // aligner.go:65-114 (fields that influence results)
     double second_best_score = 0, as_score = 0;
     double raw_mapq = 0;
     int reg = -1;
+    // record assembly (markDuplicates, CheckSplitReads, AppendBam)
+    int readmap_s = 0, readmap_e = 0;
+    bool duplicate = false;
+    Alignment* secondary = nullptr;  // the split alignment chosen for this (active) alignment
+    Alignment* primary = nullptr;    // set on a split alignment: the active alignment it belongs to
+    bool mapq_data_replaced = false; // split.mapq_data = &MapQData{second_best_score, score} (split.go:157)
+    std::vector<int> mmLocs, mmReadLocs;
+    int n_cigar = 0; const uint32_t* cigar = nullptr;  // mem_reg2aln's CIGAR, len<<4|op
 };
 
 struct CandidateMolecule {  // aligner.go:178-193
@@ -602,6 +612,142 @@ double estimateMapQualities(std::vector<std::vector<Alignment*>>& alignments, st
     return lmp;
 }
 
+// ------------------------------------------------------------------------------------------------ markDuplicates (aligner.go:611-641)
+void markDuplicates(std::vector<std::vector<Alignment*>>& alignments) {
+    struct Tuple { bool read1, reversed; int contig; int64_t pos; int mateContig; int64_t matePos;
+                   bool operator<(const Tuple& o) const { return std::tie(read1, reversed, contig, pos, mateContig, matePos) < std::tie(o.read1, o.reversed, o.contig, o.pos, o.mateContig, o.matePos); } };
+    std::set<Tuple> seen;
+    for (auto& arr : alignments)
+        for (Alignment* a : arr)
+            if (a->active) {
+                const Alignment* m = a->mate_alignment;
+                Tuple t{a->read1, a->reversed, a->contig, a->pos, m->contig, m->pos};
+                if (!seen.insert(t).second) a->duplicate = true;
+            }
+}
+
+// ------------------------------------------------------------------------------------------------ split reads (split.go:31-160)
+Alignment* GetSplitAlignment(Alignment* primary, std::vector<Alignment*>& alignments, const orc_ref_t* ref, double* second_best_out) {
+    *second_best_out = 0.0;
+    if (primary->pos == -1) return nullptr;
+    int Ps = primary->readmap_s, Pe = primary->readmap_e;
+    if (Ps > Pe) std::swap(Ps, Pe);
+    if (Pe - Ps > primary->read_len - 15) return nullptr;
+    struct Cand { Alignment* a; double score; };
+    std::vector<Cand> candidates;
+    for (Alignment* c : alignments) {
+        if (c->active || c->pos == -1) continue;
+        int Ss = c->readmap_s, Se = c->readmap_e, overlap;
+        if (Ss > Se) std::swap(Ss, Se);
+        if ((Ps < Ss && Pe > Se) || (Ss < Ps && Se > Pe)) continue;
+        else if (Ps < Ss) overlap = Pe - Ss;
+        else overlap = Se - Ps;
+        if (overlap < (Se - Ss) / 2) {
+            c->is_proper = isPair(c, primary->mate_alignment);
+            if (c->score >= 36 || c->is_proper) candidates.push_back({c, (double)c->score});
+        }
+    }
+    if (candidates.empty()) return nullptr;
+    // sort.Sort(SortSplitScoring) by score descending: insertion sort (stable) up to 12 elements, pdqsort above -- PARITY UNPINNED for
+    // ties among more than 12 candidates; a stable sort is used here
+    std::stable_sort(candidates.begin(), candidates.end(), [](const Cand& x, const Cand& y) { return x.score > y.score; });
+    Alignment* c = candidates[0].a;
+    double mapq;
+    double second_best = scoreAlignment(primary, nullptr, 0.0) + psuedoCountAlignmentScore(candidates[0].a, 0.0);
+    if (candidates.size() > 1) { mapq = candidates[0].score - candidates[1].score; second_best = scoreAlignment(primary, candidates[1].a, 0.0); }
+    else mapq = candidates[0].score;
+    int64_t start = -1, end = -1;
+    if (c->contig >= 0 && ref->centro_start) { start = ref->centro_start[c->contig]; end = ref->centro_end[c->contig]; }
+    if (c->pos > start && c->pos <= end) mapq = 0.0;
+    if (mapq > 60) mapq = 60;
+    c->mapq = (int)mapq;
+    *second_best_out = second_best;
+    return c;
+}
+
+void CheckSplitReads(std::vector<std::vector<Alignment*>>& reads, const orc_ref_t* ref) {
+    for (auto& arr : reads) {
+        Alignment* active = nullptr;
+        for (Alignment* a : arr) if (a->active) { active = a; break; }
+        double second_best;
+        Alignment* split = GetSplitAlignment(active, arr, ref, &second_best);
+        active->secondary = split;
+        if (split) {
+            split->second_best = nullptr; split->second_best_score = second_best;
+            split->as_score = scoreAlignment(split, active->mate_alignment, 0.0);
+            split->mapq_data_replaced = true;
+            split->primary = active;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ AppendBam (bamwriter.go:283-568), fields only
+struct RecOut { orc_record_t* recs; int64_t cap; int64_t n; const uint8_t* attach_bx; };
+
+int append_record(Alignment* aln, Alignment* primary, int64_t read, bool attach_bx, RecOut* X) {
+    if (X->n >= X->cap) return -1;
+    orc_record_t& R = X->recs[X->n++];
+    memset(&R, 0, sizeof(R));
+    int flags = 0;
+    if (!aln->is_proper && aln->score - 17 < 19) { aln->pos = -1; aln->mapq = 0; }
+    R.mate_rid = -1; R.mate_pos = -1; R.tlen = 0;
+    const Alignment* pm = primary->mate_alignment;
+    flags |= 1;  // mate_id >= 0 always
+    if (aln->is_proper) {
+        if (aln == primary) flags |= 0x2;
+        else if (isPair(aln, pm)) flags |= 0x2;
+    }
+    if (pm->pos == -1 || (!primary->is_proper && pm->score - 17 < 19)) { flags |= 0x8; }
+    else { if (pm->reversed) flags |= 0x20; R.mate_rid = pm->contig; R.mate_pos = pm->pos; }
+    flags |= aln->read1 ? 0x40 : 0x80;
+    if (aln->duplicate) flags |= 0x400;
+    if (pm->pos == -1) { R.mate_rid = -1; R.tlen = 0; }
+    else if (aln == primary) {
+        if (aln->contig == aln->mate_alignment->contig && (primary->is_proper || pm->score - 17 >= 19)) {
+            if (aln->reversed) R.tlen = -(aln->aend - aln->mate_alignment->pos);
+            else R.tlen = aln->mate_alignment->aend - aln->pos;
+        }
+    }
+    if (aln != primary) flags |= 256;
+    R.rid = aln->contig; R.mapq = aln->mapq;
+    if (aln->pos == -1) { flags |= 0x4; R.mapq = 0; R.rid = -1; }
+    if (aln->reversed) flags |= 0x10;
+    R.flag = flags; R.read = (int32_t)read; R.reg = aln->reg; R.primary = aln == primary; R.duplicate = aln->duplicate; R.reversed = aln->reversed;
+    R.pos = aln->pos;
+    // SEQ / QUAL range and hard clipping of split records (HardClip, bamwriter.go:664-689, on the forward-strand CIGAR)
+    R.clip_start = 0; R.clip_end = aln->read_len; R.hard = 0;
+    if (aln != primary) {
+        R.hard = 1;
+        if (aln->n_cigar >= 1 && (aln->cigar[0] & 0xf) == 3) R.clip_start = (int)(aln->cigar[0] >> 4);
+        if (aln->n_cigar >= 2 && (aln->cigar[aln->n_cigar - 1] & 0xf) == 3) R.clip_end -= (int)(aln->cigar[aln->n_cigar - 1] >> 4);
+    }
+    // tags
+    R.as = (int32_t)aln->as_score; R.xs = (int32_t)aln->second_best_score;
+    const Alignment* sb = aln->mapq_data_replaced ? nullptr : aln->second_best;
+    R.xc_reg = sb ? sb->reg : -1; R.has_xc = sb != nullptr;
+    R.xm = sb && sb->active_molecule; R.am = aln->active_molecule; R.xt = sb && aln->molecule_id == sb->molecule_id;
+    const Alignment* sa = aln->secondary ? aln->secondary : aln->primary;
+    R.sa_reg = -1;
+    if (sa && sa->pos > -1) {
+        R.sa_reg = sa->reg; R.sa_rid = sa->contig; R.sa_pos = sa->pos; R.sa_rev = sa->reversed; R.sa_hard = aln->secondary != nullptr; R.sa_mapq = sa->mapq;
+        int indel = 0;
+        for (int k = 0; k < sa->n_cigar; ++k) { const int op = sa->cigar[k] & 0xf; if (op == 1 || op == 2) indel += (int)(sa->cigar[k] >> 4); }
+        R.sa_nm = (int32_t)sa->mmLocs.size() + indel;
+    }
+    R.attach_bx = attach_bx; R.has_dm = attach_bx && aln->active_molecule; R.dm = aln->molecule_difference;
+    return 0;
+}
+
+int emit_records(std::vector<std::vector<Alignment*>>& alignments, int64_t read0, bool attach_bx, RecOut* X) {  // DoDumpToBam, bamwriter.go:635-658
+    for (size_t rl = 0; rl < alignments.size(); ++rl)
+        for (Alignment* a : alignments[rl])
+            if (a->active) {
+                if (append_record(a, a, read0 + (int64_t)rl, attach_bx, X)) return -1;
+                if (a->secondary && append_record(a->secondary, a, read0 + (int64_t)rl, attach_bx, X)) return -1;
+            }
+    return 0;
+}
+
 }  // namespace
 
 extern "C" {
@@ -628,9 +774,9 @@ int orc_walk(const orc_ref_t* ref, int l_query, const uint8_t* query, const void
     return n;
 }
 
-int orc_place(const orc_ref_t* ref, int64_t n_pairs, const uint8_t* seq, const int64_t* off, int64_t n_bc, const int64_t* bc_off, const uint8_t* run_rfa,
+static int place_impl(const orc_ref_t* ref, int64_t n_pairs, const uint8_t* seq, const int64_t* off, int64_t n_bc, const int64_t* bc_off, const uint8_t* run_rfa,
               const int64_t* rand_seed, const int64_t* reg_off, const void* regs_, const int64_t* aln, const uint32_t* cigar, double improper_penalty,
-              int delta, int64_t* cand_off, orc_cand_t* cands, int64_t cap, double* lmp_out) {
+              int delta, int64_t* cand_off, orc_cand_t* cands, int64_t cap, double* lmp_out, RecOut* X) {
     const Reg* regs = (const Reg*)regs_;
     g_improper = improper_penalty;
     int64_t n_cand = 0;
@@ -640,7 +786,7 @@ int orc_place(const orc_ref_t* ref, int64_t n_pairs, const uint8_t* seq, const i
     for (int64_t b = 0; b < n_bc; ++b) {
         const int64_t p0 = bc_off[b], p1 = bc_off[b + 1];
         const int n_reads = (int)(2 * (p1 - p0));
-        std::vector<std::vector<Alignment*>> alignments(n_reads);
+        std::vector<std::vector<Alignment*>> alignments(n_reads), full(n_reads);
         std::vector<Alignment*> pool;
         // ---- GetChains + GetAlignments (aligner.go:1633-1715, 1484-1631) ----
         int hit_num = 0;
@@ -665,6 +811,8 @@ int orc_place(const orc_ref_t* ref, int64_t n_pairs, const uint8_t* seq, const i
                     a->soft_clipped_length = w.soft_clipped_length;
                     a->pos = cpos; a->aend = caend;
                     if (cpos != -1 && reversed) { a->pos = caend + 1; a->aend = cpos + 1; }
+                    a->mmLocs = w.mmLocs; a->mmReadLocs = w.mmReadLocs; a->n_cigar = (int)a8[4]; a->cigar = cigar + a8[5];
+                    a->readmap_s = rg.qb; a->readmap_e = rg.qe;
                 } else {
                     a->id = (rl & 1) ? hit_num : 0;  // the read-1 placeholder omits hit_id (aligner.go:1665-1675)
                     a->pos = -1; a->aend = 0; a->contig = -1; a->score = 0;
@@ -673,9 +821,10 @@ int orc_place(const orc_ref_t* ref, int64_t n_pairs, const uint8_t* seq, const i
                 ++hit_num;
                 return a;
             };
-            if (g1 == g0) alignments[rl].push_back(make(-1));  // 0 >= 0 - delta: the placeholder always survives the filter
+            if (g1 == g0) { Alignment* a = make(-1); alignments[rl].push_back(a); full[rl].push_back(a); }  // 0 >= 0 - delta: the placeholder always survives the filter
             for (int64_t g = g0; g < g1; ++g) {
                 Alignment* a = make(g);
+                full[rl].push_back(a);
                 if (a->score >= bestScore - delta) alignments[rl].push_back(a);
             }
         }
@@ -700,6 +849,7 @@ int orc_place(const orc_ref_t* ref, int64_t n_pairs, const uint8_t* seq, const i
             lmp = estimateMapQualities(alignments, &mols, improper_penalty, ref);
         }
         if (lmp_out) lmp_out[b] = lmp;
+        markDuplicates(alignments);
         for (int rl = 0; rl < n_reads; ++rl)
             for (Alignment* a : alignments[rl]) {
                 orc_cand_t& c = cands[a->cand];
@@ -707,14 +857,37 @@ int orc_place(const orc_ref_t* ref, int64_t n_pairs, const uint8_t* seq, const i
                 c.mapq = a->mapq; c.molecule_id = a->molecule_id; c.active_molecule = a->active_molecule;
                 c.second_best = (a->active && a->second_best) ? a->second_best->cand : -1;
                 c.mate = a->mate_alignment ? a->mate_alignment->cand : -1;
-                c.duplicate = 0; c.pos = a->pos; c.aend = a->aend; c.log_alignment_probability = a->log_alignment_probability;
+                c.duplicate = a->duplicate; c.pos = a->pos; c.aend = a->aend; c.log_alignment_probability = a->log_alignment_probability;
                 c.as_score = a->as_score; c.xs_score = a->second_best_score; c.molecule_difference = a->molecule_difference;
                 c.sum_move_probability_change = a->sum_move_probability_change; c.molecule_confidence = a->molecule_confidence; c.raw_mapq = a->raw_mapq;
             }
+        // the candidate table above is the state after estimateMapQualities + markDuplicates; split selection and the writer edit
+        // is_proper / mapq / pos of some alignments afterwards (split.go:96,146; bamwriter.go:287-290) -- visible in the records only
+        if (X) {
+            CheckSplitReads(full, ref);
+            const bool attach_bx = X->attach_bx ? X->attach_bx[b] != 0 : (run_rfa && run_rfa[b]);
+            if (emit_records(alignments, 2 * p0, attach_bx, X) < 0) { for (auto* m : all_mols) delete m; for (auto* p : pool) delete p; return -2; }
+        }
         for (auto* m : all_mols) delete m;
         for (auto* p : pool) delete p;
     }
     return 0;
+}
+
+int orc_place(const orc_ref_t* ref, int64_t n_pairs, const uint8_t* seq, const int64_t* off, int64_t n_bc, const int64_t* bc_off, const uint8_t* run_rfa,
+              const int64_t* rand_seed, const int64_t* reg_off, const void* regs_, const int64_t* aln, const uint32_t* cigar, double improper_penalty,
+              int delta, int64_t* cand_off, orc_cand_t* cands, int64_t cap, double* lmp_out) {
+    return place_impl(ref, n_pairs, seq, off, n_bc, bc_off, run_rfa, rand_seed, reg_off, regs_, aln, cigar, improper_penalty, delta, cand_off, cands, cap, lmp_out, nullptr);
+}
+
+int orc_place_records(const orc_ref_t* ref, int64_t n_pairs, const uint8_t* seq, const int64_t* off, int64_t n_bc, const int64_t* bc_off, const uint8_t* run_rfa,
+                      const uint8_t* attach_bx, const int64_t* rand_seed, const int64_t* reg_off, const void* regs_, const int64_t* aln, const uint32_t* cigar,
+                      double improper_penalty, int delta, int64_t* cand_off, orc_cand_t* cands, int64_t cap, double* lmp_out, orc_record_t* recs, int64_t rec_cap,
+                      int64_t* n_recs) {
+    RecOut X; X.recs = recs; X.cap = rec_cap; X.n = 0; X.attach_bx = attach_bx;
+    const int rc = place_impl(ref, n_pairs, seq, off, n_bc, bc_off, run_rfa, rand_seed, reg_off, regs_, aln, cigar, improper_penalty, delta, cand_off, cands, cap, lmp_out, &X);
+    *n_recs = X.n;
+    return rc;
 }
 
 }  // extern "C"

@@ -1,5 +1,6 @@
 """GPU parity tier (pytest -m gpu): every stage of the CUDA path through the C ABI against the oracle
 (oracle/restate_*.c) and, when present, against the reference's own code (oracle/_ref)."""
+import ctypes as C
 import os
 
 import numpy as np
@@ -474,3 +475,84 @@ def test_compat_layer_per_pair_calls_batched(A, R, workdir):
             assert (b, en, rid) == (eb, ee, erid) and np.array_equal(got, exp)
     finally:
         K.close()
+
+
+# ---- row f1: record assembly (markDuplicates, CheckSplitReads, AppendBam's fields, SAM text) ----
+def _records_dataset(ctg, seed):
+    """Linked reads with what record assembly branches on: exact duplicate pairs inside a barcode, chimeric reads (two halves from
+    different places: split alignments), random reads (unmapped records, weak-alignment demotion), mates far apart (improper)."""
+    rs = S.simulate_linked_reads(ctg, n_barcodes=40, seed=seed, dash_suffix=True, sub=0.01)
+    g = np.random.default_rng(seed)
+    seq = rs.seq.copy(); off = rs.off
+    genome = np.concatenate([s for _, s in ctg])
+    for b in range(len(rs.bc_off) - 1):
+        p0, p1 = int(rs.bc_off[b]), int(rs.bc_off[b + 1])
+        for p in range(p0, p1 - 1):
+            u = g.random()
+            r1 = slice(off[2 * p], off[2 * p + 1]); r2 = slice(off[2 * p + 1], off[2 * p + 2])
+            L = r1.stop - r1.start
+            if u < 0.10:      # duplicate of the next pair
+                seq[off[2 * p + 2]:off[2 * p + 3]] = seq[r1]; seq[off[2 * p + 3]:off[2 * p + 4]] = seq[r2]
+            elif u < 0.30:    # chimera: the tail of read 1 comes from somewhere else
+                cut = int(g.integers(50, L - 45)); at = int(g.integers(0, len(genome) - L))
+                seq[r1.start + cut:r1.stop] = np.minimum(genome[at:at + L - cut], 3)
+            elif u < 0.36:    # read 2 is noise
+                seq[r2] = g.integers(0, 4, r2.stop - r2.start)
+            elif u < 0.40:    # both noise
+                seq[r1] = g.integers(0, 4, L); seq[r2] = g.integers(0, 4, r2.stop - r2.start)
+            elif u < 0.46:    # mate from far away: improper pair
+                at = int(g.integers(0, len(genome) - L)); seq[r2] = np.minimum(genome[at:at + (r2.stop - r2.start)], 3)
+    rs.seq = seq
+    return rs
+
+
+@pytest.mark.parametrize("rfa", [1, 0])
+def test_records_parity(A, R, workdir, rfa):
+    """ARACHNE_STAGE_RECORDS against the oracle's restatement of markDuplicates / CheckSplitReads / AppendBam, field by field, and the
+    library's SAM text against an independent formatter run on the oracle's records.  (Go side: parity unpinned, as rows a15-a20.)"""
+    fa, ctg, _ = util.make_dataset("rep600k", workdir)
+    R.load(fa); A.load_index(fa)
+    rs = _records_dataset(ctg, 77)
+    nb = len(rs.bc_off) - 1
+    seeds = np.array([A.name_seed(n) for n in rs.names], dtype=np.int64)
+    run_rfa = np.full(nb, rfa, np.uint8)
+    attach = (np.arange(nb) % 5 != 0).astype(np.uint8)  # work.unique_barcode
+    if rfa:
+        attach[:] = 1                                   # worthRunningRFA implies a unique barcode (aligner.go:1018-1030)
+    quals = ["".join(chr(33 + (7 * i + k) % 40) for k in range(int(rs.off[i + 1] - rs.off[i]))) for i in range(2 * rs.n_pairs)]
+    ubar = [rs.barcodes[b] for b in range(nb)]
+    res = A.align_batch(rs.seq, rs.off, rs.bc_off, stages=31, run_rfa=run_rfa, rand_seed=seeds, attach_bx=attach,
+                        sam=dict(names=rs.names, quals=quals, barcodes=ubar, read_group="sample:lib:1"))
+    ref = R.batch(rs.seq, rs.off, rescue=True, cigar=True, threads=8)
+    assert res["regs"].tobytes() == ref["regs"].tobytes()
+    P = util.PlaceOracle(fa)
+    oc, ocands, olmp, orecs = P.place_records(rs.seq, rs.off, rs.bc_off, run_rfa, attach, seeds, ref["reg_off"], ref["regs"], ref["aln"], ref["cigar"])
+    _check_place(res, oc, ocands, olmp, "records")
+    g = res["records"]
+    assert len(g) == len(orecs) and np.array_equal(res["rec_off"][1:] - res["rec_off"][:-1], np.bincount(orecs["read"], minlength=2 * rs.n_pairs))
+    for f in g.dtype.names:
+        if f in ("_pad", "dm"):
+            continue
+        d = np.nonzero(g[f] != orecs[f])[0]
+        assert len(d) == 0, (f, len(d), int(d[0]), g[d[0]], orecs[d[0]])
+    assert np.allclose(g["dm"], orecs["dm"], rtol=1e-9, atol=1e-12)
+    # the dataset exercises the branches
+    fl = g["flag"]
+    assert (g["primary"] == 0).sum() > 20 and (fl & 0x400).sum() > 10 and (fl & 0x4).sum() > 20 and (fl & 0x8).sum() > 20 and ((fl & 0x2) == 0).sum() > 50
+    assert (g["sa_reg"] >= 0).sum() > 40 and (g["has_xc"] == 1).sum() > 50 and (g["tlen"] != 0).sum() > 500
+    # SAM text: the library's formatter on its records vs a pure-Python formatter on the oracle's records
+    e = ref["aln"]
+    O = util.oracle_lib()
+    def mm_of_reg(gi):
+        r = int(np.searchsorted(ref["reg_off"], gi, side="right") - 1)
+        q = np.ascontiguousarray(rs.seq[rs.off[r]:rs.off[r + 1]])
+        out5 = np.zeros(5, np.int32); mm = np.zeros(2 * len(q) + 8, np.int32)
+        n = O.orc_walk(C.byref(P.ref), len(q), q.ctypes.data_as(C.c_void_p), ref["regs"][gi:gi + 1].ctypes.data_as(C.c_void_p), e[gi].ctypes.data_as(C.c_void_p),
+                       ref["cigar"].ctypes.data_as(C.c_void_p), out5.ctypes.data_as(C.c_void_p), mm.ctypes.data_as(C.c_void_p))  # orc_walk indexes the pool with aln8[5]
+        return mm[:n], mm[n:2 * n]
+    names = [c[0] for c in util.read_ann(fa)[1]]
+    exp = util.sam_lines(orecs, names, rs.seq, rs.off, rs.bc_off, rs.names, quals, ubar, "sample:lib:1", lambda gi: (int(e[gi, 4]), int(e[gi, 5])), ref["cigar"], mm_of_reg)
+    got = res["sam"].rstrip("\n").split("\n")
+    assert len(got) == len(exp)
+    for i, (x, y) in enumerate(zip(got, exp)):
+        assert x == y, (i, x, y)

@@ -271,6 +271,74 @@ class PlaceOracle:
         return cand_off, cands[:cand_off[-1]], lmp
 
 
+def _oracle_records(self, seq, off, bc_off, run_rfa, attach_bx, seeds, reg_off, regs, aln8, cigar, improper=-4.0, delta=17):
+    """orc_place_records: placement + markDuplicates + CheckSplitReads + AppendBam's fields (oracle/restate_place.cpp)."""
+    from arachne_b200.lib import RECORD
+    seq = np.ascontiguousarray(seq, np.uint8); off = np.ascontiguousarray(off, np.int64); bc_off = np.ascontiguousarray(bc_off, np.int64)
+    run_rfa = np.ascontiguousarray(run_rfa, np.uint8); seeds = np.ascontiguousarray(seeds, np.int64)
+    attach_bx = None if attach_bx is None else np.ascontiguousarray(attach_bx, np.uint8)
+    reg_off = np.ascontiguousarray(reg_off, np.int64); regs = np.ascontiguousarray(regs); aln8 = np.ascontiguousarray(aln8, np.int64)
+    cigar = np.ascontiguousarray(cigar, np.uint32)
+    n_pairs = (len(off) - 1) // 2; cap = len(regs) + 2 * n_pairs + 8
+    cand_off = np.zeros(2 * n_pairs + 1, np.int64); cands = np.zeros(cap, CAND); lmp = np.zeros(max(1, len(bc_off) - 1))
+    recs = np.zeros(4 * n_pairs + 8, RECORD); n_recs = C.c_int64(0)
+    vp = lambda a: a.ctypes.data_as(C.c_void_p) if a is not None else None
+    self.O.orc_place_records.argtypes = [C.POINTER(OrcRef), C.c_int64] + [C.c_void_p] * 2 + [C.c_int64] + [C.c_void_p] * 8 + [C.c_double, C.c_int, C.c_void_p, C.c_void_p,
+                                          C.c_int64, C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(C.c_int64)]
+    rc = self.O.orc_place_records(C.byref(self.ref), n_pairs, vp(seq), vp(off), len(bc_off) - 1, vp(bc_off), vp(run_rfa), vp(attach_bx), vp(seeds), vp(reg_off),
+                                  vp(regs), vp(aln8), vp(cigar), improper, delta, vp(cand_off), vp(cands), cap, vp(lmp), vp(recs), len(recs), C.byref(n_recs))
+    assert rc == 0, rc
+    return cand_off, cands[:cand_off[-1]], lmp, recs[:n_recs.value]
+
+
+PlaceOracle.place_records = _oracle_records
+
+
+def sam_lines(recs, contig_names, seq, off, bc_off, names, quals, barcodes, read_group, aln_of_reg, cigar, mm_of_reg):
+    """Independent (pure Python) SAM formatter for record fields, used on the ORACLE's records: field and tag order of AppendBam
+    (bamwriter.go:283-568).  aln_of_reg(g) -> (n_cigar, cigar_off); mm_of_reg(g) -> (ref loci, read offsets)."""
+    dec, cmpl = "ACGTN", "TGCAN"
+    out = []
+    def cig(g, hard, rev):
+        n, o = aln_of_reg(g)
+        ws = [int(cigar[o + k]) for k in range(n)]
+        if rev:
+            ws = ws[::-1]
+        return "".join("%d%s" % (w >> 4, "MIDSH"[4 if (w & 15) == 3 and hard else (w & 15)]) for w in ws)
+    def mml(g):
+        if g < 0:
+            return ""
+        a, b = mm_of_reg(g)
+        return "".join("%d,%d,1;" % (int(x), int(y)) for x, y in zip(a, b))
+    for R in recs:
+        r = int(R["read"]); pair = r >> 1
+        b = int(np.searchsorted(bc_off, pair, side="right") - 1)
+        q = seq[off[r]:off[r + 1]]; L = len(q)
+        rng = range(int(R["clip_start"]), int(R["clip_end"]))
+        rev = bool(R["reversed"])
+        s = "".join((cmpl if rev else dec)[min(int(q[L - 1 - k] if rev else q[k]), 4)] for k in rng) or "*"
+        ql = quals[r] if quals is not None else None
+        qs = ("".join((ql[L - 1 - k] if rev else ql[k]) for k in rng) if ql is not None and len(rng) else "*")
+        g = int(R["reg"])
+        f = [names[pair].rstrip("\n"), str(int(R["flag"])), contig_names[R["rid"]] if R["rid"] >= 0 else "*", str(int(R["pos"]) + 1), str(int(R["mapq"])),
+             (cig(g, bool(R["hard"]), False) if g >= 0 and aln_of_reg(g)[0] > 0 else "*"),
+             "*" if R["mate_rid"] < 0 else ("=" if R["mate_rid"] == R["rid"] else contig_names[R["mate_rid"]]), str(int(R["mate_pos"]) + 1), str(int(R["tlen"])), s, qs]
+        if read_group:
+            f.append("RG:Z:" + read_group)
+        f += ["XS:i:%d" % R["xs"], "XC:Z:" + (mml(int(R["xc_reg"])) if R["has_xc"] else ""), "AC:Z:" + mml(g), "AS:i:%d" % R["as"], "XM:Z:%d" % R["xm"], "AM:Z:%d" % R["am"],
+              "XT:i:%d" % R["xt"]]
+        if R["sa_reg"] >= 0:
+            f.append("SA:Z:%s,%d,%s,%s,%d,%d;" % (contig_names[R["sa_rid"]], R["sa_pos"], "-" if R["sa_rev"] else "+", cig(int(R["sa_reg"]), bool(R["sa_hard"]), bool(R["sa_rev"])),
+                                                 R["sa_mapq"], R["sa_nm"]))
+        bc = barcodes[b] if barcodes is not None else None
+        if R["attach_bx"] and bc is not None and "-" in bc:
+            f += ["BX:Z:" + bc, "VX:i:1"]
+            if R["has_dm"]:
+                f.append("DM:Z:%.6f" % R["dm"])
+        out.append("\t".join(f))
+    return out
+
+
 def place_mismatches(res, oc, ocands, olmp):
     """Compare the library's placement outputs with the oracle's.  Integers exactly; floating point: pair scores are sums of
     dyadic rationals (exact), the molecule penalty goes through log10 and MAPQ through pow/log10, which differ from the host
