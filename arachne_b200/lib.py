@@ -86,6 +86,61 @@ def _p(a, t):
     return a.ctypes.data_as(C.POINTER(t))
 
 
+class IngestBatch(C.Structure):  # arachne_ingest_batch_t (include/arachne_ingest.h)
+    _fields_ = [("n_pairs", C.c_int64), ("n_units", C.c_int64), ("seq", C.POINTER(C.c_uint8)), ("seq_off", C.POINTER(C.c_int64)), ("qual", C.c_void_p),
+                ("unit_off", C.POINTER(C.c_int64)), ("unique", C.POINTER(C.c_uint8)), ("run_rfa", C.POINTER(C.c_uint8)), ("valid", C.POINTER(C.c_uint8)),
+                ("rand_seed", C.POINTER(C.c_int64)), ("names", C.c_void_p), ("name_off", C.POINTER(C.c_int64)), ("barcodes", C.c_void_p),
+                ("barcode_char_off", C.POINTER(C.c_int64)), ("read_groups", C.c_void_p), ("read_group_off", C.POINTER(C.c_int64)), ("priv", C.c_void_p)]
+
+
+class Ingest:
+    """ctypes mirror of include/arachne_ingest.h: barcode-grouped FASTQ batches (reader.go:208-291) ready for align_batch.  Host only."""
+
+    def __init__(self, r1: str, r2: str, n_threads: int = 4, path: str | None = None):
+        L = self.lib = C.CDLL(path or lib_path())
+        L.arachne_last_error.restype = C.c_char_p
+        L.arachne_ingest_open.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.POINTER(C.c_void_p)]
+        L.arachne_ingest_next.argtypes = [C.c_void_p, C.c_int64, C.POINTER(C.POINTER(IngestBatch))]
+        L.arachne_ingest_batch_free.argtypes = [C.POINTER(IngestBatch)]
+        L.arachne_ingest_close.argtypes = [C.c_void_p]
+        self.h = C.c_void_p(None)
+        rc = L.arachne_ingest_open(r1.encode(), r2.encode(), n_threads, C.byref(self.h))
+        if rc:
+            raise ArachneError(f"arachne_ingest_open {rc}: {L.arachne_last_error().decode()}")
+
+    def next(self, target_pairs: int, copy: bool = True):
+        """-> dict of numpy arrays / string lists for the next batch, or None at the end of the input."""
+        pb = C.POINTER(IngestBatch)()
+        rc = self.lib.arachne_ingest_next(self.h, target_pairs, C.byref(pb))
+        if rc == 1:
+            return None
+        if rc:
+            raise ArachneError(f"arachne_ingest_next {rc}: {self.lib.arachne_last_error().decode()}")
+        try:
+            b = pb.contents; n, u = b.n_pairs, b.n_units
+            off = np.ctypeslib.as_array(b.seq_off, shape=(2 * n + 1,)).copy()
+            nb = int(off[-1])
+            out = dict(n_pairs=n, n_units=u, off=off, seq=np.ctypeslib.as_array(b.seq, shape=(max(nb, 1),))[:nb].copy(),
+                       unit_off=np.ctypeslib.as_array(b.unit_off, shape=(u + 1,)).copy(), unique=np.ctypeslib.as_array(b.unique, shape=(u,)).copy(),
+                       run_rfa=np.ctypeslib.as_array(b.run_rfa, shape=(u,)).copy(), valid=np.ctypeslib.as_array(b.valid, shape=(u,)).copy(),
+                       rand_seed=np.ctypeslib.as_array(b.rand_seed, shape=(n,)).copy())
+            if copy:
+                no = np.ctypeslib.as_array(b.name_off, shape=(n + 1,)); bo = np.ctypeslib.as_array(b.barcode_char_off, shape=(u + 1,)); go = np.ctypeslib.as_array(b.read_group_off, shape=(u + 1,))
+                names = C.string_at(b.names, int(no[-1])); bcs = C.string_at(b.barcodes, int(bo[-1])); rgs = C.string_at(b.read_groups, int(go[-1])); ql = C.string_at(b.qual, nb)
+                out["names"] = [names[no[i]:no[i + 1]].decode() for i in range(n)]
+                out["barcodes"] = [bcs[bo[i]:bo[i + 1]].decode() for i in range(u)]
+                out["read_groups"] = [rgs[go[i]:go[i + 1]].decode() for i in range(u)]
+                out["quals"] = [ql[off[i]:off[i + 1]].decode() for i in range(2 * n)]
+            return out
+        finally:
+            self.lib.arachne_ingest_batch_free(pb)
+
+    def close(self):
+        if self.h:
+            self.lib.arachne_ingest_close(self.h)
+            self.h = C.c_void_p(None)
+
+
 class AlnRegV(C.Structure):  # mem_alnreg_v / arachne_alnreg_v
     _fields_ = [("n", C.c_size_t), ("m", C.c_size_t), ("a", C.c_void_p)]
 

@@ -291,6 +291,129 @@ def parity_sample(A):
     return out
 
 
+# ---------------------------------------------------------------------------------------------- configs[4]: ksw_extend2 microbench
+def ksw_problems(n, L, seed):
+    """Extension problems with the shape mem_chain2aln's call sites give them (bwamem.c:715-771) for single-seed chains of simulated
+    reads: a read of length L copied from a random reference with 1 % substitutions and 0.05 %/base insertions and deletions; the seed is
+    its longest error-free stretch (>= 19); the LEFT flank (read and reference reversed, h0 = seed length, target = flank +
+    cal_max_gap(flank) bases of reference) and the RIGHT flank (h0 = seed length + left flank length as an upper bound of the left
+    score) each give one problem.  Half of the n problems are of this kind, half are pure-random flanks against unrelated targets (the
+    early-termination path).  Returns lists of query / target arrays and h0."""
+    g = np.random.default_rng(seed)
+    qs, ts, h0 = [], [], []
+    def max_gap(q):  # cal_max_gap (bwamem.c:621-628) with a=1, o=6, e=1, w=100
+        l = max(int((q * 1 - 6) / 1 + 1.), 1)
+        return min(l, 200)
+    n_real = n // 2
+    while len(qs) < n_real:
+        m = 4096
+        ref = g.integers(0, 4, (m, L + 420), dtype=np.uint8)
+        start = 210
+        for k in range(m):
+            r = ref[k]
+            read = r[start:start + L].copy()
+            sub = np.nonzero(g.random(L) < 0.01)[0]
+            read[sub] = (read[sub] + g.integers(1, 4, len(sub))) & 3
+            brk = set(sub.tolist())
+            tgt = r
+            if g.random() < 0.14:  # one 1-3 base indel (0.05 %/base each way over 2 x L bases)
+                p = int(g.integers(10, L - 10)); l = int(g.integers(1, 4))
+                if g.random() < 0.5:
+                    read = np.concatenate([read[:p], g.integers(0, 4, l).astype(np.uint8), read[p:L - l]])
+                else:
+                    read = np.concatenate([read[:p], read[p + l:], r[start + L:start + L + l]])
+                brk.add(p)
+            edges = [-1] + sorted(brk) + [L]
+            best = max(range(len(edges) - 1), key=lambda i: edges[i + 1] - edges[i])
+            sb, se = edges[best] + 1, edges[best + 1]
+            if se - sb < 19:
+                continue
+            if sb > 0:       # left flank, reversed
+                q = read[:sb][::-1]; tl = sb + max_gap(sb)
+                t = tgt[max(start + sb - tl, 0):start + sb][::-1]
+                qs.append(q); ts.append(t); h0.append(se - sb)
+            if se < L:       # right flank
+                q = read[se:]; tl = (L - se) + max_gap(L - se)
+                t = tgt[start + se:start + se + tl]
+                qs.append(q); ts.append(t); h0.append(min(se, 255 - (L - se)))
+            if len(qs) >= n_real:
+                break
+    qs, ts, h0 = qs[:n_real], ts[:n_real], h0[:n_real]
+    for _ in range(n - n_real):
+        ql = int(g.integers(5, max(6, L - 19))); tl = ql + max_gap(ql)
+        qs.append(g.integers(0, 4, ql).astype(np.uint8)); ts.append(g.integers(0, 4, tl).astype(np.uint8)); h0.append(int(g.integers(19, max(20, min(L - ql, 255 - ql) + 1))))
+    return qs, ts, np.array(h0, np.int32)
+
+
+def run_ksw(args):
+    """--config ksw: BASELINE.json configs[4], ksw_extend2 (bwa/ksw.c:380-479) on the grid band 16-256 x read length 100-250, GCUPS counted
+    in in-band cells exactly as ksw.c:424-448 visits them.  value = the L=150, w=100 point (the pipeline's shape)."""
+    import torch
+    from arachne_b200 import ArachneCuda
+    from tests import util
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: libarachne_cuda has no CPU path")
+    A = ArachneCuda()
+    n = args.pairs if args.pairs != 1000000 else 1 << 20
+    R = None
+    try:
+        from oracle.refbwa import RefBwa, available
+        R = RefBwa() if available() else None
+    except Exception:
+        R = None
+    clk = ClockSampler(0); clk.start()
+    grid, head, e2e_head = [], None, None
+    for L in (100, 150, 200, 250):
+        qs, ts, h0 = ksw_problems(n, L, 15 + L)
+        q, qo = util.pack(qs); t, to = util.pack(ts)
+        for w in (16, 32, 64, 100, 128, 200, 256):
+            wv = np.full(n, w, np.int32)
+            for _ in range(max(0, args.warmup - 1) if (L, w) == (150, 100) else 0):
+                A.ksw_extend(q, qo, t, to, h0, wv, end_bonus=5, zdrop=100, repeat=1)
+            t0 = time.perf_counter()
+            out, cells, ms = A.ksw_extend(q, qo, t, to, h0, wv, end_bonus=5, zdrop=100, repeat=args.steps)
+            wall = time.perf_counter() - t0
+            row = {"read_len": L, "w": w, "problems": n, "cells": int(cells), "kernel_ms": ms, "gcups": cells / ms / 1e6}
+            if R is not None and not args.no_cpu_baseline:
+                k = min(400, n); c0 = time.perf_counter(); ccells = 0
+                for i in range(k):
+                    r = R.ksw_extend2(qs[i], ts[i], w, 5, 100, int(h0[i]))
+                    if tuple(out[i]) != tuple(r):
+                        row["parity_failure"] = [i, [int(x) for x in out[i]], [int(x) for x in r]]
+                dt = time.perf_counter() - c0
+                row.update({"cpu_problems": k, "cpu_gcups_1thread": cells * (k / n) / dt / 1e9})
+            grid.append(row)
+            log(json.dumps(row))
+            if (L, w) == (150, 100):
+                head = row
+                # end to end through the C ABI: host arrays in, results out, one launch (the call above minus its warm-up launch and repeats)
+                t0 = time.perf_counter(); A.ksw_extend(q, qo, t, to, h0, wv, end_bonus=5, zdrop=100, repeat=1); e2e_head = time.perf_counter() - t0
+    clocks = clk.stop()
+    dpx = A.dpx_peak()
+    ok = not any("parity_failure" in r for r in grid)
+    line = {"metric": "ksw_extend2 banded-SW GCUPS", "value": head["gcups"], "unit": "GCUPS", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": head["kernel_ms"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32 (scores as bytes, DPX max-plus)",
+            "data": "synthetic",
+            "config": {"workload": f"configs[4]: ksw_extend2 microbench, {n} problems per point: half with the shape of mem_chain2aln's call sites for simulated 1 %-error reads "
+                                   "(left + right flank of the longest exact seed, target = flank + cal_max_gap), half pure-random; grid band {16,32,64,100,128,200,256} x read length "
+                                   "{100,150,200,250}; value = the L=150, w=100 point; h0 = seed length, end_bonus 5, zdrop 100", "name": "ksw",
+                       "l2_policy": "each point's queries + targets + results (>= 150 MB) exceed nothing but are streamed once per launch; launches of different points alternate"},
+            "grid": grid,
+            "roofline": {"kernel": "k_ext_dp (ksw_extend2, one problem per lane)", "bound": "dpx issue", "unit": "G DPX-class ops/s", "dpx_ops_per_cell": 4.75,
+                         "achieved": head["gcups"] * 4.75, "peak": dpx, "frac": head["gcups"] * 4.75 / dpx if dpx else None, "traffic": None,
+                         "peak_source": "measured in this run: independent VIADDMNMX streams (arachne_dpx_peak); the integer ALU pipe they share with the cell's 3 PRMT + 1 SHF "
+                                        "+ key max is the binding unit: 9.25 ALU-pipe instructions per cell (SASS of the 4-cell group)",
+                         "alu_ops_per_cell": 9.25, "alu_frac": head["gcups"] * 9.25 / dpx if dpx else None},
+            "e2e": {"value": head["cells"] / e2e_head / 1e9, "unit": "GCUPS", "h2d_bytes_per_step": int(sum(len(x) for x in qs) + sum(len(x) for x in ts) + 16 * n + 8 * n),
+                    "d2h_bytes_per_step": 24 * n, "timing": "host wall clock around one arachne_ksw_extend_batch call with host arrays (L=250 set sizes for the byte counts)"},
+            "gpu_launches": (args.steps + 1) * 28, "clocks": clocks, "parity_ok": ok}
+    if head.get("cpu_gcups_1thread"):
+        line["cpu_baseline"] = {"value": head["cpu_gcups_1thread"], "unit": "GCUPS", "cores": 1, "kind": "reference",
+                                "sample": f"{head['cpu_problems']} problems of the L=150, w=100 point through the reference's own ksw_extend2 (oracle/_ref), one thread, ctypes call overhead included"}
+    emit(line)
+    return 0 if ok else 3
+
+
 def run_reference(args, rank, world):
     """--impl reference: the reference's CPU implementation on this box's host cores, same workload/metric.  Rank 0 only."""
     if rank != 0:
@@ -350,6 +473,12 @@ def main():
     _REAL_STDOUT = os.dup(1)
     os.dup2(2, 1)
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.config == "ksw":
+        if rank != 0:
+            return 0
+        if args.impl == "reference":
+            args.no_cpu_baseline = False
+        return run_ksw(args)
     if args.impl == "reference":
         return run_reference(args, rank, world)
     import torch
