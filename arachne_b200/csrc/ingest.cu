@@ -10,6 +10,7 @@
 // barcodes and md5 name seeds; the caller's thread (arachne_ingest_next) walks the parsed chunks in order and applies the
 // work-unit rule.  Host code only.
 #include <zlib.h>
+#include <algorithm>
 #include <condition_variable>
 #include <cstdio>
 #include <cstdlib>
@@ -38,7 +39,7 @@ struct Parsed {  // one chunk pair
     std::vector<uint8_t> seq; std::vector<char> qual; std::vector<int32_t> len;  // 2 per pair
     std::vector<int64_t> soff;  // first base of each pair in seq / qual
     std::string names, barcodes, rgs; std::vector<int32_t> name_end, bc_end, rg_end;
-    std::vector<uint8_t> valid; std::vector<int64_t> seed;
+    std::vector<uint8_t> valid, same_prev; std::vector<int64_t> seed;  // same_prev[r]: record r has the barcode of record r - 1 of this chunk
     bool last = false; int rc = 0; std::string err;
 };
 
@@ -88,6 +89,7 @@ bool parse_header(const char* s, size_t n, std::string* name, std::string* bc, b
 
 extern "C" int64_t arachne_name_seed(const char* name, int32_t len);
 
+static void delete_batch(void* p);
 struct arachne_ingest {
     std::string path[2];
     int n_threads = 4;
@@ -101,7 +103,8 @@ struct arachne_ingest {
     Parsed cur; int cur_pos = 0; bool have_cur = false, eof = false;
     std::string last_barcode; bool have_last = false;
     long n_pairs_total = 0;
-    ~arachne_ingest() { for (auto& c : raw) if (c) c->close(); { std::lock_guard<std::mutex> l(pmu); parse_done = true; next_take = 1L << 60; pcv.notify_all(); } for (auto& t : threads) if (t.joinable()) t.join(); }
+    std::mutex pool_mu; std::vector<void*> pool;  // released batch buffers: their (already touched) memory is reused
+    ~arachne_ingest() { for (void* p : pool) delete_batch(p); for (auto& c : raw) if (c) c->close(); { std::lock_guard<std::mutex> l(pmu); parse_done = true; next_take = 1L << 60; pcv.notify_all(); } for (auto& t : threads) if (t.joinable()) t.join(); }
 };
 
 namespace {
@@ -118,16 +121,19 @@ void split_thread(arachne_ingest* I, int which) {
         if (got < 0) { I->split_rc[which] = ARACHNE_ERR_IO; I->split_err[which] = "read error in " + I->path[which]; break; }
         if (got == 0) break;
         const char* p = buf.data(); const char* end = p + got;
+        const char* seg = p;  // start of the bytes not yet appended to the chunk: one append per chunk boundary / buffer, not per line
         while (p < end) {
             const char* nl = static_cast<const char*>(memchr(p, '\n', (size_t)(end - p)));
-            if (!nl) { ch.text.append(p, (size_t)(end - p)); break; }
-            ch.text.append(p, (size_t)(nl + 1 - p)); p = nl + 1; ++line;
+            if (!nl) break;
+            p = nl + 1; ++line;
             if (++lines_in_chunk == 4 * CHUNK_RECORDS) {
+                ch.text.append(seg, (size_t)(p - seg)); seg = p;
                 ch.n_records = CHUNK_RECORDS;
                 if (!I->raw[which]->push(std::move(ch))) { gzclose(f); return; }
                 ch = RawChunk(); ch.first_line = line; lines_in_chunk = 0;
             }
         }
+        ch.text.append(seg, (size_t)(end - seg));
     }
     gzclose(f);
     if (!ch.text.empty() && ch.text.back() != '\n') { ch.text.push_back('\n'); ++lines_in_chunk; }
@@ -154,6 +160,10 @@ void parse_pair(const RawChunk& a, const RawChunk& b, Parsed* P) {
         if (hl == 0 || h1[0] != '@') { P->rc = ARACHNE_ERR_IO; char m[128]; snprintf(m, sizeof(m), "malformed FASTQ: record header expected at line %ld of R1", a.first_line + 4L * r + 1); P->err = m; return; }
         parse_header(h1 + 1, hl, &name, &bc, &valid, &rg);  // hl - 1 header bytes + the newline
         P->names += name; P->name_end.push_back((int32_t)P->names.size());
+        {
+            const int pb0 = r >= 2 ? P->bc_end[r - 2] : 0, pb1 = r >= 1 ? P->bc_end[r - 1] : 0;
+            P->same_prev.push_back(r >= 1 && (size_t)(pb1 - pb0) == bc.size() && !memcmp(P->barcodes.data() + pb0, bc.data(), bc.size()));
+        }
         P->barcodes += bc; P->bc_end.push_back((int32_t)P->barcodes.size());
         P->rgs += rg; P->rg_end.push_back((int32_t)P->rgs.size());
         P->valid.push_back(valid);
@@ -214,9 +224,16 @@ struct BatchBuf {
     std::vector<uint8_t> unique, run_rfa, valid; std::vector<int64_t> seed;
     std::string names; std::vector<int64_t> name_off{0}; std::string barcodes; std::vector<int64_t> bc_off{0}; std::string rgs; std::vector<int64_t> rg_off{0};
     arachne_ingest_batch_t pub;
+    arachne_ingest* owner = nullptr;
+    void reset() {
+        seq.clear(); qual.clear(); off.assign(1, 0); unit_off.assign(1, 0); unique.clear(); run_rfa.clear(); valid.clear(); seed.clear();
+        names.clear(); name_off.assign(1, 0); barcodes.clear(); bc_off.assign(1, 0); rgs.clear(); rg_off.assign(1, 0);
+    }
 };
 
 }  // namespace
+
+static void delete_batch(void* p) { delete static_cast<BatchBuf*>(p); }
 
 extern "C" {
 
@@ -238,7 +255,17 @@ int arachne_ingest_next(arachne_ingest_t* I, int64_t target_pairs, arachne_inges
     if (!I || !out) { set_error("arachne_ingest_next: null argument"); return ARACHNE_ERR_ARG; }
     *out = nullptr;
     if (I->eof && !(I->have_cur && I->cur_pos < I->cur.n)) return ARACHNE_INGEST_EOF;
-    auto* B = new BatchBuf();
+    BatchBuf* B = nullptr;
+    {
+        std::lock_guard<std::mutex> l(I->pool_mu);
+        if (!I->pool.empty()) { B = static_cast<BatchBuf*>(I->pool.back()); I->pool.pop_back(); }
+    }
+    if (!B) B = new BatchBuf(); else B->reset();
+    B->owner = I;
+    {   // growing a 100 MB vector by doubling copies it twice over and page-faults all of it: size from the request instead
+        const size_t want = (size_t)std::min<int64_t>(target_pairs, 4000000) + 65536;
+        B->seq.reserve(want * 320); B->qual.reserve(want * 320); B->off.reserve(2 * want + 2); B->seed.reserve(want); B->name_off.reserve(want + 1); B->names.reserve(want * 24);
+    }
     int rc = 0;
     int64_t n_pairs = 0;
     // ReadBarcodeSet, one call per loop trip (reader.go:208-291); a record that opens the next unit is simply not consumed yet
@@ -246,29 +273,37 @@ int arachne_ingest_next(arachne_ingest_t* I, int64_t target_pairs, arachne_inges
         int index = 0; bool ended_by_change = false, at_eof = false;
         std::string first_bc;
         const int64_t unit_start = n_pairs;
-        for (; index < UNIT_CAP; ++index) {
+        while (index < UNIT_CAP) {
             if (!next_record(I, &rc)) { at_eof = true; break; }
             const Parsed& P = I->cur; const int r = I->cur_pos;
             const int b0 = r ? P.bc_end[r - 1] : 0;
-            const std::string bc(P.barcodes.data() + b0, (size_t)(P.bc_end[r] - b0));
-            if (index == 0) first_bc = bc;
-            else if (bc != first_bc) { ended_by_change = true; break; }
-            // append the record
-            const int l1 = P.len[2 * r], l2 = P.len[2 * r + 1];
-            const size_t so = (size_t)P.soff[r];
-            B->seq.insert(B->seq.end(), P.seq.begin() + so, P.seq.begin() + so + l1 + l2);
-            B->qual.insert(B->qual.end(), P.qual.begin() + so, P.qual.begin() + so + l1 + l2);
-            B->off.push_back(B->off.back() + l1); B->off.push_back(B->off.back() + l2);
-            const int n0 = r ? P.name_end[r - 1] : 0; B->names.append(P.names.data() + n0, (size_t)(P.name_end[r] - n0)); B->name_off.push_back((int64_t)B->names.size());
-            B->seed.push_back(P.seed[r]);
+            const size_t bl = (size_t)(P.bc_end[r] - b0);
+            if (index == 0) first_bc.assign(P.barcodes.data() + b0, bl);
+            else if (bl != first_bc.size() || memcmp(P.barcodes.data() + b0, first_bc.data(), bl)) { ended_by_change = true; break; }
+            // how many records of this chunk can be taken in one go: the run of this barcode (same_prev marks a record whose barcode
+            // equals its predecessor's), cut by the cap and by the continuation rule (a record at index >= 200 ends the unit)
+            const bool cont = I->have_last && first_bc == I->last_barcode;
+            int lim = UNIT_CAP - index;
+            if (cont) { const int to_break = index >= UNIT_CONT ? 1 : UNIT_CONT - index + 1; lim = lim < to_break ? lim : to_break; }
+            int k = 1;
+            while (k < lim && r + k < P.n && P.same_prev[r + k]) ++k;
+            // append records [r, r + k)
+            const size_t so = (size_t)P.soff[r], se = r + k < P.n ? (size_t)P.soff[r + k] : P.seq.size();
+            B->seq.insert(B->seq.end(), P.seq.begin() + so, P.seq.begin() + se);
+            B->qual.insert(B->qual.end(), P.qual.begin() + so, P.qual.begin() + se);
+            for (int t = 2 * r; t < 2 * (r + k); ++t) B->off.push_back(B->off.back() + P.len[t]);
+            const int n0 = r ? P.name_end[r - 1] : 0; const int64_t nb0 = (int64_t)B->names.size() - n0;
+            B->names.append(P.names.data() + n0, (size_t)(P.name_end[r + k - 1] - n0));
+            for (int t = r; t < r + k; ++t) B->name_off.push_back(nb0 + P.name_end[t]);
+            B->seed.insert(B->seed.end(), P.seed.begin() + r, P.seed.begin() + r + k);
             if (index == 0) {
                 const int g0 = r ? P.rg_end[r - 1] : 0;
-                B->barcodes += bc; B->bc_off.push_back((int64_t)B->barcodes.size());
+                B->barcodes += first_bc; B->bc_off.push_back((int64_t)B->barcodes.size());
                 B->rgs.append(P.rgs.data() + g0, (size_t)(P.rg_end[r] - g0)); B->rg_off.push_back((int64_t)B->rgs.size());
                 B->valid.push_back(P.valid[r]);
             }
-            ++I->cur_pos; ++n_pairs;
-            if (index > 0 && I->have_last && first_bc == I->last_barcode && index >= UNIT_CONT) { ++index; break; }  // "abnormal break": the record stays in the unit
+            I->cur_pos += k; n_pairs += k; index += k;
+            if (cont && index - 1 >= UNIT_CONT && index - 1 > 0) break;  // "abnormal break" (reader.go:266-270): the record at index >= 200 stays in the unit
         }
         if (rc) { delete B; return rc; }
         const int64_t n_unit = n_pairs - unit_start;
@@ -292,6 +327,15 @@ int arachne_ingest_next(arachne_ingest_t* I, int64_t target_pairs, arachne_inges
     return ARACHNE_OK;
 }
 
-void arachne_ingest_batch_free(arachne_ingest_batch_t* b) { if (b) delete static_cast<BatchBuf*>(b->priv); }
+void arachne_ingest_batch_free(arachne_ingest_batch_t* b) {
+    if (!b) return;
+    auto* B = static_cast<BatchBuf*>(b->priv);
+    arachne_ingest* I = B->owner;
+    if (I) {
+        std::lock_guard<std::mutex> l(I->pool_mu);
+        if (I->pool.size() < 3) { I->pool.push_back(B); return; }
+    }
+    delete B;
+}
 
 }  // extern "C"

@@ -269,3 +269,96 @@ def test_sharded_two_ranks_gloo_matches_unsharded(workdir):
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
                         "--master-port", str(29500 + os.getpid() % 2000), script], capture_output=True, text=True, timeout=600)
     assert "SHARD_MERGE_OK" in r.stdout, (r.stdout[-2000:], r.stderr[-2000:])
+
+
+# ---- row f2: barcode-grouped FASTQ ingest (csrc/ingest.cu) against a line-by-line Python restatement of src/fastqreader/reader.go ----
+def _reader_go(r1_lines, r2_lines):
+    """ReadOneLine + ParseHeader + ReadBarcodeSet (reader.go:95-291) and worthRunningRFA (aligner.go:1018-1030) on in-memory lines."""
+    import re
+    recs = []
+    for i in range(0, min(len(r1_lines), len(r2_lines)) - 3, 4):
+        h = r1_lines[i][1:]                           # R1_line[1:], newline included
+        bx = re.search(r"BX:Z:(\S+)\s", h)
+        if bx:
+            _id = h.split()[0]; name = _id[:len(_id) - 2]; bc = bx.group(1)
+            vx = re.search(r"VX:i:([01])\s", h); valid = bool(vx and vx.group(1) == "1")
+        else:
+            name, bc, valid = "", "", False
+        f = h[:-1].split()
+        rg = f[-1] if len(f) >= 2 else ""
+        recs.append((name, bc, valid, rg, r1_lines[i + 1][:-1], r1_lines[i + 3][:-1], r2_lines[i + 1][:-1], r2_lines[i + 3][:-1]))
+    units, pos, last = [], 0, None
+    while pos < len(recs):
+        first = recs[pos][1]; idx = 0; full = None
+        while True:
+            if idx == 30000:
+                full = False; break
+            if pos + idx >= len(recs):
+                full = True; break                    # EOF: deferred error, the unit is returned as a full barcode
+            if recs[pos + idx][1] != first:
+                full = True; break                    # the record is left pending
+            if last is not None and first == last and idx >= 200:
+                idx += 1; full = False; break         # "abnormal break": the record stays
+            idx += 1
+        units.append((pos, pos + idx, full)); pos += idx; last = first
+    return recs, units
+
+
+@pytest.mark.parametrize("gz", [False, True])
+def test_ingest_matches_reader_go(tmp_path, gz):
+    import gzip, hashlib
+    from arachne_b200 import Ingest
+    g = np.random.default_rng(9)
+    # barcodes: ordinary ones, one above the 30000-record cap (-> 30000 + 201-record continuation units), a plain (no '-') one,
+    # a header without BX (empty name and barcode), one with VX:i:0, lower-case / N / '-' bases, a last field that is a read group
+    plan = [("A01C02B03D04-1", 7), ("A01C02B03D05-1", 3), ("NOBX", 2), ("A09C02B03D05", 6), ("BIG-1", 30000 + 201 + 201 + 17), ("A11C12B13D14-1", 5), ("ZZZ-1", 1)]
+    r1, r2, k = [], [], 0
+    for bc, n in plan:
+        for _ in range(n):
+            L1 = int(g.integers(30, 152)); L2 = int(g.integers(30, 152))
+            s1 = "".join("ACGTNacgt-"[int(x)] for x in g.integers(0, 10 if k % 50 == 0 else 4, L1)); s2 = "".join("ACGT"[int(x)] for x in g.integers(0, 4, L2))
+            q1 = "".join(chr(33 + int(x)) for x in g.integers(0, 41, L1)); q2 = "".join(chr(33 + int(x)) for x in g.integers(0, 41, L2))
+            tag = "" if bc == "NOBX" else "\tBX:Z:%s\tVX:i:%d" % (bc, 0 if k % 7 == 3 else 1)
+            tail = "\tRG:sample:lib:%d" % (k % 3) if k % 2 else ""
+            r1 += ["@read%d/1%s%s\n" % (k, tag, tail), s1 + "\n", "+\n", q1 + "\n"]; r2 += ["@read%d/2%s%s\n" % (k, tag, tail), s2 + "\n", "+\n", q2 + "\n"]
+            k += 1
+    p1, p2 = str(tmp_path / ("r1.fq" + (".gz" if gz else ""))), str(tmp_path / ("r2.fq" + (".gz" if gz else "")))
+    for p, lines in ((p1, r1), (p2, r2)):
+        with (gzip.open(p, "wt") if gz else open(p, "w")) as f:
+            f.write("".join(lines))
+    recs, units = _reader_go(r1, r2)
+    nt4 = np.full(256, 4, np.uint8)
+    for i, c in enumerate("ACGT"):
+        nt4[ord(c)] = i; nt4[ord(c) + 32] = i
+    nt4[ord("-")] = 5
+    I = Ingest(p1, p2, n_threads=3)
+    try:
+        got_units, pair = [], 0
+        for target in (10, 1, 100000, 50, 10**9):     # different batch sizes: units never straddle batches
+            while True:
+                b = I.next(target)
+                if b is None:
+                    break
+                assert b["unit_off"][0] == 0 and b["unit_off"][-1] == b["n_pairs"] and b["n_units"] >= 1
+                for u in range(b["n_units"]):
+                    lo, hi = int(b["unit_off"][u]), int(b["unit_off"][u + 1])
+                    got_units.append((pair + lo, pair + hi, bool(b["unique"][u])))
+                    first = recs[pair + lo]
+                    assert b["barcodes"][u] == first[1] and b["read_groups"][u] == first[3] and bool(b["valid"][u]) == first[2]
+                    assert bool(b["run_rfa"][u]) == (bool(b["unique"][u]) and "-" in first[1] and hi - lo >= 5)
+                for i in range(b["n_pairs"]):
+                    name, bc, valid, rg, s1, q1, s2, q2 = recs[pair + i]
+                    assert b["names"][i] == name
+                    assert b["rand_seed"][i] == int.from_bytes(hashlib.md5(name.encode()).digest()[:8], "little", signed=True)
+                    o = b["off"][2 * i:2 * i + 3]
+                    assert np.array_equal(b["seq"][o[0]:o[1]], nt4[np.frombuffer(s1.encode(), np.uint8)]) and np.array_equal(b["seq"][o[1]:o[2]], nt4[np.frombuffer(s2.encode(), np.uint8)])
+                    assert b["quals"][2 * i] == q1 and b["quals"][2 * i + 1] == q2
+                pair += b["n_pairs"]
+                if target != 10**9 and pair > 200:
+                    break
+        assert pair == len(recs)
+        assert got_units == units, (got_units[:12], units[:12])
+        sizes = [hi - lo for lo, hi, _ in units]
+        assert 30000 in sizes and sizes.count(201) == 2 and any(not f for _, _, f in units)
+    finally:
+        I.close()
