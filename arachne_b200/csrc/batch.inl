@@ -29,6 +29,7 @@ int arachne_index_set_option(arachne_index_t* idx, const char* name, int64_t val
     else if (!strcmp(name, "seed_blocks_per_sm") && value >= 1 && value <= 4) idx->opt_seed_blocks = (int)value;
     else if (!strcmp(name, "seed_fwd_levels") && value >= 0 && value <= 15) idx->opt_seed_kmer = (idx->opt_seed_kmer & 0xff) | (int)value << 8;
     else if (!strcmp(name, "seed_direct")) idx->opt_seed_direct = value != 0;
+    else if (!strcmp(name, "seed_impl") && (value == 2 || value == 3)) idx->opt_seed_impl = (int)value;
     else if (!strcmp(name, "seed_shared_list") && value >= -1 && value <= 16) idx->opt_seed_slist = (int)value;
     else { set_error("arachne_index_set_option: unknown option or value: %s=%lld", name, (long long)value); return ARACHNE_ERR_ARG; }
     return ARACHNE_OK;
@@ -76,12 +77,12 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
     Workspace& W = *wsp;
     const int sms = sm_count(idx->device);
     cudaStream_t st;
-    int use_seed_kmer, seed_bpsm_opt, seed_slist, use_seed_direct;
+    int use_seed_kmer, seed_bpsm_opt, seed_slist, use_seed_direct, seed_impl;
     BatchPriv* priv = nullptr;
     {
         std::lock_guard<std::mutex> g(idx->mu);
         st = idx->has_user_stream ? reinterpret_cast<cudaStream_t>(idx->user_stream) : W.own_stream;
-        use_seed_kmer = idx->opt_seed_kmer; seed_bpsm_opt = idx->opt_seed_blocks; seed_slist = idx->opt_seed_slist; use_seed_direct = idx->opt_seed_direct;
+        use_seed_kmer = idx->opt_seed_kmer; seed_bpsm_opt = idx->opt_seed_blocks; seed_slist = idx->opt_seed_slist; use_seed_direct = idx->opt_seed_direct; seed_impl = idx->opt_seed_impl;
         if (!idx->priv_pool.empty()) { priv = reinterpret_cast<BatchPriv*>(idx->priv_pool.back()); idx->priv_pool.pop_back(); }
     }
     cudaEvent_t* ev = W.ev;  // seed | sa | chain | extend | rescue | gather | cigar | end
@@ -130,8 +131,10 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
     unsigned long long* hs = W.h_scalars;
     // ---- seeding (retry with a larger per-read interval capacity if a read overflows it) ----
     if (idx->fm.seq_len >= (1ull << 40) - 2) { set_error("reference too long for the packed interval lists (2*l_pac must stay below 2^40)"); return fail(ARACHNE_ERR_ARG); }
-    const int seed_bpsm = seed_bpsm_opt >= 1 && seed_bpsm_opt <= 4 ? seed_bpsm_opt : 3, seed_blocks = sms * seed_bpsm, seed_T = seed_blocks * 256, list_rows = 2 * L1;
-    AR_ALLOC(W.d_scratch, (size_t)seed_T * list_rows * sizeof(uint4));
+    const int seed_bpsm = seed_bpsm_opt >= 1 && seed_bpsm_opt <= 4 ? seed_bpsm_opt : 3, seed_blocks = sms * seed_bpsm, list_rows = 2 * L1;
+    const S3Plan s3 = seed3_plan(maxlen);
+    const size_t seed_T = seed_impl == 3 ? (size_t)sms * s3.ns : (size_t)seed_blocks * 256;  // lanes (k_seed2) / states (k_seed3) that own a list
+    AR_ALLOC(W.d_scratch, seed_T * list_rows * sizeof(uint4));
     int intv_cap = 32;
     cudaEventRecord(ev[0], st);
     // the reads 2-bit packed with their masks: what the seeding lanes keep in shared memory (seed_kernel.cuh)
@@ -155,7 +158,11 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
         // shared-memory head of the interval lists: as many entries as fit next to the resident blocks (16 at 3 blocks/SM)
         int slist_n = 0, nwq = 0;
         const size_t seed_smem = seed_smem_plan(maxlen, seed_bpsm, seed_slist, &slist_n, &nwq);
-        if (seed_bpsm == 4) {
+        if (seed_impl == 3) {
+            AR_TRY(cudaFuncSetAttribute(k_seed3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s3.smem));
+            k_seed3<<<sms, S3_THREADS, s3.smem, st>>>(idx->fm, opt, d_off, (int)n_reads, maxlen, W.d_scratch.as<uint4>(), list_rows, so,
+                                                      W.d_misc.as<unsigned int>(), W.d_cnt.as<Counters>(), use_seed_kmer, s3.ns, d_qpk, qstride, s3.nwq, seed_direct);
+        } else if (seed_bpsm == 4) {
             AR_TRY(cudaFuncSetAttribute(k_seed2<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)seed_smem));
             k_seed2<4><<<seed_blocks, 256, seed_smem, st>>>(idx->fm, opt, d_off, (int)n_reads, maxlen, W.d_scratch.as<uint4>(), list_rows, so,
                                                              W.d_misc.as<unsigned int>(), W.d_cnt.as<Counters>(), use_seed_kmer, slist_n, d_qpk, qstride, nwq, seed_direct);

@@ -52,6 +52,7 @@ __device__ __forceinline__ void raise(Counters* c, int code, int read) {
 #include "records.cuh"
 #include "cigar_kernel.cuh"
 #include "seed_kernel.cuh"
+#include "seed3_kernel.cuh"
 namespace arachne {
 
 // ------------------------------------------------------------------------------------------------ k_expand / k_sa
@@ -446,7 +447,11 @@ int arachne_device_count(void) {
     return n;
 }
 
-int arachne_index_load(const char* prefix, int device, arachne_index_t** out) { return index_load(prefix, device, out); }
+int arachne_index_load(const char* prefix, int device, arachne_index_t** out) {
+    const int rc = index_load(prefix, device, out);
+    if (rc == ARACHNE_OK && getenv("ARACHNE_SEED_IMPL")) { const int v = atoi(getenv("ARACHNE_SEED_IMPL")); if (v == 2 || v == 3) (*out)->opt_seed_impl = v; }
+    return rc;
+}
 
 void arachne_index_free(arachne_index_t* idx) {
     if (!idx) return;
@@ -629,7 +634,10 @@ int arachne_seed_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, int6
     int maxlen = 0;
     for (int64_t i = 0; i < n_reads; ++i) maxlen = std::max<int>(maxlen, (int)(seq_off[i + 1] - seq_off[i]));
     if (maxlen > ARACHNE_MAX_READ_LEN) { set_error("read longer than %d", ARACHNE_MAX_READ_LEN); return ARACHNE_ERR_ARG; }
-    const int L1 = maxlen + 1, blocks = sm_count(idx->device) * 3, T = blocks * 256, rows = 2 * L1;
+    const S3Plan s3 = seed3_plan(maxlen);
+    const int seed_impl = idx->opt_seed_impl;
+    const int L1 = maxlen + 1, blocks = sm_count(idx->device) * 3, rows = 2 * L1;
+    const size_t T = seed_impl == 3 ? (size_t)sm_count(idx->device) * s3.ns : (size_t)blocks * 256;
     int cap = 32;
     DevBuf d_seq, d_off, d_scr, d_arena, d_next, d_in, d_nsa, d_cnt;
     int64_t nb = seq_off[n_reads];
@@ -658,9 +666,15 @@ int arachne_seed_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, int6
         if (d_c2.ensure(n_reads * 8 + 8)) { rel(); set_error("out of device memory"); return ARACHNE_ERR_CUDA; }
         AR_CUDA(cudaMemset(d_c2.p, 0, n_reads * 8 + 8));
         SeedOut so; so.intv = d_arena.as<Intv>(); so.cnt2 = d_c2.as<int>(); so.cap = cap;
+        if (seed_impl == 3) {
+            AR_CUDA(cudaFuncSetAttribute(k_seed3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s3.smem));
+            k_seed3<<<sm_count(idx->device), S3_THREADS, s3.smem>>>(idx->fm, opt, d_off.as<int64_t>(), (int)n_reads, maxlen, d_scr.as<uint4>(), rows, so,
+                                    d_next.as<unsigned int>(), d_cnt.as<Counters>(), idx->opt_seed_kmer, s3.ns, d_qpk, qstride, s3.nwq, seed_direct);
+        } else {
         AR_CUDA(cudaFuncSetAttribute(k_seed2<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)seed_smem));
         k_seed2<3><<<blocks, 256, seed_smem>>>(idx->fm, opt, d_off.as<int64_t>(), (int)n_reads, maxlen, d_scr.as<uint4>(), rows, so,
                                     d_next.as<unsigned int>(), d_cnt.as<Counters>(), idx->opt_seed_kmer, slist_n, d_qpk, qstride, nwq, seed_direct);
+        }
         AR_CUDA(cudaGetLastError());
         AR_CUDA(cudaMemcpy(&hc, d_cnt.p, sizeof(hc), cudaMemcpyDeviceToHost));
         if (!hc.err) break;
