@@ -30,6 +30,7 @@ int arachne_index_set_option(arachne_index_t* idx, const char* name, int64_t val
     else if (!strcmp(name, "seed_fwd_levels") && value >= 0 && value <= 15) idx->opt_seed_kmer = (idx->opt_seed_kmer & 0xff) | (int)value << 8;
     else if (!strcmp(name, "seed_direct")) idx->opt_seed_direct = value != 0;
     else if (!strcmp(name, "seed_impl") && (value == 2 || value == 3)) idx->opt_seed_impl = (int)value;
+    else if (!strcmp(name, "seed3_threads") && (value == 512 || value == 768 || value == 1024)) idx->opt_seed3_threads = (int)value;
     else if (!strcmp(name, "seed_shared_list") && value >= -1 && value <= 16) idx->opt_seed_slist = (int)value;
     else { set_error("arachne_index_set_option: unknown option or value: %s=%lld", name, (long long)value); return ARACHNE_ERR_ARG; }
     return ARACHNE_OK;
@@ -159,9 +160,11 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
         int slist_n = 0, nwq = 0;
         const size_t seed_smem = seed_smem_plan(maxlen, seed_bpsm, seed_slist, &slist_n, &nwq);
         if (seed_impl == 3) {
-            AR_TRY(cudaFuncSetAttribute(k_seed3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s3.smem));
-            k_seed3<<<sms, S3_THREADS, s3.smem, st>>>(idx->fm, opt, d_off, (int)n_reads, maxlen, W.d_scratch.as<uint4>(), list_rows, so,
-                                                      W.d_misc.as<unsigned int>(), W.d_cnt.as<Counters>(), use_seed_kmer, s3.ns, d_qpk, qstride, s3.nwq, seed_direct);
+            const int nt = idx->opt_seed3_threads;
+            auto kfn = nt == 512 ? k_seed3<512> : nt == 1024 ? k_seed3<1024> : k_seed3<768>;
+            AR_TRY(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s3.smem));
+            kfn<<<sms, nt, s3.smem, st>>>(idx->fm, opt, d_off, (int)n_reads, maxlen, W.d_scratch.as<uint4>(), list_rows, so,
+                                          W.d_misc.as<unsigned int>(), W.d_cnt.as<Counters>(), use_seed_kmer, s3.ns, d_qpk, qstride, s3.nwq, seed_direct);
         } else if (seed_bpsm == 4) {
             AR_TRY(cudaFuncSetAttribute(k_seed2<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)seed_smem));
             k_seed2<4><<<seed_blocks, 256, seed_smem, st>>>(idx->fm, opt, d_off, (int)n_reads, maxlen, W.d_scratch.as<uint4>(), list_rows, so,

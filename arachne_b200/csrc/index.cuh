@@ -26,6 +26,7 @@ struct arachne_index {
     void *d_bwt = nullptr, *d_sa = nullptr, *d_pac = nullptr, *d_contigs = nullptr, *d_kmer = nullptr, *d_isa = nullptr, *d_text = nullptr;
     // runtime knobs (arachne_index_set_option): use the k-mer table in seeding; resident seeding blocks per SM
     int opt_seed_kmer = 1, opt_seed_blocks = 3, opt_seed_slist = -1, opt_seed_direct = 1;
+    int opt_seed3_threads = 768;
     int opt_seed_impl = 2;  // 2: k_seed2 (one read per lane), 3: k_seed3 (states in shared memory, one queue per kind of step)
     size_t device_bytes = 0;
     std::vector<arachne::Contig> contigs;

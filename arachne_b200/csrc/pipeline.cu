@@ -450,6 +450,7 @@ int arachne_device_count(void) {
 int arachne_index_load(const char* prefix, int device, arachne_index_t** out) {
     const int rc = index_load(prefix, device, out);
     if (rc == ARACHNE_OK && getenv("ARACHNE_SEED_IMPL")) { const int v = atoi(getenv("ARACHNE_SEED_IMPL")); if (v == 2 || v == 3) (*out)->opt_seed_impl = v; }
+    if (rc == ARACHNE_OK && getenv("ARACHNE_SEED3_THREADS")) { const int v = atoi(getenv("ARACHNE_SEED3_THREADS")); if (v == 512 || v == 768 || v == 1024) (*out)->opt_seed3_threads = v; }
     return rc;
 }
 
@@ -667,8 +668,10 @@ int arachne_seed_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, int6
         AR_CUDA(cudaMemset(d_c2.p, 0, n_reads * 8 + 8));
         SeedOut so; so.intv = d_arena.as<Intv>(); so.cnt2 = d_c2.as<int>(); so.cap = cap;
         if (seed_impl == 3) {
-            AR_CUDA(cudaFuncSetAttribute(k_seed3, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s3.smem));
-            k_seed3<<<sm_count(idx->device), S3_THREADS, s3.smem>>>(idx->fm, opt, d_off.as<int64_t>(), (int)n_reads, maxlen, d_scr.as<uint4>(), rows, so,
+            const int nt = idx->opt_seed3_threads;
+            auto kfn = nt == 512 ? k_seed3<512> : nt == 1024 ? k_seed3<1024> : k_seed3<768>;
+            AR_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s3.smem));
+            kfn<<<sm_count(idx->device), nt, s3.smem>>>(idx->fm, opt, d_off.as<int64_t>(), (int)n_reads, maxlen, d_scr.as<uint4>(), rows, so,
                                     d_next.as<unsigned int>(), d_cnt.as<Counters>(), idx->opt_seed_kmer, s3.ns, d_qpk, qstride, s3.nwq, seed_direct);
         } else {
         AR_CUDA(cudaFuncSetAttribute(k_seed2<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)seed_smem));

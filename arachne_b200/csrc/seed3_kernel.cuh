@@ -18,16 +18,17 @@
 namespace arachne {
 
 enum { Q_SETUP = 0, Q_WIN, Q_OCCF, Q_OCCB, Q_TAB, Q_SA, Q_TXT, Q_N, Q_DEAD = 100 };
-constexpr int S3_THREADS = 512, S3_LH = 8, S3_WORDS = 16;
+constexpr int S3_LH = 8, S3_WORDS = 16;
+constexpr unsigned S3_RING = 1024;  // slots per queue ring (power of two, >= states per block)
 
 struct S3Plan { int ns, nwq; size_t smem; };
 inline S3Plan seed3_plan(int maxlen) {
     S3Plan p;
     p.nwq = (maxlen > 0 ? (maxlen - 1) / 32 : 0) + 2;
-    const int per_state = S3_WORDS * 4 + p.nwq * 12 + S3_LH * 16 + Q_N * 2;
-    p.ns = ((227 * 1024 - 1024) / per_state) / 32 * 32;
-    if (p.ns > 4096) p.ns = 4096;
-    p.smem = (size_t)p.ns * per_state + 256;
+    const int per_state = S3_WORDS * 4 + p.nwq * 12 + S3_LH * 16;
+    p.ns = ((227 * 1024 - 1024 - (int)(Q_N * S3_RING * 2)) / per_state) / 32 * 32;
+    if (p.ns > (int)S3_RING) p.ns = (int)S3_RING;
+    p.smem = (size_t)p.ns * per_state + Q_N * S3_RING * 2 + 256;
     return p;
 }
 
@@ -36,7 +37,8 @@ struct S3 {  // a state in registers
     int r, min_intv, phase, fresh, len, x, ret, i, n, lo, hi, j, ncur, last_start, n_rec, rec_i, emit;
 };
 
-__global__ void __launch_bounds__(S3_THREADS, 1) k_seed3(FMIndex fm, MemOpt opt, const int64_t* __restrict__ off, int n_reads, int maxlen, uint4* lists,
+template <int NT>
+__global__ void __launch_bounds__(NT, 1) k_seed3(FMIndex fm, MemOpt opt, const int64_t* __restrict__ off, int n_reads, int maxlen, uint4* lists,
                                                          int rows, SeedOut out, unsigned int* next, Counters* cnt, int use_kmer, int ns,
                                                          const ulonglong2* __restrict__ qpk, int qstride, int nwq, int use_direct) {
     extern __shared__ uint4 s3_smem[];
@@ -44,17 +46,17 @@ __global__ void __launch_bounds__(S3_THREADS, 1) k_seed3(FMIndex fm, MemOpt opt,
     uint64_t* qv = reinterpret_cast<uint64_t*>(sl + (size_t)S3_LH * ns);   // [nwq][ns]
     uint32_t* stw = reinterpret_cast<uint32_t*>(qv + (size_t)nwq * ns);    // [S3_WORDS][ns]
     uint32_t* qm = stw + (size_t)S3_WORDS * ns;                            // [nwq][ns]
-    unsigned short* qslot = reinterpret_cast<unsigned short*>(qm + (size_t)nwq * ns);  // [Q_N][ns]: state id + 1, 0 = not written yet
+    unsigned short* qslot = reinterpret_cast<unsigned short*>(qm + (size_t)nwq * ns);  // [Q_N][S3_RING]: state id + 1, 0 = not written yet
     __shared__ unsigned q_head[Q_N], q_tail[Q_N];
     __shared__ unsigned n_dead;
     const unsigned lane = threadIdx.x & 31u;
     const size_t T = (size_t)gridDim.x * ns;
-    for (int k = threadIdx.x; k < Q_N * ns; k += blockDim.x) qslot[k] = 0;
+    for (int k = threadIdx.x; k < (int)(Q_N * S3_RING); k += blockDim.x) qslot[k] = 0;
     if (threadIdx.x < Q_N) { q_head[threadIdx.x] = 0; q_tail[threadIdx.x] = threadIdx.x == Q_SETUP ? (unsigned)ns : 0u; }
     if (threadIdx.x == 0) n_dead = 0;
     __syncthreads();
     for (int k = threadIdx.x; k < ns; k += blockDim.x) {  // every state starts idle, queued for SETUP
-        qslot[Q_SETUP * ns + k] = (unsigned short)(k + 1);
+        qslot[Q_SETUP * S3_RING + k] = (unsigned short)(k + 1);
         stw[9 * ns + k] = (uint32_t)SP_IDLE << 8;
     }
     __syncthreads();
@@ -71,32 +73,32 @@ __global__ void __launch_bounds__(S3_THREADS, 1) k_seed3(FMIndex fm, MemOpt opt,
     for (;;) {
         // ------------------------------------------------------------------ pick a kind and pop up to 32 of its states
         int K = -1; unsigned base = 0, take = 0;
-        if (lane == 0) {
-            for (;;) {
-                int bestk = -1; unsigned besta = 0;
-                for (int k = 0; k < Q_N; ++k) {
-                    const unsigned a = atomicAdd(&q_tail[k], 0u) - atomicAdd(&q_head[k], 0u);
-                    if (a > besta && a <= (unsigned)ns) { besta = a; bestk = k; }
-                    if (a >= 32u && a <= (unsigned)ns) { bestk = k; besta = a; if (k != Q_SETUP) break; }  // a full batch of real work beats bookkeeping
-                }
-                if (bestk < 0) {
-                    if (atomicAdd(&n_dead, 0u) >= (unsigned)ns) break;
-                    __nanosleep(200);
-                    continue;
-                }
-                const unsigned h = atomicAdd(&q_head[bestk], 0u), t = atomicAdd(&q_tail[bestk], 0u);
-                const unsigned a = t - h;
-                if (a == 0 || a > (unsigned)ns) continue;
-                const unsigned want = a < 32u ? a : 32u;
-                if (atomicCAS(&q_head[bestk], h, h + want) == h) { K = bestk; base = h; take = want; break; }
+        for (;;) {
+            // lanes 0..Q_N-1 look at one queue each; a full batch of real work beats bookkeeping, otherwise the fullest queue
+            unsigned a = 0, h = 0;
+            if (lane < Q_N) { h = *(volatile unsigned*)&q_head[lane]; a = *(volatile unsigned*)&q_tail[lane] - h; if (a > (unsigned)ns) a = 0; }
+            const unsigned full = __ballot_sync(0xffffffffu, a >= 32u) & ~1u;  // bit 0 = SETUP
+            const unsigned score = a >= 32u && lane != Q_SETUP ? 0x40000000u + a : a;
+            const unsigned best = __reduce_max_sync(0xffffffffu, score);
+            (void)full;
+            if (best == 0) {
+                if (*(volatile unsigned*)&n_dead >= (unsigned)ns) break;
+                __nanosleep(100);
+                continue;
             }
+            const int bk = __ffs(__ballot_sync(0xffffffffu, score == best)) - 1;
+            const unsigned ba = __shfl_sync(0xffffffffu, a, bk), bh = __shfl_sync(0xffffffffu, h, bk);
+            const unsigned want = ba < 32u ? ba : 32u;
+            unsigned ok = 0;
+            if (lane == 0) ok = atomicCAS(&q_head[bk], bh, bh + want) == bh;
+            ok = __shfl_sync(0xffffffffu, ok, 0);
+            if (ok) { K = bk; base = bh; take = want; break; }
         }
-        K = __shfl_sync(0xffffffffu, K, 0); base = __shfl_sync(0xffffffffu, base, 0); take = __shfl_sync(0xffffffffu, take, 0);
         if (K < 0) break;
         const bool act = lane < take;
         int sid = 0;
         if (act) {
-            volatile unsigned short* slot = qslot + (size_t)K * ns + (base + lane) % (unsigned)ns;
+            volatile unsigned short* slot = qslot + (unsigned)K * S3_RING + ((base + lane) & (S3_RING - 1u));
             unsigned v;
             while ((v = *slot) == 0) {}
             *slot = 0;
@@ -123,15 +125,15 @@ __global__ void __launch_bounds__(S3_THREADS, 1) k_seed3(FMIndex fm, MemOpt opt,
         uint4* list = lists + gsid;                                // entry e >= S3_LH at list[e * T]
         uint4* recs = lists + (size_t)(rows >> 1) * T + gsid;      // re-seed records in the upper half
         uint4* slh = sl + sid;
-        auto lput = [&](int e, uint4 v) { if (e < S3_LH) slh[(size_t)e * ns] = v; else list[(size_t)e * T] = v; };
-        auto lget = [&](int e) -> uint4 { return e < S3_LH ? slh[(size_t)e * ns] : list[(size_t)e * T]; };
+        auto lput = [&](int e, uint4 v) { if (e < S3_LH) slh[(unsigned)e * (unsigned)ns] = v; else list[(size_t)e * T] = v; };
+        auto lget = [&](int e) -> uint4 { return e < S3_LH ? slh[(unsigned)e * (unsigned)ns] : list[(size_t)e * T]; };
         const uint64_t* qvs = qv + sid; const uint32_t* qms = qm + sid;
         auto qb = [&](int p) -> int {
             const int wd = p >> 5, sft = p & 31;
-            return ((qms[(size_t)wd * ns] >> (31 - sft)) & 1u) ? 4 : (int)((qvs[(size_t)wd * ns] >> (62 - 2 * sft)) & 3);
+            return ((qms[(unsigned)wd * (unsigned)ns] >> (31 - sft)) & 1u) ? 4 : (int)((qvs[(unsigned)wd * (unsigned)ns] >> (62 - 2 * sft)) & 3);
         };
-        auto qwin = [&](int p) -> uint64_t { const int wd = p >> 5; return fsh64(qvs[(size_t)wd * ns], qvs[(size_t)(wd + 1) * ns], (p & 31) * 2); };
-        auto mwin = [&](int p) -> uint32_t { const int wd = p >> 5; return __funnelshift_l(qms[(size_t)(wd + 1) * ns], qms[(size_t)wd * ns], p & 31); };
+        auto qwin = [&](int p) -> uint64_t { const int wd = p >> 5; return fsh64(qvs[(unsigned)wd * (unsigned)ns], qvs[(unsigned)(wd + 1) * (unsigned)ns], (p & 31) * 2); };
+        auto mwin = [&](int p) -> uint32_t { const int wd = p >> 5; return __funnelshift_l(qms[(unsigned)(wd + 1) * (unsigned)ns], qms[(unsigned)wd * (unsigned)ns], p & 31); };
         auto stat = [&](unsigned calls, unsigned blocks) { st_calls += calls; st_blocks += blocks; };
         auto emit = [&](uint64_t e0, uint64_t e1, uint64_t e2, int start, int end, bool filter) {
             const int slen = end - start;
@@ -279,7 +281,7 @@ __global__ void __launch_bounds__(S3_THREADS, 1) k_seed3(FMIndex fm, MemOpt opt,
                 m = m < kf ? m : kf;
                 const uint32_t km = (uint32_t)(qwin(s.x) >> (64 - 2 * m));
                 const uint4* all = reinterpret_cast<const uint4*>(fm.kmer_all);
-                for (int L = 1; L <= m; ++L) cp_async16(&slh[(size_t)(L - 1) * ns], all + ((1ull << (2 * L)) - 4) / 3 + (km >> (2 * (m - L))));
+                for (int L = 1; L <= m; ++L) cp_async16(&slh[(unsigned)(L - 1) * (unsigned)ns], all + klev(L) + (km >> (2 * (m - L))));
             }
             cp_async_wait_all();
             __syncwarp();
@@ -290,7 +292,7 @@ __global__ void __launch_bounds__(S3_THREADS, 1) k_seed3(FMIndex fm, MemOpt opt,
                 int L = 1;
                 for (; L < m; ++L) {
                     uint64_t a0, a1, a2;
-                    pk_unpack(slh[(size_t)L * ns], a0, a1, a2, spare);
+                    pk_unpack(slh[(unsigned)L * (unsigned)ns], a0, a1, a2, spare);
                     if (a2 != s.kx2) {
                         lput(s.n++, pk_pack(s.kx0, s.kx1, s.kx2, (unsigned)(s.x + L)));
                         if (a2 < (uint64_t)s.min_intv) { stop = true; break; }
@@ -381,7 +383,7 @@ __global__ void __launch_bounds__(S3_THREADS, 1) k_seed3(FMIndex fm, MemOpt opt,
                 praw = lget(s.j);
                 const int L = (int)(praw.w >> 24) - s.i;
                 const uint64_t code = qwin(s.i) >> (64 - 2 * L);
-                const uint4* tp = reinterpret_cast<const uint4*>(fm.kmer_all) + ((1ull << (2 * L)) - 4) / 3 + code;
+                const uint4* tp = reinterpret_cast<const uint4*>(fm.kmer_all) + klev(L) + code;
                 stat(1u, 2u);
                 asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(R[0]), "=r"(R[1]), "=r"(R[2]), "=r"(R[3]) : "l"(tp));
             }
@@ -466,15 +468,16 @@ __global__ void __launch_bounds__(S3_THREADS, 1) k_seed3(FMIndex fm, MemOpt opt,
         }
         __threadfence_block();
         if (!act) nk = -1;
-        for (int k = 0; k < Q_N; ++k) {
-            const unsigned m = __ballot_sync(0xffffffffu, nk == k);
-            if (!m) continue;
+        {
+            const unsigned grp = __match_any_sync(0xffffffffu, nk);   // the lanes that go to the same queue
+            const int leader = __ffs(grp) - 1;
+            const bool queued = nk >= 0 && nk < Q_N;
             unsigned b = 0;
-            if (lane == (unsigned)(__ffs(m) - 1)) b = atomicAdd(&q_tail[k], (unsigned)__popc(m));
-            b = __shfl_sync(0xffffffffu, b, __ffs(m) - 1);
-            if (nk == k) {
-                volatile unsigned short* slot = qslot + (size_t)k * ns + (b + __popc(m & ((1u << lane) - 1u))) % (unsigned)ns;
-                while (*slot != 0) {}  // (a slot is free again once its previous occupant was popped: at most ns states exist)
+            if (queued && (int)lane == leader) b = atomicAdd(&q_tail[nk], (unsigned)__popc(grp));
+            b = __shfl_sync(0xffffffffu, b, leader);
+            if (queued) {
+                volatile unsigned short* slot = qslot + (unsigned)nk * S3_RING + ((b + __popc(grp & ((1u << lane) - 1u))) & (S3_RING - 1u));
+                while (*slot != 0) {}  // (a slot is free again once its previous occupant was popped: at most ns <= S3_RING states exist)
                 *slot = (unsigned short)(sid + 1);
             }
         }

@@ -57,6 +57,9 @@ __device__ __forceinline__ void ld_sector(uint32_t* o, const void* p) {  // one 
 // bits [s, s + 64) of the 128-bit string a.b (s even, 0..62)
 __device__ __forceinline__ uint64_t fsh64(uint64_t a, uint64_t b, int s) { return (a << s) | ((b >> 1) >> (63 - s)); }
 
+// first entry of table level L in FMIndex::kmer_all: (4^L - 4) / 3 = 0b0101..01 (L - 1 pairs) << 2, without the 64-bit division
+__device__ __forceinline__ uint32_t klev(int L) { return (0x55555555u & ((1u << (2 * L - 2)) - 1u)) << 2; }
+
 enum { SP_IDLE = 0, SP_P1_SCAN, SP_FWD, SP_BWD, SP_P2_NEXT, SP_P3_SCAN, SP_P3, SP_DONE, SP_FSA, SP_FTXT, SP_FISA, SP_FTAB };
 
 // Reads as 2-bit words for the direct extension (below): per read `stride` pairs (bases, mask), 32 bases per u64 with base p
@@ -278,7 +281,7 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) k_seed2(FMIndex fm, MemOpt op
                     if (m >= 2) {
                         const uint32_t km = (uint32_t)(qwin(x) >> (64 - 2 * m));
                         const uint4* all = reinterpret_cast<const uint4*>(fm.kmer_all);
-                        for (int L = 1; L <= m; ++L) cp_async16(&sl[(L - 1) * 256], all + ((1ull << (2 * L)) - 4) / 3 + (km >> (2 * (m - L))));
+                        for (int L = 1; L <= m; ++L) cp_async16(&sl[(L - 1) * 256], all + klev(L) + (km >> (2 * (m - L))));
                         // the copies land while the other lanes' loads of this trip are in flight; replayed in POST
                         // waiting here costs the warp one table round trip; handing the window to the next trip (SP_FTAB, use_kmer
                         // bit 2) costs every forward pass a trip of its own and measured slower (57-60 vs 55 ms per 1 M pairs)
@@ -313,7 +316,7 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) k_seed2(FMIndex fm, MemOpt op
                 const int L = (int)(praw.w >> 24) - i;  // length of the extended match q[i, pend)
                 if (kmer_bwd && L <= kmer_k) {
                     const uint64_t code = qwin(i) >> (64 - 2 * L);
-                    tabp = (uint64_t)(reinterpret_cast<const uint4*>(fm.kmer_all) + ((1ull << (2 * L)) - 4) / 3 + code);
+                    tabp = (uint64_t)(reinterpret_cast<const uint4*>(fm.kmer_all) + klev(L) + code);
                     need = 4;
                 } else { need = 1; c = b; }
             }
