@@ -176,7 +176,7 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
         }
         AR_TRY(cudaGetLastError());
         AR_TRY(cudaMemcpyAsync(&hc, W.d_cnt.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
-        AR_TRY(cudaStreamSynchronize(st));
+        AR_TRY(W.sync(st));
         if (hc.err == 0) break;
         if (hc.err == ARACHNE_ERR_ARG) { set_error("read %d is longer than the stated max_read_len %d", hc.err_read, maxlen); return fail(ARACHNE_ERR_ARG); }
         if (attempt >= 3) { set_error("seeding: more than %d intervals at read %d", intv_cap, hc.err_read); return fail(ARACHNE_ERR_OVERFLOW); }
@@ -194,7 +194,7 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
     nl += 2;  // cub scan = init + scan kernels
     AR_TRY(cub::DeviceScan::ExclusiveSum(W.d_tmp.p, tmp_bytes, W.d_nsa.as<unsigned int>(), W.d_sa_off.as<unsigned long long>(), (int)n_reads + 1, st));
     AR_TRY(cudaMemcpyAsync(&hs[0], W.d_sa_off.as<unsigned long long>() + n_reads, 8, cudaMemcpyDeviceToHost, st));
-    AR_TRY(cudaStreamSynchronize(st));
+    AR_TRY(W.sync(st));
     const unsigned long long total_sa = hs[0];
     const size_t tsa = (size_t)total_sa + 8;
     AR_ALLOC(W.d_rows, tsa * 8);
@@ -276,7 +276,7 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
             }
             AR_TRY(cudaGetLastError());
             AR_TRY(cudaMemcpyAsync(&hs[5], &XB.ctl->n_next, 4, cudaMemcpyDeviceToHost, st));
-            AR_TRY(cudaStreamSynchronize(st));
+            AR_TRY(W.sync(st));
             if ((unsigned)hs[5] == 0) break;
             if (round > 4096) { set_error("extension rounds do not terminate"); return fail(ARACHNE_ERR_OVERFLOW); }
         }
@@ -297,7 +297,7 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
         AR_ALLOC(W.d_blist, (size_t)ext_blocks * EXT_WARPS * bcap * 8);
         unsigned long long resc_cap = (unsigned long long)n_reads * (getenv("ARACHNE_RESC_MULT") ? atoi(getenv("ARACHNE_RESC_MULT")) : 4) + 4096;
         AR_TRY(cudaMemcpyAsync(&hc, W.d_cnt.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
-        AR_TRY(cudaStreamSynchronize(st));
+        AR_TRY(W.sync(st));
         if (hc.err != 0) { set_error("internal scratch overflow (code %d) at read %d", hc.err, hc.err_read); return fail(ARACHNE_ERR_OVERFLOW); }
         AR_ALLOC(W.d_nregs_bak, (n_reads + 1) * 4);
         AR_TRY(cudaMemcpyAsync(W.d_nregs_bak.p, W.d_nregs.p, (n_reads + 1) * 4, cudaMemcpyDeviceToDevice, st));
@@ -312,7 +312,7 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
                                                             W.d_misc.as<unsigned int>(), W.d_cnt.as<Counters>());
             AR_TRY(cudaGetLastError());
             AR_TRY(cudaMemcpyAsync(&hc, W.d_cnt.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
-            AR_TRY(cudaStreamSynchronize(st));
+            AR_TRY(W.sync(st));
             if (hc.err == 0) break;
             if (hc.err != -100 || attempt >= 4) { set_error("rescue: scratch overflow (code %d) at pair %d", hc.err, hc.err_read); return fail(ARACHNE_ERR_OVERFLOW); }
             // the rescue arena was too small: regions in place are untouched (copy-on-write), so the stage can simply be re-run
@@ -331,7 +331,7 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
     AR_TRY(cub::DeviceScan::ExclusiveSum(W.d_tmp.p, tmp_bytes, W.d_nregs.as<int>(), W.d_reg_off.as<unsigned long long>(), (int)n_reads + 1, st));
     AR_TRY(cudaMemcpyAsync(&hs[1], W.d_reg_off.as<unsigned long long>() + n_reads, 8, cudaMemcpyDeviceToHost, st));
     AR_TRY(cudaMemcpyAsync(&hc, W.d_cnt.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
-    AR_TRY(cudaStreamSynchronize(st));
+    AR_TRY(W.sync(st));
     const unsigned long long total_regs = hs[1];
     if (hc.err != 0) { set_error("internal scratch overflow (code %d) at read %d", hc.err, hc.err_read); return fail(ARACHNE_ERR_OVERFLOW); }
     AR_ALLOC(W.d_out, (total_regs + 1) * sizeof(AlnReg));
@@ -411,7 +411,7 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
             AR_TRY(cudaGetLastError());
             AR_TRY(cudaMemcpyAsync(&hc, W.d_cnt.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
             AR_TRY(cudaMemcpyAsync(&hs[2], W.d_misc.as<unsigned long long>() + 1, 16, cudaMemcpyDeviceToHost, st));
-            AR_TRY(cudaStreamSynchronize(st));
+            AR_TRY(W.sync(st));
             if (hc.err == 0) break;
             if (hc.err != -101 || attempt >= 4) { set_error("cigar: scratch overflow (code %d) at read %d", hc.err, hc.err_read); return fail(ARACHNE_ERR_OVERFLOW); }
             cig_cap *= 4; mm_cap *= 4;
@@ -433,7 +433,7 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
 #include "place_host.inl"
     }
     if (!(stages & ARACHNE_STAGE_PLACE)) { cudaEventRecord(ev[8], st); cudaEventRecord(ev[9], st); }
-    AR_TRY(cudaStreamSynchronize(st));
+    AR_TRY(W.sync(st));
 
     out->n_regs = (int64_t)total_regs;
     if (!out_dev) { out->reg_off = priv->reg_off.as<int64_t>(); out->regs = priv->regs.as<arachne_alnreg_t>(); }

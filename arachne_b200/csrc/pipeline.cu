@@ -411,6 +411,13 @@ struct Workspace {
         d_first, d_keys_a, d_keys_b, d_vals_a, d_vals_b, d_seg_off, d_mol, d_list2, d_list3, d_zband, d_attach, d_rec_i, d_rec_d, d_rec_cnt, d_recs;
     cudaStream_t own_stream = nullptr;
     cudaEvent_t ev[12] = {};
+    cudaEvent_t ev_block = nullptr;  // ARACHNE_BLOCKING_SYNC=1: host waits sleep on this event instead of spinning in cudaStreamSynchronize
+    // (one spinning core per batch in flight is fine on an idle host; with 8 ranks x 2 batch threads on 16 cores it is not)
+    cudaError_t sync(cudaStream_t st) {
+        if (!ev_block) return cudaStreamSynchronize(st);
+        cudaError_t e = cudaEventRecord(ev_block, st);
+        return e != cudaSuccess ? e : cudaEventSynchronize(ev_block);
+    }
     Counters* h_cnt = nullptr;              // pinned
     unsigned long long* h_scalars = nullptr;  // pinned, 8 slots
     std::vector<DevBuf*> all() {
@@ -426,11 +433,14 @@ struct Workspace {
         for (auto& e : ev) if (cudaEventCreate(&e) != cudaSuccess) return -1;
         if (cudaMallocHost((void**)&h_cnt, sizeof(Counters)) != cudaSuccess) return -1;
         if (cudaMallocHost((void**)&h_scalars, 64) != cudaSuccess) return -1;
+        if (getenv("ARACHNE_BLOCKING_SYNC") && atoi(getenv("ARACHNE_BLOCKING_SYNC")) != 0 &&
+            cudaEventCreateWithFlags(&ev_block, cudaEventBlockingSync | cudaEventDisableTiming) != cudaSuccess) return -1;
         return 0;
     }
     void destroy() {
         for (auto* b : all()) b->release();
         for (auto& e : ev) if (e) cudaEventDestroy(e);
+        if (ev_block) cudaEventDestroy(ev_block);
         if (own_stream) cudaStreamDestroy(own_stream);
         if (h_cnt) cudaFreeHost(h_cnt);
         if (h_scalars) cudaFreeHost(h_scalars);

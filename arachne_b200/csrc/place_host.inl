@@ -21,7 +21,7 @@
     }
     h_rfa.assign((size_t)n_bc, 0);
     if (in->run_rfa && in->n_barcodes > 0) {
-        if (in_dev) { AR_TRY(cudaMemcpyAsync(h_rfa.data(), in->run_rfa, (size_t)n_bc, cudaMemcpyDeviceToHost, st)); AR_TRY(cudaStreamSynchronize(st)); d_rfa = in->run_rfa; }
+        if (in_dev) { AR_TRY(cudaMemcpyAsync(h_rfa.data(), in->run_rfa, (size_t)n_bc, cudaMemcpyDeviceToHost, st)); AR_TRY(W.sync(st)); d_rfa = in->run_rfa; }
         else {
             memcpy(h_rfa.data(), in->run_rfa, (size_t)n_bc);
             AR_ALLOC(W.d_run_rfa, (size_t)n_bc + 8);
@@ -62,7 +62,7 @@
     nl += 2;
     AR_TRY(cub::DeviceScan::ExclusiveSum(W.d_tmp.p, tb, W.d_pl_cnt.as<unsigned long long>(), W.d_pl_scan.as<unsigned long long>(), (int)n_reads + 1, st));
     AR_TRY(cudaMemcpyAsync(&hs[4], W.d_pl_scan.as<unsigned long long>() + n_reads, 8, cudaMemcpyDeviceToHost, st));
-    AR_TRY(cudaStreamSynchronize(st));
+    AR_TRY(W.sync(st));
     const long n_cands = (long)(hs[4] & 0xffffffffull);
     AR_ALLOC(W.d_cands, (size_t)(n_cands + 1) * sizeof(Cand));
     AR_ALLOC(W.d_hot, (size_t)(n_cands + 1) * sizeof(Hot));
@@ -85,7 +85,7 @@
         k_place_tag<<<sms * 4, 128, 0, st>>>(PA, (int)n_pairs, W.d_slow.as<uint64_t>(), slow_cap, W.d_misc.as<unsigned>());
         AR_TRY(cudaGetLastError());
         AR_TRY(cudaMemcpyAsync(&hc, W.d_cnt.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
-        AR_TRY(cudaStreamSynchronize(st));
+        AR_TRY(W.sync(st));
         if (hc.err == 0) break;
         if (hc.err != -102 || attempt >= 3) { set_error("placement: scratch overflow (code %d) at read %d", hc.err, hc.err_read); return fail(ARACHNE_ERR_OVERFLOW); }
         slow_cap *= 16;  // pairs with very many candidate combinations: the kernel is idempotent, re-run it with a larger pool
@@ -202,7 +202,7 @@
         AR_TRY(cudaGetLastError());
         ++nl;
         AR_TRY(cudaMemcpyAsync(&hs[6], RA2.rec_off + n_reads, 8, cudaMemcpyDeviceToHost, st));
-        AR_TRY(cudaStreamSynchronize(st));
+        AR_TRY(W.sync(st));
         out->n_records = (int64_t)hs[6];
         if (!out_dev) {
             AR_PIN(priv->rec_off, (size_t)(n_reads + 1) * 8); AR_PIN(priv->recs, (size_t)(out->n_records + 1) * sizeof(Record));

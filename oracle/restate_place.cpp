@@ -287,6 +287,127 @@ void walk_alignment(const orc_ref_t* ref, int l_query, const uint8_t* readSeq, i
     w->matches = matches; w->mismatches = mismatches; w->indels = indels; w->soft_clipped = soft_clipping; w->soft_clipped_length = soft_clipping_length;
 }
 
+// ------------------------------------------------------------------------------------------------ sort.Sort as Go 1.19+ implements it
+// Pattern-defeating quicksort of package sort (zsortinterface.go: pdqsort, insertionSort, heapSort, partition, partitionEqual,
+// partialInsertionSort, breakPatterns, choosePivot, order2, median, medianAdjacent, reverseRange), restated from the published algorithm.
+// Less(i, j) = data[i].pos < data[j].pos (ByPosition, aligner.go:203-206).  Not executable-pinned: there is no Go toolchain here.
+int g_tie_mode = 0;
+namespace gosort {
+typedef std::vector<Alignment*> V;
+inline bool less(const V& d, int i, int j) { return d[i]->pos < d[j]->pos; }
+inline void swp(V& d, int i, int j) { std::swap(d[i], d[j]); }
+void insertionSort(V& d, int a, int b) { for (int i = a + 1; i < b; ++i) for (int j = i; j > a && less(d, j, j - 1); --j) swp(d, j, j - 1); }
+void siftDown(V& d, int lo, int hi, int first) {
+    int root = lo;
+    for (;;) {
+        int child = 2 * root + 1;
+        if (child >= hi) return;
+        if (child + 1 < hi && less(d, first + child, first + child + 1)) ++child;
+        if (!less(d, first + root, first + child)) return;
+        swp(d, first + root, first + child);
+        root = child;
+    }
+}
+void heapSort(V& d, int a, int b) {
+    int first = a, lo = 0, hi = b - a;
+    for (int i = (hi - 1) / 2; i >= 0; --i) siftDown(d, i, hi, first);
+    for (int i = hi - 1; i >= 0; --i) { swp(d, first, first + i); siftDown(d, lo, i, first); }
+}
+int partition(V& d, int a, int b, int pivot, bool* already) {
+    swp(d, a, pivot);
+    int i = a + 1, j = b - 1;
+    while (i <= j && less(d, i, a)) ++i;
+    while (i <= j && !less(d, j, a)) --j;
+    if (i > j) { swp(d, j, a); *already = true; return j; }
+    swp(d, i, j); ++i; --j;
+    for (;;) {
+        while (i <= j && less(d, i, a)) ++i;
+        while (i <= j && !less(d, j, a)) --j;
+        if (i > j) break;
+        swp(d, i, j); ++i; --j;
+    }
+    swp(d, j, a);
+    *already = false;
+    return j;
+}
+int partitionEqual(V& d, int a, int b, int pivot) {
+    swp(d, a, pivot);
+    int i = a + 1, j = b - 1;
+    for (;;) {
+        while (i <= j && !less(d, a, i)) ++i;
+        while (i <= j && less(d, a, j)) --j;
+        if (i > j) break;
+        swp(d, i, j); ++i; --j;
+    }
+    return i;
+}
+bool partialInsertionSort(V& d, int a, int b) {
+    const int maxSteps = 5, shortestShifting = 50;
+    int i = a + 1;
+    for (int j = 0; j < maxSteps; ++j) {
+        while (i < b && !less(d, i, i - 1)) ++i;
+        if (i == b) return true;
+        if (b - a < shortestShifting) return false;
+        swp(d, i, i - 1);
+        if (i - a >= 2) for (int k = i - 1; k >= 1; --k) { if (!less(d, k, k - 1)) break; swp(d, k, k - 1); }
+        if (b - i >= 2) for (int k = i + 1; k < b; ++k) { if (!less(d, k, k - 1)) break; swp(d, k, k - 1); }
+    }
+    return false;
+}
+inline int bitsLen(unsigned x) { int n = 0; while (x) { ++n; x >>= 1; } return n; }
+void breakPatterns(V& d, int a, int b) {
+    int length = b - a;
+    if (length >= 8) {
+        uint64_t random = (uint64_t)length;
+        unsigned modulus = 1u << bitsLen((unsigned)length);
+        int idx = a + (length / 4) * 2 - 1;
+        for (int i = 0; i < 3; ++i) {
+            random ^= random << 13; random ^= random >> 7; random ^= random << 17;
+            int other = (int)((unsigned)random & (modulus - 1));
+            if (other >= length) other -= length;
+            swp(d, idx - 1 + i, a + other);
+        }
+    }
+}
+inline void order2(V& d, int& a, int& b, int* swaps) { if (less(d, b, a)) { ++*swaps; std::swap(a, b); } }
+inline int median(V& d, int a, int b, int c, int* swaps) { order2(d, a, b, swaps); order2(d, b, c, swaps); order2(d, a, b, swaps); return b; }
+inline int medianAdjacent(V& d, int a, int* swaps) { return median(d, a - 1, a, a + 1, swaps); }
+enum { unknownHint, increasingHint, decreasingHint };
+int choosePivot(V& d, int a, int b, int* hint) {
+    const int shortestNinther = 50, maxSwaps = 4 * 3;
+    int l = b - a, swaps = 0;
+    int i = a + l / 4 * 1, j = a + l / 4 * 2, k = a + l / 4 * 3;
+    if (l >= 8) {
+        if (l >= shortestNinther) { i = medianAdjacent(d, i, &swaps); j = medianAdjacent(d, j, &swaps); k = medianAdjacent(d, k, &swaps); }
+        j = median(d, i, j, k, &swaps);
+    }
+    if (swaps == 0) *hint = increasingHint; else if (swaps == maxSwaps) *hint = decreasingHint; else *hint = unknownHint;
+    return j;
+}
+void reverseRange(V& d, int a, int b) { int i = a, j = b - 1; while (i < j) { swp(d, i, j); ++i; --j; } }
+void pdqsort(V& d, int a, int b, int limit) {
+    const int maxInsertion = 12;
+    bool wasBalanced = true, wasPartitioned = true;
+    for (;;) {
+        int length = b - a;
+        if (length <= maxInsertion) { insertionSort(d, a, b); return; }
+        if (limit == 0) { heapSort(d, a, b); return; }
+        if (!wasBalanced) { breakPatterns(d, a, b); --limit; }
+        int hint, pivot = choosePivot(d, a, b, &hint);
+        if (hint == decreasingHint) { reverseRange(d, a, b); pivot = (b - 1) - (pivot - a); hint = increasingHint; }
+        if (wasBalanced && wasPartitioned && hint == increasingHint) { if (partialInsertionSort(d, a, b)) return; }
+        if (a > 0 && !less(d, a - 1, pivot)) { a = partitionEqual(d, a, b, pivot); continue; }
+        bool already;
+        int mid = partition(d, a, b, pivot, &already);
+        wasPartitioned = already;
+        int leftLen = mid - a, rightLen = b - mid, balanceThreshold = length / 8;
+        if (leftLen < rightLen) { wasBalanced = leftLen >= balanceThreshold; pdqsort(d, a, mid, limit); a = mid + 1; }
+        else { wasBalanced = rightLen >= balanceThreshold; pdqsort(d, mid + 1, b, limit); b = mid; }
+    }
+}
+void sort(V& d) { int n = (int)d.size(); pdqsort(d, 0, n, bitsLen((unsigned)n)); }
+}  // namespace gosort
+
 // ------------------------------------------------------------------------------------------------ tagBestAlignments (aligner.go:1397-1481)
 std::vector<std::vector<Alignment*>> tagBestAlignments(std::vector<std::vector<Alignment*>>& alignments, const int64_t* rand_seed) {
     std::vector<std::vector<Alignment*>> positions;
@@ -323,8 +444,16 @@ std::vector<std::vector<Alignment*>> tagBestAlignments(std::vector<std::vector<A
             }
         }
     }
-    // sort.Sort(ByPosition): pdqsort, unstable on equal pos -- UNPINNED; a stable order is used here
-    for (auto& p : positions) std::stable_sort(p.begin(), p.end(), [](const Alignment* a, const Alignment* b) { return a->pos < b->pos; });
+    // sort.Sort(ByPosition) (aligner.go:1477-1479): Go's pdqsort, unstable on equal pos -- UNPINNED against Go execution.  g_tie_mode picks
+    // what equal positions do here: 0 = keep insertion order (what the device does), 1 = reverse it, 2 = gosort::pdqsort below (a restatement of
+    // Go 1.24's sort.Sort from its published algorithm, deterministic: its only randomness is seeded by the slice length).
+    // tests/test_cpu_tier.py::test_place_tie_order_is_not_observable compares the three.
+    for (auto& p : positions) {
+        if (g_tie_mode == 2) { gosort::sort(p); continue; }
+        std::stable_sort(p.begin(), p.end(), [](const Alignment* a, const Alignment* b) { return a->pos < b->pos; });
+        if (g_tie_mode == 1)
+            for (size_t i = 0; i < p.size();) { size_t j = i; while (j < p.size() && p[j]->pos == p[i]->pos) ++j; std::reverse(p.begin() + i, p.begin() + j); i = j; }
+    }
     return positions;
 }
 
@@ -873,6 +1002,8 @@ static int place_impl(const orc_ref_t* ref, int64_t n_pairs, const uint8_t* seq,
     }
     return 0;
 }
+
+void orc_set_tie_mode(int mode) { g_tie_mode = mode; }
 
 int orc_place(const orc_ref_t* ref, int64_t n_pairs, const uint8_t* seq, const int64_t* off, int64_t n_bc, const int64_t* bc_off, const uint8_t* run_rfa,
               const int64_t* rand_seed, const int64_t* reg_off, const void* regs_, const int64_t* aln, const uint32_t* cigar, double improper_penalty,

@@ -86,6 +86,10 @@ int orc_place_records(const orc_ref_t *ref, int64_t n_pairs, const uint8_t *seq,
  * mm receives n ref loci then n read offsets; returns n */
 int orc_walk(const orc_ref_t *ref, int l_query, const uint8_t *query, const void *reg, const int64_t *aln8, const uint32_t *cigar, int *out5, int32_t *mm);
 
+/* how equal positions are ordered by the position-list sort (sort.Sort(ByPosition), aligner.go:1477-1479): 0 insertion order (default, = the device),
+ * 1 reversed, 2 a restatement of Go's pdqsort.  Test knob. */
+void orc_set_tie_mode(int mode);
+
 int64_t orc_name_seed(const char *name, int len);        /* int64(LittleEndian.Uint64(md5(name)[0:8])) */
 void orc_md5(const uint8_t *msg, int64_t len, uint8_t out[16]);
 void orc_gorand_float64(int64_t seed, int n, double *out); /* first n Float64() of rand.New(rand.NewSource(seed)) */

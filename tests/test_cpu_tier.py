@@ -362,3 +362,43 @@ def test_ingest_matches_reader_go(tmp_path, gz):
         assert 30000 in sizes and sizes.count(201) == 2 and any(not f for _, _, f in units)
     finally:
         I.close()
+
+
+# ---- rows a15-a20: does the order of equal positions in sort.Sort(ByPosition) (Go's unstable pdqsort, aligner.go:1477-1479) reach any output? ----
+def test_place_tie_order_is_not_observable(workdir):
+    """The device sorts the per-contig position lists stably; Go's pdqsort may order EQUAL positions differently once a list is longer than
+    12.  Run the placement oracle three ways -- ties in insertion order (= the device), ties reversed, and a restatement of Go's pdqsort -- on
+    barcodes whose lists are hundreds long with many equal positions (stLFR-style units on a repetitive reference, duplicated pairs), and
+    require identical outputs.  (Exact Go execution stays unpinned: no toolchain; this pins that the unpinned freedom changes nothing here.)"""
+    from oracle.refbwa import RefBwa, available
+    if not available():
+        pytest.skip("oracle/_ref not built")
+    fa, ctg, _ = util.make_dataset("rep600k", workdir)
+    R = RefBwa(); R.load(fa)
+    from arachne_b200 import simulate as S
+    rs = S.simulate_linked_reads(ctg, n_barcodes=3, seed=41, style="stlfr", dash_suffix=True, mol_per_bc=10.0, pairs_per_mol=20.0, sub=0.01)
+    # equal positions on purpose: copy every fifth pair onto its successor
+    seq = rs.seq.copy()
+    for p in range(0, rs.n_pairs - 1, 5):
+        a, b = rs.off[2 * p], rs.off[2 * p + 2]
+        if rs.off[2 * p + 4] - b == b - a:
+            seq[b:rs.off[2 * p + 4]] = seq[a:b]
+    ref = R.batch(seq, rs.off, rescue=True, cigar=True, threads=4)
+    P = util.PlaceOracle(fa)
+    P.O.orc_set_tie_mode.argtypes = [C.c_int]
+    seeds = np.array([P.name_seed(n) for n in rs.names], dtype=np.int64)
+    rfa = np.ones(len(rs.bc_off) - 1, np.uint8)
+    outs = []
+    try:
+        for mode in (0, 1, 2):
+            P.O.orc_set_tie_mode(mode)
+            oc, cands, lmp, recs = P.place_records(seq, rs.off, rs.bc_off, rfa, rfa, seeds, ref["reg_off"], ref["regs"], ref["aln"], ref["cigar"])
+            outs.append((oc.copy(), cands.copy(), lmp.copy(), recs.copy()))
+    finally:
+        P.O.orc_set_tie_mode(0)
+    pos = outs[0][1]["pos"][outs[0][1]["pos"] >= 0]
+    assert len(pos) - len(np.unique(pos)) > 50 and np.diff(rs.bc_off).max() > 100, "dataset has no long lists with equal positions"
+    for m in (1, 2):
+        assert np.array_equal(outs[0][0], outs[m][0])
+        assert outs[0][1].tobytes() == outs[m][1].tobytes(), "tie mode %d changes a candidate field" % m
+        assert np.array_equal(outs[0][2], outs[m][2]) and outs[0][3].tobytes() == outs[m][3].tobytes(), "tie mode %d changes a record" % m
