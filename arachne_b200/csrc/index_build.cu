@@ -270,3 +270,92 @@ extern "C" int arachne_index_build(const char* prefix_, int device, int64_t batc
     be.shutdown();
     return rc;
 }
+
+// ---------------------------------------------------------------------------------------------- pack step of `bwa index`
+// bns_fasta2bntseq(for_only = 1) + bns_dump (bwa/bntseq.c:229-328, 66-96): FASTA (plain or gzip) -> <prefix>.pac / .ann / .amb, byte for byte
+// what the reference leaves after `bwa index` -- including its replacement of every ambiguous base by lrand48() & 3 under srand48(11)
+// (bntseq.c:261,290-291; the 48-bit LCG is restated here, not taken from libc, so the files do not depend on the platform).  Records are read
+// with kseq.h's rules (bwa/kseq.h:176-215): name = text up to the first whitespace, comment = rest of the header line, sequence = every
+// following line without its line end until a line starts with '>' or '@'.  Host only.
+#include <zlib.h>
+extern "C" int arachne_index_pack(const char* fasta, const char* prefix_, int64_t* l_pac_out) {
+    using arachne::set_error;
+    if (!fasta || !prefix_) { set_error("arachne_index_pack: null argument"); return ARACHNE_ERR_ARG; }
+    gzFile f = gzopen(fasta, "rb");
+    if (!f) { set_error("cannot open %s", fasta); return ARACHNE_ERR_IO; }
+    gzbuffer(f, 1 << 20);
+    const std::string prefix(prefix_);
+    struct Ann { std::string name, anno; int64_t offset; int32_t len, n_ambs; };
+    struct Hole { int64_t offset; int32_t len; char amb; };
+    std::vector<Ann> anns; std::vector<Hole> holes; std::vector<uint8_t> pac;
+    int64_t l_pac = 0;
+    uint64_t rng = ((uint64_t)11 << 16) | 0x330e;  // srand48(11)
+    uint8_t nt4[256]; memset(nt4, 4, 256); nt4[(int)'-'] = 5;
+    for (int i = 0; i < 4; ++i) { nt4[(int)"ACGT"[i]] = (uint8_t)i; nt4[(int)"acgt"[i]] = (uint8_t)i; }
+    std::vector<char> buf(4 << 20);
+    std::string line; bool in_seq = false; int lasts = 0; bool eof = false;
+    auto put_base = [&](int ch) {
+        Ann& p = anns.back();
+        int c = nt4[(uint8_t)ch];
+        const int64_t i = p.len;
+        if (c >= 4) {
+            if (lasts == ch && !holes.empty()) ++holes.back().len;
+            else { holes.push_back({p.offset + i, 1, (char)ch}); ++p.n_ambs; }
+            rng = (0x5DEECE66Dull * rng + 0xB) & ((1ull << 48) - 1);  // lrand48()
+            c = (int)((rng >> 17) & 3);
+        }
+        lasts = ch;
+        if ((l_pac & 3) == 0) pac.push_back(0);
+        pac[(size_t)(l_pac >> 2)] |= (uint8_t)(c << ((~l_pac & 3) << 1));
+        ++l_pac; ++p.len;
+    };
+    auto handle_line = [&](std::string& ln) {  // one line without its '\n'
+        if (!ln.empty() && (ln[0] == '>' || ln[0] == '@')) {
+            if (ln.size() > 1 && ln.back() == '\r') ln.pop_back();
+            size_t e = 1; while (e < ln.size() && !isspace((unsigned char)ln[e])) ++e;
+            Ann a; a.name = ln.substr(1, e - 1);
+            a.anno = e < ln.size() ? ln.substr(e + 1) : std::string();
+            if (a.anno.empty()) a.anno = "(null)";
+            a.offset = anns.empty() ? 0 : anns.back().offset + anns.back().len; a.len = 0; a.n_ambs = 0;
+            anns.push_back(a); in_seq = true; lasts = 0;
+            return;
+        }
+        if (!in_seq || ln.empty()) return;
+        size_t n = ln.size();
+        if (n > 1 && ln[n - 1] == '\r') --n;  // KS_SEP_LINE strips one trailing '\r' (kseq.h:140)
+        for (size_t k = 0; k < n; ++k) put_base((unsigned char)ln[k]);
+    };
+    while (!eof) {
+        const int got = gzread(f, buf.data(), (unsigned)buf.size());
+        if (got < 0) { gzclose(f); set_error("read error in %s", fasta); return ARACHNE_ERR_IO; }
+        if (got == 0) { eof = true; break; }
+        const char* p = buf.data(); const char* end = p + got;
+        while (p < end) {
+            const char* nl = static_cast<const char*>(memchr(p, '\n', (size_t)(end - p)));
+            if (!nl) { line.append(p, (size_t)(end - p)); break; }
+            line.append(p, (size_t)(nl - p)); p = nl + 1;
+            handle_line(line); line.clear();
+        }
+    }
+    if (!line.empty()) handle_line(line);
+    gzclose(f);
+    if (anns.empty()) { set_error("%s holds no FASTA record", fasta); return ARACHNE_ERR_IO; }
+    FILE* fp = fopen((prefix + ".pac").c_str(), "wb");
+    if (!fp) { set_error("cannot write %s.pac", prefix.c_str()); return ARACHNE_ERR_IO; }
+    fwrite(pac.data(), 1, (size_t)((l_pac >> 2) + ((l_pac & 3) == 0 ? 0 : 1)), fp);
+    if (l_pac % 4 == 0) { const uint8_t z = 0; fwrite(&z, 1, 1, fp); }
+    const uint8_t ct = (uint8_t)(l_pac % 4); fwrite(&ct, 1, 1, fp);
+    fclose(fp);
+    fp = fopen((prefix + ".ann").c_str(), "w");
+    if (!fp) { set_error("cannot write %s.ann", prefix.c_str()); return ARACHNE_ERR_IO; }
+    fprintf(fp, "%lld %d %u\n", (long long)l_pac, (int)anns.size(), 11u);
+    for (const Ann& a : anns) { fprintf(fp, "%d %s", 0, a.name.c_str()); if (!a.anno.empty()) fprintf(fp, " %s\n", a.anno.c_str()); else fprintf(fp, "\n"); fprintf(fp, "%lld %d %d\n", (long long)a.offset, a.len, a.n_ambs); }
+    fclose(fp);
+    fp = fopen((prefix + ".amb").c_str(), "w");
+    if (!fp) { set_error("cannot write %s.amb", prefix.c_str()); return ARACHNE_ERR_IO; }
+    fprintf(fp, "%lld %d %u\n", (long long)l_pac, (int)anns.size(), (unsigned)holes.size());
+    for (const Hole& h : holes) fprintf(fp, "%lld %d %c\n", (long long)h.offset, h.len, h.amb);
+    fclose(fp);
+    if (l_pac_out) *l_pac_out = l_pac;
+    return ARACHNE_OK;
+}

@@ -266,6 +266,13 @@ class ArachneCuda:
         self._ck(self.lib.arachne_index_build(prefix.encode(), device, batch_cap, C.byref(info)))
         return {n: getattr(info, n) for n, _ in IndexBuildInfo._fields_}
 
+    def pack_fasta(self, fasta: str, prefix: str) -> int:
+        """FASTA -> <prefix>.pac/.ann/.amb as the reference's pack step writes them (bns_fasta2bntseq, bntseq.c:275-328). Host only."""
+        lp = C.c_int64(0)
+        self.lib.arachne_index_pack.argtypes = [C.c_char_p, C.c_char_p, C.POINTER(C.c_int64)]
+        self._ck(self.lib.arachne_index_pack(fasta.encode(), prefix.encode(), C.byref(lp)))
+        return lp.value
+
     # ---- index (GoBwaLoadReference, gobwa.go:128-147) ----
     def load_index(self, prefix: str, device: int = 0):
         self.close()

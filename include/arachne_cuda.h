@@ -257,6 +257,10 @@ typedef struct {
     double seconds_read, seconds_build, seconds_write;
 } arachne_index_build_info_t;
 int arachne_index_build(const char *prefix, int device, int64_t batch_cap, arachne_index_build_info_t *info);
+/* The pack step in front of it: bns_fasta2bntseq(for_only = 1) + bns_dump (bwa/bntseq.c:229-328,66-96).  FASTA (plain or gzip) ->
+ * <prefix>.pac / .ann / .amb byte-identical to what `bwa index` leaves, ambiguous bases replaced by lrand48() & 3 under srand48(11) as
+ * the reference does (bntseq.c:261,290-291).  Host only.  arachne_index_pack + arachne_index_build = `bwa index`. */
+int arachne_index_pack(const char *fasta, const char *prefix, int64_t *l_pac);
 
 /* Run this handle's batches on the caller's CUDA stream (a cudaStream_t; use != 0) or on the handle's own stream (use == 0,
  * the default), so that a caller can bracket batches with its own CUDA events. */

@@ -4,6 +4,7 @@ the thread-sequential device code, barcode sharding under gloo with world_size 2
 import ctypes as C
 import os
 import re
+import shutil
 import subprocess
 import sys
 
@@ -402,3 +403,45 @@ def test_place_tie_order_is_not_observable(workdir):
         assert np.array_equal(outs[0][0], outs[m][0])
         assert outs[0][1].tobytes() == outs[m][1].tobytes(), "tie mode %d changes a candidate field" % m
         assert np.array_equal(outs[0][2], outs[m][2]) and outs[0][3].tobytes() == outs[m][3].tobytes(), "tie mode %d changes a record" % m
+
+
+def test_pack_step_matches_bwa_index(tmp_path):
+    """arachne_index_pack against the reference's own `bwa index` pack step (bns_fasta2bntseq + bns_dump, compiled into oracle/_ref): .pac,
+    .ann and .amb byte for byte on a FASTA with N runs (the lrand48 replacement), IUPAC codes, lower case, comments, short and empty lines,
+    CRLF line ends, several contigs and lengths around the 4-base packing boundary."""
+    import gzip
+    from arachne_b200 import ArachneCuda
+    from oracle.refbwa import RefBwa, available
+    if not available():
+        pytest.skip("oracle/_ref not built")
+    g = np.random.default_rng(21)
+    for case in range(6):
+        recs = []
+        for c in range(int(g.integers(1, 6))):
+            L = int(g.integers(60, 4000)) + case
+            s = np.array(list("ACGT"))[g.integers(0, 4, L)]
+            for _ in range(int(g.integers(0, 5))):
+                a = int(g.integers(0, L - 5)); n = int(g.integers(1, 40))
+                s[a:a + n] = g.choice(list("NnRYM"))
+            low = g.random(L) < 0.2
+            s[low] = np.char.lower(s[low])
+            recs.append(("ctg%d_%d" % (case, c), ("a comment %d" % c) if c % 2 else "", "".join(s)))
+        eol = "\r\n" if case == 3 else "\n"
+        txt = ""
+        for name, com, s in recs:
+            txt += ">" + name + ((" " + com) if com else "") + eol
+            w = int(g.integers(20, 90))
+            for i in range(0, len(s), w):
+                txt += s[i:i + w] + eol
+                if i == 0 and case == 2:
+                    txt += eol  # an empty line inside a record
+        fa = str(tmp_path / ("c%d.fa" % case)) + (".gz" if case == 4 else "")
+        with (gzip.open(fa, "wt", newline="") if case == 4 else open(fa, "w", newline="")) as f:
+            f.write(txt)
+        ref_prefix = str(tmp_path / ("ref%d" % case)); shutil.copy(fa, ref_prefix)
+        RefBwa().build_index(ref_prefix)                      # the reference: FASTA at <prefix>, files next to it
+        mine = str(tmp_path / ("mine%d" % case))
+        l_pac = ArachneCuda().pack_fasta(fa, mine)
+        assert l_pac == sum(len(s) for _, _, s in recs)
+        for ext in ("pac", "ann", "amb"):
+            assert open(mine + "." + ext, "rb").read() == open(ref_prefix + "." + ext, "rb").read(), (case, ext)
