@@ -11,14 +11,24 @@ static Workspace* get_ws(arachne_index_t* idx, int slot) {
     return reinterpret_cast<Workspace*>(idx->ws[slot]);
 }
 
-// Take a free workspace slot: the first idle one; when all are busy, poll (a batch lasts ~100 ms, the poll 100 us).
-static std::unique_lock<std::mutex> take_ws(arachne_index_t* idx, int* slot) {
+// Take a free workspace slot: the first idle one; when all are busy, sleep until a batch hands its slot back.
+struct WsLease {
+    arachne_index_t* idx = nullptr; int slot = -1;
+    WsLease() = default;
+    WsLease(WsLease&& o) noexcept : idx(o.idx), slot(o.slot) { o.idx = nullptr; }
+    WsLease(const WsLease&) = delete;
+    ~WsLease() {
+        if (!idx) return;
+        { std::lock_guard<std::mutex> g(idx->ws_gate); idx->ws_busy[slot] = false; }
+        idx->ws_cv.notify_one();
+    }
+};
+static WsLease take_ws(arachne_index_t* idx, int* slot) {
+    std::unique_lock<std::mutex> g(idx->ws_gate);
     for (;;) {
-        for (int k = 0; k < arachne_index::N_WS; ++k) {
-            std::unique_lock<std::mutex> l(idx->ws_mu[k], std::try_to_lock);
-            if (l.owns_lock()) { *slot = k; return l; }
-        }
-        std::this_thread::sleep_for(std::chrono::microseconds(100));
+        for (int k = 0; k < arachne_index::N_WS; ++k)
+            if (!idx->ws_busy[k]) { idx->ws_busy[k] = true; *slot = k; WsLease l; l.idx = idx; l.slot = k; return l; }
+        idx->ws_cv.wait(g);
     }
 }
 
@@ -71,7 +81,7 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
     }
     if ((long)opt.a * maxlen > 8191) { set_error("a * read length = %ld exceeds the extension kernel's 13-bit score fields", (long)opt.a * maxlen); return ARACHNE_ERR_OPTS; }
     int ws_slot = 0;
-    std::unique_lock<std::mutex> guard = take_ws(idx, &ws_slot);
+    WsLease guard = take_ws(idx, &ws_slot);
     AR_CUDA(cudaSetDevice(idx->device));
     Workspace* wsp = get_ws(idx, ws_slot);
     if (!wsp) { set_error("cannot create the batch workspace (stream/events/pinned memory)"); return ARACHNE_ERR_CUDA; }
@@ -295,7 +305,7 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
     if (stages & ARACHNE_STAGE_RESCUE) {
         const int bcap = win_cap;  // one row-maximum entry per target row at most
         AR_ALLOC(W.d_blist, (size_t)ext_blocks * EXT_WARPS * bcap * 8);
-        unsigned long long resc_cap = (unsigned long long)n_reads * (getenv("ARACHNE_RESC_MULT") ? atoi(getenv("ARACHNE_RESC_MULT")) : 4) + 4096;
+        unsigned long long resc_cap = (unsigned long long)n_reads * (unsigned)idx->env_resc_mult + 4096;
         AR_TRY(cudaMemcpyAsync(&hc, W.d_cnt.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
         AR_TRY(W.sync(st));
         if (hc.err != 0) { set_error("internal scratch overflow (code %d) at read %d", hc.err, hc.err_read); return fail(ARACHNE_ERR_OVERFLOW); }
@@ -359,7 +369,7 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
         AR_ALLOC(W.d_alns, (total_regs + 1) * sizeof(AlnRec));
         unsigned long long cig_cap = total_regs * 4 + 4096, mm_cap = total_regs * 12 + 4096;
         // thread-per-region tiers (cigar_kernel.cuh); ARACHNE_CIGAR_TIERS=0 sends every region to the warp tier
-        const bool cigar_tiers = !(getenv("ARACHNE_CIGAR_TIERS") && atoi(getenv("ARACHNE_CIGAR_TIERS")) == 0);
+        const bool cigar_tiers = idx->env_cigar_tiers;
         const size_t band_smem = (size_t)BAND_RING * CIG_BLOCK * sizeof(int2);
         int band_per_sm = 1;
         if (cigar_tiers) {

@@ -9,6 +9,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
+#include <condition_variable>
 #include <thread>
 #include <chrono>
 #include "fmindex.cuh"
@@ -41,7 +42,8 @@ struct arachne_index {
     // shared state (options, stream choice, the pool of recycled pinned result sets).
     static constexpr int N_WS = 2;  // 3 in flight measured slower (persistent kernels of three batches oversubscribe the SMs)
     std::mutex mu;
-    std::mutex ws_mu[N_WS];
+    std::mutex ws_gate; std::condition_variable ws_cv; bool ws_busy[N_WS] = {};  // which batch workspace is leased (batch.inl::take_ws)
+    int env_resc_mult = 4; bool env_cigar_tiers = true;  // ARACHNE_RESC_MULT / ARACHNE_CIGAR_TIERS, read once at load
     void* ws[N_WS] = {};
     std::vector<void*> priv_pool;
     void* user_stream = nullptr;

@@ -460,6 +460,10 @@ int arachne_device_count(void) {
 int arachne_index_load(const char* prefix, int device, arachne_index_t** out) {
     const int rc = index_load(prefix, device, out);
     if (rc == ARACHNE_OK && getenv("ARACHNE_SEED_IMPL")) { const int v = atoi(getenv("ARACHNE_SEED_IMPL")); if (v == 2 || v == 3) (*out)->opt_seed_impl = v; }
+    if (rc == ARACHNE_OK) {  // environment knobs are read here, once, not inside the batch call
+        if (getenv("ARACHNE_RESC_MULT") && atoi(getenv("ARACHNE_RESC_MULT")) > 0) (*out)->env_resc_mult = atoi(getenv("ARACHNE_RESC_MULT"));
+        if (getenv("ARACHNE_CIGAR_TIERS") && atoi(getenv("ARACHNE_CIGAR_TIERS")) == 0) (*out)->env_cigar_tiers = false;
+    }
     if (rc == ARACHNE_OK && getenv("ARACHNE_SEED3_THREADS")) { const int v = atoi(getenv("ARACHNE_SEED3_THREADS")); if (v == 512 || v == 768 || v == 1024) (*out)->opt_seed3_threads = v; }
     return rc;
 }

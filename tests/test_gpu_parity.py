@@ -556,3 +556,24 @@ def test_records_parity(A, R, workdir, rfa):
     assert len(got) == len(exp)
     for i, (x, y) in enumerate(zip(got, exp)):
         assert x == y, (i, x, y)
+
+
+def test_determinism_two_runs(A, R, workdir):
+    """The same batch twice, and once more while a second host thread runs another batch on the handle's other workspace: every output
+    array byte-identical.  Stands in for racecheck, which the GPU pool refuses (profiles/r2a_sanitizer_unavailable.txt): the kernels that
+    write without atomics (interval halves, extension queues, copy-on-write rescue lists) would show up here as run-to-run differences."""
+    from concurrent.futures import ThreadPoolExecutor
+    fa, ctg, rs = util.make_dataset("rep600k", workdir, damaged=True)
+    A.load_index(fa)
+    seeds = np.array([A.name_seed(n) for n in rs.names], dtype=np.int64)
+    rfa = np.ones(len(rs.bc_off) - 1, np.uint8)
+    def run(_=0):
+        return A.align_batch(rs.seq, rs.off, rs.bc_off, stages=31, run_rfa=rfa, rand_seed=seeds)
+    a = run()
+    b = run()
+    with ThreadPoolExecutor(2) as ex:
+        c, d = list(ex.map(run, range(2)))
+    for other in (b, c, d):
+        for k in ("reg_off", "regs", "alns", "cigar", "mm", "cand_off", "cands", "lmp", "rec_off", "records"):
+            assert a[k].tobytes() == other[k].tobytes(), k
+    assert a["counters"]["n_ext_cells"] == b["counters"]["n_ext_cells"] and a["counters"]["n_occ_blocks"] == b["counters"]["n_occ_blocks"]
