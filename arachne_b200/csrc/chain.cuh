@@ -1,4 +1,6 @@
-// Seed chaining and chain filtering, thread-sequential per read.
+// Seed chaining and chain filtering, thread-sequential per read (k_chain runs one read per lane).  The DECISIONS are the reference's --
+// which chain a seed joins, where equal keys land in the B-tree, how ties sort -- because every one of them is observable in the
+// regions that come out; the code that takes them is written for this library.
 //   mem_chain        bwa/bwamem.c:251-315   (B-tree keyed by chain pos; kbtree.h semantics reproduced exactly,
 //                                            including where equal keys land, because that decides `lower`)
 //   test_and_merge   bwa/bwamem.c:190-211
@@ -10,31 +12,32 @@
 
 namespace arachne {
 
+// forward-strand coordinate of a forward-reverse coordinate, and which strand it was on (bns_depos, bntseq.h:86-89)
 AR_HD int64_t bns_depos(const RefView& r, int64_t pos, int* is_rev) {
-    return (*is_rev = (pos >= r.l_pac)) ? (r.l_pac << 1) - 1 - pos : pos;
+    *is_rev = pos >= r.l_pac;
+    return *is_rev ? 2 * r.l_pac - 1 - pos : pos;
 }
 
+// contig holding forward coordinate pos_f: the last contig whose offset is <= pos_f (bns_pos2rid, bntseq.c:346-363 returns the
+// same index: its bisection stops exactly there); -1 beyond the reference
 AR_HD int bns_pos2rid(const RefView& r, int64_t pos_f) {
-    int left, mid, right;
     if (pos_f >= r.l_pac) return -1;
-    left = 0; mid = 0; right = r.n_seqs;
-    while (left < right) {
-        mid = (left + right) >> 1;
-        if (pos_f >= r.contigs[mid].offset) {
-            if (mid == r.n_seqs - 1) break;
-            if (pos_f < r.contigs[mid + 1].offset) break;
-            left = mid + 1;
-        } else right = mid;
+    int lo = 0, hi = r.n_seqs;          // invariant: offset[lo] <= pos_f (offset[0] == 0), answer in [lo, hi)
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (r.contigs[mid].offset <= pos_f) lo = mid; else hi = mid;
     }
-    return mid;
+    return lo;
 }
 
+// contig of the interval [rb, re) when it lies on one strand and in one contig; -2 across the strand boundary, -1 across contigs
+// (bns_intv2rid, bntseq.c:365-373)
 AR_HD int bns_intv2rid(const RefView& r, int64_t rb, int64_t re) {
-    int is_rev, rid_b, rid_e;
     if (rb < r.l_pac && re > r.l_pac) return -2;
-    rid_b = bns_pos2rid(r, bns_depos(r, rb, &is_rev));
-    rid_e = rb < re ? bns_pos2rid(r, bns_depos(r, re - 1, &is_rev)) : rid_b;
-    return rid_b == rid_e ? rid_b : -1;
+    int strand;
+    const int first = bns_pos2rid(r, bns_depos(r, rb, &strand));
+    const int last = rb < re ? bns_pos2rid(r, bns_depos(r, re - 1, &strand)) : first;
+    return first == last ? first : -1;
 }
 
 // ---- kbtree with t = 5 (KB_DEFAULT_SIZE 512, 40-byte keys: kbtree.h:55-71), keys are chain ids ----
@@ -155,44 +158,41 @@ struct BTree {
     }
 };
 
-// test_and_merge: 1 if the seed is absorbed by (or appended to) chain c
+// Can seed `sid` join chain c?  (test_and_merge, bwamem.c:190-211.)  Three outcomes: it lies inside the chain's query and reference
+// span (absorbed: nothing changes), it continues the chain's last seed on a nearby diagonal (appended), or it cannot (0).
 AR_HD int test_and_merge(const MemOpt& opt, int64_t l_pac, Chain& c, Seed* seeds, int sid, int seed_rid) {
-    const Seed& p = seeds[sid];
-    const Seed& last = seeds[c.last_seed];
-    const Seed& first = seeds[c.first_seed];
-    int64_t qend = last.qbeg + last.len, rend = last.rbeg + last.len, x, y;
     if (seed_rid != c.rid) return 0;
-    if (p.qbeg >= first.qbeg && p.qbeg + p.len <= qend && p.rbeg >= first.rbeg && p.rbeg + p.len <= rend) return 1;
-    if ((last.rbeg < l_pac || first.rbeg < l_pac) && p.rbeg >= l_pac) return 0;
-    x = p.qbeg - last.qbeg;
-    y = p.rbeg - last.rbeg;
-    if (y >= 0 && x - y <= opt.w && y - x <= opt.w && x - last.len < opt.max_chain_gap && y - last.len < opt.max_chain_gap) {
-        seeds[c.last_seed].next = sid;
-        c.last_seed = sid;
-        ++c.n;
-        return 1;
-    }
-    return 0;
+    const Seed s = seeds[sid], head = seeds[c.first_seed], tail = seeds[c.last_seed];
+    const int64_t chain_qend = tail.qbeg + tail.len, chain_rend = tail.rbeg + tail.len;
+    const bool inside = s.qbeg >= head.qbeg && s.qbeg + s.len <= chain_qend && s.rbeg >= head.rbeg && s.rbeg + s.len <= chain_rend;
+    if (inside) return 1;
+    const bool chain_on_forward = tail.rbeg < l_pac || head.rbeg < l_pac;
+    if (chain_on_forward && s.rbeg >= l_pac) return 0;  // a chain never continues onto the other strand
+    const int64_t dq = s.qbeg - tail.qbeg, dr = s.rbeg - tail.rbeg;  // offsets from the last seed on the read / on the reference
+    const bool colinear = dr >= 0 && dq - dr <= opt.w && dr - dq <= opt.w;
+    const bool close = dq - tail.len < opt.max_chain_gap && dr - tail.len < opt.max_chain_gap;
+    if (!(colinear && close)) return 0;
+    seeds[c.last_seed].next = sid;
+    c.last_seed = sid;
+    ++c.n;
+    return 1;
 }
 
+// Bases of the read (or of the reference) covered by the chain's seeds, overlaps counted once; the chain's weight is the smaller
+// of the two coverages, capped at 2^30 - 1 (mem_chain_weight, bwamem.c:213-232)
 AR_HD int chain_weight(const Chain& c, const Seed* seeds) {
-    int64_t end;
-    int j, s, w = 0, tmp;
-    for (j = 0, end = 0, s = c.first_seed; j < c.n; ++j, s = seeds[s].next) {
-        const Seed& sd = seeds[s];
-        if (sd.qbeg >= end) w += sd.len;
-        else if (sd.qbeg + sd.len > end) w += (int)(sd.qbeg + sd.len - end);
-        end = end > sd.qbeg + sd.len ? end : sd.qbeg + sd.len;
+    int64_t q_cov = 0, r_cov = 0, q_end = 0, r_end = 0;
+    for (int k = 0, s = c.first_seed; k < c.n; ++k, s = seeds[s].next) {
+        const Seed sd = seeds[s];
+        const int64_t qe = (int64_t)sd.qbeg + sd.len, re = sd.rbeg + sd.len;
+        if (sd.qbeg >= q_end) q_cov += sd.len; else if (qe > q_end) q_cov += qe - q_end;
+        if (sd.rbeg >= r_end) r_cov += sd.len; else if (re > r_end) r_cov += re - r_end;
+        q_end = q_end > qe ? q_end : qe;
+        r_end = r_end > re ? r_end : re;
     }
-    tmp = w; w = 0;
-    for (j = 0, end = 0, s = c.first_seed; j < c.n; ++j, s = seeds[s].next) {
-        const Seed& sd = seeds[s];
-        if (sd.rbeg >= end) w += sd.len;
-        else if (sd.rbeg + sd.len > end) w += (int)(sd.rbeg + sd.len - end);
-        end = end > sd.rbeg + sd.len ? end : sd.rbeg + sd.len;
-    }
-    w = w < tmp ? w : tmp;
-    return w < (1 << 30) ? w : (1 << 30) - 1;
+    // the reference accumulates each coverage in an int; both stay far below 2^31 for reads of a few hundred bases
+    const int64_t w = q_cov < r_cov ? q_cov : r_cov;
+    return w < (1 << 30) ? (int)w : (1 << 30) - 1;
 }
 
 // mem_chain over precomputed SA values (sa_vals in the reference's visiting order: intervals in sorted order,
@@ -248,68 +248,65 @@ AR_HD int chain_seeds(const MemOpt& opt, const RefView& ref, int len, const Intv
     return n;
 }
 
-// mem_chain_flt on order[0..n): weights, introsort, keep/shadow marking.  kept_idx is scratch of n ints.
-// Leaves the surviving chain ids (in the reference's output order) in order[0..ret).
+// mem_chain_flt (bwamem.c:327-385) on order[0..n_chn).  Chains are ranked by weight (klib introsort: the permutation of equal weights is
+// part of the result), then taken greedily: a chain is KEPT unless an already kept chain overlaps it on the read by at least
+// mask_level of the shorter one and outweighs it clearly (drop_ratio, 2 x min_seed_len).  A kept chain remembers the first chain
+// it shadowed (`first`), which is kept too, as class 1; class 3 = kept without any significant overlap, 2 = kept despite one.
+// Of the classes 1 and 2 only the first max_chain_extend survive.  kept_idx: scratch of n ints.  Leaves the surviving ids, in rank
+// order, in order[0..ret).
+struct QuerySpan { int beg, end; };
+AR_HD QuerySpan chain_query_span(const Chain& c, const Seed* seeds) {
+    QuerySpan q; q.beg = seeds[c.first_seed].qbeg; q.end = seeds[c.last_seed].qbeg + seeds[c.last_seed].len; return q;
+}
 AR_HD int chain_filter(const MemOpt& opt, int n_chn, int32_t* order, Chain* chains, const Seed* seeds, int32_t* kept_idx) {
-    int i, k, n_kept = 0;
     if (n_chn == 0) return 0;
-    for (i = k = 0; i < n_chn; ++i) {
+    int n = 0;
+    for (int i = 0; i < n_chn; ++i) {  // weigh, drop the light ones
         Chain& c = chains[order[i]];
         c.first = -1; c.kept = 0;
         c.w = chain_weight(c, seeds);
-        if (c.w < opt.min_chain_weight) continue;
-        order[k++] = order[i];
+        if (c.w >= opt.min_chain_weight) order[n++] = order[i];
     }
-    n_chn = k;
-    const Chain* cc = chains;
-    ks_introsort((size_t)n_chn, order, [cc](int32_t a, int32_t b) { return cc[a].w > cc[b].w; });
-#define CH(i) chains[order[i]]
-#define CBEG(c) (seeds[(c).first_seed].qbeg)
-#define CEND(c) (seeds[(c).last_seed].qbeg + seeds[(c).last_seed].len)
-    if (n_chn == 0) return 0;
-    CH(0).kept = 3;
+    if (n == 0) return 0;
+    const Chain* by_id = chains;
+    ks_introsort((size_t)n, order, [by_id](int32_t a, int32_t b) { return by_id[a].w > by_id[b].w; });
+    auto at = [&](int rank) -> Chain& { return chains[order[rank]]; };
+    int n_kept = 0;
+    at(0).kept = 3;
     kept_idx[n_kept++] = 0;
-    for (i = 1; i < n_chn; ++i) {
-        int large_ovlp = 0;
-        Chain& ci = CH(i);
-        int bi = CBEG(ci), ei = CEND(ci);
-        for (k = 0; k < n_kept; ++k) {
-            int j = kept_idx[k];
-            Chain& cj = CH(j);
-            int bj = CBEG(cj), ej = CEND(cj);
-            int b_max = bj > bi ? bj : bi;
-            int e_min = ej < ei ? ej : ei;
-            if (e_min > b_max && (!cj.is_alt || ci.is_alt)) {
-                int li = ei - bi, lj = ej - bj;
-                int min_l = li < lj ? li : lj;
-                if (e_min - b_max >= min_l * opt.mask_level && min_l < opt.max_chain_gap) {
-                    large_ovlp = 1;
-                    if (cj.first < 0) cj.first = i;
-                    if (ci.w < cj.w * opt.drop_ratio && cj.w - ci.w >= opt.min_seed_len << 1) break;
-                }
-            }
+    for (int i = 1; i < n; ++i) {
+        Chain& cand = at(i);
+        const QuerySpan ci = chain_query_span(cand, seeds);
+        bool overlapped = false, dropped = false;
+        for (int k = 0; k < n_kept && !dropped; ++k) {
+            Chain& keeper = at(kept_idx[k]);
+            const QuerySpan cj = chain_query_span(keeper, seeds);
+            const int ov_beg = cj.beg > ci.beg ? cj.beg : ci.beg, ov_end = cj.end < ci.end ? cj.end : ci.end;
+            if (ov_end <= ov_beg || (keeper.is_alt && !cand.is_alt)) continue;  // an ALT chain never shadows a primary one
+            const int len_i = ci.end - ci.beg, len_j = cj.end - cj.beg, shorter = len_i < len_j ? len_i : len_j;
+            if (!(ov_end - ov_beg >= shorter * opt.mask_level && shorter < opt.max_chain_gap)) continue;
+            overlapped = true;
+            if (keeper.first < 0) keeper.first = i;
+            dropped = cand.w < keeper.w * opt.drop_ratio && keeper.w - cand.w >= opt.min_seed_len << 1;
         }
-        if (k == n_kept) {
-            kept_idx[n_kept++] = i;
-            ci.kept = large_ovlp ? 2 : 3;
-        }
+        if (!dropped) { kept_idx[n_kept++] = i; cand.kept = overlapped ? 2 : 3; }
     }
-    for (i = 0; i < n_kept; ++i) {
-        Chain& c = CH(kept_idx[i]);
-        if (c.first >= 0) CH(c.first).kept = 1;
+    for (int k = 0; k < n_kept; ++k) {  // the first chain each kept chain shadows stays as class 1 (it may already be class 2 / 3: overwritten as in the reference)
+        const int sh = at(kept_idx[k]).first;
+        if (sh >= 0) at(sh).kept = 1;
     }
-    for (i = k = 0; i < n_chn; ++i) {
-        if (CH(i).kept == 0 || CH(i).kept == 3) continue;
-        if (++k >= opt.max_chain_extend) break;
+    int quota = 0, i = 0;
+    for (; i < n; ++i) {  // classes 1 and 2 count against max_chain_extend ...
+        const int kc = at(i).kept;
+        if (kc == 0 || kc == 3) continue;
+        if (++quota >= opt.max_chain_extend) break;
     }
-    for (; i < n_chn; ++i)
-        if (CH(i).kept < 3) CH(i).kept = 0;
-    for (i = k = 0; i < n_chn; ++i)
-        if (CH(i).kept != 0) order[k++] = order[i];
-#undef CH
-#undef CBEG
-#undef CEND
-    return k;
+    for (; i < n; ++i)     // ... everything of those classes from the chain that exhausts it onwards is dropped (that chain included, as at bwamem.c:376-379)
+        if (at(i).kept < 3) at(i).kept = 0;
+    int out = 0;
+    for (i = 0; i < n; ++i)
+        if (at(i).kept != 0) order[out++] = order[i];
+    return out;
 }
 
 }  // namespace arachne
