@@ -296,10 +296,13 @@ int arachne_ingest_next(arachne_ingest_t* I, int64_t target_pairs, arachne_inges
             B->names.append(P.names.data() + n0, (size_t)(P.name_end[r + k - 1] - n0));
             for (int t = r; t < r + k; ++t) B->name_off.push_back(nb0 + P.name_end[t]);
             B->seed.insert(B->seed.end(), P.seed.begin() + r, P.seed.begin() + r + k);
+            {
+                const int g0 = r ? P.rg_end[r - 1] : 0; const int64_t gb0 = (int64_t)B->rgs.size() - g0;
+                B->rgs.append(P.rgs.data() + g0, (size_t)(P.rg_end[r + k - 1] - g0));
+                for (int t = r; t < r + k; ++t) B->rg_off.push_back(gb0 + P.rg_end[t]);
+            }
             if (index == 0) {
-                const int g0 = r ? P.rg_end[r - 1] : 0;
                 B->barcodes += first_bc; B->bc_off.push_back((int64_t)B->barcodes.size());
-                B->rgs.append(P.rgs.data() + g0, (size_t)(P.rg_end[r] - g0)); B->rg_off.push_back((int64_t)B->rgs.size());
                 B->valid.push_back(P.valid[r]);
             }
             I->cur_pos += k; n_pairs += k; index += k;

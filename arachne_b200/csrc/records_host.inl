@@ -27,7 +27,7 @@ void sam_mm_list(SamBuf& o, const arachne_batch_out_t* out, int reg) {
 }  // namespace
 
 int arachne_records_sam(const arachne_index_t* idx, const arachne_batch_in_t* in, const arachne_batch_out_t* out, const char* const* names,
-                        const char* const* quals, const char* const* barcodes, const char* read_group, char** sam, size_t* sam_len) {
+                        const char* const* quals, const char* const* barcodes, const char* const* read_groups, char** sam, size_t* sam_len) {
     if (!idx || !in || !out || !names || !sam || !sam_len) { set_error("arachne_records_sam: null argument"); return ARACHNE_ERR_ARG; }
     if (!out->records || !out->rec_off || (out->n_regs && (!out->alns || !out->cigar))) { set_error("arachne_records_sam: the batch has no host-side records (run ARACHNE_STAGE_RECORDS without ARACHNE_OUT_DEVICE)"); return ARACHNE_ERR_ARG; }
     if (in->flags & ARACHNE_IN_DEVICE) { set_error("arachne_records_sam: needs the host copy of the reads"); return ARACHNE_ERR_ARG; }
@@ -58,7 +58,7 @@ int arachne_records_sam(const arachne_index_t* idx, const arachne_batch_in_t* in
         const char* ql = quals ? quals[R.read] : nullptr;
         if (!ql || R.clip_end <= R.clip_start) o.s.push_back('*');
         else for (int k = R.clip_start; k < R.clip_end; ++k) o.s.push_back(R.reversed ? ql[len - 1 - k] : ql[k]);
-        if (read_group && *read_group) { o.s.append("\tRG:Z:"); o.s += read_group; }
+        if (read_groups && read_groups[pair] && *read_groups[pair]) { o.s.append("\tRG:Z:"); o.s += read_groups[pair]; }
         o.s.append("\tXS:i:"); o.num(R.xs);
         o.s.append("\tXC:Z:"); if (R.has_xc) sam_mm_list(o, out, R.xc_reg);
         o.s.append("\tAC:Z:"); sam_mm_list(o, out, R.reg);

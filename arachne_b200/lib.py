@@ -125,11 +125,11 @@ class Ingest:
                        run_rfa=np.ctypeslib.as_array(b.run_rfa, shape=(u,)).copy(), valid=np.ctypeslib.as_array(b.valid, shape=(u,)).copy(),
                        rand_seed=np.ctypeslib.as_array(b.rand_seed, shape=(n,)).copy())
             if copy:
-                no = np.ctypeslib.as_array(b.name_off, shape=(n + 1,)); bo = np.ctypeslib.as_array(b.barcode_char_off, shape=(u + 1,)); go = np.ctypeslib.as_array(b.read_group_off, shape=(u + 1,))
+                no = np.ctypeslib.as_array(b.name_off, shape=(n + 1,)); bo = np.ctypeslib.as_array(b.barcode_char_off, shape=(u + 1,)); go = np.ctypeslib.as_array(b.read_group_off, shape=(n + 1,))
                 names = C.string_at(b.names, int(no[-1])); bcs = C.string_at(b.barcodes, int(bo[-1])); rgs = C.string_at(b.read_groups, int(go[-1])); ql = C.string_at(b.qual, nb)
                 out["names"] = [names[no[i]:no[i + 1]].decode() for i in range(n)]
                 out["barcodes"] = [bcs[bo[i]:bo[i + 1]].decode() for i in range(u)]
-                out["read_groups"] = [rgs[go[i]:go[i + 1]].decode() for i in range(u)]
+                out["read_groups"] = [rgs[go[i]:go[i + 1]].decode() for i in range(n)]
                 out["quals"] = [ql[off[i]:off[i + 1]].decode() for i in range(2 * n)]
             return out
         finally:
@@ -417,8 +417,8 @@ class ArachneCuda:
     # ---- batch hot path ----
     def align_batch(self, seq, off, bc_off=None, score_delta=25, stages=0, run_rfa=None, rand_seed=None, improper_penalty=-4.0, centromeres=None,
                     attach_bx=None, sam=None):
-        """sam: dict(names=[...n_pairs], quals=[...2*n_pairs] or None, barcodes=[...n_barcodes] or None, read_group=str or None) -> res["sam"]
-        (needs stages & 16)."""
+        """sam: dict(names=[...n_pairs], quals=[...2*n_pairs] or None, barcodes=[...n_barcodes] or None, read_groups=[...n_pairs] or
+        read_group=str (the same for every pair) or None) -> res["sam"] (needs stages & 16)."""
         seq = np.ascontiguousarray(seq, dtype=np.uint8); off = np.ascontiguousarray(off, dtype=np.int64)
         n_pairs = (len(off) - 1) // 2
         bi = BatchIn(); bi.n_pairs = n_pairs; bi.seq = _p(seq, C.c_uint8); bi.seq_off = _p(off, C.c_int64)
@@ -457,11 +457,12 @@ class ArachneCuda:
                 if sam is not None:
                     arr = lambda xs: (C.c_char_p * len(xs))(*[x.encode() if isinstance(x, str) else x for x in xs]) if xs is not None else None
                     txt, ln = C.c_void_p(None), C.c_size_t(0)
-                    self.lib.arachne_records_sam.argtypes = [C.c_void_p, C.POINTER(BatchIn), C.POINTER(BatchOut), C.c_void_p, C.c_void_p, C.c_void_p, C.c_char_p,
+                    self.lib.arachne_records_sam.argtypes = [C.c_void_p, C.POINTER(BatchIn), C.POINTER(BatchOut), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                                              C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]
                     nm, ql, bcs = arr(sam["names"]), arr(sam.get("quals")), arr(sam.get("barcodes"))
-                    rg = sam.get("read_group")
-                    self._ck(self.lib.arachne_records_sam(self.idx, C.byref(bi), po, nm, ql, bcs, rg.encode() if rg else None, C.byref(txt), C.byref(ln)))
+                    rgl = sam.get("read_groups") or ([sam["read_group"]] * n_pairs if sam.get("read_group") else None)
+                    rgs = arr(rgl)
+                    self._ck(self.lib.arachne_records_sam(self.idx, C.byref(bi), po, nm, ql, bcs, rgs, C.byref(txt), C.byref(ln)))
                     res["sam"] = C.string_at(txt.value, ln.value).decode()
                     C.CDLL(None).free(txt)
         finally:

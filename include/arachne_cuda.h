@@ -290,10 +290,11 @@ void arachne_batch_free(arachne_batch_out_t *out);
 /* SAM text of every record of a batch that ran ARACHNE_STAGE_RECORDS with host outputs: one line per record, fields
  * QNAME FLAG RNAME POS MAPQ CIGAR RNEXT PNEXT TLEN SEQ QUAL and the tags in AppendBam's order (RG XS XC AC AS XM AM XT SA BX VX DM;
  * bamwriter.go:399-566).  `in` is the batch's input (host seq / seq_off / barcode_off).  names: n_pairs read names (FastQRecord.ReadInfo);
- * quals: 2*n_pairs ASCII quality strings or NULL ('*'); barcodes: n_barcodes strings or NULL; read_group may be NULL.
+ * quals: 2*n_pairs ASCII quality strings or NULL ('*'); barcodes: n_barcodes strings or NULL; read_groups: n_pairs strings
+ * (FastQRecord.ReadGroupId, reader.go:143-152; an empty string writes no RG tag) or NULL.
  * *sam is malloc'ed: release it with free().  BAM encoding itself (biogo/hts in the reference) stays with the host. */
 int arachne_records_sam(const arachne_index_t *idx, const arachne_batch_in_t *in, const arachne_batch_out_t *out, const char *const *names,
-                        const char *const *quals, const char *const *barcodes, const char *read_group, char **sam, size_t *sam_len);
+                        const char *const *quals, const char *const *barcodes, const char *const *read_groups, char **sam, size_t *sam_len);
 
 /* ---- stage entry points (device kernels on caller problems) ---- */
 /* ksw_extend2 (bwa/ksw.c:380-479) on n independent problems; query i = q[q_off[i]..q_off[i+1]), same for t.

@@ -32,8 +32,8 @@ typedef struct {
     const int64_t *name_off;         /* n_pairs+1 */
     const char *barcodes;            /* barcode of every unit, concatenated */
     const int64_t *barcode_char_off; /* n_units+1 */
-    const char *read_groups;         /* FastQRecord.ReadGroupId of the unit's first record (reader.go:143-152) */
-    const int64_t *read_group_off;   /* n_units+1 */
+    const char *read_groups;         /* FastQRecord.ReadGroupId of every pair (reader.go:143-152: the header's last field), concatenated */
+    const int64_t *read_group_off;   /* n_pairs+1 */
     void *priv;
 } arachne_ingest_batch_t;
 

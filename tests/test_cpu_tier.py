@@ -345,11 +345,11 @@ def test_ingest_matches_reader_go(tmp_path, gz):
                     lo, hi = int(b["unit_off"][u]), int(b["unit_off"][u + 1])
                     got_units.append((pair + lo, pair + hi, bool(b["unique"][u])))
                     first = recs[pair + lo]
-                    assert b["barcodes"][u] == first[1] and b["read_groups"][u] == first[3] and bool(b["valid"][u]) == first[2]
+                    assert b["barcodes"][u] == first[1] and bool(b["valid"][u]) == first[2]
                     assert bool(b["run_rfa"][u]) == (bool(b["unique"][u]) and "-" in first[1] and hi - lo >= 5)
                 for i in range(b["n_pairs"]):
                     name, bc, valid, rg, s1, q1, s2, q2 = recs[pair + i]
-                    assert b["names"][i] == name
+                    assert b["names"][i] == name and b["read_groups"][i] == rg
                     assert b["rand_seed"][i] == int.from_bytes(hashlib.md5(name.encode()).digest()[:8], "little", signed=True)
                     o = b["off"][2 * i:2 * i + 3]
                     assert np.array_equal(b["seq"][o[0]:o[1]], nt4[np.frombuffer(s1.encode(), np.uint8)]) and np.array_equal(b["seq"][o[1]:o[2]], nt4[np.frombuffer(s2.encode(), np.uint8)])

@@ -573,7 +573,63 @@ def test_determinism_two_runs(A, R, workdir):
     b = run()
     with ThreadPoolExecutor(2) as ex:
         c, d = list(ex.map(run, range(2)))
+    def pools(x):  # CIGAR / mismatch words per region: the pool OFFSETS are handed out by atomics and may differ run to run, the words may not
+        al = x["alns"]
+        cg = np.concatenate([x["cigar"][o:o + n] for o, n in zip(al["cigar_off"].tolist(), al["n_cigar"].tolist())] + [np.zeros(0, np.uint32)])
+        mm = np.concatenate([x["mm"][o:o + 2 * n] for o, n in zip(al["mm_off"].tolist(), al["n_mm"].tolist())] + [np.zeros(0, np.int32)])
+        return cg, mm
+    cga, mma = pools(a)
     for other in (b, c, d):
-        for k in ("reg_off", "regs", "alns", "cigar", "mm", "cand_off", "cands", "lmp", "rec_off", "records"):
+        for k in ("reg_off", "regs", "cand_off", "cands", "lmp", "rec_off", "records"):
             assert a[k].tobytes() == other[k].tobytes(), k
+        for f in a["alns"].dtype.names:
+            if f not in ("cigar_off", "mm_off"):
+                assert np.array_equal(a["alns"][f], other["alns"][f]), f
+        cgo, mmo = pools(other)
+        assert np.array_equal(cga, cgo) and np.array_equal(mma, mmo)
     assert a["counters"]["n_ext_cells"] == b["counters"]["n_ext_cells"] and a["counters"]["n_occ_blocks"] == b["counters"]["n_occ_blocks"]
+
+
+def test_fastq_to_sam_end_to_end(A, R, workdir, tmp_path):
+    """scripts/align_fastq.py's path: FASTQ files -> native ingest (work units, md5 seeds, flags) -> all stages -> SAM text, against the same
+    reads fed directly + the oracle's records formatted by the independent Python formatter.  The pieces are pinned separately; this pins
+    that they fit together (offsets, unit flags, per-pair read groups, names with mate suffixes stripped)."""
+    import subprocess, sys as _sys
+    fa, ctg, _ = util.make_dataset("rep600k", workdir)
+    rs = _records_dataset(ctg, 91)
+    nb = len(rs.bc_off) - 1
+    quals = ["".join(chr(35 + (3 * i + k) % 38) for k in range(int(rs.off[i + 1] - rs.off[i]))) for i in range(2 * rs.n_pairs)]
+    dec = np.frombuffer(b"ACGTN", np.uint8)
+    r1, r2 = str(tmp_path / "r1.fq"), str(tmp_path / "r2.fq")
+    with open(r1, "w") as f1, open(r2, "w") as f2:
+        for b in range(nb):
+            for p in range(int(rs.bc_off[b]), int(rs.bc_off[b + 1])):
+                for f, i, m in ((f1, 2 * p, 1), (f2, 2 * p + 1, 2)):
+                    s = dec[np.minimum(rs.seq[rs.off[i]:rs.off[i + 1]], 4)].tobytes().decode()
+                    f.write("@%s/%d\tBX:Z:%s\tVX:i:1\n%s\n+\n%s\n" % (rs.names[p], m, rs.barcodes[b], s, quals[i]))
+    out = str(tmp_path / "out.sam")
+    subprocess.run([_sys.executable, os.path.join(util.ROOT, "scripts", "align_fastq.py"), fa, r1, r2, "-o", out, "--batch-pairs", "700", "--threads", "3"], check=True)
+    got = [l for l in open(out).read().split("\n") if l and not l.startswith("@")]
+    # expectation: the reference's C code + the oracle's records on the same reads; RG is the header's last field (reader.go:143-152)
+    R.load(fa)
+    ref = R.batch(rs.seq, rs.off, rescue=True, cigar=True, threads=8)
+    P = util.PlaceOracle(fa)
+    from arachne_b200 import workunits as W
+    uo, uq, ub = W.work_units(rs.bc_off, rs.barcodes)
+    rfa = W.worth_running_rfa(uo, uq, ub, rs.barcodes)
+    seeds = np.array([P.name_seed(n) for n in rs.names], dtype=np.int64)
+    oc, ocands, olmp, orecs = P.place_records(rs.seq, rs.off, uo, rfa, uq, seeds, ref["reg_off"], ref["regs"], ref["aln"], ref["cigar"])
+    e = ref["aln"]; O = util.oracle_lib()
+    def mm_of_reg(gi):
+        r = int(np.searchsorted(ref["reg_off"], gi, side="right") - 1)
+        q = np.ascontiguousarray(rs.seq[rs.off[r]:rs.off[r + 1]])
+        out5 = np.zeros(5, np.int32); mm = np.zeros(2 * len(q) + 8, np.int32)
+        n = O.orc_walk(C.byref(P.ref), len(q), q.ctypes.data_as(C.c_void_p), ref["regs"][gi:gi + 1].ctypes.data_as(C.c_void_p), e[gi].ctypes.data_as(C.c_void_p),
+                       ref["cigar"].ctypes.data_as(C.c_void_p), out5.ctypes.data_as(C.c_void_p), mm.ctypes.data_as(C.c_void_p))
+        return mm[:n], mm[n:2 * n]
+    names = [c[0] for c in util.read_ann(fa)[1]]
+    ubar = [rs.barcodes[b] for b in ub.tolist()]
+    exp = util.sam_lines(orecs, names, rs.seq, rs.off, uo, rs.names, quals, ubar, "VX:i:1", lambda gi: (int(e[gi, 4]), int(e[gi, 5])), ref["cigar"], mm_of_reg)
+    assert len(got) == len(exp) and len(got) >= 2 * rs.n_pairs
+    for i, (x, y) in enumerate(zip(got, exp)):
+        assert x == y, (i, x, y)
