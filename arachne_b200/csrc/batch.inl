@@ -351,10 +351,11 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
                                              W.d_resc.as<AlnReg>(), W.d_out.as<AlnReg>(), W.d_reg_read.as<int>());
     AR_TRY(cudaGetLastError());
     static_assert(sizeof(unsigned long long) == sizeof(int64_t), "");
+    const bool out_regs = !out_dev && !(in->flags & ARACHNE_OUT_NO_REGIONS);
     if (!out_dev) {
-        AR_PIN(priv->regs, (total_regs + 1) * sizeof(AlnReg));
+        if (out_regs) AR_PIN(priv->regs, (total_regs + 1) * sizeof(AlnReg));
         AR_TRY(cudaMemcpyAsync(priv->reg_off.p, W.d_reg_off.p, (n_reads + 1) * 8, cudaMemcpyDeviceToHost, st));
-        if (total_regs) AR_TRY(cudaMemcpyAsync(priv->regs.p, W.d_out.p, total_regs * sizeof(AlnReg), cudaMemcpyDeviceToHost, st));
+        if (total_regs && out_regs) AR_TRY(cudaMemcpyAsync(priv->regs.p, W.d_out.p, total_regs * sizeof(AlnReg), cudaMemcpyDeviceToHost, st));
     }
     cudaEventRecord(ev[6], st);
     // ---- CIGAR + candidate statistics ----
@@ -446,7 +447,7 @@ int arachne_align_batch(arachne_index_t* idx, const arachne_mem_opt_t* opt_, con
     AR_TRY(W.sync(st));
 
     out->n_regs = (int64_t)total_regs;
-    if (!out_dev) { out->reg_off = priv->reg_off.as<int64_t>(); out->regs = priv->regs.as<arachne_alnreg_t>(); }
+    if (!out_dev) { out->reg_off = priv->reg_off.as<int64_t>(); out->regs = out_regs ? priv->regs.as<arachne_alnreg_t>() : nullptr; }
     out->n_occ_lookups = hc.occ;
     out->n_occ_blocks = hc.occ_blocks;
     out->n_sa_lookups = total_sa;

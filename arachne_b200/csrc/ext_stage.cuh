@@ -362,7 +362,7 @@ __global__ void __launch_bounds__(XDP_BLOCK) k_ext_dp(MemOpt opt, RefView ref, E
         const int M = __viaddmin_s32_relu(hd, sc, hd << 8);                            \
         const int h = __vimax3_s32(M, e, f);                                           \
         const int e2 = __viaddmax_s32_relu(M, -oe_del, e * one - e_del);               \
-        f = __viaddmax_s32_relu(M, -oe_ins, f * one - e_ins);                          \
+        f = __viaddmax_s32(f, -e_ins, M * one - oe_ins);                               \
         p[(u_) * XDP_BLOCK] = XCol<kWide>::pack((cw_), h1, e2, c256);                  \
         k##u_ = h * c256 + (u_);                                                       \
         h1 = h;                                                                        \

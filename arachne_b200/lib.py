@@ -21,7 +21,7 @@ CAND = np.dtype([("reg", "<i4"), ("read", "<i4"), ("id", "<i4"), ("active", "<i4
 assert ALNREG.itemsize == 88 and ALN.itemsize == 72 and CAND.itemsize == 120
 
 STAGE_REGIONS, STAGE_RESCUE, STAGE_CIGAR, STAGE_PLACE = 1, 2, 4, 8
-IN_DEVICE, OUT_DEVICE = 1, 2
+IN_DEVICE, OUT_DEVICE, OUT_NO_REGIONS = 1, 2, 4
 COUNTERS = ("n_occ_lookups", "n_occ_blocks", "n_sa_lookups", "n_lf_steps", "n_ext_calls", "n_ext_cells", "n_glb_cells", "n_kernel_launches")
 STAGE_MS = ("seed", "sa", "chain", "extend", "rescue", "cigar", "place", "total")
 
@@ -377,12 +377,12 @@ class ArachneCuda:
         finally:
             self.lib.arachne_batch_free(po)
 
-    def align_batch_host(self, seq, off, score_delta=25, stages=0, bc_off=None, run_rfa=None, rand_seed=None, improper_penalty=-4.0):
+    def align_batch_host(self, seq, off, score_delta=25, stages=0, bc_off=None, run_rfa=None, rand_seed=None, improper_penalty=-4.0, flags=0):
         """The C-ABI call exactly as a host makes it (host buffers in, pinned host results out), without converting the
         results to numpy: returns counts, the bytes that crossed PCIe in each direction, counters and stage times."""
         n_pairs = (len(off) - 1) // 2
         bi = BatchIn(); bi.n_pairs = n_pairs; bi.seq = _p(seq, C.c_uint8); bi.seq_off = _p(off, C.c_int64)
-        bi.score_delta = score_delta; bi.stages = stages; bi.improper_penalty = improper_penalty; bi.delta = 17
+        bi.score_delta = score_delta; bi.stages = stages; bi.improper_penalty = improper_penalty; bi.delta = 17; bi.flags = flags
         h2d = seq.nbytes + off.nbytes
         if bc_off is not None:
             bi.n_barcodes = len(bc_off) - 1; bi.barcode_off = _p(bc_off, C.c_int64); h2d += bc_off.nbytes
@@ -394,12 +394,13 @@ class ArachneCuda:
         self._ck(self.lib.arachne_align_batch(self.idx, C.byref(self.opt), C.byref(bi), C.byref(po)))
         try:
             o = po.contents
-            d2h = (o.n_reads + 1) * 8 + o.n_regs * 88 + (o.n_regs * 72 + o.n_cigar * 4 + o.n_mm * 4 if o.alns else 0)
+            d2h = (o.n_reads + 1) * 8 + (o.n_regs * 88 if o.regs else 0) + (o.n_regs * 72 + o.n_cigar * 4 + o.n_mm * 4 if o.alns else 0)
             if o.cands:
                 d2h += (o.n_reads + 1) * 8 + o.n_cands * 120 + max(1, bi.n_barcodes) * 8
             mapq_sum = int(np.frombuffer(C.string_at(o.cands, min(o.n_cands, 64) * 120), dtype=CAND)["mapq"].sum()) if o.cands and o.n_cands else -1
             return dict(n_regs=o.n_regs, n_cigar=o.n_cigar, n_mm=o.n_mm, n_cands=o.n_cands, h2d_bytes=h2d, d2h_bytes=d2h,
-                        first_score=(int(np.frombuffer(C.string_at(o.regs, 88), dtype=ALNREG)["score"][0]) if o.n_regs else -1), mapq_probe=mapq_sum,
+                        first_score=(int(np.frombuffer(C.string_at(o.regs, 88), dtype=ALNREG)["score"][0]) if o.n_regs and o.regs else
+                                     int(np.frombuffer(C.string_at(o.alns, 72), dtype=ALN)["score"][0]) if o.n_regs and o.alns else -1), mapq_probe=mapq_sum,
                         counters={k: getattr(o, k) for k in COUNTERS}, ms={k: getattr(o, "ms_" + k) for k in STAGE_MS})
         finally:
             self.lib.arachne_batch_free(po)
@@ -416,7 +417,7 @@ class ArachneCuda:
 
     # ---- batch hot path ----
     def align_batch(self, seq, off, bc_off=None, score_delta=25, stages=0, run_rfa=None, rand_seed=None, improper_penalty=-4.0, centromeres=None,
-                    attach_bx=None, sam=None):
+                    attach_bx=None, sam=None, flags=0):
         """sam: dict(names=[...n_pairs], quals=[...2*n_pairs] or None, barcodes=[...n_barcodes] or None, read_groups=[...n_pairs] or
         read_group=str (the same for every pair) or None) -> res["sam"] (needs stages & 16)."""
         seq = np.ascontiguousarray(seq, dtype=np.uint8); off = np.ascontiguousarray(off, dtype=np.int64)
@@ -425,7 +426,7 @@ class ArachneCuda:
         if bc_off is not None:
             bc_off = np.ascontiguousarray(bc_off, dtype=np.int64)
             bi.n_barcodes = len(bc_off) - 1; bi.barcode_off = _p(bc_off, C.c_int64)
-        bi.score_delta = score_delta; bi.stages = stages; bi.improper_penalty = improper_penalty; bi.delta = 17
+        bi.score_delta = score_delta; bi.stages = stages; bi.improper_penalty = improper_penalty; bi.delta = 17; bi.flags = flags
         if run_rfa is not None:
             run_rfa = np.ascontiguousarray(run_rfa, dtype=np.uint8); bi.run_rfa = _p(run_rfa, C.c_uint8)
         if rand_seed is not None:
@@ -440,7 +441,8 @@ class ArachneCuda:
         try:
             o = po.contents
             res = dict(reg_off=np.ctypeslib.as_array(o.reg_off, shape=(o.n_reads + 1,)).copy(),
-                       regs=(np.frombuffer(C.string_at(o.regs, o.n_regs * 88), dtype=ALNREG).copy() if o.n_regs else np.zeros(0, ALNREG)),
+                       regs=(np.frombuffer(C.string_at(o.regs, o.n_regs * 88), dtype=ALNREG).copy() if o.n_regs and o.regs else
+                             None if o.n_regs else np.zeros(0, ALNREG)),
                        counters={k: getattr(o, k) for k in COUNTERS}, ms={k: getattr(o, "ms_" + k) for k in STAGE_MS})
             if o.alns and o.n_regs:
                 res["alns"] = np.frombuffer(C.string_at(o.alns, o.n_regs * 72), dtype=ALN).copy()

@@ -186,7 +186,11 @@ enum {
 
 enum {
     ARACHNE_IN_DEVICE = 1,     /* seq / seq_off are device pointers on the index's device (inputs already resident in HBM) */
-    ARACHNE_OUT_DEVICE = 2     /* leave the results in the handle's device workspace: only counts, counters and stage times come back */
+    ARACHNE_OUT_DEVICE = 2,    /* leave the results in the handle's device workspace: only counts, counters and stage times come back */
+    ARACHNE_OUT_NO_REGIONS = 4 /* do not copy the mem_alnreg_t array to the host (out->regs = NULL; reg_off, alns, cigar, mm and the
+                                  placement / record arrays come back as usual).  For callers that consume alignments, candidates or
+                                  records: the regions are an intermediate of the path (gobwa.go:326-335 keeps them only to hand each
+                                  one back to mem_reg2aln) and are 1/3 of the result bytes */
 };
 
 enum {

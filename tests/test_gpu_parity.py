@@ -590,6 +590,26 @@ def test_determinism_two_runs(A, R, workdir):
     assert a["counters"]["n_ext_cells"] == b["counters"]["n_ext_cells"] and a["counters"]["n_occ_blocks"] == b["counters"]["n_occ_blocks"]
 
 
+def test_out_no_regions_flag(A, R, workdir):
+    """ARACHNE_OUT_NO_REGIONS: the region array is not copied back (regs is NULL) and every other array -- and the SAM text made from
+    them -- is what the plain call returns."""
+    from arachne_b200.lib import OUT_NO_REGIONS
+    fa, ctg, rs = util.make_dataset("rep600k", workdir, damaged=True)
+    A.load_index(fa)
+    seeds = np.array([A.name_seed(n) for n in rs.names], dtype=np.int64)
+    rfa = np.ones(len(rs.bc_off) - 1, np.uint8)
+    sam = dict(names=list(rs.names), quals=None, barcodes=None, read_group=None)
+    a = A.align_batch(rs.seq, rs.off, rs.bc_off, stages=31, run_rfa=rfa, rand_seed=seeds, sam=sam)
+    b = A.align_batch(rs.seq, rs.off, rs.bc_off, stages=31, run_rfa=rfa, rand_seed=seeds, sam=sam, flags=OUT_NO_REGIONS)
+    assert len(a["regs"]) > 0 and b["regs"] is None
+    for k in ("reg_off", "cand_off", "cands", "lmp", "rec_off", "records"):
+        assert a[k].tobytes() == b[k].tobytes(), k
+    for f in a["alns"].dtype.names:
+        if f not in ("cigar_off", "mm_off"):
+            assert np.array_equal(a["alns"][f], b["alns"][f]), f
+    assert a["sam"] == b["sam"] and a["sam"].count("\n") == len(a["records"])
+
+
 def test_fastq_to_sam_end_to_end(A, R, workdir, tmp_path):
     """scripts/align_fastq.py's path: FASTQ files -> native ingest (work units, md5 seeds, flags) -> all stages -> SAM text, against the same
     reads fed directly + the oracle's records formatted by the independent Python formatter.  The pieces are pinned separately; this pins
