@@ -470,3 +470,52 @@ class ArachneCuda:
         finally:
             self.lib.arachne_batch_free(po)
         return res
+
+
+FQ_FORMATS = ("unknown", "standard", "haplotagging", "stlfr", "tellseq")  # ARACHNE_FQ_* (include/arachne_preprocess.h)
+
+
+class PreprocessOpt(C.Structure):  # arachne_preprocess_opt_t
+    _fields_ = [("tag", C.c_char_p), ("standardize", C.c_int32), ("sort", C.c_int32), ("device", C.c_int32), ("compress_level", C.c_int32)]
+
+
+class PreprocessStats(C.Structure):  # arachne_preprocess_stats_t
+    _fields_ = [("n_pairs", C.c_int64), ("n_barcodes", C.c_int64), ("n_no_tag", C.c_int64), ("n_invalid", C.c_int64), ("format", C.c_int32),
+                ("ms_read", C.c_float), ("ms_sort", C.c_float), ("ms_write", C.c_float)]
+
+
+def _pp_lib(path=None):
+    L = C.CDLL(path or lib_path())
+    L.arachne_last_error.restype = C.c_char_p
+    L.arachne_fastq_format.argtypes = [C.c_char_p, C.c_char_p, C.POINTER(C.c_int)]
+    L.arachne_fastq_header_format.argtypes = [C.c_char_p]
+    L.arachne_preprocess.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.POINTER(PreprocessOpt), C.POINTER(PreprocessStats)]
+    return L
+
+
+def fastq_header_format(header: str) -> str:
+    """The format patterns of src/preprocess/standardize.go:16-25 on one header line (without '@')."""
+    return FQ_FORMATS[_pp_lib().arachne_fastq_header_format(header.encode())]
+
+
+def fastq_format(r1: str, r2: str) -> str:
+    """findFastqFormat (standardize.go:98-125). Host only."""
+    L = _pp_lib(); f = C.c_int(0)
+    rc = L.arachne_fastq_format(r1.encode(), r2.encode(), C.byref(f))
+    if rc:
+        raise ArachneError(f"arachne_fastq_format {rc}: {L.arachne_last_error().decode()}")
+    return FQ_FORMATS[f.value]
+
+
+def preprocess(r1: str, r2: str, out_r1: str, out_r2: str, tag: str = "BX", standardize: bool = True, sort: bool = True, device: int = 0,
+               compress_level: int = 4) -> dict:
+    """`arachne preprocess` (src/preprocess/preprocess.go:43-110 + standardize.go) without samtools: standard headers, pairs in barcode
+    order (stable device radix sort).  sort=True needs a CUDA device."""
+    L = _pp_lib()
+    o = PreprocessOpt(tag.encode(), int(standardize), int(sort), device, compress_level); st = PreprocessStats()
+    rc = L.arachne_preprocess(r1.encode(), r2.encode(), out_r1.encode(), out_r2.encode(), C.byref(o), C.byref(st))
+    if rc:
+        raise ArachneError(f"arachne_preprocess {rc}: {L.arachne_last_error().decode()}")
+    d = {k: getattr(st, k) for k, _ in PreprocessStats._fields_}
+    d["format"] = FQ_FORMATS[st.format]
+    return d
