@@ -842,3 +842,5 @@ int arachne_ksw_global_batch(int device, const arachne_mem_opt_t* opt_, int64_t 
 }
 
 }  // extern "C"
+
+#include "noalloc.inl"

@@ -307,6 +307,21 @@ int arachne_records_sam(const arachne_index_t *idx, const arachne_batch_in_t *in
 int arachne_ksw_extend_batch(int device, const arachne_mem_opt_t *opt, int64_t n, const uint8_t *q, const int64_t *q_off, const uint8_t *t,
                              const int64_t *t_off, const int32_t *h0, const int32_t *w, int end_bonus, int zdrop, int32_t *out,
                              uint64_t *cells, float *kernel_ms, int repeat);
+/* NO COUNTERPART IN THE REFERENCE -- added for callers that cannot call cudaMalloc (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid allocation).  The same ksw_extend2 batch as arachne_ksw_extend_batch,
+ * but the call allocates NOTHING, on the device or through any library: the problem queue, the per-problem results and the control
+ * words live in one static device array of the library (8 KB + 72 B per problem = 4.5 MB, held by every GPU that loads the library
+ * until the process exits), so a call takes at most ARACHNE_KSW_STATIC_MAX_PROBLEMS problems and is refused with ARACHNE_ERR_ARG
+ * beyond that.  ALL pointers except opt are DEVICE pointers on `device`: q / t bases as codes 0..4, q_off / t_off n+1 offsets, h0 / w per
+ * problem; max_qlen an upper bound of the query lengths (1..ARACHNE_MAX_READ_LEN).  d_out: n x 6 ints as above ({-1 x 6} for a problem the
+ * kernels refuse: qlen outside 1..max_qlen, h0 <= 0, h0 + qlen * a > 8191); d_status: one int, 0 or 1 + the index of the first refused
+ * problem; d_cells: in-band cell count (may be NULL).  The work is queued on cuda_stream (NULL: the default stream) and the call returns
+ * without waiting.  Every call shares the static array: calls on one stream are safe, calls that OVERLAP on the GPU (other streams, other
+ * host threads) race. */
+#define ARACHNE_KSW_STATIC_MAX_PROBLEMS 65536
+int arachne_ksw_extend_static(int device, const arachne_mem_opt_t *opt, int64_t n, const uint8_t *d_q, const int64_t *d_q_off,
+                              const uint8_t *d_t, const int64_t *d_t_off, const int32_t *d_h0, const int32_t *d_w, int max_qlen,
+                              int end_bonus, int zdrop, int32_t *d_out, int32_t *d_status, uint64_t *d_cells, void *cuda_stream);
 /* Measured DPX issue peak of the device (independent 32-bit VIADDMNMX streams): the denominator of the extension kernel's roofline
  * (not in MEASURED_PEAKS.json).  gops = 1e9 viaddmax per second. */
 int arachne_dpx_peak(int device, double *gops, float *kernel_ms);
