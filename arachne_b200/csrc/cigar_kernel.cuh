@@ -230,50 +230,73 @@ __device__ __forceinline__ int band_gen_cigar(const MemOpt& opt, const RegView& 
     }
     const int w = cig_eff_w(opt, lq, rlen, w_);
     if (w > BAND_WMAX || rlen > z_rows) return -1;
-    // ksw_global2 (ksw.c:504-606): eh[j] = {H(i-1,j-1), E(i,j)} lives in ring slot j & 63.  The slot also carries the
-    // query base of column j (low 3 bits of .y, E above them), so the cell loop has no global load: a column's base is
-    // fetched once, when the sliding band first reaches it.  "-infinity" is -2^26 here instead of the reference's -2^30
-    // so that E survives the 3-bit shift; only differences between sentinel-derived values and the order between those and
-    // real scores (|score| < 2^12) ever matter, and both are unchanged.
-    constexpr int NEG = -(1 << 26);
+    // ksw_global2 (ksw.c:504-606): eh[j] = {H(i-1,j-1), E(i,j)} lives in ring slot j & 63: .x = H, .y = E << 16 | selector.
+    // The selector (q * 0x1111 + 0x8880: "byte q, sign-replicated") is a ready-made PRMT selector into the row's substitution
+    // scores {s(tb,0..3) in one register, s(N) = -1 in another}, so a cell's score is one instruction and the cell loop has no
+    // global load: a column's base is fetched once, when the sliding band first reaches it.
+    // "-infinity": -2^26 for H and F, -2^14 for the 16-bit E (the reference: -2^30).  Only two things about sentinels ever
+    // matter -- that anything derived from one stays below every real score, and that a real cell's choice between a real and
+    // a sentinel candidate goes to the real one; comparisons between two sentinel-derived values only set direction bits the
+    // backtrack never reads (it reaches a cell's E / F bit only through a real E / F).  Real scores are above
+    // -(len * (b + 2e) + 2o) and a sentinel drifts down by at most e per row and column; the guard below keeps both well
+    // inside 16 bits, anything else is tier 3's.
+    constexpr int NEG = -(1 << 26), NEGE = -(1 << 14);
     const int e_del = opt.e_del, e_ins = opt.e_ins, oe_del = opt.o_del + opt.e_del, oe_ins = opt.o_ins + opt.e_ins;
+    {
+        const int lmax = lq > rlen ? lq : rlen, emax = e_del > e_ins ? e_del : e_ins, omax = opt.o_del > opt.o_ins ? opt.o_del : opt.o_ins;
+        if (lmax * (opt.b + 2 * emax + opt.a) + 2 * omax + (2 * w + 2) * emax > 6000) return -1;
+    }
     const uint8_t* qp = v.rev ? v.q + v.qe - 1 : v.q + v.qb;
     const int qs = v.rev ? -1 : 1;
+    auto slot_y = [](int e, int q) -> int { return (int)(((unsigned)e << 16) | (unsigned)((q > 4 ? 4 : q) * 0x1111 + 0x8880)); };
     for (int j = 0; j <= lq && j <= w + 1; ++j) {
         const int qb = j < lq ? qp[j * qs] : 0;
-        ring[j & (BAND_RING - 1)][tid] = make_int2(j == 0 ? 0 : (j <= w ? -(opt.o_ins + e_ins * j) : NEG), (NEG << 3) | qb);
+        ring[j & (BAND_RING - 1)][tid] = make_int2(j == 0 ? 0 : (j <= w ? -(opt.o_ins + e_ins * j) : NEG), slot_y(NEGE, qb));
     }
+    const unsigned mis4 = (unsigned)(-opt.b & 0xff) * 0x01010101u, lut_hi = 0xffu;  // s(N, .) = -1 (bwa_fill_scmat)
     // direction codes: 8 cells per 32-bit word, lane-interleaved: word k of row i of lane t at z32[(i*8 + k)*T] (z32 already offset by t)
     for (int i = 0; i < rlen; ++i) {
-        const int tb = v.T(i);
+        const int tb = v.T(i) & 3;
+        const unsigned lut_lo = (mis4 & ~(0xffu << (tb << 3))) | ((unsigned)(opt.a & 0xff) << (tb << 3));
         const int beg = i > w ? i - w : 0, end = i + w + 1 < lq ? i + w + 1 : lq;
         const int qnext = end < lq ? qp[end * qs] : 0;  // base of the column the band reaches in the next row
         int f = NEG, left = beg == 0 ? -(opt.o_del + e_del * (i + 1)) : NEG;
         unsigned* zi = z32 + (long)i * (2 * BAND_ZCHUNK) * T;
+#define BAND_CELL(slot_, u_)                                                                    \
+    {                                                                                           \
+        const int2 he = (slot_);                                                                \
+        int sc_;                                                                                \
+        asm("prmt.b32 %0, %1, %2, %3;" : "=r"(sc_) : "r"(lut_lo), "r"(lut_hi), "r"(he.y));      \
+        const int m = he.x + sc_;                                                               \
+        int e = he.y >> 16, h, x;                                                               \
+        unsigned d = m >= e ? 0u : 1u; h = m >= e ? m : e;                                      \
+        if (h < f) { d = 2u; h = f; }                                                           \
+        x = m - oe_del; e -= e_del;                                                             \
+        if (e > x) d |= 4u; else e = x;                                                         \
+        (slot_) = make_int2(left, (int)__byte_perm((unsigned)he.y, (unsigned)e, 0x5410));       \
+        left = h;                                                                               \
+        x = m - oe_ins; f -= e_ins;                                                             \
+        if (f > x) d |= 8u; else f = x;                                                         \
+        acc |= d << (4 * (u_));                                                                 \
+    }
         for (int j0 = beg; j0 < end; j0 += 8) {
             unsigned acc = 0;
+            const int s0 = j0 & (BAND_RING - 1);
+            if (j0 + 8 <= end && s0 <= BAND_RING - 8) {  // a full group that does not wrap: constant slot offsets, no per-cell test
+                int2* rp = &ring[s0][tid];
 #pragma unroll
-            for (int u = 0; u < 8; ++u) {
-                const int j = j0 + u;
-                if (j < end) {
-                    const int2 he = ring[j & (BAND_RING - 1)][tid];
-                    const int qb = he.y & 7;
-                    const int m = he.x + ((qb > 3) ? -1 : (qb == tb ? opt.a : -opt.b));
-                    int e = he.y >> 3, h, x;
-                    unsigned d = m >= e ? 0u : 1u; h = m >= e ? m : e;
-                    if (h < f) { d = 2u; h = f; }
-                    x = m - oe_del; e -= e_del;
-                    if (e > x) d |= 4u; else e = x;
-                    ring[j & (BAND_RING - 1)][tid] = make_int2(left, (e << 3) | qb);
-                    left = h;
-                    x = m - oe_ins; f -= e_ins;
-                    if (f > x) d |= 8u; else f = x;
-                    acc |= d << (4 * u);
+                for (int u = 0; u < 8; ++u) BAND_CELL(rp[u * CIG_BLOCK], u)
+            } else {
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    const int j = j0 + u;
+                    if (j < end) BAND_CELL(ring[j & (BAND_RING - 1)][tid], u)
                 }
             }
             zi[(long)((j0 - beg) >> 3) * T] = acc;
         }
-        ring[end & (BAND_RING - 1)][tid] = make_int2(left, (NEG << 3) | qnext);
+#undef BAND_CELL
+        ring[end & (BAND_RING - 1)][tid] = make_int2(left, slot_y(NEGE, qnext));
         *cells += end > beg ? end - beg : 0;
     }
     *score = ring[lq & (BAND_RING - 1)][tid].x;
