@@ -168,17 +168,6 @@ constexpr int EXT_WARPS = 4;
 // a rescue SW get private copies with room to grow (each mem_matesw call adds at most one region).
 constexpr unsigned long long RESC_FLAG = 1ull << 63;
 
-__device__ __forceinline__ bool matesw_would_run(const RefView& ref, const PeStat pes[4], const AlnReg& a, const AlnReg* ma, int n_ma) {
-    int skip[4];
-    for (int r = 0; r < 4; ++r) skip[r] = pes[r].failed ? 1 : 0;
-    for (int i = 0; i < n_ma; ++i) {
-        int64_t dist;
-        int r = infer_dir(ref.l_pac, a.rb, ma[i].rb, &dist);
-        if (dist >= pes[r].low && dist <= pes[r].high) skip[r] = 1;
-    }
-    return skip[0] + skip[1] + skip[2] + skip[3] != 4;
-}
-
 __global__ void __launch_bounds__(EXT_WARPS * 32) k_rescue(MemOpt opt, RefView ref, int score_delta, const uint8_t* __restrict__ seq,
                                                            const int64_t* __restrict__ off, int n_pairs, const unsigned long long* __restrict__ sa_off,
                                                            AlnReg* regs, int* n_regs, unsigned long long* reg_loc, AlnReg* resc,
@@ -209,10 +198,10 @@ __global__ void __launch_bounds__(EXT_WARPS * 32) k_rescue(MemOpt opt, RefView r
         bool need = false;
         if (l1 > 0)
             for (int i = 0, num = 0; i < n2 && num < 50 && !need; ++i)
-                if (r2[i].score >= best2 - score_delta) { ++num; need = matesw_would_run(ref, pes, r2[i], r1, n1); }
+                if (r2[i].score >= best2 - score_delta) { ++num; need = rescue_open_classes(ref.l_pac, pes, r2[i], r1, n1) != 0; }
         if (l2 > 0)
             for (int i = 0, num = 0; i < n1 && num < 50 && !need; ++i)
-                if (r1[i].score >= best1 - score_delta) { ++num; need = matesw_would_run(ref, pes, r1[i], r2, n2); }
+                if (r1[i].score >= best1 - score_delta) { ++num; need = rescue_open_classes(ref.l_pac, pes, r1[i], r2, n2) != 0; }
         if (!need) continue;
         const int cap1 = n1 + 50, cap2 = n2 + 50;
         unsigned long long pos = 0;

@@ -18,115 +18,150 @@ AR_HD void gobwa_pestat(PeStat pes[4]) {  // gobwa.go:229-237
     pes[1].low = -35; pes[1].high = 500; pes[1].failed = 0; pes[1].avg = 200.0; pes[1].std = 100.0;
 }
 
-AR_HD int infer_dir(int64_t l_pac, int64_t b1, int64_t b2, int64_t* dist) {
-    int r1 = (b1 >= l_pac), r2 = (b2 >= l_pac);
-    int64_t p2 = r1 == r2 ? b2 : (l_pac << 1) - 1 - b2;
-    *dist = p2 > b1 ? p2 - b1 : b1 - p2;
-    return (r1 == r2 ? 0 : 1) ^ (p2 > b1 ? 0 : 3);
+// Relative placement of a mate hit against an anchor hit, both given by their start in forward-reverse coordinates: the mate is
+// mirrored onto the anchor's strand when the two lie on different strands, then `cls` = bit 0: different strands, bit 1: mate start
+// not beyond the anchor's -- XOR-folded the way mem_infer_dir numbers its four classes (bwamem_pair.c:23-30: FF / FR / RF / RR as
+// 0..3) -- and `dist` the distance between the two starts.
+struct PairGeom { int cls; int64_t dist; };
+AR_HD PairGeom pair_geometry(int64_t l_pac, int64_t anchor_rb, int64_t mate_rb) {
+    const bool same_strand = (anchor_rb >= l_pac) == (mate_rb >= l_pac);
+    const int64_t m = same_strand ? mate_rb : 2 * l_pac - 1 - mate_rb;
+    PairGeom g;
+    g.cls = (same_strand ? 0 : 1) ^ (m > anchor_rb ? 0 : 3);
+    g.dist = m > anchor_rb ? m - anchor_rb : anchor_rb - m;
+    return g;
+}
+
+// Bit r set = orientation class r has a usable insert model and none of the mate's n_ma hits sits at a distance the model accepts
+// from the anchor: the classes mem_matesw runs a Smith-Waterman for (bwamem_pair.c:116-124).  0 = nothing to rescue; k_rescue asks
+// this first so that pairs with nothing to do (most) never get a private copy of their lists.
+AR_HD unsigned rescue_open_classes(int64_t l_pac, const PeStat pes[4], const AlnReg& anchor, const AlnReg* ma, int n_ma) {
+    unsigned open = 0;
+    for (int r = 0; r < 4; ++r) open |= (pes[r].failed ? 0u : 1u) << r;
+    for (int i = 0; i < n_ma && open; ++i) {
+        const PairGeom g = pair_geometry(l_pac, anchor.rb, ma[i].rb);
+        if (g.dist >= pes[g.cls].low && g.dist <= pes[g.cls].high) open &= ~(1u << g.cls);
+    }
+    return open;
 }
 
 constexpr int KSW_XBYTE = 0x10000, KSW_XSTOP = 0x20000, KSW_XSUBO = 0x40000, KSW_XSTART = 0x80000;
 
 struct LocalAln { int score, te, qe, score2, te2, tb, qb; };
 
-// mem_matesw: try to find the mate `ms` near anchor `a`; ma/n_ma is the mate's region list (capacity cap).
-// rbuf: window buffer of >= rcap bytes.  Returns the number of SW runs, or a negative error.
+// Where a mate of l_ms bases in orientation class `cls` can lie around an anchor that starts at anchor_rb: its start is low..high
+// away, ahead of the anchor for classes 0 / 1 and behind it for 2 / 3; a mate on the anchor's strand (classes 0, 3) extends the
+// window by its length at the far end, a mate on the other strand (1, 2: it is searched reverse-complemented) at the near end.
+// Clipped to the forward-reverse text; the caller clips to the contig.  (bwamem_pair.c:136-144)
+struct RefWindow { int64_t beg, end; };
+AR_HD RefWindow rescue_window(int cls, bool mate_rc, const PeStat& pe, int64_t anchor_rb, int l_ms, int64_t l_pac) {
+    const bool ahead = cls < 2;
+    RefWindow w;
+    w.beg = ahead ? anchor_rb + pe.low : anchor_rb - pe.high;
+    w.end = ahead ? anchor_rb + pe.high : anchor_rb - pe.low;
+    if (mate_rc) w.beg -= l_ms; else w.end += l_ms;
+    if (w.beg < 0) w.beg = 0;
+    if (w.end > 2 * l_pac) w.end = 2 * l_pac;
+    return w;
+}
+
+// The region a rescue hit becomes (bwamem_pair.c:151-163): everything zero except the spans, score, csub, the anchor's contig and ALT
+// flag, secondary = -1 and seedcov = half the shorter span.  A reverse-complemented mate's spans are mirrored back.
+AR_HD AlnReg rescued_region(const AlnReg& anchor, const LocalAln& aln, bool mate_rc, int64_t win_beg, int l_ms, int64_t l_pac) {
+    AlnReg b;
+    b.truesc = b.sub = b.alt_sc = b.sub_n = b.w = b.secondary_all = b.seedlen0 = 0; b.frac_rep = 0.f; b.hash = 0;
+    b.rid = anchor.rid;
+    b.n_comp_is_alt = anchor.n_comp_is_alt & ~0x3fffffff;  // is_alt copied, n_comp = 0
+    const int q_lo = aln.qb, q_hi = aln.qe + 1;
+    const int64_t t_lo = win_beg + aln.tb, t_hi = win_beg + aln.te + 1;
+    b.qb = mate_rc ? l_ms - q_hi : q_lo;
+    b.qe = mate_rc ? l_ms - q_lo : q_hi;
+    b.rb = mate_rc ? 2 * l_pac - t_hi : t_lo;
+    b.re = mate_rc ? 2 * l_pac - t_lo : t_hi;
+    b.score = aln.score;
+    b.csub = aln.score2;
+    b.secondary = -1;
+    const int64_t r_span = b.re - b.rb, q_span = b.qe - b.qb;
+    b.seedcov = (int)((r_span < q_span ? r_span : q_span) >> 1);
+    return b;
+}
+
+// mem_matesw (bwamem_pair.c:111-180): look for the mate `ms` near anchor `a` in every orientation class that is still open;
+// ma / n_ma is the mate's region list (capacity cap, kept in descending score order).  rbuf: window buffer of >= rcap bytes.
+// Returns the number of SW runs, or a negative error.
 template <class Ctx>
 AR_HD int matesw(Ctx& ctx, const MemOpt& opt, const RefView& ref, const PeStat pes[4], const AlnReg& a, int l_ms, const uint8_t* ms,
                  AlnReg* ma, int* n_ma, int cap, uint8_t* rbuf, int rcap) {
     const int64_t l_pac = ref.l_pac;
-    int i, r, skip[4], n = 0;
-    for (r = 0; r < 4; ++r) skip[r] = pes[r].failed ? 1 : 0;
-    for (i = 0; i < *n_ma; ++i) {
-        int64_t dist;
-        r = infer_dir(l_pac, a.rb, ma[i].rb, &dist);
-        if (dist >= pes[r].low && dist <= pes[r].high) skip[r] = 1;
-    }
-    if (skip[0] + skip[1] + skip[2] + skip[3] == 4) return 0;
-    for (r = 0; r < 4; ++r) {
-        if (skip[r]) continue;
-        int is_rev = (r >> 1 != (r & 1));
-        int is_larger = !(r >> 1);
-        int64_t rb, re;
-        int rid = -1;
-        if (!is_rev) {
-            rb = is_larger ? a.rb + pes[r].low : a.rb - pes[r].high;
-            re = (is_larger ? a.rb + pes[r].high : a.rb - pes[r].low) + l_ms;
-        } else {
-            rb = (is_larger ? a.rb + pes[r].low : a.rb - pes[r].high) - l_ms;
-            re = is_larger ? a.rb + pes[r].high : a.rb - pes[r].low;
-        }
-        if (rb < 0) rb = 0;
-        if (re > l_pac << 1) re = l_pac << 1;
-        if (rb < re) rid = fetch_window(ref, &rb, (rb + re) >> 1, &re);
-        if (a.rid == rid && re - rb >= opt.min_seed_len) {
-            if (re - rb > rcap) return -2;
-            ctx.fetch_ref(ref, rb, re, rbuf);
-            int xtra = KSW_XSUBO | KSW_XSTART | (l_ms * opt.a < 250 ? KSW_XBYTE : 0) | (opt.min_seed_len * opt.a);
+    const unsigned open = rescue_open_classes(l_pac, pes, a, ma, *n_ma);
+    if (!open) return 0;
+    int n_sw = 0;
+    for (int cls = 0; cls < 4; ++cls) {
+        if (!(open >> cls & 1)) continue;
+        const bool mate_rc = cls == 1 || cls == 2;  // the mate lies on the other strand: it enters the SW reverse-complemented
+        RefWindow w = rescue_window(cls, mate_rc, pes[cls], a.rb, l_ms, l_pac);
+        const int rid = w.beg < w.end ? fetch_window(ref, &w.beg, (w.beg + w.end) >> 1, &w.end) : -1;
+        if (rid == a.rid && w.end - w.beg >= opt.min_seed_len) {
+            if (w.end - w.beg > rcap) return -2;
+            ctx.fetch_ref(ref, w.beg, w.end, rbuf);
+            const int xtra = KSW_XSUBO | KSW_XSTART | (l_ms * opt.a < 250 ? KSW_XBYTE : 0) | (opt.min_seed_len * opt.a);
             LocalAln aln;
-            // the mate enters reverse-complemented when is_rev (bwamem_pair.c:131-135)
-            ctx.ksw_local(opt, l_ms, ms, is_rev, (int)(re - rb), rbuf, xtra, &aln);
+            ctx.ksw_local(opt, l_ms, ms, mate_rc, (int)(w.end - w.beg), rbuf, xtra, &aln);
+            ++n_sw;
             if (aln.score >= opt.min_seed_len && aln.qb >= 0) {
-                AlnReg b;
-                b.truesc = b.sub = b.alt_sc = b.sub_n = b.w = b.secondary_all = b.seedlen0 = 0; b.frac_rep = 0.f; b.hash = 0;
-                b.rid = a.rid;
-                b.n_comp_is_alt = a.n_comp_is_alt & ~0x3fffffff;  // is_alt copied, n_comp = 0
-                b.qb = is_rev ? l_ms - (aln.qe + 1) : aln.qb;
-                b.qe = is_rev ? l_ms - aln.qb : aln.qe + 1;
-                b.rb = is_rev ? (l_pac << 1) - (rb + aln.te + 1) : rb + aln.tb;
-                b.re = is_rev ? (l_pac << 1) - (rb + aln.tb) : rb + aln.te + 1;
-                b.score = aln.score;
-                b.csub = aln.score2;
-                b.secondary = -1;
-                b.seedcov = (int)((b.re - b.rb < b.qe - b.qb ? b.re - b.rb : b.qe - b.qb) >> 1);
                 if (*n_ma >= cap) return -3;
-                int nn = *n_ma + 1, pos;
-                for (pos = 0; pos < nn - 1; ++pos)
-                    if (ma[pos].score < b.score) break;
+                const AlnReg b = rescued_region(a, aln, mate_rc, w.beg, l_ms, l_pac);
+                int at = 0;  // in front of the first hit that scores less
+                while (at < *n_ma && ma[at].score >= b.score) ++at;
+                ctx.sync();  // every lane has read the list before the leader shifts it
                 if (ctx.leader()) {
-                    for (i = nn - 1; i > pos; --i) ma[i] = ma[i - 1];
-                    ma[pos] = b;
+                    for (int k = *n_ma; k > at; --k) ma[k] = ma[k - 1];
+                    ma[at] = b;
                 }
-                *n_ma = nn;
+                ++*n_ma;
                 ctx.sync();
             }
-            ++n;
         }
-        if (n) {
-            int m = sort_dedup_patch(ctx, opt, ref, (const uint8_t*)nullptr, *n_ma, ma, rbuf, rcap);
+        if (n_sw) {  // once any SW has run, the list is de-duplicated after every class (bwamem_pair.c:175)
+            const int m = sort_dedup_patch(ctx, opt, ref, (const uint8_t*)nullptr, *n_ma, ma, rbuf, rcap);
             if (m < 0) return m;
             *n_ma = m;
         }
     }
-    return n;
+    return n_sw;
 }
 
-// GoBwaMemMateSW after the two mem_align1_core calls.  r1/r2 are the reads' region lists with room for cap1/cap2.
+// One direction of GoBwaMemMateSW's rescue (gobwa.go:285-300 / 302-324): every anchor among the first n_anchor entries of `anchors`
+// that scores within score_delta of `best` -- at most 50 of them -- gets a mem_matesw call for the mate.  Only the mate's list changes; the
+// anchors' list is the other read's and stays as it is for the whole walk.
+template <class Ctx>
+AR_HD int rescue_from(Ctx& ctx, const MemOpt& opt, const RefView& ref, const PeStat pes[4], int score_delta, const AlnReg* anchors, int n_anchor,
+                      int best, int l_mate, const uint8_t* mate, AlnReg* mate_regs, int* n_mate, int cap, uint8_t* rbuf, int rcap) {
+    if (l_mate <= 0) return 0;
+    for (int i = 0, tried = 0; i < n_anchor && tried < 50; ++i) {
+        if (anchors[i].score < best - score_delta) continue;
+        ++tried;
+        const AlnReg anchor = anchors[i];
+        const int rc = matesw(ctx, opt, ref, pes, anchor, l_mate, mate, mate_regs, n_mate, cap, rbuf, rcap);
+        if (rc < 0) return rc;
+    }
+    return 0;
+}
+
+// GoBwaMemMateSW after the two mem_align1_core calls.  r1/r2 are the reads' region lists with room for cap1/cap2.  Both best scores
+// are taken BEFORE any rescue (gobwa.go:264-283): read 2's rescue still filters read 1's grown list by read 1's old best.
 template <class Ctx>
 AR_HD int pair_rescue(Ctx& ctx, const MemOpt& opt, const RefView& ref, int score_delta, int l1, const uint8_t* s1, int l2, const uint8_t* s2,
                       AlnReg* r1, int* n1, int cap1, AlnReg* r2, int* n2, int cap2, uint8_t* rbuf, int rcap) {
     PeStat pes[4];
     gobwa_pestat(pes);
-    int best1 = 0, best2 = 0, i, num, rc;
-    for (i = 0; i < *n1; ++i) if (r1[i].score > best1) best1 = r1[i].score;
-    for (i = 0; i < *n2; ++i) if (r2[i].score > best2) best2 = r2[i].score;
-    const int n2_0 = *n2;  // the Go loop walks the pre-rescue list of read 2 (gobwa.go:285-300); r2 is not modified here
-    for (i = 0, num = 0; i < n2_0 && num < 50 && l1 > 0; ++i)
-        if (r2[i].score >= best2 - score_delta) {
-            ++num;
-            const AlnReg anchor = r2[i];
-            rc = matesw(ctx, opt, ref, pes, anchor, l1, s1, r1, n1, cap1, rbuf, rcap);
-            if (rc < 0) return rc;
-        }
-    const int n1_1 = *n1;  // read 1's list after its own rescue (gobwa.go:302-324); r1 is not modified here
-    for (i = 0, num = 0; i < n1_1 && num < 50 && l2 > 0; ++i)
-        if (r1[i].score >= best1 - score_delta) {
-            ++num;
-            const AlnReg anchor = r1[i];
-            rc = matesw(ctx, opt, ref, pes, anchor, l2, s2, r2, n2, cap2, rbuf, rcap);
-            if (rc < 0) return rc;
-        }
-    return 0;
+    int best1 = 0, best2 = 0;
+    for (int i = 0; i < *n1; ++i) best1 = r1[i].score > best1 ? r1[i].score : best1;
+    for (int i = 0; i < *n2; ++i) best2 = r2[i].score > best2 ? r2[i].score : best2;
+    // read 1 is looked for around read 2's hits, then read 2 around read 1's hits INCLUDING the ones just rescued
+    int rc = rescue_from(ctx, opt, ref, pes, score_delta, r2, *n2, best2, l1, s1, r1, n1, cap1, rbuf, rcap);
+    if (rc < 0) return rc;
+    return rescue_from(ctx, opt, ref, pes, score_delta, r1, *n1, best1, l2, s2, r2, n2, cap2, rbuf, rcap);
 }
 
 }  // namespace arachne

@@ -110,6 +110,41 @@ def test_hostsim_pipeline_golden(HS, workdir, name):
     assert n_cig > 50
 
 
+def test_hostsim_pipeline_live(HS, workdir):
+    """The host build of the chaining / extension-driver / de-duplication / mate-rescue code against the reference's own C code on
+    freshly simulated pairs (needs oracle/_ref): wrecked mates that only rescue can place, and pairs re-arranged so that their hits
+    fall into each of mem_infer_dir's four orientation classes (same strand, swapped order, both)."""
+    from oracle.refbwa import RefBwa, available
+    if not available():
+        pytest.skip("oracle/_ref not built")
+    fa, ctg, rs = util.make_dataset("rep600k", workdir, damaged=True)
+    R = RefBwa().load(fa); HS.load(fa)
+    n_pairs = min(800, rs.n_pairs)
+    reads = [rs.seq[rs.off[i]:rs.off[i + 1]].copy() for i in range(2 * n_pairs)]
+    rc = lambda s: np.where(s[::-1] < 4, 3 - s[::-1], 4).astype(np.uint8)
+    for p in range(n_pairs):
+        k = p % 8
+        if k == 5: reads[2 * p + 1] = rc(reads[2 * p + 1])                       # both mates on one strand
+        elif k == 6: reads[2 * p], reads[2 * p + 1] = reads[2 * p + 1], reads[2 * p]  # order swapped
+        elif k == 7: reads[2 * p] = rc(reads[2 * p])                             # the other same-strand arrangement
+    seq, off = util.pack(reads)
+    ref = R.batch(seq, off, rescue=True, cigar=False, threads=4)
+    plain = R.batch(seq, off, rescue=False, cigar=False, threads=4)
+    assert ref["regs"].tobytes() != plain["regs"].tobytes(), "dataset does not exercise rescue"
+    from arachne_b200.lib import ALNREG
+    exp = ref["regs"].view(ALNREG); ro = ref["reg_off"]
+    exp1 = plain["regs"].view(ALNREG); ro1 = plain["reg_off"]
+    n_rescued = 0
+    for p in range(n_pairs):
+        for k in (2 * p, 2 * p + 1):
+            assert HS.align1(reads[k]).tobytes() == exp1[ro1[k]:ro1[k + 1]].tobytes(), ("align1", k)
+        o1, o2 = HS.pair(reads[2 * p], reads[2 * p + 1])
+        for k, got in ((2 * p, o1), (2 * p + 1, o2)):
+            assert got.tobytes() == exp[ro[k]:ro[k + 1]].tobytes(), ("pair", k)
+            n_rescued += int(ro[k + 1] - ro[k] != ro1[k + 1] - ro1[k])
+    assert n_rescued >= 10, n_rescued
+
+
 def test_hostsim_seed_intervals_live(HS, workdir):
     """mem_collect_intv restated from bwt_smem1 / bwt_seed_strategy1 calls on the reference's code (needs oracle/_ref)."""
     from oracle.refbwa import RefBwa, available
