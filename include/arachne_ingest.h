@@ -37,8 +37,10 @@ typedef struct {
     void *priv;
 } arachne_ingest_batch_t;
 
-/* r1 / r2: FASTQ files, gzip-compressed or plain, barcode-sorted, headers `@name/1 BX:Z:<barcode> VX:i:<0|1> [...]`.
- * n_threads: parser threads (<= 0: 4); two more threads decompress and split the files. */
+/* r1 / r2: FASTQ files, barcode-sorted, headers `@name/1 BX:Z:<barcode> VX:i:<0|1> [...]`; each file plain text, gzip (one zlib
+ * stream per file: the slow case) or BGZF / bgzip (blocks inflated by up to n_threads threads per file); told apart by their first bytes.
+ * n_threads: parser threads (<= 0: 4); two more threads read and split the files.  A read or format error in either file is returned
+ * by the arachne_ingest_next call that reaches it.  ARACHNE_INGEST_STATS=1 prints the CPU seconds of every pipeline step at close. */
 int arachne_ingest_open(const char *r1, const char *r2, int n_threads, arachne_ingest_t **out);
 /* The next batch: whole work units, as many as it takes to reach target_pairs pairs (at least one unit).
  * ARACHNE_OK, ARACHNE_INGEST_EOF when the input is exhausted (*out NULL), or a negative ARACHNE_ERR_*. */

@@ -340,7 +340,19 @@ def _reader_go(r1_lines, r2_lines):
     return recs, units
 
 
-@pytest.mark.parametrize("gz", [False, True])
+def _bgzf_bytes(data: bytes, block: int, level: int = 1) -> bytes:
+    """`data` as a BGZF file (SAM spec 4.1): gzip members of at most `block` input bytes with the BC extra field + the EOF marker."""
+    import struct, zlib
+    out = []
+    for i in range(0, len(data), block):
+        d = data[i:i + block]
+        c = zlib.compressobj(level, zlib.DEFLATED, -15); comp = c.compress(d) + c.flush()
+        out.append(struct.pack("<BBBBIBBHBBHH", 0x1f, 0x8b, 8, 4, 0, 0, 0xff, 6, 66, 67, 2, len(comp) + 25) + comp + struct.pack("<II", zlib.crc32(d), len(d)))
+    out.append(bytes.fromhex("1f8b08040000000000ff0600424302001b0003000000000000000000"))
+    return b"".join(out)
+
+
+@pytest.mark.parametrize("gz", [False, True, "bgzf", "bgzf_small", "members"])
 def test_ingest_matches_reader_go(tmp_path, gz):
     import gzip, hashlib
     from arachne_b200 import Ingest
@@ -353,6 +365,8 @@ def test_ingest_matches_reader_go(tmp_path, gz):
         for _ in range(n):
             L1 = int(g.integers(30, 152)); L2 = int(g.integers(30, 152))
             s1 = "".join("ACGTNacgt-"[int(x)] for x in g.integers(0, 10 if k % 50 == 0 else 4, L1)); s2 = "".join("ACGT"[int(x)] for x in g.integers(0, 4, L2))
+            if k % 97 == 5:                    # every byte value a sequence line can hold, in a shuffled order (the 16-at-a-time base conversion)
+                s1 = "".join(chr(int(x)) for x in g.permutation([c for c in range(1, 256) if c != 10])[:L1])
             q1 = "".join(chr(33 + int(x)) for x in g.integers(0, 41, L1)); q2 = "".join(chr(33 + int(x)) for x in g.integers(0, 41, L2))
             tag = "" if bc == "NOBX" else "\tBX:Z:%s\tVX:i:%d" % (bc, 0 if k % 7 == 3 else 1)
             tail = "\tRG:sample:lib:%d" % (k % 3) if k % 2 else ""
@@ -360,8 +374,15 @@ def test_ingest_matches_reader_go(tmp_path, gz):
             k += 1
     p1, p2 = str(tmp_path / ("r1.fq" + (".gz" if gz else ""))), str(tmp_path / ("r2.fq" + (".gz" if gz else "")))
     for p, lines in ((p1, r1), (p2, r2)):
-        with (gzip.open(p, "wt") if gz else open(p, "w")) as f:
-            f.write("".join(lines))
+        text = "".join(lines).encode("latin-1")
+        if gz in ("bgzf", "bgzf_small"):       # bgzip-style blocks (inflated by a team of threads); 0xff00 is bgzip's block size
+            blob = _bgzf_bytes(text, 0xff00 if gz == "bgzf" else 777)
+        elif gz == "members":                  # a gzip file of several members without the BC field: the zlib stream path
+            blob = b"".join(gzip.compress(text[i:i + 200_000]) for i in range(0, len(text), 200_000))
+        else:
+            blob = gzip.compress(text, 1) if gz else text
+        with open(p, "wb") as f:
+            f.write(blob)
     recs, units = _reader_go(r1, r2)
     nt4 = np.full(256, 4, np.uint8)
     for i, c in enumerate("ACGT"):
@@ -387,7 +408,7 @@ def test_ingest_matches_reader_go(tmp_path, gz):
                     assert b["names"][i] == name and b["read_groups"][i] == rg
                     assert b["rand_seed"][i] == int.from_bytes(hashlib.md5(name.encode()).digest()[:8], "little", signed=True)
                     o = b["off"][2 * i:2 * i + 3]
-                    assert np.array_equal(b["seq"][o[0]:o[1]], nt4[np.frombuffer(s1.encode(), np.uint8)]) and np.array_equal(b["seq"][o[1]:o[2]], nt4[np.frombuffer(s2.encode(), np.uint8)])
+                    assert np.array_equal(b["seq"][o[0]:o[1]], nt4[np.frombuffer(s1.encode("latin-1"), np.uint8)]) and np.array_equal(b["seq"][o[1]:o[2]], nt4[np.frombuffer(s2.encode(), np.uint8)])
                     assert b["quals"][2 * i] == q1 and b["quals"][2 * i + 1] == q2
                 pair += b["n_pairs"]
                 if target != 10**9 and pair > 200:
@@ -398,6 +419,48 @@ def test_ingest_matches_reader_go(tmp_path, gz):
         assert 30000 in sizes and sizes.count(201) == 2 and any(not f for _, _, f in units)
     finally:
         I.close()
+
+
+def test_ingest_bad_inputs_fail_loudly(tmp_path):
+    """A truncated or corrupted BGZF file, a record that does not start with '@' and a missing file are errors, never silent short reads."""
+    from arachne_b200 import Ingest
+    from arachne_b200.lib import ArachneError
+    rec = lambda k, m: "@r%d/%d\tBX:Z:A01C02B03D04-1\tVX:i:1\nACGTACGTAC\n+\nIIIIIIIIII\n" % (k, m)
+    good1 = "".join(rec(k, 1) for k in range(3000)).encode(); good2 = "".join(rec(k, 2) for k in range(3000)).encode()
+    blob = _bgzf_bytes(good1, 4096)
+    cases = {"truncated": blob[:len(blob) // 2 + 11], "crc": blob[:200] + bytes([blob[200] ^ 0x55]) + blob[201:], "garbage_after": blob[:4000] + b"not a block at all, just text" * 3}
+    p2 = str(tmp_path / "r2.fq"); open(p2, "wb").write(good2)
+    for name, data in cases.items():
+        p1 = str(tmp_path / (name + ".fq.gz")); open(p1, "wb").write(data)
+        I = Ingest(p1, p2, n_threads=2)
+        try:
+            with pytest.raises(ArachneError):
+                while I.next(1000) is not None:
+                    pass
+        finally:
+            I.close()
+    bad = str(tmp_path / "bad.fq"); open(bad, "wb").write(good1[:500] + b"oops\n" + good1[500:])
+    I = Ingest(bad, p2, n_threads=2)
+    try:
+        with pytest.raises(ArachneError, match="malformed FASTQ"):
+            while I.next(1000) is not None:
+                pass
+    finally:
+        I.close()
+    with pytest.raises(ArachneError):
+        Ingest(str(tmp_path / "missing.fq"), p2)
+    # the good pair, for contrast, reads to the end: 3000 pairs in one unit of one barcode
+    ok = str(tmp_path / "ok.fq.gz"); open(ok, "wb").write(blob)
+    I = Ingest(ok, p2, n_threads=2); n = 0
+    try:
+        while True:
+            b = I.next(1000)
+            if b is None:
+                break
+            n += b["n_pairs"]
+    finally:
+        I.close()
+    assert n == 3000
 
 
 # ---- rows a15-a20: does the order of equal positions in sort.Sort(ByPosition) (Go's unstable pdqsort, aligner.go:1477-1479) reach any output? ----
