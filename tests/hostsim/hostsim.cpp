@@ -245,4 +245,12 @@ int hs_reg2aln(void* h_, int len, const uint8_t* seq, const arachne_alnreg_t* re
     for (int i = 0; i < a.n_mm; ++i) { mm[i] = m[i]; mm[a.n_mm + i] = m[len + i]; }
     return 0;
 }
+
+// ks_introsort (csrc/common.cuh) with the two region orders of mem_sort_dedup_patch: 0 = by re (alnreg_slt2, bwamem.c:390-392),
+// 1 = by score desc, rb, qb (alnreg_slt, :393-395).  The permutation of equal keys is what the test compares with the reference's.
+void hs_introsort_regs(int mode, int n, arachne_alnreg_t* a_) {
+    AlnReg* a = (AlnReg*)a_;
+    if (mode == 0) ks_introsort((size_t)n, a, [](const AlnReg& x, const AlnReg& y) { return x.re < y.re; });
+    else ks_introsort((size_t)n, a, [](const AlnReg& x, const AlnReg& y) { return x.score > y.score || (x.score == y.score && (x.rb < y.rb || (x.rb == y.rb && x.qb < y.qb))); });
+}
 }

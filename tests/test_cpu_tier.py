@@ -60,6 +60,29 @@ def test_oracle_ksw_local_golden(O):
         assert util.orc_local(O, q, t, int(d["loc_x"][i])) == tuple(d["loc_out"][i]), i
 
 
+def test_oracle_edge_kats_golden(O):
+    """Targeted known answers of the reference (tests/golden/ksw_edge.npz, scripts/make_golden.py::edge_problems; SURVEY 8c): rows that die
+    at once, z-drop after a good prefix, 7..40-base insertions / deletions under bands 1..256, N bases, 1-base and empty operands, stale
+    eh[] columns, tandem repeats; the u8 / i16 switch of the mate-rescue kernel at 249 / 250 bases with >= 7-base gap blocks, second
+    copies and homopolymers; global-alignment traceback ties."""
+    d = util.load_golden("ksw_edge")
+    n_zdrop = 0
+    for i, (q, t) in enumerate(_problems(d, "ext")):
+        h0, w, zd, eb = (int(x) for x in d["ext_par"][i])
+        got, _ = util.orc_extend(O, q, t, w, eb, zd, h0)
+        assert got == tuple(d["ext_out"][i]), (i, got, tuple(d["ext_out"][i]))
+        if zd == 10:
+            n_zdrop += got != util.orc_extend(O, q, t, w, eb, 0, h0)[0]
+    assert n_zdrop >= 10  # the z-drop cases really take the z-drop exit
+    for i, (q, t) in enumerate(_problems(d, "loc")):
+        assert util.orc_local(O, q, t, int(d["loc_x"][i])) == tuple(d["loc_out"][i]), i
+    assert {len(q) for q, _ in _problems(d, "loc")} == {248, 249, 250, 251}
+    co = d["glb_co"]
+    for i, (q, t) in enumerate(_problems(d, "glb")):
+        sc, cig = util.orc_global(O, q, t, int(d["glb_w"][i]))
+        assert sc == d["glb_score"][i] and cig == list(d["glb_cig"][co[i]:co[i + 1]]), i
+
+
 def test_oracle_vs_reference_live(O):
     """Fresh random problems against the reference's compiled sources (skipped where oracle/_ref is absent)."""
     from oracle.refbwa import RefBwa, available
@@ -108,6 +131,22 @@ def test_hostsim_pipeline_golden(HS, workdir, name):
                     assert np.array_equal(cig, d["s7_cigar"][e[5]:e[5] + e[4]]), j
                     n_cig += 1
     assert n_cig > 50
+
+
+def test_hostsim_introsort_tie_permutations(HS):
+    """The order klib's introsort leaves EQUAL keys in is observable (which of two equal-score regions survives de-duplication, which chain
+    is extended first).  The product's ks_introsort (csrc/common.cuh) against the permutations the reference's own ks_introsort_mem_ars2 /
+    _mem_ars produced on tie-heavy arrays of 0..5000 regions (tests/golden/introsort.npz, scripts/make_golden.py::introsort_cases)."""
+    sys.path.insert(0, os.path.join(ROOT, "scripts"))
+    from make_golden import introsort_cases
+    d = util.load_golden("introsort")
+    cases = introsort_cases(); k = 0
+    for mode in (0, 1):
+        for a in cases:
+            got = HS.introsort_regs(mode, a)["hash"]
+            assert np.array_equal(got, d["perm"][d["perm_off"][k]:d["perm_off"][k + 1]]), (mode, len(a))
+            k += 1
+    assert k == len(d["perm_off"]) - 1
 
 
 def test_hostsim_pipeline_live(HS, workdir):

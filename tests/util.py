@@ -155,7 +155,13 @@ class HostSim:
         L.hs_pair.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint8), C.c_int, C.POINTER(C.c_uint8), C.c_int, C.c_void_p, C.POINTER(C.c_int),
                               C.c_void_p, C.POINTER(C.c_int), C.c_int]
         L.hs_reg2aln.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint8), C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32), C.c_int, C.POINTER(C.c_int32)]
+        L.hs_introsort_regs.argtypes = [C.c_int, C.c_int, C.c_void_p]
         self.h = None
+
+    def introsort_regs(self, mode, regs):
+        out = regs.copy()
+        self.lib.hs_introsort_regs(mode, len(out), out.ctypes.data_as(C.c_void_p))
+        return out
 
     def load(self, prefix):
         self.h = L = self.lib.hs_load(prefix.encode())
