@@ -149,6 +149,42 @@ def test_hostsim_introsort_tie_permutations(HS):
     assert k == len(d["perm_off"]) - 1
 
 
+def test_hostsim_chain_level_live(HS, workdir):
+    """Rows a7 / a8 at their own level: the chains csrc/chain.cuh forms and keeps -- every chain's pos, contig, seed count, weight and
+    `kept` class, every seed, frac_rep, in the reference's order -- against the reference's own mem_chain / mem_chain_flt (needs
+    oracle/_ref).  An exact-repeat reference gives reads dozens of chains (B-tree splits, equal keys, equal weights: the tie
+    permutations of the weight sort), the diverged-repeat one the shadowing / drop rules."""
+    from oracle.refbwa import RefBwa, available
+    if not available():
+        pytest.skip("oracle/_ref not built")
+    from arachne_b200 import simulate as S
+    fa, ctg, rs = util.make_dataset("rep600k", workdir, damaged=True)
+    sets = [(fa, [rs.seq[rs.off[i]:rs.off[i + 1]] for i in range(0, 1200)])]
+    xfa = os.path.join(workdir, "xrep.fa")
+    xctg = util.exact_repeat_reference()
+    if not os.path.exists(xfa + ".bwt"):
+        S.write_fasta(xfa, xctg); RefBwa().build_index(xfa)
+    xrs = S.simulate_linked_reads(xctg, n_barcodes=30, seed=77, sub=0.01, ins=0.001, dele=0.001)
+    sets.append((xfa, [xrs.seq[xrs.off[i]:xrs.off[i + 1]] for i in range(min(1200, 2 * xrs.n_pairs))]))
+    most, n_multi, n_dropped = 0, 0, 0
+    for prefix, reads in sets:
+        R = RefBwa().load(prefix); HS.load(prefix)
+        for k, q in enumerate(reads):
+            raw = None
+            for flt in (False, True):
+                ech, esd, efr = R.mem_chain(q, do_flt=flt)
+                gch, gsd, gfr = HS.chain(q, do_flt=flt)
+                assert np.array_equal(gch, ech) and np.array_equal(gsd, esd), (prefix, k, flt, gch[:4], ech[:4])
+                if len(ech):
+                    assert gfr == efr, (prefix, k, gfr, efr)
+                if not flt:
+                    raw = len(ech)
+                else:
+                    n_dropped += raw > len(ech)
+            most = max(most, raw); n_multi += raw > 9
+    assert most >= 20 and n_multi >= 20 and n_dropped >= 20, (most, n_multi, n_dropped)  # B-tree deeper than its root; the filter really drops
+
+
 def test_hostsim_pipeline_live(HS, workdir):
     """The host build of the chaining / extension-driver / de-duplication / mate-rescue code against the reference's own C code on
     freshly simulated pairs (needs oracle/_ref): wrecked mates that only rescue can place, and pairs re-arranged so that their hits
@@ -167,13 +203,13 @@ def test_hostsim_pipeline_live(HS, workdir):
         elif k == 6: reads[2 * p], reads[2 * p + 1] = reads[2 * p + 1], reads[2 * p]  # order swapped
         elif k == 7: reads[2 * p] = rc(reads[2 * p])                             # the other same-strand arrangement
     seq, off = util.pack(reads)
-    ref = R.batch(seq, off, rescue=True, cigar=False, threads=4)
+    ref = R.batch(seq, off, rescue=True, cigar=True, threads=4)
     plain = R.batch(seq, off, rescue=False, cigar=False, threads=4)
     assert ref["regs"].tobytes() != plain["regs"].tobytes(), "dataset does not exercise rescue"
     from arachne_b200.lib import ALNREG
     exp = ref["regs"].view(ALNREG); ro = ref["reg_off"]
     exp1 = plain["regs"].view(ALNREG); ro1 = plain["reg_off"]
-    n_rescued = 0
+    n_rescued = n_cig = n_gapped = 0
     for p in range(n_pairs):
         for k in (2 * p, 2 * p + 1):
             assert HS.align1(reads[k]).tobytes() == exp1[ro1[k]:ro1[k + 1]].tobytes(), ("align1", k)
@@ -181,7 +217,14 @@ def test_hostsim_pipeline_live(HS, workdir):
         for k, got in ((2 * p, o1), (2 * p + 1, o2)):
             assert got.tobytes() == exp[ro[k]:ro[k + 1]].tobytes(), ("pair", k)
             n_rescued += int(ro[k + 1] - ro[k] != ro1[k + 1] - ro1[k])
-    assert n_rescued >= 10, n_rescued
+            if p % 2 == 0:  # mem_reg2aln + the GetAlignments walk of every region of every second pair (csrc/cigar.cuh, the warp tier's logic)
+                for j in range(ro[k], ro[k + 1]):
+                    a, cig, _mm = HS.reg2aln(reads[k], exp[j:j + 1])
+                    e = ref["aln"][j]
+                    assert (a["pos"], a["rid"], a["is_rev"], a["nm"], a["n_cigar"], a["score"], a["sub"]) == (e[0], e[1], e[2], e[3], e[4], e[6], e[7]), j
+                    assert np.array_equal(cig, ref["cigar"][e[5]:e[5] + e[4]]), j
+                    n_cig += 1; n_gapped += len(cig) > 1 and bool(np.any((cig & 0xf) != 0) and np.any((cig & 0xf) == 1) | np.any((cig & 0xf) == 2))
+    assert n_rescued >= 10 and n_cig >= 500 and n_gapped >= 20, (n_rescued, n_cig, n_gapped)
 
 
 def test_hostsim_seed_intervals_live(HS, workdir):

@@ -156,7 +156,16 @@ class HostSim:
                               C.c_void_p, C.POINTER(C.c_int), C.c_int]
         L.hs_reg2aln.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint8), C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32), C.c_int, C.POINTER(C.c_int32)]
         L.hs_introsort_regs.argtypes = [C.c_int, C.c_int, C.c_void_p]
+        L.hs_chain.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint8), C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_float)]
         self.h = None
+
+    def chain(self, q, do_flt=False, cap=4096):
+        """csrc/chain.cuh on the host: chain rows {pos, rid, n, w, kept, first_seed_row}, seed rows {rbeg, qbeg, len, score}, frac_rep."""
+        q, qp = u8p(q)
+        ch = np.zeros((cap, 6), dtype=np.int64); sd = np.zeros((cap * 4, 4), dtype=np.int64); ns = C.c_int(0); fr = C.c_float(0)
+        n = self.lib.hs_chain(self.h, len(q), qp, int(do_flt), ch.ctypes.data_as(C.c_void_p), cap, sd.ctypes.data_as(C.c_void_p), cap * 4, C.byref(ns), C.byref(fr))
+        assert 0 <= n <= cap and ns.value <= cap * 4, (n, ns.value)
+        return ch[:n], sd[:ns.value], fr.value
 
     def introsort_regs(self, mode, regs):
         out = regs.copy()
