@@ -294,7 +294,7 @@ struct arachne_ingest {
     std::vector<std::thread> threads;
     // parsed chunks, re-ordered by index
     std::mutex take_mu;  // chunk i of both files is popped by one thread at a time
-    std::mutex pmu; std::condition_variable pcv; std::map<long, Parsed> parsed; long next_parse = 0, next_take = 0; bool parse_done = false;
+    std::mutex pmu; std::condition_variable pcv; std::map<long, Parsed> parsed; long next_parse = 0, next_take = 0; std::atomic<bool> parse_done{false};  // set under take_mu by the parsers, under pmu at close
     int split_rc[2] = {0, 0}; std::string split_err[2];
     // assembler state (ReadBarcodeSet's)
     Parsed cur; int cur_pos = 0; bool have_cur = false, eof = false;

@@ -50,6 +50,18 @@ class RefBwa:
         L.ref_bwt_sa.restype = C.c_uint64; L.ref_bwt_sa.argtypes = [C.c_void_p, C.c_uint64]
         L.ref_bwt_2occ4.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
         L.ref_bwt_meta.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
+        # every entry that takes the index handle declares its arguments: an undeclared Python int is passed as a 32-bit C int, which
+        # only worked while the handle happened to lie in the low heap (found by running the suite under the ASan allocator)
+        u8, i64, u64, i32 = C.POINTER(C.c_uint8), C.POINTER(C.c_int64), C.POINTER(C.c_uint64), C.POINTER(C.c_int)
+        L.ref_smem1.argtypes = [C.c_void_p, C.c_int, u8, C.c_int, C.c_int, u64, C.c_int, i32]
+        L.ref_seed_strategy1.argtypes = [C.c_void_p, C.c_int, u8, C.c_int, C.c_int, C.c_int, u64]
+        L.ref_mem_chain.argtypes = [C.c_void_p, C.c_int, u8, C.c_int, i64, C.c_int, i64, C.c_int, i32, C.POINTER(C.c_float)]
+        L.ref_align1.argtypes = [C.c_void_p, C.c_int, u8, C.c_void_p, C.c_int]
+        L.ref_pair.argtypes = [C.c_void_p, C.c_int, u8, C.c_int, u8, C.c_int, C.c_int, C.c_void_p, C.c_int, i32, C.c_void_p, C.c_int, i32]
+        L.ref_reg2aln.argtypes = [C.c_void_p, C.c_int, u8, C.c_void_p, i64, C.POINTER(C.c_uint32), C.c_int]
+        L.ref_ksw_extend2.argtypes = [C.c_int, u8, C.c_int, u8, C.c_int, C.c_int, C.c_int, C.c_int, i32]
+        L.ref_ksw_global2.argtypes = [C.c_int, u8, C.c_int, u8, C.c_int, i32, C.POINTER(C.c_uint32), C.c_int]
+        L.ref_ksw_align2.argtypes = [C.c_int, u8, C.c_int, u8, C.c_int, i32]
         assert L.ref_sizeof_alnreg() == 88
         self.idx = None
 

@@ -145,7 +145,7 @@ class HostSim:
     def __init__(self):
         d = os.path.join(ROOT, "tests", "hostsim")
         subprocess.run(["make", "-s", "-C", d], check=True, stdout=subprocess.DEVNULL)
-        L = self.lib = C.CDLL(os.path.join(d, "libhostsim.so"))
+        L = self.lib = C.CDLL(os.environ.get("ARACHNE_HOSTSIM_LIB") or os.path.join(d, "libhostsim.so"))  # override: the sanitizer build (scripts/hostsim_sanitize.sh)
         L.hs_load.restype = C.c_void_p; L.hs_load.argtypes = [C.c_char_p]
         L.hs_free.argtypes = [C.c_void_p]
         L.hs_occ.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
@@ -413,7 +413,7 @@ def hostsim_index_build(pac_bytes, l_pac, batch_cap=0):
     """The product's index-construction driver (csrc/index_build.cuh) on the TEST-ONLY host backend -> the bytes of
     <prefix>.bwt and <prefix>.sa as bwt_dump_bwt / bwt_dump_sa lay them out (bwa/bwt.c:385-409) + driver statistics."""
     HostSim()  # builds libhostsim.so
-    H = C.CDLL(os.path.join(ROOT, "tests", "hostsim", "libhostsim.so"))
+    H = C.CDLL(os.environ.get("ARACHNE_HOSTSIM_LIB") or os.path.join(ROOT, "tests", "hostsim", "libhostsim.so"))
     H.hostsim_index_build.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]
     n = 2 * l_pac
     buf = np.zeros(l_pac // 4 + 16, np.uint8)
