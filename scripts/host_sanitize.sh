@@ -42,3 +42,8 @@ for san in address,undefined thread; do
     echo "exit code $?"; grep "ingest ok\|ingest bad" "$W/ingest_$san.log"
     echo "sanitizer reports: $(grep -c 'WARNING: ThreadSanitizer\|ERROR: AddressSanitizer\|runtime error' "$W/ingest_$san.log")"
 done
+echo "== build + run: the whole library with its HOST code under ASan + UBSan (nvcc -Xcompiler -fsanitize=...), CPU tier against it"
+nvcc -gencode arch=compute_100a,code=sm_100a -O1 -g -std=c++17 -shared -Xcompiler -fPIC,-fsanitize=address,-fsanitize=undefined,-fno-sanitize-recover=undefined,-fno-omit-frame-pointer \
+    -Iinclude -o "$W/libarachne_asan.so" arachne_b200/csrc/*.cu -lz -lasan -lubsan || exit 1
+ARACHNE_LIB="$W/libarachne_asan.so" ASAN_OPTIONS=detect_leaks=0:protect_shadow_gap=0 UBSAN_OPTIONS=print_stacktrace=1 LD_PRELOAD=$ASAN \
+    python -m pytest tests/ -q -m "not gpu" -p no:cacheprovider -k "not gloo" 2>&1 | grep -v "site-packages\|<frozen" | tail -8
