@@ -429,8 +429,8 @@ def run_reference(args, rank, world):
             times.append(dt)
     ms = 1e3 * sum(times) / len(times)
     val = npairs / (ms / 1e3)
-    line = base_line(args, 1, val, ms)
-    line["config"]["reference_arm_step"] = f"{npairs} pairs per step (a bounded sample of the arm's {args.pairs}-pair step: same generator, same work-unit rule)"
+    line = base_line(args, world, val, ms)  # `config` is the arm's own, word for word; what the CPU step really was is said beside it
+    line["reference_arm_step"] = f"{npairs} pairs per step (a bounded sample of the arm's {args.pairs}-pair step: same generator, same work-unit rule); rank 0's host cores only"
     line.update({"impl": "reference", "dtype": "int32", "n_gpus": args.gpus,
                  "cpu_baseline": {"value": val, "unit": "pairs/s", "cores": threads, "kind": "reference",
                                   "sample": f"{npairs} pairs per step of the same workload (oracle/_ref: the reference's BWA C sources, gobwa.go call sequence, {threads} pthreads over pairs)"},
