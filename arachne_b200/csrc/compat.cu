@@ -90,6 +90,8 @@ static void run_batch(arachne_compat* c, std::vector<Request*>& reqs) {
         reqs[p]->block = b;
     }
     if (out) arachne_batch_free(out);
+    if (rc != ARACHNE_OK)  // all or nothing: a caller that gets an error code never sees (and could never release) a block
+        for (Request* r : reqs) { free(r->block); r->block = nullptr; }
     for (Request* r : reqs) r->rc = rc;
 }
 

@@ -47,3 +47,9 @@ nvcc -gencode arch=compute_100a,code=sm_100a -O1 -g -std=c++17 -shared -Xcompile
     -Iinclude -o "$W/libarachne_asan.so" arachne_b200/csrc/*.cu -lz -lasan -lubsan || exit 1
 ARACHNE_LIB="$W/libarachne_asan.so" ASAN_OPTIONS=detect_leaks=0:protect_shadow_gap=0 UBSAN_OPTIONS=print_stacktrace=1 LD_PRELOAD=$ASAN \
     python -m pytest tests/ -q -m "not gpu" -p no:cacheprovider -k "not gloo" 2>&1 | grep -v "site-packages\|<frozen" | tail -8
+echo "== build + run: the gobwa-shaped layer (csrc/compat.cu) over the mock batch backend with -fsanitize=thread, 64 caller threads"
+( cd tests/hostsim && g++ -O1 -g -std=c++17 -fPIC -shared -fsanitize=thread -Wno-subobject-linkage -I/usr/local/cuda/include -x c++ compat_mock.cpp \
+    -o "$W/libcompat_mock_tsan.so" -L../../oracle/_ref -lbwa_ref -Wl,-rpath,"$ROOT/oracle/_ref" -lpthread ) || exit 1
+ARACHNE_COMPAT_MOCK_LIB="$W/libcompat_mock_tsan.so" TSAN_OPTIONS="report_signal_unsafe=0 exitcode=0" LD_PRELOAD=$TSAN \
+    python -m pytest tests/test_cpu_tier.py -q -k "compat_layer" -p no:cacheprovider > "$W/compat_tsan.log" 2>&1
+tail -1 "$W/compat_tsan.log"; echo "sanitizer reports: $(grep -c 'WARNING: ThreadSanitizer' "$W/compat_tsan.log")"

@@ -267,6 +267,74 @@ def test_hostsim_seed_intervals_live(HS, workdir):
         assert [a[3] for a in got.tolist()] == [a[3] for a in exp], r
 
 
+# ---- the gobwa-shaped layer's own logic (csrc/compat.cu is host code) over a mock batch backend served by the reference's C code ----
+def test_compat_layer_batching_logic_on_mock_backend(workdir):
+    """64 threads make per-pair GoBwaMemMateSW + per-candidate GoBwaSmithWaterman calls (the reference's worker goroutines): every region array,
+    mem_aln_t field and CIGAR word equals the reference's own per-pair results; calls were batched and batches overlapped (two leaders at
+    once); a region stays addressable until its block is released and not after; a failing batch gives every caller of that batch the error
+    and leaves no block behind.  The same layer runs over the GPU in tests/test_gpu_parity.py; scripts/host_sanitize.sh runs THIS under TSan."""
+    from concurrent.futures import ThreadPoolExecutor
+    from oracle.refbwa import RefBwa, available
+    if not available():
+        pytest.skip("oracle/_ref not built")
+    from arachne_b200.lib import Compat, ArachneError
+    fa, ctg, rs = util.make_dataset("rep600k", workdir, damaged=True)
+    R = RefBwa().load(fa)
+    n = min(rs.n_pairs, 1200)
+    ref = R.batch(rs.seq, rs.off, rescue=True, cigar=True, threads=8)
+    B = util.CompatMockBackend(fa)
+    K = Compat(B, max_batch_pairs=48, max_wait_us=1500)
+    try:
+        def one(p):
+            r1 = np.ascontiguousarray(rs.seq[rs.off[2 * p]:rs.off[2 * p + 1]]); r2 = np.ascontiguousarray(rs.seq[rs.off[2 * p + 1]:rs.off[2 * p + 2]])
+            g1, g2, a1, a2, owner = K.mem_mate_sw(r1, r2, 25)
+            alns = [K.reg2aln(base + 88 * k) for base, g in ((a1, g1), (a2, g2)) for k in range(len(g))]
+            return p, g1, g2, alns, owner, (a1 or a2)
+        with ThreadPoolExecutor(64) as ex:
+            out = list(ex.map(one, range(n)))
+        st = K.stats()
+        assert st["n_calls"] == n and st["n_batches"] < n // 4 and 8 < st["max_batch"] <= 48 and st["n_live_blocks"] == n, st
+        assert B.lib.mock_max_batches_in_flight() >= 2  # while one leader's batch runs, the next leader is already collecting / running
+        e = ref["aln"]
+        for p, g1, g2, alns, owner, _ in out:
+            lo, mid, hi = (int(ref["reg_off"][2 * p + k]) for k in range(3))
+            assert g1.tobytes() == ref["regs"][lo:mid].tobytes() and g2.tobytes() == ref["regs"][mid:hi].tobytes(), p
+            assert len(alns) == hi - lo
+            for k, a in enumerate(alns):
+                x = e[lo + k]
+                assert (a["pos"], a["rid"], a["is_rev"], a["nm"], a["n_cigar"], a["score"], a["sub"]) == (x[0], x[1], x[2], x[3], x[4], x[6], x[7]), (p, k)
+                assert np.array_equal(a["cigar"], ref["cigar"][x[5]:x[5] + x[4]]), (p, k)
+        # lifetime: still addressable after everything else ran, gone once released; an address inside a block but off a record boundary is refused
+        p, _, _, alns, owner, addr = next(o for o in out if o[5])
+        again = K.reg2aln(addr)
+        assert again["pos"] == alns[0]["pos"] and np.array_equal(again["cigar"], alns[0]["cigar"])
+        with pytest.raises(ArachneError):
+            K.reg2aln(addr + 8)
+        K.release(owner)
+        with pytest.raises(ArachneError):
+            K.reg2aln(addr)
+        for o in out:
+            if o[4] is not owner:
+                K.release(o[4])
+        assert K.stats()["n_live_blocks"] == 0
+        # a failing batch: every caller of it gets the error, nobody a block
+        B.lib.mock_fail_next_batches(1)
+        def attempt(p):
+            try:
+                one(p); return True
+            except ArachneError:
+                return False
+        with ThreadPoolExecutor(16) as ex:
+            ok = list(ex.map(attempt, range(16)))
+        st2 = K.stats()
+        assert not all(ok) and st2["n_live_blocks"] == sum(ok), (ok, st2)
+        # GetSeq = bns_fetch_seq with its clamp
+        got, b, en, rid = K.fetch_seq(100, 250, 400)
+        assert (b, en, rid) == (100, 400, 0) and len(got) == 300 and got.max() <= 3
+    finally:
+        K.close(); B.close()
+
+
 # ---- C ABI surface ----
 # ---- index construction (csrc/index_build.cuh on the host backend) vs the reference's own `bwa index` output ----
 @pytest.mark.parametrize("name", ["tiny_rand", "tiny_rep"])

@@ -217,6 +217,34 @@ class HostSim:
         return a, np.array(cig[:a["n_cigar"]], dtype=np.uint32), np.array(mm[:2 * a["n_mm"]], dtype=np.int32)
 
 
+class CompatMockBackend:
+    """tests/hostsim/libcompat_mock.so: csrc/compat.cu (the gobwa-shaped layer, host code) over batch entry points served by the reference's
+    own C code.  Quacks like ArachneCuda as far as arachne_b200.lib.Compat needs (lib, idx, opt, _ck)."""
+
+    def __init__(self, prefix):
+        from arachne_b200.lib import MemOpt, ArachneError
+        d = os.path.join(ROOT, "tests", "hostsim")
+        if not os.environ.get("ARACHNE_COMPAT_MOCK_LIB"):
+            subprocess.run(["make", "-s", "-C", d, "libcompat_mock.so"], check=True, stdout=subprocess.DEVNULL)
+        L = self.lib = C.CDLL(os.environ.get("ARACHNE_COMPAT_MOCK_LIB") or os.path.join(d, "libcompat_mock.so"))
+        L.arachne_last_error.restype = C.c_char_p
+        L.mock_index_open.restype = C.c_void_p; L.mock_index_open.argtypes = [C.c_char_p]
+        L.mock_index_close.argtypes = [C.c_void_p]
+        L.arachne_opts_default.argtypes = [C.POINTER(MemOpt)]
+        L.mock_fail_next_batches.argtypes = [C.c_int]
+        self._err = ArachneError
+        self.idx = C.c_void_p(L.mock_index_open(prefix.encode()))
+        assert self.idx
+        self.opt = MemOpt(); assert L.arachne_opts_default(C.byref(self.opt)) == 0
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise self._err("%d: %s" % (rc, self.lib.arachne_last_error().decode()))
+
+    def close(self):
+        self.lib.mock_index_close(self.idx)
+
+
 def orc_local(O, q, t, xtra):
     q, qp = u8p(q); t, tp = u8p(t); out = (C.c_int * 7)()
     O.orc_local(C.byref(DEFAULT_SC), len(q), qp, len(t), tp, xtra, out)
