@@ -53,3 +53,8 @@ echo "== build + run: the gobwa-shaped layer (csrc/compat.cu) over the mock batc
 ARACHNE_COMPAT_MOCK_LIB="$W/libcompat_mock_tsan.so" TSAN_OPTIONS="report_signal_unsafe=0 exitcode=0" LD_PRELOAD=$TSAN \
     python -m pytest tests/test_cpu_tier.py -q -k "compat_layer" -p no:cacheprovider > "$W/compat_tsan.log" 2>&1
 tail -1 "$W/compat_tsan.log"; echo "sanitizer reports: $(grep -c 'WARNING: ThreadSanitizer' "$W/compat_tsan.log")"
+echo "== build + run: the whole library with its HOST code under ThreadSanitizer; preprocess / ingest / pack / ABI tests of the CPU tier against it"
+nvcc -gencode arch=compute_100a,code=sm_100a -O1 -g -std=c++17 -shared -Xcompiler -fPIC,-fsanitize=thread -Iinclude -o "$W/libarachne_tsan.so" arachne_b200/csrc/*.cu -lz -ltsan || exit 1
+ARACHNE_LIB="$W/libarachne_tsan.so" TSAN_OPTIONS="report_signal_unsafe=0 exitcode=0" LD_PRELOAD=$TSAN python -m pytest tests/test_preprocess.py tests/test_cpu_tier.py -q -m "not gpu" \
+    -p no:cacheprovider -k "preprocess or standardize or ingest or pack or abi or header" > "$W/lib_tsan.log" 2>&1
+tail -1 "$W/lib_tsan.log"; echo "sanitizer reports: $(grep -c 'WARNING: ThreadSanitizer' "$W/lib_tsan.log")"
