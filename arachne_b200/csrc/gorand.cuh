@@ -13,12 +13,21 @@
 
 namespace arachne {
 
+// AR_GR_FN / AR_GR_M: under nvcc exactly the qualifiers this code has always had; the TEST-ONLY host simulation (tests/hostsim, which
+// defines ARACHNE_HOSTSIM) compiles the same generator with plain inline functions and host copies of the two tables.
 #if defined(__CUDACC__)
 __device__ const uint64_t d_gorand_cooked[607] = GORAND_TABLE_INIT;
 __device__ const uint32_t d_gorand_pw[3 * 607] = GORAND_PW_INIT;
+#define AR_GR_FN __device__ __forceinline__
+#define AR_GR_M __device__
+#elif defined(ARACHNE_HOSTSIM)
+static const uint64_t d_gorand_cooked[607] = GORAND_TABLE_INIT;
+static const uint32_t d_gorand_pw[3 * 607] = GORAND_PW_INIT;
+#define AR_GR_FN inline
+#define AR_GR_M
+#endif
 #define GORAND_COOKED d_gorand_cooked
 #define GORAND_PW d_gorand_pw
-#endif
 
 constexpr int GORAND_LEN = 607, GORAND_TAP = 273;
 constexpr uint32_t GORAND_M31 = 2147483647u;
@@ -37,29 +46,29 @@ AR_HD uint32_t gorand_mulmod(uint32_t a, uint32_t b) {  // a*b mod 2^31-1 (== Sc
     return p == GORAND_M31 ? 0u : (uint32_t)p;
 }
 
-#if defined(__CUDACC__)
-__device__ __forceinline__ uint64_t gorand_word(uint32_t s, int j) {  // seeded state word j
+#if defined(__CUDACC__) || defined(ARACHNE_HOSTSIM)
+AR_GR_FN uint64_t gorand_word(uint32_t s, int j) {  // seeded state word j
     const uint64_t x0 = gorand_mulmod(s, GORAND_PW[3 * j]), x1 = gorand_mulmod(s, GORAND_PW[3 * j + 1]), x2 = gorand_mulmod(s, GORAND_PW[3 * j + 2]);
     return ((x0 << 40) ^ (x1 << 20) ^ x2) ^ GORAND_COOKED[j];
 }
 
-__device__ __forceinline__ double gorand_to_float(uint64_t u) { return (double)(int64_t)(u & 0x7fffffffffffffffull) / 9223372036854775808.0; }
+AR_GR_FN double gorand_to_float(uint64_t u) { return (double)(int64_t)(u & 0x7fffffffffffffffull) / 9223372036854775808.0; }
 
 struct GoRandDev {
     uint32_t s;
     int n;            // outputs consumed
     uint64_t* state;  // 607 words of global scratch, or nullptr while stateless
     int tap, feed;
-    __device__ void init(int64_t seed) { s = gorand_norm_seed(seed); n = 0; state = nullptr; tap = 0; feed = GORAND_LEN - GORAND_TAP; }
+    AR_GR_M void init(int64_t seed) { s = gorand_norm_seed(seed); n = 0; state = nullptr; tap = 0; feed = GORAND_LEN - GORAND_TAP; }
     // switch to the stateful generator positioned after the n outputs already taken
-    __device__ void materialise(uint64_t* scratch) {
+    AR_GR_M void materialise(uint64_t* scratch) {
         state = scratch;
         for (int j = 0; j < GORAND_LEN; ++j) state[j] = gorand_word(s, j);
         tap = 0; feed = GORAND_LEN - GORAND_TAP;
         const int done = n; n = 0;
         for (int i = 0; i < done; ++i) next_u64();
     }
-    __device__ uint64_t next_u64() {
+    AR_GR_M uint64_t next_u64() {
         if (state) {
             if (--tap < 0) tap += GORAND_LEN;
             if (--feed < 0) feed += GORAND_LEN;
@@ -71,10 +80,10 @@ struct GoRandDev {
         ++n;
         return x;
     }
-    __device__ bool stateless_ok(int more) const { return state != nullptr || n + more <= GORAND_TAP; }
+    AR_GR_M bool stateless_ok(int more) const { return state != nullptr || n + more <= GORAND_TAP; }
     // rand.Float64: retry when the quotient rounds to 1.0 (a retry consumes an output, so it is only taken statefully or
     // while the stateless window lasts)
-    __device__ double float64(bool* need_state) {
+    AR_GR_M double float64(bool* need_state) {
         for (;;) {
             if (!state && n >= GORAND_TAP) { *need_state = true; return 0.0; }
             double f = gorand_to_float(next_u64());

@@ -7,7 +7,9 @@
 #include <cstring>
 #include <string>
 #include <vector>
+#define ARACHNE_HOSTSIM 1
 #include "../../arachne_b200/csrc/bwt_image.h"
+#include "../../arachne_b200/csrc/gorand.cuh"
 #include "smem.cuh"
 #include "../../arachne_b200/csrc/ext_driver.cuh"
 #include "../../arachne_b200/csrc/rescue.cuh"
@@ -252,5 +254,22 @@ void hs_introsort_regs(int mode, int n, arachne_alnreg_t* a_) {
     AlnReg* a = (AlnReg*)a_;
     if (mode == 0) ks_introsort((size_t)n, a, [](const AlnReg& x, const AlnReg& y) { return x.re < y.re; });
     else ks_introsort((size_t)n, a, [](const AlnReg& x, const AlnReg& y) { return x.score > y.score || (x.score == y.score && (x.rb < y.rb || (x.rb == y.rb && x.qb < y.qb))); });
+}
+
+// The device's Go math/rand (csrc/gorand.cuh: stateless closed form for the first 273 outputs, materialised 607-word state after) as
+// k_place_tag drives it: Float64 outputs 0..n-1 of NewSource(seed), switching to the stateful generator after `switch_at` outputs
+// (0 = stateful from the start, as for pairs with many candidate combinations; >= 273 = only when the stateless window runs out).
+int hs_gorand_float64(int64_t seed, int n, int switch_at, double* out) {
+    std::vector<uint64_t> scratch(GORAND_LEN);
+    GoRandDev r; r.init(seed);
+    if (switch_at == 0) r.materialise(scratch.data());
+    for (int i = 0; i < n; ++i) {
+        if (!r.state && i == switch_at) r.materialise(scratch.data());
+        bool need = false;
+        double f = r.float64(&need);
+        if (need) { r.materialise(scratch.data()); need = false; f = r.float64(&need); if (need) return -1; }
+        out[i] = f;
+    }
+    return 0;
 }
 }

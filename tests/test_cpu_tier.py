@@ -133,6 +133,26 @@ def test_hostsim_pipeline_golden(HS, workdir, name):
     assert n_cig > 50
 
 
+def test_go_math_rand_pinned(HS):
+    """Row a17's noise source: Go's math/rand (ALFG 607 / 273 seeded through the Lehmer LCG) as the DEVICE computes it (csrc/gorand.cuh in the
+    host build: closed-form stateless outputs, the materialised state, the switch between them at any point) and as the oracle computes it,
+    against tests/golden/gorand_float64.json -- 700 Float64 outputs for 11 seeds (0, negative, beyond 2^31, the int64 extremes) from
+    scripts/gen_go_rng_table.py, whose generator is itself checked against Go's published outputs for NewSource(1)."""
+    import json
+    rows = json.load(open(os.path.join(util.GOLDEN, "gorand_float64.json")))
+    O = util.oracle_lib()
+    O.orc_gorand_float64.argtypes = [C.c_int64, C.c_int, C.POINTER(C.c_double)]
+    assert len(rows) == 11
+    for row in rows:
+        seed, exp = int(row[0]), [float.fromhex(x) for x in row[1:]]
+        out = (C.c_double * len(exp))(); O.orc_gorand_float64(seed, len(exp), out)
+        assert list(out) == exp, ("oracle", seed)
+        for switch_at in (0, 1, 100, 272, 273, 10**9):
+            assert HS.gorand_float64(seed, len(exp), switch_at) == exp, ("device code", seed, switch_at)
+    one = [float.fromhex(x) for x in rows[1][1:3]]
+    assert rows[1][0] == 1 and one == [0.6046602879796196, 0.9405090880450124]  # the values every Go programmer has seen
+
+
 def test_hostsim_introsort_tie_permutations(HS):
     """The order klib's introsort leaves EQUAL keys in is observable (which of two equal-score regions survives de-duplication, which chain
     is extended first).  The product's ks_introsort (csrc/common.cuh) against the permutations the reference's own ks_introsort_mem_ars2 /

@@ -156,6 +156,7 @@ class HostSim:
                               C.c_void_p, C.POINTER(C.c_int), C.c_int]
         L.hs_reg2aln.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint8), C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32), C.c_int, C.POINTER(C.c_int32)]
         L.hs_introsort_regs.argtypes = [C.c_int, C.c_int, C.c_void_p]
+        L.hs_gorand_float64.argtypes = [C.c_int64, C.c_int, C.c_int, C.POINTER(C.c_double)]
         L.hs_chain.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint8), C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_float)]
         self.h = None
 
@@ -166,6 +167,11 @@ class HostSim:
         n = self.lib.hs_chain(self.h, len(q), qp, int(do_flt), ch.ctypes.data_as(C.c_void_p), cap, sd.ctypes.data_as(C.c_void_p), cap * 4, C.byref(ns), C.byref(fr))
         assert 0 <= n <= cap and ns.value <= cap * 4, (n, ns.value)
         return ch[:n], sd[:ns.value], fr.value
+
+    def gorand_float64(self, seed, n, switch_at):
+        out = (C.c_double * n)()
+        assert self.lib.hs_gorand_float64(seed, n, switch_at, out) == 0
+        return list(out)
 
     def introsort_regs(self, mode, regs):
         out = regs.copy()
