@@ -292,52 +292,89 @@ extern "C" int arachne_index_pack(const char* fasta, const char* prefix_, int64_
     uint64_t rng = ((uint64_t)11 << 16) | 0x330e;  // srand48(11)
     uint8_t nt4[256]; memset(nt4, 4, 256); nt4[(int)'-'] = 5;
     for (int i = 0; i < 4; ++i) { nt4[(int)"ACGT"[i]] = (uint8_t)i; nt4[(int)"acgt"[i]] = (uint8_t)i; }
-    std::vector<char> buf(4 << 20);
-    std::string line; bool in_seq = false; int lasts = 0; bool eof = false;
-    auto put_base = [&](int ch) {
+    // kseq.h's reader, character for character (kseq.h:95-141 ks_getuntil2, :176-215 kseq_read): which bytes end up in a record's sequence
+    // depends on details such as "a trailing CR is dropped when the ACCUMULATED string is longer than one byte" and "only the first byte
+    // of a line is tested for '>', '+', '@'", and every byte that gets in is a base of the packed reference.
+    struct KStream {
+        gzFile f; std::vector<char> buf; int beg = 0, end = 0; bool at_eof = false, io_error = false;
+        bool refill() {
+            if (at_eof) return false;
+            const int got = gzread(f, buf.data(), (unsigned)buf.size());
+            if (got < 0) io_error = true;
+            beg = 0; end = got > 0 ? got : 0;
+            if (end == 0) { at_eof = true; return false; }
+            return true;
+        }
+        int getc() { if (beg >= end && !refill()) return -1; return (unsigned char)buf[beg++]; }
+        // Appends to str up to (not including) the next delimiter -- '\n' when `line`, any isspace byte otherwise -- and consumes the
+        // delimiter (*dret receives it).  False when nothing was left to read.
+        bool until(bool line, std::string& str, int* dret) {
+            bool gotany = false;
+            for (;;) {
+                if (beg >= end && !refill()) break;
+                int i = beg;
+                if (line) { const void* nl = memchr(buf.data() + beg, '\n', (size_t)(end - beg)); i = nl ? (int)(static_cast<const char*>(nl) - buf.data()) : end; }
+                else while (i < end && !isspace((unsigned char)buf[i])) ++i;
+                gotany = true;
+                str.append(buf.data() + beg, (size_t)(i - beg));
+                beg = i + 1;
+                if (i < end) { if (dret) *dret = (unsigned char)buf[i]; break; }
+            }
+            if (!gotany && at_eof) return false;
+            if (line && str.size() > 1 && str.back() == '\r') str.pop_back();
+            return true;
+        }
+    } ks;
+    ks.f = f; ks.buf.resize(4 << 20);
+    auto add_record = [&](const std::string& name, const std::string& comment, const std::string& seq) {  // add1, bntseq.c:227-273
+        Ann a; a.name = name; a.anno = comment.empty() ? std::string("(null)") : comment;
+        a.offset = anns.empty() ? 0 : anns.back().offset + anns.back().len; a.len = 0; a.n_ambs = 0;
+        anns.push_back(a);
         Ann& p = anns.back();
-        int c = nt4[(uint8_t)ch];
-        const int64_t i = p.len;
-        if (c >= 4) {
-            if (lasts == ch && !holes.empty()) ++holes.back().len;
-            else { holes.push_back({p.offset + i, 1, (char)ch}); ++p.n_ambs; }
-            rng = (0x5DEECE66Dull * rng + 0xB) & ((1ull << 48) - 1);  // lrand48()
-            c = (int)((rng >> 17) & 3);
+        int lasts = 0;
+        for (size_t k = 0; k < seq.size(); ++k) {
+            const int ch = (unsigned char)seq[k];
+            int c = nt4[ch];
+            if (c >= 4) {
+                if (lasts == ch && !holes.empty()) ++holes.back().len;
+                else { holes.push_back({p.offset + p.len, 1, (char)ch}); ++p.n_ambs; }
+                rng = (0x5DEECE66Dull * rng + 0xB) & ((1ull << 48) - 1);  // lrand48()
+                c = (int)((rng >> 17) & 3);
+            }
+            lasts = ch;
+            if ((l_pac & 3) == 0) pac.push_back(0);
+            pac[(size_t)(l_pac >> 2)] |= (uint8_t)(c << ((~l_pac & 3) << 1));
+            ++l_pac; ++p.len;
         }
-        lasts = ch;
-        if ((l_pac & 3) == 0) pac.push_back(0);
-        pac[(size_t)(l_pac >> 2)] |= (uint8_t)(c << ((~l_pac & 3) << 1));
-        ++l_pac; ++p.len;
     };
-    auto handle_line = [&](std::string& ln) {  // one line without its '\n'
-        if (!ln.empty() && (ln[0] == '>' || ln[0] == '@')) {
-            if (ln.size() > 1 && ln.back() == '\r') ln.pop_back();
-            size_t e = 1; while (e < ln.size() && !isspace((unsigned char)ln[e])) ++e;
-            Ann a; a.name = ln.substr(1, e - 1);
-            a.anno = e < ln.size() ? ln.substr(e + 1) : std::string();
-            if (a.anno.empty()) a.anno = "(null)";
-            a.offset = anns.empty() ? 0 : anns.back().offset + anns.back().len; a.len = 0; a.n_ambs = 0;
-            anns.push_back(a); in_seq = true; lasts = 0;
-            return;
+    int last_char = 0, c = 0;
+    std::string name, comment, seq, qual;
+    for (;;) {  // one kseq_read per trip
+        if (last_char == 0) {
+            while ((c = ks.getc()) != -1 && c != '>' && c != '@') {}
+            if (c == -1) break;
+            last_char = c;
         }
-        if (!in_seq || ln.empty()) return;
-        size_t n = ln.size();
-        if (n > 1 && ln[n - 1] == '\r') --n;  // KS_SEP_LINE strips one trailing '\r' (kseq.h:140)
-        for (size_t k = 0; k < n; ++k) put_base((unsigned char)ln[k]);
-    };
-    while (!eof) {
-        const int got = gzread(f, buf.data(), (unsigned)buf.size());
-        if (got < 0) { gzclose(f); set_error("read error in %s", fasta); return ARACHNE_ERR_IO; }
-        if (got == 0) { eof = true; break; }
-        const char* p = buf.data(); const char* end = p + got;
-        while (p < end) {
-            const char* nl = static_cast<const char*>(memchr(p, '\n', (size_t)(end - p)));
-            if (!nl) { line.append(p, (size_t)(end - p)); break; }
-            line.append(p, (size_t)(nl - p)); p = nl + 1;
-            handle_line(line); line.clear();
+        name.clear(); comment.clear(); seq.clear(); qual.clear();
+        if (!ks.until(false, name, &c)) break;
+        if (c != '\n') ks.until(true, comment, nullptr);
+        while ((c = ks.getc()) != -1 && c != '>' && c != '+' && c != '@') {
+            if (c == '\n') continue;
+            seq.push_back((char)c);
+            ks.until(true, seq, nullptr);
         }
+        if (c == '>' || c == '@') last_char = c;
+        if (c == '+') {  // a FASTQ record: its quality string must have the sequence's length, else the reference stops reading here
+            while ((c = ks.getc()) != -1 && c != '\n') {}
+            if (c == -1) break;
+            while (ks.until(true, qual, nullptr) && qual.size() < seq.size()) {}
+            last_char = 0;
+            if (qual.size() != seq.size()) break;
+        }
+        add_record(name, comment, seq);
+        if (c == -1) break;
     }
-    if (!line.empty()) handle_line(line);
+    if (ks.io_error) { gzclose(f); set_error("read error in %s", fasta); return ARACHNE_ERR_IO; }
     gzclose(f);
     if (anns.empty()) { set_error("%s holds no FASTA record", fasta); return ARACHNE_ERR_IO; }
     FILE* fp = fopen((prefix + ".pac").c_str(), "wb");

@@ -1,0 +1,124 @@
+#!/usr/bin/env python
+"""Time-boxed differential fuzzing of what runs without a GPU, each against the reference's own compiled C code (oracle/_ref):
+  ksw    the oracle's restatement of ksw_extend2 / ksw_global2 / ksw_align2 (the checker of the GPU DP tests) on random + adversarial problems
+  index  the index-construction driver (csrc/index_build.cuh on the test-only host backend) -> .bwt / .sa bytes vs `bwa index`
+  pack   arachne_index_pack -> .pac / .ann / .amb vs `bwa index` on FASTA with N runs, IUPAC codes, lower case, CRLF, odd line widths
+python scripts/cpu_fuzz.py [seconds per part=120] [first_seed=1] [parts=ksw,index,pack]   -> one JSON line; non-zero exit on the first divergence."""
+import json, os, shutil, sys, tempfile, time
+import numpy as np
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from arachne_b200 import ArachneCuda, simulate as S
+from oracle.refbwa import RefBwa
+from tests import util
+
+budget = float(sys.argv[1]) if len(sys.argv) > 1 else 120.0
+seed0 = int(sys.argv[2]) if len(sys.argv) > 2 else 1
+parts = (sys.argv[3] if len(sys.argv) > 3 else "ksw,index,pack").split(",")
+out = dict(first_seed=seed0)
+
+
+def fail(what, **kw):
+    print(json.dumps(dict(divergence=what, **kw, **out))); sys.exit(1)
+
+
+# ---- ksw ----
+O = util.oracle_lib(); R = RefBwa(); t0 = time.time(); n = 0; seed = seed0
+while "ksw" in parts and time.time() - t0 < budget:
+    g = np.random.default_rng(seed)
+    qs, ts, h0, w = util.extension_problems(seed, 300)
+    for i in range(len(qs)):
+        zd, eb = [(100, 5), (0, 0), (20, 5), (10, 0), (1, 0)][i % 5]
+        if util.orc_extend(O, qs[i], ts[i], int(w[i]), eb, zd, int(h0[i]))[0] != R.ksw_extend2(qs[i], ts[i], int(w[i]), eb, zd, int(h0[i])):
+            fail("ksw_extend2", seed=seed, i=i)
+        if len(ts[i]) and len(qs[i]):
+            ww = max(abs(len(ts[i]) - len(qs[i])) + 3, int(w[i]))
+            if util.orc_global(O, qs[i], ts[i], ww) != R.ksw_global2(qs[i], ts[i], ww):
+                fail("ksw_global2", seed=seed, i=i)
+        if i % 3 == 0 and len(qs[i]) >= 20 and len(ts[i]):
+            L = len(qs[i]); xtra = 0x40000 | 0x80000 | (0x10000 if L < 250 else 0) | 19
+            t = np.concatenate([g.integers(0, 4, int(g.integers(0, 200))).astype(np.uint8), ts[i], g.integers(0, 4, int(g.integers(0, 200))).astype(np.uint8)])
+            if util.orc_local(O, qs[i], t, xtra) != R.ksw_align2(qs[i], t, xtra):
+                fail("ksw_align2", seed=seed, i=i)
+        n += 1
+    seed += 1
+out["ksw"] = dict(problems=n, seconds=round(time.time() - t0, 1))
+
+# ---- index construction ----
+t0 = time.time(); n = 0; seed = seed0; total = 0
+with tempfile.TemporaryDirectory() as wd:
+    while "index" in parts and time.time() - t0 < budget:
+        g = np.random.default_rng(seed)
+        kind = int(g.integers(0, 5)); L = int(g.integers(1, 6000)) if kind else int(g.integers(1, 40))
+        if kind <= 1: s = g.integers(0, 4, L)
+        elif kind == 2: s = np.tile(g.integers(0, 4, int(g.integers(1, 9))), L // 4 + 1)[:L]            # tandem
+        elif kind == 3: s = np.concatenate([g.integers(0, 4, L), np.full(int(g.integers(1, 300)), int(g.integers(0, 4)))])  # homopolymer at the end
+        else:
+            unit = g.integers(0, 4, int(g.integers(20, 400)))                                            # exact repeats with unique spacers
+            s = np.concatenate([np.concatenate([unit, g.integers(0, 4, int(g.integers(0, 50)))]) for _ in range(int(g.integers(2, 12)))])
+        cuts = sorted(set(int(x) for x in g.integers(1, max(2, len(s)), int(g.integers(0, 4))))) if len(s) > 2 else []
+        ctg = [("c%d" % k, np.asarray(p, np.uint8)) for k, p in enumerate(np.split(np.asarray(s, np.uint8), cuts)) if len(p)]
+        fa = os.path.join(wd, "i%d.fa" % seed)
+        S.write_fasta(fa, ctg); RefBwa().build_index(fa)
+        l_pac = sum(len(p) for _, p in ctg)
+        bwt, sa, st = util.hostsim_index_build(open(fa + ".pac", "rb").read(), l_pac, batch_cap=int(g.choice([0, 0, 64, 1000])))
+        if bwt != open(fa + ".bwt", "rb").read() or sa != open(fa + ".sa", "rb").read():
+            fail("index_build", seed=seed, l_pac=l_pac)
+        for ext in ("", ".bwt", ".sa", ".pac", ".ann", ".amb"):
+            os.remove(fa + ext)
+        n += 1; total += l_pac; seed += 1
+out["index"] = dict(references=n, bases=total, seconds=round(time.time() - t0, 1))
+
+# ---- pack step ----
+A = ArachneCuda(); t0 = time.time(); n = 0; seed = seed0
+with tempfile.TemporaryDirectory() as wd:
+    while "pack" in parts and time.time() - t0 < budget:
+        # kseq's corner cases on purpose: CR-only lines, CRLF, text before the first header, '@' headers, '>' / '@' / '+' inside lines, lines
+        # that START with '+' (the record turns into FASTQ: accepted when the quality length matches, reading stops when it does not),
+        # comments that are a lone CR, names run into the end of the file, blank lines, no final newline
+        g = np.random.default_rng(seed); txt = ""
+        eol = "\r\n" if seed % 5 == 3 else "\n"
+        if seed % 7 == 2: txt += "leading junk without a header" + eol + eol
+        for c in range(int(g.integers(1, 7))):
+            L = int(g.integers(1, 3000))
+            s = np.array(list("ACGT"))[g.integers(0, 4, L)]
+            for _ in range(int(g.integers(0, 6))):
+                a = int(g.integers(0, L)); k = int(g.integers(1, 60)); s[a:a + k] = g.choice(list("NnRYKMSWBDHVryu-.*>@+ "))
+            low = g.random(L) < g.choice([0.0, 0.3]); s[low] = np.char.lower(s[low])
+            s = "".join(s)
+            head = (">" if g.random() < 0.8 else "@") + "ctg%d_%d" % (seed, c)
+            u = g.random()
+            if u < 0.4: head += (" " if c % 3 else "\t") + "note %d x" % c
+            elif u < 0.5: head += " "            # an empty comment; with CRLF the comment is a lone CR
+            txt += head + eol
+            w = int(g.integers(1, 120)); fastq = g.random() < 0.15; seq_chars = 0
+            for i in range(0, L, w):
+                line = s[i:i + w]
+                if line[0] in ">@+" and g.random() < 0.7: line = "A" + line[1:]   # mostly keep the record going; sometimes let kseq see a header / '+' here
+                txt += line + eol
+                if g.random() < 0.03: txt += eol
+            if fastq:
+                txt += "+" + ("anything" if g.random() < 0.5 else "") + eol
+                ql = L if g.random() < 0.7 else int(g.integers(0, L + 5))
+                q = "".join(chr(33 + int(x)) for x in g.integers(0, 40, ql))
+                for i in range(0, ql, w): txt += q[i:i + w] + eol
+        if seed % 11 == 4: txt = txt.rstrip("\r\n")
+        if seed % 13 == 5: txt += ">lastname_without_newline"
+        fa = os.path.join(wd, "p%d.fa" % seed); open(fa, "w", newline="").write(txt)
+        ref = os.path.join(wd, "ref%d" % seed); shutil.copy(fa, ref); RefBwa().build_index(ref)
+        mine = os.path.join(wd, "mine%d" % seed)
+        ref_empty = open(ref + ".ann").read().split()[1] == "0"  # no record survived kseq: the reference leaves degenerate files, we refuse
+        try:
+            A.pack_fasta(fa, mine)
+            if ref_empty: fail("pack accepted an input without records", seed=seed)
+        except Exception as e:
+            if not ref_empty: fail("pack error: %s" % e, seed=seed)
+            for p in os.listdir(wd): os.remove(os.path.join(wd, p))
+            n += 1; seed += 1
+            continue
+        for ext in ("pac", "ann", "amb"):
+            if open(mine + "." + ext, "rb").read() != open(ref + "." + ext, "rb").read(): fail("pack ." + ext, seed=seed)
+        for p in os.listdir(wd): os.remove(os.path.join(wd, p))
+        n += 1; seed += 1
+out["pack"] = dict(fasta_files=n, seconds=round(time.time() - t0, 1))
+print(json.dumps(dict(divergence=None, **out)))

@@ -40,6 +40,7 @@ static bool slurp(const std::string& p, std::vector<uint8_t>& v) {
     v.resize(n); size_t g = fread(v.data(), 1, n, f); fclose(f); return g == (size_t)n;
 }
 
+static long g_score_only_dp = 0;
 struct HostCtx {
     uint64_t cells = 0, calls = 0;
     bool leader() const { return true; }
@@ -59,6 +60,7 @@ struct HostCtx {
         return r;
     }
     int ksw_global(const MemOpt& o, int qlen, const uint8_t* q, int qs, int tlen, const uint8_t* t, int ts, int w, uint32_t* cigar, int cap, int* nc) {
+        if (!cigar) ++g_score_only_dp;  // the score-only use is mem_patch_reg's re-alignment of two colinear regions (csrc/extend.cuh::gen_score)
         std::vector<uint8_t> qq(qlen + 1), tt(tlen + 1);
         for (int i = 0; i < qlen; ++i) qq[i] = q[(long)i * qs];
         for (int i = 0; i < tlen; ++i) tt[i] = t[(long)i * ts];
@@ -272,4 +274,6 @@ int hs_gorand_float64(int64_t seed, int n, int switch_at, double* out) {
     }
     return 0;
 }
+
+long hs_patch_dp_calls(void) { return g_score_only_dp; }  // how often region patching got as far as its global re-alignment
 }

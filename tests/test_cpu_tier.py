@@ -701,8 +701,8 @@ def test_pack_step_matches_bwa_index(tmp_path):
             w = int(g.integers(20, 90))
             for i in range(0, len(s), w):
                 txt += s[i:i + w] + eol
-                if i == 0 and case == 2:
-                    txt += eol  # an empty line inside a record
+                if i == 0 and case in (2, 3):
+                    txt += eol  # an empty line inside a record; under CRLF it is a lone CR, which kseq drops only because the ACCUMULATED sequence is longer than one byte (found by scripts/cpu_fuzz.py)
         fa = str(tmp_path / ("c%d.fa" % case)) + (".gz" if case == 4 else "")
         with (gzip.open(fa, "wt", newline="") if case == 4 else open(fa, "w", newline="")) as f:
             f.write(txt)

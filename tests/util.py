@@ -156,6 +156,7 @@ class HostSim:
                               C.c_void_p, C.POINTER(C.c_int), C.c_int]
         L.hs_reg2aln.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint8), C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32), C.c_int, C.POINTER(C.c_int32)]
         L.hs_introsort_regs.argtypes = [C.c_int, C.c_int, C.c_void_p]
+        L.hs_patch_dp_calls.restype = C.c_long
         L.hs_gorand_float64.argtypes = [C.c_int64, C.c_int, C.c_int, C.POINTER(C.c_double)]
         L.hs_chain.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint8), C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_float)]
         self.h = None
