@@ -118,7 +118,10 @@ using bases_fn = void (*)(const char*, size_t, uint8_t*);
 bases_fn pick_bases_to_codes() { return bases_to_codes_scalar; }
 #endif
 
-inline bool is_space(char c) { return c == ' ' || c == '\t' || c == '\n' || c == '\r' || c == '\v' || c == '\f'; }
+// Two notions of white space meet in ParseHeader: strings.Fields splits at unicode.IsSpace (of the ASCII range: space, \t \n \v \f \r), the
+// regular expressions' \s and \S are RE2's (space, \t \n \f \r: a vertical tab is NOT white space there).
+inline bool is_space(char c) { return c == ' ' || c == '\t' || c == '\n' || c == '\r' || c == '\v' || c == '\f'; }   // strings.Fields
+inline bool re_space(char c) { return c == ' ' || c == '\t' || c == '\n' || c == '\r' || c == '\f'; }                // regexp \s
 
 // ParseHeader on the header line without its '@' (the n bytes include the newline, as the reference's ReadString leaves it), results
 // appended to the chunk's string pools.  Without a `BX:Z:(\S+)\s` match the reference leaves name and barcode empty and valid false.
@@ -136,7 +139,7 @@ inline bool parse_header(const char* s, size_t n, const HeaderOut& o, bool* vali
     for (const char* at = s; at + 5 <= s + n;) {  // leftmost match of BX:Z:(\S+)\s
         const char* hit = static_cast<const char*>(memmem(at, (size_t)(s + n - at), "BX:Z:", 5));
         if (!hit) break;
-        const char* v = hit + 5; const char* e = v; while (e < s + n && !is_space(*e)) ++e;
+        const char* v = hit + 5; const char* e = v; while (e < s + n && !re_space(*e)) ++e;
         if (e > v && e < s + n) { bx = v; bx_len = (size_t)(e - v); break; }
         at = hit + 1;
     }
@@ -147,7 +150,7 @@ inline bool parse_header(const char* s, size_t n, const HeaderOut& o, bool* vali
     for (const char* at = s; at + 7 <= s + n;) {  // leftmost match of VX:i:([01])\s
         const char* hit = static_cast<const char*>(memmem(at, (size_t)(s + n - at), "VX:i:", 5));
         if (!hit || hit + 7 > s + n) break;
-        if ((hit[5] == '0' || hit[5] == '1') && is_space(hit[6])) { *valid = hit[5] == '1'; break; }
+        if ((hit[5] == '0' || hit[5] == '1') && re_space(hit[6])) { *valid = hit[5] == '1'; break; }
         at = hit + 1;
     }
     return true;

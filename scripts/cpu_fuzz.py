@@ -3,7 +3,10 @@
   ksw    the oracle's restatement of ksw_extend2 / ksw_global2 / ksw_align2 (the checker of the GPU DP tests) on random + adversarial problems
   index  the index-construction driver (csrc/index_build.cuh on the test-only host backend) -> .bwt / .sa bytes vs `bwa index`
   pack   arachne_index_pack -> .pac / .ann / .amb vs `bwa index` on FASTA with N runs, IUPAC codes, lower case, CRLF, odd line widths
-python scripts/cpu_fuzz.py [seconds per part=120] [first_seed=1] [parts=ksw,index,pack]   -> one JSON line; non-zero exit on the first divergence."""
+  ingest the FASTQ ingest (csrc/ingest.cu) vs the line-by-line Python restatement of reader.go in tests/test_cpu_tier.py (the one part
+         without a compiled reference: Go) on headers with odd white space, repeated / empty / trailing BX and VX tags, short names,
+         barcode runs around the 200- and 30000-record rules, plain / gzip / BGZF files
+python scripts/cpu_fuzz.py [seconds per part=120] [first_seed=1] [parts=ksw,index,pack,ingest]   -> one JSON line; non-zero exit on the first divergence."""
 import json, os, shutil, sys, tempfile, time
 import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -14,7 +17,7 @@ from tests import util
 
 budget = float(sys.argv[1]) if len(sys.argv) > 1 else 120.0
 seed0 = int(sys.argv[2]) if len(sys.argv) > 2 else 1
-parts = (sys.argv[3] if len(sys.argv) > 3 else "ksw,index,pack").split(",")
+parts = (sys.argv[3] if len(sys.argv) > 3 else "ksw,index,pack,ingest").split(",")
 out = dict(first_seed=seed0)
 
 
@@ -121,4 +124,80 @@ with tempfile.TemporaryDirectory() as wd:
         for p in os.listdir(wd): os.remove(os.path.join(wd, p))
         n += 1; seed += 1
 out["pack"] = dict(fasta_files=n, seconds=round(time.time() - t0, 1))
+# ---- FASTQ ingest ----
+import gzip
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+from tests.test_cpu_tier import _reader_go, _bgzf_bytes
+from arachne_b200 import Ingest
+t0 = time.time(); n = 0; seed = seed0; npairs = 0
+with tempfile.TemporaryDirectory() as wd:
+    while "ingest" in parts and time.time() - t0 < budget:
+        g = np.random.default_rng(seed)
+        ws = [" ", "\t", "  ", "\t ", "\v", "\f", "\r"]
+        def header(k, mate, bc, vx):
+            name = g.choice(["read%d" % k, "r", "", "x%d" % k, "a b"]) + "/%d" % mate
+            tags = []
+            u = g.random()
+            if bc is not None:
+                if u < 0.85: tags.append("BX:Z:" + bc)
+                elif u < 0.9: tags += ["BX:Z:", "BX:Z:" + bc]          # an empty BX first: the regex moves on to the next one
+                elif u < 0.95: tags += ["xBX:Z:" + bc]                   # matches inside a longer token too
+                else: tags += ["BX:Z:" + bc + "\vmore"]                 # a vertical tab is \S for the regex
+            if vx is not None: tags.append("VX:i:%s" % vx)
+            if g.random() < 0.3: tags.append("RG:%d" % (k % 3))
+            g.shuffle(tags)
+            h = "@" + name
+            for t in tags: h += str(g.choice(ws)) + t
+            if g.random() < 0.1: h += str(g.choice(ws))
+            return h + "\n"
+        r1, r2, k = [], [], 0
+        plan = []
+        for _ in range(int(g.integers(1, 12))):
+            bc = g.choice(["A01C02B03D04-1", "B%02d-1" % g.integers(0, 99), "plain%d" % g.integers(0, 9), None, "N-N"])
+            cnt = int(g.choice([1, 2, 4, 5, 6, 30, 199, 200, 201, 202, 403])) if g.random() < 0.97 else 30000 + int(g.integers(0, 500))
+            plan.append((None if bc is None else str(bc), cnt))
+        if g.random() < 0.3: plan.append(plan[-1])                       # the same barcode again right after: the continuation rule
+        for bc, cnt in plan:
+            for _ in range(cnt):
+                L1 = int(g.integers(0, 152)) if g.random() < 0.05 else 40; L2 = 40
+                s1 = "".join("ACGTNacgt-"[int(x)] for x in g.integers(0, 10 if k % 40 == 0 else 4, L1)); s2 = "ACGT" * 10
+                q1 = "I" * (L1 if g.random() < 0.97 else max(0, L1 - 3)); q2 = "I" * L2
+                vx = g.choice(["0", "1", None, "2"])
+                r1 += [header(k, 1, bc, None if vx is None else str(vx)), s1 + "\n", "+\n", q1 + "\n"]; r2 += [header(k, 2, bc, None), s2 + "\n", "+\n", q2 + "\n"]
+                k += 1
+        if g.random() < 0.2: r2 = r2[:len(r2) - 4 * int(g.integers(1, 3))]   # R2 ends early
+        if g.random() < 0.2: r1[-1] = r1[-1][:-1]                            # no final newline
+        kind = int(g.integers(0, 4))
+        p1, p2 = os.path.join(wd, "a%d" % seed), os.path.join(wd, "b%d" % seed)
+        for p, lines in ((p1, r1), (p2, r2)):
+            text = "".join(lines).encode("latin-1")
+            blob = text if kind == 0 else gzip.compress(text, 1) if kind == 1 else _bgzf_bytes(text, int(g.choice([0xff00, 500, 4096])))
+            open(p, "wb").write(blob)
+        if not r1[-1].endswith("\n"): r1[-1] += "\n"
+        recs, units = _reader_go(r1, r2)
+        # quality shorter than the sequence is padded with '!' by the ingest (the reference would index past it)
+        I = Ingest(p1, p2, n_threads=int(g.integers(1, 5)))
+        try:
+            got_units, pair = [], 0
+            while True:
+                b = I.next(int(g.choice([1, 7, 300, 10**9])))
+                if b is None: break
+                for u in range(b["n_units"]):
+                    lo, hi = int(b["unit_off"][u]), int(b["unit_off"][u + 1])
+                    got_units.append((pair + lo, pair + hi, bool(b["unique"][u])))
+                    first = recs[pair + lo]
+                    if b["barcodes"][u] != first[1] or bool(b["valid"][u]) != first[2] or bool(b["run_rfa"][u]) != (bool(b["unique"][u]) and "-" in first[1] and hi - lo >= 5):
+                        fail("ingest unit fields", seed=seed, unit=len(got_units) - 1)
+                for i in range(b["n_pairs"]):
+                    name, bc, valid, rg, s1, q1, s2, q2 = recs[pair + i]
+                    o = b["off"][2 * i:2 * i + 3]
+                    if b["names"][i] != name or b["read_groups"][i] != rg or o[1] - o[0] != len(s1) or o[2] - o[1] != len(s2) or b["quals"][2 * i] != (q1 + "!" * len(s1))[:len(s1)]:
+                        fail("ingest record fields", seed=seed, pair=pair + i, got=(b["names"][i], b["read_groups"][i]), want=(name, rg))
+                pair += b["n_pairs"]
+            if pair != len(recs) or got_units != units: fail("ingest units", seed=seed, pairs=(pair, len(recs)))
+        finally:
+            I.close()
+        for p in os.listdir(wd): os.remove(os.path.join(wd, p))
+        n += 1; npairs += len(recs); seed += 1
+out["ingest"] = dict(file_pairs=n, pairs=npairs, seconds=round(time.time() - t0, 1))
 print(json.dumps(dict(divergence=None, **out)))

@@ -484,13 +484,15 @@ def _reader_go(r1_lines, r2_lines):
     recs = []
     for i in range(0, min(len(r1_lines), len(r2_lines)) - 3, 4):
         h = r1_lines[i][1:]                           # R1_line[1:], newline included
-        bx = re.search(r"BX:Z:(\S+)\s", h)
+        # Go's regexp (RE2) \s is [\t\n\f\r ]; strings.Fields splits at unicode.IsSpace, which adds \v in the ASCII range
+        bx = re.search(r"BX:Z:([^\t\n\f\r ]+)[\t\n\f\r ]", h)
+        fields = lambda t: [x for x in re.split(r"[\t\n\v\f\r ]+", t) if x]
         if bx:
-            _id = h.split()[0]; name = _id[:len(_id) - 2]; bc = bx.group(1)
-            vx = re.search(r"VX:i:([01])\s", h); valid = bool(vx and vx.group(1) == "1")
+            _id = fields(h)[0]; name = _id[:len(_id) - 2] if len(_id) >= 2 else ""; bc = bx.group(1)
+            vx = re.search(r"VX:i:([01])[\t\n\f\r ]", h); valid = bool(vx and vx.group(1) == "1")
         else:
             name, bc, valid = "", "", False
-        f = h[:-1].split()
+        f = fields(h[:-1])
         rg = f[-1] if len(f) >= 2 else ""
         recs.append((name, bc, valid, rg, r1_lines[i + 1][:-1], r1_lines[i + 3][:-1], r2_lines[i + 1][:-1], r2_lines[i + 3][:-1]))
     units, pos, last = [], 0, None
