@@ -58,3 +58,8 @@ nvcc -gencode arch=compute_100a,code=sm_100a -O1 -g -std=c++17 -shared -Xcompile
 ARACHNE_LIB="$W/libarachne_tsan.so" TSAN_OPTIONS="report_signal_unsafe=0 exitcode=0" LD_PRELOAD=$TSAN python -m pytest tests/test_preprocess.py tests/test_cpu_tier.py -q -m "not gpu" \
     -p no:cacheprovider -k "preprocess or standardize or ingest or pack or abi or header" > "$W/lib_tsan.log" 2>&1
 tail -1 "$W/lib_tsan.log"; echo "sanitizer reports: $(grep -c 'WARNING: ThreadSanitizer' "$W/lib_tsan.log")"
+echo "== build + run: the ORACLE itself (oracle/restate_ksw.c, restate_place.cpp: the checker of the GPU tests) under ASan + UBSan"
+( cd oracle && g++ -O1 -g -fPIC -shared -fsanitize=address,undefined -fno-sanitize-recover=undefined -fno-omit-frame-pointer -x c restate_ksw.c -x c++ -std=c++17 restate_place.cpp \
+    -o "$W/liboracle_asan.so" -lm -lpthread ) || exit 1
+ARACHNE_ORACLE_LIB="$W/liboracle_asan.so" ASAN_OPTIONS=detect_leaks=0 UBSAN_OPTIONS=print_stacktrace=1 LD_PRELOAD=$ASAN \
+    python -m pytest tests/test_cpu_tier.py -q -p no:cacheprovider -k "oracle or place or go_math" 2>&1 | grep -v "site-packages\|<frozen" | tail -3

@@ -23,7 +23,7 @@ def oracle_lib():
     """liboracle.so (our CPU restatement); built on demand with plain gcc/g++."""
     path = os.path.join(ROOT, "oracle", "liboracle.so")
     subprocess.run(["make", "-s", "-C", os.path.join(ROOT, "oracle"), "restate"], check=True, stdout=subprocess.DEVNULL)
-    return C.CDLL(path)
+    return C.CDLL(os.environ.get("ARACHNE_ORACLE_LIB") or path)  # override: the sanitizer build (scripts/host_sanitize.sh)
 
 
 def u8p(a):
