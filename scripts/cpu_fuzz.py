@@ -6,7 +6,9 @@
   ingest the FASTQ ingest (csrc/ingest.cu) vs the line-by-line Python restatement of reader.go in tests/test_cpu_tier.py (the one part
          without a compiled reference: Go) on headers with odd white space, repeated / empty / trailing BX and VX tags, short names,
          barcode runs around the 200- and 30000-record rules, plain / gzip / BGZF files
-python scripts/cpu_fuzz.py [seconds per part=120] [first_seed=1] [parts=ksw,index,pack,ingest]   -> one JSON line; non-zero exit on the first divergence."""
+  headers the preprocess row's hand-written header scanners (the reference's five patterns, standardize.go:16-25) vs Python `re` on the same
+         patterns (oracle/preprocess_oracle.py), and the header rewriting of whole files in the four formats
+python scripts/cpu_fuzz.py [seconds per part=120] [first_seed=1] [parts=ksw,index,pack,ingest,headers]   -> one JSON line; non-zero exit on the first divergence."""
 import json, os, shutil, sys, tempfile, time
 import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -17,7 +19,7 @@ from tests import util
 
 budget = float(sys.argv[1]) if len(sys.argv) > 1 else 120.0
 seed0 = int(sys.argv[2]) if len(sys.argv) > 2 else 1
-parts = (sys.argv[3] if len(sys.argv) > 3 else "ksw,index,pack,ingest").split(",")
+parts = (sys.argv[3] if len(sys.argv) > 3 else "ksw,index,pack,ingest,headers").split(",")
 out = dict(first_seed=seed0)
 
 
@@ -200,4 +202,33 @@ with tempfile.TemporaryDirectory() as wd:
         for p in os.listdir(wd): os.remove(os.path.join(wd, p))
         n += 1; npairs += len(recs); seed += 1
 out["ingest"] = dict(file_pairs=n, pairs=npairs, seconds=round(time.time() - t0, 1))
+# ---- preprocess: header patterns and rewriting ----
+from arachne_b200 import lib as L
+from oracle import preprocess_oracle as PO
+from tests.test_preprocess import make_fastq
+t0 = time.time(); n = 0; nf = 0; seed = seed0
+pieces = ["r1", "/1", "/2", "\t", " ", "BX:Z:", "VX:i:", "0", "1", "2", "A01C02B03D04", "A01C02B03D0", "A99C00B12D77", "#", "12_7_1444", "1_2", "_", "x", ":", "ACGTNACGTACGTACGTA",
+          "ACGTACGTACGTACGTAC", "1:N:0:ATCACG", "2:N:0:", "atc", "N", "RG:Z:l", "\t\t", "  ", "", "A01", "C02", "B03D04", "D04\t", "Y", ",", "+", "0_0_0", "1536_1536_1536"]
+with tempfile.TemporaryDirectory() as wd:
+    while "headers" in parts and time.time() - t0 < budget:
+        g = np.random.default_rng(seed)
+        for _ in range(2000):
+            h = "".join(str(g.choice(pieces)) for _ in range(int(g.integers(0, 9))))
+            if L.fastq_header_format(h) != PO.header_format(h): fail("header_format", seed=seed, header=h, got=L.fastq_header_format(h), want=PO.header_format(h))
+            n += 1
+        fmt = str(g.choice(["standard", "haplotagging", "stlfr", "tellseq"])); gz = bool(g.random() < 0.3)
+        d = os.path.join(wd, "f%d" % seed); os.makedirs(d)
+        r1, r2 = make_fastq(d, fmt, n=int(g.integers(1, 600)), seed=int(g.integers(1 << 30)), gz=gz)
+        o1, o2 = os.path.join(d, "o1"), os.path.join(d, "o2")
+        try:
+            st = L.preprocess(r1, r2, o1, o2, sort=False); e1, e2, est = PO.preprocess(r1, r2, sort=False)
+            if open(o1, "rb").read() != e1 or open(o2, "rb").read() != e2 or any(st[k] != est[k] for k in ("n_pairs", "format", "n_barcodes", "n_no_tag", "n_invalid")):
+                fail("standardize", seed=seed, fmt=fmt)
+        except L.ArachneError as e:   # the first 200 headers may not decide a format for a tiny file: both sides must then refuse
+            try:
+                PO.preprocess(r1, r2, sort=False); fail("standardize refused: %s" % e, seed=seed, fmt=fmt)
+            except Exception:
+                pass
+        shutil.rmtree(d); nf += 1; seed += 1
+out["headers"] = dict(headers=n, files=nf, seconds=round(time.time() - t0, 1))
 print(json.dumps(dict(divergence=None, **out)))
