@@ -16,7 +16,7 @@ from tests import util
 budget = float(sys.argv[1]) if len(sys.argv) > 1 else 300.0
 seed0 = int(sys.argv[2]) if len(sys.argv) > 2 else 1
 HS = util.HostSim()
-t0 = time.time(); stats = dict(rounds=0, pairs=0, regions=0, rescued_reads=0, cigars=0, gapped_cigars=0, chains_checked=0, patched_or_merged=0)
+t0 = time.time(); stats = dict(rounds=0, pairs=0, regions=0, rescued_reads=0, cigars=0, gapped_cigars=0, chains_checked=0, patched_or_merged=0, occ_sa_checked=0)
 rc = lambda s: np.where(s[::-1] < 4, 3 - s[::-1], 4).astype(np.uint8)
 
 
@@ -73,6 +73,14 @@ with tempfile.TemporaryDirectory() as wd:
         ctg = make_reference(g, int(g.integers(0, 4)))
         fa = os.path.join(wd, "f%d.fa" % seed)
         S.write_fasta(fa, ctg); R = RefBwa(); R.build_index(fa); R.load(fa); HS.load(fa)
+        prim, *L2, sl = R.bwt_meta()
+        ks = [0, 1, prim - 1, prim, prim + 1, sl - 1, sl, 63, 64, 65, 127, 128, 129] + [int(x) for x in g.integers(0, sl + 1, 400)]
+        for k in ks:   # rows a1 / a2 / a6: the re-cut 32-byte-sector image, occ counts at block edges / primary / the k - 1 wrap, SA rows
+            l = min(sl, k + int(g.integers(0, 300)))
+            if k < 0 or k > sl: continue
+            if HS.occ(k, l) != sum(R.occ4(k, l), []) or HS.occ(k - 1, l) != sum(R.occ4(k - 1, l), []) or HS.sa(k) != R.sa(k):
+                print(json.dumps(dict(divergence="occ/sa", seed=seed, k=k, l=l, **stats))); sys.exit(1)
+            stats["occ_sa_checked"] += 1
         reads = make_reads(g, ctg)
         seq, off = util.pack(reads)
         ref = R.batch(seq, off, rescue=True, cigar=True, threads=8); plain = R.batch(seq, off, rescue=False, cigar=False, threads=8)
