@@ -44,6 +44,7 @@ __device__ __forceinline__ void pk_unpack(uint4 v, uint64_t& x0, uint64_t& x1, u
     end = (unsigned)(hi >> 56);
 }
 
+#if defined(__CUDACC__)
 __device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
     const unsigned a = (unsigned)__cvta_generic_to_shared(smem);
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(a), "l"(gmem));
@@ -54,6 +55,19 @@ __device__ __forceinline__ void ld_sector(uint32_t* o, const void* p) {  // one 
     asm volatile("ld.global.nc.L1::no_allocate.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                  : "=r"(o[0]), "=r"(o[1]), "=r"(o[2]), "=r"(o[3]), "=r"(o[4]), "=r"(o[5]), "=r"(o[6]), "=r"(o[7]) : "l"(p));
 }
+__device__ __forceinline__ void ld_nc8(uint32_t* o, const void* p) {   // 8 bytes past L1 (an SA / inverse-SA entry, a text word)
+    asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(o[0]), "=r"(o[1]) : "l"(p));
+}
+__device__ __forceinline__ void ld_nc16(uint32_t* o, uint64_t p) {     // 16 bytes past L1 (a k-mer table entry)
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(o[0]), "=r"(o[1]), "=r"(o[2]), "=r"(o[3]) : "l"(p));
+}
+#else  // TEST-ONLY host build (tests/hostsim/hostsim_seed.cpp runs this kernel one lane at a time): the same bytes by plain copies
+inline void cp_async16(void* smem, const void* gmem) { memcpy(smem, gmem, 16); }
+inline void cp_async_wait_all() {}
+inline void ld_sector(uint32_t* o, const void* p) { memcpy(o, p, 32); }
+inline void ld_nc8(uint32_t* o, const void* p) { memcpy(o, p, 8); }
+inline void ld_nc16(uint32_t* o, uint64_t p) { memcpy(o, reinterpret_cast<const void*>(p), 16); }
+#endif
 // bits [s, s + 64) of the 128-bit string a.b (s even, 0..62)
 __device__ __forceinline__ uint64_t fsh64(uint64_t a, uint64_t b, int s) { return (a << s) | ((b >> 1) >> (63 - s)); }
 
@@ -350,15 +364,15 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) k_seed2(FMIndex fm, MemOpt op
             if (!same) ld_sector(R + 8, fm.blocks + lb);
         } else if (need == 2) {
             const uint64_t* a = phase == SP_FSA ? fm.sa + kx0 : fm.isa + (fm.seq_len - dpos - (uint64_t)(i - x));
-            asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(R[0]), "=r"(R[1]) : "l"(a));
+            ld_nc8(R, a);
         } else if (need == 3) {
             const uint64_t* tp = fm.text + ((dpos + (uint64_t)(i - x)) >> 5);
 #pragma unroll
             for (int d = 0; d <= DIRECT_WORDS; ++d)
-                asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(R[2 * d]), "=r"(R[2 * d + 1]) : "l"(tp + d));
+                ld_nc8(R + 2 * d, tp + d);
         } else if (need == 4) {
             stat(1u, 2u);
-            asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(R[0]), "=r"(R[1]), "=r"(R[2]), "=r"(R[3]) : "l"(tabp));
+            ld_nc16(R, tabp);
         }
         __syncwarp();
         // ------------------------------------------------------------------ CONSUME: bwt_extend on (sx, is_back), base c / the loaded entry

@@ -1,6 +1,7 @@
 #!/usr/bin/env python
 """Differential fuzzing of the thread-sequential device logic (tests/hostsim: chaining, extension driver, de-duplication / patching, mate
-rescue, mem_reg2aln of the warp tier -- the same csrc/*.cuh the kernels compile) against the reference's own C code (oracle/_ref), on
+rescue, mem_reg2aln of the warp tier, and the shipped seeding kernel k_seed2 run one lane at a time -- the same csrc/*.cuh the kernels
+compile) against the reference's own C code (oracle/_ref), on
 references and reads drawn to reach the rare branches: diverged and exact repeats, tandem arrays, short contigs (window clamps), read
 lengths 30..250, heavy substitutions / indels, N runs, chimeric reads (region patching and colinear merges), wrecked mates (rescue).
 CPU only.   python scripts/hostsim_fuzz.py [seconds=300] [first_seed=1]   -> one JSON line; non-zero exit on the first divergence."""
@@ -16,7 +17,9 @@ from tests import util
 budget = float(sys.argv[1]) if len(sys.argv) > 1 else 300.0
 seed0 = int(sys.argv[2]) if len(sys.argv) > 2 else 1
 HS = util.HostSim()
-t0 = time.time(); stats = dict(rounds=0, pairs=0, regions=0, rescued_reads=0, cigars=0, gapped_cigars=0, chains_checked=0, patched_or_merged=0, occ_sa_checked=0)
+from arachne_b200 import ArachneCuda
+OPT = ArachneCuda().opt
+t0 = time.time(); stats = dict(rounds=0, pairs=0, regions=0, rescued_reads=0, cigars=0, gapped_cigars=0, chains_checked=0, patched_or_merged=0, occ_sa_checked=0, seed_reads_checked=0, seed_intervals=0)
 rc = lambda s: np.where(s[::-1] < 4, 3 - s[::-1], 4).astype(np.uint8)
 
 
@@ -83,6 +86,16 @@ with tempfile.TemporaryDirectory() as wd:
             stats["occ_sa_checked"] += 1
         reads = make_reads(g, ctg)
         seq, off = util.pack(reads)
+        # rows a3-a5 on the SHIPPED seeding kernel (csrc/seed_kernel.cuh run one lane at a time, tests/hostsim/hostsim_seed.cpp) with a random
+        # choice of its shortcuts, against mem_collect_intv composed from the reference's bwt_smem1 / bwt_seed_strategy1
+        si, K = HS.seed_index(fa, kmer_k=int(g.choice([-1, -1, 0, 4, 6])), direct=bool(g.random() < 0.7))
+        use_kmer = int(g.choice([0, 1, 5, 1 | (int(g.integers(1, 15)) << 8)])); use_direct = int(g.random() < 0.7)
+        io, iv, _st = HS.seed2(si, OPT, seq, off, use_kmer, use_direct, int(g.choice([-1, 0, 3, 16])), int(g.integers(0, 256)))
+        HS.seed_index_free(si)
+        for r in range(0, len(reads), 3):
+            if [tuple(int(v) for v in a) for a in iv[io[r]:io[r + 1]]] != util.ref_collect_intv(R, reads[r]):
+                print(json.dumps(dict(divergence="seed intervals", seed=seed, read=r, use_kmer=use_kmer, use_direct=use_direct, K=K, **stats))); sys.exit(1)
+            stats["seed_reads_checked"] += 1; stats["seed_intervals"] += int(io[r + 1] - io[r])
         ref = R.batch(seq, off, rescue=True, cigar=True, threads=8); plain = R.batch(seq, off, rescue=False, cigar=False, threads=8)
         exp = ref["regs"].view(ALNREG); ro = ref["reg_off"]; exp1 = plain["regs"].view(ALNREG); ro1 = plain["reg_off"]
         for p in range(len(reads) // 2):

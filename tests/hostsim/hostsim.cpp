@@ -276,4 +276,6 @@ int hs_gorand_float64(int64_t seed, int n, int switch_at, double* out) {
 }
 
 long hs_patch_dp_calls(void) { return g_score_only_dp; }  // how often region patching got as far as its global re-alignment
+
+const void* hs_fm(void* h) { return &((HostIndex*)h)->fm; }  // for hostsim_seed.cpp
 }

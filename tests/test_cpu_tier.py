@@ -247,6 +247,63 @@ def test_hostsim_pipeline_live(HS, workdir):
     assert n_rescued >= 10 and n_cig >= 500 and n_gapped >= 20, (n_rescued, n_cig, n_gapped)
 
 
+def _seed_test_reads(ctg, rs, n_sim=160):
+    """Simulated reads + exact substrings of both strands (direct comparison running into the read's end), an N inside an exact match,
+    all-N, shorter than a seed, tandem repeat, homopolymer: what tests/test_gpu_parity.py::test_seed_intervals_every_shortcut uses."""
+    g = np.random.default_rng(11)
+    ref = np.concatenate([np.asarray(c[1], dtype=np.uint8) for c in ctg])
+    reads = [rs.seq[rs.off[r]:rs.off[r + 1]] for r in range(0, min(len(rs.off) - 1, n_sim))]
+    for k in range(30):
+        p = int(g.integers(0, len(ref) - 260)); L = int(g.choice([30, 100, 150, 250]))
+        s = ref[p:p + L].copy()
+        if s.max() > 3:
+            continue
+        if k % 3 == 1:
+            s = (3 - s)[::-1].copy()
+        if k % 3 == 2:
+            s[int(g.integers(20, L - 5))] = 4
+        reads.append(s)
+    reads += [np.full(40, 4, dtype=np.uint8), np.zeros(12, dtype=np.uint8), np.array([0, 1, 2, 3] * 30, dtype=np.uint8), np.zeros(150, dtype=np.uint8),
+              np.zeros(0, dtype=np.uint8), np.array([0, 1] * 100, dtype=np.uint8)]
+    return reads
+
+
+@pytest.mark.parametrize("name", ["rand1m", "rep600k"])
+def test_hostsim_shipped_seed_kernel(HS, workdir, name):
+    """Rows a3-a5 on the code the GPU runs: csrc/seed_kernel.cuh (k_pack_reads, k_seed2, k_sort_intv) and the index builders of
+    csrc/index_kernels.cuh, compiled for the host through tests/hostsim/cuda_lane_shim.h and run one lane at a time (k_seed2's lanes are
+    independent automata), against the reference's own bwt_smem1 / bwt_seed_strategy1 composed into mem_collect_intv -- with the k-mer
+    tables / forward windows / direct text extension on and off, different numbers of shared list slots and different lanes of the block
+    (the lane-strided layouts).  The bwt_extend counter (bench.py takes the roofline's algorithmic bytes from a pass with the shortcuts off)
+    stays within 1 % when a shortcut replaces the calls it counts."""
+    from oracle.refbwa import RefBwa, available
+    if not available():
+        pytest.skip("oracle/_ref not built")
+    from arachne_b200 import ArachneCuda
+    fa, ctg, rs = util.make_dataset(name, workdir)
+    R = RefBwa().load(fa); HS.load(fa)
+    reads = _seed_test_reads(ctg, rs)
+    seq, off = util.pack(reads)
+    opt = ArachneCuda().opt
+    si, K = HS.seed_index(fa)
+    assert K >= 8
+    try:
+        base = None
+        for use_kmer, direct, slist, lane in [(0, 0, -1, 0), (1, 0, -1, 37), (0, 1, -1, 255), (1, 1, -1, 0), (5, 1, -1, 1), (1 | (3 << 8), 1, 4, 100), (1 | (14 << 8), 1, 16, 31), (1, 1, 0, 200)]:
+            io, iv, st = HS.seed2(si, opt, seq, off, use_kmer, direct, slist, lane)
+            if base is None:
+                base = (io, iv, st)
+                for r, q in enumerate(reads):
+                    got = [tuple(int(v) for v in a) for a in iv[io[r]:io[r + 1]]]
+                    assert got == util.ref_collect_intv(R, q), (name, r)
+                assert st[0] > 100 * len(reads) and st[0] <= st[1] <= 2 * st[0]
+            else:
+                assert np.array_equal(io, base[0]) and np.array_equal(iv, base[1]), (name, use_kmer, direct, slist, lane)
+            assert abs(st[0] - base[2][0]) <= 0.01 * base[2][0], (st, base[2])
+    finally:
+        HS.seed_index_free(si)
+
+
 def test_hostsim_seed_intervals_live(HS, workdir):
     """mem_collect_intv restated from bwt_smem1 / bwt_seed_strategy1 calls on the reference's code (needs oracle/_ref)."""
     from oracle.refbwa import RefBwa, available

@@ -156,6 +156,10 @@ class HostSim:
                               C.c_void_p, C.POINTER(C.c_int), C.c_int]
         L.hs_reg2aln.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint8), C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32), C.c_int, C.POINTER(C.c_int32)]
         L.hs_introsort_regs.argtypes = [C.c_int, C.c_int, C.c_void_p]
+        L.hs_seed_index.restype = C.c_void_p; L.hs_seed_index.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int]
+        L.hs_seed_index_free.argtypes = [C.c_void_p]
+        L.hs_seed2.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(C.c_uint8), C.POINTER(C.c_int64), C.c_int, C.c_int, C.c_int, C.c_int,
+                               C.POINTER(C.c_uint64), C.c_int64, C.POINTER(C.c_int64), C.POINTER(C.c_uint64)]
         L.hs_patch_dp_calls.restype = C.c_long
         L.hs_gorand_float64.argtypes = [C.c_int64, C.c_int, C.c_int, C.POINTER(C.c_double)]
         L.hs_chain.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint8), C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_float)]
@@ -173,6 +177,33 @@ class HostSim:
         out = (C.c_double * n)()
         assert self.lib.hs_gorand_float64(seed, n, switch_at, out) == 0
         return list(out)
+
+    def seed_index(self, prefix, kmer_k=-1, direct=True):
+        """The HBM-only index structures of the loaded index (k-mer tables of depth kmer_k, -1 = the loader's own rule min(14, log4(n) - 1);
+        dense SA + inverse SA + both-strand text when `direct`), built by the product's own builder kernels run on the host."""
+        pac = np.fromfile(prefix + ".pac", dtype=np.uint8)
+        l_pac = int(open(prefix + ".ann").readline().split()[0])
+        if kmer_k < 0:
+            n, kmer_k = 2 * l_pac, 0
+            while n > 3:
+                n >>= 2; kmer_k += 1
+            kmer_k = min(kmer_k - 1, 14)
+        self._seed_keep = pac
+        return self.lib.hs_seed_index(self.h, pac.ctypes.data, l_pac, max(kmer_k, 0), int(direct)), kmer_k
+
+    def seed_index_free(self, si):
+        self.lib.hs_seed_index_free(si)
+
+    def seed2(self, si, opt, seq, off, use_kmer=1, use_direct=1, slist_want=-1, lane=0):
+        """k_pack_reads -> k_seed2 -> k_sort_intv (csrc/seed_kernel.cuh, the shipped kernels) run one lane at a time on the host:
+        -> (intv_off [n + 1], intervals [m, 4] = x0 x1 x2 info, (bwt_extend calls, reference occ blocks))."""
+        seq, sp = u8p(seq); off = np.ascontiguousarray(off, dtype=np.int64); n = len(off) - 1
+        cap = 64 * n + 1024
+        iv = np.zeros((cap, 4), np.uint64); io = np.zeros(n + 1, np.int64); st = (C.c_uint64 * 2)()
+        rc = self.lib.hs_seed2(si, C.byref(opt), n, sp, off.ctypes.data_as(C.POINTER(C.c_int64)), use_kmer, use_direct, slist_want, lane,
+                               iv.ctypes.data_as(C.POINTER(C.c_uint64)), cap, io.ctypes.data_as(C.POINTER(C.c_int64)), st)
+        assert rc == 0, rc
+        return io, iv[:io[-1]], (int(st[0]), int(st[1]))
 
     def introsort_regs(self, mode, regs):
         out = regs.copy()
