@@ -214,6 +214,26 @@ __global__ void __launch_bounds__(CIG_BLOCK) k_cigar_fast(MemOpt opt, RefView re
     }
 }
 
+// PRMT (default mode): byte i of the result is byte (sel >> 4i) & 7 of the 8 bytes {hi:lo}, or that byte's sign replicated when bit 3 of
+// the selector nibble is set.  The host definition (TEST-ONLY build, tests/hostsim/hostsim_cigar.cpp) states the same thing in C.
+#if defined(__CUDACC__)
+__device__ __forceinline__ int cig_prmt(unsigned lo, unsigned hi, int sel) {
+    int r;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(lo), "r"(hi), "r"(sel));
+    return r;
+}
+#else
+inline int cig_prmt(unsigned lo, unsigned hi, int sel) {
+    const unsigned long long src = (unsigned long long)hi << 32 | lo;
+    unsigned r = 0;
+    for (int i = 0; i < 4; ++i) {
+        const unsigned n = ((unsigned)sel >> (4 * i)) & 0xfu, b = (unsigned)(src >> (8 * (n & 7u))) & 0xffu;
+        r |= ((n & 8u) ? ((b & 0x80u) ? 0xffu : 0u) : b) << (8 * i);
+    }
+    return (int)r;
+}
+#endif
+
 // ------------------------------------------------------------------------------------------------ tier 2
 // One bwa_gen_cigar2 call for band parameter w_ (bwa.c:121-207) on the lane's ring.  Returns n_cigar >= 0 with the CIGAR
 // in c (forward-strand order), or -1 when this lane cannot do it (band or CIGAR too large -> tier 3).
@@ -265,9 +285,7 @@ __device__ __forceinline__ int band_gen_cigar(const MemOpt& opt, const RegView& 
 #define BAND_CELL(slot_, u_)                                                                    \
     {                                                                                           \
         const int2 he = (slot_);                                                                \
-        int sc_;                                                                                \
-        asm("prmt.b32 %0, %1, %2, %3;" : "=r"(sc_) : "r"(lut_lo), "r"(lut_hi), "r"(he.y));      \
-        const int m = he.x + sc_;                                                               \
+        const int m = he.x + cig_prmt(lut_lo, lut_hi, he.y);                                    \
         int e = he.y >> 16, h, x;                                                               \
         unsigned d = m >= e ? 0u : 1u; h = m >= e ? m : e;                                      \
         if (h < f) { d = 2u; h = f; }                                                           \

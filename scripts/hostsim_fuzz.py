@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Differential fuzzing of the thread-sequential device logic (tests/hostsim: chaining, extension driver, de-duplication / patching, mate
-rescue, mem_reg2aln of the warp tier, and the shipped seeding kernel k_seed2 run one lane at a time -- the same csrc/*.cuh the kernels
+rescue, mem_reg2aln of the warp tier, the shipped seeding kernel k_seed2 and the shipped CIGAR tiers k_cigar_fast / k_cigar_band run one lane at a time -- the same csrc/*.cuh the kernels
 compile) against the reference's own C code (oracle/_ref), on
 references and reads drawn to reach the rare branches: diverged and exact repeats, tandem arrays, short contigs (window clamps), read
 lengths 30..250, heavy substitutions / indels, N runs, chimeric reads (region patching and colinear merges), wrecked mates (rescue).
@@ -19,7 +19,7 @@ seed0 = int(sys.argv[2]) if len(sys.argv) > 2 else 1
 HS = util.HostSim()
 from arachne_b200 import ArachneCuda
 OPT = ArachneCuda().opt
-t0 = time.time(); stats = dict(rounds=0, pairs=0, regions=0, rescued_reads=0, cigars=0, gapped_cigars=0, chains_checked=0, patched_or_merged=0, occ_sa_checked=0, seed_reads_checked=0, seed_intervals=0)
+t0 = time.time(); stats = dict(rounds=0, pairs=0, regions=0, rescued_reads=0, cigars=0, gapped_cigars=0, chains_checked=0, patched_or_merged=0, occ_sa_checked=0, seed_reads_checked=0, seed_intervals=0, tier_regions=0, tier2_regions=0, tier3_regions=0)
 rc = lambda s: np.where(s[::-1] < 4, 3 - s[::-1], 4).astype(np.uint8)
 
 
@@ -98,6 +98,16 @@ with tempfile.TemporaryDirectory() as wd:
             stats["seed_reads_checked"] += 1; stats["seed_intervals"] += int(io[r + 1] - io[r])
         ref = R.batch(seq, off, rescue=True, cigar=True, threads=8); plain = R.batch(seq, off, rescue=False, cigar=False, threads=8)
         exp = ref["regs"].view(ALNREG); ro = ref["reg_off"]; exp1 = plain["regs"].view(ALNREG); ro1 = plain["reg_off"]
+        # row a13 on the SHIPPED lane-per-region CIGAR tiers (csrc/cigar_kernel.cuh run one lane at a time, tests/hostsim/hostsim_cigar.cpp)
+        t_alns, t_cig, t_mm, t_list3, t_cnt = HS.cigar_tiers(OPT, seq, off, ro, exp)
+        t_left = set(int(x) for x in t_list3)
+        for j in range(len(exp)):
+            if j in t_left: continue
+            a = t_alns[j]; e = ref["aln"][j]
+            if (a["pos"], a["rid"], a["is_rev"], a["nm"], a["n_cigar"], a["score"], a["sub"]) != (e[0], e[1], e[2], e[3], e[4], e[6], e[7]) or \
+                    not np.array_equal(t_cig[a["cigar_off"]:a["cigar_off"] + a["n_cigar"]], ref["cigar"][e[5]:e[5] + e[4]]):
+                print(json.dumps(dict(divergence="cigar tiers", seed=seed, region=j, **stats))); sys.exit(1)
+        stats["tier_regions"] += len(exp) - len(t_left); stats["tier2_regions"] += t_cnt["tier2"]; stats["tier3_regions"] += t_cnt["tier3"]
         for p in range(len(reads) // 2):
             for k in (2 * p, 2 * p + 1):
                 got = HS.align1(reads[k])

@@ -97,6 +97,7 @@ void* hs_load(const char* prefix_) {
     std::string prefix(prefix_);
     auto* h = new HostIndex();
     if (!slurp(prefix + ".bwt", h->bwt) || !slurp(prefix + ".sa", h->sa_raw) || !slurp(prefix + ".pac", h->pac)) { delete h; return nullptr; }
+    h->pac.resize(h->pac.size() + 16, 0);  // the CIGAR tiers read the packed reference in 32-bit words (the device buffer is padded too)
     const uint64_t* bh = (const uint64_t*)h->bwt.data();
     FMIndex& fm = h->fm;
     fm.primary = bh[0]; fm.L2[0] = 0; for (int i = 1; i <= 4; ++i) fm.L2[i] = bh[i];
@@ -278,4 +279,5 @@ int hs_gorand_float64(int64_t seed, int n, int switch_at, double* out) {
 long hs_patch_dp_calls(void) { return g_score_only_dp; }  // how often region patching got as far as its global re-alignment
 
 const void* hs_fm(void* h) { return &((HostIndex*)h)->fm; }  // for hostsim_seed.cpp
+const void* hs_ref(void* h) { return &((HostIndex*)h)->ref; }  // for hostsim_cigar.cpp
 }

@@ -304,6 +304,57 @@ def test_hostsim_shipped_seed_kernel(HS, workdir, name):
         HS.seed_index_free(si)
 
 
+def _check_cigar_tiers(HS, R, opt, reads, what):
+    """Every region of `reads` through the shipped CIGAR tiers on the host: pos / contig / strand / NM / score / sub / CIGAR words against the
+    reference's mem_reg2aln, and the GetAlignments walk's fields (matches, mismatches, indels, clips, mismatch loci on both axes) against
+    the warp tier's implementation of the same walk (csrc/cigar.cuh in the host build).  -> counts."""
+    from arachne_b200.lib import ALNREG
+    seq, off = util.pack(reads)
+    ref = R.batch(seq, off, rescue=True, cigar=True, threads=4)
+    regs = ref["regs"].view(ALNREG); ro = ref["reg_off"]
+    alns, cig, mm, list3, cnt = HS.cigar_tiers(opt, seq, off, ro, regs)
+    left = set(int(g) for g in list3)
+    reg_read = np.repeat(np.arange(len(reads)), np.diff(ro))
+    n_gapped = 0
+    for g in range(len(regs)):
+        if g in left:
+            continue
+        a, e = alns[g], ref["aln"][g]
+        assert (a["pos"], a["rid"], a["is_rev"], a["nm"], a["n_cigar"], a["score"], a["sub"]) == (e[0], e[1], e[2], e[3], e[4], e[6], e[7]), (what, g)
+        c = cig[a["cigar_off"]:a["cigar_off"] + a["n_cigar"]]
+        assert np.array_equal(c, ref["cigar"][e[5]:e[5] + e[4]]), (what, g)
+        n_gapped += bool(np.any(((c & 0xf) == 1) | ((c & 0xf) == 2)))
+        w, wc, wm = HS.reg2aln(reads[reg_read[g]], regs[g:g + 1])
+        for f in ("matches", "mismatches", "indels", "soft_clipped", "soft_clipped_length", "n_mm"):
+            assert a[f] == w[f], (what, g, f)
+        assert np.array_equal(mm[a["mm_off"]:a["mm_off"] + 2 * a["n_mm"]], wm), (what, g)
+    cnt["regions"] = len(regs); cnt["gapped"] = n_gapped
+    return cnt
+
+
+def test_hostsim_shipped_cigar_tiers(HS, workdir):
+    """Row a13 (+ the walk of a15) on the code the GPU runs for nearly every region: csrc/cigar_kernel.cuh's k_cigar_fast and k_cigar_band
+    compiled for the host through tests/hostsim/cuda_lane_shim.h and run one lane at a time (a lane owns its regions, ring column and
+    traceback slice), staged as csrc/batch.inl stages them.  Reads of 100 / 150 / 250 bases with substitutions and indels, wrecked mates."""
+    from oracle.refbwa import RefBwa, available
+    if not available():
+        pytest.skip("oracle/_ref not built")
+    from arachne_b200 import ArachneCuda, simulate as S
+    opt = ArachneCuda().opt
+    fa, ctg, rs = util.make_dataset("rep600k", workdir, damaged=True)
+    R = RefBwa().load(fa); HS.load(fa)
+    tot = dict(regions=0, gapped=0, tier2=0, tier3=0, band_cells=0)
+    sets = [("rep600k", [rs.seq[rs.off[i]:rs.off[i + 1]] for i in range(600)])]
+    for L, seed in ((100, 5), (250, 6)):
+        r2 = S.simulate_linked_reads(ctg, n_barcodes=6, seed=seed, read_len=L, sub=0.03, ins=0.01, dele=0.01)
+        sets.append(("len%d" % L, [r2.seq[r2.off[i]:r2.off[i + 1]] for i in range(min(300, 2 * r2.n_pairs))]))
+    for what, reads in sets:
+        c = _check_cigar_tiers(HS, R, opt, reads, what)
+        for k in tot:
+            tot[k] += c[k]
+    assert tot["tier3"] < tot["regions"] // 2 and tot["regions"] > 1500 and tot["gapped"] > 300 and tot["tier2"] > 300 and tot["band_cells"] > 100000, tot
+
+
 def test_hostsim_seed_intervals_live(HS, workdir):
     """mem_collect_intv restated from bwt_smem1 / bwt_seed_strategy1 calls on the reference's code (needs oracle/_ref)."""
     from oracle.refbwa import RefBwa, available

@@ -156,6 +156,8 @@ class HostSim:
                               C.c_void_p, C.POINTER(C.c_int), C.c_int]
         L.hs_reg2aln.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint8), C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32), C.c_int, C.POINTER(C.c_int32)]
         L.hs_introsort_regs.argtypes = [C.c_int, C.c_int, C.c_void_p]
+        L.hs_cigar_tiers.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(C.c_uint8), C.POINTER(C.c_int64), C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
+                                     C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64), C.c_void_p, C.POINTER(C.c_uint64)]
         L.hs_seed_index.restype = C.c_void_p; L.hs_seed_index.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int]
         L.hs_seed_index_free.argtypes = [C.c_void_p]
         L.hs_seed2.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(C.c_uint8), C.POINTER(C.c_int64), C.c_int, C.c_int, C.c_int, C.c_int,
@@ -204,6 +206,21 @@ class HostSim:
                                iv.ctypes.data_as(C.POINTER(C.c_uint64)), cap, io.ctypes.data_as(C.POINTER(C.c_int64)), st)
         assert rc == 0, rc
         return io, iv[:io[-1]], (int(st[0]), int(st[1]))
+
+    def cigar_tiers(self, opt, seq, off, reg_off, regs):
+        """The shipped lane-per-region CIGAR tiers (csrc/cigar_kernel.cuh) run one lane at a time over every region of the batch.
+        -> (alns [n_regs] ALN records, cigar pool, mismatch pool, list3 = regions left to the warp tier, dict of counts)."""
+        from arachne_b200.lib import ALN
+        seq, sp = u8p(seq); off = np.ascontiguousarray(off, dtype=np.int64); n_reads = len(off) - 1
+        regs = np.ascontiguousarray(regs); n = len(regs)
+        reg_read = np.repeat(np.arange(n_reads, dtype=np.int32), np.diff(reg_off).astype(np.int64))
+        alns = np.zeros(n + 1, dtype=ALN); cig_cap = 64 * n + 4096; mm_cap = 600 * n + 4096
+        cig = np.zeros(cig_cap, np.uint32); mm = np.zeros(mm_cap, np.int32); used = (C.c_uint64 * 2)(); counts = (C.c_uint64 * 3)()
+        list3 = np.zeros(n + 1, np.uint32)
+        rc = self.lib.hs_cigar_tiers(self.h, C.byref(opt), n_reads, sp, off.ctypes.data_as(C.POINTER(C.c_int64)), n, regs.ctypes.data, reg_read.ctypes.data,
+                                     alns.ctypes.data, cig.ctypes.data, cig_cap, mm.ctypes.data, mm_cap, used, list3.ctypes.data, counts)
+        assert rc == 0, rc
+        return alns[:n], cig[:used[0]], mm[:used[1]], list3[:counts[1]].copy(), dict(tier2=int(counts[0]), tier3=int(counts[1]), band_cells=int(counts[2]))
 
     def introsort_regs(self, mode, regs):
         out = regs.copy()
