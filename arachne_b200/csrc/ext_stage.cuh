@@ -182,6 +182,13 @@ struct ExtDpArgs {
     Counters* cnt;
 };
 
+// PRMT, default mode (see cig_prmt in cigar_kernel.cuh); the host definition serves the TEST-ONLY warp emulation (tests/hostsim/hostsim_extdp.cpp)
+#if defined(__CUDACC__)
+__device__ __forceinline__ int xdp_prmt(uint32_t lo, uint32_t hi, uint32_t sel) { int s; asm("prmt.b32 %0, %1, %2, %3;" : "=r"(s) : "r"(lo), "r"(hi), "r"(sel)); return s; }
+#else
+inline int xdp_prmt(uint32_t lo, uint32_t hi, uint32_t sel) { return (int)__byte_perm(lo, hi, sel); }
+#endif
+
 // Column-word codecs.  Narrow (the pipeline's): E << 24 | H << 16 | PRMT selector, scores <= 255.  Wide: E << 17 | H << 4 | q,
 // 13-bit scores, plain mask-and-shift code -- only for callers of the stage entry point whose h0 + a * qlen exceeds a byte.
 template <bool kWide> struct XCol;
@@ -189,7 +196,7 @@ template <> struct XCol<false> {
     static __device__ __forceinline__ uint32_t init(int h, uint32_t q) { return (uint32_t)h << 16 | (q * 0x1111u + 0x8880u); }
     static __device__ __forceinline__ int H(uint32_t w) { return (int)__byte_perm(w, 0u, 0x4442); }
     static __device__ __forceinline__ int E(uint32_t w) { return (int)(w >> 24); }
-    static __device__ __forceinline__ int score(uint32_t lo, uint32_t hi, uint32_t w) { int s; asm("prmt.b32 %0, %1, %2, %3;" : "=r"(s) : "r"(lo), "r"(hi), "r"(w)); return s; }
+    static __device__ __forceinline__ int score(uint32_t lo, uint32_t hi, uint32_t w) { return xdp_prmt(lo, hi, w); }
     static __device__ __forceinline__ uint32_t pack(uint32_t w, int h, int e, int c256) { return __byte_perm(w, (uint32_t)(e * c256 + h), 0x5410); }
     static __device__ __forceinline__ uint32_t with_h(uint32_t w, int h) { return (w & 0xffffu) | (uint32_t)h << 16; }
     static __device__ __forceinline__ bool zero(uint32_t w) { return (w >> 16) == 0; }

@@ -140,14 +140,17 @@ AR_HD int sort_dedup_patch(Ctx& ctx, const MemOpt& opt, const RefView& ref, cons
             const int64_t ov_qry = old.qb < cur.qb ? old.qe - cur.qb : cur.qe - old.qb;
             const int64_t len_ref = ar_min(old.re - old.rb, cur.re - cur.rb), len_qry = (int64_t)ar_min(old.qe - old.qb, cur.qe - cur.qb);
             if (ov_ref > opt.mask_level_redun * len_ref && ov_qry > opt.mask_level_redun * len_qry) {  // one of them is redundant
-                if (cur.score < old.score) { if (lead) cur.qe = cur.qb; ctx.sync(); break; }
-                if (lead) old.qe = old.qb;
+                const bool drop_cur = cur.score < old.score;
+                ctx.sync();  // every lane has read the pair before the leader marks one of them (a lane still reading would take another branch)
+                if (lead) { if (drop_cur) cur.qe = cur.qb; else old.qe = old.qb; }
                 ctx.sync();
+                if (drop_cur) break;
             } else if (old.rb < cur.rb && query != nullptr) {
                 int w = 0;
                 const int merged = patch_reg(ctx, opt, ref, query, old, cur, &w, rbuf, rcap);
                 if (merged < 0) return merged;
                 if (merged > 0) {
+                    ctx.sync();
                     if (lead) {
                         const int n_comp = (cur.n_comp_is_alt & 0x3fffffff) + (old.n_comp_is_alt & 0x3fffffff) + 1;
                         cur.n_comp_is_alt = (cur.n_comp_is_alt & ~0x3fffffff) | (n_comp & 0x3fffffff);
@@ -163,6 +166,7 @@ AR_HD int sort_dedup_patch(Ctx& ctx, const MemOpt& opt, const RefView& ref, cons
         }
     }
     int m = 0;
+    ctx.sync();  // the loop's last reads are done before the leader compacts and re-sorts the array
     if (lead) {
         m = compact(n);
         ks_introsort((size_t)m, a, [](const AlnReg& x, const AlnReg& y) {

@@ -1,6 +1,7 @@
 #!/usr/bin/env python
 """Time-boxed differential fuzzing of what runs without a GPU, each against the reference's own compiled C code (oracle/_ref):
-  ksw    the oracle's restatement of ksw_extend2 / ksw_global2 / ksw_align2 (the checker of the GPU DP tests) on random + adversarial problems
+  ksw    the oracle's restatement of ksw_extend2 / ksw_global2 / ksw_align2 (the checker of the GPU DP tests) on random + adversarial problems,
+         and the SHIPPED extension DP kernel k_ext_dp run as one warp of fibers on the host
   index  the index-construction driver (csrc/index_build.cuh on the test-only host backend) -> .bwt / .sa bytes vs `bwa index`
   pack   arachne_index_pack -> .pac / .ann / .amb vs `bwa index` on FASTA with N runs, IUPAC codes, lower case, CRLF, odd line widths
   ingest the FASTQ ingest (csrc/ingest.cu) vs the line-by-line Python restatement of reader.go in tests/test_cpu_tier.py (the one part
@@ -28,10 +29,18 @@ def fail(what, **kw):
 
 
 # ---- ksw ----
-O = util.oracle_lib(); R = RefBwa(); t0 = time.time(); n = 0; seed = seed0
+O = util.oracle_lib(); R = RefBwa(); t0 = time.time(); n = 0; seed = seed0; n_dp = 0
+HS = util.HostSim(); OPT = ArachneCuda().opt
 while "ksw" in parts and time.time() - t0 < budget:
     g = np.random.default_rng(seed)
     qs, ts, h0, w = util.extension_problems(seed, 300)
+    # the SHIPPED DP kernel k_ext_dp as one warp of fibers on the host (tests/hostsim/hostsim_extdp.cpp), against the reference itself
+    zd, eb = [(100, 5), (0, 0), (20, 5), (10, 0), (1, 0)][seed % 5]
+    got, _ = HS.ext_dp(OPT, qs, ts, h0, w, end_bonus=eb, zdrop=zd, codec=seed % 2, warp=seed % 4)
+    for i in range(len(qs)):
+        if tuple(int(x) for x in got[i]) != R.ksw_extend2(qs[i], ts[i], int(w[i]), eb, zd, int(h0[i])):
+            fail("k_ext_dp", seed=seed, i=i)
+    n_dp += len(qs)
     for i in range(len(qs)):
         zd, eb = [(100, 5), (0, 0), (20, 5), (10, 0), (1, 0)][i % 5]
         if util.orc_extend(O, qs[i], ts[i], int(w[i]), eb, zd, int(h0[i]))[0] != R.ksw_extend2(qs[i], ts[i], int(w[i]), eb, zd, int(h0[i])):
@@ -47,7 +56,7 @@ while "ksw" in parts and time.time() - t0 < budget:
                 fail("ksw_align2", seed=seed, i=i)
         n += 1
     seed += 1
-out["ksw"] = dict(problems=n, seconds=round(time.time() - t0, 1))
+out["ksw"] = dict(problems=n, shipped_dp_kernel_problems=n_dp, seconds=round(time.time() - t0, 1))
 
 # ---- index construction ----
 t0 = time.time(); n = 0; seed = seed0; total = 0

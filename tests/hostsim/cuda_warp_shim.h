@@ -1,0 +1,116 @@
+// TEST-ONLY: one WARP of a kernel on the host, for kernels whose lanes cooperate (shuffles, ballots, warp reductions, one lane writing
+// another lane's shared-memory column between warp barriers: k_ext_dp).  The 32 lanes are 32 fibers (ucontext) of one host thread, each
+// with its own stack = its own registers; a collective (__shfl_sync, __ballot_sync, __reduce_max_sync, __syncwarp -- always with the full
+// mask in the kernels run here) is a rendezvous: a lane publishes its operand, yields until all 32 have arrived, and reads the others'.
+// Between collectives a lane runs alone, which is one of the interleavings the hardware allows; shared memory is ordinary memory, ordered
+// by the rendezvous exactly where the kernel has a barrier.  A kernel that skipped a barrier it needs could still pass here -- this checks
+// the arithmetic and the protocol, not races.  g++ compiles the kernel source unchanged.  Never shipped.
+#pragma once
+#include <ucontext.h>
+#include <cstdio>
+#include <cstdlib>
+#include <functional>
+#include <vector>
+#include "cuda_shim_common.h"
+
+namespace warpsim {
+constexpr int W = 32;
+struct Lane { ucontext_t ctx; std::vector<char> stack; LaneIdx3 tid; bool done = false; };
+struct Warp {
+    Lane lane[W];
+    ucontext_t sched;
+    int cur = 0;
+    unsigned long long xchg[2][W];  // operands of collective number g live in xchg[g & 1]
+    long gen = 0;                   // collectives completed by the whole warp
+    int arrived = 0;
+    long lane_gen[W];               // collectives each lane has entered
+    std::function<void()> body;
+};
+inline Warp*& cur_warp() { static Warp* w = nullptr; return w; }
+inline void yield() { Warp* w = cur_warp(); swapcontext(&w->lane[w->cur].ctx, &w->sched); }
+// enter collective: publish v, wait for the warp; returns the buffer holding this collective's operands
+inline const unsigned long long* rendezvous(unsigned long long v) {
+    Warp* w = cur_warp();
+    const int me = w->cur;
+    const long g = w->lane_gen[me]++;
+    if (g != w->gen) { fprintf(stderr, "warpsim: lane %d entered collective %ld while the warp is at %ld (divergent collective)\n", me, g, w->gen); abort(); }
+    w->xchg[g & 1][me] = v;
+    if (++w->arrived == W) { w->arrived = 0; ++w->gen; }
+    while (w->gen <= g) yield();
+    return w->xchg[g & 1];
+}
+inline void lane_entry() { Warp* w = cur_warp(); w->body(); w->lane[w->cur].done = true; yield(); }
+// run `body` as 32 lanes with threadIdx.x = first_tid .. first_tid + 31
+inline void run_warp(unsigned first_tid, const std::function<void()>& body) {
+    Warp* w = new Warp();
+    cur_warp() = w;
+    w->body = body;
+    for (int l = 0; l < W; ++l) {
+        Lane& L = w->lane[l];
+        L.stack.resize(1 << 20); L.tid.x = first_tid + (unsigned)l; w->lane_gen[l] = 0;
+        getcontext(&L.ctx);
+        L.ctx.uc_stack.ss_sp = L.stack.data(); L.ctx.uc_stack.ss_size = L.stack.size(); L.ctx.uc_link = &w->sched;
+        makecontext(&L.ctx, lane_entry, 0);
+    }
+    for (;;) {
+        int live = 0;
+        for (int l = 0; l < W; ++l) {
+            if (w->lane[l].done) continue;
+            ++live; w->cur = l;
+            swapcontext(&w->sched, &w->lane[l].ctx);
+        }
+        if (!live) break;
+        int finished = 0;
+        for (int l = 0; l < W; ++l) finished += w->lane[l].done;
+        if (w->arrived > 0 && finished > 0 && w->arrived + finished == W) {
+            fprintf(stderr, "warpsim: %d lanes wait in a collective that the %d finished lanes will never enter\n", w->arrived, finished); abort();
+        }
+    }
+    cur_warp() = nullptr;
+    delete w;
+}
+}  // namespace warpsim
+
+static LaneIdx3 blockIdx;
+static LaneDim3 blockDim, gridDim;
+#define threadIdx (warpsim::cur_warp()->lane[warpsim::cur_warp()->cur].tid)
+#define __shared__            /* `extern __shared__ T name[]` names a global array the test defines; a kernel with block-scope __shared__
+                                 arrays would get one copy per lane here and must not be RUN under this shim (compiling it is fine) */
+
+inline void __syncwarp(unsigned = 0xffffffffu) { warpsim::rendezvous(0); }
+inline void __syncthreads() { warpsim::rendezvous(0); }   // (only kernels of one warp per block are RUN under this shim)
+inline unsigned __ballot_sync(unsigned, bool p) {
+    const unsigned long long* x = warpsim::rendezvous(p ? 1u : 0u);
+    unsigned m = 0;
+    for (int l = 0; l < warpsim::W; ++l) m |= (unsigned)(x[l] & 1u) << l;
+    return m;
+}
+inline bool __all_sync(unsigned m, bool p) { return __ballot_sync(m, p) == 0xffffffffu; }
+inline bool __any_sync(unsigned m, bool p) { return __ballot_sync(m, p) != 0u; }
+template <class T> inline T __shfl_sync(unsigned, T v, int src) {
+    static_assert(sizeof(T) <= 8, "shuffle operand");
+    unsigned long long raw = 0; memcpy(&raw, &v, sizeof(T));
+    const unsigned long long* x = warpsim::rendezvous(raw);
+    T out; memcpy(&out, &x[src & 31], sizeof(T));
+    return out;
+}
+inline int __reduce_max_sync(unsigned, int v) {
+    const unsigned long long* x = warpsim::rendezvous((unsigned long long)(long long)v);
+    int m = (int)(long long)x[0];
+    for (int l = 1; l < warpsim::W; ++l) m = std::max(m, (int)(long long)x[l]);
+    return m;
+}
+template <class T> inline T __shfl_up_sync(unsigned, T v, unsigned delta) {  // lanes below delta keep their own value
+    static_assert(sizeof(T) <= 8, "shuffle operand");
+    unsigned long long raw = 0; memcpy(&raw, &v, sizeof(T));
+    const int me = warpsim::cur_warp()->cur;
+    const unsigned long long* x = warpsim::rendezvous(raw);
+    T out; memcpy(&out, &x[me >= (int)delta ? me - (int)delta : me], sizeof(T));
+    return out;
+}
+inline int __reduce_min_sync(unsigned, int v) {
+    const unsigned long long* x = warpsim::rendezvous((unsigned long long)(long long)v);
+    int m = (int)(long long)x[0];
+    for (int l = 1; l < warpsim::W; ++l) m = std::min(m, (int)(long long)x[l]);
+    return m;
+}

@@ -229,11 +229,17 @@ def test_hostsim_pipeline_live(HS, workdir):
     from arachne_b200.lib import ALNREG
     exp = ref["regs"].view(ALNREG); ro = ref["reg_off"]
     exp1 = plain["regs"].view(ALNREG); ro1 = plain["reg_off"]
-    n_rescued = n_cig = n_gapped = 0
+    n_rescued = n_cig = n_gapped = n_warp_rescued = n_warp_cig = 0
+    from arachne_b200 import ArachneCuda
+    opt = ArachneCuda().opt
     for p in range(n_pairs):
         for k in (2 * p, 2 * p + 1):
             assert HS.align1(reads[k]).tobytes() == exp1[ro1[k]:ro1[k + 1]].tobytes(), ("align1", k)
         o1, o2 = HS.pair(reads[2 * p], reads[2 * p + 1])
+        if p % 2 == 0:  # the same rescue on the device's own warp primitives (csrc/warp_ctx.cuh as a warp of 32 fibers: striped-semantics local SW, leader writes)
+            w1, w2 = HS.pair_warp(opt, reads[2 * p], reads[2 * p + 1], exp1[ro1[2 * p]:ro1[2 * p + 1]], exp1[ro1[2 * p + 1]:ro1[2 * p + 2]])
+            assert w1.tobytes() == exp[ro[2 * p]:ro[2 * p + 1]].tobytes() and w2.tobytes() == exp[ro[2 * p + 1]:ro[2 * p + 2]].tobytes(), ("warp rescue", p)
+            n_warp_rescued += int(len(w1) != ro1[2 * p + 1] - ro1[2 * p]) + int(len(w2) != ro1[2 * p + 2] - ro1[2 * p + 1])
         for k, got in ((2 * p, o1), (2 * p + 1, o2)):
             assert got.tobytes() == exp[ro[k]:ro[k + 1]].tobytes(), ("pair", k)
             n_rescued += int(ro[k + 1] - ro[k] != ro1[k + 1] - ro1[k])
@@ -243,8 +249,12 @@ def test_hostsim_pipeline_live(HS, workdir):
                     e = ref["aln"][j]
                     assert (a["pos"], a["rid"], a["is_rev"], a["nm"], a["n_cigar"], a["score"], a["sub"]) == (e[0], e[1], e[2], e[3], e[4], e[6], e[7]), j
                     assert np.array_equal(cig, ref["cigar"][e[5]:e[5] + e[4]]), j
+                    if p % 8 == 0:  # the same region on the device's warp tier (WarpCtx: ksw_global2 striped over 32 lanes, leader backtrack)
+                        wa, wcig, wmm = HS.reg2aln_warp(opt, reads[k], exp[j:j + 1])
+                        assert all(wa[f] == a[f] for f in a.dtype.names if f not in ("cigar_off", "mm_off")) and np.array_equal(wcig, cig) and np.array_equal(wmm, _mm), ("warp tier", j)
+                        n_warp_cig += 1
                     n_cig += 1; n_gapped += len(cig) > 1 and bool(np.any((cig & 0xf) != 0) and np.any((cig & 0xf) == 1) | np.any((cig & 0xf) == 2))
-    assert n_rescued >= 10 and n_cig >= 500 and n_gapped >= 20, (n_rescued, n_cig, n_gapped)
+    assert n_rescued >= 10 and n_cig >= 500 and n_gapped >= 20 and n_warp_rescued >= 5 and n_warp_cig >= 100, (n_rescued, n_cig, n_gapped, n_warp_rescued, n_warp_cig)
 
 
 def _seed_test_reads(ctg, rs, n_sim=160):
@@ -353,6 +363,40 @@ def test_hostsim_shipped_cigar_tiers(HS, workdir):
         for k in tot:
             tot[k] += c[k]
     assert tot["tier3"] < tot["regions"] // 2 and tot["regions"] > 1500 and tot["gapped"] > 300 and tot["tier2"] > 300 and tot["band_cells"] > 100000, tot
+
+
+def test_hostsim_shipped_extension_dp_kernel(HS, O):
+    """Row a10 on the code the GPU runs: k_ext_dp (csrc/ext_stage.cuh) -- one problem per lane, row-synchronous, descriptor pool dealt out by
+    shuffles, first rows filled by the whole warp, DPX cells on packed column words, both column codecs -- compiled for the host and run as
+    one warp of 32 fibers (tests/hostsim/cuda_warp_shim.h: every collective is a rendezvous of the 32 lanes), against the oracle's
+    ksw_extend2 on the random + adversarial problems of the GPU test, and against the REFERENCE's answers on the targeted edge cases of
+    tests/golden/ksw_edge.npz (rows dying at once, z-drop, long gaps under bands 1..256, N bases, 1-base / empty operands, stale columns)."""
+    from arachne_b200 import ArachneCuda
+    opt = ArachneCuda().opt
+    qs, ts, h0, w = util.extension_problems(101, 1500)
+    for codec in ("byte", "wide"):
+        if codec == "byte":
+            hh = np.minimum(h0, 255 - np.array([len(x) for x in qs])).astype(np.int32)
+            keep = [i for i in range(len(qs)) if hh[i] > 0]
+        else:
+            hh = h0; keep = list(range(len(qs)))
+        q2 = [qs[i] for i in keep]; t2 = [ts[i] for i in keep]; h2 = hh[keep]; w2 = w[keep]
+        for k, (zdrop, eb) in enumerate(((100, 5), (0, 0), (20, 5))):
+            out, cells = HS.ext_dp(opt, q2, t2, h2, w2, end_bonus=eb, zdrop=zdrop, codec=1 if codec == "wide" else 0, warp=k)
+            tot = 0
+            for i in range(len(q2)):
+                exp, c = util.orc_extend(O, q2[i], t2[i], int(w2[i]), eb, zdrop, int(h2[i]))
+                assert tuple(out[i]) == exp, (codec, zdrop, i, tuple(out[i]), exp)
+                tot += c
+            assert cells == tot   # the GCUPS numerator: the reference's own in-band count
+    d = util.load_golden("ksw_edge")
+    pr = _problems(d, "ext"); par = d["ext_par"]
+    for zd, eb in sorted(set((int(p[2]), int(p[3])) for p in par)):
+        sel = [i for i in range(len(pr)) if (int(par[i][2]), int(par[i][3])) == (zd, eb)]
+        for codec in (0, 1):
+            out, _ = HS.ext_dp(opt, [pr[i][0] for i in sel], [pr[i][1] for i in sel], par[sel, 0], par[sel, 1], end_bonus=eb, zdrop=zd, codec=codec, warp=3)
+            for k, i in enumerate(sel):
+                assert tuple(out[k]) == tuple(d["ext_out"][i]), ("edge", i, zd, eb, codec, tuple(out[k]), tuple(d["ext_out"][i]))
 
 
 def test_hostsim_seed_intervals_live(HS, workdir):

@@ -156,6 +156,11 @@ class HostSim:
                               C.c_void_p, C.POINTER(C.c_int), C.c_int]
         L.hs_reg2aln.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint8), C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32), C.c_int, C.POINTER(C.c_int32)]
         L.hs_introsort_regs.argtypes = [C.c_int, C.c_int, C.c_void_p]
+        L.hs_reg2aln_warp.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_uint8), C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32), C.c_int, C.POINTER(C.c_int32)]
+        L.hs_pair_rescue_warp.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_uint8), C.c_int, C.POINTER(C.c_uint8), C.c_int, C.c_void_p, C.POINTER(C.c_int),
+                                          C.c_void_p, C.POINTER(C.c_int), C.c_int]
+        L.hs_ext_dp.argtypes = [C.c_void_p, C.c_int64, C.POINTER(C.c_uint8), C.POINTER(C.c_int64), C.POINTER(C.c_uint8), C.POINTER(C.c_int64), C.c_void_p, C.c_void_p,
+                                C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.POINTER(C.c_uint64)]
         L.hs_cigar_tiers.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(C.c_uint8), C.POINTER(C.c_int64), C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
                                      C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64), C.c_void_p, C.POINTER(C.c_uint64)]
         L.hs_seed_index.restype = C.c_void_p; L.hs_seed_index.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int]
@@ -221,6 +226,39 @@ class HostSim:
                                      alns.ctypes.data, cig.ctypes.data, cig_cap, mm.ctypes.data, mm_cap, used, list3.ctypes.data, counts)
         assert rc == 0, rc
         return alns[:n], cig[:used[0]], mm[:used[1]], list3[:counts[1]].copy(), dict(tier2=int(counts[0]), tier3=int(counts[1]), band_cells=int(counts[2]))
+
+    def ext_dp(self, opt, qs, ts, h0, w, end_bonus=5, zdrop=100, codec=0, warp=0):
+        """The shipped extension DP kernel k_ext_dp (csrc/ext_stage.cuh) as one warp of 32 fibers on the host (tests/hostsim/hostsim_extdp.cpp).
+        -> (n x 6 array {score, qle, tle, gtle, gscore, max_off}, in-band cells)."""
+        q, qo = pack(qs); t, to = pack(ts)
+        q, qp = u8p(np.concatenate([q, np.zeros(16, np.uint8)])); t, tp = u8p(np.concatenate([t, np.zeros(16, np.uint8)]))
+        h0 = np.ascontiguousarray(h0, dtype=np.int32); w = np.ascontiguousarray(w, dtype=np.int32)
+        out = np.zeros((len(qs), 6), np.int32); cells = C.c_uint64(0)
+        rc = self.lib.hs_ext_dp(C.byref(opt), len(qs), qp, qo.ctypes.data_as(C.POINTER(C.c_int64)), tp, to.ctypes.data_as(C.POINTER(C.c_int64)), h0.ctypes.data, w.ctypes.data,
+                                end_bonus, zdrop, codec, warp, out.ctypes.data, C.byref(cells))
+        assert rc == 0, rc
+        return out, cells.value
+
+    def pair_warp(self, opt, r1, r2, regs1, regs2, score_delta=25, cap=512):
+        """GoBwaMemMateSW's rescue on the device's own warp-cooperative context (csrc/warp_ctx.cuh) as one warp of fibers: the region lists
+        of both reads after mem_align1_core in, the lists after rescue out."""
+        from arachne_b200.lib import ALNREG
+        r1, p1 = u8p(r1); r2, p2 = u8p(r2)
+        o1 = np.zeros(cap, dtype=ALNREG); o2 = np.zeros(cap, dtype=ALNREG); o1[:len(regs1)] = regs1; o2[:len(regs2)] = regs2
+        n1 = C.c_int(len(regs1)); n2 = C.c_int(len(regs2))
+        rc = self.lib.hs_pair_rescue_warp(self.h, C.byref(opt), len(r1), p1, len(r2), p2, score_delta, o1.ctypes.data, C.byref(n1), o2.ctypes.data, C.byref(n2), cap)
+        assert rc == 0, rc
+        return o1[:n1.value], o2[:n2.value]
+
+    def reg2aln_warp(self, opt, q, reg):
+        """reg2aln on the device's warp tier (csrc/cigar.cuh with the WarpCtx of csrc/warp_ctx.cuh) as one warp of fibers."""
+        from arachne_b200.lib import ALN
+        q, qp = u8p(q); out = np.zeros(1, dtype=ALN); cap = 2 * len(q) + 64; cig = (C.c_uint32 * cap)(); mm = (C.c_int32 * (2 * len(q) + 8))()
+        r = np.ascontiguousarray(reg)
+        rc = self.lib.hs_reg2aln_warp(self.h, C.byref(opt), len(q), qp, r.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p), cig, cap, mm)
+        assert rc == 0, rc
+        a = out[0]
+        return a, np.array(cig[:a["n_cigar"]], dtype=np.uint32), np.array(mm[:2 * a["n_mm"]], dtype=np.int32)
 
     def introsort_regs(self, mode, regs):
         out = regs.copy()
