@@ -19,7 +19,7 @@ seed0 = int(sys.argv[2]) if len(sys.argv) > 2 else 1
 HS = util.HostSim()
 from arachne_b200 import ArachneCuda
 OPT = ArachneCuda().opt
-t0 = time.time(); stats = dict(rounds=0, pairs=0, regions=0, rescued_reads=0, cigars=0, gapped_cigars=0, chains_checked=0, patched_or_merged=0, occ_sa_checked=0, seed_reads_checked=0, seed_intervals=0, tier_regions=0, tier2_regions=0, tier3_regions=0)
+t0 = time.time(); stats = dict(rounds=0, pairs=0, regions=0, rescued_reads=0, cigars=0, gapped_cigars=0, chains_checked=0, patched_or_merged=0, occ_sa_checked=0, seed_reads_checked=0, seed_intervals=0, tier_regions=0, tier2_regions=0, tier3_regions=0, warp_tier_regions=0, warp_rescues=0)
 rc = lambda s: np.where(s[::-1] < 4, 3 - s[::-1], 4).astype(np.uint8)
 
 
@@ -107,6 +107,14 @@ with tempfile.TemporaryDirectory() as wd:
             if (a["pos"], a["rid"], a["is_rev"], a["nm"], a["n_cigar"], a["score"], a["sub"]) != (e[0], e[1], e[2], e[3], e[4], e[6], e[7]) or \
                     not np.array_equal(t_cig[a["cigar_off"]:a["cigar_off"] + a["n_cigar"]], ref["cigar"][e[5]:e[5] + e[4]]):
                 print(json.dumps(dict(divergence="cigar tiers", seed=seed, region=j, **stats))); sys.exit(1)
+        # what the lane tiers leave goes to the warp tier: csrc/cigar.cuh on the device's WarpCtx as a warp of 32 fibers (hostsim_rescue.cpp)
+        reg_read = np.repeat(np.arange(len(reads)), np.diff(ro))
+        for j in sorted(t_left)[:40]:
+            wa, wcig, _wmm = HS.reg2aln_warp(OPT, reads[reg_read[j]], exp[j:j + 1]); e = ref["aln"][j]
+            if (wa["pos"], wa["rid"], wa["is_rev"], wa["nm"], wa["n_cigar"], wa["score"], wa["sub"]) != (e[0], e[1], e[2], e[3], e[4], e[6], e[7]) or \
+                    not np.array_equal(wcig, ref["cigar"][e[5]:e[5] + e[4]]):
+                print(json.dumps(dict(divergence="warp cigar tier", seed=seed, region=int(j), **stats))); sys.exit(1)
+            stats["warp_tier_regions"] += 1
         stats["tier_regions"] += len(exp) - len(t_left); stats["tier2_regions"] += t_cnt["tier2"]; stats["tier3_regions"] += t_cnt["tier3"]
         for p in range(len(reads) // 2):
             for k in (2 * p, 2 * p + 1):
@@ -119,6 +127,12 @@ with tempfile.TemporaryDirectory() as wd:
                         if not (np.array_equal(gch, ech) and np.array_equal(gsd, esd)):
                             print(json.dumps(dict(divergence="chain", seed=seed, read=k, flt=flt, **stats))); sys.exit(1)
                         stats["chains_checked"] += len(ech)
+            if (ro[2 * p + 2] - ro[2 * p]) != (ro1[2 * p + 2] - ro1[2 * p]) and stats["warp_rescues"] < 40 * (stats["rounds"] + 1):
+                # a pair that rescue changed: the same on the device's own warp context (striped local SW, leader writes between barriers)
+                w1, w2 = HS.pair_warp(OPT, reads[2 * p], reads[2 * p + 1], exp1[ro1[2 * p]:ro1[2 * p + 1]], exp1[ro1[2 * p + 1]:ro1[2 * p + 2]])
+                if w1.tobytes() != exp[ro[2 * p]:ro[2 * p + 1]].tobytes() or w2.tobytes() != exp[ro[2 * p + 1]:ro[2 * p + 2]].tobytes():
+                    print(json.dumps(dict(divergence="warp rescue", seed=seed, pair=p, **stats))); sys.exit(1)
+                stats["warp_rescues"] += 1
             o1, o2 = HS.pair(reads[2 * p], reads[2 * p + 1])
             for k, got in ((2 * p, o1), (2 * p + 1, o2)):
                 if got.tobytes() != exp[ro[k]:ro[k + 1]].tobytes():
