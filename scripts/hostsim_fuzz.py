@@ -18,8 +18,8 @@ budget = float(sys.argv[1]) if len(sys.argv) > 1 else 300.0
 seed0 = int(sys.argv[2]) if len(sys.argv) > 2 else 1
 HS = util.HostSim()
 from arachne_b200 import ArachneCuda
-OPT = ArachneCuda().opt
-t0 = time.time(); stats = dict(rounds=0, pairs=0, regions=0, rescued_reads=0, cigars=0, gapped_cigars=0, chains_checked=0, patched_or_merged=0, occ_sa_checked=0, seed_reads_checked=0, seed_intervals=0, tier_regions=0, tier2_regions=0, tier3_regions=0, warp_tier_regions=0, warp_rescues=0)
+ARACHNE = ArachneCuda(); OPT = ARACHNE.opt; PO_CLS = util.PlaceOracle
+t0 = time.time(); stats = dict(rounds=0, pairs=0, regions=0, rescued_reads=0, cigars=0, gapped_cigars=0, chains_checked=0, patched_or_merged=0, occ_sa_checked=0, seed_reads_checked=0, seed_intervals=0, tier_regions=0, tier2_regions=0, tier3_regions=0, warp_tier_regions=0, warp_rescues=0, placed_candidates=0, molecules=0)
 rc = lambda s: np.where(s[::-1] < 4, 3 - s[::-1], 4).astype(np.uint8)
 
 
@@ -66,7 +66,7 @@ def make_reads(g, ctg):
         elif u < 0.40: reads[a], reads[b] = reads[b], reads[a]
         elif u < 0.43: reads[a] = g.integers(0, 4, len(reads[a])).astype(np.uint8)
         elif u < 0.45: reads[a] = reads[a][:int(g.integers(0, 25))]   # shorter than a seed, or empty
-    return reads
+    return reads, rs
 
 
 seed = seed0
@@ -84,7 +84,7 @@ with tempfile.TemporaryDirectory() as wd:
             if HS.occ(k, l) != sum(R.occ4(k, l), []) or HS.occ(k - 1, l) != sum(R.occ4(k - 1, l), []) or HS.sa(k) != R.sa(k):
                 print(json.dumps(dict(divergence="occ/sa", seed=seed, k=k, l=l, **stats))); sys.exit(1)
             stats["occ_sa_checked"] += 1
-        reads = make_reads(g, ctg)
+        reads, rs = make_reads(g, ctg)
         seq, off = util.pack(reads)
         # rows a3-a5 on the SHIPPED seeding kernel (csrc/seed_kernel.cuh run one lane at a time, tests/hostsim/hostsim_seed.cpp) with a random
         # choice of its shortcuts, against mem_collect_intv composed from the reference's bwt_smem1 / bwt_seed_strategy1
@@ -116,6 +116,19 @@ with tempfile.TemporaryDirectory() as wd:
                 print(json.dumps(dict(divergence="warp cigar tier", seed=seed, region=int(j), **stats))); sys.exit(1)
             stats["warp_tier_regions"] += 1
         stats["tier_regions"] += len(exp) - len(t_left); stats["tier2_regions"] += t_cnt["tier2"]; stats["tier3_regions"] += t_cnt["tier3"]
+        # rows a15-a20 on the SHIPPED placement kernels (csrc/place.cuh + markDuplicates; k_place_rfa as a warp of fibers, hostsim_place.cpp)
+        # against the restatement of the Go code, on this round's barcodes with a random choice of which of them run the optimizer
+        t_all = t_alns.copy()
+        for j in t_left:
+            t_all[j] = HS.reg2aln(reads[reg_read[j]], exp[j:j + 1])[0]
+        seeds = np.array([ARACHNE.name_seed(nm) for nm in rs.names], dtype=np.int64)
+        run_rfa = (g.random(len(rs.bc_off) - 1) < 0.7).astype(np.uint8)
+        pres = HS.place(off, ro, exp, t_all, rs.bc_off, run_rfa, seeds)
+        oc, ocands, olmp = PO_CLS(fa).place(seq, off, rs.bc_off, run_rfa, seeds, ro, ref["regs"], ref["aln"], ref["cigar"])
+        bad = util.place_mismatches(pres, oc, ocands, olmp)
+        if bad:
+            print(json.dumps(dict(divergence="placement", seed=seed, what=bad[:3], **stats))); sys.exit(1)
+        stats["placed_candidates"] += len(ocands); stats["molecules"] += int(max(0, ocands["molecule_id"].max() + 1)) if len(ocands) else 0
         for p in range(len(reads) // 2):
             for k in (2 * p, 2 * p + 1):
                 got = HS.align1(reads[k])

@@ -74,8 +74,11 @@ inline void run_warp(unsigned first_tid, const std::function<void()>& body) {
 static LaneIdx3 blockIdx;
 static LaneDim3 blockDim, gridDim;
 #define threadIdx (warpsim::cur_warp()->lane[warpsim::cur_warp()->cur].tid)
-#define __shared__            /* `extern __shared__ T name[]` names a global array the test defines; a kernel with block-scope __shared__
-                                 arrays would get one copy per lane here and must not be RUN under this shim (compiling it is fine) */
+#ifndef __shared__
+#define __shared__            /* `extern __shared__ T name[]` names a global array the test defines.  A kernel with block-scope __shared__
+                                 variables needs one copy per BLOCK: a test that runs such a kernel (one block at a time) defines __shared__
+                                 as `static` before including this header (hostsim_place.cpp) */
+#endif
 
 inline void __syncwarp(unsigned = 0xffffffffu) { warpsim::rendezvous(0); }
 inline void __syncthreads() { warpsim::rendezvous(0); }   // (only kernels of one warp per block are RUN under this shim)
@@ -113,4 +116,12 @@ inline int __reduce_min_sync(unsigned, int v) {
     int m = (int)(long long)x[0];
     for (int l = 1; l < warpsim::W; ++l) m = std::min(m, (int)(long long)x[l]);
     return m;
+}
+template <class T> inline T __shfl_down_sync(unsigned, T v, unsigned delta) {  // lanes whose source is beyond the warp keep their own value
+    static_assert(sizeof(T) <= 8, "shuffle operand");
+    unsigned long long raw = 0; memcpy(&raw, &v, sizeof(T));
+    const int me = warpsim::cur_warp()->cur;
+    const unsigned long long* x = warpsim::rendezvous(raw);
+    T out; memcpy(&out, &x[me + (int)delta < warpsim::W ? me + (int)delta : me], sizeof(T));
+    return out;
 }

@@ -399,6 +399,43 @@ def test_hostsim_shipped_extension_dp_kernel(HS, O):
                 assert tuple(out[k]) == tuple(d["ext_out"][i]), ("edge", i, zd, eb, codec, tuple(out[k]), tuple(d["ext_out"][i]))
 
 
+@pytest.mark.parametrize("name,rfa", [("rand1m", 1), ("rep600k", 1), ("rep600k", 0), ("stlfr", 1)])
+def test_hostsim_shipped_placement_kernels(HS, workdir, name, rfa):
+    """Rows a15-a20 on the code the GPU runs: csrc/place.cuh (candidates, tagBestAlignments with the device's Go PRNG, molecules, the
+    optimizer sweep and MAPQ) and markDuplicates of csrc/records.cuh, compiled for the host and staged as csrc/place_host.inl stages them;
+    k_place_rfa -- one warp per barcode, 23 block barriers, warp shuffles -- runs as 32 fibers whose barriers are rendezvous
+    (tests/hostsim/hostsim_place.cpp).  Against the CPU restatement of the Go code with the tolerances of the GPU test (the Go half stays
+    unpinned: both sides are restatements).  "stlfr": hundreds of pairs and dozens of molecules per barcode."""
+    from oracle.refbwa import RefBwa, available
+    if not available():
+        pytest.skip("oracle/_ref not built")
+    from arachne_b200 import ArachneCuda, simulate as S
+    from arachne_b200.lib import ALNREG
+    A = ArachneCuda(); opt = A.opt
+    if name == "stlfr":
+        fa, ctg, _ = util.make_dataset("rep600k", workdir, damaged=True)
+        rs = S.simulate_linked_reads(ctg, n_barcodes=3, seed=41, style="stlfr", dash_suffix=True, mol_per_bc=14.0, pairs_per_mol=9.0, sub=0.01)
+    else:
+        fa, ctg, rs = util.make_dataset(name, workdir, damaged=True)
+    R = RefBwa().load(fa); HS.load(fa)
+    reads = [rs.seq[rs.off[i]:rs.off[i + 1]] for i in range(2 * rs.n_pairs)]
+    ref = R.batch(rs.seq, rs.off, rescue=True, cigar=True, threads=8)
+    regs = ref["regs"].view(ALNREG)
+    alns = HS.all_alns(opt, reads, rs.seq, rs.off, ref["reg_off"], regs)
+    seeds = np.array([A.name_seed(n) for n in rs.names], dtype=np.int64)
+    run_rfa = np.full(len(rs.bc_off) - 1, rfa, np.uint8)
+    res = HS.place(rs.off, ref["reg_off"], regs, alns, rs.bc_off, run_rfa, seeds)
+    oc, ocands, olmp = util.PlaceOracle(fa).place(rs.seq, rs.off, rs.bc_off, run_rfa, seeds, ref["reg_off"], ref["regs"], ref["aln"], ref["cigar"])
+    bad = util.place_mismatches(res, oc, ocands, olmp)
+    assert not bad, (name, rfa, bad)
+    act = ocands[ocands["active"] == 1]
+    assert len(act) == 2 * rs.n_pairs
+    if rfa:
+        assert ocands["molecule_id"].max() >= 1 and act["active_molecule"].sum() > 0
+    if name == "stlfr":
+        assert np.diff(rs.bc_off).max() > 100
+
+
 def test_hostsim_seed_intervals_live(HS, workdir):
     """mem_collect_intv restated from bwt_smem1 / bwt_seed_strategy1 calls on the reference's code (needs oracle/_ref)."""
     from oracle.refbwa import RefBwa, available

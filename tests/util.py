@@ -156,6 +156,9 @@ class HostSim:
                               C.c_void_p, C.POINTER(C.c_int), C.c_int]
         L.hs_reg2aln.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint8), C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32), C.c_int, C.POINTER(C.c_int32)]
         L.hs_introsort_regs.argtypes = [C.c_int, C.c_int, C.c_void_p]
+        L.hs_place.restype = C.c_long
+        L.hs_place.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_int,
+                               C.c_void_p, C.c_void_p, C.c_long, C.c_void_p]
         L.hs_reg2aln_warp.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_uint8), C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32), C.c_int, C.POINTER(C.c_int32)]
         L.hs_pair_rescue_warp.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_uint8), C.c_int, C.POINTER(C.c_uint8), C.c_int, C.c_void_p, C.POINTER(C.c_int),
                                           C.c_void_p, C.POINTER(C.c_int), C.c_int]
@@ -259,6 +262,32 @@ class HostSim:
         assert rc == 0, rc
         a = out[0]
         return a, np.array(cig[:a["n_cigar"]], dtype=np.uint32), np.array(mm[:2 * a["n_mm"]], dtype=np.int32)
+
+    def all_alns(self, opt, reads, seq, off, reg_off, regs):
+        """The CIGAR stage's per-region records for a batch, as the device stages them: the shipped lane tiers (cigar_tiers) + the warp tier's
+        logic (reg2aln) for what they leave.  -> ALN array [n_regs] (pool offsets are not meaningful across the two sources)."""
+        alns, cig, mm, list3, cnt = self.cigar_tiers(opt, seq, off, reg_off, regs)
+        alns = alns.copy()
+        reg_read = np.repeat(np.arange(len(off) - 1), np.diff(reg_off).astype(np.int64))
+        for g in list3:
+            a, _c, _m = self.reg2aln(reads[reg_read[g]], regs[g:g + 1])
+            alns[g] = a
+        return alns
+
+    def place(self, seq_off, reg_off, regs, alns, bc_off, run_rfa, seeds, improper=-4.0, delta=17):
+        """ARACHNE_STAGE_PLACE by the shipped kernels on the host (csrc/place.cuh, csrc/records.cuh's markDuplicates; k_place_rfa as a warp of
+        fibers), staged as csrc/place_host.inl stages them.  -> dict(cand_off, cands, lmp) shaped like the library's result."""
+        from arachne_b200.lib import CAND
+        seq_off = np.ascontiguousarray(seq_off, np.int64); n_reads = len(seq_off) - 1
+        reg_off = np.ascontiguousarray(reg_off, np.uint64); regs = np.ascontiguousarray(regs); alns = np.ascontiguousarray(alns)
+        bc_off = np.ascontiguousarray(bc_off, np.int64); run_rfa = np.ascontiguousarray(run_rfa, np.uint8); seeds = np.ascontiguousarray(seeds, np.int64)
+        cap = len(regs) + n_reads + 8
+        cand_off = np.zeros(n_reads + 1, np.int64); cands = np.zeros(cap, CAND); lmp = np.zeros(max(1, len(bc_off) - 1))
+        vp = lambda a: a.ctypes.data_as(C.c_void_p)
+        n = self.lib.hs_place(self.h, n_reads, vp(seq_off), vp(reg_off), vp(regs), vp(alns), len(bc_off) - 1, vp(bc_off), vp(run_rfa), vp(seeds), improper, delta,
+                              vp(cand_off), vp(cands), cap, vp(lmp))
+        assert n >= 0, n
+        return dict(cand_off=cand_off, cands=cands[:n], lmp=lmp)
 
     def introsort_regs(self, mode, regs):
         out = regs.copy()
