@@ -49,9 +49,11 @@ extern "C" {
 // ARACHNE_STAGE_PLACE on host arrays.  reg_off: n_reads + 1; regs / alns: per region (alns = the CIGAR stage's records); bc_off: n_bc + 1 pair
 // indices; run_rfa: n_bc flags; rand_seed: n_pairs.  Outputs: cand_off (n_reads + 1), cands (capacity cand_cap), lmp (n_bc).  Returns the
 // number of candidates, or a negative error.
+// With recs_out != null also ARACHNE_STAGE_RECORDS (CheckSplitReads, the fields of every SAM record): attach_bx per barcode (null: run_rfa),
+// cig_pool = the CIGAR words alns[].cigar_off points into; rec_off: n_reads + 1, recs_out: capacity 2 * n_reads; *n_recs receives the count.
 long hs_place(void* h, int64_t n_reads, const int64_t* seq_off, const uint64_t* reg_off, const arachne_alnreg_t* regs, const arachne_aln_t* alns, int n_bc,
               const int64_t* bc_off, const uint8_t* run_rfa, const int64_t* rand_seed, double improper, int delta, int64_t* cand_off, arachne_cand_t* cands_out,
-              long cand_cap, double* lmp_out) {
+              long cand_cap, double* lmp_out, const uint8_t* attach_bx, const uint32_t* cig_pool, int64_t* rec_off_out, arachne_record_t* recs_out, long* n_recs) {
     static_assert(sizeof(AlnRec) == sizeof(arachne_aln_t) && sizeof(Cand) == sizeof(arachne_cand_t), "layouts");
     const RefView ref = *static_cast<const RefView*>(hs_ref(h));
     const int64_t n_pairs = n_reads / 2;
@@ -117,6 +119,24 @@ long hs_place(void* h, int64_t n_reads, const int64_t* seq_off, const uint64_t* 
         launch(1, [&] { k_rec_dup_keys(PA, act.data(), ka.data(), va.data()); });
         sort_pairs(ka, kb, va, vb, n_reads, 64);
         launch(1, [&] { k_rec_dup_mark(PA, act.data(), kb.data(), vb.data()); });
+        if (recs_out) {
+            static_assert(sizeof(Record) == sizeof(arachne_record_t), "Record layout");
+            const size_t nr1 = (size_t)n_reads + 1;
+            std::vector<int> ri(4 * nr1, 0); std::vector<double> rd(2 * nr1, 0.0); std::vector<unsigned long long> rcnt((size_t)n_reads + 2, 0), roff2((size_t)n_reads + 2, 0);
+            std::vector<Record> recs((size_t)2 * n_reads + 1);
+            RecArgs RA2;
+            RA2.P = PA; RA2.attach_bx = attach_bx;
+            RA2.act = act.data(); RA2.split_reg = ri.data(); RA2.split_mapq = ri.data() + nr1; RA2.split_proper = ri.data() + 2 * nr1;
+            RA2.split_as = rd.data(); RA2.split_xs = rd.data() + nr1; RA2.rec_cnt = rcnt.data(); RA2.rec_off = roff2.data(); RA2.recs = nullptr;
+            launch(1, [&] { k_rec_split(RA2); });
+            { unsigned long long run = 0; for (int64_t i = 0; i <= n_reads; ++i) { roff2[(size_t)i] = run; run += rcnt[(size_t)i]; } }
+            RA2.recs = recs.data();
+            launch(1, [&] { k_rec_emit(RA2, cig_pool); });
+            const long nrec = (long)roff2[(size_t)n_reads];
+            for (int64_t i = 0; i <= n_reads; ++i) rec_off_out[i] = (int64_t)roff2[(size_t)i];
+            memcpy(recs_out, recs.data(), (size_t)nrec * sizeof(Record));
+            *n_recs = nrec;
+        }
     }
     if (cnt.err) return cnt.err;
     for (int64_t i = 0; i <= n_reads; ++i) cand_off[i] = (int64_t)coff[(size_t)i];

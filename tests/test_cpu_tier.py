@@ -436,6 +436,52 @@ def test_hostsim_shipped_placement_kernels(HS, workdir, name, rfa):
         assert np.diff(rs.bc_off).max() > 100
 
 
+@pytest.mark.parametrize("rfa", [1, 0])
+def test_hostsim_shipped_record_kernels(HS, workdir, rfa):
+    """Row f1 on the code the GPU runs: markDuplicates, CheckSplitReads and the fields of every SAM record (csrc/records.cuh: k_rec_active,
+    k_rec_dup_keys / _mark, k_rec_split, k_rec_emit) after the shipped placement kernels, all on the host (tests/hostsim/hostsim_place.cpp),
+    against the oracle's restatement field by field -- on the GPU test's dataset (exact duplicate pairs, chimeric reads, noise reads, distant
+    mates: duplicates, split alignments, unmapped / demoted / improper records)."""
+    from oracle.refbwa import RefBwa, available
+    if not available():
+        pytest.skip("oracle/_ref not built")
+    from arachne_b200 import ArachneCuda
+    from arachne_b200.lib import ALNREG
+    from tests.test_gpu_parity import _records_dataset
+    A = ArachneCuda(); opt = A.opt
+    fa, ctg, _ = util.make_dataset("rep600k", workdir)
+    R = RefBwa().load(fa); HS.load(fa)
+    rs = _records_dataset(ctg, 77)
+    nb = len(rs.bc_off) - 1
+    reads = [rs.seq[rs.off[i]:rs.off[i + 1]] for i in range(2 * rs.n_pairs)]
+    seeds = np.array([A.name_seed(n) for n in rs.names], dtype=np.int64)
+    run_rfa = np.full(nb, rfa, np.uint8)
+    attach = (np.arange(nb) % 5 != 0).astype(np.uint8)
+    if rfa:
+        attach[:] = 1
+    ref = R.batch(rs.seq, rs.off, rescue=True, cigar=True, threads=8)
+    regs = ref["regs"].view(ALNREG)
+    alns = HS.all_alns(opt, reads, rs.seq, rs.off, ref["reg_off"], regs)
+    e = ref["aln"]
+    assert np.array_equal(alns["n_cigar"], e[:, 4])
+    alns["cigar_off"] = e[:, 5]                     # one pool for every region: the reference's (its words equal ours, checked elsewhere)
+    res = HS.place(rs.off, ref["reg_off"], regs, alns, rs.bc_off, run_rfa, seeds, records=(attach, ref["cigar"]))
+    oc, ocands, olmp, orecs = util.PlaceOracle(fa).place_records(rs.seq, rs.off, rs.bc_off, run_rfa, attach, seeds, ref["reg_off"], ref["regs"], ref["aln"], ref["cigar"])
+    bad = util.place_mismatches(res, oc, ocands, olmp)
+    assert not bad, bad
+    g = res["records"]
+    assert len(g) == len(orecs) and np.array_equal(res["rec_off"][1:] - res["rec_off"][:-1], np.bincount(orecs["read"], minlength=2 * rs.n_pairs))
+    for f in g.dtype.names:
+        if f in ("_pad", "dm"):
+            continue
+        d = np.nonzero(g[f] != orecs[f])[0]
+        assert len(d) == 0, (f, len(d), int(d[0]), g[d[0]], orecs[d[0]])
+    assert np.allclose(g["dm"], orecs["dm"], rtol=1e-9, atol=1e-12)
+    fl = g["flag"]
+    assert (g["primary"] == 0).sum() > 20 and (fl & 0x400).sum() > 10 and (fl & 0x4).sum() > 20 and (fl & 0x8).sum() > 20 and ((fl & 0x2) == 0).sum() > 50
+    assert (g["sa_reg"] >= 0).sum() > 40 and (g["has_xc"] == 1).sum() > 50 and (g["tlen"] != 0).sum() > 500
+
+
 def test_hostsim_seed_intervals_live(HS, workdir):
     """mem_collect_intv restated from bwt_smem1 / bwt_seed_strategy1 calls on the reference's code (needs oracle/_ref)."""
     from oracle.refbwa import RefBwa, available

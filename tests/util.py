@@ -158,7 +158,7 @@ class HostSim:
         L.hs_introsort_regs.argtypes = [C.c_int, C.c_int, C.c_void_p]
         L.hs_place.restype = C.c_long
         L.hs_place.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_int,
-                               C.c_void_p, C.c_void_p, C.c_long, C.c_void_p]
+                               C.c_void_p, C.c_void_p, C.c_long, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_long)]
         L.hs_reg2aln_warp.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_uint8), C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32), C.c_int, C.POINTER(C.c_int32)]
         L.hs_pair_rescue_warp.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.POINTER(C.c_uint8), C.c_int, C.POINTER(C.c_uint8), C.c_int, C.c_void_p, C.POINTER(C.c_int),
                                           C.c_void_p, C.POINTER(C.c_int), C.c_int]
@@ -274,7 +274,7 @@ class HostSim:
             alns[g] = a
         return alns
 
-    def place(self, seq_off, reg_off, regs, alns, bc_off, run_rfa, seeds, improper=-4.0, delta=17):
+    def place(self, seq_off, reg_off, regs, alns, bc_off, run_rfa, seeds, improper=-4.0, delta=17, records=None):
         """ARACHNE_STAGE_PLACE by the shipped kernels on the host (csrc/place.cuh, csrc/records.cuh's markDuplicates; k_place_rfa as a warp of
         fibers), staged as csrc/place_host.inl stages them.  -> dict(cand_off, cands, lmp) shaped like the library's result."""
         from arachne_b200.lib import CAND
@@ -284,10 +284,19 @@ class HostSim:
         cap = len(regs) + n_reads + 8
         cand_off = np.zeros(n_reads + 1, np.int64); cands = np.zeros(cap, CAND); lmp = np.zeros(max(1, len(bc_off) - 1))
         vp = lambda a: a.ctypes.data_as(C.c_void_p)
+        if records is None:
+            n = self.lib.hs_place(self.h, n_reads, vp(seq_off), vp(reg_off), vp(regs), vp(alns), len(bc_off) - 1, vp(bc_off), vp(run_rfa), vp(seeds), improper, delta,
+                                  vp(cand_off), vp(cands), cap, vp(lmp), None, None, None, None, None)
+            assert n >= 0, n
+            return dict(cand_off=cand_off, cands=cands[:n], lmp=lmp)
+        # records = (attach_bx per barcode, the CIGAR pool alns["cigar_off"] points into): also ARACHNE_STAGE_RECORDS
+        from arachne_b200.lib import RECORD
+        attach = np.ascontiguousarray(records[0], np.uint8); pool = np.ascontiguousarray(records[1], np.uint32)
+        rec_off = np.zeros(n_reads + 1, np.int64); recs = np.zeros(2 * n_reads + 1, RECORD); nrec = C.c_long(0)
         n = self.lib.hs_place(self.h, n_reads, vp(seq_off), vp(reg_off), vp(regs), vp(alns), len(bc_off) - 1, vp(bc_off), vp(run_rfa), vp(seeds), improper, delta,
-                              vp(cand_off), vp(cands), cap, vp(lmp))
+                              vp(cand_off), vp(cands), cap, vp(lmp), vp(attach), vp(pool), vp(rec_off), vp(recs), C.byref(nrec))
         assert n >= 0, n
-        return dict(cand_off=cand_off, cands=cands[:n], lmp=lmp)
+        return dict(cand_off=cand_off, cands=cands[:n], lmp=lmp, rec_off=rec_off, records=recs[:nrec.value])
 
     def introsort_regs(self, mode, regs):
         out = regs.copy()
