@@ -1,7 +1,7 @@
 // Stage kernels between seeding and extension: one SA row per seed occurrence (k_expand), bwt_sa (k_sa), chaining (k_chain).
 // Included by pipeline.cu inside the build; tests/hostsim compiles the same text for the host.
 #pragma once
-#include "index.cuh"
+#include "fmindex.cuh"
 #include "counters.cuh"
 #include "chain.cuh"
 #include "warp_ctx.cuh"

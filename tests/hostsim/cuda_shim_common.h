@@ -18,7 +18,7 @@ struct LaneIdx3 { unsigned x = 0, y = 0, z = 0; };
 
 #define __device__
 #define __host__
-#define __global__
+#define __global__ inline   /* a kernel header may be compiled into several test TUs */
 #define __forceinline__ inline
 #define __noinline__
 #define __launch_bounds__(...)

@@ -15,59 +15,67 @@
 
 namespace warpsim {
 constexpr int W = 32;
+constexpr int MAXB = 256;  // run_block: a whole block of up to 256 lanes whose only collective is __syncthreads (k_ext_binbase)
 struct Lane { ucontext_t ctx; std::vector<char> stack; LaneIdx3 tid; bool done = false; };
 struct Warp {
-    Lane lane[W];
+    Lane lane[MAXB];
+    int n = W;                      // lanes running
     ucontext_t sched;
     int cur = 0;
-    unsigned long long xchg[2][W];  // operands of collective number g live in xchg[g & 1]
-    long gen = 0;                   // collectives completed by the whole warp
+    unsigned long long xchg[2][MAXB];  // operands of collective number g live in xchg[g & 1]
+    long gen = 0;                   // collectives completed by all lanes
     int arrived = 0;
-    long lane_gen[W];               // collectives each lane has entered
+    long lane_gen[MAXB];            // collectives each lane has entered
     std::function<void()> body;
 };
 inline Warp*& cur_warp() { static Warp* w = nullptr; return w; }
 inline void yield() { Warp* w = cur_warp(); swapcontext(&w->lane[w->cur].ctx, &w->sched); }
-// enter collective: publish v, wait for the warp; returns the buffer holding this collective's operands
-inline const unsigned long long* rendezvous(unsigned long long v) {
+// enter collective: publish v, wait for the others; returns the buffer holding this collective's operands
+inline const unsigned long long* rendezvous(unsigned long long v, bool warp_level = true) {
     Warp* w = cur_warp();
     const int me = w->cur;
+    if (warp_level && w->n != W) { fprintf(stderr, "warpsim: warp collective inside run_block (only __syncthreads is emulated across warps)\n"); abort(); }
     const long g = w->lane_gen[me]++;
     if (g != w->gen) { fprintf(stderr, "warpsim: lane %d entered collective %ld while the warp is at %ld (divergent collective)\n", me, g, w->gen); abort(); }
     w->xchg[g & 1][me] = v;
-    if (++w->arrived == W) { w->arrived = 0; ++w->gen; }
+    if (++w->arrived == w->n) { w->arrived = 0; ++w->gen; }
     while (w->gen <= g) yield();
     return w->xchg[g & 1];
 }
 inline void lane_entry() { Warp* w = cur_warp(); w->body(); w->lane[w->cur].done = true; yield(); }
-// run `body` as 32 lanes with threadIdx.x = first_tid .. first_tid + 31
-inline void run_warp(unsigned first_tid, const std::function<void()>& body) {
+// run `body` as n lanes with threadIdx.x = first_tid .. first_tid + n - 1
+inline void run_lanes(unsigned first_tid, int n, size_t stack_bytes, const std::function<void()>& body) {
     Warp* w = new Warp();
     cur_warp() = w;
-    w->body = body;
-    for (int l = 0; l < W; ++l) {
+    w->body = body; w->n = n;
+    for (int l = 0; l < n; ++l) {
         Lane& L = w->lane[l];
-        L.stack.resize(1 << 20); L.tid.x = first_tid + (unsigned)l; w->lane_gen[l] = 0;
+        L.stack.resize(stack_bytes); L.tid.x = first_tid + (unsigned)l; w->lane_gen[l] = 0;
         getcontext(&L.ctx);
         L.ctx.uc_stack.ss_sp = L.stack.data(); L.ctx.uc_stack.ss_size = L.stack.size(); L.ctx.uc_link = &w->sched;
         makecontext(&L.ctx, lane_entry, 0);
     }
     for (;;) {
         int live = 0;
-        for (int l = 0; l < W; ++l) {
+        for (int l = 0; l < n; ++l) {
             if (w->lane[l].done) continue;
             ++live; w->cur = l;
             swapcontext(&w->sched, &w->lane[l].ctx);
         }
         if (!live) break;
         int finished = 0;
-        for (int l = 0; l < W; ++l) finished += w->lane[l].done;
-        if (w->arrived > 0 && finished > 0 && w->arrived + finished == W) {
+        for (int l = 0; l < n; ++l) finished += w->lane[l].done;
+        if (w->arrived > 0 && finished > 0 && w->arrived + finished == n) {
             fprintf(stderr, "warpsim: %d lanes wait in a collective that the %d finished lanes will never enter\n", w->arrived, finished); abort();
         }
     }
     cur_warp() = nullptr;
     delete w;
+}
+inline void run_warp(unsigned first_tid, const std::function<void()>& body) { run_lanes(first_tid, W, 1 << 20, body); }
+inline void run_block(int n_threads, const std::function<void()>& body) {
+    if (n_threads > MAXB) { fprintf(stderr, "warpsim: run_block of %d lanes\n", n_threads); abort(); }
+    run_lanes(0, n_threads, 1 << 17, body);
 }
 }  // namespace warpsim
 
@@ -81,7 +89,7 @@ static LaneDim3 blockDim, gridDim;
 #endif
 
 inline void __syncwarp(unsigned = 0xffffffffu) { warpsim::rendezvous(0); }
-inline void __syncthreads() { warpsim::rendezvous(0); }   // (only kernels of one warp per block are RUN under this shim)
+inline void __syncthreads() { warpsim::rendezvous(0, warpsim::cur_warp()->n == warpsim::W); }   // one warp per block (run_warp), or a whole block whose only collective this is (run_block)
 inline unsigned __ballot_sync(unsigned, bool p) {
     const unsigned long long* x = warpsim::rendezvous(p ? 1u : 0u);
     unsigned m = 0;
@@ -101,6 +109,12 @@ inline int __reduce_max_sync(unsigned, int v) {
     const unsigned long long* x = warpsim::rendezvous((unsigned long long)(long long)v);
     int m = (int)(long long)x[0];
     for (int l = 1; l < warpsim::W; ++l) m = std::max(m, (int)(long long)x[l]);
+    return m;
+}
+inline unsigned __reduce_add_sync(unsigned, unsigned v) {
+    const unsigned long long* x = warpsim::rendezvous(v);
+    unsigned m = 0;
+    for (int l = 0; l < warpsim::W; ++l) m += (unsigned)x[l];
     return m;
 }
 template <class T> inline T __shfl_up_sync(unsigned, T v, unsigned delta) {  // lanes below delta keep their own value

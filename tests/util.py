@@ -215,6 +215,22 @@ class HostSim:
         assert rc == 0, rc
         return io, iv[:io[-1]], (int(st[0]), int(st[1]))
 
+    def stages(self, opt, seq, off, intv_off, intv, rescue=True, score_delta=25, warp=0):
+        """SA intervals -> final region lists through the shipped stage kernels in batch.inl's launch order (hostsim_stages.cpp): k_expand, k_sa,
+        k_chain, the extension rounds (k_ext_drive / k_ext_binbase / k_ext_scatter / k_ext_dp on the packed reference / k_ext_roll),
+        k_ext_finish, k_init_loc, k_rescue, k_gather_regs2.  -> (reg_off [n + 1], regs, info dict)."""
+        from arachne_b200.lib import ALNREG
+        seq, sp = u8p(seq); off = np.ascontiguousarray(off, dtype=np.int64); n = len(off) - 1
+        intv = np.ascontiguousarray(intv, dtype=np.uint64); intv_off = np.ascontiguousarray(intv_off, dtype=np.int64)
+        cap = 600 * n + 4096
+        regs = np.zeros(cap, dtype=ALNREG); ro = np.zeros(n + 1, np.int64); info = np.zeros(6, np.int64)
+        self.lib.hs_stages.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
+                                       C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
+        rc = self.lib.hs_stages(self.h, C.addressof(opt), n, seq.ctypes.data, off.ctypes.data, intv.ctypes.data, intv_off.ctypes.data, 3 if rescue else 1,
+                                score_delta, warp, regs.ctypes.data, cap, ro.ctypes.data, info.ctypes.data)
+        assert rc == 0, (rc, info)
+        return ro, regs[:ro[-1]].copy(), dict(rounds=int(info[0]), total_sa=int(info[1]), problems=int(info[2]), rescued=int(info[3]))
+
     def cigar_tiers(self, opt, seq, off, reg_off, regs):
         """The shipped lane-per-region CIGAR tiers (csrc/cigar_kernel.cuh) run one lane at a time over every region of the batch.
         -> (alns [n_regs] ALN records, cigar pool, mismatch pool, list3 = regions left to the warp tier, dict of counts)."""
