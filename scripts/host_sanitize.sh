@@ -10,8 +10,8 @@ ROOT=$PWD; W=${TMPDIR:-/tmp}/arachne_sanitize; mkdir -p "$W"
 ASAN=$(gcc -print-file-name=libasan.so); TSAN=$(gcc -print-file-name=libtsan.so)
 make -s -C oracle restate
 echo "== build: hostsim with -fsanitize=address,undefined -fno-sanitize-recover=undefined"
-( cd tests/hostsim && g++ -O1 -g -std=c++17 -fPIC -shared -fsanitize=address,undefined -fno-sanitize-recover=undefined -fno-omit-frame-pointer -x c++ \
-    hostsim.cpp hostsim_index.cpp hostsim_seed.cpp hostsim_cigar.cpp hostsim_extdp.cpp hostsim_rescue.cpp hostsim_place.cpp -o "$W/libhostsim_asan.so" -L../../oracle -loracle -Wl,-rpath,"$ROOT/oracle" -lm ) || exit 1
+( cd tests/hostsim && g++ -O1 -g -std=c++17 -fPIC -fno-extern-tls-init -shared -fsanitize=address,undefined -fno-sanitize-recover=undefined -fno-omit-frame-pointer -x c++ \
+    hostsim.cpp hostsim_index.cpp hostsim_seed.cpp hostsim_cigar.cpp hostsim_extdp.cpp hostsim_rescue.cpp hostsim_place.cpp hostsim_stages.cpp -o "$W/libhostsim_asan.so" -L../../oracle -loracle -Wl,-rpath,"$ROOT/oracle" -lm ) || exit 1
 echo "== run: hostsim tests (goldens, live against the reference's C code, chain level, introsort permutations, index build)"
 ASAN_OPTIONS=detect_leaks=0 UBSAN_OPTIONS=print_stacktrace=1 LD_PRELOAD=$ASAN ARACHNE_HOSTSIM_LIB="$W/libhostsim_asan.so" \
     python -m pytest tests/test_cpu_tier.py -q -k "hostsim" -p no:cacheprovider 2>&1 | grep -v "site-packages\|<frozen" | tail -15

@@ -19,7 +19,7 @@ seed0 = int(sys.argv[2]) if len(sys.argv) > 2 else 1
 HS = util.HostSim()
 from arachne_b200 import ArachneCuda
 ARACHNE = ArachneCuda(); OPT = ARACHNE.opt; PO_CLS = util.PlaceOracle
-t0 = time.time(); stats = dict(rounds=0, pairs=0, regions=0, rescued_reads=0, cigars=0, gapped_cigars=0, chains_checked=0, patched_or_merged=0, occ_sa_checked=0, seed_reads_checked=0, seed_intervals=0, tier_regions=0, tier2_regions=0, tier3_regions=0, warp_tier_regions=0, warp_rescues=0, placed_candidates=0, molecules=0)
+t0 = time.time(); stats = dict(staged_reads=0, staged_dp_problems=0, staged_rescued_pairs=0, rounds=0, pairs=0, regions=0, rescued_reads=0, cigars=0, gapped_cigars=0, chains_checked=0, patched_or_merged=0, occ_sa_checked=0, seed_reads_checked=0, seed_intervals=0, tier_regions=0, tier2_regions=0, tier3_regions=0, warp_tier_regions=0, warp_rescues=0, placed_candidates=0, molecules=0)
 rc = lambda s: np.where(s[::-1] < 4, 3 - s[::-1], 4).astype(np.uint8)
 
 
@@ -98,6 +98,14 @@ with tempfile.TemporaryDirectory() as wd:
             stats["seed_reads_checked"] += 1; stats["seed_intervals"] += int(io[r + 1] - io[r])
         ref = R.batch(seq, off, rescue=True, cigar=True, threads=8); plain = R.batch(seq, off, rescue=False, cigar=False, threads=8)
         exp = ref["regs"].view(ALNREG); ro = ref["reg_off"]; exp1 = plain["regs"].view(ALNREG); ro1 = plain["reg_off"]
+        # rows a6-a12 on the SHIPPED stage kernels in batch.inl's launch order (k_expand .. k_ext_dp on the packed reference .. k_rescue ..
+        # k_gather_regs2 as blocks of fibers, tests/hostsim/hostsim_stages.cpp), fed with the intervals the shipped seeding kernel just produced
+        st_rescue = bool(g.random() < 0.5); st_warp = int(g.integers(0, 4)); st_wide = bool(g.random() < 0.3)
+        sro, sregs, sinfo = HS.stages(OPT, seq, off, io, iv, rescue=st_rescue, warp=st_warp, wide=st_wide)
+        want = ref if st_rescue else plain
+        if not np.array_equal(sro, want["reg_off"]) or sregs.tobytes() != want["regs"].view(ALNREG).tobytes():
+            print(json.dumps(dict(divergence="staged kernels", seed=seed, rescue=st_rescue, warp=st_warp, wide=st_wide, **stats))); sys.exit(1)
+        stats["staged_reads"] += len(reads); stats["staged_dp_problems"] += sinfo["problems"]; stats["staged_rescued_pairs"] += sinfo["rescued"]
         # row a13 on the SHIPPED lane-per-region CIGAR tiers (csrc/cigar_kernel.cuh run one lane at a time, tests/hostsim/hostsim_cigar.cpp)
         t_alns, t_cig, t_mm, t_list3, t_cnt = HS.cigar_tiers(OPT, seq, off, ro, exp)
         t_left = set(int(x) for x in t_list3)

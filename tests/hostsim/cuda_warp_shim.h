@@ -10,13 +10,14 @@
 #include <cstdio>
 #include <cstdlib>
 #include <functional>
+#include <memory>
 #include <vector>
 #include "cuda_shim_common.h"
 
 namespace warpsim {
 constexpr int W = 32;
 constexpr int MAXB = 256;  // run_block: a whole block of up to 256 lanes whose only collective is __syncthreads (k_ext_binbase)
-struct Lane { ucontext_t ctx; std::vector<char> stack; LaneIdx3 tid; bool done = false; };
+struct Lane { ucontext_t ctx; std::unique_ptr<char[]> stack; LaneIdx3 tid; bool done = false; };  // stacks are not zero-filled: only touched pages cost
 struct Warp {
     Lane lane[MAXB];
     int n = W;                      // lanes running
@@ -50,9 +51,9 @@ inline void run_lanes(unsigned first_tid, int n, size_t stack_bytes, const std::
     w->body = body; w->n = n;
     for (int l = 0; l < n; ++l) {
         Lane& L = w->lane[l];
-        L.stack.resize(stack_bytes); L.tid.x = first_tid + (unsigned)l; w->lane_gen[l] = 0;
+        L.stack.reset(new char[stack_bytes]); L.tid.x = first_tid + (unsigned)l; w->lane_gen[l] = 0;
         getcontext(&L.ctx);
-        L.ctx.uc_stack.ss_sp = L.stack.data(); L.ctx.uc_stack.ss_size = L.stack.size(); L.ctx.uc_link = &w->sched;
+        L.ctx.uc_stack.ss_sp = L.stack.get(); L.ctx.uc_stack.ss_size = stack_bytes; L.ctx.uc_link = &w->sched;
         makecontext(&L.ctx, lane_entry, 0);
     }
     for (;;) {

@@ -10,13 +10,9 @@
 #include "cuda_lane_shim.h"
 #include "../../include/arachne_cuda.h"
 #include "../../arachne_b200/csrc/common.cuh"
+#include "../../arachne_b200/csrc/counters.cuh"
 
 namespace arachne {
-struct Counters {  // csrc/pipeline.cu
-    unsigned long long occ, occ_blocks, sa_lookups, lf_steps, ext_calls, ext_cells, glb_cells;
-    int err, err_read;
-};
-inline void raise(Counters* c, int code, int read) { if (atomicCAS(&c->err, 0, code) == 0) c->err_read = read; }
 }  // namespace arachne
 #include "../../arachne_b200/csrc/cigar_kernel.cuh"
 namespace arachne { int2 ring_raw[BAND_RING * CIG_BLOCK]; }  // k_cigar_band's dynamic shared memory

@@ -8,16 +8,12 @@
 #include "cuda_warp_shim.h"
 #include "../../include/arachne_cuda.h"
 #include "../../arachne_b200/csrc/common.cuh"
+#ifndef AR_D
+#define AR_D inline
+#endif
+#include "../../arachne_b200/csrc/stage_kernels.cuh"  // Counters, ChainBufs (named by the round kernels of ext_stage.cuh, which hostsim_stages.cpp runs)
 
 namespace arachne {
-struct Counters {  // csrc/pipeline.cu
-    unsigned long long occ, occ_blocks, sa_lookups, lf_steps, ext_calls, ext_cells, glb_cells;
-    int err, err_read;
-};
-inline void raise(Counters* c, int code, int read) { if (atomicCAS(&c->err, 0, code) == 0) c->err_read = read; }
-struct ChainBufs {  // csrc/pipeline.cu (only named by the round kernels of ext_stage.cuh, which are compiled here but not run)
-    Seed* seeds; Seed* kseeds; Chain* chains; struct BNode* nodes; int32_t* order; int32_t* kept; int* n_chain; int* n_kseed;
-};
 uint32_t xcols[(ARACHNE_MAX_READ_LEN + 8) * 128];  // k_ext_dp's dynamic shared memory: [ncols][XDP_BLOCK]
 }  // namespace arachne
 #include "../../arachne_b200/csrc/ext_stage.cuh"

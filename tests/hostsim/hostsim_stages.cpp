@@ -36,8 +36,8 @@ template <class F> void warp(unsigned first_tid, unsigned block_dim, F&& f) {
 extern "C" {
 
 // intv: 4 u64 per SA interval {x0, x1, x2, info}, read r owns intv_off[r] .. intv_off[r + 1] (mem_collect_intv's output, sorted).
-// stages: 1 = regions of mem_align1_core, 3 = + mate rescue (reads 2p / 2p + 1 are a pair).  warp_id: which of a block's four warps runs the
-// warp kernels.  regs_out / reg_off (n_reads + 1): the final lists.  info: {rounds, total_sa, dp problems, pairs rescued, err, err_read}.
+// stages: 1 = regions of mem_align1_core, 3 = + mate rescue (reads 2p / 2p + 1 are a pair).  warp_id: bits 0-1 which of a block's four warps runs the
+// warp kernels, bit 2 forces k_ext_dp's 13-bit column codec (the pipeline takes it when a * max read length exceeds a byte).  regs_out / reg_off (n_reads + 1): the final lists.  info: {rounds, total_sa, dp problems, pairs rescued, err, err_read}.
 int hs_stages(void* h, const arachne_mem_opt_t* opt_, int64_t n_reads_, const uint8_t* seq, const int64_t* off, const uint64_t* intv, const int64_t* intv_off_in,
               int stages, int score_delta, int warp_id, arachne_alnreg_t* regs_out, int64_t regs_cap, int64_t* reg_off_out, int64_t* info) {
     static_assert(XDP_BLOCK == 128, "xcols is sized for 128 lanes");
@@ -107,7 +107,7 @@ int hs_stages(void* h, const arachne_mem_opt_t* opt_, int64_t n_reads_, const ui
     DA.seq = seq; DA.tbytes = nullptr; DA.res = XB.res; DA.n_items = &ctl.n_next; DA.head = &ctl.head;
     DA.ncols = std::max(1, maxlen - opt.min_seed_len) + 2;
     DA.zdrop = opt.zdrop; DA.one = 1; DA.cnt = &cnt;
-    const bool narrow = (long)opt.a * maxlen <= 255;
+    const bool narrow = (long)opt.a * maxlen <= 255 && !(warp_id & 4);
     memset(arachne::xcols, 0xcd, sizeof(arachne::xcols));
     int round = 0; long n_prob = 0;
     for (;;) {

@@ -365,6 +365,51 @@ def test_hostsim_shipped_cigar_tiers(HS, workdir):
     assert tot["tier3"] < tot["regions"] // 2 and tot["regions"] > 1500 and tot["gapped"] > 300 and tot["tier2"] > 300 and tot["band_cells"] > 100000, tot
 
 
+def _intervals_of(R, reads):
+    """mem_collect_intv of every read from the reference's own code, flattened the way the stage kernels take them."""
+    iv = [util.ref_collect_intv(R, q) for q in reads]
+    io = np.zeros(len(reads) + 1, np.int64); io[1:] = np.cumsum([len(x) for x in iv])
+    flat = np.array([t for x in iv for t in x], dtype=np.uint64).reshape(-1, 4)
+    return io, flat
+
+
+def test_hostsim_shipped_stage_kernels_in_launch_order(HS, workdir):
+    """Rows a6-a12 on the code the GPU runs, kernel by kernel in csrc/batch.inl's launch order: k_expand, k_sa, k_chain (csrc/stage_kernels.cuh),
+    the extension rounds k_ext_drive / k_ext_binbase / k_ext_scatter / k_ext_dp on the PACKED reference / k_ext_roll and k_ext_finish
+    (csrc/ext_stage.cuh), k_init_loc, k_rescue and k_gather_regs2 (csrc/pair_kernels.cuh), compiled for the host and run as blocks of fibers
+    (tests/hostsim/hostsim_stages.cpp).  Region lists byte-identical to the reference's mem_align1_core (no rescue) and GoBwaMemMateSW (with),
+    from every warp slot of the block and with either column codec of the DP kernel; pairs re-arranged into all four orientation classes."""
+    from oracle.refbwa import RefBwa, available
+    if not available():
+        pytest.skip("oracle/_ref not built")
+    from arachne_b200 import ArachneCuda
+    from arachne_b200.lib import ALNREG
+    fa, ctg, rs = util.make_dataset("rep600k", workdir, damaged=True)
+    R = RefBwa().load(fa); HS.load(fa)
+    n_pairs = min(240, rs.n_pairs)
+    reads = [rs.seq[rs.off[i]:rs.off[i + 1]].copy() for i in range(2 * n_pairs)]
+    rc = lambda s: np.where(s[::-1] < 4, 3 - s[::-1], 4).astype(np.uint8)
+    for p in range(n_pairs):
+        k = p % 8
+        if k == 5: reads[2 * p + 1] = rc(reads[2 * p + 1])
+        elif k == 6: reads[2 * p], reads[2 * p + 1] = reads[2 * p + 1], reads[2 * p]
+        elif k == 7: reads[2 * p] = rc(reads[2 * p])
+    reads[6] = np.full(40, 4, np.uint8)        # all N: no interval, no chain, no region
+    reads[9] = reads[9][:12].copy()            # shorter than a seed
+    seq, off = util.pack(reads)
+    opt = ArachneCuda().opt
+    io, flat = _intervals_of(R, reads)
+    plain = R.batch(seq, off, rescue=False, cigar=False, threads=4)
+    full = R.batch(seq, off, rescue=True, cigar=False, threads=4)
+    assert full["regs"].tobytes() != plain["regs"].tobytes(), "dataset does not exercise rescue"
+    for rescue, warp, wide, exp in ((False, 0, False, plain), (False, 2, True, plain), (True, 1, False, full), (True, 3, True, full)):
+        ro, regs, info = HS.stages(opt, seq, off, io, flat, rescue=rescue, warp=warp, wide=wide)
+        assert np.array_equal(ro, exp["reg_off"]), (rescue, warp, wide)
+        assert regs.tobytes() == exp["regs"].view(ALNREG).tobytes(), (rescue, warp, wide)
+        assert info["rounds"] >= 3 and info["problems"] >= 2 * n_pairs and info["total_sa"] >= 2 * n_pairs, info
+        assert (info["rescued"] >= 10) == rescue, info
+
+
 def test_hostsim_shipped_extension_dp_kernel(HS, O):
     """Row a10 on the code the GPU runs: k_ext_dp (csrc/ext_stage.cuh) -- one problem per lane, row-synchronous, descriptor pool dealt out by
     shuffles, first rows filled by the whole warp, DPX cells on packed column words, both column codecs -- compiled for the host and run as

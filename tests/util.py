@@ -215,7 +215,7 @@ class HostSim:
         assert rc == 0, rc
         return io, iv[:io[-1]], (int(st[0]), int(st[1]))
 
-    def stages(self, opt, seq, off, intv_off, intv, rescue=True, score_delta=25, warp=0):
+    def stages(self, opt, seq, off, intv_off, intv, rescue=True, score_delta=25, warp=0, wide=False):
         """SA intervals -> final region lists through the shipped stage kernels in batch.inl's launch order (hostsim_stages.cpp): k_expand, k_sa,
         k_chain, the extension rounds (k_ext_drive / k_ext_binbase / k_ext_scatter / k_ext_dp on the packed reference / k_ext_roll),
         k_ext_finish, k_init_loc, k_rescue, k_gather_regs2.  -> (reg_off [n + 1], regs, info dict)."""
@@ -227,7 +227,7 @@ class HostSim:
         self.lib.hs_stages.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                        C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
         rc = self.lib.hs_stages(self.h, C.addressof(opt), n, seq.ctypes.data, off.ctypes.data, intv.ctypes.data, intv_off.ctypes.data, 3 if rescue else 1,
-                                score_delta, warp, regs.ctypes.data, cap, ro.ctypes.data, info.ctypes.data)
+                                score_delta, (warp & 3) | (4 if wide else 0), regs.ctypes.data, cap, ro.ctypes.data, info.ctypes.data)
         assert rc == 0, (rc, info)
         return ro, regs[:ro[-1]].copy(), dict(rounds=int(info[0]), total_sa=int(info[1]), problems=int(info[2]), rescued=int(info[3]))
 
