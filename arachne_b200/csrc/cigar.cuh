@@ -129,7 +129,8 @@ AR_HD int reg2aln(Ctx& ctx, const MemOpt& opt, const RefView& ref, int l_query, 
         clip5 = is_rev ? l_query - qe : qb;
         clip3 = is_rev ? qb : l_query - qe;
     }
-    // final layout in place: [clip5] ops [clip3]
+    // final layout in place: [clip5] ops [clip3].  Every lane has to be done reading cigar[0] / cigar[n_cigar - 1] above before the leader moves them.
+    ctx.sync();
     if (ctx.leader()) {
         int shift = (clip5 ? 1 : 0) - c0;
         if (shift > 0) for (int k = n_cigar - 1; k >= 0; --k) cigar[k + shift] = cigar[k + c0];

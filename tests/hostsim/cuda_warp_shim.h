@@ -3,8 +3,8 @@
 // with its own stack = its own registers; a collective (__shfl_sync, __ballot_sync, __reduce_max_sync, __syncwarp -- always with the full
 // mask in the kernels run here) is a rendezvous: a lane publishes its operand, yields until all 32 have arrived, and reads the others'.
 // Between collectives a lane runs alone, which is one of the interleavings the hardware allows; shared memory is ordinary memory, ordered
-// by the rendezvous exactly where the kernel has a barrier.  A kernel that skipped a barrier it needs could still pass here -- this checks
-// the arithmetic and the protocol, not races.  g++ compiles the kernel source unchanged.  Never shipped.
+// by the rendezvous exactly where the kernel has a barrier.  The order in which lanes run between two barriers is selectable (lane_order):
+// running the tests under more than one order catches a barrier missing before or after a leader's write; it is not a race detector.  g++ compiles the kernel source unchanged.  Never shipped.
 #pragma once
 #include <ucontext.h>
 #include <cstdio>
@@ -30,6 +30,10 @@ struct Warp {
     std::function<void()> body;
 };
 inline Warp*& cur_warp() { static Warp* w = nullptr; return w; }
+// Which lane runs first between two collectives: 0 = lane 0 upwards (a leader's writes land before the others read), 1 = lane 31 downwards (the
+// others read before the leader writes), 2 = the starting lane rotates.  A kernel whose barriers are complete gives the same results under all
+// three; one that leans on lock-step execution of a converged warp does not (hs_warp_order(), WARPSIM_ORDER).
+inline int& lane_order() { static int o = getenv("WARPSIM_ORDER") ? atoi(getenv("WARPSIM_ORDER")) : 0; return o; }
 inline void yield() { Warp* w = cur_warp(); swapcontext(&w->lane[w->cur].ctx, &w->sched); }
 // enter collective: publish v, wait for the others; returns the buffer holding this collective's operands
 inline const unsigned long long* rendezvous(unsigned long long v, bool warp_level = true) {
@@ -56,13 +60,16 @@ inline void run_lanes(unsigned first_tid, int n, size_t stack_bytes, const std::
         L.ctx.uc_stack.ss_sp = L.stack.get(); L.ctx.uc_stack.ss_size = stack_bytes; L.ctx.uc_link = &w->sched;
         makecontext(&L.ctx, lane_entry, 0);
     }
+    long pass = 0;
     for (;;) {
         int live = 0;
-        for (int l = 0; l < n; ++l) {
+        for (int i = 0; i < n; ++i) {
+            const int l = lane_order() == 1 ? n - 1 - i : lane_order() == 2 ? (int)((i + pass * 7) % n) : i;
             if (w->lane[l].done) continue;
             ++live; w->cur = l;
             swapcontext(&w->sched, &w->lane[l].ctx);
         }
+        ++pass;
         if (!live) break;
         int finished = 0;
         for (int l = 0; l < n; ++l) finished += w->lane[l].done;

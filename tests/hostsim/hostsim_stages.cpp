@@ -35,6 +35,8 @@ template <class F> void warp(unsigned first_tid, unsigned block_dim, F&& f) {
 
 extern "C" {
 
+void hs_warp_order(int order) { warpsim::lane_order() = order; }  // one setting for the whole library (an inline function's static)
+
 // intv: 4 u64 per SA interval {x0, x1, x2, info}, read r owns intv_off[r] .. intv_off[r + 1] (mem_collect_intv's output, sorted).
 // stages: 1 = regions of mem_align1_core, 3 = + mate rescue (reads 2p / 2p + 1 are a pair).  warp_id: bits 0-1 which of a block's four warps runs the
 // warp kernels, bit 2 forces k_ext_dp's 13-bit column codec (the pipeline takes it when a * max read length exceeds a byte).  regs_out / reg_off (n_reads + 1): the final lists.  info: {rounds, total_sa, dp problems, pairs rescued, err, err_read}.
@@ -155,6 +157,32 @@ int hs_stages(void* h, const arachne_mem_opt_t* opt_, int64_t n_reads_, const ui
         for (unsigned long long g = reg_off[(size_t)r]; g < reg_off[(size_t)r + 1]; ++g)
             if (reg_read[(size_t)g] != r) return -21;
     if (info) { info[0] = round; info[1] = (int64_t)total_sa; info[2] = n_prob; info[3] = n_rescued; info[4] = cnt.err; info[5] = cnt.err_read; }
+    return cnt.err;
+}
+
+// The wide-band CIGAR tier as shipped: k_cigar (csrc/pair_kernels.cuh) over the regions in `list` (what k_cigar_fast / k_cigar_band handed over;
+// list == nullptr: every region), one warp of fibers.  alns: n_regs records, filled at the listed indices; pools as in batch.inl.
+int hs_k_cigar(void* h, const arachne_mem_opt_t* opt_, int64_t n_reads, const uint8_t* seq, const int64_t* off, int64_t n_regs, const arachne_alnreg_t* regs,
+               const int32_t* reg_read, const uint32_t* list, uint32_t n_list, int warp_id, arachne_aln_t* alns, uint32_t* cig_pool, uint64_t cig_cap,
+               int32_t* mm_pool, uint64_t mm_cap, uint64_t* used2) {
+    MemOpt opt; memcpy(&opt, opt_, sizeof(opt));
+    const RefView ref = *static_cast<const RefView*>(hs_ref(h));
+    int maxlen = 1;
+    for (int64_t r = 0; r < n_reads; ++r) maxlen = std::max<int>(maxlen, (int)(off[r + 1] - off[r]));
+    const int win_cap = 2 * maxlen + 1024 + 4 * opt.w;
+    const long z_cap = (long)maxlen * (maxlen + 1024);  // batch.inl's sizing of the traceback scratch
+    const int cig_scr_cap = 2 * maxlen + 64, mm_scr_cap = 2 * maxlen + 8;
+    std::vector<uint8_t> win((size_t)EXT_WARPS * win_cap), zbuf((size_t)EXT_WARPS * z_cap);
+    std::vector<uint32_t> cig_scr((size_t)EXT_WARPS * cig_scr_cap);
+    std::vector<int32_t> mm_scr((size_t)EXT_WARPS * mm_scr_cap);
+    Counters cnt; memset(&cnt, 0, sizeof(cnt));
+    unsigned long long used[2] = {0, 0}; unsigned next = 0;
+    const unsigned nl = n_list;
+    warp(32u * (unsigned)(warp_id & 3), EXT_WARPS * 32, [&] {
+        k_cigar(opt, ref, seq, off, (long)n_regs, reinterpret_cast<const AlnReg*>(regs), reg_read, reinterpret_cast<AlnRec*>(alns), cig_pool, cig_cap, mm_pool, mm_cap,
+                used, win.data(), win_cap, zbuf.data(), z_cap, cig_scr.data(), cig_scr_cap, mm_scr.data(), mm_scr_cap, &next, &cnt, list, list ? &nl : nullptr);
+    });
+    used2[0] = used[0]; used2[1] = used[1];
     return cnt.err;
 }
 

@@ -338,7 +338,18 @@ def _check_cigar_tiers(HS, R, opt, reads, what):
         for f in ("matches", "mismatches", "indels", "soft_clipped", "soft_clipped_length", "n_mm"):
             assert a[f] == w[f], (what, g, f)
         assert np.array_equal(mm[a["mm_off"]:a["mm_off"] + 2 * a["n_mm"]], wm), (what, g)
-    cnt["regions"] = len(regs); cnt["gapped"] = n_gapped
+    # what the lane tiers hand over, through the shipped wide-band kernel itself (k_cigar as a warp of fibers: queue, pools, leader stores)
+    lst = list3[:200]
+    kal, kcig, kmm = HS.k_cigar(opt, seq, off, ro, regs, lst, warp=len(reads) % 4)
+    for g in (int(x) for x in lst):
+        a, e = kal[g], ref["aln"][g]
+        assert (a["pos"], a["rid"], a["is_rev"], a["nm"], a["n_cigar"], a["score"], a["sub"]) == (e[0], e[1], e[2], e[3], e[4], e[6], e[7]), (what, "k_cigar", g)
+        assert np.array_equal(kcig[a["cigar_off"]:a["cigar_off"] + a["n_cigar"]], ref["cigar"][e[5]:e[5] + e[4]]), (what, "k_cigar", g)
+        w, wc, wm = HS.reg2aln(reads[reg_read[g]], regs[g:g + 1])
+        for f in ("matches", "mismatches", "indels", "soft_clipped", "soft_clipped_length", "n_mm"):
+            assert a[f] == w[f], (what, "k_cigar", g, f)
+        assert np.array_equal(kmm[a["mm_off"]:a["mm_off"] + 2 * a["n_mm"]], wm), (what, "k_cigar", g)
+    cnt["regions"] = len(regs); cnt["gapped"] = n_gapped; cnt["k_cigar"] = len(lst)
     return cnt
 
 
@@ -353,7 +364,7 @@ def test_hostsim_shipped_cigar_tiers(HS, workdir):
     opt = ArachneCuda().opt
     fa, ctg, rs = util.make_dataset("rep600k", workdir, damaged=True)
     R = RefBwa().load(fa); HS.load(fa)
-    tot = dict(regions=0, gapped=0, tier2=0, tier3=0, band_cells=0)
+    tot = dict(regions=0, gapped=0, tier2=0, tier3=0, band_cells=0, k_cigar=0)
     sets = [("rep600k", [rs.seq[rs.off[i]:rs.off[i + 1]] for i in range(600)])]
     for L, seed in ((100, 5), (250, 6)):
         r2 = S.simulate_linked_reads(ctg, n_barcodes=6, seed=seed, read_len=L, sub=0.03, ins=0.01, dele=0.01)
@@ -362,7 +373,7 @@ def test_hostsim_shipped_cigar_tiers(HS, workdir):
         c = _check_cigar_tiers(HS, R, opt, reads, what)
         for k in tot:
             tot[k] += c[k]
-    assert tot["tier3"] < tot["regions"] // 2 and tot["regions"] > 1500 and tot["gapped"] > 300 and tot["tier2"] > 300 and tot["band_cells"] > 100000, tot
+    assert tot["tier3"] < tot["regions"] // 2 and tot["regions"] > 1500 and tot["gapped"] > 300 and tot["tier2"] > 300 and tot["band_cells"] > 100000 and tot["k_cigar"] > 200, tot
 
 
 def _intervals_of(R, reads):

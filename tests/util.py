@@ -231,6 +231,24 @@ class HostSim:
         assert rc == 0, (rc, info)
         return ro, regs[:ro[-1]].copy(), dict(rounds=int(info[0]), total_sa=int(info[1]), problems=int(info[2]), rescued=int(info[3]))
 
+    def k_cigar(self, opt, seq, off, reg_off, regs, list3=None, warp=0):
+        """The shipped wide-band CIGAR kernel (k_cigar, csrc/pair_kernels.cuh) as a warp of fibers over the regions in list3 (None: all).
+        -> (alns [n_regs] valid at the listed regions, cigar pool, mismatch pool)."""
+        from arachne_b200.lib import ALN
+        seq, sp = u8p(seq); off = np.ascontiguousarray(off, dtype=np.int64); n_reads = len(off) - 1
+        regs = np.ascontiguousarray(regs); n = len(regs)
+        reg_read = np.repeat(np.arange(n_reads, dtype=np.int32), np.diff(reg_off).astype(np.int64))
+        alns = np.zeros(n + 1, dtype=ALN); cig_cap = 64 * n + 4096; mm_cap = 600 * n + 4096
+        cig = np.zeros(cig_cap, np.uint32); mm = np.zeros(mm_cap, np.int32); used = (C.c_uint64 * 2)()
+        lst = None if list3 is None else np.ascontiguousarray(list3, dtype=np.uint32)
+        self.lib.hs_k_cigar.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int,
+                                        C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p]
+        rc = self.lib.hs_k_cigar(self.h, C.addressof(opt), n_reads, seq.ctypes.data, off.ctypes.data, n, regs.ctypes.data, reg_read.ctypes.data,
+                                 None if lst is None else lst.ctypes.data, 0 if lst is None else len(lst), warp, alns.ctypes.data, cig.ctypes.data, cig_cap,
+                                 mm.ctypes.data, mm_cap, used)
+        assert rc == 0, rc
+        return alns[:n], cig[:used[0]], mm[:used[1]]
+
     def cigar_tiers(self, opt, seq, off, reg_off, regs):
         """The shipped lane-per-region CIGAR tiers (csrc/cigar_kernel.cuh) run one lane at a time over every region of the batch.
         -> (alns [n_regs] ALN records, cigar pool, mismatch pool, list3 = regions left to the warp tier, dict of counts)."""
