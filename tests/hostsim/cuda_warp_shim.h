@@ -9,6 +9,7 @@
 #include <ucontext.h>
 #include <cstdio>
 #include <cstdlib>
+#include <algorithm>
 #include <functional>
 #include <memory>
 #include <vector>
@@ -31,7 +32,7 @@ struct Warp {
 };
 inline Warp*& cur_warp() { static Warp* w = nullptr; return w; }
 // Which lane runs first between two collectives: 0 = lane 0 upwards (a leader's writes land before the others read), 1 = lane 31 downwards (the
-// others read before the leader writes), 2 = the starting lane rotates.  A kernel whose barriers are complete gives the same results under all
+// others read before the leader writes), 2 = the starting lane rotates, >= 3 = a random permutation per pass (the number seeds it).  A kernel whose barriers are complete gives the same results under all
 // three; one that leans on lock-step execution of a converged warp does not (hs_warp_order(), WARPSIM_ORDER).
 inline int& lane_order() { static int o = getenv("WARPSIM_ORDER") ? atoi(getenv("WARPSIM_ORDER")) : 0; return o; }
 inline void yield() { Warp* w = cur_warp(); swapcontext(&w->lane[w->cur].ctx, &w->sched); }
@@ -60,11 +61,17 @@ inline void run_lanes(unsigned first_tid, int n, size_t stack_bytes, const std::
         L.ctx.uc_stack.ss_sp = L.stack.get(); L.ctx.uc_stack.ss_size = stack_bytes; L.ctx.uc_link = &w->sched;
         makecontext(&L.ctx, lane_entry, 0);
     }
-    long pass = 0;
+    long pass = 0; int perm[MAXB];
     for (;;) {
         int live = 0;
+        if (lane_order() >= 3) {  // a fresh random permutation per pass; the order number is the seed
+            static unsigned long long rng = 0;
+            if (!rng) rng = 0x9e3779b97f4a7c15ull * (unsigned long long)lane_order();
+            for (int i = 0; i < n; ++i) perm[i] = i;
+            for (int i = n - 1; i > 0; --i) { rng = rng * 6364136223846793005ull + 1442695040888963407ull; std::swap(perm[i], perm[(rng >> 33) % (unsigned)(i + 1)]); }
+        }
         for (int i = 0; i < n; ++i) {
-            const int l = lane_order() == 1 ? n - 1 - i : lane_order() == 2 ? (int)((i + pass * 7) % n) : i;
+            const int l = lane_order() == 1 ? n - 1 - i : lane_order() == 2 ? (int)((i + pass * 7) % n) : lane_order() >= 3 ? perm[i] : i;
             if (w->lane[l].done) continue;
             ++live; w->cur = l;
             swapcontext(&w->sched, &w->lane[l].ctx);
