@@ -41,6 +41,11 @@ while "ksw" in parts and time.time() - t0 < budget:
         if tuple(int(x) for x in got[i]) != R.ksw_extend2(qs[i], ts[i], int(w[i]), eb, zd, int(h0[i])):
             fail("k_ext_dp", seed=seed, i=i)
     n_dp += len(qs)
+    # the allocation-free entry's launch sequence around the same kernel (csrc/xs_kernels.cuh; scratch persisting between calls), with refusals
+    hb = h0.copy(); bad = sorted(set(int(x) for x in g.integers(0, len(qs), 3))); hb[bad] = 0
+    got2, status, _ = HS.xs_static(OPT, qs, ts, hb, w, end_bonus=eb, zdrop=zd, warp=(seed + 1) % 4)
+    if status != bad[0] + 1 or any(tuple(got2[i]) != ((-1,) * 6 if i in bad else tuple(got[i])) for i in range(len(qs))):
+        fail("arachne_ksw_extend_static kernels", seed=seed)
     for i in range(len(qs)):
         zd, eb = [(100, 5), (0, 0), (20, 5), (10, 0), (1, 0)][i % 5]
         if util.orc_extend(O, qs[i], ts[i], int(w[i]), eb, zd, int(h0[i]))[0] != R.ksw_extend2(qs[i], ts[i], int(w[i]), eb, zd, int(h0[i])):

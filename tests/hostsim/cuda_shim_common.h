@@ -27,6 +27,7 @@ template <class T, class V> inline T atomicAdd(T* p, V v) { const T old = *p; *p
 template <class T, class V> inline T atomicSub(T* p, V v) { const T old = *p; *p = (T)(old - (T)v); return old; }
 template <class T, class V> inline T atomicExch(T* p, V v) { const T old = *p; *p = (T)v; return old; }
 template <class T, class V> inline T atomicMin(T* p, V v) { const T old = *p; if ((T)v < old) *p = (T)v; return old; }
+template <class T, class V> inline T atomicMax(T* p, V v) { const T old = *p; if ((T)v > old) *p = (T)v; return old; }
 inline int atomicCAS(int* p, int cmp, int val) { const int old = *p; if (old == cmp) *p = val; return old; }
 template <class T> inline T __ldg(const T* p) { return *p; }
 inline int __clz(int x) { return x == 0 ? 32 : __builtin_clz((unsigned)x); }

@@ -21,6 +21,7 @@ namespace arachne { thread_local uint32_t xcols[(ARACHNE_MAX_READ_LEN + 8) * 128
 #include "../../arachne_b200/csrc/stage_kernels.cuh"
 #include "../../arachne_b200/csrc/ext_stage.cuh"
 #include "../../arachne_b200/csrc/pair_kernels.cuh"
+#include "../../arachne_b200/csrc/xs_kernels.cuh"
 
 using namespace arachne;
 extern "C" const void* hs_ref(void* h);
@@ -184,6 +185,32 @@ int hs_k_cigar(void* h, const arachne_mem_opt_t* opt_, int64_t n_reads, const ui
     });
     used2[0] = used[0]; used2[1] = used[1];
     return cnt.err;
+}
+
+// arachne_ksw_extend_static()'s launch sequence (csrc/noalloc.inl) on the host: control block cleared, k_xs_count, k_xs_base (its block of 256),
+// k_xs_queue, k_ext_dp<false, true> over the sorted queue, k_xs_finish.  The queue / result arrays are NOT cleared between calls, as the static
+// scratch is not: a call must write every slot it reads.  out: n x 6, {-1 x 6} for refused problems; status: 0 or 1 + lowest refused index.
+int hs_xs_static(const arachne_mem_opt_t* opt_, int64_t n, const uint8_t* q, const int64_t* q_off, const uint8_t* t, const int64_t* t_off, const int32_t* h0,
+                 const int32_t* w, int max_qlen, int end_bonus, int zdrop, int warp_id, int32_t* out, int32_t* status, uint64_t* cells) {
+    static std::vector<ExtProb> queue(65536);   // stand-ins for the static device scratch: they keep the last call's contents
+    static std::vector<ExtRes> res(65536);
+    static XsCtl ctl;
+    if (n > 65536 || max_qlen < 1 || max_qlen > ARACHNE_MAX_READ_LEN) return ARACHNE_ERR_ARG;
+    MemOpt opt; memcpy(&opt, opt_, sizeof(opt));
+    XsIn I; I.n = (long)n; I.q_off = q_off; I.t_off = t_off; I.h0 = h0; I.w = w; I.end_bonus = end_bonus; I.max_qlen = max_qlen; I.a = opt.a;
+    memset(&ctl, 0, sizeof(ctl));
+    warp(0, 32, [&] { k_xs_count(I, &ctl, out); });
+    blockIdx.x = 0; blockDim.x = 256; gridDim.x = 1;
+    warpsim::run_block(256, [&] { k_xs_base(&ctl); });
+    warp(0, 32, [&] { k_xs_queue(I, &ctl, queue.data()); });
+    ExtDpArgs DA;
+    DA.seq = q; DA.tbytes = t; DA.queue = queue.data(); DA.res = res.data(); DA.n_items = &ctl.n_items; DA.head = &ctl.head;
+    DA.ncols = max_qlen + 2; DA.zdrop = zdrop; DA.one = 1; DA.cnt = &ctl.cnt;
+    RefView no_ref; memset(&no_ref, 0, sizeof(no_ref));
+    memset(arachne::xcols, 0xcd, sizeof(arachne::xcols));
+    warp(32u * (unsigned)(warp_id & 3), XDP_BLOCK, [&] { k_ext_dp<false, true>(opt, no_ref, DA); });
+    warp(0, 32, [&] { k_xs_finish(I, &ctl, res.data(), out, status, reinterpret_cast<unsigned long long*>(cells)); });
+    return ctl.cnt.err;
 }
 
 }  // extern "C"

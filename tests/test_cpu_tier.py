@@ -465,6 +465,53 @@ def test_hostsim_shipped_extension_dp_kernel(HS, O):
                 assert tuple(out[k]) == tuple(d["ext_out"][i]), ("edge", i, zd, eb, codec, tuple(out[k]), tuple(d["ext_out"][i]))
 
 
+def test_hostsim_allocation_free_entry_kernels(HS, O):
+    """arachne_ksw_extend_static (include/arachne_cuda.h) without a GPU: its launch sequence -- control block cleared, k_xs_count, k_xs_base
+    (block of 256), k_xs_queue, k_ext_dp<false, true>, k_xs_finish (csrc/xs_kernels.cuh, csrc/ext_stage.cuh) -- compiled for the host and run
+    as blocks of fibers over a scratch that persists between calls like the static device array.  The CPU twin of tests/test_zz_no_alloc.py,
+    against the oracle's ksw_extend2: two calls in a row (the second smaller, other parameters), refusals reported through the status word
+    with the lowest refused index, the other problems still answered."""
+    from arachne_b200 import ArachneCuda
+    opt = ArachneCuda().opt
+    qs, ts, h0, w = util.extension_problems(211, 1200)
+    assert any(int(h0[i]) + len(qs[i]) > 255 for i in range(len(qs)))
+
+    def expect(qs, ts, h0, w, eb, zd):
+        rows, tot = [], 0
+        for i in range(len(qs)):
+            e, c = util.orc_extend(O, qs[i], ts[i], int(w[i]), eb, zd, int(h0[i]))
+            rows.append(e); tot += c
+        return np.array(rows, np.int32).reshape(-1, 6), tot
+
+    exp, exp_cells = expect(qs, ts, h0, w, 5, 100)
+    out, status, cells = HS.xs_static(opt, qs, ts, h0, w, 5, 100, warp=1)
+    assert status == 0 and np.array_equal(out, exp) and cells == exp_cells
+    # straight after: fewer and other problems, other parameters; nothing of call 1 may survive in the scratch
+    sel = list(range(len(qs) - 1, 0, -3))[:300]
+    qs2 = [qs[i] for i in sel]; ts2 = [ts[i][: max(0, len(ts[i]) - 7)] for i in sel]; h2 = h0[sel]; w2 = np.maximum(1, w[sel] // 2).astype(np.int32)
+    exp2, exp_cells2 = expect(qs2, ts2, h2, w2, 0, 20)
+    out2, status2, cells2 = HS.xs_static(opt, qs2, ts2, h2, w2, 0, 20, max_qlen=255, warp=2)
+    assert status2 == 0 and np.array_equal(out2, exp2) and cells2 == exp_cells2
+    # refusals: h0 = 0 (ksw.c:385 asserts h0 > 0), a query longer than the declared bound, a score beyond the 13-bit codec; the lowest index is reported
+    h_bad = h0.copy(); h_bad[17] = 0; h_bad[400] = 8191
+    lens = np.array([len(x) for x in qs]); mq = int(np.sort(lens)[len(lens) // 2])
+    too_long = [i for i in range(len(qs)) if lens[i] > mq]
+    assert too_long
+    out3, status3, _ = HS.xs_static(opt, qs, ts, h_bad, w, 5, 100, max_qlen=mq, warp=3)
+    bad = sorted(set([17, 400] + too_long))
+    assert status3 == bad[0] + 1
+    for i in bad:
+        assert tuple(out3[i]) == (-1,) * 6, i
+    keep = [i for i in range(len(qs)) if i not in bad]
+    assert np.array_equal(out3[keep], exp[keep])
+    # an empty call, and empty targets (ksw.c:409 never enters its loop: the score stays h0)
+    out4, status4, cells4 = HS.xs_static(opt, [], [], np.zeros(0, np.int32), np.zeros(0, np.int32))
+    assert status4 == 0 and len(out4) == 0 and cells4 == 0
+    out5, status5, _ = HS.xs_static(opt, qs[:40], [np.zeros(0, np.uint8)] * 40, h0[:40], w[:40])
+    exp5, _ = expect(qs[:40], [np.zeros(0, np.uint8)] * 40, h0[:40], w[:40], 5, 100)
+    assert status5 == 0 and np.array_equal(out5, exp5)
+
+
 @pytest.mark.parametrize("name,rfa", [("rand1m", 1), ("rep600k", 1), ("rep600k", 0), ("stlfr", 1)])
 def test_hostsim_shipped_placement_kernels(HS, workdir, name, rfa):
     """Rows a15-a20 on the code the GPU runs: csrc/place.cuh (candidates, tagBestAlignments with the device's Go PRNG, molecules, the

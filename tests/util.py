@@ -276,6 +276,21 @@ class HostSim:
         assert rc == 0, rc
         return out, cells.value
 
+    def xs_static(self, opt, qs, ts, h0, w, end_bonus=5, zdrop=100, max_qlen=None, warp=0):
+        """arachne_ksw_extend_static's launch sequence on the host (csrc/xs_kernels.cuh around k_ext_dp; hostsim_stages.cpp::hs_xs_static): the
+        scratch persists between calls as the static device array does.  -> (n x 6, status, in-band cells)."""
+        q, qo = pack(qs); t, to = pack(ts)
+        q, _ = u8p(np.concatenate([q, np.zeros(16, np.uint8)])); t, _ = u8p(np.concatenate([t, np.zeros(16, np.uint8)]))
+        h0 = np.ascontiguousarray(h0, dtype=np.int32); w = np.ascontiguousarray(w, dtype=np.int32)
+        n = len(qs); out = np.full((n + 1, 6), 12345, np.int32); cells = C.c_uint64(0); status = C.c_int32(77)
+        mq = max_qlen if max_qlen is not None else max([len(x) for x in qs] + [1])
+        self.lib.hs_xs_static.argtypes = [C.c_void_p, C.c_int64] + [C.c_void_p] * 6 + [C.c_int] * 4 + [C.c_void_p] * 3
+        rc = self.lib.hs_xs_static(C.addressof(opt), n, q.ctypes.data, qo.ctypes.data, t.ctypes.data, to.ctypes.data, h0.ctypes.data, w.ctypes.data, mq, end_bonus, zdrop, warp,
+                                   out.ctypes.data, C.addressof(status), C.addressof(cells))
+        assert rc == 0, rc
+        assert tuple(out[n]) == (12345,) * 6
+        return out[:n], status.value, cells.value
+
     def pair_warp(self, opt, r1, r2, regs1, regs2, score_delta=25, cap=512):
         """GoBwaMemMateSW's rescue on the device's own warp-cooperative context (csrc/warp_ctx.cuh) as one warp of fibers: the region lists
         of both reads after mem_align1_core in, the lists after rescue out."""
