@@ -101,10 +101,11 @@ with tempfile.TemporaryDirectory() as wd:
         # rows a6-a12 on the SHIPPED stage kernels in batch.inl's launch order (k_expand .. k_ext_dp on the packed reference .. k_rescue ..
         # k_gather_regs2 as blocks of fibers, tests/hostsim/hostsim_stages.cpp), fed with the intervals the shipped seeding kernel just produced
         st_rescue = bool(g.random() < 0.5); st_warp = int(g.integers(0, 4)); st_wide = bool(g.random() < 0.3)
-        sro, sregs, sinfo = HS.stages(OPT, seq, off, io, iv, rescue=st_rescue, warp=st_warp, wide=st_wide)
+        st_block = bool(g.random() < 0.5)  # the warp-cooperative kernels as whole blocks (their warps interleaving on the shared queue counters) or as one warp
+        sro, sregs, sinfo = HS.stages(OPT, seq, off, io, iv, rescue=st_rescue, warp=st_warp, wide=st_wide, block=st_block)
         want = ref if st_rescue else plain
         if not np.array_equal(sro, want["reg_off"]) or sregs.tobytes() != want["regs"].view(ALNREG).tobytes():
-            print(json.dumps(dict(divergence="staged kernels", seed=seed, rescue=st_rescue, warp=st_warp, wide=st_wide, **stats))); sys.exit(1)
+            print(json.dumps(dict(divergence="staged kernels", seed=seed, rescue=st_rescue, warp=st_warp, wide=st_wide, block=st_block, **stats))); sys.exit(1)
         stats["staged_reads"] += len(reads); stats["staged_dp_problems"] += sinfo["problems"]; stats["staged_rescued_pairs"] += sinfo["rescued"]
         # row a13 on the SHIPPED lane-per-region CIGAR tiers (csrc/cigar_kernel.cuh run one lane at a time, tests/hostsim/hostsim_cigar.cpp)
         t_alns, t_cig, t_mm, t_list3, t_cnt = HS.cigar_tiers(OPT, seq, off, ro, exp)

@@ -1,10 +1,12 @@
-// TEST-ONLY: one WARP of a kernel on the host, for kernels whose lanes cooperate (shuffles, ballots, warp reductions, one lane writing
-// another lane's shared-memory column between warp barriers: k_ext_dp).  The 32 lanes are 32 fibers (ucontext) of one host thread, each
-// with its own stack = its own registers; a collective (__shfl_sync, __ballot_sync, __reduce_max_sync, __syncwarp -- always with the full
-// mask in the kernels run here) is a rendezvous: a lane publishes its operand, yields until all 32 have arrived, and reads the others'.
-// Between collectives a lane runs alone, which is one of the interleavings the hardware allows; shared memory is ordinary memory, ordered
-// by the rendezvous exactly where the kernel has a barrier.  The order in which lanes run between two barriers is selectable (lane_order):
-// running the tests under more than one order catches a barrier missing before or after a leader's write; it is not a race detector.  g++ compiles the kernel source unchanged.  Never shipped.
+// TEST-ONLY: one WARP -- or one whole BLOCK of up to 8 warps -- of a kernel on the host, for kernels whose lanes cooperate (shuffles, ballots,
+// warp reductions, one lane writing another lane's shared-memory column between warp barriers: k_ext_dp).  Every lane is a fiber (ucontext) of
+// one host thread with its own stack = its own registers; a collective (__shfl_sync, __ballot_sync, __reduce_*_sync, __syncwarp -- always with
+// the full mask in the kernels run here -- and __syncthreads) is a rendezvous of its group, the lane's warp or the block: a lane publishes its
+// operand, yields until the whole group has arrived, and reads the others'.  Between collectives a lane runs alone, which is one of the
+// interleavings the hardware allows; shared memory is ordinary memory, ordered by the rendezvous exactly where the kernel has a barrier.  The
+// order in which lanes run between two barriers is selectable (lane_order): running the tests under more than one order catches a barrier
+// missing before or after a leader's write, and under run_block the warps of a block interleave at every collective (queue heads, pool
+// cursors and claim counters are then really shared).  It is not a race detector.  g++ compiles the kernel source unchanged.  Never shipped.
 #pragma once
 #include <ucontext.h>
 #include <cstdio>
@@ -17,17 +19,21 @@
 
 namespace warpsim {
 constexpr int W = 32;
-constexpr int MAXB = 256;  // run_block: a whole block of up to 256 lanes whose only collective is __syncthreads (k_ext_binbase)
+constexpr int MAXB = 256;  // run_block: a whole block of up to 256 lanes = 8 warps
 struct Lane { ucontext_t ctx; std::unique_ptr<char[]> stack; LaneIdx3 tid; bool done = false; };  // stacks are not zero-filled: only touched pages cost
-struct Warp {
+struct Group {                      // the lanes that meet in one kind of collective: a warp, or the whole block
+    unsigned long long xchg[2][MAXB];  // operands of collective number g live in xchg[g & 1]
+    long gen = 0;                   // collectives completed by all lanes of the group
+    int arrived = 0, size = 0;
+};
+struct Warp {                       // (a block of one or more warps)
     Lane lane[MAXB];
     int n = W;                      // lanes running
     ucontext_t sched;
     int cur = 0;
-    unsigned long long xchg[2][MAXB];  // operands of collective number g live in xchg[g & 1]
-    long gen = 0;                   // collectives completed by all lanes
-    int arrived = 0;
-    long lane_gen[MAXB];            // collectives each lane has entered
+    Group warp[MAXB / W], block;
+    long lane_gen[2][MAXB];         // collectives each lane has entered: [0] warp level, [1] block level
+    long progress = 0;              // rendezvous entered or completed, lanes finished: a pass without any is a deadlock
     std::function<void()> body;
 };
 inline Warp*& cur_warp() { static Warp* w = nullptr; return w; }
@@ -36,27 +42,32 @@ inline Warp*& cur_warp() { static Warp* w = nullptr; return w; }
 // three; one that leans on lock-step execution of a converged warp does not (hs_warp_order(), WARPSIM_ORDER).
 inline int& lane_order() { static int o = getenv("WARPSIM_ORDER") ? atoi(getenv("WARPSIM_ORDER")) : 0; return o; }
 inline void yield() { Warp* w = cur_warp(); swapcontext(&w->lane[w->cur].ctx, &w->sched); }
-// enter collective: publish v, wait for the others; returns the buffer holding this collective's operands
+// enter collective: publish v, wait for the others; returns the buffer holding this collective's operands (indexed by lane within the group)
 inline const unsigned long long* rendezvous(unsigned long long v, bool warp_level = true) {
     Warp* w = cur_warp();
     const int me = w->cur;
-    if (warp_level && w->n != W) { fprintf(stderr, "warpsim: warp collective inside run_block (only __syncthreads is emulated across warps)\n"); abort(); }
-    const long g = w->lane_gen[me]++;
-    if (g != w->gen) { fprintf(stderr, "warpsim: lane %d entered collective %ld while the warp is at %ld (divergent collective)\n", me, g, w->gen); abort(); }
-    w->xchg[g & 1][me] = v;
-    if (++w->arrived == w->n) { w->arrived = 0; ++w->gen; }
-    while (w->gen <= g) yield();
-    return w->xchg[g & 1];
+    Group& G = warp_level ? w->warp[me / W] : w->block;
+    const int idx = warp_level ? me % W : me;
+    const long g = w->lane_gen[warp_level ? 0 : 1][me]++;
+    if (g != G.gen) { fprintf(stderr, "warpsim: lane %d entered %s collective %ld while its group is at %ld (divergent collective)\n", me, warp_level ? "warp" : "block", g, G.gen); abort(); }
+    G.xchg[g & 1][idx] = v;
+    ++w->progress;
+    if (++G.arrived == G.size) { G.arrived = 0; ++G.gen; }
+    while (G.gen <= g) yield();
+    return G.xchg[g & 1];
 }
-inline void lane_entry() { Warp* w = cur_warp(); w->body(); w->lane[w->cur].done = true; yield(); }
+inline int lane_in_warp() { return cur_warp()->cur % W; }
+inline void lane_entry() { Warp* w = cur_warp(); w->body(); w->lane[w->cur].done = true; ++w->progress; yield(); }
 // run `body` as n lanes with threadIdx.x = first_tid .. first_tid + n - 1
 inline void run_lanes(unsigned first_tid, int n, size_t stack_bytes, const std::function<void()>& body) {
     Warp* w = new Warp();
     cur_warp() = w;
     w->body = body; w->n = n;
+    w->block.size = n;
+    for (int g = 0; g * W < n; ++g) w->warp[g].size = n - g * W < W ? n - g * W : W;
     for (int l = 0; l < n; ++l) {
         Lane& L = w->lane[l];
-        L.stack.reset(new char[stack_bytes]); L.tid.x = first_tid + (unsigned)l; w->lane_gen[l] = 0;
+        L.stack.reset(new char[stack_bytes]); L.tid.x = first_tid + (unsigned)l; w->lane_gen[0][l] = w->lane_gen[1][l] = 0;
         getcontext(&L.ctx);
         L.ctx.uc_stack.ss_sp = L.stack.get(); L.ctx.uc_stack.ss_size = stack_bytes; L.ctx.uc_link = &w->sched;
         makecontext(&L.ctx, lane_entry, 0);
@@ -78,19 +89,21 @@ inline void run_lanes(unsigned first_tid, int n, size_t stack_bytes, const std::
         }
         ++pass;
         if (!live) break;
-        int finished = 0;
-        for (int l = 0; l < n; ++l) finished += w->lane[l].done;
-        if (w->arrived > 0 && finished > 0 && w->arrived + finished == n) {
-            fprintf(stderr, "warpsim: %d lanes wait in a collective that the %d finished lanes will never enter\n", w->arrived, finished); abort();
+        if (w->progress == 0) {
+            int finished = 0;
+            for (int l = 0; l < n; ++l) finished += w->lane[l].done;
+            fprintf(stderr, "warpsim: deadlock: %d of %d lanes wait in collectives that the others (%d finished) will never enter\n", live, n, finished); abort();
         }
+        w->progress = 0;
     }
     cur_warp() = nullptr;
     delete w;
 }
 inline void run_warp(unsigned first_tid, const std::function<void()>& body) { run_lanes(first_tid, W, 1 << 20, body); }
-inline void run_block(int n_threads, const std::function<void()>& body) {
+// a whole block: warp collectives meet within each warp of 32, __syncthreads across all lanes; the warps interleave at every collective
+inline void run_block(int n_threads, const std::function<void()>& body, size_t stack_bytes = 1 << 17) {
     if (n_threads > MAXB) { fprintf(stderr, "warpsim: run_block of %d lanes\n", n_threads); abort(); }
-    run_lanes(0, n_threads, 1 << 17, body);
+    run_lanes(0, n_threads, stack_bytes, body);
 }
 }  // namespace warpsim
 
@@ -104,7 +117,7 @@ static LaneDim3 blockDim, gridDim;
 #endif
 
 inline void __syncwarp(unsigned = 0xffffffffu) { warpsim::rendezvous(0); }
-inline void __syncthreads() { warpsim::rendezvous(0, warpsim::cur_warp()->n == warpsim::W); }   // one warp per block (run_warp), or a whole block whose only collective this is (run_block)
+inline void __syncthreads() { warpsim::rendezvous(0, false); }   // all lanes that run: the warp under run_warp (a kernel of one warp per block, or whose warps never meet), the block under run_block
 inline unsigned __ballot_sync(unsigned, bool p) {
     const unsigned long long* x = warpsim::rendezvous(p ? 1u : 0u);
     unsigned m = 0;
@@ -135,7 +148,7 @@ inline unsigned __reduce_add_sync(unsigned, unsigned v) {
 template <class T> inline T __shfl_up_sync(unsigned, T v, unsigned delta) {  // lanes below delta keep their own value
     static_assert(sizeof(T) <= 8, "shuffle operand");
     unsigned long long raw = 0; memcpy(&raw, &v, sizeof(T));
-    const int me = warpsim::cur_warp()->cur;
+    const int me = warpsim::lane_in_warp();
     const unsigned long long* x = warpsim::rendezvous(raw);
     T out; memcpy(&out, &x[me >= (int)delta ? me - (int)delta : me], sizeof(T));
     return out;
@@ -149,7 +162,7 @@ inline int __reduce_min_sync(unsigned, int v) {
 template <class T> inline T __shfl_down_sync(unsigned, T v, unsigned delta) {  // lanes whose source is beyond the warp keep their own value
     static_assert(sizeof(T) <= 8, "shuffle operand");
     unsigned long long raw = 0; memcpy(&raw, &v, sizeof(T));
-    const int me = warpsim::cur_warp()->cur;
+    const int me = warpsim::lane_in_warp();
     const unsigned long long* x = warpsim::rendezvous(raw);
     T out; memcpy(&out, &x[me + (int)delta < warpsim::W ? me + (int)delta : me], sizeof(T));
     return out;

@@ -23,7 +23,7 @@ using namespace arachne;
 extern "C" {
 
 // n ksw_extend2 problems (byte targets, as the stage entry point takes them).  codec: 0 = chosen as the entry point chooses it, 1 = force the
-// 13-bit column codec.  warp: which of the block's four warps runs.  out: n x 6 {score, qle, tle, gtle, gscore, max_off}.
+// 13-bit column codec.  warp: which of the block's four warps runs; + 8: all four.  out: n x 6 {score, qle, tle, gtle, gscore, max_off}.
 int hs_ext_dp(const arachne_mem_opt_t* opt_, int64_t n, const uint8_t* q, const int64_t* q_off, const uint8_t* t, const int64_t* t_off, const int32_t* h0,
               const int32_t* w, int end_bonus, int zdrop, int codec, int warp, int32_t* out, uint64_t* cells) {
     static_assert(XDP_BLOCK == 128, "xcols is sized for 128 lanes");
@@ -52,8 +52,11 @@ int hs_ext_dp(const arachne_mem_opt_t* opt_, int64_t n, const uint8_t* q, const 
     RefView no_ref; memset(&no_ref, 0, sizeof(no_ref));
     memset(arachne::xcols, 0xcd, sizeof(arachne::xcols));
     blockIdx.x = 0; blockDim.x = XDP_BLOCK; gridDim.x = 1;
-    if (wide) warpsim::run_warp(32u * (unsigned)(warp & 3), [&] { k_ext_dp<false, true>(opt, no_ref, DA); });
-    else warpsim::run_warp(32u * (unsigned)(warp & 3), [&] { k_ext_dp<false, false>(opt, no_ref, DA); });
+    auto launch = [&](const std::function<void()>& f) {  // one of the block's four warps, or (bit 3 of warp) the whole block of four sharing the queue head
+        if (warp & 8) warpsim::run_block(XDP_BLOCK, f, 1 << 20); else warpsim::run_warp(32u * (unsigned)(warp & 3), f);
+    };
+    if (wide) launch([&] { k_ext_dp<false, true>(opt, no_ref, DA); });
+    else launch([&] { k_ext_dp<false, false>(opt, no_ref, DA); });
     for (int64_t i = 0; i < n; ++i) {
         const ExtRes& R = res[(size_t)i];
         int32_t* o = out + 6 * i;

@@ -32,6 +32,13 @@ template <class F> void warp(unsigned first_tid, unsigned block_dim, F&& f) {
     blockIdx.x = 0; blockDim.x = block_dim; gridDim.x = 1;
     warpsim::run_warp(first_tid, f);
 }
+// a warp-cooperative kernel either as ONE of its block's warps (slot = warp_id & 3; for a 256-thread block, one of the first four) or, with
+// bit 3 of warp_id set, as the WHOLE block: all its warps as fibers, interleaving at every collective and sharing the queue counters
+template <class F> void coop(int warp_id, unsigned block_dim, F&& f) {
+    blockIdx.x = 0; blockDim.x = block_dim; gridDim.x = 1;
+    if (warp_id & 8) warpsim::run_block((int)block_dim, f, 1 << 20);
+    else warpsim::run_warp(32u * (unsigned)(warp_id & 3), f);
+}
 }  // namespace
 
 extern "C" {
@@ -40,7 +47,8 @@ void hs_warp_order(int order) { warpsim::lane_order() = order; }  // one setting
 
 // intv: 4 u64 per SA interval {x0, x1, x2, info}, read r owns intv_off[r] .. intv_off[r + 1] (mem_collect_intv's output, sorted).
 // stages: 1 = regions of mem_align1_core, 3 = + mate rescue (reads 2p / 2p + 1 are a pair).  warp_id: bits 0-1 which of a block's four warps runs the
-// warp kernels, bit 2 forces k_ext_dp's 13-bit column codec (the pipeline takes it when a * max read length exceeds a byte).  regs_out / reg_off (n_reads + 1): the final lists.  info: {rounds, total_sa, dp problems, pairs rescued, err, err_read}.
+// warp kernels, bit 2 forces k_ext_dp's 13-bit column codec (the pipeline takes it when a * max read length exceeds a byte), bit 3 runs
+// the warp kernels as whole blocks (see coop above).  regs_out / reg_off (n_reads + 1): the final lists.  info: {rounds, total_sa, dp problems, pairs rescued, err, err_read}.
 int hs_stages(void* h, const arachne_mem_opt_t* opt_, int64_t n_reads_, const uint8_t* seq, const int64_t* off, const uint64_t* intv, const int64_t* intv_off_in,
               int stages, int score_delta, int warp_id, arachne_alnreg_t* regs_out, int64_t regs_cap, int64_t* reg_off_out, int64_t* info) {
     static_assert(XDP_BLOCK == 128, "xcols is sized for 128 lanes");
@@ -48,7 +56,6 @@ int hs_stages(void* h, const arachne_mem_opt_t* opt_, int64_t n_reads_, const ui
     const RefView ref = *static_cast<const RefView*>(hs_ref(h));
     const FMIndex fm = *static_cast<const FMIndex*>(hs_fm(h));
     const int n_reads = (int)n_reads_;
-    const unsigned wt = 32u * (unsigned)(warp_id & 3);
     int maxlen = 1, cap = 1;
     for (int r = 0; r < n_reads; ++r) {
         maxlen = std::max<int>(maxlen, (int)(off[r + 1] - off[r]));
@@ -83,7 +90,7 @@ int hs_stages(void* h, const arachne_mem_opt_t* opt_, int64_t n_reads_, const ui
     unsigned long long misc[8] = {0};
 
     warp(0, 32, [&] { k_expand(opt, n_reads, arena.data(), intv_off.data(), cap, intv_n.data(), sa_off.data(), rows.data()); });
-    warp(wt, 256, [&] { k_sa(fm, total_sa, rows.data(), &misc[0], &cnt); });
+    coop(warp_id, 256, [&] { k_sa(fm, total_sa, rows.data(), &misc[0], &cnt); });
     ChainBufs cb;
     cb.seeds = seeds.data(); cb.kseeds = kseeds.data(); cb.chains = chains.data(); cb.nodes = nodes.data();
     cb.order = order.data(); cb.kept = kept.data(); cb.n_chain = n_chain.data(); cb.n_kseed = n_kseed.data();
@@ -120,8 +127,8 @@ int hs_stages(void* h, const arachne_mem_opt_t* opt_, int64_t n_reads_, const ui
         warp(0, 32, [&] { k_ext_scatter(XB, round); });
         DA.queue = XB.queue_next;
         n_prob += ctl.n_next;
-        if (narrow) warp(wt, XDP_BLOCK, [&] { k_ext_dp<true, false>(opt, ref, DA); });
-        else warp(wt, XDP_BLOCK, [&] { k_ext_dp<true, true>(opt, ref, DA); });
+        if (narrow) coop(warp_id, XDP_BLOCK, [&] { k_ext_dp<true, false>(opt, ref, DA); });
+        else coop(warp_id, XDP_BLOCK, [&] { k_ext_dp<true, true>(opt, ref, DA); });
         warp(0, 1, [&] { if (threadIdx.x == 0) k_ext_roll(&ctl); });
         std::swap(XB.queue_cur, XB.queue_next);
         ++round;
@@ -141,7 +148,7 @@ int hs_stages(void* h, const arachne_mem_opt_t* opt_, int64_t n_reads_, const ui
         std::vector<uint8_t> win((size_t)EXT_WARPS * win_cap);
         std::vector<uint64_t> blists((size_t)EXT_WARPS * bcap);
         unsigned long long resc_used = 0; unsigned next = 0;
-        warp(wt, EXT_WARPS * 32, [&] {
+        coop(warp_id, EXT_WARPS * 32, [&] {
             k_rescue(opt, ref, score_delta, seq, off, n_pairs, sa_off.data(), regs.data(), n_regs.data(), reg_loc.data(), resc.data(), resc_cap, &resc_used,
                      win.data(), win_cap, blists.data(), bcap, &next, &cnt);
         });
@@ -179,7 +186,7 @@ int hs_k_cigar(void* h, const arachne_mem_opt_t* opt_, int64_t n_reads, const ui
     Counters cnt; memset(&cnt, 0, sizeof(cnt));
     unsigned long long used[2] = {0, 0}; unsigned next = 0;
     const unsigned nl = n_list;
-    warp(32u * (unsigned)(warp_id & 3), EXT_WARPS * 32, [&] {
+    coop(warp_id, EXT_WARPS * 32, [&] {
         k_cigar(opt, ref, seq, off, (long)n_regs, reinterpret_cast<const AlnReg*>(regs), reg_read, reinterpret_cast<AlnRec*>(alns), cig_pool, cig_cap, mm_pool, mm_cap,
                 used, win.data(), win_cap, zbuf.data(), z_cap, cig_scr.data(), cig_scr_cap, mm_scr.data(), mm_scr_cap, &next, &cnt, list, list ? &nl : nullptr);
     });
@@ -208,7 +215,7 @@ int hs_xs_static(const arachne_mem_opt_t* opt_, int64_t n, const uint8_t* q, con
     DA.ncols = max_qlen + 2; DA.zdrop = zdrop; DA.one = 1; DA.cnt = &ctl.cnt;
     RefView no_ref; memset(&no_ref, 0, sizeof(no_ref));
     memset(arachne::xcols, 0xcd, sizeof(arachne::xcols));
-    warp(32u * (unsigned)(warp_id & 3), XDP_BLOCK, [&] { k_ext_dp<false, true>(opt, no_ref, DA); });
+    coop(warp_id, XDP_BLOCK, [&] { k_ext_dp<false, true>(opt, no_ref, DA); });
     warp(0, 32, [&] { k_xs_finish(I, &ctl, res.data(), out, status, reinterpret_cast<unsigned long long*>(cells)); });
     return ctl.cnt.err;
 }

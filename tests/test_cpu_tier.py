@@ -343,7 +343,7 @@ def _check_cigar_tiers(HS, R, opt, reads, what):
     order = {"rep600k": 1, "len100": 2}.get(what, 0)  # the lanes' scheduling order differs between the read sets (0 is the one that exposed reg2aln's missing barrier, on len250)
     HS.lib.hs_warp_order(order)
     try:
-        kal, kcig, kmm = HS.k_cigar(opt, seq, off, ro, regs, lst, warp=len(reads) % 4)
+        kal, kcig, kmm = HS.k_cigar(opt, seq, off, ro, regs, lst, warp=len(reads) % 4, block=what != "len250")
     finally:
         HS.lib.hs_warp_order(0)
     for g in (int(x) for x in lst):
@@ -419,10 +419,12 @@ def test_hostsim_shipped_stage_kernels_in_launch_order(HS, workdir):
     full = R.batch(seq, off, rescue=True, cigar=False, threads=4)
     assert full["regs"].tobytes() != plain["regs"].tobytes(), "dataset does not exercise rescue"
     # each configuration under another scheduling order of the emulated lanes (ascending, descending, rotating, random: cuda_warp_shim.h)
-    for order, (rescue, warp, wide, exp) in zip((0, 1, 2, 7), ((False, 0, False, plain), (False, 2, True, plain), (True, 1, False, full), (True, 3, True, full))):
+    # ... and the warp-cooperative kernels either as one of their block's warps or as the whole block, its warps sharing the queue counters
+    for order, (rescue, warp, wide, block, exp) in zip((0, 1, 2, 7), ((False, 0, False, False, plain), (False, 2, True, True, plain), (True, 1, False, False, full),
+                                                                     (True, 3, True, True, full))):
         HS.lib.hs_warp_order(order)
         try:
-            ro, regs, info = HS.stages(opt, seq, off, io, flat, rescue=rescue, warp=warp, wide=wide)
+            ro, regs, info = HS.stages(opt, seq, off, io, flat, rescue=rescue, warp=warp, wide=wide, block=block)
         finally:
             HS.lib.hs_warp_order(0)
         assert np.array_equal(ro, exp["reg_off"]), (rescue, warp, wide)
@@ -448,7 +450,7 @@ def test_hostsim_shipped_extension_dp_kernel(HS, O):
             hh = h0; keep = list(range(len(qs)))
         q2 = [qs[i] for i in keep]; t2 = [ts[i] for i in keep]; h2 = hh[keep]; w2 = w[keep]
         for k, (zdrop, eb) in enumerate(((100, 5), (0, 0), (20, 5))):
-            out, cells = HS.ext_dp(opt, q2, t2, h2, w2, end_bonus=eb, zdrop=zdrop, codec=1 if codec == "wide" else 0, warp=k)
+            out, cells = HS.ext_dp(opt, q2, t2, h2, w2, end_bonus=eb, zdrop=zdrop, codec=1 if codec == "wide" else 0, warp=k + (8 if k == 2 else 0))  # k == 2: all four warps of the block
             tot = 0
             for i in range(len(q2)):
                 exp, c = util.orc_extend(O, q2[i], t2[i], int(w2[i]), eb, zdrop, int(h2[i]))
@@ -490,7 +492,7 @@ def test_hostsim_allocation_free_entry_kernels(HS, O):
     sel = list(range(len(qs) - 1, 0, -3))[:300]
     qs2 = [qs[i] for i in sel]; ts2 = [ts[i][: max(0, len(ts[i]) - 7)] for i in sel]; h2 = h0[sel]; w2 = np.maximum(1, w[sel] // 2).astype(np.int32)
     exp2, exp_cells2 = expect(qs2, ts2, h2, w2, 0, 20)
-    out2, status2, cells2 = HS.xs_static(opt, qs2, ts2, h2, w2, 0, 20, max_qlen=255, warp=2)
+    out2, status2, cells2 = HS.xs_static(opt, qs2, ts2, h2, w2, 0, 20, max_qlen=255, block=True)  # the whole block of four warps on one queue
     assert status2 == 0 and np.array_equal(out2, exp2) and cells2 == exp_cells2
     # refusals: h0 = 0 (ksw.c:385 asserts h0 > 0), a query longer than the declared bound, a score beyond the 13-bit codec; the lowest index is reported
     h_bad = h0.copy(); h_bad[17] = 0; h_bad[400] = 8191

@@ -215,10 +215,11 @@ class HostSim:
         assert rc == 0, rc
         return io, iv[:io[-1]], (int(st[0]), int(st[1]))
 
-    def stages(self, opt, seq, off, intv_off, intv, rescue=True, score_delta=25, warp=0, wide=False):
+    def stages(self, opt, seq, off, intv_off, intv, rescue=True, score_delta=25, warp=0, wide=False, block=False):
         """SA intervals -> final region lists through the shipped stage kernels in batch.inl's launch order (hostsim_stages.cpp): k_expand, k_sa,
         k_chain, the extension rounds (k_ext_drive / k_ext_binbase / k_ext_scatter / k_ext_dp on the packed reference / k_ext_roll),
-        k_ext_finish, k_init_loc, k_rescue, k_gather_regs2.  -> (reg_off [n + 1], regs, info dict)."""
+        k_ext_finish, k_init_loc, k_rescue, k_gather_regs2.  block: the warp-cooperative kernels as whole blocks (all warps as fibers sharing the queue counters) instead of one warp.
+        -> (reg_off [n + 1], regs, info dict)."""
         from arachne_b200.lib import ALNREG
         seq, sp = u8p(seq); off = np.ascontiguousarray(off, dtype=np.int64); n = len(off) - 1
         intv = np.ascontiguousarray(intv, dtype=np.uint64); intv_off = np.ascontiguousarray(intv_off, dtype=np.int64)
@@ -227,11 +228,11 @@ class HostSim:
         self.lib.hs_stages.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                        C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
         rc = self.lib.hs_stages(self.h, C.addressof(opt), n, seq.ctypes.data, off.ctypes.data, intv.ctypes.data, intv_off.ctypes.data, 3 if rescue else 1,
-                                score_delta, (warp & 3) | (4 if wide else 0), regs.ctypes.data, cap, ro.ctypes.data, info.ctypes.data)
+                                score_delta, (warp & 3) | (4 if wide else 0) | (8 if block else 0), regs.ctypes.data, cap, ro.ctypes.data, info.ctypes.data)
         assert rc == 0, (rc, info)
         return ro, regs[:ro[-1]].copy(), dict(rounds=int(info[0]), total_sa=int(info[1]), problems=int(info[2]), rescued=int(info[3]))
 
-    def k_cigar(self, opt, seq, off, reg_off, regs, list3=None, warp=0):
+    def k_cigar(self, opt, seq, off, reg_off, regs, list3=None, warp=0, block=False):
         """The shipped wide-band CIGAR kernel (k_cigar, csrc/pair_kernels.cuh) as a warp of fibers over the regions in list3 (None: all).
         -> (alns [n_regs] valid at the listed regions, cigar pool, mismatch pool)."""
         from arachne_b200.lib import ALN
@@ -244,7 +245,7 @@ class HostSim:
         self.lib.hs_k_cigar.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_int,
                                         C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p]
         rc = self.lib.hs_k_cigar(self.h, C.addressof(opt), n_reads, seq.ctypes.data, off.ctypes.data, n, regs.ctypes.data, reg_read.ctypes.data,
-                                 None if lst is None else lst.ctypes.data, 0 if lst is None else len(lst), warp, alns.ctypes.data, cig.ctypes.data, cig_cap,
+                                 None if lst is None else lst.ctypes.data, 0 if lst is None else len(lst), (warp & 3) | (8 if block else 0), alns.ctypes.data, cig.ctypes.data, cig_cap,
                                  mm.ctypes.data, mm_cap, used)
         assert rc == 0, rc
         return alns[:n], cig[:used[0]], mm[:used[1]]
@@ -276,7 +277,7 @@ class HostSim:
         assert rc == 0, rc
         return out, cells.value
 
-    def xs_static(self, opt, qs, ts, h0, w, end_bonus=5, zdrop=100, max_qlen=None, warp=0):
+    def xs_static(self, opt, qs, ts, h0, w, end_bonus=5, zdrop=100, max_qlen=None, warp=0, block=False):
         """arachne_ksw_extend_static's launch sequence on the host (csrc/xs_kernels.cuh around k_ext_dp; hostsim_stages.cpp::hs_xs_static): the
         scratch persists between calls as the static device array does.  -> (n x 6, status, in-band cells)."""
         q, qo = pack(qs); t, to = pack(ts)
@@ -285,7 +286,7 @@ class HostSim:
         n = len(qs); out = np.full((n + 1, 6), 12345, np.int32); cells = C.c_uint64(0); status = C.c_int32(77)
         mq = max_qlen if max_qlen is not None else max([len(x) for x in qs] + [1])
         self.lib.hs_xs_static.argtypes = [C.c_void_p, C.c_int64] + [C.c_void_p] * 6 + [C.c_int] * 4 + [C.c_void_p] * 3
-        rc = self.lib.hs_xs_static(C.addressof(opt), n, q.ctypes.data, qo.ctypes.data, t.ctypes.data, to.ctypes.data, h0.ctypes.data, w.ctypes.data, mq, end_bonus, zdrop, warp,
+        rc = self.lib.hs_xs_static(C.addressof(opt), n, q.ctypes.data, qo.ctypes.data, t.ctypes.data, to.ctypes.data, h0.ctypes.data, w.ctypes.data, mq, end_bonus, zdrop, (warp & 3) | (8 if block else 0),
                                    out.ctypes.data, C.addressof(status), C.addressof(cells))
         assert rc == 0, rc
         assert tuple(out[n]) == (12345,) * 6
