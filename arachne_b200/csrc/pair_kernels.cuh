@@ -132,4 +132,20 @@ __global__ void __launch_bounds__(EXT_WARPS * 32) k_cigar(MemOpt opt, RefView re
     }
 }
 
+// ------------------------------------------------------------------------------------------------ k_ksw_global (stage entry point arachne_ksw_global_batch)
+__global__ void __launch_bounds__(EXT_WARPS * 32) k_ksw_global(MemOpt opt, long n, const uint8_t* __restrict__ q, const int64_t* __restrict__ q_off,
+                                                               const uint8_t* __restrict__ t, const int64_t* __restrict__ t_off,
+                                                               const int* __restrict__ w, int* scores, uint8_t* zbuf, long z_cap,
+                                                               uint32_t* cig, int cig_cap, int* n_cig) {
+    const int lane = threadIdx.x & 31;
+    const long gw = (blockIdx.x * (long)blockDim.x + threadIdx.x) >> 5;
+    WarpCtx ctx; ctx.lane = lane; ctx.cells = nullptr; ctx.z = zbuf ? zbuf + gw * z_cap : nullptr; ctx.z_cap = z_cap;
+    for (long i = gw; i < n; i += ((long)gridDim.x * blockDim.x) >> 5) {
+        int qlen = (int)(q_off[i + 1] - q_off[i]), tlen = (int)(t_off[i + 1] - t_off[i]);
+        int nc = 0;
+        int sc = ctx.ksw_global(opt, qlen, q + q_off[i], 1, tlen, t + t_off[i], 1, w[i], cig ? cig + i * (long)cig_cap : nullptr, cig_cap, &nc);
+        if (lane == 0) { scores[i] = sc; if (n_cig) n_cig[i] = nc; }
+    }
+}
+
 }  // namespace arachne

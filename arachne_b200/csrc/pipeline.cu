@@ -76,26 +76,6 @@ __global__ void k_dpx_peak(int* out, int iters, int seed) {
     }
     if ((a0 ^ a1 ^ a2 ^ a3 ^ a4 ^ a5 ^ a6 ^ a7) == 0x7fffffff) out[0] = a0;
 }
-__global__ void k_occ(FMIndex fm, long n, const uint64_t* k, const uint64_t* l, uint64_t* cnt) {
-    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x)
-        fm_2occ4(fm, k[i], l[i], cnt + 8 * i, cnt + 8 * i + 4);
-}
-
-__global__ void __launch_bounds__(EXT_WARPS * 32) k_ksw_global(MemOpt opt, long n, const uint8_t* __restrict__ q, const int64_t* __restrict__ q_off,
-                                                               const uint8_t* __restrict__ t, const int64_t* __restrict__ t_off,
-                                                               const int* __restrict__ w, int* scores, uint8_t* zbuf, long z_cap,
-                                                               uint32_t* cig, int cig_cap, int* n_cig) {
-    const int lane = threadIdx.x & 31;
-    const long gw = (blockIdx.x * (long)blockDim.x + threadIdx.x) >> 5;
-    WarpCtx ctx; ctx.lane = lane; ctx.cells = nullptr; ctx.z = zbuf ? zbuf + gw * z_cap : nullptr; ctx.z_cap = z_cap;
-    for (long i = gw; i < n; i += ((long)gridDim.x * blockDim.x) >> 5) {
-        int qlen = (int)(q_off[i + 1] - q_off[i]), tlen = (int)(t_off[i + 1] - t_off[i]);
-        int nc = 0;
-        int sc = ctx.ksw_global(opt, qlen, q + q_off[i], 1, tlen, t + t_off[i], 1, w[i], cig ? cig + i * (long)cig_cap : nullptr, cig_cap, &nc);
-        if (lane == 0) { scores[i] = sc; if (n_cig) n_cig[i] = nc; }
-    }
-}
-
 // ------------------------------------------------------------------------------------------------ host side
 struct DevBuf {
     void* p = nullptr;

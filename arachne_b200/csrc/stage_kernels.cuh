@@ -107,4 +107,10 @@ __global__ void __launch_bounds__(128) k_chain(MemOpt opt, RefView ref, const in
     }
 }
 
+// ------------------------------------------------------------------------------------------------ k_occ (stage entry point arachne_occ_batch)
+__global__ void k_occ(FMIndex fm, long n, const uint64_t* k, const uint64_t* l, uint64_t* cnt) {
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x)
+        fm_2occ4(fm, k[i], l[i], cnt + 8 * i, cnt + 8 * i + 4);
+}
+
 }  // namespace arachne

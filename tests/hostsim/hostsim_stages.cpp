@@ -220,4 +220,28 @@ int hs_xs_static(const arachne_mem_opt_t* opt_, int64_t n, const uint8_t* q, con
     return ctl.cnt.err;
 }
 
+// The stage entry point arachne_ksw_global_batch's kernel (k_ksw_global: ksw_global2 with CIGAR on the warp context, a warp per problem), sized as
+// the entry sizes it: traceback slice = min(qlen, 2w + 1) x tlen, CIGAR slots = qlen + tlen + 2.  cig: n x cig_cap words, n_cig: n.
+int hs_k_ksw_global(const arachne_mem_opt_t* opt_, int64_t n, const uint8_t* q, const int64_t* q_off, const uint8_t* t, const int64_t* t_off, const int32_t* w,
+                    int warp_id, int32_t* scores, uint32_t* cig, int cig_cap, int32_t* n_cig) {
+    MemOpt opt; memcpy(&opt, opt_, sizeof(opt));
+    long zmax = 1;
+    for (int64_t i = 0; i < n; ++i) {
+        const long ql = q_off[i + 1] - q_off[i], tl = t_off[i + 1] - t_off[i];
+        if (ql > ARACHNE_MAX_READ_LEN || ql < 1 || cig_cap < ql + tl + 2) return ARACHNE_ERR_ARG;
+        zmax = std::max(zmax, std::min<long>(ql, 2L * w[i] + 1) * tl);
+    }
+    std::vector<uint8_t> zbuf((size_t)EXT_WARPS * zmax);
+    // the kernel deals problems out statically (problem i to warp i mod 4): either the whole block, or its four warps one after the other
+    for (int k = 0; k < ((warp_id & 8) ? 1 : EXT_WARPS); ++k)
+        coop((warp_id & 8) | ((warp_id + k) & 3), EXT_WARPS * 32, [&] { k_ksw_global(opt, (long)n, q, q_off, t, t_off, w, scores, zbuf.data(), zmax, cig, cig_cap, n_cig); });
+    return 0;
+}
+
+// arachne_occ_batch's kernel: bwt_2occ4 of n row pairs, 8 counts each
+void hs_k_occ(void* h, int64_t n, const uint64_t* k, const uint64_t* l, uint64_t* cnt) {
+    const FMIndex fm = *static_cast<const FMIndex*>(hs_fm(h));
+    warp(0, 32, [&] { k_occ(fm, (long)n, k, l, cnt); });
+}
+
 }  // extern "C"

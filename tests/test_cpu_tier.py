@@ -467,6 +467,37 @@ def test_hostsim_shipped_extension_dp_kernel(HS, O):
                 assert tuple(out[k]) == tuple(d["ext_out"][i]), ("edge", i, zd, eb, codec, tuple(out[k]), tuple(d["ext_out"][i]))
 
 
+def test_hostsim_stage_entry_kernels(HS, O, workdir):
+    """The kernels behind the stage entry points arachne_ksw_global_batch and arachne_occ_batch (k_ksw_global: ksw_global2 with CIGAR on the
+    warp context; k_occ: bwt_2occ4) on the host: the REFERENCE's scores and CIGARs on the global-alignment edge cases of
+    tests/golden/ksw_edge.npz, the oracle's on random problems (one warp and the whole block of four), occ counts of a golden index."""
+    from arachne_b200 import ArachneCuda
+    opt = ArachneCuda().opt
+    d = util.load_golden("ksw_edge")
+    pr = _problems(d, "glb"); co = d["glb_co"]
+    keep = [i for i in range(len(pr)) if 1 <= len(pr[i][0]) <= 255]
+    assert len(keep) >= 30
+    for block in (False, True):
+        sc, cigs = HS.k_ksw_global(opt, [pr[i][0] for i in keep], [pr[i][1] for i in keep], d["glb_w"][keep], warp=1, block=block)
+        for k, i in enumerate(keep):
+            assert sc[k] == d["glb_score"][i] and cigs[k] == list(d["glb_cig"][co[i]:co[i + 1]]), ("edge", i, block)
+    qs, ts, _h0, w = util.extension_problems(77, 240)
+    sel = [i for i in range(len(qs)) if len(ts[i]) > 0]
+    ww = np.array([max(abs(len(ts[i]) - len(qs[i])) + 3, int(w[i])) for i in sel], np.int32)
+    sc, cigs = HS.k_ksw_global(opt, [qs[i] for i in sel], [ts[i] for i in sel], ww, warp=2, block=True)
+    for k, i in enumerate(sel):
+        esc, ecig = util.orc_global(O, qs[i], ts[i], int(ww[k]))
+        assert sc[k] == esc and cigs[k] == ecig, ("random", i)
+    dg, prefix = util.load_golden("tiny_rep", workdir)
+    HS.load(prefix)
+    g = np.random.default_rng(4)
+    sl = 8 * (len(dg["idx_pac"]) - 1) - 8   # a little under 2 * l_pac, the BWT's length
+    ks = g.integers(0, sl, 300).astype(np.uint64); ls = np.minimum(ks + g.integers(0, 500, 300).astype(np.uint64), sl).astype(np.uint64)
+    got = HS.k_occ(ks, ls)
+    for i in range(len(ks)):
+        assert [int(x) for x in got[i]] == HS.occ(int(ks[i]), int(ls[i])), i
+
+
 def test_hostsim_allocation_free_entry_kernels(HS, O):
     """arachne_ksw_extend_static (include/arachne_cuda.h) without a GPU: its launch sequence -- control block cleared, k_xs_count, k_xs_base
     (block of 256), k_xs_queue, k_ext_dp<false, true>, k_xs_finish (csrc/xs_kernels.cuh, csrc/ext_stage.cuh) -- compiled for the host and run

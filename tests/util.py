@@ -292,6 +292,26 @@ class HostSim:
         assert tuple(out[n]) == (12345,) * 6
         return out[:n], status.value, cells.value
 
+    def k_ksw_global(self, opt, qs, ts, w, warp=0, block=False):
+        """arachne_ksw_global_batch's kernel (k_ksw_global: ksw_global2 + CIGAR on the warp context) as fibers.  -> (scores, list of CIGAR lists)."""
+        q, qo = pack(qs); t, to = pack(ts)
+        q, _ = u8p(np.concatenate([q, np.zeros(16, np.uint8)])); t, _ = u8p(np.concatenate([t, np.zeros(16, np.uint8)]))
+        w = np.ascontiguousarray(w, dtype=np.int32); n = len(qs)
+        cap = max([len(a) + len(b) + 2 for a, b in zip(qs, ts)] + [4])
+        sc = np.zeros(n + 1, np.int32); cig = np.zeros((n + 1, cap), np.uint32); nc = np.zeros(n + 1, np.int32)
+        self.lib.hs_k_ksw_global.argtypes = [C.c_void_p, C.c_int64] + [C.c_void_p] * 5 + [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        rc = self.lib.hs_k_ksw_global(C.addressof(opt), n, q.ctypes.data, qo.ctypes.data, t.ctypes.data, to.ctypes.data, w.ctypes.data, (warp & 3) | (8 if block else 0),
+                                      sc.ctypes.data, cig.ctypes.data, cap, nc.ctypes.data)
+        assert rc == 0, rc
+        return sc[:n], [list(int(x) for x in cig[i, :nc[i]]) for i in range(n)]
+
+    def k_occ(self, k, l):
+        """arachne_occ_batch's kernel (k_occ) on the host image.  -> [n, 8] counts."""
+        k = np.ascontiguousarray(k, dtype=np.uint64); l = np.ascontiguousarray(l, dtype=np.uint64); out = np.zeros((len(k), 8), np.uint64)
+        self.lib.hs_k_occ.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]; self.lib.hs_k_occ.restype = None
+        self.lib.hs_k_occ(self.h, len(k), k.ctypes.data, l.ctypes.data, out.ctypes.data)
+        return out
+
     def pair_warp(self, opt, r1, r2, regs1, regs2, score_delta=25, cap=512):
         """GoBwaMemMateSW's rescue on the device's own warp-cooperative context (csrc/warp_ctx.cuh) as one warp of fibers: the region lists
         of both reads after mem_align1_core in, the lists after rescue out."""
