@@ -2,11 +2,11 @@
 //
 // Stages of one batch (reads = 2 x pairs), every stage one or a few kernels over the whole batch:
 //   k_pack_reads, k_seed2, k_sort_intv   mem_collect_intv: SMEMs + re-seeding + LAST-like seeds -> SA intervals (seed_kernel.cuh)
-//   k_expand, k_sa                       one SA row per seed occurrence (bwamem.c:278-283), bwt_sa
-//   k_chain                              chaining, chain weights, chain filter (chain.cuh)
+//   k_expand, k_sa                       one SA row per seed occurrence (bwamem.c:278-283), bwt_sa (stage_kernels.cuh)
+//   k_chain                              chaining, chain weights, chain filter (chain.cuh; kernel in stage_kernels.cuh)
 //   k_ext_drive / k_ext_dp rounds        mem_chain2aln driver + ksw_extend2 as queues of uniform problems, region dedup (ext_stage.cuh)
-//   k_rescue                             mem_matesw as GoBwaMemMateSW drives it (rescue.cuh, warp_ctx.cuh)
-//   k_cigar_fast / _band / k_cigar       mem_reg2aln + the GetAlignments walk (cigar_kernel.cuh, cigar.cuh)
+//   k_rescue                             mem_matesw as GoBwaMemMateSW drives it (rescue.cuh, warp_ctx.cuh; kernel in pair_kernels.cuh)
+//   k_cigar_fast / _band / k_cigar       mem_reg2aln + the GetAlignments walk (cigar_kernel.cuh, cigar.cuh; k_cigar in pair_kernels.cuh)
 //   k_place_*                            tagBestAlignments .. optimizer .. MAPQ (place.cuh)
 // The index is read-only and shared; all per-batch state lives in a device workspace that is reused (batch.inl).
 #include <cuda_runtime.h>
